@@ -1,0 +1,161 @@
+// ORACLE (test infrastructure only) — warp-field geometry: anchors, LBS warp, unprojection,
+// point-to-plane, warped-surface Jacobians. See oracle_common.h for status.
+#include "oracle_common.h"
+
+using namespace oracle;
+
+// cpp/core/kernel/KnnUtilities.h:37-118 (brute-force KNN, replace-current-max, strict <,
+// first-max scan) + cpp/geometry/functional/kernel/WarpUtilities.h:35-247 (weights) +
+// cpp/geometry/functional/kernel/WarpAnchorComputationImpl.h:42-139 (plumbing).
+// node_weights == nullptr -> FixedNodeWeight with node_coverage; else VariableNodeWeight
+// (node_weights[n] is used directly as "node_coverage_squared", WarpUtilities.h:66).
+// minimum_valid_anchor_count > 0 selects the threshold variants
+// (cpp/geometry/functional/WarpAnchorComputation.cpp:74-148).
+ORACLE_API void oracle_compute_anchors_euclidean(
+		const float* points, int64_t point_count, const float* nodes, int node_count,
+		const float* node_weights, float node_coverage, int anchor_count, int minimum_valid_anchor_count,
+		int32_t* anchors, float* weights) {
+	const float fixed_c2 = node_coverage * node_coverage;
+	for (int64_t i = 0; i < point_count; i++) {
+		int32_t* idx = anchors + i * anchor_count;
+		float* w = weights + i * anchor_count;  // doubles as squared-distance scratch (WarpUtilities.h:190)
+		V3 p = load3(points + i * 3);
+		for (int a = 0; a < anchor_count; a++) { idx[a] = -1; w[a] = INFINITY; }
+		int max_at = 0;
+		float max_d2 = INFINITY;
+		for (int n = 0; n < node_count; n++) {
+			V3 d = sub(load3(nodes + n * 3), p);
+			float d2 = dot3(d, d);
+			if (d2 < max_d2) {
+				w[max_at] = d2;
+				idx[max_at] = n;
+				max_at = 0;
+				max_d2 = w[0];
+				for (int a = 1; a < anchor_count; a++) {
+					if (w[a] > max_d2) { max_at = a; max_d2 = w[a]; }
+				}
+			}
+		}
+		float weight_sum = 0.0f;
+		int valid = anchor_count;
+		if (minimum_valid_anchor_count > 0) {
+			valid = 0;
+			for (int a = 0; a < anchor_count; a++) {
+				float d2 = w[a];
+				float c2 = node_weights ? (idx[a] >= 0 ? node_weights[idx[a]] : fixed_c2) : fixed_c2;
+				if (d2 > 4 * c2) { idx[a] = -1; continue; }  // weight slot keeps d2 (reference leaves it)
+				float weight = expf(-d2 / (2 * c2));
+				weight_sum += weight;
+				w[a] = weight;
+				valid++;
+			}
+			if (valid < minimum_valid_anchor_count) continue;  // point rejected, no normalisation
+		} else {
+			for (int a = 0; a < anchor_count; a++) {
+				float d2 = w[a];
+				float c2 = node_weights ? (idx[a] >= 0 ? node_weights[idx[a]] : fixed_c2) : fixed_c2;
+				float weight = expf(-d2 / (2 * c2));
+				weight_sum += weight;
+				w[a] = weight;
+			}
+		}
+		// NormalizeAnchorWeights, WarpUtilities.h:35-46
+		if (weight_sum > 0.0f) {
+			for (int a = 0; a < anchor_count; a++) w[a] /= weight_sum;
+		} else if (valid > 0) {
+			for (int a = 0; a < anchor_count; a++) w[a] = 1.0f / (float) valid;
+		}
+	}
+}
+
+// cpp/geometry/functional/kernel/Warp3dPointsAndNormalsImpl.h:334-438 + BlendWarp
+// WarpUtilities.h:447-467 (+ :527-541 threshold variant). normals may be nullptr.
+// minimum_valid_anchor_count <= 0 -> no thresholding.
+ORACLE_API void oracle_warp_points_normals(
+		const float* points, const float* normals, int64_t point_count,
+		const float* nodes, const float* node_rotations, const float* node_translations,
+		const int32_t* anchors, const float* anchor_weights, int anchor_count, int minimum_valid_anchor_count,
+		const double* extrinsics44, float* warped_points, float* warped_normals) {
+	TransformIndexer transform(IDENTITY3, extrinsics44, 1.0f);
+	for (int64_t i = 0; i < point_count; i++) {
+		V3 pc, nc = {0, 0, 0};
+		transform.RigidTransform(points[i * 3], points[i * 3 + 1], points[i * 3 + 2], &pc.x, &pc.y, &pc.z);
+		if (normals) transform.Rotate(normals[i * 3], normals[i * 3 + 1], normals[i * 3 + 2], &nc.x, &nc.y, &nc.z);
+		V3 wp = {0, 0, 0}, wn = {0, 0, 0};
+		const int32_t* idx = anchors + i * anchor_count;
+		const float* w = anchor_weights + i * anchor_count;
+		bool do_warp = true;
+		if (minimum_valid_anchor_count > 0) {
+			int valid = 0;
+			for (int a = 0; a < anchor_count; a++) valid += (idx[a] != -1);
+			do_warp = valid >= minimum_valid_anchor_count;
+		}
+		if (do_warp) {
+			for (int a = 0; a < anchor_count; a++) {
+				int n = idx[a];
+				if (n == -1) continue;
+				float weight = w[a];
+				const float* R = node_rotations + n * 9;
+				V3 g = load3(nodes + n * 3);
+				V3 t = load3(node_translations + n * 3);
+				// warped_point += w * (node + R*(p - node) + t)
+				V3 rotated = matvec(R, sub(pc, g));
+				wp = add(wp, scale(weight, add(add(g, rotated), t)));
+				if (normals) wn = add(wn, scale(weight, matvec(R, nc)));
+			}
+		}
+		store3(warped_points + i * 3, wp);
+		if (normals && warped_normals) store3(warped_normals + i * 3, wn);
+	}
+}
+
+// cpp/geometry/functional/kernel/PerspectiveProjectionImpl.h:62-150.
+// depth is float32 [H,W]; pose = inverse(extrinsics) is computed by the caller in double
+// (Open3D InverseTransformation) and passed here as pose44.
+ORACLE_API void oracle_unproject_depth(
+		const float* depth, int rows, int cols, const double* intrinsics33, const double* pose44,
+		float depth_scale, float depth_max, float* points, uint8_t* mask) {
+	TransformIndexer transform(intrinsics33, pose44, 1.0f);
+	for (int64_t i = 0; i < (int64_t) rows * cols; i++) {
+		int64_t y = i / cols, x = i % cols;
+		float d = depth[i] / depth_scale;
+		float* out = points + i * 3;
+		out[0] = out[1] = out[2] = 0.f;
+		if (mask) mask[i] = 0;
+		if (d > 0 && d < depth_max) {
+			float xc, yc, zc;
+			transform.Unproject((float) x, (float) y, d, &xc, &yc, &zc);
+			transform.RigidTransform(xc, yc, zc, out, out + 1, out + 2);
+			if (mask) mask[i] = 1;
+		}
+	}
+}
+
+// cpp/geometry/functional/kernel/PointToPlaneDistancesImpl.h:25-52: n1 . (v1 - v2)
+ORACLE_API void oracle_point_to_plane_distances(
+		const float* normals1, const float* vertices1, const float* vertices2, int64_t count, float* distances) {
+	for (int64_t i = 0; i < count; i++) {
+		distances[i] = dot3(load3(normals1 + i * 3), sub(load3(vertices1 + i * 3), load3(vertices2 + i * 3)));
+	}
+}
+
+// cpp/alignment/functional/kernel/WarpedSurfaceJacobiansImpl.h:33-158 (TVertexRotationOnly=false).
+// out_position_jacobians [V,A,4] = (-w R (v - g), w); out_normal_jacobians [V,A,3] = -w R n.
+ORACLE_API void oracle_warped_surface_jacobians(
+		const float* vertex_positions, const float* vertex_normals, int64_t vertex_count,
+		const float* nodes, const float* node_rotations, const int32_t* anchors, const float* anchor_weights,
+		int anchor_count, float* out_position_jacobians, float* out_normal_jacobians) {
+	memset(out_position_jacobians, 0, sizeof(float) * vertex_count * anchor_count * 4);
+	memset(out_normal_jacobians, 0, sizeof(float) * vertex_count * anchor_count * 3);
+	for (int64_t wi = 0; wi < vertex_count * anchor_count; wi++) {
+		int64_t v = wi / anchor_count;
+		int n = anchors[wi];
+		if (n == -1) continue;
+		float w = anchor_weights[wi];
+		const float* R = node_rotations + n * 9;
+		V3 rv = matvec(R, sub(load3(vertex_positions + v * 3), load3(nodes + n * 3)));
+		store3(out_position_jacobians + wi * 4, scale(-w, rv));
+		out_position_jacobians[wi * 4 + 3] = w;
+		store3(out_normal_jacobians + wi * 3, scale(-w, matvec(R, load3(vertex_normals + v * 3))));
+	}
+}

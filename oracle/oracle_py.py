@@ -1,0 +1,316 @@
+"""ctypes/numpy bindings for the CPU oracle (TEST INFRASTRUCTURE ONLY).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module. The product package (dynamicfuion_python_b200) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+_REF = None
+
+MAX_ANCHOR_COUNT = 8
+
+
+def build(force=False):
+    """Compile liboracle.so (and oracle/_ref when /root/reference is present)."""
+    so = os.path.join(_HERE, "liboracle.so")
+    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith((".cpp", ".h"))]
+    stale = (not os.path.exists(so)) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
+    if force or stale:
+        subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
+    if os.path.isdir("/root/reference/cpp"):
+        subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(so):
+            build()
+        _LIB = C.CDLL(so)
+        _LIB.oracle_rasterize_ndc_triangles.restype = C.c_int64
+        _LIB.oracle_pixel_vertex_anchor_jacobians.restype = C.c_int64
+    return _LIB
+
+
+def ref_lib():
+    """The reference's own device-function headers compiled verbatim (None if not built)."""
+    global _REF
+    if _REF is None:
+        so = os.path.join(_HERE, "_ref", "libnnrt_ref.so")
+        if not os.path.exists(so):
+            return None
+        _REF = C.CDLL(so)
+    return _REF
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _i64(a):
+    return np.ascontiguousarray(a, dtype=np.int64)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def compute_anchors(points, nodes, anchor_count=4, min_valid=0, node_coverage=0.05, node_weights=None):
+    points, nodes = _f32(points), _f32(nodes)
+    nw = None if node_weights is None else _f32(node_weights)
+    V = points.shape[0]
+    anchors = np.empty((V, anchor_count), np.int32)
+    weights = np.empty((V, anchor_count), np.float32)
+    lib().oracle_compute_anchors_euclidean(_p(points), C.c_int64(V), _p(nodes), C.c_int(nodes.shape[0]), _p(nw),
+                                           C.c_float(node_coverage), C.c_int(anchor_count), C.c_int(min_valid),
+                                           _p(anchors), _p(weights))
+    return anchors, weights
+
+
+def warp(points, normals, nodes, rotations, translations, anchors, weights, extrinsics=None, min_valid=0):
+    points, normals = _f32(points), _f32(normals)
+    nodes, rotations, translations = _f32(nodes), _f32(rotations), _f32(translations)
+    anchors, weights = _i32(anchors), _f32(weights)
+    ext = _f64(np.eye(4) if extrinsics is None else extrinsics)
+    wp, wn = np.empty_like(points), np.empty_like(normals)
+    lib().oracle_warp_points_normals(_p(points), _p(normals), C.c_int64(points.shape[0]), _p(nodes), _p(rotations), _p(translations),
+                                     _p(anchors), _p(weights), C.c_int(anchors.shape[1]), C.c_int(min_valid), _p(ext), _p(wp), _p(wn))
+    return wp, wn
+
+
+def intrinsics_to_ndc(K, height, width):
+    K = _f64(K)
+    out = np.empty(9, np.float64)
+    rng = np.empty(4, np.float32)
+    lib().oracle_intrinsics_to_ndc(_p(K), C.c_int(height), C.c_int(width), _p(out), _p(rng))
+    return out.reshape(3, 3), rng
+
+
+def face_vertices_ndc(positions, triangles, K, height, width, near=0.0, far=float("inf")):
+    positions, triangles, K = _f32(positions), _i64(triangles), _f64(K)
+    F = triangles.shape[0]
+    out = np.empty((F, 3, 3), np.float32)
+    mask = np.empty(F, np.uint8)
+    lib().oracle_face_vertices_ndc(_p(positions), _p(triangles), C.c_int64(F), _p(K), C.c_int(height), C.c_int(width),
+                                   C.c_float(near), C.c_float(far), _p(out), _p(mask))
+    return out, mask.astype(bool)
+
+
+def rasterize(face_ndc, clip_mask, height, width, blur_radius_pixels=0.0, faces_per_pixel=8, bin_size=-1, max_faces_per_bin=-1,
+              perspective_correct=False, clip_barycentric=False, cull_back_faces=True, parallel=True):
+    face_ndc = _f32(face_ndc)
+    mask = None if clip_mask is None else np.ascontiguousarray(clip_mask, dtype=np.uint8)
+    K = faces_per_pixel
+    idx = np.empty((height, width, K), np.int64)
+    depth = np.empty((height, width, K), np.float32)
+    bary = np.empty((height, width, K, 3), np.float32)
+    dist = np.empty((height, width, K), np.float32)
+    dropped = lib().oracle_rasterize_ndc_triangles(
+        _p(face_ndc), _p(mask), C.c_int64(face_ndc.shape[0]), C.c_int(height), C.c_int(width), C.c_float(blur_radius_pixels),
+        C.c_int(K), C.c_int(bin_size), C.c_int(max_faces_per_bin), C.c_int(perspective_correct), C.c_int(clip_barycentric),
+        C.c_int(cull_back_faces), C.c_int(parallel), _p(idx), _p(depth), _p(bary), _p(dist))
+    return idx, depth, bary, dist, dropped
+
+
+def interpolate_vertex_attributes(pixel_faces, bary, face_attributes):
+    pixel_faces, bary, face_attributes = _i64(pixel_faces), _f32(bary), _f32(face_attributes)
+    H, W, K = pixel_faces.shape
+    Cn = face_attributes.shape[2]
+    out = np.empty((H, W, K, Cn), np.float32)
+    lib().oracle_interpolate_vertex_attributes(_p(pixel_faces), _p(bary), C.c_int64(H * W), C.c_int(K), _p(face_attributes), C.c_int(Cn), _p(out))
+    return out
+
+
+def unproject_depth(depth, K, extrinsics=None, depth_scale=1000.0, depth_max=3.0):
+    depth, K = _f32(depth), _f64(K)
+    ext = np.eye(4) if extrinsics is None else np.asarray(extrinsics, np.float64)
+    pose = _f64(np.linalg.inv(ext))
+    H, W = depth.shape[:2]
+    pts = np.empty((H * W, 3), np.float32)
+    mask = np.empty(H * W, np.uint8)
+    lib().oracle_unproject_depth(_p(depth), C.c_int(H), C.c_int(W), _p(K), _p(pose), C.c_float(depth_scale), C.c_float(depth_max), _p(pts), _p(mask))
+    return pts, mask.astype(bool)
+
+
+def point_to_plane(normals1, vertices1, vertices2):
+    n1, v1, v2 = _f32(normals1), _f32(vertices1), _f32(vertices2)
+    out = np.empty(v1.shape[0], np.float32)
+    lib().oracle_point_to_plane_distances(_p(n1), _p(v1), _p(v2), C.c_int64(v1.shape[0]), _p(out))
+    return out
+
+
+def warped_surface_jacobians(positions, normals, nodes, rotations, anchors, weights):
+    positions, normals, nodes, rotations = _f32(positions), _f32(normals), _f32(nodes), _f32(rotations)
+    anchors, weights = _i32(anchors), _f32(weights)
+    V, A = anchors.shape
+    jv = np.empty((V, A, 4), np.float32)
+    jn = np.empty((V, A, 3), np.float32)
+    lib().oracle_warped_surface_jacobians(_p(positions), _p(normals), C.c_int64(V), _p(nodes), _p(rotations), _p(anchors), _p(weights),
+                                          C.c_int(A), _p(jv), _p(jn))
+    return jv, jn
+
+
+def rasterized_surface_jacobians(wpos, wnrm, triangles, pixel_faces, bary, ndc_K, perspective_correct=True, parallel=True):
+    wpos, wnrm, triangles = _f32(wpos), _f32(wnrm), _i64(triangles)
+    pixel_faces, bary, ndc_K = _i64(pixel_faces), _f32(bary), _f64(ndc_K)
+    H, W, K = pixel_faces.shape
+    jv = np.empty((H, W, 3, 9), np.float32)
+    jn = np.empty((H, W, 3, 10), np.float32)
+    lib().oracle_rasterized_surface_jacobians(_p(wpos), _p(wnrm), _p(triangles), _p(pixel_faces), _p(bary), C.c_int(H), C.c_int(W), C.c_int(K),
+                                              _p(ndc_K), C.c_int(perspective_correct), C.c_int(parallel), _p(jv), _p(jn))
+    return jv, jn
+
+
+def associate_faces_with_anchors(triangles, anchors):
+    triangles, anchors = _i64(triangles), _i32(anchors)
+    F = triangles.shape[0]
+    fa = np.empty((F, 3 * MAX_ANCHOR_COUNT, 7), np.int32)
+    counts = np.empty(F, np.int32)
+    lib().oracle_associate_faces_with_anchors(_p(triangles), C.c_int64(F), _p(anchors), C.c_int(anchors.shape[1]), _p(fa), _p(counts))
+    return fa, counts
+
+
+def arap_terms(edges, nodes, rotations, translations, arap_weight, arrow_base, edge_layer_indices=None, layer_radii=None,
+               node_coverage_weights=None):
+    """Returns (edge_residuals [3E], edge_jacobians [E,5], diag [N,6,6], wing [E,6,6], wing_coords [E,2], g_arap [6N])."""
+    edges, nodes, rotations, translations = _i32(edges), _f32(nodes), _f32(rotations), _f32(translations)
+    E, N = edges.shape[0], nodes.shape[0]
+    eli = None if edge_layer_indices is None else np.ascontiguousarray(edge_layer_indices, np.int8)
+    radii = None if layer_radii is None else _f32(layer_radii)
+    ncw = None if node_coverage_weights is None else _f32(node_coverage_weights)
+    res = np.empty(3 * E, np.float32)
+    jac = np.empty((E, 5), np.float32)
+    lib().oracle_arap_residuals(_p(edges), C.c_int64(E), _p(eli), _p(radii), _p(ncw), _p(nodes), _p(translations), _p(rotations),
+                                C.c_float(arap_weight), _p(res))
+    lib().oracle_arap_edge_jacobians(_p(edges), C.c_int64(E), _p(eli), _p(radii), _p(ncw), _p(nodes), _p(rotations), C.c_float(arap_weight), _p(jac))
+    diag = np.empty((N, 6, 6), np.float32)
+    wing = np.empty((E, 6, 6), np.float32)
+    coords = np.empty((E, 2), np.int32)
+    rc = lib().oracle_arap_hessian(_p(edges), C.c_int64(E), _p(jac), C.c_int(arrow_base), C.c_int(N), _p(diag), _p(wing), _p(coords))
+    if rc != 0:
+        raise ValueError("edge outside the defined regime i < arrow_base <= j")
+    g = np.empty(6 * N, np.float32)
+    lib().oracle_negative_arap_gradient(_p(res), _p(jac), _p(edges), C.c_int64(E), C.c_int(N), _p(g))
+    return res, jac, diag, wing, coords, g
+
+
+def solve_block_diagonal(blocks, b):
+    blocks, b = _f32(blocks), _f32(b)
+    n, s = blocks.shape[0], blocks.shape[1]
+    x = np.empty(n * s, np.float32)
+    fails = lib().oracle_solve_block_diagonal_cholesky(_p(blocks), _p(b), C.c_int(n), C.c_int(s), _p(x))
+    return x, fails
+
+
+def schur_complement(diag, arrow_base, wing, wing_coords, corner_upper=None, corner_upper_coords=None):
+    diag, wing, wing_coords = _f32(diag), _f32(wing), _i32(wing_coords)
+    N = diag.shape[0]
+    n = (N - arrow_base) * 6
+    cu = None if corner_upper is None else _f32(corner_upper)
+    cuc = None if corner_upper_coords is None else _i32(corner_upper_coords)
+    ncu = 0 if cu is None else cu.shape[0]
+    S = np.empty((n, n), np.float32)
+    lib().oracle_arrowhead_schur_complement(_p(diag), C.c_int(N), C.c_int(arrow_base), _p(wing), _p(wing_coords), C.c_int64(wing.shape[0]),
+                                            _p(cu), _p(cuc), C.c_int64(ncu), _p(S), None, None)
+    return S
+
+
+def solve_arrowhead(diag, arrow_base, wing, wing_coords, b, corner_upper=None, corner_upper_coords=None):
+    diag, wing, wing_coords, b = _f32(diag), _f32(wing), _i32(wing_coords), _f32(b)
+    N = diag.shape[0]
+    cu = None if corner_upper is None else _f32(corner_upper)
+    cuc = None if corner_upper_coords is None else _i32(corner_upper_coords)
+    ncu = 0 if cu is None else cu.shape[0]
+    x = np.empty(6 * N, np.float32)
+    fails = lib().oracle_solve_arrowhead_cholesky(_p(diag), C.c_int(N), C.c_int(arrow_base), _p(wing), _p(wing_coords), C.c_int64(wing.shape[0]),
+                                                  _p(cu), _p(cuc), C.c_int64(ncu), _p(b), _p(x))
+    return x, fails
+
+
+def rodrigues(vectors):
+    v = _f32(vectors)
+    out = np.empty((v.shape[0], 3, 3), np.float32)
+    lib().oracle_rodrigues(_p(v), C.c_int(v.shape[0]), _p(out))
+    return out
+
+
+class _FitParams(C.Structure):
+    _fields_ = [
+        ("vertex_positions", C.c_void_p), ("vertex_normals", C.c_void_p), ("triangles", C.c_void_p),
+        ("vertex_count", C.c_int64), ("face_count", C.c_int64),
+        ("nodes", C.c_void_p), ("node_count", C.c_int32), ("edges", C.c_void_p), ("edge_count", C.c_int64), ("arrow_base", C.c_int32),
+        ("edge_layer_indices", C.c_void_p), ("layer_decimation_radii", C.c_void_p), ("node_coverage_weights", C.c_void_p),
+        ("anchors", C.c_void_p), ("anchor_weights", C.c_void_p), ("anchor_count", C.c_int32),
+        ("reference_points", C.c_void_p), ("reference_mask", C.c_void_p), ("height", C.c_int32), ("width", C.c_int32),
+        ("intrinsics", C.c_void_p), ("extrinsics", C.c_void_p),
+        ("iteration_count", C.c_int32), ("use_perspective_correction", C.c_int32), ("max_depth", C.c_float),
+        ("use_tukey", C.c_int32), ("tukey_cutoff", C.c_float), ("levenberg_marquardt_factor", C.c_float),
+        ("arap_term_weight", C.c_float), ("use_huber", C.c_int32), ("huber_constant", C.c_float),
+        ("max_pixels_per_node", C.c_int32), ("parallel", C.c_int32),
+        ("node_rotations", C.c_void_p), ("node_translations", C.c_void_p),
+        ("trace_hessian_diag", C.c_void_p), ("trace_negative_gradient", C.c_void_p), ("trace_deltas", C.c_void_p),
+        ("last_pixel_faces", C.c_void_p), ("last_residuals", C.c_void_p), ("last_residual_mask", C.c_void_p),
+        ("stage_seconds", C.c_void_p),
+    ]
+
+
+def fit_to_image(positions, normals, triangles, nodes, edges, arrow_base, anchors, anchor_weights, reference_points, reference_mask,
+                 height, width, K, extrinsics=None, rotations=None, translations=None, iteration_count=10,
+                 use_perspective_correction=True, max_depth=10.0, use_tukey=False, tukey_cutoff=0.01, lm_factor=0.0,
+                 arap_term_weight=200.0, use_huber=False, huber_constant=1e-4, edge_layer_indices=None, layer_radii=None,
+                 node_coverage_weights=None, max_pixels_per_node=0, parallel=False, trace=True):
+    """The reference GN loop on the CPU. Returns dict with final rotations/translations and per-iteration traces."""
+    positions, normals, triangles = _f32(positions), _f32(normals), _i64(triangles)
+    nodes = _f32(nodes)
+    N = nodes.shape[0]
+    edges = np.zeros((0, 2), np.int32) if edges is None else _i32(edges)
+    anchors, anchor_weights = _i32(anchors), _f32(anchor_weights)
+    ref_pts = _f32(reference_points).reshape(-1, 3)
+    ref_mask = np.ascontiguousarray(reference_mask, np.uint8).reshape(-1)
+    Kd = _f64(K)
+    ext = _f64(np.eye(4) if extrinsics is None else extrinsics)
+    R = _f32(np.tile(np.eye(3, dtype=np.float32), (N, 1, 1)) if rotations is None else rotations).copy()
+    t = _f32(np.zeros((N, 3), np.float32) if translations is None else translations).copy()
+    eli = None if edge_layer_indices is None else np.ascontiguousarray(edge_layer_indices, np.int8)
+    radii = None if layer_radii is None else _f32(layer_radii)
+    ncw = None if node_coverage_weights is None else _f32(node_coverage_weights)
+    if edges.shape[0] > 0 and eli is None and ncw is None:
+        raise ValueError("edges need edge_layer_indices+layer_radii or node_coverage_weights")
+    PX = height * width
+    tr_H = np.zeros((iteration_count, N, 6, 6), np.float32) if trace else None
+    tr_g = np.zeros((iteration_count, N, 6), np.float32) if trace else None
+    tr_d = np.zeros((iteration_count, N, 6), np.float32) if trace else None
+    last_faces = np.empty(PX, np.int64)
+    last_res = np.empty(PX, np.float32)
+    last_mask = np.empty(PX, np.uint8)
+    stage = np.zeros(8, np.float64)
+    p = _FitParams(
+        _p(positions), _p(normals), _p(triangles), positions.shape[0], triangles.shape[0],
+        _p(nodes), N, _p(edges), edges.shape[0], arrow_base, _p(eli), _p(radii), _p(ncw),
+        _p(anchors), _p(anchor_weights), anchors.shape[1],
+        _p(ref_pts), _p(ref_mask), height, width, _p(Kd), _p(ext),
+        iteration_count, int(use_perspective_correction), max_depth, int(use_tukey), tukey_cutoff, lm_factor,
+        arap_term_weight, int(use_huber), huber_constant, max_pixels_per_node, int(parallel),
+        _p(R), _p(t), _p(tr_H), _p(tr_g), _p(tr_d), _p(last_faces), _p(last_res), _p(last_mask), _p(stage))
+    rc = lib().oracle_fit_to_image(C.byref(p))
+    if rc != 0:
+        raise RuntimeError(f"oracle_fit_to_image failed: {rc}")
+    return dict(rotations=R, translations=t, hessian_diag=tr_H, negative_gradient=tr_g, deltas=tr_d,
+                pixel_faces=last_faces.reshape(height, width), residuals=last_res.reshape(height, width),
+                residual_mask=last_mask.reshape(height, width).astype(bool), stage_seconds=stage)

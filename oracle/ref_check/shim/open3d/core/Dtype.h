@@ -1,0 +1,2 @@
+#pragma once
+#include <open3d/core/Tensor.h>
