@@ -1,0 +1,78 @@
+"""ctypes binding of libnnrt_b200.so (include/nnrt_b200.h). There is no CPU fallback: if the CUDA library is missing
+or fails to load, importing the product path raises."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libnnrt_b200.so")
+
+P, I32, I64, F32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+
+_SIGNATURES = {
+    "nnrt_b200_version": (C.c_int, []),
+    "nnrt_b200_last_error": (C.c_char_p, []),
+    "nnrt_b200_compute_anchors_euclidean": (C.c_int, [P, I64, P, I32, P, F32, I32, I32, P, P, P]),
+    "nnrt_b200_warp_points_normals": (C.c_int, [P, P, I64, P, P, P, I32, P, P, I32, I32, P, P, P, P]),
+    "nnrt_b200_face_vertices_ndc": (C.c_int, [P, I64, P, I64, P, I32, I32, F32, F32, P, P, P]),
+    "nnrt_b200_rasterize_ndc_triangles": (C.c_int, [P, P, I64, I32, I32, F32, I32, I32, I32, I32, I32, I32, P, P, P, P, P]),
+    "nnrt_b200_interpolate_vertex_attributes": (C.c_int, [P, P, I64, I32, P, I32, P, P]),
+    "nnrt_b200_unproject_depth": (C.c_int, [P, I32, I32, I32, P, P, F32, F32, P, P, P]),
+    "nnrt_b200_point_to_plane_distances": (C.c_int, [P, P, P, I64, P, P]),
+    "nnrt_b200_warped_surface_jacobians": (C.c_int, [P, P, I64, P, P, P, P, I32, P, P, P]),
+    "nnrt_b200_rasterized_surface_jacobians": (C.c_int, [P, P, P, P, P, I32, I32, I32, P, I32, P, P, P]),
+    "nnrt_b200_associate_faces_with_anchors": (C.c_int, [P, I64, P, I32, P, P, P]),
+    "nnrt_b200_solve_block_sparse_arrowhead_cholesky": (C.c_int, [P, I32, I32, P, P, I64, P, P, I64, P, P, P]),
+    "nnrt_b200_arrowhead_schur_complement": (C.c_int, [P, I32, I32, P, P, I64, P, P, I64, P, P]),
+    "nnrt_b200_solve_block_diagonal_cholesky": (C.c_int, [P, P, I32, I32, P, P]),
+    "nnrt_b200_precondition_diagonal_blocks": (C.c_int, [P, I32, I32, F32, P]),
+    "nnrt_b200_rodrigues": (C.c_int, [P, I32, P, P]),
+    "nnrt_b200_matmul3d_3x3": (C.c_int, [P, P, I32, P, P]),
+    "nnrt_b200_fitter_default_options": (None, [P]),
+    "nnrt_b200_fitter_create": (C.c_int, [P, I64, I64, I32, I64, I32, I32, I32, P]),
+    "nnrt_b200_fitter_destroy": (None, [P]),
+    "nnrt_b200_fitter_workspace_bytes": (I64, [P]),
+    "nnrt_b200_fitter_set_model": (C.c_int, [P, P, P, P, P, P, I32, P, P, I32, P, P, P, P]),
+    "nnrt_b200_fitter_set_reference_points": (C.c_int, [P, P, P, P]),
+    "nnrt_b200_fitter_set_reference_depth": (C.c_int, [P, P, I32, P, F32, P, P]),
+    "nnrt_b200_fitter_fit": (C.c_int, [P, P, P, P, P, I32, P]),
+    "nnrt_b200_fitter_status": (C.c_int, [P, P]),
+    "nnrt_b200_fitter_get_diagnostics": (C.c_int, [P, P, P, P, P, P, P, P]),
+    "nnrt_b200_fitter_launches_per_iteration": (I32, [P]),
+    "nnrt_b200_fitter_profile_iteration": (C.c_int, [P, P, P, P, P, P, P]),
+}
+
+
+class FitterOptions(C.Structure):
+    _fields_ = [("max_iteration_count", I32), ("use_perspective_correction", I32), ("max_depth", F32), ("use_tukey_penalty", I32),
+                ("tukey_penalty_cutoff", F32), ("preconditioning_dampening_factor", F32), ("arap_term_weight", F32),
+                ("use_huber_penalty", I32), ("huber_penalty_constant", F32)]
+
+
+_lib = None
+
+
+def exported_symbols():
+    return sorted(_SIGNATURES)
+
+
+def lib():
+    """Loads the CUDA library; raises if it is missing (no fallback path exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} not found: build it with `python -m dynamicfuion_python_b200.build` "
+                               "(or __graft_entry__.build()); this package has no CPU fallback")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def check(rc):
+    """LogError semantics of the reference: a failing call raises RuntimeError with the library's message."""
+    if rc != 0:
+        msg = lib().nnrt_b200_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"nnrt_b200 error {rc}: {msg}")

@@ -1,0 +1,561 @@
+// Host class behind the C ABI of nnrt::alignment::DeformableMeshToImageFitter
+// (cpp/alignment/DeformableMeshToImageFitter.h:30-126, .cpp:56-329): a workspace sized once per problem shape, once-per-fit
+// re-layout of the inputs into 128-bit SoA records, and the GN/LM loop issued as one CUDA graph (7 kernels / iteration,
+// no allocation, no host sync inside the loop).
+#include <vector>
+#include <cstring>
+#include "fitter_kernels.cuh"
+#include "solver_kernels.cuh"
+#include "../../include/nnrt_b200.h"
+
+namespace nnrt_b200 {
+
+// ---- once-per-fit layout kernels -------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) pack_float4_kernel(const float* __restrict__ src, int64_t n, float4* __restrict__ dst) {
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) dst[i] = make_float4(src[i * 3], src[i * 3 + 1], src[i * 3 + 2], 0.f);
+}
+__global__ void __launch_bounds__(256) pack_triangles_kernel(const int64_t* __restrict__ src, int64_t n, int4* __restrict__ dst) {
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) dst[i] = make_int4((int) src[i * 3], (int) src[i * 3 + 1], (int) src[i * 3 + 2], 0);
+}
+__global__ void __launch_bounds__(256) pack_reference_kernel(const float* __restrict__ points, const uint8_t* __restrict__ mask, int64_t n,
+                                                              float4* __restrict__ dst) {
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) dst[i] = make_float4(points[i * 3], points[i * 3 + 1], points[i * 3 + 2], (mask == nullptr || mask[i]) ? 1.f : 0.f);
+}
+template<typename TDepth>
+__global__ void __launch_bounds__(256) reference_from_depth_kernel(const TDepth* __restrict__ depth, const uint8_t* __restrict__ user_mask,
+                                                                    int rows, int cols, Intrinsics k, float depth_scale, float depth_max,
+                                                                    float4* __restrict__ dst) {
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= (int64_t) rows * cols) return;
+	const int y = (int) (i / cols), x = (int) (i % cols);
+	const float d = (float) depth[i] / depth_scale;
+	float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
+	if (d > 0 && d < depth_max) {
+		out = make_float4(((float) x - k.cx) * d / k.fx, ((float) y - k.cy) * d / k.fy, d, 1.f);
+		if (user_mask && !user_mask[i]) out.w = 0.f;
+	}
+	dst[i] = out;
+}
+// compact AssociateFacesWithAnchors (cpp/alignment/functional/kernel/AssociateFacesWithAnchorsImpl.h:69-106)
+__global__ void __launch_bounds__(256) face_anchor_table_kernel(const int4* __restrict__ triangles, int64_t face_count,
+                                                                 const int32_t* __restrict__ anchors, int anchor_count,
+                                                                 int2* __restrict__ entries, uint8_t* __restrict__ counts) {
+	const int64_t f = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (f >= face_count) return;
+	const int max_entries = 3 * anchor_count;
+	int2* e = entries + f * max_entries;
+	const int4 tri = triangles[f];
+	int count = 0;
+	for (int fv = 0; fv < 3; fv++) {
+		const int vi = fv == 0 ? tri.x : fv == 1 ? tri.y : tri.z;
+		for (int a = 0; a < anchor_count; a++) {
+			const int node = anchors[(int64_t) vi * anchor_count + a];
+			if (node == -1) continue;
+			int k = 0;
+			while (k < count && e[k].x != node) k++;
+			if (k == count) { e[k] = make_int2(node, (int) 0xFFFFFFFF); count++; }
+			const unsigned packed = (unsigned) e[k].y;
+			e[k].y = (int) ((packed & ~(0xFFu << (8 * fv))) | ((unsigned) a << (8 * fv)));
+		}
+	}
+	for (int k = count; k < max_entries; k++) e[k] = make_int2(-1, (int) 0xFFFFFFFF);
+	counts[f] = (uint8_t) count;
+}
+
+// ---- per-iteration: ARAP term + data term -> block-sparse arrowhead system ---------------------------------------
+struct GraphDeviceData {
+	const float* nodes; int node_count; int arrow_base;
+	const int2* edges; int edge_count;
+	const float* edge_weight_residual;  // lambda-free edge weight used by the residual (radii[layer[node_j]] or max coverage)
+	const float* edge_weight_jacobian;  // edge weight used by the Jacobian (radii[layer[edge]] or max coverage)
+	const int* out_offsets; const int* out_edges;  // CSR: edges by stem node i (== wing rows)
+	const int* in_offsets; const int* in_edges;    // CSR: edges by corner node j
+	float arap_weight; float lm_factor; int use_huber; float huber_constant;
+};
+
+__device__ __forceinline__ void arap_edge(const GraphDeviceData& g, const float* __restrict__ rotations, const float* __restrict__ translations,
+                                          int e, float3& s, float& a, float3& residual) {
+	const int2 ij = g.edges[e];
+	const float3 gi = make_float3(g.nodes[ij.x * 3], g.nodes[ij.x * 3 + 1], g.nodes[ij.x * 3 + 2]);
+	const float3 gj = make_float3(g.nodes[ij.y * 3], g.nodes[ij.y * 3 + 1], g.nodes[ij.y * 3 + 2]);
+	const float3 ti = make_float3(translations[ij.x * 3], translations[ij.x * 3 + 1], translations[ij.x * 3 + 2]);
+	const float3 tj = make_float3(translations[ij.y * 3], translations[ij.y * 3 + 1], translations[ij.y * 3 + 2]);
+	float R[9];
+#pragma unroll
+	for (int k = 0; k < 9; k++) R[k] = rotations[ij.x * 9 + k];
+	const float3 rd = matvec3(R, gi - gj);
+	const float wj = g.edge_weight_jacobian[e], wr = g.edge_weight_residual[e];
+	a = g.arap_weight * wj;                       // dE_i/dt_i = +a I, dE_j/dt_j = -a I   (ArapJacobianImpl.h:74-110)
+	s = (-g.arap_weight * wj) * rd;               // dense rotation Jacobian, used as a skew generator
+	residual = (g.arap_weight * wr) * (((gi + ti) - (gj + tj)) - rd);  // DeformableMeshToImageFitterImpl.h:697-713
+	if (g.use_huber) {                            // DeformableMeshToImageFitter.cpp:435-444
+		const float dl = g.huber_constant, half = 0.5f * dl * dl;
+		residual.x = residual.x >= dl ? fabsf(residual.x) - half : 0.5f * residual.x * residual.x;
+		residual.y = residual.y >= dl ? fabsf(residual.y) - half : 0.5f * residual.y * residual.y;
+		residual.z = residual.z >= dl ? fabsf(residual.z) - half : 0.5f * residual.z * residual.z;
+	}
+}
+
+// One thread per node: D_n = J_d^T J_d (from the pixel accumulators) + sum of ARAP blocks + lambda I, b_n = -J^T r, and the
+// wing blocks B_e = dE_i^T dE_j of the node's outgoing edges (ArapHessianImpl.h:117-189, ComputeNegativeArapGradient
+// DeformableMeshToImageFitterImpl.h:496-540, PreconditionDiagonalBlocksImpl.h). Replaces 8 launches + float atomics.
+__global__ void __launch_bounds__(128) build_system_kernel(GraphDeviceData g, const float* __restrict__ rotations,
+                                                            const float* __restrict__ translations, float* __restrict__ accumulators,
+                                                            float* __restrict__ diag, float* __restrict__ rhs, float* __restrict__ wing) {
+	const int n = blockIdx.x * blockDim.x + threadIdx.x;
+	if (n >= g.node_count) return;
+	float H[36], b[6];
+	float* acc = accumulators + (int64_t) n * kAccumStride;
+	{
+		int o = 0;
+#pragma unroll
+		for (int c0 = 0; c0 < 6; c0++)
+#pragma unroll
+			for (int c1 = c0; c1 < 6; c1++) { const float v = acc[o++]; H[c0 * 6 + c1] = v; H[c1 * 6 + c0] = v; }
+#pragma unroll
+		for (int c = 0; c < 6; c++) b[c] = 0.f - acc[21 + c];
+#pragma unroll
+		for (int k = 0; k < 27; k++) acc[k] = 0.f;  // clean for the next iteration's assembly
+	}
+	if (g.edge_count > 0) {
+		if (n < g.arrow_base) {
+			for (int q = g.out_offsets[n]; q < g.out_offsets[n + 1]; q++) {
+				const int e = g.out_edges[q];
+				float3 s, r; float a;
+				arap_edge(g, rotations, translations, e, s, a, r);
+				// dE_i = [S | a I] with S = skew(s); dE_j = [0 | -a I]
+				const float S[9] = {0.f, -s.z, s.y, s.z, 0.f, -s.x, -s.y, s.x, 0.f};
+				float dEi[18];
+#pragma unroll
+				for (int rr = 0; rr < 3; rr++)
+#pragma unroll
+					for (int c = 0; c < 3; c++) { dEi[rr * 6 + c] = S[rr * 3 + c]; dEi[rr * 6 + 3 + c] = rr == c ? a : 0.f; }
+				float* B = wing + (int64_t) e * 36;
+				const float bj = -a;
+#pragma unroll
+				for (int rr = 0; rr < 6; rr++)
+#pragma unroll
+					for (int c = 0; c < 6; c++) {
+						H[rr * 6 + c] += sum3(dEi[rr] * dEi[c], dEi[6 + rr] * dEi[6 + c], dEi[12 + rr] * dEi[12 + c]);
+						// dE_j column c: zero for c < 3, bj * unit(c-3) otherwise
+						B[rr * 6 + c] = c < 3 ? 0.f : sum3(dEi[rr] * (c == 3 ? bj : 0.f), dEi[6 + rr] * (c == 4 ? bj : 0.f), dEi[12 + rr] * (c == 5 ? bj : 0.f));
+					}
+				const float rv[3] = {r.x, r.y, r.z};
+#pragma unroll
+				for (int c = 0; c < 6; c++) b[c] -= sum3(dEi[c] * rv[0], dEi[6 + c] * rv[1], dEi[12 + c] * rv[2]);
+			}
+		} else {
+			const int cj = n - g.arrow_base;
+			for (int q = g.in_offsets[cj]; q < g.in_offsets[cj + 1]; q++) {
+				const int e = g.in_edges[q];
+				float3 s, r; float a;
+				arap_edge(g, rotations, translations, e, s, a, r);
+				const float bj = -a;
+				H[3 * 6 + 3] += bj * bj; H[4 * 6 + 4] += bj * bj; H[5 * 6 + 5] += bj * bj;
+				b[3] -= bj * r.x; b[4] -= bj * r.y; b[5] -= bj * r.z;
+			}
+		}
+	}
+	if (g.lm_factor > 0.f) {
+#pragma unroll
+		for (int c = 0; c < 6; c++) H[c * 6 + c] += g.lm_factor;
+	}
+#pragma unroll
+	for (int k = 0; k < 36; k++) diag[(int64_t) n * 36 + k] = H[k];
+#pragma unroll
+	for (int c = 0; c < 6; c++) rhs[n * 6 + c] = b[c];
+}
+
+__global__ void __launch_bounds__(256) diagnostics_convert_kernel(const int32_t* __restrict__ faces, const uint8_t* __restrict__ mask_in, int64_t n,
+                                                                   int64_t* __restrict__ faces_out, uint8_t* __restrict__ mask_out) {
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	if (faces_out) faces_out[i] = faces[i];
+	if (mask_out) mask_out[i] = mask_in[i];
+}
+
+}  // namespace nnrt_b200
+
+// ---- host class --------------------------------------------------------------------------------------------------
+struct nnrt_b200_fitter {
+	nnrt_b200_fitter_options opt;
+	int64_t V, F, E; int N, A, H, W;
+	int arrow_base = 0, corner_blocks = 0;
+	bool model_set = false, reference_set = false;
+	// arena
+	char* arena = nullptr; size_t arena_bytes = 0, arena_used = 0;
+	int* host_flags = nullptr;  // pinned
+	// device views
+	nnrt_b200::FitterDeviceData d{};
+	nnrt_b200::GraphDeviceData g{};
+	nnrt_b200::ArrowheadSystem sys{};
+	float4 *positions, *normals, *wpos, *wnrm, *vjac, *refpts;
+	int4* tris; int2* fa_entries; uint8_t* fa_counts;
+	int32_t* anchors; float* weights; float* nodes;
+	int2* edges; float *ew_res, *ew_jac; int *out_offsets, *out_edges, *in_offsets, *in_edges, *wing_columns;
+	float *accum, *sys_diag, *sys_rhs, *wing, *dinv, *stem_y, *wing_x, *schur, *corner_rhs, *x, *corner_scratch;
+	unsigned long long* keys; nnrt_b200::BandItem* queue; int* counters;
+	int32_t* diag_faces; float* diag_res; uint8_t* diag_mask;
+	// cached graph
+	cudaGraphExec_t graph_exec = nullptr;
+	struct GraphKey { float* R; float* t; double K[9]; double T[16]; int iters; cudaStream_t stream; } graph_key{};
+
+	template<typename T> T* take(size_t count) {
+		const size_t bytes = (count * sizeof(T) + 255) & ~size_t(255);
+		T* p = reinterpret_cast<T*>(arena + arena_used);
+		arena_used += bytes;
+		return p;
+	}
+};
+
+namespace nnrt_b200 {
+
+static size_t layout(nnrt_b200_fitter* f, bool assign) {
+	// two passes: measure (arena == nullptr), then assign
+	f->arena_used = 0;
+	const int64_t V = f->V, F = f->F, E = f->E, PX = (int64_t) f->H * f->W;
+	const int N = f->N, A = f->A;
+	const int64_t nmax = (int64_t) N * 6;  // corner can be at most all nodes
+	(void) assign;
+	f->positions = f->take<float4>(V); f->normals = f->take<float4>(V);
+	f->wpos = f->take<float4>(V); f->wnrm = f->take<float4>(V); f->vjac = f->take<float4>(V * A * 2);
+	f->tris = f->take<int4>(F); f->fa_entries = f->take<int2>(F * 3 * A); f->fa_counts = f->take<uint8_t>(F);
+	f->anchors = f->take<int32_t>(V * A); f->weights = f->take<float>(V * A); f->nodes = f->take<float>((int64_t) N * 3);
+	f->edges = f->take<int2>(E + 1); f->ew_res = f->take<float>(E + 1); f->ew_jac = f->take<float>(E + 1);
+	f->out_offsets = f->take<int>(N + 2); f->out_edges = f->take<int>(E + 1);
+	f->in_offsets = f->take<int>(N + 2); f->in_edges = f->take<int>(E + 1); f->wing_columns = f->take<int>(E + 1);
+	f->refpts = f->take<float4>(PX);
+	f->keys = f->take<unsigned long long>(PX);
+	f->queue = f->take<BandItem>(F + 65536); f->counters = f->take<int>(4);
+	f->accum = f->take<float>((int64_t) N * kAccumStride);
+	f->sys_diag = f->take<float>((int64_t) N * 36); f->sys_rhs = f->take<float>(nmax); f->wing = f->take<float>((E + 1) * 36);
+	f->dinv = f->take<float>((int64_t) N * 36); f->stem_y = f->take<float>(nmax); f->wing_x = f->take<float>((E + 1) * 36);
+	// dense corner: sized for the worst case the graph can ask for is N blocks; allocate lazily bounded by what set_model needs
+	f->x = f->take<float>(nmax);
+	f->diag_faces = f->take<int32_t>(PX); f->diag_res = f->take<float>(PX); f->diag_mask = f->take<uint8_t>(PX);
+	return f->arena_used;
+}
+
+}  // namespace nnrt_b200
+
+using namespace nnrt_b200;
+
+extern "C" void nnrt_b200_fitter_default_options(nnrt_b200_fitter_options* o) {
+	if (!o) return;
+	o->max_iteration_count = 100; o->use_perspective_correction = 1; o->max_depth = 10.0f; o->use_tukey_penalty = 0;
+	o->tukey_penalty_cutoff = 0.01f; o->preconditioning_dampening_factor = 0.0f; o->arap_term_weight = 200.f;
+	o->use_huber_penalty = 0; o->huber_penalty_constant = 0.0001f;
+}
+
+extern "C" int nnrt_b200_fitter_create(const nnrt_b200_fitter_options* options, int64_t vertex_count, int64_t face_count, int32_t node_count,
+                                       int64_t edge_count, int32_t anchor_count, int32_t image_height, int32_t image_width,
+                                       nnrt_b200_fitter** out_fitter) {
+	NNRT_CHECK_ARG(out_fitter, "fitter_create: null output");
+	NNRT_CHECK_ARG(vertex_count > 0 && face_count > 0 && node_count > 0 && edge_count >= 0, "fitter_create: counts must be positive");
+	NNRT_CHECK_ARG(anchor_count >= 1 && anchor_count <= kMaxAnchors, "anchor_count must be in [1, %d], got %d", kMaxAnchors, anchor_count);
+	NNRT_CHECK_ARG(image_height > 0 && image_width > 0, "fitter_create: image size must be positive");
+	NNRT_CHECK_ARG(node_count <= 32767, "node_count (currently, %d) cannot exceed int16_t max, which is 32767.", node_count);
+	nnrt_b200_fitter_options opt;
+	nnrt_b200_fitter_default_options(&opt);
+	if (options) opt = *options;
+	// cpp/alignment/DeformableMeshToImageFitter.cpp:79-82
+	NNRT_CHECK_ARG(opt.preconditioning_dampening_factor >= 0.f && opt.preconditioning_dampening_factor <= 1.f,
+	               "`preconditioning_dampening_factor` should be a small non-negative value between 0 and 1. Got %f.", opt.preconditioning_dampening_factor);
+	auto* f = new nnrt_b200_fitter();
+	f->opt = opt; f->V = vertex_count; f->F = face_count; f->E = edge_count; f->N = node_count; f->A = anchor_count;
+	f->H = image_height; f->W = image_width;
+	const size_t bytes = layout(f, false);
+	if (cudaMalloc(&f->arena, bytes) != cudaSuccess) { delete f; set_last_error("fitter_create: cudaMalloc of %zu bytes failed", bytes); return kCudaError; }
+	f->arena_bytes = bytes;
+	layout(f, true);
+	if (cudaMallocHost(&f->host_flags, 4 * sizeof(int)) != cudaSuccess) { cudaFree(f->arena); delete f; return kCudaError; }
+	memset(f->host_flags, 0, 4 * sizeof(int));
+	f->schur = nullptr; f->corner_rhs = nullptr; f->corner_scratch = nullptr;
+	cudaMemset(f->arena, 0, bytes);
+	launch_fill_keys(f->keys, (int64_t) f->H * f->W, nullptr);
+	if (cudaDeviceSynchronize() != cudaSuccess) { set_last_error("fitter_create: workspace initialisation failed"); return kCudaError; }
+	*out_fitter = f;
+	return kOk;
+}
+
+extern "C" void nnrt_b200_fitter_destroy(nnrt_b200_fitter* f) {
+	if (!f) return;
+	if (f->graph_exec) cudaGraphExecDestroy(f->graph_exec);
+	cudaFree(f->arena);
+	cudaFree(f->schur);  // corner buffers are allocated by set_model (their size depends on arrow_base)
+	cudaFreeHost(f->host_flags);
+	delete f;
+}
+
+extern "C" int64_t nnrt_b200_fitter_workspace_bytes(const nnrt_b200_fitter* f) { return f ? (int64_t) f->arena_bytes : 0; }
+extern "C" int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter*) { return 7; }
+
+extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vertex_positions, const float* vertex_normals,
+                                          const int64_t* triangles, const float* nodes, const int32_t* edges, int32_t arrow_base,
+                                          const int8_t* edge_layer_indices, const float* layer_decimation_radii, int32_t layer_count,
+                                          const float* node_coverage_weights, const int32_t* anchors, const float* anchor_weights,
+                                          void* stream) {
+	NNRT_CHECK_ARG(f, "fitter_set_model: null fitter");
+	NNRT_CHECK_ARG(vertex_positions && triangles && nodes && anchors && anchor_weights, "fitter_set_model: null pointer argument");
+	// cpp/alignment/DeformableMeshToImageFitter.cpp:346-348
+	NNRT_CHECK_ARG(vertex_normals, "Input warped mesh needs to have normals defined; it doesn't.");
+	auto s = (cudaStream_t) stream;
+	const int64_t V = f->V, F = f->F, E = f->E;
+	const int N = f->N, A = f->A;
+	if (E > 0) {
+		NNRT_CHECK_ARG(edges, "fitter_set_model: edge_count > 0 but edges is null");
+		NNRT_CHECK_ARG((edge_layer_indices && layer_decimation_radii && layer_count > 0) || node_coverage_weights,
+		               "fitter_set_model: edges need edge_layer_indices + layer_decimation_radii, or node_coverage_weights");
+		NNRT_CHECK_ARG(arrow_base >= 1 && arrow_base <= N, "first_layer_node_count (currently, %d) must be in [1, node_count = %d].", arrow_base, N);
+	} else {
+		arrow_base = N;  // no regularisation edges: block-diagonal system (DeformableMeshToImageFitter.cpp:248-254)
+	}
+	pack_float4_kernel<<<blocks_for(V, 256), 256, 0, s>>>(vertex_positions, V, f->positions);
+	pack_float4_kernel<<<blocks_for(V, 256), 256, 0, s>>>(vertex_normals, V, f->normals);
+	pack_triangles_kernel<<<blocks_for(F, 256), 256, 0, s>>>(triangles, F, f->tris);
+	NNRT_CUDA(cudaMemcpyAsync(f->anchors, anchors, sizeof(int32_t) * V * A, cudaMemcpyDeviceToDevice, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->weights, anchor_weights, sizeof(float) * V * A, cudaMemcpyDeviceToDevice, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->nodes, nodes, sizeof(float) * N * 3, cudaMemcpyDeviceToDevice, s));
+	face_anchor_table_kernel<<<blocks_for(F, 256), 256, 0, s>>>(f->tris, F, f->anchors, A, f->fa_entries, f->fa_counts);
+	NNRT_LAUNCH_CHECK();
+
+	// graph topology is static for the fit: build CSR + per-edge weights on the host once (the reference re-derives them per iteration)
+	std::vector<int32_t> h_edges((size_t) E * 2);
+	std::vector<int> out_off(N + 2, 0), in_off(N + 2, 0), out_e((size_t) E + 1), in_e((size_t) E + 1), wcol((size_t) E + 1);
+	std::vector<float> ew_res((size_t) E + 1, 0.f), ew_jac((size_t) E + 1, 0.f);
+	if (E > 0) {
+		NNRT_CUDA(cudaMemcpyAsync(h_edges.data(), edges, sizeof(int32_t) * E * 2, cudaMemcpyDeviceToHost, s));
+		std::vector<int8_t> h_layers;
+		std::vector<float> h_radii, h_cov;
+		const int64_t layer_len = E > N ? E : N;
+		if (edge_layer_indices && layer_decimation_radii) {
+			h_layers.resize((size_t) layer_len); h_radii.resize((size_t) layer_count);
+			NNRT_CUDA(cudaMemcpyAsync(h_layers.data(), edge_layer_indices, (size_t) layer_len, cudaMemcpyDeviceToHost, s));
+			NNRT_CUDA(cudaMemcpyAsync(h_radii.data(), layer_decimation_radii, sizeof(float) * layer_count, cudaMemcpyDeviceToHost, s));
+		} else {
+			h_cov.resize((size_t) N);
+			NNRT_CUDA(cudaMemcpyAsync(h_cov.data(), node_coverage_weights, sizeof(float) * N, cudaMemcpyDeviceToHost, s));
+		}
+		NNRT_CUDA(cudaStreamSynchronize(s));
+		const int nc = N - arrow_base;
+		for (int64_t e = 0; e < E; e++) {
+			const int i = h_edges[e * 2], j = h_edges[e * 2 + 1];
+			// the only regime in which the reference's ARAP Hessian is defined: every edge is a wing block
+			NNRT_CHECK_ARG(i >= 0 && i < arrow_base && j >= arrow_base && j < N,
+			               "edge %lld = (%d, %d) must connect a first-layer node (< %d) to a coarser-layer node (>= %d)", (long long) e, i, j, arrow_base, arrow_base);
+			out_off[i + 1]++; in_off[j - arrow_base + 1]++;
+			wcol[e] = j;
+			if (!h_layers.empty()) {
+				const int lr = h_layers[j], lj = h_layers[e];  // sic: residual indexes the layer table by node j (…FitterImpl.h:708), Jacobian by edge
+				NNRT_CHECK_ARG(lr >= 0 && lr < layer_count && lj >= 0 && lj < layer_count, "edge layer index out of range");
+				ew_res[e] = h_radii[lr]; ew_jac[e] = h_radii[lj];
+			} else {
+				ew_res[e] = ew_jac[e] = h_cov[i] > h_cov[j] ? h_cov[i] : h_cov[j];
+			}
+		}
+		for (int i = 0; i < arrow_base; i++) out_off[i + 1] += out_off[i];
+		for (int c = 0; c < nc; c++) in_off[c + 1] += in_off[c];
+		std::vector<int> oc(out_off.begin(), out_off.end()), ic(in_off.begin(), in_off.end());
+		for (int64_t e = 0; e < E; e++) {
+			out_e[oc[h_edges[e * 2]]++] = (int) e;
+			in_e[ic[h_edges[e * 2 + 1] - arrow_base]++] = (int) e;
+		}
+		for (int i = 0; i < arrow_base; i++)
+			for (int q = out_off[i]; q < out_off[i + 1]; q++)
+				for (int q2 = q + 1; q2 < out_off[i + 1]; q2++)
+					NNRT_CHECK_ARG(wcol[out_e[q]] != wcol[out_e[q2]], "duplicate edge (%d, %d)", i, wcol[out_e[q]]);
+	}
+	NNRT_CUDA(cudaMemcpyAsync(f->edges, h_edges.data(), sizeof(int32_t) * E * 2, cudaMemcpyHostToDevice, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->ew_res, ew_res.data(), sizeof(float) * (E + 1), cudaMemcpyHostToDevice, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->ew_jac, ew_jac.data(), sizeof(float) * (E + 1), cudaMemcpyHostToDevice, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->out_offsets, out_off.data(), sizeof(int) * (N + 2), cudaMemcpyHostToDevice, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->in_offsets, in_off.data(), sizeof(int) * (N + 2), cudaMemcpyHostToDevice, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->out_edges, out_e.data(), sizeof(int) * (E + 1), cudaMemcpyHostToDevice, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->in_edges, in_e.data(), sizeof(int) * (E + 1), cudaMemcpyHostToDevice, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->wing_columns, wcol.data(), sizeof(int) * (E + 1), cudaMemcpyHostToDevice, s));
+	NNRT_CUDA(cudaStreamSynchronize(s));  // host staging vectors go out of scope
+
+	// dense corner buffers (size depends on arrow_base)
+	const int corner_blocks = N - arrow_base;
+	if (corner_blocks != f->corner_blocks || f->schur == nullptr) {
+		if (f->schur) { cudaFree(f->schur); f->schur = nullptr; }
+		const size_t n = (size_t) corner_blocks * 6;
+		const size_t scratch = corner_scratch_bytes(corner_blocks);
+		const size_t total = (n * n + n + 16) * sizeof(float) + (scratch > 227 * 1024 ? scratch : 0);
+		NNRT_CUDA(cudaMalloc(&f->schur, total));
+		NNRT_CUDA(cudaMemset(f->schur, 0, total));
+		f->corner_rhs = f->schur + n * n;
+		f->corner_scratch = scratch > 227 * 1024 ? f->corner_rhs + n + 16 : nullptr;
+	}
+	f->arrow_base = arrow_base; f->corner_blocks = corner_blocks;
+	f->model_set = true;
+	if (f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
+	return kOk;
+}
+
+extern "C" int nnrt_b200_fitter_set_reference_points(nnrt_b200_fitter* f, const float* reference_points, const uint8_t* reference_mask,
+                                                     void* stream) {
+	NNRT_CHECK_ARG(f && reference_points, "fitter_set_reference_points: null pointer argument");
+	const int64_t px = (int64_t) f->H * f->W;
+	pack_reference_kernel<<<blocks_for(px, 256), 256, 0, (cudaStream_t) stream>>>(reference_points, reference_mask, px, f->refpts);
+	NNRT_LAUNCH_CHECK();
+	f->reference_set = true;
+	return kOk;
+}
+
+extern "C" int nnrt_b200_fitter_set_reference_depth(nnrt_b200_fitter* f, const void* depth, int32_t depth_dtype, const uint8_t* user_mask,
+                                                    float depth_scale, const double* intrinsics_host, void* stream) {
+	NNRT_CHECK_ARG(f && depth && intrinsics_host, "fitter_set_reference_depth: null pointer argument");
+	NNRT_CHECK_ARG(depth_dtype == 0 || depth_dtype == 1, "depth dtype must be float32 (0) or uint16 (1)");
+	const int64_t px = (int64_t) f->H * f->W;
+	const Intrinsics k = intrinsics_from_host(intrinsics_host);
+	auto s = (cudaStream_t) stream;
+	if (depth_dtype == 0)
+		reference_from_depth_kernel<float><<<blocks_for(px, 256), 256, 0, s>>>((const float*) depth, user_mask, f->H, f->W, k, depth_scale, f->opt.max_depth, f->refpts);
+	else
+		reference_from_depth_kernel<uint16_t><<<blocks_for(px, 256), 256, 0, s>>>((const uint16_t*) depth, user_mask, f->H, f->W, k, depth_scale, f->opt.max_depth, f->refpts);
+	NNRT_LAUNCH_CHECK();
+	f->reference_set = true;
+	return kOk;
+}
+
+namespace nnrt_b200 {
+
+struct IterationContext {
+	FitterDeviceData d; GraphDeviceData g; ArrowheadSystem sys; DataTermParams p; NdcCamera cam; Rigid extrinsics;
+};
+
+static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const double* T) {
+	IterationContext c{};
+	c.d.positions = f->positions; c.d.normals = f->normals; c.d.triangles = f->tris; c.d.vertex_count = f->V; c.d.face_count = f->F;
+	c.d.anchors = f->anchors; c.d.anchor_weights = f->weights; c.d.anchor_count = f->A;
+	c.d.face_anchor_entries = f->fa_entries; c.d.face_anchor_counts = f->fa_counts;
+	c.d.nodes = f->nodes; c.d.node_count = f->N; c.d.arrow_base = f->arrow_base;
+	c.d.warped_positions = f->wpos; c.d.warped_normals = f->wnrm; c.d.vertex_jacobians = f->vjac;
+	c.d.keys = f->keys; c.d.band_queue = f->queue; c.d.counters = f->counters; c.d.band_queue_capacity = (int) (f->F + 65536);
+	c.d.reference_points = f->refpts; c.d.accumulators = f->accum;
+	c.d.diag_pixel_faces = f->diag_faces; c.d.diag_residuals = f->diag_res; c.d.diag_mask = f->diag_mask;
+	c.g.nodes = f->nodes; c.g.node_count = f->N; c.g.arrow_base = f->arrow_base; c.g.edges = f->edges; c.g.edge_count = (int) f->E;
+	c.g.edge_weight_residual = f->ew_res; c.g.edge_weight_jacobian = f->ew_jac;
+	c.g.out_offsets = f->out_offsets; c.g.out_edges = f->out_edges; c.g.in_offsets = f->in_offsets; c.g.in_edges = f->in_edges;
+	c.g.arap_weight = f->opt.arap_term_weight; c.g.lm_factor = f->opt.preconditioning_dampening_factor;
+	c.g.use_huber = f->opt.use_huber_penalty; c.g.huber_constant = f->opt.huber_penalty_constant;
+	c.sys.node_count = f->N; c.sys.arrow_base = f->arrow_base; c.sys.diagonal_blocks = f->sys_diag; c.sys.rhs = f->sys_rhs;
+	c.sys.wing_blocks = f->wing; c.sys.wing_columns = f->wing_columns; c.sys.row_offsets = f->out_offsets; c.sys.row_blocks = f->out_edges;
+	c.sys.corner_upper_blocks = nullptr; c.sys.corner_upper_coordinates = nullptr; c.sys.corner_upper_count = 0;
+	c.sys.inverted_stem = f->dinv; c.sys.stem_y = f->stem_y; c.sys.wing_x = f->wing_x; c.sys.schur = f->schur; c.sys.corner_rhs = f->corner_rhs;
+	c.sys.flags = f->counters;
+	c.cam = ndc_camera_from_host(K, f->H, f->W);
+	c.p.height = f->H; c.p.width = f->W; c.p.pinhole = intrinsics_from_host(K); c.p.ndc = c.cam.k; c.p.max_depth = f->opt.max_depth;
+	c.p.perspective_correct = f->opt.use_perspective_correction; c.p.use_tukey = f->opt.use_tukey_penalty;
+	c.p.tukey_cutoff = f->opt.tukey_penalty_cutoff;
+	// RasterizeNdcTriangles(..., blur 0.5 px, ...) (DeformableMeshToImageFitter.cpp:124-127); ImageSpaceDistanceToNdc
+	c.p.blur_radius = 0.5f / (fminf((float) f->H, (float) f->W) / 2.0f);
+	c.extrinsics = rigid_from_host(T);
+	return c;
+}
+
+// One GN/LM iteration = 7 launches. `ev` (optional, 8 events) brackets the stages for profile_iteration.
+static int enqueue_iteration(nnrt_b200_fitter* f, const IterationContext& c, float* R, float* t, cudaStream_t s, cudaEvent_t* ev) {
+	if (ev) cudaEventRecord(ev[0], s);
+	launch_warp_vertices(c.d, R, t, c.extrinsics, s);
+	if (ev) cudaEventRecord(ev[1], s);
+	launch_face_raster(c.d, c.p, c.cam, s);
+	if (ev) cudaEventRecord(ev[2], s);
+	launch_band_raster(c.d, c.p, c.cam, s);
+	if (ev) cudaEventRecord(ev[3], s);
+	if (launch_assemble(c.d, c.p, s) != kOk) return kInvalidArgument;
+	if (ev) cudaEventRecord(ev[4], s);
+	build_system_kernel<<<(f->N + 127) / 128, 128, 0, s>>>(c.g, R, t, f->accum, f->sys_diag, f->sys_rhs, f->wing);
+	launch_stem_eliminate(c.sys, s);
+	if (ev) cudaEventRecord(ev[5], s);
+	const int rc = launch_corner_solve(c.sys, f->x, R, t, true, f->corner_scratch, s);
+	if (ev) cudaEventRecord(ev[6], s);
+	if (rc != kOk) return rc;
+	NNRT_LAUNCH_CHECK();
+	return kOk;
+}
+
+}  // namespace nnrt_b200
+
+extern "C" int nnrt_b200_fitter_fit(nnrt_b200_fitter* f, float* node_rotations, float* node_translations, const double* intrinsics_host,
+                                    const double* extrinsics_host, int32_t iteration_count, void* stream) {
+	NNRT_CHECK_ARG(f && node_rotations && node_translations && intrinsics_host, "fitter_fit: null pointer argument");
+	NNRT_CHECK_ARG(f->model_set, "fitter_fit: set_model has not been called");
+	NNRT_CHECK_ARG(f->reference_set, "fitter_fit: no reference observation set");
+	if (iteration_count <= 0) iteration_count = f->opt.max_iteration_count;
+	auto s = (cudaStream_t) stream;
+	static const double I4[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+	const double* T = extrinsics_host ? extrinsics_host : I4;
+	nnrt_b200_fitter::GraphKey key{};
+	key.R = node_rotations; key.t = node_translations; key.iters = iteration_count; key.stream = s;
+	memcpy(key.K, intrinsics_host, sizeof(key.K)); memcpy(key.T, T, sizeof(key.T));
+	if (f->graph_exec == nullptr || memcmp(&key, &f->graph_key, sizeof(key)) != 0) {
+		if (f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
+		const IterationContext c = make_context(f, intrinsics_host, T);
+		cudaStream_t cs;
+		NNRT_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+		NNRT_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+		int rc = kOk;
+		for (int it = 0; it < iteration_count && rc == kOk; it++) rc = enqueue_iteration(f, c, node_rotations, node_translations, cs, nullptr);
+		cudaGraph_t graph = nullptr;
+		const cudaError_t end = cudaStreamEndCapture(cs, &graph);
+		cudaStreamDestroy(cs);
+		if (rc != kOk || end != cudaSuccess) {
+			if (graph) cudaGraphDestroy(graph);
+			if (rc == kOk) { set_last_error("fitter_fit: graph capture failed: %s", cudaGetErrorString(end)); rc = kCudaError; }
+			return rc;
+		}
+		const cudaError_t inst = cudaGraphInstantiate(&f->graph_exec, graph, 0);
+		cudaGraphDestroy(graph);
+		if (inst != cudaSuccess) { f->graph_exec = nullptr; set_last_error("fitter_fit: graph instantiation failed: %s", cudaGetErrorString(inst)); return kCudaError; }
+		f->graph_key = key;
+	}
+	NNRT_CUDA(cudaGraphLaunch(f->graph_exec, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->host_flags, f->counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, s));
+	return kOk;
+}
+
+// Waits for `stream` and reports what the last fit recorded on the device: band-queue overflow or a non-positive-definite block.
+extern "C" int nnrt_b200_fitter_status(nnrt_b200_fitter* f, void* stream) {
+	NNRT_CHECK_ARG(f, "fitter_status: null fitter");
+	NNRT_CUDA(cudaStreamSynchronize((cudaStream_t) stream));
+	if (f->host_flags[1]) { set_last_error("fitter: large-face band queue overflow"); return kQueueOverflow; }
+	if (f->host_flags[2]) { set_last_error("fitter: a Hessian block was not positive definite"); return kNotPositiveDefinite; }
+	return kOk;
+}
+
+extern "C" int nnrt_b200_fitter_get_diagnostics(nnrt_b200_fitter* f, float* hessian_diagonal, float* negative_gradient, float* deltas,
+                                                int64_t* pixel_face_indices, float* residuals, uint8_t* residual_mask, void* stream) {
+	NNRT_CHECK_ARG(f, "fitter_get_diagnostics: null fitter");
+	auto s = (cudaStream_t) stream;
+	const int64_t px = (int64_t) f->H * f->W;
+	if (hessian_diagonal) NNRT_CUDA(cudaMemcpyAsync(hessian_diagonal, f->sys_diag, sizeof(float) * f->N * 36, cudaMemcpyDeviceToDevice, s));
+	if (negative_gradient) NNRT_CUDA(cudaMemcpyAsync(negative_gradient, f->sys_rhs, sizeof(float) * f->N * 6, cudaMemcpyDeviceToDevice, s));
+	if (deltas) NNRT_CUDA(cudaMemcpyAsync(deltas, f->x, sizeof(float) * f->N * 6, cudaMemcpyDeviceToDevice, s));
+	if (residuals) NNRT_CUDA(cudaMemcpyAsync(residuals, f->diag_res, sizeof(float) * px, cudaMemcpyDeviceToDevice, s));
+	if (pixel_face_indices || residual_mask) {
+		diagnostics_convert_kernel<<<blocks_for(px, 256), 256, 0, s>>>(f->diag_faces, f->diag_mask, px, pixel_face_indices, residual_mask);
+		NNRT_LAUNCH_CHECK();
+	}
+	return kOk;
+}
+
+extern "C" int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* f, float* node_rotations, float* node_translations,
+                                                  const double* intrinsics_host, const double* extrinsics_host, float* stage_ms6, void* stream) {
+	NNRT_CHECK_ARG(f && node_rotations && node_translations && intrinsics_host && stage_ms6, "fitter_profile_iteration: null pointer argument");
+	NNRT_CHECK_ARG(f->model_set && f->reference_set, "fitter_profile_iteration: model / reference not set");
+	static const double I4[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+	auto s = (cudaStream_t) stream;
+	const IterationContext c = make_context(f, intrinsics_host, extrinsics_host ? extrinsics_host : I4);
+	cudaEvent_t ev[7];
+	for (auto& e : ev) NNRT_CUDA(cudaEventCreate(&e));
+	const int rc = enqueue_iteration(f, c, node_rotations, node_translations, s, ev);
+	NNRT_CUDA(cudaStreamSynchronize(s));
+	for (int k = 0; k < 6; k++) cudaEventElapsedTime(stage_ms6 + k, ev[k], ev[k + 1]);
+	for (auto& e : ev) cudaEventDestroy(e);
+	return rc;
+}

@@ -1,0 +1,61 @@
+// Host-side helpers of the C ABI layer: thread-local error message, CUDA error checks, launch sizing.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdarg>
+#include <cstdint>
+#include "common.cuh"
+
+namespace nnrt_b200 {
+
+void set_last_error(const char* fmt, ...);
+
+#define NNRT_CHECK_ARG(cond, ...)                                 \
+	do {                                                          \
+		if (!(cond)) {                                            \
+			::nnrt_b200::set_last_error(__VA_ARGS__);             \
+			return ::nnrt_b200::kInvalidArgument;                 \
+		}                                                         \
+	} while (0)
+
+#define NNRT_CUDA(call)                                                                                   \
+	do {                                                                                                  \
+		cudaError_t err__ = (call);                                                                       \
+		if (err__ != cudaSuccess) {                                                                       \
+			::nnrt_b200::set_last_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(err__), __FILE__, __LINE__); \
+			return ::nnrt_b200::kCudaError;                                                               \
+		}                                                                                                 \
+	} while (0)
+
+#define NNRT_LAUNCH_CHECK() NNRT_CUDA(cudaGetLastError())
+
+inline unsigned blocks_for(int64_t n, int threads) { return (unsigned) ((n + threads - 1) / threads); }
+
+inline Intrinsics intrinsics_from_host(const double* K) { return Intrinsics{(float) K[0], (float) K[4], (float) K[2], (float) K[5]}; }
+inline Rigid rigid_from_host(const double* T44) {
+	Rigid r;
+	for (int i = 0; i < 3; i++)
+		for (int j = 0; j < 4; j++) r.e[i * 4 + j] = T44 ? (float) T44[i * 4 + j] : (i == j ? 1.f : 0.f);
+	return r;
+}
+// rendering::kernel::ImageSpaceIntrinsicsToNdc (cpp/rendering/kernel/CoordinateSystemConversions.h:108-148), double precision on the host
+struct NdcCamera {
+	Intrinsics k;
+	float min_x, max_x, min_y, max_y;
+};
+inline NdcCamera ndc_camera_from_host(const double* K, int height, int width) {
+	const double fx = K[0], fy = K[4], cx = K[2], cy = K[5];
+	const double smaller = width < height ? (double) width : (double) height;
+	float range_x = 2.0f, range_y = 2.0f;
+	if (width > height) range_x = ((float) width * 2.0f) / (float) height;
+	if (height > width) range_y = ((float) height * 2.0f) / (float) width;
+	const double fx_ndc = 2.0 * fx / smaller, fy_ndc = -2.0 * fy / smaller;
+	const double cx_ndc = -(2.0 * cx - (double) width) / smaller, cy_ndc = (2.0 * cy - (double) height) / smaller;
+	NdcCamera c;
+	c.k = Intrinsics{(float) fx_ndc, (float) fy_ndc, (float) cx_ndc, (float) cy_ndc};
+	c.min_x = (float) (cx_ndc - range_x / 2.f); c.max_x = (float) (cx_ndc + range_x / 2.f);
+	c.min_y = (float) (cy_ndc - range_y / 2.f); c.max_y = (float) (cy_ndc + range_y / 2.f);
+	return c;
+}
+
+}  // namespace nnrt_b200

@@ -1,0 +1,39 @@
+// Block-sparse arrowhead solve on device (core::linalg::SolveBlockSparseArrowheadCholesky,
+// cpp/core/linalg/SolveBlockSparseArrowheadCholesky.cpp:31-94) in two launches:
+//   stem_eliminate: one warp per block row. Stem rows: 6x6 Cholesky inverse D^-1, y = D^-1 b, X_e = D^-1 B_e for the row's wing
+//                   blocks, Schur update S -= B_e1^T X_e2 and rhs update b_C -= X_e^T b (float atomics into the dense corner).
+//                   Corner rows: S_diag += C_jj, b_C += b_j.
+//   corner_solve:   single CTA; packed lower-triangular Cholesky of S in shared memory with the right-hand side carried as an
+//                   extra row (forward substitution for free), warp-level back substitution, stem back-substitution
+//                   x_i = y_i - sum_e X_e x_C, optional fused node update (Rodrigues, R <- R dR, t += dt).
+// This replaces cuSOLVER potrfBatched + MAGMA potrs_batched + 5 cuBLAS gemmBatched + potrf + 2 trsm + their host syncs.
+#pragma once
+#include "host_util.h"
+
+namespace nnrt_b200 {
+
+struct ArrowheadSystem {
+	int node_count, arrow_base;
+	const float* diagonal_blocks;   // [N,36]
+	const float* rhs;               // [6N]
+	const float* wing_blocks;       // [W,36]
+	const int* wing_columns;        // [W] global block column (>= arrow_base)
+	const int* row_offsets;         // [arrow_base+1] CSR over wing blocks by stem row
+	const int* row_blocks;          // [W] wing block ids grouped by row
+	const float* corner_upper_blocks; const int* corner_upper_coordinates; int corner_upper_count;
+	// workspace
+	float* inverted_stem;           // [arrow_base,36]
+	float* stem_y;                  // [arrow_base,6]
+	float* wing_x;                  // [W,36]  D^-1 B
+	float* schur;                   // [(6Nc)^2], must be zero on entry
+	float* corner_rhs;              // [6Nc], must be zero on entry
+	int* flags;                     // flags[2] set when a block is not positive definite
+};
+
+void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s);
+// x [6N]; if node_rotations != nullptr the update is applied in place; clear_corner zeroes schur / corner_rhs after reading.
+int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotations, float* node_translations, bool clear_corner,
+                        float* scratch_global, cudaStream_t s);
+size_t corner_scratch_bytes(int corner_blocks);
+
+}  // namespace nnrt_b200

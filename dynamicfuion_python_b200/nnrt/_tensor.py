@@ -1,0 +1,99 @@
+"""Tensor plumbing between Python callers and the C ABI: torch owns device memory and streams, nothing else.
+
+Accepts torch tensors, numpy arrays and anything exposing __dlpack__ (e.g. open3d.core.Tensor when Open3D is
+present); returns torch CUDA tensors. A mesh argument is duck-typed like the reference's bindings accept an
+open3d.t.geometry.TriangleMesh: an object with .vertex["positions"|"normals"] and .triangle["indices"], or a
+(positions, normals, triangles) tuple, or a dict with those keys.
+"""
+import numpy as np
+import torch
+
+from .. import _lib
+
+
+def device():
+    if not torch.cuda.is_available():
+        raise RuntimeError("nnrt (B200 build) needs a CUDA device; there is no CPU path")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def to_torch(x):
+    if isinstance(x, torch.Tensor):
+        return x
+    if isinstance(x, np.ndarray):
+        return torch.from_numpy(np.ascontiguousarray(x))
+    if hasattr(x, "__dlpack__"):
+        return torch.from_dlpack(x)
+    return torch.as_tensor(x)
+
+
+def cuda(x, dtype):
+    t = to_torch(x)
+    if t.dtype == torch.bool and dtype == torch.uint8:
+        t = t.to(torch.uint8)
+    return t.to(device=device(), dtype=dtype).contiguous()
+
+
+def host_f64(x, shape):
+    """Host-side float64 matrix (intrinsics / extrinsics live on CPU:0 in the reference API)."""
+    t = to_torch(x).detach().to("cpu", torch.float64).contiguous()
+    if tuple(t.shape) != tuple(shape):
+        raise RuntimeError(f"expected a tensor of shape {tuple(shape)}, got {tuple(t.shape)}")
+    return t
+
+
+def ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def empty(shape, dtype):
+    return torch.empty(shape, dtype=dtype, device=device())
+
+
+def call(name, *args):
+    _lib.check(getattr(_lib.lib(), name)(*args))
+
+
+class MeshView:
+    """positions [V,3] f32, normals [V,3] f32 or None, triangles [F,3] int64 on the device."""
+
+    def __init__(self, mesh):
+        pos = nrm = tri = None
+        if isinstance(mesh, MeshView):
+            pos, nrm, tri = mesh.positions, mesh.normals, mesh.triangles
+        elif isinstance(mesh, (tuple, list)):
+            pos, nrm, tri = (list(mesh) + [None, None])[:3]
+        elif isinstance(mesh, dict):
+            pos, nrm, tri = mesh.get("positions"), mesh.get("normals"), mesh.get("triangles", mesh.get("indices"))
+        elif hasattr(mesh, "vertex") and hasattr(mesh, "triangle"):
+            pos = mesh.vertex["positions"]
+            nrm = mesh.vertex["normals"] if "normals" in mesh.vertex else None
+            tri = mesh.triangle["indices"] if "indices" in mesh.triangle else None
+        else:
+            raise RuntimeError("mesh must be an Open3D t.geometry.TriangleMesh-like object, a dict or a (positions, normals, triangles) tuple")
+        if pos is None:
+            raise RuntimeError("Argument mesh needs to have vertex positions defined.")
+        self.positions = cuda(pos, torch.float32)
+        self.normals = None if nrm is None else cuda(nrm, torch.float32)
+        self.triangles = None if tri is None else cuda(tri, torch.int64)
+
+    def with_vertices(self, positions, normals):
+        out = MeshView.__new__(MeshView)
+        out.positions, out.normals, out.triangles = positions, normals, self.triangles
+        return out
+
+    # minimal Open3D-like accessors so results can be consumed the same way
+    @property
+    def vertex(self):
+        d = {"positions": self.positions}
+        if self.normals is not None:
+            d["normals"] = self.normals
+        return d
+
+    @property
+    def triangle(self):
+        return {} if self.triangles is None else {"indices": self.triangles}

@@ -1,0 +1,164 @@
+"""nnrt.alignment — DeformableMeshToImageFitter (cpp/alignment/DeformableMeshToImageFitter.h:30-126; C++-only in the reference,
+exposed here under its natural name with the constructor's argument names and defaults)."""
+import ctypes as C
+import enum
+
+import torch
+
+from ... import _lib
+from .. import _tensor as T
+from ..geometry import WarpNodeCoverageComputationMethod
+from . import functional
+
+
+class IterationMode(enum.IntEnum):
+    ALL = 0
+    TRANSLATION_ONLY = 1
+    ROTATION_ONLY = 2
+
+
+class DeformableMeshToImageFitter:
+    def __init__(self, max_iteration_count=100, iteration_mode_sequence=(IterationMode.ALL,), minimal_update_threshold=1e-6,
+                 use_perspective_correction=True, max_depth=10.0, use_tukey_penalty_for_depth_term=False, tukey_penalty_cutoff_cm=0.01,
+                 preconditioning_dampening_factor=0.0, arap_term_weight=200.0, use_huber_penalty_for_arap_term=False,
+                 huber_penalty_constant=0.0001):
+        if preconditioning_dampening_factor < 0.0 or preconditioning_dampening_factor > 1.0:  # DeformableMeshToImageFitter.cpp:79-82
+            raise RuntimeError("`preconditioning_dampening_factor` should be a small non-negative value between 0 and 1. "
+                               f"Got {preconditioning_dampening_factor}.")
+        modes = [IterationMode(m) for m in iteration_mode_sequence]
+        if any(m != IterationMode.ALL for m in modes):
+            raise RuntimeError("this build implements IterationMode.ALL; TRANSLATION_ONLY / ROTATION_ONLY are not built yet")
+        self.max_iteration_count = int(max_iteration_count)
+        self.iteration_mode_sequence = modes
+        self.min_update_threshold = float(minimal_update_threshold)  # the reference never updates `maximum_update` (:100,111): unused
+        self.options = _lib.FitterOptions(self.max_iteration_count, int(bool(use_perspective_correction)), float(max_depth),
+                                          int(bool(use_tukey_penalty_for_depth_term)), float(tukey_penalty_cutoff_cm),
+                                          float(preconditioning_dampening_factor), float(arap_term_weight),
+                                          int(bool(use_huber_penalty_for_arap_term)), float(huber_penalty_constant))
+        self._handle = None
+        self._shape = None
+        self._model_key = None
+        self._keep = None
+
+    def __del__(self):
+        self._release()
+
+    def _release(self):
+        if getattr(self, "_handle", None):
+            _lib.lib().nnrt_b200_fitter_destroy(self._handle)
+            self._handle = None
+
+    def _ensure(self, shape):
+        if self._handle is not None and self._shape == shape:
+            return
+        self._release()
+        handle = C.c_void_p()
+        v, f, n, e, a, h, w = shape
+        _lib.check(_lib.lib().nnrt_b200_fitter_create(C.byref(self.options), v, f, n, e, a, h, w, C.byref(handle)))
+        self._handle, self._shape, self._model_key = handle, shape, None
+
+    def workspace_bytes(self):
+        return 0 if self._handle is None else _lib.lib().nnrt_b200_fitter_workspace_bytes(self._handle)
+
+    # --- setup -------------------------------------------------------------------------------------------------
+    def _set_model(self, warp_field, canonical_mesh, image_size, anchors=None, anchor_weights=None):
+        mesh = T.MeshView(canonical_mesh)
+        if mesh.normals is None:
+            raise RuntimeError("Input warped mesh needs to have normals defined; it doesn't.")
+        if mesh.triangles is None:
+            raise RuntimeError("Argument mesh needs to have both triangle vertex indices and vertex positions.")
+        if anchors is None:  # warp_field.PrecomputeAnchorsAndWeights(canonical_mesh, true), DeformableMeshToImageFitter.cpp:96-97
+            anchors, anchor_weights = warp_field.precompute_anchors_and_weights(mesh)
+        anchors, anchor_weights = T.cuda(anchors, torch.int32), T.cuda(anchor_weights, torch.float32)
+        edges = getattr(warp_field, "edges", None)
+        e = 0 if edges is None else int(edges.shape[0])
+        n = warp_field.nodes.shape[0]
+        self._ensure((mesh.positions.shape[0], mesh.triangles.shape[0], n, e, anchors.shape[1], int(image_size[0]), int(image_size[1])))
+        fixed = warp_field.warp_node_coverage_computation_method == WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE
+        eli = radii = ncw = None
+        layer_count = 0
+        if e > 0:
+            if fixed:
+                eli, radii = warp_field.edge_layer_indices, warp_field.layer_decimation_radii
+                layer_count = radii.shape[0]
+                if eli.shape[0] < max(e, n):
+                    raise RuntimeError("edge_layer_indices must have at least max(edge_count, node_count) entries")
+            else:
+                ncw = warp_field.node_coverage_weights
+        base = getattr(warp_field, "first_layer_node_count", n)
+        T.call("nnrt_b200_fitter_set_model", self._handle, T.ptr(mesh.positions), T.ptr(mesh.normals), T.ptr(mesh.triangles),
+               T.ptr(warp_field.nodes), T.ptr(edges) if e > 0 else None, int(base), T.ptr(eli), T.ptr(radii), int(layer_count), T.ptr(ncw),
+               T.ptr(anchors), T.ptr(anchor_weights), T.stream())
+
+    def _fit(self, warp_field, intrinsic_matrix, extrinsic_matrix, iteration_count=None):
+        K = T.host_f64(intrinsic_matrix, (3, 3))
+        ext = T.host_f64(torch.eye(4, dtype=torch.float64) if extrinsic_matrix is None else extrinsic_matrix, (4, 4))
+        R, t = warp_field.node_rotations, warp_field.node_translations
+        if not (R.is_contiguous() and t.is_contiguous() and R.is_cuda and t.is_cuda):
+            raise RuntimeError("warp field node rotations / translations must be contiguous CUDA tensors")
+        iters = self.max_iteration_count if iteration_count is None else int(iteration_count)
+        T.call("nnrt_b200_fitter_fit", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), iters, T.stream())
+        self._keep = (K, ext)
+
+    def check_status(self):
+        """Waits for the stream and raises if the last fit overflowed its band queue or met a non-positive-definite block."""
+        T.call("nnrt_b200_fitter_status", self._handle, T.stream())
+
+    # --- FitToImage overloads (cpp/alignment/DeformableMeshToImageFitter.cpp:85-329) --------------------------------
+    def fit_to_image(self, warp_field, canonical_mesh, *args, **kwargs):
+        """fit_to_image(warp_field, canonical_mesh, reference_color_image, reference_depth_image, reference_image_mask, intrinsic_matrix,
+        extrinsic_matrix, depth_scale), or with a reference point cloud:
+        fit_to_image(warp_field, canonical_mesh, reference_color_image, reference_point_cloud, reference_point_mask, intrinsic_matrix,
+        extrinsic_matrix, rendering_image_size). The colour image is unused by the reference beyond its size and may be None."""
+        names = ["reference_color_image", "reference", "reference_mask", "intrinsic_matrix", "extrinsic_matrix", "last"]
+        vals = dict(zip(names, args))
+        vals.update(kwargs)
+        ref = vals.get("reference", vals.get("reference_depth_image", vals.get("reference_point_cloud")))
+        mask = vals.get("reference_mask", vals.get("reference_image_mask", vals.get("reference_point_mask")))
+        K, ext = vals["intrinsic_matrix"], vals.get("extrinsic_matrix")
+        last = vals.get("last", vals.get("depth_scale", vals.get("rendering_image_size")))
+        anchors, weights = vals.get("anchors"), vals.get("anchor_weights")
+        ref_t = ref.point["positions"] if hasattr(ref, "point") else (ref.as_tensor() if hasattr(ref, "as_tensor") else ref)
+        ref_t = T.to_torch(ref_t)
+        is_points = ref_t.dim() == 2 and ref_t.shape[1] == 3 and isinstance(last, (tuple, list))
+        if is_points:
+            image_size = (int(last[0]), int(last[1]))
+            self._set_model(warp_field, canonical_mesh, image_size, anchors, weights)
+            pts = T.cuda(ref_t, torch.float32)
+            m = None if mask is None else T.cuda(T.to_torch(mask).reshape(-1), torch.uint8)
+            T.call("nnrt_b200_fitter_set_reference_points", self._handle, T.ptr(pts), T.ptr(m), T.stream())
+        else:
+            depth = ref_t[..., 0] if ref_t.dim() == 3 else ref_t
+            image_size = (int(depth.shape[0]), int(depth.shape[1]))
+            self._set_model(warp_field, canonical_mesh, image_size, anchors, weights)
+            if depth.dtype == torch.uint16:
+                d, code = T.cuda(depth.view(torch.int16), torch.int16), 1
+            else:
+                d, code = T.cuda(depth, torch.float32), 0
+            m = None if mask is None else T.cuda(T.to_torch(mask).reshape(-1), torch.uint8)
+            Kh = T.host_f64(K, (3, 3))
+            T.call("nnrt_b200_fitter_set_reference_depth", self._handle, T.ptr(d), code, T.ptr(m), float(1000.0 if last is None else last),
+                   Kh.data_ptr(), T.stream())
+        self._fit(warp_field, K, ext, vals.get("iteration_count"))
+
+    def diagnostics(self):
+        """Last iteration's system and per-pixel outputs: dict(hessian_diagonal [N,6,6], negative_gradient [N,6], deltas [N,6],
+        pixel_face_indices [H,W] int64, residuals [H,W], residual_mask [H,W] bool)."""
+        _, _, n, _, _, h, w = self._shape
+        Hd, g, d = T.empty((n, 6, 6), torch.float32), T.empty((n, 6), torch.float32), T.empty((n, 6), torch.float32)
+        faces, res, mask = T.empty((h, w), torch.int64), T.empty((h, w), torch.float32), T.empty((h, w), torch.uint8)
+        T.call("nnrt_b200_fitter_get_diagnostics", self._handle, T.ptr(Hd), T.ptr(g), T.ptr(d), T.ptr(faces), T.ptr(res), T.ptr(mask), T.stream())
+        return dict(hessian_diagonal=Hd, negative_gradient=g, deltas=d, pixel_face_indices=faces, residuals=res, residual_mask=mask.to(torch.bool))
+
+    def profile_iteration(self, warp_field, intrinsic_matrix, extrinsic_matrix=None):
+        """Runs ONE iteration outside the graph with CUDA events between stages; returns ms for
+        [warp, raster_small, raster_large, assemble, arap_stem, corner_solve_update]."""
+        K = T.host_f64(intrinsic_matrix, (3, 3))
+        ext = T.host_f64(torch.eye(4, dtype=torch.float64) if extrinsic_matrix is None else extrinsic_matrix, (4, 4))
+        out = (C.c_float * 6)()
+        T.call("nnrt_b200_fitter_profile_iteration", self._handle, T.ptr(warp_field.node_rotations), T.ptr(warp_field.node_translations),
+               K.data_ptr(), ext.data_ptr(), out, T.stream())
+        return list(out)
+
+    def launches_per_iteration(self):
+        return int(_lib.lib().nnrt_b200_fitter_launches_per_iteration(self._handle))

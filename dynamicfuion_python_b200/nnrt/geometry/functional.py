@@ -1,0 +1,132 @@
+"""nnrt.geometry.functional — same names, argument order and defaults as cpp/pybind/geometry/functional/functional.cpp:51-140."""
+import torch
+
+from .. import _tensor as T
+
+
+def _anchors(points, nodes, node_weights, node_coverage, anchor_count, minimum_valid_anchor_count):
+    pts = T.cuda(points, torch.float32)
+    shape = pts.shape
+    if shape[-1] != 3:
+        raise RuntimeError(f"points must have shape [..., 3], got {tuple(shape)}")
+    flat = pts.reshape(-1, 3)
+    nd = T.cuda(nodes, torch.float32)
+    nw = None if node_weights is None else T.cuda(node_weights, torch.float32)
+    if nw is not None and nw.numel() != nd.shape[0]:
+        raise RuntimeError("node_coverage_weights must have one entry per node")
+    anchors = T.empty((flat.shape[0], anchor_count), torch.int32)
+    weights = T.empty((flat.shape[0], anchor_count), torch.float32)
+    T.call("nnrt_b200_compute_anchors_euclidean", T.ptr(flat), flat.shape[0], T.ptr(nd), nd.shape[0], T.ptr(nw), float(node_coverage),
+           int(anchor_count), int(minimum_valid_anchor_count), T.ptr(anchors), T.ptr(weights), T.stream())
+    out_shape = tuple(shape[:-1]) + (anchor_count,)
+    return anchors.reshape(out_shape), weights.reshape(out_shape)
+
+
+def compute_anchors_and_weights_euclidean_fixed_node_weight(points, nodes, anchor_count, minimum_valid_anchor_count, node_coverage_weight):
+    """ComputeAnchorsAndWeights_Euclidean_FixedNodeWeight (cpp/geometry/functional/WarpAnchorComputation.cpp:74-110)."""
+    return _anchors(points, nodes, None, node_coverage_weight, anchor_count, minimum_valid_anchor_count)
+
+
+def compute_anchors_and_weights_euclidean_variable_node_weight(points, nodes, node_coverage_weights, anchor_count, minimum_valid_anchor_count):
+    """ComputeAnchorsAndWeights_Euclidean_VariableNodeWeight (cpp/geometry/functional/WarpAnchorComputation.cpp:112-148)."""
+    return _anchors(points, nodes, node_coverage_weights, 0.0, anchor_count, minimum_valid_anchor_count)
+
+
+def _warp(points, normals, nodes, node_rotations, node_translations, anchors, anchor_weights, minimum_valid_anchor_count, extrinsics):
+    nd = T.cuda(nodes, torch.float32)
+    R = T.cuda(node_rotations, torch.float32)
+    t = T.cuda(node_translations, torch.float32)
+    a = T.cuda(anchors, torch.int32)
+    w = T.cuda(anchor_weights, torch.float32)
+    if tuple(R.shape) != (nd.shape[0], 3, 3) or tuple(t.shape) != (nd.shape[0], 3):
+        raise RuntimeError("node_rotations must be [N,3,3] and node_translations [N,3]")
+    if a.shape != w.shape or a.shape[0] != points.shape[0]:
+        raise RuntimeError("anchors / anchor_weights must be [point_count, anchor_count]")
+    ext = T.host_f64(torch.eye(4, dtype=torch.float64) if extrinsics is None else extrinsics, (4, 4))
+    wp = torch.empty_like(points)
+    wn = None if normals is None else torch.empty_like(normals)
+    T.call("nnrt_b200_warp_points_normals", T.ptr(points), T.ptr(normals), points.shape[0], T.ptr(nd), T.ptr(R), T.ptr(t), nd.shape[0],
+           T.ptr(a), T.ptr(w), a.shape[1], int(minimum_valid_anchor_count), ext.data_ptr(), T.ptr(wp), T.ptr(wn), T.stream())
+    return wp, wn
+
+
+def warp_triangle_mesh(input_mesh, nodes, node_rotations, node_translations, *args, threshold_nodes_by_distance=False,
+                       minimum_valid_anchor_count=0, extrinsics=None, **kwargs):
+    """Both overloads of warp_triangle_mesh (cpp/geometry/functional/Warping.cpp:169-263): (anchor_count, node_coverage, ...) computes
+    anchors on the fly; (anchors, anchor_weights, ...) uses supplied anchors."""
+    names = ["a0", "a1", "threshold_nodes_by_distance", "minimum_valid_anchor_count", "extrinsics"]
+    vals = dict(zip(names, args))
+    for key in ("anchor_count", "anchors"):
+        if key in kwargs:
+            vals["a0"] = kwargs.pop(key)
+    for key in ("node_coverage", "anchor_weights"):
+        if key in kwargs:
+            vals["a1"] = kwargs.pop(key)
+    if kwargs:
+        raise TypeError(f"unexpected arguments {sorted(kwargs)}")
+    threshold = vals.get("threshold_nodes_by_distance", threshold_nodes_by_distance)
+    min_valid = vals.get("minimum_valid_anchor_count", minimum_valid_anchor_count)
+    ext = vals.get("extrinsics", extrinsics)
+    mesh = T.MeshView(input_mesh)
+    if isinstance(vals["a0"], int):
+        anchors, weights = compute_anchors_and_weights_euclidean_fixed_node_weight(mesh.positions, nodes, vals["a0"],
+                                                                                   min_valid if threshold else 0, vals["a1"])
+    else:
+        anchors, weights = vals["a0"], vals["a1"]
+    wp, wn = _warp(mesh.positions, mesh.normals, nodes, node_rotations, node_translations, anchors, weights,
+                   min_valid if threshold else 0, ext)
+    return mesh.with_vertices(wp, wn)
+
+
+def warp_point_cloud(input_point_cloud, nodes, node_rotations, node_translations, a0, a1, minimum_valid_anchor_count, extrinsics=None):
+    """warp_point_cloud, both overloads (cpp/pybind/geometry/functional/functional.cpp:94-109). Returns warped positions [P,3]."""
+    pts = input_point_cloud.point["positions"] if hasattr(input_point_cloud, "point") else input_point_cloud
+    pts = T.cuda(pts, torch.float32)
+    if isinstance(a0, int):
+        a0, a1 = compute_anchors_and_weights_euclidean_fixed_node_weight(pts, nodes, a0, minimum_valid_anchor_count, a1)
+    wp, _ = _warp(pts, None, nodes, node_rotations, node_translations, a0, a1, minimum_valid_anchor_count, extrinsics)
+    return wp
+
+
+def compute_point_to_plane_distances(mesh1, mesh2_or_point_cloud):
+    """ComputePointToPlaneDistances (cpp/geometry/functional/kernel/PointToPlaneDistancesImpl.h:25-52): n1 . (v1 - v2)."""
+    m1 = T.MeshView(mesh1)
+    if m1.normals is None:
+        raise RuntimeError("mesh1 needs to have vertex normals defined.")
+    if hasattr(mesh2_or_point_cloud, "point"):
+        v2 = T.cuda(mesh2_or_point_cloud.point["positions"], torch.float32)
+    elif isinstance(mesh2_or_point_cloud, (torch.Tensor,)) or type(mesh2_or_point_cloud).__module__ == "numpy":
+        v2 = T.cuda(mesh2_or_point_cloud, torch.float32)
+    else:
+        v2 = T.MeshView(mesh2_or_point_cloud).positions
+    if v2.shape != m1.positions.shape:
+        raise RuntimeError("both point sets must have the same number of points")
+    out = T.empty((m1.positions.shape[0],), torch.float32)
+    T.call("nnrt_b200_point_to_plane_distances", T.ptr(m1.normals), T.ptr(m1.positions), T.ptr(v2), v2.shape[0], T.ptr(out), T.stream())
+    return out
+
+
+def unproject_raster_depth_without_filtering(depth, intrinsics, extrinsics=None, depth_scale=1000.0, depth_max=3.0, preserve_pixel_layout=False):
+    """UnprojectDepthImageWithoutFiltering (cpp/geometry/functional/kernel/PerspectiveProjectionImpl.h:62-150) -> (points, mask)."""
+    d = T.to_torch(depth.as_tensor() if hasattr(depth, "as_tensor") else depth)
+    if d.dim() == 3 and d.shape[2] == 1:
+        d = d[..., 0]
+    if d.dtype in (torch.uint16, torch.int16):
+        d = T.cuda(d.view(torch.int16) if d.dtype == torch.uint16 else d, torch.int16)
+        dtype_code = 1
+    elif d.dtype == torch.float32:
+        d = T.cuda(d, torch.float32)
+        dtype_code = 0
+    else:
+        raise RuntimeError("depth must be UInt16 or Float32")
+    rows, cols = d.shape
+    K = T.host_f64(intrinsics, (3, 3))
+    ext = T.host_f64(torch.eye(4, dtype=torch.float64) if extrinsics is None else extrinsics, (4, 4))
+    pts = T.empty((rows * cols, 3), torch.float32)
+    mask = T.empty((rows * cols,), torch.uint8)
+    T.call("nnrt_b200_unproject_depth", T.ptr(d), dtype_code, rows, cols, K.data_ptr(), ext.data_ptr(), float(depth_scale), float(depth_max),
+           T.ptr(pts), T.ptr(mask), T.stream())
+    mask = mask.to(torch.bool)
+    if preserve_pixel_layout:
+        return pts.reshape(rows, cols, 3), mask.reshape(rows, cols)
+    return pts, mask

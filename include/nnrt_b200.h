@@ -1,0 +1,189 @@
+/* nnrt_b200 — C ABI of the sm_100a dense-depth Gauss-Newton path.
+ *
+ * Drop-in boundary for the hot path of henry123-boy/Dynamicfuion_python (`nnrt` pybind11 module,
+ * cpp/pybind/nnrt_pybind.cpp:23-40). Each entry point replaces the kernel(s) behind one reference
+ * host function (cited per function, paths relative to the reference's cpp/). All pointers are
+ * DEVICE pointers unless the name ends in `_host`; all tensors are contiguous row-major; `stream`
+ * is a cudaStream_t passed as void* (NULL = default stream). Every function returns 0 on success,
+ * otherwise an nnrt_b200_status; nnrt_b200_last_error() returns a message for the calling thread.
+ * No function allocates per call except where a workspace argument is documented as optional.
+ */
+#ifndef NNRT_B200_H
+#define NNRT_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+typedef enum {
+	NNRT_B200_OK = 0, NNRT_B200_INVALID_ARGUMENT = 1, NNRT_B200_CUDA_ERROR = 2, NNRT_B200_QUEUE_OVERFLOW = 3,
+	NNRT_B200_NOT_POSITIVE_DEFINITE = 4, NNRT_B200_UNSUPPORTED = 5
+} nnrt_b200_status;
+
+const char* nnrt_b200_last_error(void);
+int nnrt_b200_version(void);
+
+/* geometry::functional::ComputeAnchorsAndWeights_Euclidean_{Fixed,Variable}NodeWeight
+ * (geometry/functional/WarpAnchorComputation.cpp:74-148; kernel/WarpAnchorComputationImpl.h:42-139).
+ * node_weights == NULL selects the fixed-coverage variant. anchors [V,A] int32, weights [V,A] f32. */
+int nnrt_b200_compute_anchors_euclidean(const float* points, int64_t point_count, const float* nodes, int32_t node_count,
+                                        const float* node_weights, float node_coverage, int32_t anchor_count,
+                                        int32_t minimum_valid_anchor_count, int32_t* anchors, float* weights, void* stream);
+
+/* geometry::functional::WarpTriangleMeshUsingSuppliedAnchors / WarpPointCloud (geometry/functional/Warping.cpp:169-263;
+ * kernel/Warp3dPointsAndNormalsImpl.h:334-438). normals / warped_normals may be NULL (points only).
+ * extrinsics_host: 4x4 row-major f64 on the host (as in the reference API). */
+int nnrt_b200_warp_points_normals(const float* points, const float* normals, int64_t point_count, const float* nodes,
+                                  const float* node_rotations, const float* node_translations, int32_t node_count,
+                                  const int32_t* anchors, const float* anchor_weights, int32_t anchor_count,
+                                  int32_t minimum_valid_anchor_count, const double* extrinsics_host, float* warped_points,
+                                  float* warped_normals, void* stream);
+
+/* rendering::functional::GetMeshNdcFaceVerticesAndClipMask (rendering/functional/ExtractFaceVertices.cpp:56-85;
+ * kernel/ExtractClippedFaceVerticesImpl.h:33-194). triangles int64 [F,3]; out face_vertices_ndc [F,3,3] f32
+ * (zeros for masked faces), clip_mask [F] u8 (1 = keep). */
+int nnrt_b200_face_vertices_ndc(const float* vertex_positions, int64_t vertex_count, const int64_t* triangles, int64_t face_count,
+                                const double* intrinsics_host, int32_t image_height, int32_t image_width, float near_clip,
+                                float far_clip, float* face_vertices_ndc, uint8_t* clip_mask, void* stream);
+
+/* rendering::RasterizeNdcTriangles (rendering/RasterizeNdcTriangles.cpp:32-128; kernel/RasterizeNdcTrianglesImpl.h,
+ * kernel/RayFaceIntersection.h). clip_mask may be NULL. bin_size / max_faces_per_bin are accepted for API
+ * compatibility and validated like the reference (bins-per-side < 22 for an explicit bin_size) but do not affect
+ * results: faces are scattered to pixels with 64-bit atomic-min keys, there are no bins to overflow.
+ * Outputs: pixel_face_indices [H,W,K] int64, pixel_depths [H,W,K], pixel_barycentric [H,W,K,3], pixel_face_distances [H,W,K]
+ * (all -1 where empty). */
+int nnrt_b200_rasterize_ndc_triangles(const float* face_vertices_ndc, const uint8_t* clip_mask, int64_t face_count,
+                                      int32_t image_height, int32_t image_width, float blur_radius_pixels, int32_t faces_per_pixel,
+                                      int32_t bin_size, int32_t max_faces_per_bin, int32_t perspective_correct,
+                                      int32_t clip_barycentric, int32_t cull_back_faces, int64_t* pixel_face_indices,
+                                      float* pixel_depths, float* pixel_barycentric, float* pixel_face_distances, void* stream);
+
+/* rendering::functional::InterpolateVertexAttributes (rendering/functional/kernel/InterpolateFaceAttributesImpl.h:31-71). */
+int nnrt_b200_interpolate_vertex_attributes(const int64_t* pixel_face_indices, const float* pixel_barycentric, int64_t pixel_count,
+                                            int32_t faces_per_pixel, const float* face_attributes, int32_t channels,
+                                            float* pixel_attributes, void* stream);
+
+/* geometry::functional::UnprojectDepthImageWithoutFiltering (geometry/functional/kernel/PerspectiveProjectionImpl.h:62-150).
+ * depth_dtype: 0 = float32, 1 = uint16. points [H*W,3] (zeros where invalid), mask [H*W] u8. */
+int nnrt_b200_unproject_depth(const void* depth, int32_t depth_dtype, int32_t rows, int32_t cols, const double* intrinsics_host,
+                              const double* extrinsics_host, float depth_scale, float depth_max, float* points, uint8_t* mask,
+                              void* stream);
+
+/* geometry::functional::ComputePointToPlaneDistances (geometry/functional/kernel/PointToPlaneDistancesImpl.h:25-52). */
+int nnrt_b200_point_to_plane_distances(const float* normals1, const float* vertices1, const float* vertices2, int64_t count,
+                                       float* distances, void* stream);
+
+/* alignment::functional::WarpedSurfaceJacobians (alignment/functional/kernel/WarpedSurfaceJacobiansImpl.h:33-158).
+ * position_jacobians [V,A,4], normal_jacobians [V,A,3]. */
+int nnrt_b200_warped_surface_jacobians(const float* vertex_positions, const float* vertex_normals, int64_t vertex_count,
+                                       const float* nodes, const float* node_rotations, const int32_t* anchors,
+                                       const float* anchor_weights, int32_t anchor_count, float* position_jacobians,
+                                       float* normal_jacobians, void* stream);
+
+/* alignment::functional::RasterizedSurfaceJacobians (alignment/functional/kernel/RasterizedSurfaceJacobiansImpl.h:43-201,
+ * BarycentricCoordinateJacobians.h). Outputs [H,W,3,9] and [H,W,3,10] f32 (zeros where uncovered). */
+int nnrt_b200_rasterized_surface_jacobians(const float* warped_positions, const float* warped_normals, const int64_t* triangles,
+                                           const int64_t* pixel_face_indices, const float* pixel_barycentric, int32_t image_height,
+                                           int32_t image_width, int32_t faces_per_pixel, const double* ndc_intrinsics_host,
+                                           int32_t perspective_correct, float* rendered_vertex_jacobians,
+                                           float* rendered_normal_jacobians, void* stream);
+
+/* alignment::functional::AssociateFacesWithAnchors (alignment/functional/kernel/AssociateFacesWithAnchorsImpl.h:33-107).
+ * Compact replacement of the 1152 B/face Blob: face_anchor_entries [F, 3*A, 2] int32 = (node index, packed slots:
+ * byte k = anchor slot of face vertex k or 0xFF), in the reference's first-appearance order; face_anchor_counts [F] int32. */
+int nnrt_b200_associate_faces_with_anchors(const int64_t* triangles, int64_t face_count, const int32_t* vertex_anchors,
+                                           int32_t anchor_count, int32_t* face_anchor_entries, int32_t* face_anchor_counts,
+                                           void* stream);
+
+/* core::linalg::SolveBlockSparseArrowheadCholesky (core/linalg/SolveBlockSparseArrowheadCholesky.cpp:31-94) on a
+ * BlockSparseArrowheadMatrix (core/linalg/BlockSparseArrowheadMatrix.h:46-107): diagonal_blocks [N,6,6],
+ * upper_wing_blocks [Wc,6,6] + coordinates [Wc,2] (global block row < arrow_base, col >= arrow_base),
+ * corner_upper_blocks [Cu,6,6] + coordinates (may be NULL / 0). b, x: [6N]. */
+int nnrt_b200_solve_block_sparse_arrowhead_cholesky(const float* diagonal_blocks, int32_t diagonal_block_count, int32_t arrow_base,
+                                                    const float* upper_wing_blocks, const int32_t* upper_wing_coordinates,
+                                                    int64_t upper_wing_count, const float* corner_upper_blocks,
+                                                    const int32_t* corner_upper_coordinates, int64_t corner_upper_count,
+                                                    const float* b, float* x, void* stream);
+/* core::linalg::ComputeSchurComplementOfArrowStem_Dense (core/linalg/SchurComplement.cpp:32-77): out [(6Nc),(6Nc)]. */
+int nnrt_b200_arrowhead_schur_complement(const float* diagonal_blocks, int32_t diagonal_block_count, int32_t arrow_base,
+                                         const float* upper_wing_blocks, const int32_t* upper_wing_coordinates,
+                                         int64_t upper_wing_count, const float* corner_upper_blocks,
+                                         const int32_t* corner_upper_coordinates, int64_t corner_upper_count, float* schur,
+                                         void* stream);
+/* core::linalg::SolveBlockDiagonalCholesky (core/linalg/SolveBlockDiagonalGeneric.h:27-90), block_size 3 or 6. */
+int nnrt_b200_solve_block_diagonal_cholesky(const float* blocks, const float* b, int32_t block_count, int32_t block_size, float* x,
+                                            void* stream);
+/* core::linalg::PreconditionDiagonalBlocks (core/linalg/PreconditionDiagonalBlocksImpl.h:29-51), in place. */
+int nnrt_b200_precondition_diagonal_blocks(float* blocks, int32_t block_count, int32_t block_size, float lambda, void* stream);
+/* core::linalg::AxisAngleVectorsToMatricesRodrigues (core/linalg/RodriguesImpl.h:66-100). */
+int nnrt_b200_rodrigues(const float* axis_angles, int32_t count, float* matrices, void* stream);
+/* core::linalg::Matmul3D for batched 3x3 (core/linalg/Matmul3D_CUDA.cpp), c = a * b. */
+int nnrt_b200_matmul3d_3x3(const float* a, const float* b, int32_t count, float* c, void* stream);
+
+/* ---- nnrt::alignment::DeformableMeshToImageFitter (alignment/DeformableMeshToImageFitter.h:30-126, .cpp:56-329) ---- */
+typedef struct nnrt_b200_fitter nnrt_b200_fitter;
+
+typedef struct {
+	int32_t max_iteration_count;          /* default 100 */
+	int32_t use_perspective_correction;   /* default 1 */
+	float max_depth;                      /* default 10 */
+	int32_t use_tukey_penalty;            /* default 0 */
+	float tukey_penalty_cutoff;           /* default 0.01 */
+	float preconditioning_dampening_factor; /* in [0,1], default 0 (LM lambda) */
+	float arap_term_weight;               /* default 200 */
+	int32_t use_huber_penalty;            /* default 0 */
+	float huber_penalty_constant;         /* default 1e-4 */
+} nnrt_b200_fitter_options;
+
+void nnrt_b200_fitter_default_options(nnrt_b200_fitter_options* options);
+/* Creates a fitter with a workspace sized once for (V, F, N, E, A, H, W); the iteration loop allocates nothing. */
+int nnrt_b200_fitter_create(const nnrt_b200_fitter_options* options, int64_t vertex_count, int64_t face_count, int32_t node_count,
+                            int64_t edge_count, int32_t anchor_count, int32_t image_height, int32_t image_width,
+                            nnrt_b200_fitter** out_fitter);
+void nnrt_b200_fitter_destroy(nnrt_b200_fitter* fitter);
+int64_t nnrt_b200_fitter_workspace_bytes(const nnrt_b200_fitter* fitter);
+
+/* Once-per-fit inputs (device pointers; copied/re-laid-out into the workspace on `stream`):
+ * canonical mesh, graph in virtual node order (edges [E,2] int32 with i < arrow_base <= j; E may be 0),
+ * precomputed anchors/weights [V,A] (PrecomputeAnchorsAndWeights, geometry/HierarchicalGraphWarpField.cpp:234-259).
+ * edge_layer_indices [>=max(E,N)] int8 + layer_decimation_radii select FIXED_NODE_COVERAGE edge weights; otherwise
+ * node_coverage_weights [N] (MINIMAL_K_NEIGHBOR_NODE_DISTANCE). */
+int nnrt_b200_fitter_set_model(nnrt_b200_fitter* fitter, const float* vertex_positions, const float* vertex_normals,
+                               const int64_t* triangles, const float* nodes, const int32_t* edges, int32_t arrow_base,
+                               const int8_t* edge_layer_indices, const float* layer_decimation_radii, int32_t layer_count,
+                               const float* node_coverage_weights, const int32_t* anchors, const float* anchor_weights,
+                               void* stream);
+/* Reference observation: reference_points [H*W,3] f32 + reference_mask [H*W] u8 (FitToImage overload .cpp:85-94),
+ * or a depth image (overload .cpp:278-314: depth / depth_scale, unprojected with the camera intrinsics, optional user mask). */
+int nnrt_b200_fitter_set_reference_points(nnrt_b200_fitter* fitter, const float* reference_points, const uint8_t* reference_mask,
+                                          void* stream);
+int nnrt_b200_fitter_set_reference_depth(nnrt_b200_fitter* fitter, const void* depth, int32_t depth_dtype, const uint8_t* user_mask,
+                                         float depth_scale, const double* intrinsics_host, void* stream);
+/* Runs `iteration_count` GN/LM iterations (<= 0: options.max_iteration_count) as one CUDA graph launch.
+ * node_rotations [N,3,3] / node_translations [N,3] are updated in place. */
+int nnrt_b200_fitter_fit(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations, const double* intrinsics_host,
+                         const double* extrinsics_host, int32_t iteration_count, void* stream);
+/* Diagnostics of the LAST iteration executed (copied out on `stream`): any pointer may be NULL.
+ * hessian_diagonal [N,6,6] (data + ARAP + damping), negative_gradient [N,6], deltas [N,6],
+ * pixel_face_indices [H*W] int64, residuals [H*W] f32, residual_mask [H*W] u8. */
+int nnrt_b200_fitter_get_diagnostics(nnrt_b200_fitter* fitter, float* hessian_diagonal, float* negative_gradient, float* deltas,
+                                     int64_t* pixel_face_indices, float* residuals, uint8_t* residual_mask, void* stream);
+/* Waits for `stream`, then reports device-side conditions recorded by the last fit (queue overflow, non-PD block). */
+int nnrt_b200_fitter_status(nnrt_b200_fitter* fitter, void* stream);
+/* Number of kernel launches one iteration issues (for bench.py's gpu_launches). */
+int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter* fitter);
+/* Per-stage device time of one iteration measured with CUDA events outside graph capture (ms):
+ * [warp, raster_small, raster_large, assemble, arap_stem, corner_solve_update]. */
+int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,
+                                       const double* intrinsics_host, const double* extrinsics_host, float* stage_ms6, void* stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif

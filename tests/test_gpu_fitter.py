@@ -1,0 +1,157 @@
+"""GPU parity of the arrowhead solver and of whole GN iterations against the CPU oracle."""
+import numpy as np
+import pytest
+import torch
+
+from util import oracle_fit, rel_close, scene_with_target
+
+pytestmark = pytest.mark.gpu
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def _random_arrowhead(rng, n_stem, n_corner, degree, with_corner_upper=False):
+    N = n_stem + n_corner
+    diag = np.zeros((N, 6, 6), np.float32)
+    for i in range(N):
+        a = rng.normal(size=(6, 6))
+        diag[i] = (a @ a.T + 6 * np.eye(6)) * 4
+    coords, blocks = [], []
+    for i in range(n_stem):
+        for j in rng.choice(n_corner, size=min(degree, n_corner), replace=False):
+            coords.append((i, n_stem + int(j)))
+            blocks.append(rng.normal(size=(6, 6)) * 0.3)
+    cu, cuc = None, None
+    if with_corner_upper:
+        cuc = np.array([(n_stem + a, n_stem + b) for a in range(n_corner) for b in range(a + 1, n_corner) if (a + b) % 3 == 0], np.int32)
+        cu = (rng.normal(size=(len(cuc), 6, 6)) * 0.2).astype(np.float32)
+    b = rng.normal(size=6 * N).astype(np.float32)
+    return diag, np.array(blocks, np.float32).reshape(-1, 6, 6), np.array(coords, np.int32).reshape(-1, 2), cu, cuc, b
+
+
+def _dense(diag, wing, coords, cu, cuc):
+    N = diag.shape[0]
+    A = np.zeros((6 * N, 6 * N))
+    for i in range(N):
+        A[6 * i:6 * i + 6, 6 * i:6 * i + 6] = diag[i]
+    for blk, (i, j) in zip(wing, coords):
+        A[6 * i:6 * i + 6, 6 * j:6 * j + 6] = blk
+        A[6 * j:6 * j + 6, 6 * i:6 * i + 6] = blk.T
+    if cu is not None:
+        for blk, (i, j) in zip(cu, cuc):
+            A[6 * i:6 * i + 6, 6 * j:6 * j + 6] = blk
+            A[6 * j:6 * j + 6, 6 * i:6 * i + 6] = blk.T
+    return A
+
+
+@pytest.mark.parametrize("n_stem,n_corner,degree,cu", [(208, 41, 4, False), (16, 4, 2, False), (30, 8, 3, True), (5, 0, 0, False), (0, 7, 0, True)])
+def test_arrowhead_solver(nnrt, oracle, n_stem, n_corner, degree, cu):
+    """Shapes of the reference's only solver fixture (249 blocks: stem 208, corner 41; cpp/tests/test_block_sparse_arrowhead_solver.cpp:33-35)
+    plus degenerate ones; checked against the oracle and a dense float64 solve with the reference's tolerance AllClose(1e-4, 1e-5)."""
+    rng = np.random.default_rng(11)
+    diag, wing, coords, cub, cuc, b = _random_arrowhead(rng, n_stem, n_corner, degree, cu)
+    L = nnrt.core.linalg
+    A = L.BlockSparseArrowheadMatrix()
+    A.arrow_base_block_index, A.diagonal_block_count = n_stem, n_stem + n_corner
+    A.set_diagonal_blocks(diag)
+    if len(wing):
+        A.upper_wing_blocks, A.upper_wing_block_coordinates = wing, coords
+    if cub is not None and len(cub):
+        A.corner_upper_blocks, A.corner_upper_block_coordinates = cub, cuc
+    x = _np(L.solve_block_sparse_arrowhead_cholesky(A, b))
+    xo, fails = oracle.solve_arrowhead(diag, n_stem, wing.reshape(-1, 6, 6), coords, b, cub, cuc)
+    assert fails == 0
+    xd = np.linalg.solve(_dense(diag, wing, coords, cub, cuc), b.astype(np.float64))
+    np.testing.assert_allclose(x, xd, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(x, xo, rtol=1e-4, atol=1e-5)
+    if n_corner:
+        S = _np(L.compute_schur_complement_of_arrow_stem_dense(A))
+        So = oracle.schur_complement(diag, n_stem, wing.reshape(-1, 6, 6), coords, cub, cuc)
+        np.testing.assert_allclose(S, So, rtol=1e-4, atol=1e-4)
+
+
+def test_block_diagonal_and_precondition(nnrt, oracle):
+    rng = np.random.default_rng(12)
+    diag, _, _, _, _, b = _random_arrowhead(rng, 50, 0, 0)
+    L = nnrt.core.linalg
+    x = _np(L.solve_block_diagonal_cholesky(diag, b))
+    xo, _ = oracle.solve_block_diagonal(diag, b)
+    np.testing.assert_allclose(x, xo, rtol=1e-4, atol=1e-6)
+    d = torch.tensor(diag, device="cuda")
+    L.precondition_diagonal_blocks(d, 0.25)
+    expect = diag.copy()
+    expect[:, range(6), range(6)] += 0.25
+    assert np.array_equal(_np(d), expect)
+
+
+def _gpu_fit(nnrt, s, iterations, **opts):
+    G = nnrt.geometry
+    has_edges = len(s["edges"]) > 0
+    wf = G.HierarchicalGraphWarpField(s["nodes"], s["edges"] if has_edges else None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+                                      G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
+    args = dict(max_iteration_count=iterations, preconditioning_dampening_factor=s["lm_factor"], arap_term_weight=s["arap_term_weight"])
+    args.update(opts)
+    fitter = nnrt.alignment.DeformableMeshToImageFitter(**args)
+    fitter.fit_to_image(wf, (s["positions"], s["normals"], s["triangles"]), None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4),
+                        (s["height"], s["width"]), anchors=s["anchors"], anchor_weights=s["anchor_weights"])
+    fitter.check_status()
+    return wf, fitter
+
+
+@pytest.mark.parametrize("config,h,w", [("tinyr", 120, 160), ("C1", 120, 160), ("C1e", 240, 320)])
+def test_single_iteration_parity(nnrt, oracle, config, h, w):
+    """One GN iteration from the identity state: face indices and coverage bit-exact, residuals / J^T J / J^T r within 1e-4 relative,
+    deltas within 1e-3 relative (BASELINE.json north_star tolerances)."""
+    s = scene_with_target(oracle, config, h, w)
+    ref = oracle_fit(oracle, s, 1)
+    wf, fitter = _gpu_fit(nnrt, s, 1)
+    d = fitter.diagnostics()
+    assert np.array_equal(_np(d["pixel_face_indices"]), ref["pixel_faces"])
+    assert np.array_equal(_np(d["residual_mask"]), ref["residual_mask"])
+    ok, worst = rel_close(_np(d["residuals"]), ref["residuals"], 1e-4)
+    assert ok, f"residuals {worst}"
+    ok, worst = rel_close(_np(d["hessian_diagonal"]), ref["hessian_diag"][0], 1e-4)
+    assert ok, f"J^T J {worst}"
+    ok, worst = rel_close(_np(d["negative_gradient"]), ref["negative_gradient"][0], 1e-4, floor_scale=1e-4)
+    assert ok, f"J^T r {worst}"
+    ok, worst = rel_close(_np(d["deltas"]), ref["deltas"][0], 1e-3, floor_scale=1e-3)
+    assert ok, f"deltas {worst}"
+    np.testing.assert_allclose(_np(wf.node_translations), ref["translations"], rtol=1e-3, atol=1e-6)
+    np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
+
+
+def test_ten_iterations_track_oracle(nnrt, oracle):
+    """Ten free-running iterations: the state after every iteration count stays within 1e-3 of the oracle's, and the fit converges."""
+    s = scene_with_target(oracle, "tinyr", 120, 160)
+    for iters in (2, 5, 10):
+        ref = oracle_fit(oracle, s, iters)
+        wf, fitter = _gpu_fit(nnrt, s, iters)
+        scale = np.abs(ref["translations"]).max()
+        assert np.abs(_np(wf.node_translations) - ref["translations"]).max() <= 1e-3 * scale + 1e-6
+        assert np.abs(_np(wf.node_rotations) - ref["rotations"]).max() <= 1e-4
+        d = fitter.diagnostics()
+        mismatch = (_np(d["pixel_face_indices"]) != ref["pixel_faces"]).sum()
+        assert mismatch <= 20, mismatch  # the reference's own CPU/CUDA tolerance (cpp/tests/test_rasterize.cpp:281,300)
+    err = np.abs(_np(wf.node_translations) - s["translations_gt"]).max()
+    assert err < 0.5 * np.abs(s["translations_gt"]).max()
+
+
+def test_tukey_and_huber_options(nnrt, oracle):
+    s = scene_with_target(oracle, "tinyr", 120, 160)
+    ref = oracle_fit(oracle, s, 1, use_tukey=True, tukey_cutoff=0.01, use_huber=True, huber_constant=1e-4)
+    wf, fitter = _gpu_fit(nnrt, s, 1, use_tukey_penalty_for_depth_term=True, tukey_penalty_cutoff_cm=0.01,
+                          use_huber_penalty_for_arap_term=True, huber_penalty_constant=1e-4)
+    d = fitter.diagnostics()
+    ok, worst = rel_close(_np(d["hessian_diagonal"]), ref["hessian_diag"][0], 1e-4)
+    assert ok, worst
+    ok, worst = rel_close(_np(d["deltas"]), ref["deltas"][0], 1e-3, floor_scale=1e-3)
+    assert ok, worst
+
+
+def test_fitter_argument_errors(nnrt):
+    with pytest.raises(RuntimeError):
+        nnrt.alignment.DeformableMeshToImageFitter(preconditioning_dampening_factor=1.5)
+    with pytest.raises(RuntimeError):
+        nnrt.geometry.GraphWarpField(np.zeros((2, 3), np.float32), anchor_count=4)
