@@ -458,7 +458,7 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	return c;
 }
 
-// One GN/LM iteration = 7 launches. `ev` (optional, 8 events) brackets the stages for profile_iteration.
+// One GN/LM iteration = 7 launches. `ev` (optional, 8 events = 7 stages) brackets the stages for profile_iteration.
 static int enqueue_iteration(nnrt_b200_fitter* f, const IterationContext& c, float* R, float* t, cudaStream_t s, cudaEvent_t* ev) {
 	if (ev) cudaEventRecord(ev[0], s);
 	launch_warp_vertices(c.d, R, t, c.extrinsics, s);
@@ -470,10 +470,11 @@ static int enqueue_iteration(nnrt_b200_fitter* f, const IterationContext& c, flo
 	if (launch_assemble(c.d, c.p, s) != kOk) return kInvalidArgument;
 	if (ev) cudaEventRecord(ev[4], s);
 	build_system_kernel<<<(f->N + 127) / 128, 128, 0, s>>>(c.g, R, t, f->accum, f->sys_diag, f->sys_rhs, f->wing);
-	launch_stem_eliminate(c.sys, s);
 	if (ev) cudaEventRecord(ev[5], s);
-	const int rc = launch_corner_solve(c.sys, f->x, R, t, true, f->corner_scratch, s);
+	launch_stem_eliminate(c.sys, s);
 	if (ev) cudaEventRecord(ev[6], s);
+	const int rc = launch_corner_solve(c.sys, f->x, R, t, true, f->corner_scratch, s);
+	if (ev) cudaEventRecord(ev[7], s);
 	if (rc != kOk) return rc;
 	NNRT_LAUNCH_CHECK();
 	return kOk;
@@ -545,17 +546,17 @@ extern "C" int nnrt_b200_fitter_get_diagnostics(nnrt_b200_fitter* f, float* hess
 }
 
 extern "C" int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* f, float* node_rotations, float* node_translations,
-                                                  const double* intrinsics_host, const double* extrinsics_host, float* stage_ms6, void* stream) {
-	NNRT_CHECK_ARG(f && node_rotations && node_translations && intrinsics_host && stage_ms6, "fitter_profile_iteration: null pointer argument");
+                                                  const double* intrinsics_host, const double* extrinsics_host, float* stage_ms7, void* stream) {
+	NNRT_CHECK_ARG(f && node_rotations && node_translations && intrinsics_host && stage_ms7, "fitter_profile_iteration: null pointer argument");
 	NNRT_CHECK_ARG(f->model_set && f->reference_set, "fitter_profile_iteration: model / reference not set");
 	static const double I4[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
 	auto s = (cudaStream_t) stream;
 	const IterationContext c = make_context(f, intrinsics_host, extrinsics_host ? extrinsics_host : I4);
-	cudaEvent_t ev[7];
+	cudaEvent_t ev[8];
 	for (auto& e : ev) NNRT_CUDA(cudaEventCreate(&e));
 	const int rc = enqueue_iteration(f, c, node_rotations, node_translations, s, ev);
 	NNRT_CUDA(cudaStreamSynchronize(s));
-	for (int k = 0; k < 6; k++) cudaEventElapsedTime(stage_ms6 + k, ev[k], ev[k + 1]);
+	for (int k = 0; k < 7; k++) cudaEventElapsedTime(stage_ms7 + k, ev[k], ev[k + 1]);
 	for (auto& e : ev) cudaEventDestroy(e);
 	return rc;
 }

@@ -152,10 +152,10 @@ class DeformableMeshToImageFitter:
 
     def profile_iteration(self, warp_field, intrinsic_matrix, extrinsic_matrix=None):
         """Runs ONE iteration outside the graph with CUDA events between stages; returns ms for
-        [warp, raster_small, raster_large, assemble, arap_stem, corner_solve_update]."""
+        [warp_vertices, face_raster, band_raster, assemble, build_system, stem_eliminate, corner_solve_update]."""
         K = T.host_f64(intrinsic_matrix, (3, 3))
         ext = T.host_f64(torch.eye(4, dtype=torch.float64) if extrinsic_matrix is None else extrinsic_matrix, (4, 4))
-        out = (C.c_float * 6)()
+        out = (C.c_float * 7)()
         T.call("nnrt_b200_fitter_profile_iteration", self._handle, T.ptr(warp_field.node_rotations), T.ptr(warp_field.node_translations),
                K.data_ptr(), ext.data_ptr(), out, T.stream())
         return list(out)

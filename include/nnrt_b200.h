@@ -176,9 +176,9 @@ int nnrt_b200_fitter_status(nnrt_b200_fitter* fitter, void* stream);
 /* Number of kernel launches one iteration issues (for bench.py's gpu_launches). */
 int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter* fitter);
 /* Per-stage device time of one iteration measured with CUDA events outside graph capture (ms):
- * [warp, raster_small, raster_large, assemble, arap_stem, corner_solve_update]. */
+ * [warp_vertices, face_raster, band_raster, assemble, build_system, stem_eliminate, corner_solve_update]. */
 int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,
-                                       const double* intrinsics_host, const double* extrinsics_host, float* stage_ms6, void* stream);
+                                       const double* intrinsics_host, const double* extrinsics_host, float* stage_ms7, void* stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop
