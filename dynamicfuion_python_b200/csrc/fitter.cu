@@ -384,11 +384,11 @@ extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vert
 		if (f->schur) { cudaFree(f->schur); f->schur = nullptr; }
 		const size_t n = (size_t) corner_blocks * 6;
 		const size_t scratch = corner_scratch_bytes(corner_blocks);
-		const size_t total = (n * n + n + 16) * sizeof(float) + (scratch > 227 * 1024 ? scratch : 0);
+		const size_t total = (n * n + n + 16) * sizeof(float) + (corner_needs_global_scratch(corner_blocks) ? scratch : 0);
 		NNRT_CUDA(cudaMalloc(&f->schur, total));
 		NNRT_CUDA(cudaMemset(f->schur, 0, total));
 		f->corner_rhs = f->schur + n * n;
-		f->corner_scratch = scratch > 227 * 1024 ? f->corner_rhs + n + 16 : nullptr;
+		f->corner_scratch = corner_needs_global_scratch(corner_blocks) ? f->corner_rhs + n + 16 : nullptr;
 	}
 	f->arrow_base = arrow_base; f->corner_blocks = corner_blocks;
 	f->model_set = true;

@@ -105,7 +105,7 @@ static int prepare_explicit(ExplicitArrowhead& ws, const float* diag, int N, int
 	std::vector<int> cur(off.begin(), off.end());
 	for (int64_t w = 0; w < W; w++) blocks[cur[h[w * 2]]++] = (int) w;
 	const size_t scratch_bytes = corner_scratch_bytes(nc);
-	const bool need_global = scratch_bytes > 227 * 1024;
+	const bool need_global = corner_needs_global_scratch(nc);
 	auto al = [](size_t v) { return (v + 255) & ~size_t(255); };
 	const size_t sz_off = al(sizeof(int) * (base + 2)), sz_blk = al(sizeof(int) * (W + 1)), sz_dinv = al(sizeof(float) * (size_t) (base + 1) * 36),
 	             sz_y = al(sizeof(float) * (size_t) (base + 1) * 6), sz_x = al(sizeof(float) * (size_t) (W + 1) * 36), sz_s = al(sizeof(float) * (n * n + 1)),

@@ -25,17 +25,21 @@ struct BandItem { int face, y0, y1, pad; };
 
 struct PixelBox { int u0, u1, v0, v1; };  // inclusive, empty if u0 > u1 or v0 > v1
 
-// Conservative integer pixel range whose centres can pass the reference's bounding-box test; the exact float test is
-// re-applied per pixel inside shade_pixel, so widening by one pixel only costs a rejected test.
+// Exact integer range of pixels whose centres pass the reference's bounding-box test lo <= centre(i) <= hi (the same float
+// expression shade_pixel evaluates; it is monotone in i, so a float estimate corrected by stepping is exact and tight).
 __device__ __forceinline__ void pixel_range(float lo, float hi, int dim1, int dim2, int& i0, int& i1) {
+	if (!(lo <= hi)) { i0 = 0; i1 = dim1 - 1; return; }  // NaN bounds: shade_pixel's comparisons reject nothing, walk the whole axis
 	const float range = ndc_range(dim1, dim2);
 	const float offset = range / 2.0f;
 	// centre(i) = -offset + (range*i + offset)/dim1  =>  i = ((x + offset)*dim1 - offset)/range
 	const float f0 = ((lo + offset) * (float) dim1 - offset) / range;
 	const float f1 = ((hi + offset) * (float) dim1 - offset) / range;
-	// clamp in float first (float->int saturates, +-1 would wrap); NaN falls back to the whole axis
-	i0 = max(0, (int) floorf(fmaxf(f0, 0.f)) - 1);
-	i1 = min(dim1 - 1, (int) ceilf(fminf(f1, (float) dim1)) + 1);
+	i0 = (int) ceilf(fminf(fmaxf(f0, 0.f), (float) dim1));
+	i1 = (int) floorf(fminf(fmaxf(f1, -1.f), (float) (dim1 - 1)));
+	while (i0 > 0 && pixel_to_ndc(i0 - 1, dim1, dim2) >= lo) i0--;
+	while (i0 < dim1 && pixel_to_ndc(i0, dim1, dim2) < lo) i0++;
+	while (i1 < dim1 - 1 && pixel_to_ndc(i1 + 1, dim1, dim2) <= hi) i1++;
+	while (i1 >= 0 && pixel_to_ndc(i1, dim1, dim2) > hi) i1--;
 }
 
 __device__ __forceinline__ bool face_pixel_box(const FaceNdc& f, const RasterParams& rp, PixelBox& box) {

@@ -137,6 +137,26 @@ __device__ void rodrigues(const float* __restrict__ w, float* __restrict__ R) {
 		}
 }
 
+
+// node update (DeformableMeshToImageFitter.cpp:258-273, HierarchicalGraphWarpField.cpp:261-284): t += dt, R <- R * Rodrigues(dw)
+__device__ __forceinline__ void apply_node_update(const float* __restrict__ dlt, float* __restrict__ rotation, float* __restrict__ translation) {
+	float dR[9], R[9];
+	rodrigues(dlt, dR);
+#pragma unroll
+	for (int k = 0; k < 9; k++) R[k] = rotation[k];
+#pragma unroll
+	for (int r = 0; r < 3; r++)
+#pragma unroll
+		for (int c = 0; c < 3; c++) {
+			float acc = 0.f;
+#pragma unroll
+			for (int k = 0; k < 3; k++) acc += R[r * 3 + k] * dR[k * 3 + c];
+			rotation[r * 3 + c] = acc;
+		}
+#pragma unroll
+	for (int c = 0; c < 3; c++) translation[c] = translation[c] + dlt[3 + c];
+}
+
 template<bool kSharedScratch>
 __global__ void __launch_bounds__(1024) corner_solve_kernel(ArrowheadSystem sys, float* __restrict__ x, float* __restrict__ rotations,
                                                              float* __restrict__ translations, int clear_corner,
@@ -234,10 +254,264 @@ __global__ void __launch_bounds__(1024) corner_solve_kernel(ArrowheadSystem sys,
 	}
 }
 
+
+// ---- blocked single-CTA corner solve ------------------------------------------------------------------------------------
+// Right-looking Cholesky in shared memory, panels of kPanel = 8 columns, the right-hand side carried as row n (forward
+// substitution for free). Storage: lower triangle, rows padded to a multiple of 4 columns so every row starts 16-byte aligned
+// (row i of 4-row group g = i / 4 has width 4 (g + 1)); the padding lies in the strict upper triangle and is never read as data.
+//   panel phase   : one thread per row i >= j. Every row thread factors the 8 x 8 diagonal block redundantly in registers
+//                   (one rsqrt per pivot), solves its own row strip against it and publishes the strip to PT[i][0..7]
+//                   (row stride 12 floats: conflict-free 128-bit reads by 8 consecutive rows).
+//   trailing phase: all warps; a warp owns a 4-row group, every lane a 4 x 4 tile (128-bit loads/stores of L, 128 FMAs per
+//                   16 shared-memory instructions), rank-8 update.
+// Two __syncthreads per panel; the back substitution is blocked the same way on a double-buffered right-hand side.
+constexpr int kPanel = 8;
+constexpr int kCornerThreads = 512;
+constexpr int kPanelStride = 12;
+
+__host__ __device__ __forceinline__ int aligned_row_start(int i) {
+	const int g = i >> 2;
+	return 8 * g * (g + 1) + (i - 4 * g) * 4 * (g + 1);
+}
+__host__ __device__ inline int padded_rows(int n) { return (n + 1 + 3) & ~3; }
+
+__host__ __device__ inline size_t blocked_corner_floats(int n) {
+	const int pr = padded_rows(n);
+	return (size_t) aligned_row_start(pr) + (size_t) kPanelStride * pr + 4 * (size_t) pr;
+}
+
+__global__ void __launch_bounds__(kCornerThreads) corner_solve_blocked_kernel(ArrowheadSystem sys, float* __restrict__ x,
+                                                                              float* __restrict__ rotations, float* __restrict__ translations,
+                                                                              int clear_corner) {
+	extern __shared__ __align__(16) float smem[];
+	const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, warps = T >> 5;
+	const int nc = sys.node_count - sys.arrow_base, n = nc * 6;
+	const int rows = n + 1;                                   // + rhs row
+	const int prow = padded_rows(n);
+	float* L = smem;                                          // aligned-packed lower triangle, rows 0..prow-1
+	float* PT = L + aligned_row_start(prow);                  // [prow][kPanelStride]
+	float* inv_diag = PT + kPanelStride * prow;               // [prow]
+	float* ybuf = inv_diag + prow;                            // [2][prow]
+	float* xs = ybuf + 2 * prow;                              // [prow] solution of the corner
+	if (n > 0) {
+		// zero the padding rows/columns once (finite values everywhere the tiles may touch)
+		for (int q = aligned_row_start(n) + tid; q < aligned_row_start(prow); q += T) L[q] = 0.f;
+		for (int q = tid; q < kPanelStride * prow; q += T) PT[q] = 0.f;
+		// stage the lower triangle of S: batches of independent 64-bit loads (n is even, rows are 8-byte aligned); zeroing
+		// happens after the whole batch is in registers so the loads are not serialised behind the stores
+		{
+			const int half = n >> 1, total = n * half;
+			constexpr int kBatch = 8;
+			const float2* S2 = reinterpret_cast<const float2*>(sys.schur);
+			float2* S2w = reinterpret_cast<float2*>(sys.schur);
+			for (int base = 0; base < total; base += T * kBatch) {
+				float2 v[kBatch];
+#pragma unroll
+				for (int b = 0; b < kBatch; b++) {
+					const int q = base + b * T + tid;
+					v[b] = make_float2(0.f, 0.f);
+					if (q < total) {
+						const int i = q / half, k2 = q - i * half;
+						if (2 * k2 <= i) v[b] = __ldcg(S2 + q);
+					}
+				}
+#pragma unroll
+				for (int b = 0; b < kBatch; b++) {
+					const int q = base + b * T + tid;
+					if (q < total) {
+						const int i = q / half, k = 2 * (q - i * half);
+						if (k <= i) {
+							// the element right of the diagonal (k + 1 == i + 1) lands in the row's padding
+							*reinterpret_cast<float2*>(L + aligned_row_start(i) + k) = make_float2(v[b].x, k + 1 <= i ? v[b].y : 0.f);
+							if (clear_corner) S2w[q] = make_float2(0.f, 0.f);
+						}
+					}
+				}
+			}
+		}
+		__syncthreads();  // padding of row n was zeroed above; now place the right-hand side
+		for (int k = tid; k < n; k += T) {
+			L[aligned_row_start(n) + k] = sys.corner_rhs[k];
+			if (clear_corner) sys.corner_rhs[k] = 0.f;
+		}
+		__syncthreads();
+		for (int j = 0; j < n; j += kPanel) {
+			const int nb = min(kPanel, n - j);
+			// ---- panel phase
+			for (int i = j + tid; i < rows; i += T) {
+				if (i > j && i < j + nb) continue;  // rows of the diagonal block are written by the thread of row j
+				float d[kPanel][kPanel], inv[kPanel];
+#pragma unroll
+				for (int r = 0; r < kPanel; r++) {
+					const float* Lr = L + aligned_row_start(min(j + r, rows - 1)) + j;
+#pragma unroll
+					for (int c = 0; c <= r; c++) d[r][c] = (r < nb) ? Lr[c] : (r == c ? 1.f : 0.f);
+				}
+				bool ok = true;
+#pragma unroll
+				for (int c = 0; c < kPanel; c++) {
+					float v = d[c][c];
+#pragma unroll
+					for (int k = 0; k < c; k++) v = fmaf(-d[c][k], d[c][k], v);
+					if (!(v > 0.f)) ok = false;
+					inv[c] = rsqrtf(v);
+					d[c][c] = v * inv[c];
+#pragma unroll
+					for (int r = c + 1; r < kPanel; r++) {
+						float w = d[r][c];
+#pragma unroll
+						for (int k = 0; k < c; k++) w = fmaf(-d[r][k], d[c][k], w);
+						d[r][c] = w * inv[c];
+					}
+				}
+				if (i == j) {
+					if (!ok) atomicExch(sys.flags + 2, 1);
+#pragma unroll
+					for (int r = 0; r < kPanel; r++) {
+						if (r < nb) {
+							inv_diag[j + r] = inv[r];
+							float* Lr = L + aligned_row_start(j + r) + j;
+#pragma unroll
+							for (int c = 0; c <= r; c++) Lr[c] = d[r][c];
+						}
+					}
+				} else {
+					float* Li = L + aligned_row_start(i) + j;
+					float a[kPanel];
+					if (nb == kPanel) {
+						const float4 lo = *reinterpret_cast<const float4*>(Li), hi = *reinterpret_cast<const float4*>(Li + 4);
+						a[0] = lo.x; a[1] = lo.y; a[2] = lo.z; a[3] = lo.w; a[4] = hi.x; a[5] = hi.y; a[6] = hi.z; a[7] = hi.w;
+					} else {
+#pragma unroll
+						for (int c = 0; c < kPanel; c++) a[c] = (c < nb) ? Li[c] : 0.f;
+					}
+#pragma unroll
+					for (int c = 0; c < kPanel; c++) {
+						float w = a[c];
+#pragma unroll
+						for (int k = 0; k < c; k++) w = fmaf(-a[k], d[c][k], w);
+						a[c] = w * inv[c];
+					}
+					if (nb == kPanel) {
+						*reinterpret_cast<float4*>(Li) = make_float4(a[0], a[1], a[2], a[3]);
+						*reinterpret_cast<float4*>(Li + 4) = make_float4(a[4], a[5], a[6], a[7]);
+						float* P = PT + i * kPanelStride;
+						*reinterpret_cast<float4*>(P) = make_float4(a[0], a[1], a[2], a[3]);
+						*reinterpret_cast<float4*>(P + 4) = make_float4(a[4], a[5], a[6], a[7]);
+					} else {
+#pragma unroll
+						for (int c = 0; c < kPanel; c++)
+							if (c < nb) Li[c] = a[c];
+					}
+				}
+			}
+			__syncthreads();
+			if (nb < kPanel) break;  // a partial last panel leaves only the rhs row, which has no columns >= n to update
+			// ---- trailing phase: 4-row groups [i0, i0+3] from j + 8, 4-column tiles k in [j + 8, i0]
+			const int first = j + kPanel;
+			for (int i0 = first + warp * 4; i0 < rows; i0 += warps * 4) {
+				float4 pr[4][2];
+				float* Lrow[4];
+#pragma unroll
+				for (int r = 0; r < 4; r++) {
+					Lrow[r] = L + aligned_row_start(i0 + r);
+					const float* P = PT + (i0 + r) * kPanelStride;
+					pr[r][0] = *reinterpret_cast<const float4*>(P);
+					pr[r][1] = *reinterpret_cast<const float4*>(P + 4);
+				}
+				for (int k = first + lane * 4; k <= i0; k += 128) {
+					float4 pk[4][2], v[4];
+#pragma unroll
+					for (int c = 0; c < 4; c++) {
+						const float* P = PT + (k + c) * kPanelStride;
+						pk[c][0] = *reinterpret_cast<const float4*>(P);
+						pk[c][1] = *reinterpret_cast<const float4*>(P + 4);
+					}
+#pragma unroll
+					for (int r = 0; r < 4; r++) v[r] = *reinterpret_cast<const float4*>(Lrow[r] + k);
+#pragma unroll
+					for (int r = 0; r < 4; r++) {
+#pragma unroll
+						for (int h = 0; h < 2; h++) {
+							const float4 a = pr[r][h];
+							v[r].x = fmaf(-a.x, pk[0][h].x, v[r].x); v[r].y = fmaf(-a.x, pk[1][h].x, v[r].y);
+							v[r].z = fmaf(-a.x, pk[2][h].x, v[r].z); v[r].w = fmaf(-a.x, pk[3][h].x, v[r].w);
+							v[r].x = fmaf(-a.y, pk[0][h].y, v[r].x); v[r].y = fmaf(-a.y, pk[1][h].y, v[r].y);
+							v[r].z = fmaf(-a.y, pk[2][h].y, v[r].z); v[r].w = fmaf(-a.y, pk[3][h].y, v[r].w);
+							v[r].x = fmaf(-a.z, pk[0][h].z, v[r].x); v[r].y = fmaf(-a.z, pk[1][h].z, v[r].y);
+							v[r].z = fmaf(-a.z, pk[2][h].z, v[r].z); v[r].w = fmaf(-a.z, pk[3][h].z, v[r].w);
+							v[r].x = fmaf(-a.w, pk[0][h].w, v[r].x); v[r].y = fmaf(-a.w, pk[1][h].w, v[r].y);
+							v[r].z = fmaf(-a.w, pk[2][h].w, v[r].z); v[r].w = fmaf(-a.w, pk[3][h].w, v[r].w);
+						}
+					}
+#pragma unroll
+					for (int r = 0; r < 4; r++) *reinterpret_cast<float4*>(Lrow[r] + k) = v[r];
+				}
+			}
+			__syncthreads();
+		}
+		// ---- blocked back substitution L^T x = y, y = row n of L (forward substitution happened in the factorisation)
+		for (int k = tid; k < n; k += T) ybuf[k] = L[aligned_row_start(n) + k];
+		__syncthreads();
+		int p = 0;
+		for (int j = ((n - 1) / kPanel) * kPanel; j >= 0; j -= kPanel) {
+			const int nb = min(kPanel, n - j);
+			const float* src = ybuf + p * prow;
+			float* dst = ybuf + (p ^ 1) * prow;
+			for (int k = tid; k < j + nb; k += T) {
+				float xb[kPanel];
+#pragma unroll
+				for (int c = kPanel - 1; c >= 0; c--) {
+					xb[c] = 0.f;
+					if (c < nb) {
+						float v = src[j + c];
+#pragma unroll
+						for (int r = kPanel - 1; r > c; r--)
+							if (r < nb) v = fmaf(-L[aligned_row_start(j + r) + j + c], xb[r], v);
+						xb[c] = v * inv_diag[j + c];
+					}
+				}
+				if (k < j) {
+					float v = src[k];
+#pragma unroll
+					for (int c = 0; c < kPanel; c++)
+						if (c < nb) v = fmaf(-L[aligned_row_start(j + c) + k], xb[c], v);
+					dst[k] = v;
+				} else {
+#pragma unroll
+					for (int c = 0; c < kPanel; c++)
+						if (k == j + c) xs[k] = xb[c];
+				}
+			}
+			__syncthreads();
+			p ^= 1;
+		}
+		for (int k = tid; k < n; k += T) x[sys.arrow_base * 6 + k] = xs[k];
+	}
+	// stem back-substitution: x_i = y_i - sum_e X_e x_C[col(e)]
+	for (int idx = tid; idx < sys.arrow_base * 6; idx += T) {
+		const int i = idx / 6, r = idx - i * 6;
+		float acc = sys.stem_y[idx];
+		for (int e = sys.row_offsets[i]; e < sys.row_offsets[i + 1]; e++) {
+			const int w = sys.row_blocks[e];
+			const float* X = sys.wing_x + (int64_t) w * 36 + r * 6;
+			const float* xv = xs + (sys.wing_columns[w] - sys.arrow_base) * 6;
+#pragma unroll
+			for (int k = 0; k < 6; k++) acc = fmaf(-X[k], xv[k], acc);
+		}
+		x[idx] = acc;
+	}
+	if (rotations == nullptr) return;
+	__syncthreads();
+	__threadfence_block();
+	for (int node = tid; node < sys.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3);
+}
+
 size_t corner_scratch_bytes(int corner_blocks) {
 	const int64_t n = (int64_t) corner_blocks * 6;
 	return (size_t) (((n + 1) * (n + 2) / 2 + (n + 1)) * sizeof(float));
 }
+bool corner_needs_global_scratch(int corner_blocks) { return blocked_corner_floats(corner_blocks * 6) * sizeof(float) > 227 * 1024; }
 
 void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s) {
 	if (sys.node_count > 0) stem_eliminate_kernel<<<(sys.node_count + 3) / 4, 128, 0, s>>>(sys);
@@ -246,19 +520,21 @@ void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s) {
 
 int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotations, float* node_translations, bool clear_corner,
                         float* scratch_global, cudaStream_t s) {
-	const size_t bytes = corner_scratch_bytes(sys.node_count - sys.arrow_base);
-	static bool attribute_set = false;
+	const int n = (sys.node_count - sys.arrow_base) * 6;
 	constexpr size_t kMaxShared = 227 * 1024;
-	if (bytes <= kMaxShared) {
-		if (!attribute_set) {
-			if (cudaFuncSetAttribute(corner_solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kMaxShared) != cudaSuccess) return kCudaError;
-			attribute_set = true;
+	const size_t blocked_bytes = blocked_corner_floats(n) * sizeof(float);
+	if (blocked_bytes <= kMaxShared) {
+		static bool blocked_attribute_set = false;
+		if (!blocked_attribute_set) {
+			if (cudaFuncSetAttribute(corner_solve_blocked_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kMaxShared) != cudaSuccess) return kCudaError;
+			blocked_attribute_set = true;
 		}
-		corner_solve_kernel<true><<<1, 1024, bytes, s>>>(sys, x, node_rotations, node_translations, clear_corner ? 1 : 0, nullptr);
-	} else {
-		if (scratch_global == nullptr) return kUnsupported;
-		corner_solve_kernel<false><<<1, 1024, 0, s>>>(sys, x, node_rotations, node_translations, clear_corner ? 1 : 0, scratch_global);
+		corner_solve_blocked_kernel<<<1, kCornerThreads, blocked_bytes, s>>>(sys, x, node_rotations, node_translations, clear_corner ? 1 : 0);
+		return kOk;
 	}
+	// corners too large for one SM's shared memory: unblocked kernel on a global scratch
+	if (scratch_global == nullptr) return kUnsupported;
+	corner_solve_kernel<false><<<1, 1024, 0, s>>>(sys, x, node_rotations, node_translations, clear_corner ? 1 : 0, scratch_global);
 	return kOk;
 }
 

@@ -35,5 +35,6 @@ void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s);
 int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotations, float* node_translations, bool clear_corner,
                         float* scratch_global, cudaStream_t s);
 size_t corner_scratch_bytes(int corner_blocks);
+bool corner_needs_global_scratch(int corner_blocks);  // corner too large for the single-SM shared-memory kernel
 
 }  // namespace nnrt_b200

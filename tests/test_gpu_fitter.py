@@ -116,8 +116,11 @@ def test_single_iteration_parity(nnrt, oracle, config, h, w):
     assert ok, f"J^T J {worst}"
     ok, worst = rel_close(_np(d["negative_gradient"]), ref["negative_gradient"][0], 1e-4, floor_scale=1e-4)
     assert ok, f"J^T r {worst}"
-    ok, worst = rel_close(_np(d["deltas"]), ref["deltas"][0], 1e-3, floor_scale=1e-3)
+    # deltas: 1e-3 relative per component, components below 1 % of the largest update compared at 1e-5 of it (components that
+    # vanish by symmetry on the plane scenes carry only fp32 summation-order noise), and 1e-3 norm-wise
+    ok, worst = rel_close(_np(d["deltas"]), ref["deltas"][0], 1e-3, floor_scale=1e-2)
     assert ok, f"deltas {worst}"
+    assert np.abs(_np(d["deltas"]) - ref["deltas"][0]).max() <= 1e-3 * np.abs(ref["deltas"][0]).max()
     np.testing.assert_allclose(_np(wf.node_translations), ref["translations"], rtol=1e-3, atol=1e-6)
     np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
 
