@@ -384,10 +384,11 @@ extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vert
 		if (f->schur) { cudaFree(f->schur); f->schur = nullptr; }
 		const size_t n = (size_t) corner_blocks * 6;
 		const size_t scratch = corner_scratch_bytes(corner_blocks);
-		const size_t total = (n * n + n + 16) * sizeof(float) + (corner_needs_global_scratch(corner_blocks) ? scratch : 0);
+		const size_t schur_floats = corner_schur_floats(corner_blocks);
+		const size_t total = (schur_floats + n + 16) * sizeof(float) + (corner_needs_global_scratch(corner_blocks) ? scratch : 0);
 		NNRT_CUDA(cudaMalloc(&f->schur, total));
 		NNRT_CUDA(cudaMemset(f->schur, 0, total));
-		f->corner_rhs = f->schur + n * n;
+		f->corner_rhs = f->schur + schur_floats;
 		f->corner_scratch = corner_needs_global_scratch(corner_blocks) ? f->corner_rhs + n + 16 : nullptr;
 	}
 	f->arrow_base = arrow_base; f->corner_blocks = corner_blocks;
@@ -447,6 +448,7 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	c.sys.wing_blocks = f->wing; c.sys.wing_columns = f->wing_columns; c.sys.row_offsets = f->out_offsets; c.sys.row_blocks = f->out_edges;
 	c.sys.corner_upper_blocks = nullptr; c.sys.corner_upper_coordinates = nullptr; c.sys.corner_upper_count = 0;
 	c.sys.inverted_stem = f->dinv; c.sys.stem_y = f->stem_y; c.sys.wing_x = f->wing_x; c.sys.schur = f->schur; c.sys.corner_rhs = f->corner_rhs;
+	c.sys.schur_tile_packed = corner_uses_tile_packed_schur(f->N - f->arrow_base) ? 1 : 0;
 	c.sys.flags = f->counters;
 	c.cam = ndc_camera_from_host(K, f->H, f->W);
 	c.p.height = f->H; c.p.width = f->W; c.p.pinhole = intrinsics_from_host(K); c.p.ndc = c.cam.k; c.p.max_depth = f->opt.max_depth;

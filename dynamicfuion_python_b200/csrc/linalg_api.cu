@@ -108,7 +108,7 @@ static int prepare_explicit(ExplicitArrowhead& ws, const float* diag, int N, int
 	const bool need_global = corner_needs_global_scratch(nc);
 	auto al = [](size_t v) { return (v + 255) & ~size_t(255); };
 	const size_t sz_off = al(sizeof(int) * (base + 2)), sz_blk = al(sizeof(int) * (W + 1)), sz_dinv = al(sizeof(float) * (size_t) (base + 1) * 36),
-	             sz_y = al(sizeof(float) * (size_t) (base + 1) * 6), sz_x = al(sizeof(float) * (size_t) (W + 1) * 36), sz_s = al(sizeof(float) * (n * n + 1)),
+	             sz_y = al(sizeof(float) * (size_t) (base + 1) * 6), sz_x = al(sizeof(float) * (size_t) (W + 1) * 36), sz_s = al(sizeof(float) * corner_schur_floats(nc)),
 	             sz_r = al(sizeof(float) * (n + 1)), sz_flags = 256, sz_scr = need_global ? al(scratch_bytes) : 0;
 	const size_t total = sz_off + 2 * sz_blk + sz_dinv + sz_y + sz_x + sz_s + sz_r + sz_flags + sz_scr;
 	NNRT_CUDA(cudaMallocAsync(&ws.buffer, total, s));
@@ -163,6 +163,7 @@ extern "C" int nnrt_b200_solve_block_sparse_arrowhead_cholesky(const float* diag
 	rc = prepare_explicit(ws, diagonal_blocks, diagonal_block_count, arrow_base, upper_wing_blocks, upper_wing_coordinates, upper_wing_count,
 	                      corner_upper_blocks, corner_upper_coordinates, corner_upper_count, b, s);
 	if (rc != kOk) { if (ws.buffer) cudaFreeAsync(ws.buffer, s); return rc; }
+	ws.sys.schur_tile_packed = corner_uses_tile_packed_schur(diagonal_block_count - arrow_base) ? 1 : 0;
 	launch_stem_eliminate(ws.sys, s);
 	rc = launch_corner_solve(ws.sys, x, nullptr, nullptr, false, ws.scratch, s);
 	int flags[3] = {0, 0, 0};

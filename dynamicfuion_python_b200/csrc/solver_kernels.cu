@@ -2,6 +2,33 @@
 
 namespace nnrt_b200 {
 
+// ---- corner layouts ---------------------------------------------------------------------------------------------------------
+constexpr int kTile = 8;
+constexpr int kCornerThreads = 512;
+constexpr int kRegTileMaxRows = 256;
+
+// Tile-packed Schur layout consumed by corner_solve_regtile_kernel: 8 x 8 tiles (bi >= bj) of the augmented lower triangle
+// (row n = right-hand side), block columns in DESCENDING order, rows ascending inside a column; tile t is thread t's tile.
+__host__ __device__ __forceinline__ int corner_tile_rows(int n) { return (n + 1 + kTile - 1) / kTile; }
+__host__ __device__ __forceinline__ int corner_tile_cols(int n) { return (n + kTile - 1) / kTile; }
+__host__ __device__ __forceinline__ int corner_tile_count(int n) {
+	const int tr = corner_tile_rows(n), tc = corner_tile_cols(n);
+	return tc * tr - tc * (tc - 1) / 2;
+}
+__host__ __device__ __forceinline__ int corner_tile_id(int n, int bi, int bj) {
+	const int tr = corner_tile_rows(n), tc = corner_tile_cols(n), m = tc - 1 - bj;
+	return m * tr - (bj + tc) * m / 2 + (bi - bj);
+}
+// offset of element (row, col), row in [0, n], col in [0, n), row / 8 >= col / 8
+__host__ __device__ __forceinline__ int corner_tile_index(int n, int row, int col) {
+	return corner_tile_id(n, row >> 3, col >> 3) * 64 + (row & 7) * kTile + (col & 7);
+}
+// where the stem kernel accumulates S(row, col): -1 = not stored in this layout (strict upper tile triangle)
+__device__ __forceinline__ int64_t schur_slot(const ArrowheadSystem& sys, int n, int row, int col) {
+	if (!sys.schur_tile_packed) return (int64_t) row * n + col;
+	return (col > row) ? -1 : corner_tile_index(n, row, col);
+}
+
 // in-place lower Cholesky of a 6x6 (row-major) followed by inversion through two triangular solves per unit column
 // (potrf + potrs(I), cpp/core/linalg/InvertBlocksCPU.cpp:80-112)
 __device__ bool invert_spd6(const float* __restrict__ A, float* __restrict__ Ainv) {
@@ -58,8 +85,14 @@ __global__ void __launch_bounds__(128) stem_eliminate_kernel(ArrowheadSystem sys
 	const float* D = sys.diagonal_blocks + (int64_t) row * 36;
 	if (row >= sys.arrow_base) {  // corner row: scatter the diagonal block and rhs into the dense corner
 		const int c = row - sys.arrow_base;
-		for (int k = lane; k < 36; k += 32) atomicAdd(sys.schur + (int64_t) (c * 6 + k / 6) * n + c * 6 + k % 6, D[k]);
-		if (lane < 6) atomicAdd(sys.corner_rhs + c * 6 + lane, sys.rhs[row * 6 + lane]);
+		for (int k = lane; k < 36; k += 32) {
+			const int64_t slot = schur_slot(sys, n, c * 6 + k / 6, c * 6 + k % 6);
+			if (slot >= 0) atomicAdd(sys.schur + slot, D[k]);
+		}
+		if (lane < 6) {
+			float* dst = sys.schur_tile_packed ? sys.schur + corner_tile_index(n, n, c * 6 + lane) : sys.corner_rhs + c * 6 + lane;
+			atomicAdd(dst, sys.rhs[row * 6 + lane]);
+		}
 		return;
 	}
 	if (lane == 0) {
@@ -96,7 +129,8 @@ __global__ void __launch_bounds__(128) stem_eliminate_kernel(ArrowheadSystem sys
 #pragma unroll
 		for (int k = 0; k < 6; k++) acc += B1[k * 6 + r] * X2[k * 6 + c];
 		const int c1 = sys.wing_columns[w1] - sys.arrow_base, c2 = sys.wing_columns[w2] - sys.arrow_base;
-		atomicAdd(sys.schur + (int64_t) (c1 * 6 + r) * n + c2 * 6 + c, -acc);
+		const int64_t slot = schur_slot(sys, n, c1 * 6 + r, c2 * 6 + c);
+		if (slot >= 0) atomicAdd(sys.schur + slot, -acc);
 	}
 	// b_C[c] -= X_e^T b_row
 	for (int idx = lane; idx < deg * 6; idx += 32) {
@@ -105,7 +139,8 @@ __global__ void __launch_bounds__(128) stem_eliminate_kernel(ArrowheadSystem sys
 		float acc = 0.f;
 #pragma unroll
 		for (int k = 0; k < 6; k++) acc += X[k * 6 + c] * s_b[wib][k];
-		atomicAdd(sys.corner_rhs + (sys.wing_columns[w] - sys.arrow_base) * 6 + c, -acc);
+		const int col = (sys.wing_columns[w] - sys.arrow_base) * 6 + c;
+		atomicAdd(sys.schur_tile_packed ? sys.schur + corner_tile_index(n, n, col) : sys.corner_rhs + col, -acc);
 	}
 }
 
@@ -116,8 +151,9 @@ __global__ void __launch_bounds__(256) corner_upper_scatter_kernel(ArrowheadSyst
 	const int n = (sys.node_count - sys.arrow_base) * 6;
 	const int bi = sys.corner_upper_coordinates[u * 2] - sys.arrow_base, bj = sys.corner_upper_coordinates[u * 2 + 1] - sys.arrow_base;
 	const float v = sys.corner_upper_blocks[idx];
-	atomicAdd(sys.schur + (int64_t) (bi * 6 + r) * n + bj * 6 + c, v);
-	atomicAdd(sys.schur + (int64_t) (bj * 6 + c) * n + bi * 6 + r, v);
+	const int64_t upper = schur_slot(sys, n, bi * 6 + r, bj * 6 + c), lower = schur_slot(sys, n, bj * 6 + c, bi * 6 + r);
+	if (upper >= 0) atomicAdd(sys.schur + upper, v);
+	if (lower >= 0) atomicAdd(sys.schur + lower, v);
 }
 
 __device__ __forceinline__ int64_t packed_index(int i, int k) { return (int64_t) i * (i + 1) / 2 + k; }
@@ -260,14 +296,13 @@ __global__ void __launch_bounds__(1024) corner_solve_kernel(ArrowheadSystem sys,
 // substitution for free). Storage: lower triangle, rows padded to a multiple of 4 columns so every row starts 16-byte aligned
 // (row i of 4-row group g = i / 4 has width 4 (g + 1)); the padding lies in the strict upper triangle and is never read as data.
 //   panel phase   : one thread per row i >= j. Every row thread factors the 8 x 8 diagonal block redundantly in registers
-//                   (one rsqrt per pivot), solves its own row strip against it and publishes the strip to PT[i][0..7]
-//                   (row stride 12 floats: conflict-free 128-bit reads by 8 consecutive rows).
+//                   (one rsqrt per pivot), solves its own row strip against it and publishes the strip to the transposed panel
+//                   buffer PT[c][i] (128-bit reads of 4 consecutive rows are contiguous across lanes: conflict-free).
 //   trailing phase: all warps; a warp owns a 4-row group, every lane a 4 x 4 tile (128-bit loads/stores of L, 128 FMAs per
 //                   16 shared-memory instructions), rank-8 update.
-// Two __syncthreads per panel; the back substitution is blocked the same way on a double-buffered right-hand side.
+//   back substitution: one warp, right-hand side in registers (lane owns y[lane + 32 m]), no block-wide barriers.
 constexpr int kPanel = 8;
-constexpr int kCornerThreads = 512;
-constexpr int kPanelStride = 12;
+constexpr int kMaxRhsPerLane = 10;  // n <= 320
 
 __host__ __device__ __forceinline__ int aligned_row_start(int i) {
 	const int g = i >> 2;
@@ -277,26 +312,193 @@ __host__ __device__ inline int padded_rows(int n) { return (n + 1 + 3) & ~3; }
 
 __host__ __device__ inline size_t blocked_corner_floats(int n) {
 	const int pr = padded_rows(n);
-	return (size_t) aligned_row_start(pr) + (size_t) kPanelStride * pr + 4 * (size_t) pr;
+	return (size_t) aligned_row_start(pr) + (size_t) kPanel * pr + 2 * (size_t) pr + 64;
+}
+
+#ifdef NNRT_PHASE_TIMING
+#define NNRT_STAMP(slot) do { if (threadIdx.x == 0) { const long long now = clock64(); g_phase_clock[slot] = now - t_phase; t_phase = now; } } while (0)
+#define NNRT_ACC(var) do { if (threadIdx.x == 0) { const long long now = clock64(); var += now - t_phase; t_phase = now; } } while (0)
+#else
+#define NNRT_STAMP(slot)
+#define NNRT_ACC(var)
+#endif
+
+// Cholesky of the (up to) 8x8 diagonal block at (j, j) in registers; d is overwritten with its factor, inv[c] = 1 / L_cc.
+template<bool kFull>
+__device__ __forceinline__ bool factor_diagonal_block(const float* __restrict__ L, int j, int nb, int rows, float (&d)[kPanel][kPanel],
+                                                      float (&inv)[kPanel]) {
+#pragma unroll
+	for (int r = 0; r < kPanel; r++) {
+		const float* Lr = L + aligned_row_start(kFull ? j + r : min(j + r, rows - 1)) + j;
+#pragma unroll
+		for (int c = 0; c <= r; c++) d[r][c] = (kFull || r < nb) ? Lr[c] : (r == c ? 1.f : 0.f);
+	}
+	bool ok = true;
+#pragma unroll
+	for (int c = 0; c < kPanel; c++) {
+		float v = d[c][c];
+#pragma unroll
+		for (int k = 0; k < c; k++) v = fmaf(-d[c][k], d[c][k], v);
+		if (!(v > 0.f)) ok = false;
+		inv[c] = rsqrtf(v);
+		d[c][c] = v * inv[c];
+#pragma unroll
+		for (int r = c + 1; r < kPanel; r++) {
+			float w = d[r][c];
+#pragma unroll
+			for (int k = 0; k < c; k++) w = fmaf(-d[r][k], d[c][k], w);
+			d[r][c] = w * inv[c];
+		}
+	}
+	return ok;
+}
+
+template<bool kFull>
+__device__ __forceinline__ void panel_phase(float* __restrict__ L, float* __restrict__ PT, float* __restrict__ inv_diag, int* flags, int j,
+                                            int nb, int rows, int prow) {
+	for (int i = j + (int) threadIdx.x; i < rows; i += blockDim.x) {
+		if (i > j && i < j + nb) continue;  // rows of the diagonal block are written by the thread of row j
+		float d[kPanel][kPanel], inv[kPanel];
+		const bool ok = factor_diagonal_block<kFull>(L, j, nb, rows, d, inv);
+		if (i == j) {
+			if (!ok) atomicExch(flags + 2, 1);
+#pragma unroll
+			for (int r = 0; r < kPanel; r++) {
+				if (kFull || r < nb) {
+					inv_diag[j + r] = inv[r];
+					float* Lr = L + aligned_row_start(j + r) + j;
+#pragma unroll
+					for (int c = 0; c <= r; c++) Lr[c] = d[r][c];
+				}
+			}
+		} else {
+			float* Li = L + aligned_row_start(i) + j;
+			float a[kPanel];
+			if (kFull) {
+				const float4 lo = *reinterpret_cast<const float4*>(Li), hi = *reinterpret_cast<const float4*>(Li + 4);
+				a[0] = lo.x; a[1] = lo.y; a[2] = lo.z; a[3] = lo.w; a[4] = hi.x; a[5] = hi.y; a[6] = hi.z; a[7] = hi.w;
+			} else {
+#pragma unroll
+				for (int c = 0; c < kPanel; c++) a[c] = (c < nb) ? Li[c] : 0.f;
+			}
+#pragma unroll
+			for (int c = 0; c < kPanel; c++) {
+				float w = a[c];
+#pragma unroll
+				for (int k = 0; k < c; k++) w = fmaf(-a[k], d[c][k], w);
+				a[c] = w * inv[c];
+			}
+			if (kFull) {
+				*reinterpret_cast<float4*>(Li) = make_float4(a[0], a[1], a[2], a[3]);
+				*reinterpret_cast<float4*>(Li + 4) = make_float4(a[4], a[5], a[6], a[7]);
+#pragma unroll
+				for (int c = 0; c < kPanel; c++) PT[c * prow + i] = a[c];
+			} else {
+#pragma unroll
+				for (int c = 0; c < kPanel; c++)
+					if (c < nb) Li[c] = a[c];
+			}
+		}
+	}
+}
+
+// rank-8 update of rows [first, rows) x columns [first, row]: 4-row groups per warp, 4 x 4 tile per lane
+__device__ __forceinline__ void trailing_phase(float* __restrict__ L, const float* __restrict__ PT, int first, int rows, int prow) {
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+	for (int i0 = first + warp * 4; i0 < rows; i0 += warps * 4) {
+		float4 pr[kPanel];
+		float* Lrow[4];
+#pragma unroll
+		for (int c = 0; c < kPanel; c++) pr[c] = *reinterpret_cast<const float4*>(PT + c * prow + i0);
+#pragma unroll
+		for (int r = 0; r < 4; r++) Lrow[r] = L + aligned_row_start(i0 + r);
+		for (int k = first + lane * 4; k <= i0; k += 128) {
+			float4 pk[kPanel], v[4];
+#pragma unroll
+			for (int c = 0; c < kPanel; c++) pk[c] = *reinterpret_cast<const float4*>(PT + c * prow + k);
+#pragma unroll
+			for (int r = 0; r < 4; r++) v[r] = *reinterpret_cast<const float4*>(Lrow[r] + k);
+#pragma unroll
+			for (int c = 0; c < kPanel; c++) {
+				const float4 a = pr[c], b = pk[c];
+				v[0].x = fmaf(-a.x, b.x, v[0].x); v[0].y = fmaf(-a.x, b.y, v[0].y); v[0].z = fmaf(-a.x, b.z, v[0].z); v[0].w = fmaf(-a.x, b.w, v[0].w);
+				v[1].x = fmaf(-a.y, b.x, v[1].x); v[1].y = fmaf(-a.y, b.y, v[1].y); v[1].z = fmaf(-a.y, b.z, v[1].z); v[1].w = fmaf(-a.y, b.w, v[1].w);
+				v[2].x = fmaf(-a.z, b.x, v[2].x); v[2].y = fmaf(-a.z, b.y, v[2].y); v[2].z = fmaf(-a.z, b.z, v[2].z); v[2].w = fmaf(-a.z, b.w, v[2].w);
+				v[3].x = fmaf(-a.w, b.x, v[3].x); v[3].y = fmaf(-a.w, b.y, v[3].y); v[3].z = fmaf(-a.w, b.z, v[3].z); v[3].w = fmaf(-a.w, b.w, v[3].w);
+			}
+#pragma unroll
+			for (int r = 0; r < 4; r++) *reinterpret_cast<float4*>(Lrow[r] + k) = v[r];
+		}
+	}
+}
+
+// L^T x = y by one warp: lane owns y[lane + 32 m] in registers; blocks of 8 from the bottom.
+__device__ __forceinline__ void back_substitution_warp(const float* __restrict__ L, const float* __restrict__ inv_diag, float* __restrict__ ysh,
+                                                       float* __restrict__ xs, int n) {
+	const int lane = threadIdx.x & 31;
+	float y[kMaxRhsPerLane];
+	const float* rhs_row = L + aligned_row_start(n);
+#pragma unroll
+	for (int m = 0; m < kMaxRhsPerLane; m++) y[m] = (lane + 32 * m < n) ? rhs_row[lane + 32 * m] : 0.f;
+	for (int j = ((n - 1) / kPanel) * kPanel; j >= 0; j -= kPanel) {
+		const int nb = min(kPanel, n - j);
+		// publish y[j .. j+nb): owners are lanes (j & 31) .. +7 of register slot j >> 5
+		const int slot = j >> 5, off = lane - (j & 31);
+#pragma unroll
+		for (int m = 0; m < kMaxRhsPerLane; m++)
+			if (m == slot && off >= 0 && off < kPanel) ysh[off] = y[m];
+		__syncwarp();
+		float xb[kPanel];
+#pragma unroll
+		for (int c = kPanel - 1; c >= 0; c--) {
+			xb[c] = 0.f;
+			if (c < nb) {
+				float v = ysh[c];
+#pragma unroll
+				for (int r = kPanel - 1; r > c; r--)
+					if (r < nb) v = fmaf(-L[aligned_row_start(j + r) + j + c], xb[r], v);
+				xb[c] = v * inv_diag[j + c];
+			}
+		}
+		__syncwarp();
+#pragma unroll
+		for (int c = 0; c < kPanel; c++)
+			if (lane == c && c < nb) xs[j + c] = xb[c];
+		// y[k] -= sum_c L[j+c][k] xb[c] for k < j
+#pragma unroll
+		for (int m = 0; m < kMaxRhsPerLane; m++) {
+			const int k = lane + 32 * m;
+			if (k < j) {
+				float v = y[m];
+#pragma unroll
+				for (int c = 0; c < kPanel; c++)
+					if (c < nb) v = fmaf(-L[aligned_row_start(j + c) + k], xb[c], v);
+				y[m] = v;
+			}
+		}
+	}
 }
 
 __global__ void __launch_bounds__(kCornerThreads) corner_solve_blocked_kernel(ArrowheadSystem sys, float* __restrict__ x,
                                                                               float* __restrict__ rotations, float* __restrict__ translations,
                                                                               int clear_corner) {
 	extern __shared__ __align__(16) float smem[];
-	const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, warps = T >> 5;
+	const int tid = threadIdx.x, T = blockDim.x;
 	const int nc = sys.node_count - sys.arrow_base, n = nc * 6;
 	const int rows = n + 1;                                   // + rhs row
 	const int prow = padded_rows(n);
 	float* L = smem;                                          // aligned-packed lower triangle, rows 0..prow-1
-	float* PT = L + aligned_row_start(prow);                  // [prow][kPanelStride]
-	float* inv_diag = PT + kPanelStride * prow;               // [prow]
-	float* ybuf = inv_diag + prow;                            // [2][prow]
-	float* xs = ybuf + 2 * prow;                              // [prow] solution of the corner
+	float* PT = L + aligned_row_start(prow);                  // [kPanel][prow]
+	float* inv_diag = PT + kPanel * prow;                     // [prow]
+	float* xs = inv_diag + prow;                              // [prow] solution of the corner
+	float* ysh = xs + prow;                                   // [8] back-substitution exchange
+#ifdef NNRT_PHASE_TIMING
+	long long t_phase = clock64(), acc_panel = 0, acc_trail = 0;
+#endif
 	if (n > 0) {
 		// zero the padding rows/columns once (finite values everywhere the tiles may touch)
 		for (int q = aligned_row_start(n) + tid; q < aligned_row_start(prow); q += T) L[q] = 0.f;
-		for (int q = tid; q < kPanelStride * prow; q += T) PT[q] = 0.f;
+		for (int q = tid; q < kPanel * prow; q += T) PT[q] = 0.f;
 		// stage the lower triangle of S: batches of independent 64-bit loads (n is even, rows are 8-byte aligned); zeroing
 		// happens after the whole batch is in registers so the loads are not serialised behind the stores
 		{
@@ -335,158 +537,25 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_blocked_kernel(Ar
 			if (clear_corner) sys.corner_rhs[k] = 0.f;
 		}
 		__syncthreads();
+		NNRT_STAMP(0);
 		for (int j = 0; j < n; j += kPanel) {
 			const int nb = min(kPanel, n - j);
-			// ---- panel phase
-			for (int i = j + tid; i < rows; i += T) {
-				if (i > j && i < j + nb) continue;  // rows of the diagonal block are written by the thread of row j
-				float d[kPanel][kPanel], inv[kPanel];
-#pragma unroll
-				for (int r = 0; r < kPanel; r++) {
-					const float* Lr = L + aligned_row_start(min(j + r, rows - 1)) + j;
-#pragma unroll
-					for (int c = 0; c <= r; c++) d[r][c] = (r < nb) ? Lr[c] : (r == c ? 1.f : 0.f);
-				}
-				bool ok = true;
-#pragma unroll
-				for (int c = 0; c < kPanel; c++) {
-					float v = d[c][c];
-#pragma unroll
-					for (int k = 0; k < c; k++) v = fmaf(-d[c][k], d[c][k], v);
-					if (!(v > 0.f)) ok = false;
-					inv[c] = rsqrtf(v);
-					d[c][c] = v * inv[c];
-#pragma unroll
-					for (int r = c + 1; r < kPanel; r++) {
-						float w = d[r][c];
-#pragma unroll
-						for (int k = 0; k < c; k++) w = fmaf(-d[r][k], d[c][k], w);
-						d[r][c] = w * inv[c];
-					}
-				}
-				if (i == j) {
-					if (!ok) atomicExch(sys.flags + 2, 1);
-#pragma unroll
-					for (int r = 0; r < kPanel; r++) {
-						if (r < nb) {
-							inv_diag[j + r] = inv[r];
-							float* Lr = L + aligned_row_start(j + r) + j;
-#pragma unroll
-							for (int c = 0; c <= r; c++) Lr[c] = d[r][c];
-						}
-					}
-				} else {
-					float* Li = L + aligned_row_start(i) + j;
-					float a[kPanel];
-					if (nb == kPanel) {
-						const float4 lo = *reinterpret_cast<const float4*>(Li), hi = *reinterpret_cast<const float4*>(Li + 4);
-						a[0] = lo.x; a[1] = lo.y; a[2] = lo.z; a[3] = lo.w; a[4] = hi.x; a[5] = hi.y; a[6] = hi.z; a[7] = hi.w;
-					} else {
-#pragma unroll
-						for (int c = 0; c < kPanel; c++) a[c] = (c < nb) ? Li[c] : 0.f;
-					}
-#pragma unroll
-					for (int c = 0; c < kPanel; c++) {
-						float w = a[c];
-#pragma unroll
-						for (int k = 0; k < c; k++) w = fmaf(-a[k], d[c][k], w);
-						a[c] = w * inv[c];
-					}
-					if (nb == kPanel) {
-						*reinterpret_cast<float4*>(Li) = make_float4(a[0], a[1], a[2], a[3]);
-						*reinterpret_cast<float4*>(Li + 4) = make_float4(a[4], a[5], a[6], a[7]);
-						float* P = PT + i * kPanelStride;
-						*reinterpret_cast<float4*>(P) = make_float4(a[0], a[1], a[2], a[3]);
-						*reinterpret_cast<float4*>(P + 4) = make_float4(a[4], a[5], a[6], a[7]);
-					} else {
-#pragma unroll
-						for (int c = 0; c < kPanel; c++)
-							if (c < nb) Li[c] = a[c];
-					}
-				}
-			}
+			if (nb == kPanel) panel_phase<true>(L, PT, inv_diag, sys.flags, j, nb, rows, prow);
+			else panel_phase<false>(L, PT, inv_diag, sys.flags, j, nb, rows, prow);
 			__syncthreads();
+			NNRT_ACC(acc_panel);
 			if (nb < kPanel) break;  // a partial last panel leaves only the rhs row, which has no columns >= n to update
-			// ---- trailing phase: 4-row groups [i0, i0+3] from j + 8, 4-column tiles k in [j + 8, i0]
-			const int first = j + kPanel;
-			for (int i0 = first + warp * 4; i0 < rows; i0 += warps * 4) {
-				float4 pr[4][2];
-				float* Lrow[4];
-#pragma unroll
-				for (int r = 0; r < 4; r++) {
-					Lrow[r] = L + aligned_row_start(i0 + r);
-					const float* P = PT + (i0 + r) * kPanelStride;
-					pr[r][0] = *reinterpret_cast<const float4*>(P);
-					pr[r][1] = *reinterpret_cast<const float4*>(P + 4);
-				}
-				for (int k = first + lane * 4; k <= i0; k += 128) {
-					float4 pk[4][2], v[4];
-#pragma unroll
-					for (int c = 0; c < 4; c++) {
-						const float* P = PT + (k + c) * kPanelStride;
-						pk[c][0] = *reinterpret_cast<const float4*>(P);
-						pk[c][1] = *reinterpret_cast<const float4*>(P + 4);
-					}
-#pragma unroll
-					for (int r = 0; r < 4; r++) v[r] = *reinterpret_cast<const float4*>(Lrow[r] + k);
-#pragma unroll
-					for (int r = 0; r < 4; r++) {
-#pragma unroll
-						for (int h = 0; h < 2; h++) {
-							const float4 a = pr[r][h];
-							v[r].x = fmaf(-a.x, pk[0][h].x, v[r].x); v[r].y = fmaf(-a.x, pk[1][h].x, v[r].y);
-							v[r].z = fmaf(-a.x, pk[2][h].x, v[r].z); v[r].w = fmaf(-a.x, pk[3][h].x, v[r].w);
-							v[r].x = fmaf(-a.y, pk[0][h].y, v[r].x); v[r].y = fmaf(-a.y, pk[1][h].y, v[r].y);
-							v[r].z = fmaf(-a.y, pk[2][h].y, v[r].z); v[r].w = fmaf(-a.y, pk[3][h].y, v[r].w);
-							v[r].x = fmaf(-a.z, pk[0][h].z, v[r].x); v[r].y = fmaf(-a.z, pk[1][h].z, v[r].y);
-							v[r].z = fmaf(-a.z, pk[2][h].z, v[r].z); v[r].w = fmaf(-a.z, pk[3][h].z, v[r].w);
-							v[r].x = fmaf(-a.w, pk[0][h].w, v[r].x); v[r].y = fmaf(-a.w, pk[1][h].w, v[r].y);
-							v[r].z = fmaf(-a.w, pk[2][h].w, v[r].z); v[r].w = fmaf(-a.w, pk[3][h].w, v[r].w);
-						}
-					}
-#pragma unroll
-					for (int r = 0; r < 4; r++) *reinterpret_cast<float4*>(Lrow[r] + k) = v[r];
-				}
-			}
+			trailing_phase(L, PT, j + kPanel, rows, prow);
 			__syncthreads();
+			NNRT_ACC(acc_trail);
 		}
-		// ---- blocked back substitution L^T x = y, y = row n of L (forward substitution happened in the factorisation)
-		for (int k = tid; k < n; k += T) ybuf[k] = L[aligned_row_start(n) + k];
+#ifdef NNRT_PHASE_TIMING
+		if (tid == 0) { g_phase_clock[1] = acc_panel; g_phase_clock[2] = acc_trail; }
+#endif
+		if (tid < 32) back_substitution_warp(L, inv_diag, ysh, xs, n);
 		__syncthreads();
-		int p = 0;
-		for (int j = ((n - 1) / kPanel) * kPanel; j >= 0; j -= kPanel) {
-			const int nb = min(kPanel, n - j);
-			const float* src = ybuf + p * prow;
-			float* dst = ybuf + (p ^ 1) * prow;
-			for (int k = tid; k < j + nb; k += T) {
-				float xb[kPanel];
-#pragma unroll
-				for (int c = kPanel - 1; c >= 0; c--) {
-					xb[c] = 0.f;
-					if (c < nb) {
-						float v = src[j + c];
-#pragma unroll
-						for (int r = kPanel - 1; r > c; r--)
-							if (r < nb) v = fmaf(-L[aligned_row_start(j + r) + j + c], xb[r], v);
-						xb[c] = v * inv_diag[j + c];
-					}
-				}
-				if (k < j) {
-					float v = src[k];
-#pragma unroll
-					for (int c = 0; c < kPanel; c++)
-						if (c < nb) v = fmaf(-L[aligned_row_start(j + c) + k], xb[c], v);
-					dst[k] = v;
-				} else {
-#pragma unroll
-					for (int c = 0; c < kPanel; c++)
-						if (k == j + c) xs[k] = xb[c];
-				}
-			}
-			__syncthreads();
-			p ^= 1;
-		}
 		for (int k = tid; k < n; k += T) x[sys.arrow_base * 6 + k] = xs[k];
+		NNRT_STAMP(3);
 	}
 	// stem back-substitution: x_i = y_i - sum_e X_e x_C[col(e)]
 	for (int idx = tid; idx < sys.arrow_base * 6; idx += T) {
@@ -503,13 +572,329 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_blocked_kernel(Ar
 	}
 	if (rotations == nullptr) return;
 	__syncthreads();
+	NNRT_STAMP(4);
 	__threadfence_block();
 	for (int node = tid; node < sys.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3);
+#ifdef NNRT_PHASE_TIMING
+	__syncthreads();
+	NNRT_STAMP(5);
+#endif
+}
+
+// Blackwell packed fp32 FMA (FFMA2): two independent IEEE fp32 fused multiply-adds per lane per instruction.
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+	unsigned long long ra, rb, rc, rd;
+	ra = *reinterpret_cast<unsigned long long*>(&a); rb = *reinterpret_cast<unsigned long long*>(&b); rc = *reinterpret_cast<unsigned long long*>(&c);
+	asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+	return *reinterpret_cast<float2*>(&rd);
+}
+__device__ __forceinline__ float negate_bits(float v) { return __int_as_float(__float_as_int(v) ^ (int) 0x80000000u); }  // ALU pipe, not FMA
+
+// ---- register-tiled single-CTA corner solve (n + 1 <= 256) ---------------------------------------------------------------
+// The trailing matrix never round-trips through shared memory: thread t owns ONE 8 x 8 tile (bi, bj), bi >= bj, of the
+// augmented lower triangle (rhs = row n) in 64 registers for the whole factorisation. Tiles are handed out by descending
+// block column, so at panel p the live tiles are exactly threads [0, live(p)) and finished warps fall through to the barriers.
+//   panel p, step A: the threads of block column p (one warp's worth) factor the raw diagonal tile published by its owner
+//                    (redundantly, in registers), solve their own 8 rows against it, publish the strip to PT[c][row] and the
+//                    final rows to the packed factor Lf (read by the back substitution only).
+//   panel p, step B: every live tile with bj > p does its rank-8 update from PT: 32 LDS.128 per 512 FMAs.
+// Shared-memory traffic per panel is the panel strip only; the smem-resident variant above moves every trailing element twice.
+__host__ __device__ inline size_t regtile_corner_floats(int n) {
+	const int tr = (n + 1 + kTile - 1) / kTile, prow = tr * kTile;
+	return (size_t) aligned_row_start(prow) + (size_t) kTile * prow /*PT*/ + 64 /*raw diag*/ + (size_t) tr * 64 /*W*/ + (size_t) prow + 32 /*xs*/ +
+	       (size_t) ((n + 31) / 32) * 1024 /*Dinv*/ + (size_t) prow /*inv_diag*/ + 64;
+}
+__host__ __device__ inline bool regtile_corner_fits(int n) {
+	const int tr = (n + 1 + kTile - 1) / kTile, tc = (n + kTile - 1) / kTile;
+	// tiles (bi >= bj): sum over bj of (tr - bj)
+	const int tiles = tc * tr - tc * (tc - 1) / 2;
+	return n > 0 && n + 1 <= kRegTileMaxRows && tiles <= kCornerThreads && regtile_corner_floats(n) * sizeof(float) <= 227 * 1024;
+}
+
+__global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(ArrowheadSystem sys, float* __restrict__ x,
+                                                                              float* __restrict__ rotations, float* __restrict__ translations,
+                                                                              int clear_corner) {
+	extern __shared__ __align__(16) float smem[];
+	const int tid = threadIdx.x, T = blockDim.x;
+	const int nc = sys.node_count - sys.arrow_base, n = nc * 6;
+	const int tr = (n + 1 + kTile - 1) / kTile, tc = (n + kTile - 1) / kTile, prow = tr * kTile;
+	float* Lf = smem;                                         // final factor, aligned-packed rows (back substitution)
+	float* PT = Lf + aligned_row_start(prow);                 // [8][prow] current panel strip, transposed
+	float* D11 = PT + kTile * prow;                           // [64] raw diagonal tile of the next panel
+	float* W = D11 + 64;                                      // [tr][64] inverse of each factored diagonal block (lower, row-major 8x8)
+	float* xs = W + tr * 64;                                  // [prow + 32] corner solution
+	float* Dinv = xs + prow + 32;                             // [groups][32][32] inverses of the 32 x 32 diagonal blocks of L
+	float* inv_diag = Dinv + ((n + 31) / 32) * 1024;          // [prow] 1 / L_jj
+#ifdef NNRT_PHASE_TIMING
+	long long t_phase = clock64(), acc_panel = 0, acc_trail = 0;
+#endif
+	// ---- tile assignment: block columns in descending order, rows ascending inside a column
+	int bi = -1, bj = -1;
+	{
+		int offset = 0;
+		for (int b = tc - 1; b >= 0; b--) {
+			const int count = tr - b;
+			if (tid >= offset && tid < offset + count) { bj = b; bi = b + (tid - offset); }
+			offset += count;
+		}
+	}
+	const bool has_tile = bj >= 0;
+	float a[kTile][kTile];
+	// ---- load this thread's tile: the stem kernel accumulated S and the rhs row directly in tile-packed order, so the tile is
+	// 16 coalesced 128-bit loads; the buffer is zeroed behind the load for the next iteration's accumulation
+	if (has_tile) {
+		float4* tile = reinterpret_cast<float4*>(sys.schur) + (int64_t) tid * 16;
+		float4 v[16];
+#pragma unroll
+		for (int q = 0; q < 16; q++) v[q] = __ldcg(tile + q);
+#pragma unroll
+		for (int r = 0; r < kTile; r++) {
+			a[r][0] = v[2 * r].x; a[r][1] = v[2 * r].y; a[r][2] = v[2 * r].z; a[r][3] = v[2 * r].w;
+			a[r][4] = v[2 * r + 1].x; a[r][5] = v[2 * r + 1].y; a[r][6] = v[2 * r + 1].z; a[r][7] = v[2 * r + 1].w;
+		}
+		if (clear_corner) {
+#pragma unroll
+			for (int q = 0; q < 16; q++) tile[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+		}
+		if (bi == 0 && bj == 0) {
+#pragma unroll
+			for (int r = 0; r < kTile; r++)
+#pragma unroll
+				for (int c = 0; c < kTile; c++) D11[r * kTile + c] = a[r][c];
+		}
+	}
+	__syncthreads();
+	NNRT_STAMP(0);
+	for (int p = 0; p < tc; p++) {
+		const int j = p * kTile, nb = min(kTile, n - j);
+		if (bj == p) {
+			// ---- step A: factor the diagonal tile (redundantly), then finish this thread's rows
+			float d[kTile][kTile], inv[kTile];
+#pragma unroll
+			for (int r = 0; r < kTile; r++)
+#pragma unroll
+				for (int c = 0; c <= r; c++) d[r][c] = (r < nb) ? D11[r * kTile + c] : (r == c ? 1.f : 0.f);
+			bool ok = true;
+#pragma unroll
+			for (int c = 0; c < kTile; c++) {
+				float v = d[c][c];
+#pragma unroll
+				for (int k = 0; k < c; k++) v = fmaf(-d[c][k], d[c][k], v);
+				if (!(v > 0.f)) ok = false;
+				inv[c] = rsqrtf(v);
+				d[c][c] = v * inv[c];
+#pragma unroll
+				for (int r = c + 1; r < kTile; r++) {
+					float w = d[r][c];
+#pragma unroll
+					for (int k = 0; k < c; k++) w = fmaf(-d[r][k], d[c][k], w);
+					d[r][c] = w * inv[c];
+				}
+			}
+			if (bi == p) {
+				if (!ok) atomicExch(sys.flags + 2, 1);
+				// final rows of the diagonal block + inverse of the block for the back substitution
+#pragma unroll
+				for (int r = 0; r < kTile; r++) {
+					float* Lr = Lf + aligned_row_start(j + r) + j;
+					if (r < nb) {
+						inv_diag[j + r] = inv[r];
+#pragma unroll
+						for (int c = 0; c <= r; c++) Lr[c] = d[r][c];
+					} else {
+						// rows below a partial last block (the rhs row among them): forward-substitute against the block
+#pragma unroll
+						for (int c = 0; c < kTile; c++) {
+							float w = a[r][c];
+#pragma unroll
+							for (int k = 0; k < c; k++) w = fmaf(-a[r][k], d[c][k], w);
+							a[r][c] = w * inv[c];
+							if (c < nb) Lr[c] = a[r][c];
+						}
+					}
+				}
+				float* Wp = W + p * 64;
+#pragma unroll
+				for (int c = 0; c < kTile; c++) {
+					float w[kTile];
+#pragma unroll
+					for (int r = 0; r < kTile; r++) {
+						if (r < c) w[r] = 0.f;
+						else if (r == c) w[r] = inv[c];
+						else {
+							float acc = 0.f;
+#pragma unroll
+							for (int k = c; k < r; k++) acc = fmaf(d[r][k], w[k], acc);
+							w[r] = -acc * inv[r];
+						}
+						Wp[r * kTile + c] = w[r];
+					}
+				}
+			} else {
+#pragma unroll
+				for (int r = 0; r < kTile; r++) {
+#pragma unroll
+					for (int c = 0; c < kTile; c++) {
+						float w = a[r][c];
+#pragma unroll
+						for (int k = 0; k < c; k++) w = fmaf(-a[r][k], d[c][k], w);
+						a[r][c] = w * inv[c];
+					}
+				}
+				const int row0 = bi * kTile;
+#pragma unroll
+				for (int c = 0; c < kTile; c++) {
+					*reinterpret_cast<float4*>(PT + c * prow + row0) = make_float4(a[0][c], a[1][c], a[2][c], a[3][c]);
+					*reinterpret_cast<float4*>(PT + c * prow + row0 + 4) = make_float4(a[4][c], a[5][c], a[6][c], a[7][c]);
+				}
+#pragma unroll
+				for (int r = 0; r < kTile; r++) {
+					float* Lr = Lf + aligned_row_start(row0 + r) + j;
+					*reinterpret_cast<float4*>(Lr) = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
+					*reinterpret_cast<float4*>(Lr + 4) = make_float4(a[r][4], a[r][5], a[r][6], a[r][7]);
+				}
+			}
+		}
+		__syncthreads();
+		NNRT_ACC(acc_panel);
+		if (bj > p) {
+			// ---- step B: rank-8 update of the register tile
+			const int row0 = bi * kTile, col0 = bj * kTile;
+#ifdef NNRT_PHASE_TIMING
+			const long long tb0 = clock64();
+#endif
+			// c-loop kept rolled (two steps per trip, operands of the next step prefetched) so the body stays inside the L0
+			// instruction cache; the fully unrolled form is fetch-bound (measured 2.3 cycles / instruction)
+			const float* pr_base = PT + row0;
+			const float* pk_base = PT + col0;
+			float4 r0 = *reinterpret_cast<const float4*>(pr_base), r1 = *reinterpret_cast<const float4*>(pr_base + 4);
+			float4 k0 = *reinterpret_cast<const float4*>(pk_base), k1 = *reinterpret_cast<const float4*>(pk_base + 4);
+#pragma unroll 1
+			for (int c = 0; c < kTile; c += 2) {
+				const float* pr1 = pr_base + (c + 1) * prow;
+				const float* pk1 = pk_base + (c + 1) * prow;
+				const float4 s0 = *reinterpret_cast<const float4*>(pr1), s1 = *reinterpret_cast<const float4*>(pr1 + 4);
+				const float4 q0 = *reinterpret_cast<const float4*>(pk1), q1 = *reinterpret_cast<const float4*>(pk1 + 4);
+				{
+					const float pr[kTile] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+					const float pk[kTile] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
+#pragma unroll
+					for (int r = 0; r < kTile; r++)
+#pragma unroll
+						for (int cc = 0; cc < kTile; cc++) a[r][cc] = fmaf(-pr[r], pk[cc], a[r][cc]);
+				}
+				const int cn = min(c + 2, kTile - 1);
+				const float* pr2 = pr_base + cn * prow;
+				const float* pk2 = pk_base + cn * prow;
+				r0 = *reinterpret_cast<const float4*>(pr2); r1 = *reinterpret_cast<const float4*>(pr2 + 4);
+				k0 = *reinterpret_cast<const float4*>(pk2); k1 = *reinterpret_cast<const float4*>(pk2 + 4);
+				{
+					const float pr[kTile] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+					const float pk[kTile] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+					for (int r = 0; r < kTile; r++)
+#pragma unroll
+						for (int cc = 0; cc < kTile; cc++) a[r][cc] = fmaf(-pr[r], pk[cc], a[r][cc]);
+				}
+			}
+#ifdef NNRT_PHASE_TIMING
+			if (tid == 0 && p == 0) g_phase_clock[12] = clock64() - tb0;
+#endif
+			if (bi == p + 1 && bj == p + 1) {
+#pragma unroll
+				for (int r = 0; r < kTile; r++)
+#pragma unroll
+					for (int c = 0; c < kTile; c++) D11[r * kTile + c] = a[r][c];
+			}
+		}
+		__syncthreads();
+#ifdef NNRT_PHASE_TIMING
+		if (tid == 0 && (p == 0 || p == 8 || p == 16 || p == 24)) g_phase_clock[8 + p / 8] = clock64() - t_phase;
+#endif
+		NNRT_ACC(acc_trail);
+	}
+#ifdef NNRT_PHASE_TIMING
+	if (tid == 0) { g_phase_clock[1] = acc_panel; g_phase_clock[2] = acc_trail; }
+#endif
+	// ---- back substitution L^T x = y (y = row n of Lf), rows in groups of 32.
+	// (I) every 32 x 32 diagonal block of L is inverted explicitly, one thread per column (256 independent forward substitutions,
+	//     all groups at once); (II) per group, top down: the owning warp forms x_g = Linv_gg^T y_g as a 32-term dot product per
+	//     lane (y_g by shuffle), one block barrier publishes x_g, every thread above folds it into its y (32 FMAs).
+	{
+		const int lane = tid & 31, warp = tid >> 5;
+		const int groups = (n + 31) >> 5;
+		if (warp < groups) {
+			const int base = warp << 5, jc = base + lane;
+			float z[32];
+#pragma unroll
+			for (int r = 0; r < 32; r++) {
+				float acc = 0.f;
+				const bool row_ok = base + r < n;
+				if (r > 0) {
+					const float* Lr = Lf + aligned_row_start(row_ok ? base + r : base) + base;
+#pragma unroll
+					for (int k = 0; k < r; k++) acc = fmaf(Lr[k], z[k], acc);
+				}
+				// rows >= n read padding above: never let those values (possibly NaN bit patterns left in shared memory) through
+				const float di = row_ok ? inv_diag[base + r] : 0.f;
+				z[r] = !row_ok ? 0.f : (r == lane) ? di : (r > lane ? -acc * di : 0.f);
+				Dinv[(warp * 32 + r) * 32 + lane] = (jc < n) ? z[r] : 0.f;
+			}
+		}
+		float y = (tid < n) ? Lf[aligned_row_start(n) + tid] : 0.f;
+		__syncthreads();
+		for (int g = groups - 1; g >= 0; g--) {
+			const int base = g << 5;
+			if (warp == g) {
+				const float* Dg = Dinv + g * 1024 + lane;
+				float acc = 0.f;
+#pragma unroll
+				for (int r = 0; r < 32; r++) acc = fmaf(Dg[r * 32], __shfl_sync(0xFFFFFFFFu, y, r), acc);
+				xs[base + lane] = acc;
+			}
+			__syncthreads();
+			if (tid < base) {
+#pragma unroll 8
+				for (int c = 0; c < 32; c++)
+					if (base + c < n) y = fmaf(-Lf[aligned_row_start(base + c) + tid], xs[base + c], y);
+			}
+		}
+		__syncthreads();
+		for (int k = tid; k < n; k += T) x[sys.arrow_base * 6 + k] = xs[k];
+		NNRT_STAMP(3);
+	}
+	// stem back-substitution: x_i = y_i - sum_e X_e x_C[col(e)]
+	for (int idx = tid; idx < sys.arrow_base * 6; idx += T) {
+		const int i = idx / 6, r = idx - i * 6;
+		float acc = sys.stem_y[idx];
+		for (int e = sys.row_offsets[i]; e < sys.row_offsets[i + 1]; e++) {
+			const int w = sys.row_blocks[e];
+			const float* X = sys.wing_x + (int64_t) w * 36 + r * 6;
+			const float* xv = xs + (sys.wing_columns[w] - sys.arrow_base) * 6;
+#pragma unroll
+			for (int k = 0; k < 6; k++) acc = fmaf(-X[k], xv[k], acc);
+		}
+		x[idx] = acc;
+	}
+	if (rotations == nullptr) return;
+	__syncthreads();
+	NNRT_STAMP(4);
+	__threadfence_block();
+	for (int node = tid; node < sys.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3);
+#ifdef NNRT_PHASE_TIMING
+	__syncthreads();
+	NNRT_STAMP(5);
+#endif
 }
 
 size_t corner_scratch_bytes(int corner_blocks) {
 	const int64_t n = (int64_t) corner_blocks * 6;
 	return (size_t) (((n + 1) * (n + 2) / 2 + (n + 1)) * sizeof(float));
+}
+bool corner_uses_tile_packed_schur(int corner_blocks) { return regtile_corner_fits(corner_blocks * 6); }
+size_t corner_schur_floats(int corner_blocks) {
+	const size_t n = (size_t) corner_blocks * 6, dense = n * n, packed = (size_t) corner_tile_count((int) n) * 64;
+	return (dense > packed ? dense : packed) + 64;
 }
 bool corner_needs_global_scratch(int corner_blocks) { return blocked_corner_floats(corner_blocks * 6) * sizeof(float) > 227 * 1024; }
 
@@ -523,6 +908,16 @@ int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotati
 	const int n = (sys.node_count - sys.arrow_base) * 6;
 	constexpr size_t kMaxShared = 227 * 1024;
 	const size_t blocked_bytes = blocked_corner_floats(n) * sizeof(float);
+	if (sys.schur_tile_packed) {
+		if (!regtile_corner_fits(n)) return kInvalidArgument;
+		static bool regtile_attribute_set = false;
+		if (!regtile_attribute_set) {
+			if (cudaFuncSetAttribute(corner_solve_regtile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kMaxShared) != cudaSuccess) return kCudaError;
+			regtile_attribute_set = true;
+		}
+		corner_solve_regtile_kernel<<<1, kCornerThreads, regtile_corner_floats(n) * sizeof(float), s>>>(sys, x, node_rotations, node_translations, clear_corner ? 1 : 0);
+		return kOk;
+	}
 	if (blocked_bytes <= kMaxShared) {
 		static bool blocked_attribute_set = false;
 		if (!blocked_attribute_set) {

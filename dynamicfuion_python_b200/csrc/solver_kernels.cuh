@@ -25,8 +25,9 @@ struct ArrowheadSystem {
 	float* inverted_stem;           // [arrow_base,36]
 	float* stem_y;                  // [arrow_base,6]
 	float* wing_x;                  // [W,36]  D^-1 B
-	float* schur;                   // [(6Nc)^2], must be zero on entry
-	float* corner_rhs;              // [6Nc], must be zero on entry
+	float* schur;                   // dense [(6Nc)^2], or tile-packed lower triangle + rhs row (schur_tile_packed); zero on entry
+	float* corner_rhs;              // [6Nc], must be zero on entry (unused when schur_tile_packed)
+	int schur_tile_packed;          // 1: the register-tiled corner kernel consumes `schur` as [tile][8][8] (see corner_tile_index)
 	int* flags;                     // flags[2] set when a block is not positive definite
 };
 
@@ -35,6 +36,8 @@ void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s);
 int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotations, float* node_translations, bool clear_corner,
                         float* scratch_global, cudaStream_t s);
 size_t corner_scratch_bytes(int corner_blocks);
+bool corner_uses_tile_packed_schur(int corner_blocks);   // true when launch_corner_solve will pick the register-tiled kernel
+size_t corner_schur_floats(int corner_blocks);            // allocation size of `schur` valid for either layout
 bool corner_needs_global_scratch(int corner_blocks);  // corner too large for the single-SM shared-memory kernel
 
 }  // namespace nnrt_b200

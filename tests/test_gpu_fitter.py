@@ -125,18 +125,42 @@ def test_single_iteration_parity(nnrt, oracle, config, h, w):
     np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
 
 
-def test_ten_iterations_track_oracle(nnrt, oracle):
-    """Ten free-running iterations: the state after every iteration count stays within 1e-3 of the oracle's, and the fit converges."""
+def test_ten_consecutive_iterations_parity(nnrt, oracle):
+    """Ten consecutive GN iterations, each checked against the oracle started from the SAME state (the GPU's state before that
+    iteration): deltas within 1e-3 relative (BASELINE.json), face indices within the reference's own 20-pixel tolerance."""
     s = scene_with_target(oracle, "tinyr", 120, 160)
-    for iters in (2, 5, 10):
-        ref = oracle_fit(oracle, s, iters)
-        wf, fitter = _gpu_fit(nnrt, s, iters)
-        scale = np.abs(ref["translations"]).max()
-        assert np.abs(_np(wf.node_translations) - ref["translations"]).max() <= 1e-3 * scale + 1e-6
-        assert np.abs(_np(wf.node_rotations) - ref["rotations"]).max() <= 1e-4
+    G = nnrt.geometry
+    wf = G.HierarchicalGraphWarpField(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
+                                      G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
+    fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=1, preconditioning_dampening_factor=s["lm_factor"],
+                                                        arap_term_weight=s["arap_term_weight"])
+    for it in range(10):
+        R0, t0 = _np(wf.node_rotations).copy(), _np(wf.node_translations).copy()
+        fitter.fit_to_image(wf, (s["positions"], s["normals"], s["triangles"]), None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4),
+                            (s["height"], s["width"]), anchors=s["anchors"], anchor_weights=s["anchor_weights"])
+        fitter.check_status()
+        ref = oracle_fit(oracle, s, 1, rotations=R0, translations=t0)
         d = fitter.diagnostics()
-        mismatch = (_np(d["pixel_face_indices"]) != ref["pixel_faces"]).sum()
-        assert mismatch <= 20, mismatch  # the reference's own CPU/CUDA tolerance (cpp/tests/test_rasterize.cpp:281,300)
+        mismatch = int((_np(d["pixel_face_indices"]) != ref["pixel_faces"]).sum())
+        assert mismatch <= 20, (it, mismatch)  # cpp/tests/test_rasterize.cpp:281,300
+        if mismatch == 0:
+            ok, worst = rel_close(_np(d["hessian_diagonal"]), ref["hessian_diag"][0], 1e-4)
+            assert ok, f"iteration {it}: J^T J {worst}"
+        ok, worst = rel_close(_np(d["deltas"]), ref["deltas"][0], 1e-3, floor_scale=1e-2)
+        assert ok, f"iteration {it}: deltas {worst}"
+        np.testing.assert_allclose(_np(wf.node_translations), ref["translations"], rtol=1e-3, atol=1e-6)
+        np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
+
+
+def test_ten_iterations_free_running(nnrt, oracle):
+    """Ten free-running iterations in one graph launch: the fit converges towards the ground truth and stays close to the oracle's
+    free-running state (two fp32 implementations of an iteration drift apart slowly; per-iteration parity is tested above)."""
+    s = scene_with_target(oracle, "tinyr", 120, 160)
+    ref = oracle_fit(oracle, s, 10)
+    wf, fitter = _gpu_fit(nnrt, s, 10)
+    scale = np.abs(ref["translations"]).max()
+    assert np.abs(_np(wf.node_translations) - ref["translations"]).max() <= 5e-2 * scale
+    assert np.abs(_np(wf.node_rotations) - ref["rotations"]).max() <= 1e-2
     err = np.abs(_np(wf.node_translations) - s["translations_gt"]).max()
     assert err < 0.5 * np.abs(s["translations_gt"]).max()
 

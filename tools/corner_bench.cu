@@ -1,0 +1,76 @@
+// Developer harness (not shipped): times the arrowhead stem + corner kernels on a random 208+41 system, checks x against a
+// dense float64 solve on the host, and prints the corner kernel's phase breakdown from clock64 stamps (-DNNRT_PHASE_TIMING).
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -fmad=false -std=c++17 -DNNRT_PHASE_TIMING -o tools/corner_bench tools/corner_bench.cu
+#include <cstdio>
+#include <cstdlib>
+#include <cmath>
+#include <vector>
+#include <random>
+__device__ long long g_phase_clock[16];
+#include "../dynamicfuion_python_b200/csrc/solver_kernels.cu"
+namespace nnrt_b200 { void set_last_error(const char*, ...) {} }
+using namespace nnrt_b200;
+
+template<typename T> T* upload(const std::vector<T>& v) { T* d; cudaMalloc(&d, sizeof(T) * (v.size() + 1)); cudaMemcpy(d, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice); return d; }
+
+int main(int argc, char** argv) {
+	const int base = argc > 1 ? atoi(argv[1]) : 208, nc = argc > 2 ? atoi(argv[2]) : 41, deg = 4, N = base + nc, n = nc * 6;
+	std::mt19937 rng(7); std::normal_distribution<float> g(0.f, 1.f);
+	std::vector<float> diag((size_t) N * 36), rhs((size_t) N * 6), wing((size_t) base * deg * 36);
+	std::vector<int> cols((size_t) base * deg), off(base + 2), blocks((size_t) base * deg);
+	for (int i = 0; i < N; i++) {
+		float a[36]; for (auto& v : a) v = g(rng);
+		for (int r = 0; r < 6; r++) for (int c = 0; c < 6; c++) { float s = 0; for (int k = 0; k < 6; k++) s += a[r * 6 + k] * a[c * 6 + k]; diag[(size_t) i * 36 + r * 6 + c] = 4 * (s + (r == c ? 6.f : 0.f)); }
+	}
+	for (auto& v : rhs) v = g(rng);
+	for (auto& v : wing) v = 0.3f * g(rng);
+	for (int i = 0; i < base; i++) { off[i] = i * deg; for (int e = 0; e < deg; e++) { cols[i * deg + e] = base + (i * 7 + e * 11) % nc; blocks[i * deg + e] = i * deg + e; } }
+	off[base] = base * deg;
+	ArrowheadSystem sys{};
+	sys.node_count = N; sys.arrow_base = base; sys.diagonal_blocks = upload(diag); sys.rhs = upload(rhs); sys.wing_blocks = upload(wing);
+	sys.wing_columns = upload(cols); sys.row_offsets = upload(off); sys.row_blocks = upload(blocks);
+	std::vector<float> z((size_t) n * n + (size_t) N * 36 + 64, 0.f);
+	sys.inverted_stem = upload(z); sys.stem_y = upload(z); sys.wing_x = upload(std::vector<float>((size_t) base * deg * 36, 0.f));
+	sys.schur = upload(z); sys.corner_rhs = upload(z); sys.schur_tile_packed = corner_uses_tile_packed_schur(nc) ? 1 : 0; sys.flags = upload(std::vector<int>(8, 0));
+	float* x = upload(std::vector<float>((size_t) N * 6, 0.f));
+	float* R = upload(std::vector<float>((size_t) N * 9, 0.f)); float* t = upload(std::vector<float>((size_t) N * 3, 0.f));
+	cudaEvent_t e0, e1, e2; cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
+	float ms_stem = 0, ms_corner = 0; const int reps = 20;
+	for (int rep = 0; rep < reps + 3; rep++) {
+		cudaEventRecord(e0); launch_stem_eliminate(sys, 0); cudaEventRecord(e1);
+		int rc = launch_corner_solve(sys, x, R, t, true, nullptr, 0); cudaEventRecord(e2); cudaEventSynchronize(e2);
+		if (rc) { printf("launch rc %d\n", rc); return 1; }
+		float a, b; cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);
+		if (rep >= 3) { ms_stem += a; ms_corner += b; }
+	}
+	{  // race hunt: many repetitions, every result compared with the first
+		std::vector<float> first((size_t) N * 6), cur((size_t) N * 6);
+		int bad = 0;
+		for (int rep = 0; rep < 300; rep++) {
+			launch_stem_eliminate(sys, 0); launch_corner_solve(sys, x, R, t, true, nullptr, 0);
+			cudaMemcpy(cur.data(), x, sizeof(float) * N * 6, cudaMemcpyDeviceToHost);
+			if (rep == 0) first = cur;
+			double worst = 0; for (int i = 0; i < N * 6; i++) { double d = fabs((double) cur[i] - first[i]); if (!(d <= 1e-4)) worst = 1e9; else worst = fmax(worst, d); }
+			if (worst > 1e-4) { if (bad < 5) printf("  rep %d deviates\n", rep); bad++; }
+		}
+		printf("race hunt: %d / 300 repetitions deviate\n", bad);
+	}
+	printf("stem %.2f us  corner %.2f us  (%s)\n", 1e3 * ms_stem / reps, 1e3 * ms_corner / reps, cudaGetErrorString(cudaGetLastError()));
+	long long ph[16]; cudaMemcpyFromSymbol(ph, g_phase_clock, sizeof(ph));
+	const char* names[] = {"stage S", "panels", "trailing", "backsub", "stem backsub", "node update"};
+	for (int k = 0; k < 6; k++) printf("  %-14s %8lld cycles\n", names[k], ph[k]);
+	printf("  trailing at p=0/8/16/24: %lld %lld %lld %lld   pure step B at p=0 (thread 0): %lld\n", ph[8], ph[9], ph[10], ph[11], ph[12]);
+	// check against dense double solve
+	std::vector<float> hx((size_t) N * 6); cudaMemcpy(hx.data(), x, sizeof(float) * N * 6, cudaMemcpyDeviceToHost);
+	const int M = N * 6; std::vector<double> A((size_t) M * M, 0.0), bb(M);
+	for (int i = 0; i < N; i++) for (int r = 0; r < 6; r++) for (int c = 0; c < 6; c++) A[(size_t) (i * 6 + r) * M + i * 6 + c] = diag[(size_t) i * 36 + r * 6 + c];
+	for (int w = 0; w < base * deg; w++) { int i = w / deg, j = cols[w]; for (int r = 0; r < 6; r++) for (int c = 0; c < 6; c++) { A[(size_t) (i * 6 + r) * M + j * 6 + c] += 0; } }
+	// duplicates (same column twice in a row) are summed by the kernels' Schur update only through separate blocks: emulate by accumulation
+	for (int w = 0; w < base * deg; w++) { int i = w / deg, j = cols[w]; for (int r = 0; r < 6; r++) for (int c = 0; c < 6; c++) { A[(size_t) (i * 6 + r) * M + j * 6 + c] += wing[(size_t) w * 36 + r * 6 + c]; A[(size_t) (j * 6 + c) * M + i * 6 + r] += wing[(size_t) w * 36 + r * 6 + c]; } }
+	for (int i = 0; i < M; i++) bb[i] = rhs[i];
+	for (int k = 0; k < M; k++) { double p = A[(size_t) k * M + k]; for (int i = k + 1; i < M; i++) { double f = A[(size_t) i * M + k] / p; if (f == 0) continue; for (int c = k; c < M; c++) A[(size_t) i * M + c] -= f * A[(size_t) k * M + c]; bb[i] -= f * bb[k]; } }
+	for (int k = M - 1; k >= 0; k--) { double s = bb[k]; for (int c = k + 1; c < M; c++) s -= A[(size_t) k * M + c] * bb[c]; bb[k] = s / A[(size_t) k * M + k]; }
+	double worst = 0, scale = 0; for (int i = 0; i < M; i++) { worst = fmax(worst, fabs(bb[i] - hx[i])); scale = fmax(scale, fabs(bb[i])); }
+	printf("max |x - x_f64| = %.3e (|x|_inf %.3e)\n", worst, scale);
+	return 0;
+}
