@@ -115,8 +115,8 @@ def scaled_motion(s, scale):
 
 STAGES = ["warp_vertices", "face_raster", "band_raster", "assemble", "build_system", "stem_eliminate", "corner_solve_update"]
 STAGE_KERNEL = {"warp_vertices": "warp_vertices_kernel<4>", "face_raster": "face_raster_kernel", "band_raster": "band_raster_kernel",
-                "assemble": "assemble_kernel<4>", "build_system": "build_system_kernel", "stem_eliminate": "stem_eliminate_kernel",
-                "corner_solve_update": "corner_solve_kernel<true>"}
+                "assemble": "assemble_kernel<4>", "build_system": "system_stem_kernel", "stem_eliminate": "(fused into system_stem_kernel)",
+                "corner_solve_update": "corner_solve_regtile_kernel"}
 SETUP_LAUNCHES = 6  # anchors, 3 pack kernels, face-anchor table, reference unprojection
 
 

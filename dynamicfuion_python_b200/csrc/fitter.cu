@@ -169,6 +169,188 @@ __global__ void __launch_bounds__(128) build_system_kernel(GraphDeviceData g, co
 	for (int c = 0; c < 6; c++) rhs[n * 6 + c] = b[c];
 }
 
+// Fused replacement of build_system_kernel + stem_eliminate_kernel on the fitter path: ONE WARP PER NODE.
+//   stem node  : H = data-term block + sum of its edges' ARAP blocks + lambda I (same summation order as build_system_kernel),
+//                wing blocks B_e kept in shared memory, D^-1 by six lanes (one unit column each), y = D^-1 b, X_e = D^-1 B_e,
+//                Schur update S -= B_e1^T X_e2 and rhs update b_C -= X_e^T b straight into the corner kernel's tile-packed buffer.
+//   corner node: H = data-term block + sum over incoming edges (lanes stride over edges, shuffle reduction) + lambda I, scattered
+//                into the corner buffer together with its right-hand side.
+// Saves one launch, the global round trip of the wing blocks and ~30 us of single-thread-per-node latency per iteration.
+constexpr int kStemWarps = 4;
+
+__device__ __forceinline__ float skew_entry(float3 s, int r, int c) {
+	// [[0,-sz,sy],[sz,0,-sx],[-sy,sx,0]]
+	const float v = (r + c == 1) ? s.z : (r + c == 2) ? s.y : s.x;
+	const bool neg = (r == 0 && c == 1) || (r == 1 && c == 2) || (r == 2 && c == 0);
+	return r == c ? 0.f : (neg ? -v : v);
+}
+
+__global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDeviceData g, ArrowheadSystem sys, const float* __restrict__ rotations,
+                                                                      const float* __restrict__ translations, float* __restrict__ accumulators,
+                                                                      float* __restrict__ diag, float* __restrict__ rhs) {
+	__shared__ float s_H[kStemWarps][36], s_b[kStemWarps][8], s_dinv[kStemWarps][36], s_dE[kStemWarps][20];
+	__shared__ float s_B[kStemWarps][kMaxStemDegree][36], s_X[kStemWarps][kMaxStemDegree][36];
+	__shared__ int s_col[kStemWarps][kMaxStemDegree];
+	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+	const int node = blockIdx.x * kStemWarps + wib;
+	if (node >= g.node_count) return;
+	const int nc = sys.node_count - sys.arrow_base, n = nc * 6;
+	float* H = s_H[wib];
+	float* b = s_b[wib];
+	// ---- data term from the pixel accumulators (21 upper-triangular + 6), cleaned for the next iteration
+	{
+		float* acc = accumulators + (int64_t) node * kAccumStride;
+		if (lane < 27) {
+			const float v = acc[lane];
+			acc[lane] = 0.f;
+			if (lane < 21) {
+				int c0 = 0, o = lane;
+				while (o >= 6 - c0) { o -= 6 - c0; c0++; }
+				const int c1 = c0 + o;
+				H[c0 * 6 + c1] = v; H[c1 * 6 + c0] = v;
+			} else {
+				b[lane - 21] = 0.f - v;
+			}
+		}
+	}
+	__syncwarp();
+	if (node < g.arrow_base) {
+		const int e0 = g.out_offsets[node], deg = min(g.out_offsets[node + 1] - e0, kMaxStemDegree);
+		for (int q = 0; q < deg; q++) {
+			const int e = g.out_edges[e0 + q];
+			float3 sk, r; float a;
+			arap_edge(g, rotations, translations, e, sk, a, r);
+			// dE_i (3 x 6) = [skew(s) | a I] staged per warp
+			if (lane < 18) { const int rr = lane / 6, c = lane % 6; s_dE[wib][lane] = c < 3 ? skew_entry(sk, rr, c) : (rr == c - 3 ? a : 0.f); }
+			if (lane == 0) s_col[wib][q] = g.edges[e].y;
+			__syncwarp();
+			const float* dE = s_dE[wib];
+			const float bj = -a;
+			for (int k = lane; k < 36; k += 32) {
+				const int rr = k / 6, c = k % 6;
+				H[k] += sum3(dE[rr] * dE[c], dE[6 + rr] * dE[6 + c], dE[12 + rr] * dE[12 + c]);
+				s_B[wib][q][k] = c < 3 ? 0.f : sum3(dE[rr] * (c == 3 ? bj : 0.f), dE[6 + rr] * (c == 4 ? bj : 0.f), dE[12 + rr] * (c == 5 ? bj : 0.f));
+			}
+			if (lane < 6) b[lane] -= sum3(dE[lane] * r.x, dE[6 + lane] * r.y, dE[12 + lane] * r.z);
+			__syncwarp();
+		}
+		if (lane < 6 && g.lm_factor > 0.f) H[lane * 7] += g.lm_factor;
+		__syncwarp();
+		for (int k = lane; k < 36; k += 32) diag[(int64_t) node * 36 + k] = H[k];
+		if (lane < 6) rhs[node * 6 + lane] = b[lane];
+		// ---- D^-1: every one of six lanes factors H (redundantly) and solves for its unit column
+		if (lane < 6) {
+			float L[36];
+#pragma unroll
+			for (int k = 0; k < 36; k++) L[k] = H[k];
+			bool ok = true;
+#pragma unroll
+			for (int j = 0; j < 6; j++) {
+				float dj = L[j * 6 + j];
+#pragma unroll
+				for (int k = 0; k < j; k++) dj -= L[j * 6 + k] * L[j * 6 + k];
+				if (!(dj > 0.f)) ok = false;
+				dj = sqrtf(dj);
+				L[j * 6 + j] = dj;
+#pragma unroll
+				for (int i = j + 1; i < 6; i++) {
+					float v = L[i * 6 + j];
+#pragma unroll
+					for (int k = 0; k < j; k++) v -= L[i * 6 + k] * L[j * 6 + k];
+					L[i * 6 + j] = v / dj;
+				}
+			}
+			if (!ok && lane == 0) atomicExch(sys.flags + 2, 1);
+			float xcol[6];
+#pragma unroll
+			for (int i = 0; i < 6; i++) {
+				float v = (i == lane) ? 1.f : 0.f;
+#pragma unroll
+				for (int k = 0; k < i; k++) v -= L[i * 6 + k] * xcol[k];
+				xcol[i] = v / L[i * 6 + i];
+			}
+#pragma unroll
+			for (int i = 5; i >= 0; i--) {
+				float v = xcol[i];
+#pragma unroll
+				for (int k = i + 1; k < 6; k++) v -= L[k * 6 + i] * xcol[k];
+				xcol[i] = v / L[i * 6 + i];
+			}
+#pragma unroll
+			for (int i = 0; i < 6; i++) s_dinv[wib][i * 6 + lane] = xcol[i];
+		}
+		__syncwarp();
+		const float* Dinv = s_dinv[wib];
+		if (lane < 6) {
+			float acc = 0.f;
+#pragma unroll
+			for (int k = 0; k < 6; k++) acc += Dinv[lane * 6 + k] * b[k];
+			sys.stem_y[node * 6 + lane] = acc;
+		}
+		// X_e = D^-1 B_e (kept in shared memory for the Schur update, written out for the back substitution)
+		for (int idx = lane; idx < deg * 36; idx += 32) {
+			const int q = idx / 36, k = idx % 36, rr = k / 6, c = k % 6;
+			float acc = 0.f;
+#pragma unroll
+			for (int m = 0; m < 6; m++) acc += Dinv[rr * 6 + m] * s_B[wib][q][m * 6 + c];
+			s_X[wib][q][k] = acc;
+			sys.wing_x[(int64_t) g.out_edges[e0 + q] * 36 + k] = acc;
+		}
+		__syncwarp();
+		// S[c1, c2] -= B_e1^T X_e2 ; with the tile-packed layout only block pairs on or below the diagonal are stored
+		for (int idx = lane; idx < deg * deg * 36; idx += 32) {
+			const int pair = idx / 36, k = idx % 36, rr = k / 6, c = k % 6;
+			const int q1 = pair / deg, q2 = pair % deg;
+			const int c1 = s_col[wib][q1] - sys.arrow_base, c2 = s_col[wib][q2] - sys.arrow_base;
+			if (sys.schur_tile_packed && c1 < c2) continue;
+			float acc = 0.f;
+#pragma unroll
+			for (int m = 0; m < 6; m++) acc += s_B[wib][q1][m * 6 + rr] * s_X[wib][q2][m * 6 + c];
+			const int64_t slot = schur_slot(sys, n, c1 * 6 + rr, c2 * 6 + c);
+			if (slot >= 0) atomicAdd(sys.schur + slot, -acc);
+		}
+		// b_C[c] -= X_e^T b
+		for (int idx = lane; idx < deg * 6; idx += 32) {
+			const int q = idx / 6, c = idx % 6;
+			float acc = 0.f;
+#pragma unroll
+			for (int m = 0; m < 6; m++) acc += s_X[wib][q][m * 6 + c] * b[m];
+			const int col = (s_col[wib][q] - sys.arrow_base) * 6 + c;
+			atomicAdd(sys.schur_tile_packed ? sys.schur + corner_tile_index(n, n, col) : sys.corner_rhs + col, -acc);
+		}
+	} else {
+		const int cj = node - g.arrow_base;
+		float h_add = 0.f, b3 = 0.f, b4 = 0.f, b5 = 0.f;
+		for (int q = g.in_offsets[cj] + lane; q < g.in_offsets[cj + 1]; q += 32) {
+			float3 sk, r; float a;
+			arap_edge(g, rotations, translations, g.in_edges[q], sk, a, r);
+			const float bj = -a;
+			h_add += bj * bj; b3 -= bj * r.x; b4 -= bj * r.y; b5 -= bj * r.z;
+		}
+#pragma unroll
+		for (int off = 16; off >= 1; off >>= 1) {
+			h_add += __shfl_xor_sync(0xFFFFFFFFu, h_add, off); b3 += __shfl_xor_sync(0xFFFFFFFFu, b3, off);
+			b4 += __shfl_xor_sync(0xFFFFFFFFu, b4, off); b5 += __shfl_xor_sync(0xFFFFFFFFu, b5, off);
+		}
+		if (lane == 0) {
+			H[21] += h_add; H[28] += h_add; H[35] += h_add;
+			b[3] += b3; b[4] += b4; b[5] += b5;
+		}
+		__syncwarp();
+		if (lane < 6 && g.lm_factor > 0.f) H[lane * 7] += g.lm_factor;
+		__syncwarp();
+		for (int k = lane; k < 36; k += 32) {
+			diag[(int64_t) node * 36 + k] = H[k];
+			const int64_t slot = schur_slot(sys, n, cj * 6 + k / 6, cj * 6 + k % 6);
+			if (slot >= 0) atomicAdd(sys.schur + slot, H[k]);
+		}
+		if (lane < 6) {
+			rhs[node * 6 + lane] = b[lane];
+			atomicAdd(sys.schur_tile_packed ? sys.schur + corner_tile_index(n, n, cj * 6 + lane) : sys.corner_rhs + cj * 6 + lane, b[lane]);
+		}
+	}
+}
+
 __global__ void __launch_bounds__(256) diagnostics_convert_kernel(const int32_t* __restrict__ faces, const uint8_t* __restrict__ mask_in, int64_t n,
                                                                    int64_t* __restrict__ faces_out, uint8_t* __restrict__ mask_out) {
 	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -184,7 +366,7 @@ struct nnrt_b200_fitter {
 	nnrt_b200_fitter_options opt;
 	int64_t V, F, E; int N, A, H, W;
 	int arrow_base = 0, corner_blocks = 0;
-	bool model_set = false, reference_set = false;
+	bool model_set = false, reference_set = false, fused_stem = true;
 	// arena
 	char* arena = nullptr; size_t arena_bytes = 0, arena_used = 0;
 	int* host_flags = nullptr;  // pinned
@@ -291,7 +473,7 @@ extern "C" void nnrt_b200_fitter_destroy(nnrt_b200_fitter* f) {
 }
 
 extern "C" int64_t nnrt_b200_fitter_workspace_bytes(const nnrt_b200_fitter* f) { return f ? (int64_t) f->arena_bytes : 0; }
-extern "C" int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter*) { return 7; }
+extern "C" int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter* f) { return (f && !f->fused_stem) ? 7 : 6; }
 
 extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vertex_positions, const float* vertex_normals,
                                           const int64_t* triangles, const float* nodes, const int32_t* edges, int32_t arrow_base,
@@ -312,6 +494,7 @@ extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vert
 		NNRT_CHECK_ARG(arrow_base >= 1 && arrow_base <= N, "first_layer_node_count (currently, %d) must be in [1, node_count = %d].", arrow_base, N);
 	} else {
 		arrow_base = N;  // no regularisation edges: block-diagonal system (DeformableMeshToImageFitter.cpp:248-254)
+		f->fused_stem = true;
 	}
 	pack_float4_kernel<<<blocks_for(V, 256), 256, 0, s>>>(vertex_positions, V, f->positions);
 	pack_float4_kernel<<<blocks_for(V, 256), 256, 0, s>>>(vertex_normals, V, f->normals);
@@ -356,6 +539,9 @@ extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vert
 				ew_res[e] = ew_jac[e] = h_cov[i] > h_cov[j] ? h_cov[i] : h_cov[j];
 			}
 		}
+		int max_degree = 0;
+		for (int i = 0; i < arrow_base; i++) max_degree = out_off[i + 1] > max_degree ? out_off[i + 1] : max_degree;
+		f->fused_stem = max_degree <= kMaxStemDegree;
 		for (int i = 0; i < arrow_base; i++) out_off[i + 1] += out_off[i];
 		for (int c = 0; c < nc; c++) in_off[c + 1] += in_off[c];
 		std::vector<int> oc(out_off.begin(), out_off.end()), ic(in_off.begin(), in_off.end());
@@ -471,10 +657,15 @@ static int enqueue_iteration(nnrt_b200_fitter* f, const IterationContext& c, flo
 	if (ev) cudaEventRecord(ev[3], s);
 	if (launch_assemble(c.d, c.p, s) != kOk) return kInvalidArgument;
 	if (ev) cudaEventRecord(ev[4], s);
-	build_system_kernel<<<(f->N + 127) / 128, 128, 0, s>>>(c.g, R, t, f->accum, f->sys_diag, f->sys_rhs, f->wing);
-	if (ev) cudaEventRecord(ev[5], s);
-	launch_stem_eliminate(c.sys, s);
-	if (ev) cudaEventRecord(ev[6], s);
+	if (f->fused_stem) {
+		system_stem_kernel<<<(f->N + kStemWarps - 1) / kStemWarps, kStemWarps * 32, 0, s>>>(c.g, c.sys, R, t, f->accum, f->sys_diag, f->sys_rhs);
+		if (ev) { cudaEventRecord(ev[5], s); cudaEventRecord(ev[6], s); }
+	} else {  // stem rows with more than kMaxStemDegree edges: unfused pair of kernels
+		build_system_kernel<<<(f->N + 127) / 128, 128, 0, s>>>(c.g, R, t, f->accum, f->sys_diag, f->sys_rhs, f->wing);
+		if (ev) cudaEventRecord(ev[5], s);
+		launch_stem_eliminate(c.sys, s);
+		if (ev) cudaEventRecord(ev[6], s);
+	}
 	const int rc = launch_corner_solve(c.sys, f->x, R, t, true, f->corner_scratch, s);
 	if (ev) cudaEventRecord(ev[7], s);
 	if (rc != kOk) return rc;

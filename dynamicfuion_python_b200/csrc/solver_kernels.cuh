@@ -31,6 +31,33 @@ struct ArrowheadSystem {
 	int* flags;                     // flags[2] set when a block is not positive definite
 };
 
+// ---- corner layouts ---------------------------------------------------------------------------------------------------------
+constexpr int kTile = 8;
+constexpr int kCornerThreads = 512;
+constexpr int kRegTileMaxRows = 256;
+
+// Tile-packed Schur layout consumed by corner_solve_regtile_kernel: 8 x 8 tiles (bi >= bj) of the augmented lower triangle
+// (row n = right-hand side), block columns in DESCENDING order, rows ascending inside a column; tile t is thread t's tile.
+__host__ __device__ __forceinline__ int corner_tile_rows(int n) { return (n + 1 + kTile - 1) / kTile; }
+__host__ __device__ __forceinline__ int corner_tile_cols(int n) { return (n + kTile - 1) / kTile; }
+__host__ __device__ __forceinline__ int corner_tile_count(int n) {
+	const int tr = corner_tile_rows(n), tc = corner_tile_cols(n);
+	return tc * tr - tc * (tc - 1) / 2;
+}
+__host__ __device__ __forceinline__ int corner_tile_id(int n, int bi, int bj) {
+	const int tr = corner_tile_rows(n), tc = corner_tile_cols(n), m = tc - 1 - bj;
+	return m * tr - (bj + tc) * m / 2 + (bi - bj);
+}
+// offset of element (row, col), row in [0, n], col in [0, n), row / 8 >= col / 8
+__host__ __device__ __forceinline__ int corner_tile_index(int n, int row, int col) {
+	return corner_tile_id(n, row >> 3, col >> 3) * 64 + (row & 7) * kTile + (col & 7);
+}
+// where the stem kernel accumulates S(row, col): -1 = not stored in this layout (strict upper tile triangle)
+__device__ __forceinline__ int64_t schur_slot(const ArrowheadSystem& sys, int n, int row, int col) {
+	if (!sys.schur_tile_packed) return (int64_t) row * n + col;
+	return (col > row) ? -1 : corner_tile_index(n, row, col);
+}
+
 void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s);
 // x [6N]; if node_rotations != nullptr the update is applied in place; clear_corner zeroes schur / corner_rhs after reading.
 int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotations, float* node_translations, bool clear_corner,

@@ -144,7 +144,9 @@ def test_ten_consecutive_iterations_parity(nnrt, oracle):
         mismatch = int((_np(d["pixel_face_indices"]) != ref["pixel_faces"]).sum())
         assert mismatch <= 20, (it, mismatch)  # cpp/tests/test_rasterize.cpp:281,300
         if mismatch == 0:
-            ok, worst = rel_close(_np(d["hessian_diagonal"]), ref["hessian_diag"][0], 1e-4)
+            # entries below 0.1 % of the largest are sums with heavy cancellation: both fp32 summation orders (oracle: sequential
+            # over the node's pixel list; GPU: warp tree + atomics) carry more than 1e-4 of such an entry
+            ok, worst = rel_close(_np(d["hessian_diagonal"]), ref["hessian_diag"][0], 1e-4, floor_scale=1e-3)
             assert ok, f"iteration {it}: J^T J {worst}"
         ok, worst = rel_close(_np(d["deltas"]), ref["deltas"][0], 1e-3, floor_scale=1e-2)
         assert ok, f"iteration {it}: deltas {worst}"
@@ -152,17 +154,20 @@ def test_ten_consecutive_iterations_parity(nnrt, oracle):
         np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
 
 
-def test_ten_iterations_free_running(nnrt, oracle):
-    """Ten free-running iterations in one graph launch: the fit converges towards the ground truth and stays close to the oracle's
-    free-running state (two fp32 implementations of an iteration drift apart slowly; per-iteration parity is tested above)."""
-    s = scene_with_target(oracle, "tinyr", 120, 160)
+@pytest.mark.parametrize("config,h,w,converges", [("tinyr", 120, 160, False), ("C2r", 240, 320, True)])
+def test_ten_iterations_free_running(nnrt, oracle, config, h, w, converges):
+    """Ten free-running iterations in one graph launch stay close to the oracle's free-running state (two fp32 implementations of
+    the iteration drift apart slowly; per-iteration parity is tested above). On the bench scene (C2r) the reference's iteration is
+    contractive and must reduce the translation error; on tinyr the reference itself oscillates (a corner node slides)."""
+    s = scene_with_target(oracle, config, h, w)
     ref = oracle_fit(oracle, s, 10)
     wf, fitter = _gpu_fit(nnrt, s, 10)
     scale = np.abs(ref["translations"]).max()
     assert np.abs(_np(wf.node_translations) - ref["translations"]).max() <= 5e-2 * scale
     assert np.abs(_np(wf.node_rotations) - ref["rotations"]).max() <= 1e-2
-    err = np.abs(_np(wf.node_translations) - s["translations_gt"]).max()
-    assert err < 0.5 * np.abs(s["translations_gt"]).max()
+    if converges:
+        err = np.abs(_np(wf.node_translations) - s["translations_gt"]).max()
+        assert err < 0.5 * np.abs(s["translations_gt"]).max()
 
 
 def test_tukey_and_huber_options(nnrt, oracle):
