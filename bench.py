@@ -210,10 +210,8 @@ def run_b200(args):
     e2e_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
 
-    times = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms = float(times[0]), float(times[1])
+    from dynamicfuion_python_b200 import frame_batch
+    dev_ms, e2e_ms = frame_batch.max_over_ranks([dev_ms, e2e_ms], dev)  # frames are sharded, no data-path collective: only the clock is reduced
 
     # ---- per-kernel stage times (CUDA events between the 7 launches of an iteration, outside the graph) for the roofline
     stage_ms = np.zeros(7)

@@ -40,7 +40,12 @@ __global__ void __launch_bounds__(256) warp_vertices_kernel(FitterDeviceData d, 
 			const float3 g = make_float3(__ldg(d.nodes + node * 3), __ldg(d.nodes + node * 3 + 1), __ldg(d.nodes + node * 3 + 2));
 			const float3 t = make_float3(__ldg(translations + node * 3), __ldg(translations + node * 3 + 1), __ldg(translations + node * 3 + 2));
 			wp = wp + w[a] * ((g + matvec3(R, pc - g)) + t);
-			wn = wn + w[a] * matvec3(R, nc);
+			{  // scalar folded into the matrix, as Eigen evaluates w * (R * n) (WarpUtilities.h:466)
+				float wR[9];
+#pragma unroll
+				for (int k = 0; k < 9; k++) wR[k] = w[a] * R[k];
+				wn = wn + matvec3(wR, nc);
+			}
 			// Jacobian records use the canonical (un-extrinsic'd) vertex and normal, as the reference does
 			const float3 rv = matvec3(R, p - g);
 			const float3 rn = matvec3(R, n);

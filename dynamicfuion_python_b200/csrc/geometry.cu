@@ -115,7 +115,12 @@ __global__ void __launch_bounds__(256) warp_points_kernel(const float* __restric
 			const float3 g = make_float3(nodes[n * 3], nodes[n * 3 + 1], nodes[n * 3 + 2]);
 			const float3 t = make_float3(translations[n * 3], translations[n * 3 + 1], translations[n * 3 + 2]);
 			wp = wp + weight * ((g + matvec3(R, pc - g)) + t);
-			if (normals) wn = wn + weight * matvec3(R, nc);
+			if (normals) {  // scalar folded into the matrix, as Eigen evaluates w * (R * n) (WarpUtilities.h:466)
+				float wR[9];
+#pragma unroll
+				for (int k = 0; k < 9; k++) wR[k] = weight * R[k];
+				wn = wn + matvec3(wR, nc);
+			}
 		}
 	}
 	warped_points[i * 3] = wp.x; warped_points[i * 3 + 1] = wp.y; warped_points[i * 3 + 2] = wp.z;

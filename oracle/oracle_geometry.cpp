@@ -101,7 +101,14 @@ ORACLE_API void oracle_warp_points_normals(
 				// warped_point += w * (node + R*(p - node) + t)
 				V3 rotated = matvec(R, sub(pc, g));
 				wp = add(wp, scale(weight, add(add(g, rotated), t)));
-				if (normals) wn = add(wn, scale(weight, matvec(R, nc)));
+				if (normals) {
+					// `anchor_weight * (node_rotation * source_normal)` (WarpUtilities.h:466): Eigen folds the scalar into the lazy
+					// 3x3 product, i.e. each coefficient is sum_k (w * R_ik) * n_k — verified bit-exact against the compiled header
+					// (tests/test_oracle_vs_ref.py); w * (R n) differs in the last ulp
+					const float wR[9] = {weight * R[0], weight * R[1], weight * R[2], weight * R[3], weight * R[4], weight * R[5],
+					                     weight * R[6], weight * R[7], weight * R[8]};
+					wn = add(wn, matvec(wR, nc));
+				}
 			}
 		}
 		store3(warped_points + i * 3, wp);

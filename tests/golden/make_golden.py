@@ -1,0 +1,103 @@
+"""Regenerates tests/golden/*.npz from the reference checkout (run in the build container, where /root/reference exists).
+
+Nothing here copies reference source: the script PARSES the inline tensors of the reference's own Catch2 tests (known-answer
+vectors) and sub-samples one of its binary fixtures, and stores them as numpy arrays with their provenance:
+  reference_kats.npz   inline vectors of cpp/tests/test_{anchor_computation,rodrigues,unproject_3d_points,linalg_cholesky,matmul3d}.cpp
+  mesh_warp_219.npz    every 8th vertex of tests/test_data/mesh_warping/test_{input,gt}_mesh.ply + nodes/rotations/translations.npy
+  oracle_fit_tinyr.npz one full GN iteration of the ORACLE on the seeded 'tinyr' scene (regression pin of the oracle itself)
+"""
+import os
+import re
+import sys
+
+import numpy as np
+
+REF = os.environ.get("NNRT_REFERENCE", "/root/reference")
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+_NUM = re.compile(r"[-+]?(?:\d+\.\d*|\.\d+|\d+)(?:[eE][-+]?\d+)?")
+
+
+def inline_tensor(cpp_text, name, occurrence=0):
+    """Values of `o3c::Tensor name(std::vector<T>{ ... }, ...)` as float64 (bools become 0/1)."""
+    text = re.sub(r"//[^\n]*", "", cpp_text)
+    hits = [m for m in re.finditer(r"\b" + re.escape(name) + r"\s*\(\s*std::vector<([^>]+)>\s*\{", text)]
+    m = hits[occurrence]
+    depth, i = 1, m.end()
+    while depth:
+        depth += {"{": 1, "}": -1}.get(text[i], 0)
+        i += 1
+    body = text[m.end():i - 1]
+    if "bool" in m.group(1):
+        return np.array([1.0 if t == "true" else 0.0 for t in re.findall(r"true|false", body)])
+    return np.array([float(t) for t in _NUM.findall(re.sub(r"(?<=[\d.])f\b", "", body))])
+
+
+def read(path):
+    with open(os.path.join(REF, path)) as fh:
+        return fh.read()
+
+
+def read_ply_vertices(path):
+    with open(path, "rb") as fh:
+        header = b""
+        while not header.endswith(b"end_header\n"):
+            header += fh.readline()
+        n = int(re.search(rb"element vertex (\d+)", header).group(1))
+        dt = np.dtype([("p", "<f8", 3), ("n", "<f8", 3), ("c", "u1", 3)])
+        v = np.frombuffer(fh.read(n * dt.itemsize), dtype=dt)
+    return v["p"].copy(), v["n"].copy()
+
+
+def main():
+    out = {}
+    t = read("cpp/tests/test_anchor_computation.cpp")
+    out["anchors/vertices"] = inline_tensor(t, "vertices").reshape(8, 3)
+    out["anchors/nodes"] = inline_tensor(t, "nodes").reshape(2, 3)
+    out["anchors/node_weights"] = inline_tensor(t, "node_weights")
+    out["anchors/anchors_gt_sorted_desc"] = inline_tensor(t, "anchors_gt").reshape(8, 4)
+    out["anchors/weights_gt_sorted_desc"] = inline_tensor(t, "weights_gt").reshape(8, 4)
+    t = read("cpp/tests/test_rodrigues.cpp")
+    out["rodrigues/axis_angle_vectors"] = inline_tensor(t, "axis_angle_vectors").reshape(3, 3)
+    out["rodrigues/expected_matrices"] = inline_tensor(t, "expected_matrices").reshape(3, 3, 3)
+    t = read("cpp/tests/test_unproject_3d_points.cpp")
+    out["unproject/intrinsics"] = inline_tensor(t, "intrinsics").reshape(3, 3)
+    out["unproject/depth_u16"] = inline_tensor(t, "depth").reshape(4, 4)
+    out["unproject/points_gt"] = inline_tensor(t, "points_ground_truth").reshape(16, 3)
+    out["unproject/mask_gt"] = inline_tensor(t, "mask_ground_truth").reshape(16)
+    t = read("cpp/tests/test_mesh_warping.cpp")
+    out["warp9/vertices_gt"] = inline_tensor(t, "warped_plane_vertices_ground_truth").reshape(9, 3)
+    out["warp9/normals_gt"] = inline_tensor(t, "warped_plane_normals_ground_truth").reshape(9, 3)
+    t = read("cpp/tests/test_linalg_cholesky.cpp")
+    for key in ("A_blocks", "B", "expected_X"):
+        try:
+            out["block_cholesky/" + key] = inline_tensor(t, key)
+        except IndexError:
+            pass
+    np.savez_compressed(os.path.join(HERE, "reference_kats.npz"), **out)
+    print("reference_kats.npz:", {k: v.shape for k, v in out.items()})
+
+    d = os.path.join(REF, "tests/test_data/mesh_warping")
+    vin, nin = read_ply_vertices(os.path.join(d, "test_input_mesh.ply"))
+    vgt, _ = read_ply_vertices(os.path.join(d, "test_gt_mesh.ply"))
+    sel = slice(0, None, 8)
+    np.savez_compressed(os.path.join(HERE, "mesh_warp_219.npz"), vertices=vin[sel].astype(np.float32), normals=nin[sel].astype(np.float32),
+                        warped_gt=vgt[sel], nodes=np.load(os.path.join(d, "nodes.npy")), rotations=np.load(os.path.join(d, "rotations.npy")),
+                        translations=np.load(os.path.join(d, "translations.npy")), node_coverage=np.float32(0.05))
+    print("mesh_warp_219.npz:", vin[sel].shape)
+
+    from oracle import oracle_py as oracle
+    from util import scene_with_target, oracle_fit
+    s = scene_with_target(oracle, "tinyr", 120, 160)
+    ref = oracle_fit(oracle, s, 1, parallel=False)
+    np.savez_compressed(os.path.join(HERE, "oracle_fit_tinyr.npz"), hessian_diag=ref["hessian_diag"][0], negative_gradient=ref["negative_gradient"][0],
+                        deltas=ref["deltas"][0], pixel_faces=ref["pixel_faces"].astype(np.int32), residual_sum=np.float64(ref["residuals"].astype(np.float64).sum()),
+                        translations=ref["translations"], rotations=ref["rotations"])
+    print("oracle_fit_tinyr.npz written")
+
+
+if __name__ == "__main__":
+    main()
