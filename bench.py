@@ -373,8 +373,14 @@ def main():
     peak, peak_kind = load_peaks()
     achieved = stage_bytes[dominant] / (stage_ms[dominant] * 1e-3) / 1e9 if stage_ms[dominant] > 0 else 0.0
     iter_ms_profiled = sum(stage_ms.values())
+    traffic = None
+    try:  # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (profiles/ncu_traffic.json)
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
+            traffic = json.load(fh).get(STAGE_KERNEL[dominant].split("(")[0], {}).get("dram_bytes_per_launch")
+    except (OSError, ValueError):
+        pass
     roofline = {"bound": "hbm", "kernel": STAGE_KERNEL[dominant], "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": stage_bytes[dominant],
+                "traffic": traffic, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": stage_bytes[dominant],
                 "avg_launch_ms": stage_ms[dominant], "share_of_iteration": stage_ms[dominant] / iter_ms_profiled if iter_ms_profiled else None,
                 "stage_ms": stage_ms, "iteration_algorithmic_bytes": bytes_by["total"],
                 "iteration_achieved_gbs": bytes_by["total"] / (iter_ms_profiled * 1e-3) / 1e9 if iter_ms_profiled else None}
