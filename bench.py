@@ -280,6 +280,7 @@ def cpu_baseline_sample(s, iterations):
     """Bounded CPU sample: one frame, `iterations` GN iterations timed, extrapolated to ITERATIONS_PER_FRAME."""
     from oracle import oracle_py as oracle
     oracle.lib()
+    oracle.set_num_threads(host_cores())  # torchrun exports OMP_NUM_THREADS=1
     depth = oracle_target_depth(oracle, s, s["frame_scales"][0])
     oracle_frame(oracle, s, depth, 1)  # warm-up (page faults, OpenMP pool)
     setup_s, iter_s = oracle_frame(oracle, s, depth, iterations)
@@ -299,6 +300,7 @@ def run_reference(args):
         return None
     from oracle import oracle_py as oracle
     oracle.lib()
+    threads = oracle.set_num_threads(host_cores())  # torchrun exports OMP_NUM_THREADS=1
     s = make_bench_scene()
     depth = oracle_target_depth(oracle, s, s["frame_scales"][0])
     _, probe = oracle_frame(oracle, s, depth, 1)
@@ -314,7 +316,7 @@ def run_reference(args):
     frame_s = total_setup / args.steps + per_iter * ITERATIONS_PER_FRAME
     value = 1.0 / frame_s
     sample = (f"each step = per-fit setup + {iters} of {ITERATIONS_PER_FRAME} GN iterations of {WORKLOAD} @640x480, extrapolated to a full frame; "
-              f"{host_cores()} threads on '{cpu_model()}'")
+              f"{threads} threads on '{cpu_model()}'")
     return {"impl": "reference", "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": frame_s * 1e3, "ms_per_iteration": per_iter * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": bench_config(args.gpus),

@@ -205,3 +205,18 @@ ORACLE_API int oracle_fit_to_image(OracleFitParams* p) {
 	if (p->stage_seconds) for (int i = 0; i < 8; i++) p->stage_seconds[i] = st[i];
 	return 0;
 }
+
+// Thread control for the timed CPU baseline: launchers such as torchrun export OMP_NUM_THREADS=1, which would silently turn the
+// "all host cores" baseline into a single-thread one.
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+extern "C" __attribute__((visibility("default"))) int oracle_set_num_threads(int n) {
+#ifdef _OPENMP
+	if (n > 0) omp_set_num_threads(n);
+	return omp_get_max_threads();
+#else
+	(void) n;
+	return 1;
+#endif
+}

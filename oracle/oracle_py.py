@@ -40,6 +40,11 @@ def lib():
     return _LIB
 
 
+def set_num_threads(n):
+    """Sets the OpenMP team size of the oracle (returns the size in effect); overrides an inherited OMP_NUM_THREADS."""
+    return int(lib().oracle_set_num_threads(C.c_int(int(n))))
+
+
 def ref_lib():
     """The reference's own device-function headers compiled verbatim (None if not built)."""
     global _REF
