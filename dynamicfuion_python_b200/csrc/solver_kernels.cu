@@ -666,7 +666,7 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 			}
 			if (bi == p) {
 				if (!ok) atomicExch(sys.flags + 2, 1);
-				// final rows of the diagonal block + inverse of the block for the back substitution
+				// final rows of the diagonal block
 #pragma unroll
 				for (int r = 0; r < kTile; r++) {
 					float* Lr = Lf + aligned_row_start(j + r) + j;
@@ -684,23 +684,6 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 							a[r][c] = w * inv[c];
 							if (c < nb) Lr[c] = a[r][c];
 						}
-					}
-				}
-				float* Wp = W + p * 64;
-#pragma unroll
-				for (int c = 0; c < kTile; c++) {
-					float w[kTile];
-#pragma unroll
-					for (int r = 0; r < kTile; r++) {
-						if (r < c) w[r] = 0.f;
-						else if (r == c) w[r] = inv[c];
-						else {
-							float acc = 0.f;
-#pragma unroll
-							for (int k = c; k < r; k++) acc = fmaf(d[r][k], w[k], acc);
-							w[r] = -acc * inv[r];
-						}
-						Wp[r * kTile + c] = w[r];
 					}
 				}
 			} else {
@@ -771,7 +754,12 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 				}
 			}
 #ifdef NNRT_PHASE_TIMING
-			if (tid == 0 && p == 0) g_phase_clock[12] = clock64() - tb0;
+			if (p == 0) {  // per-warp completion time of step B, forced after the accumulators by data dependence
+				long long tend;
+				asm volatile("mov.u64 %0, %%clock64;" : "=l"(tend) : "f"(a[0][0]), "f"(a[7][7]), "f"(a[3][4]), "f"(a[4][3]));
+				if ((tid & 31) == 0) { g_warp_clock[tid >> 5] = tend - tb0; g_warp_abs[tid >> 5] = tb0; g_warp_abs[32 + (tid >> 5)] = tend; }
+				if (tid == 0) g_phase_clock[12] = tend - tb0;
+			}
 #endif
 			if (bi == p + 1 && bj == p + 1) {
 #pragma unroll
@@ -780,8 +768,12 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 					for (int c = 0; c < kTile; c++) D11[r * kTile + c] = a[r][c];
 			}
 		}
+#ifdef NNRT_PHASE_TIMING
+		if (p == 0 && (tid & 31) == 0) g_warp_abs[64 + (tid >> 5)] = clock64();
+#endif
 		__syncthreads();
 #ifdef NNRT_PHASE_TIMING
+		if (p == 0 && (tid & 31) == 0) g_warp_abs[96 + (tid >> 5)] = clock64();
 		if (tid == 0 && (p == 0 || p == 8 || p == 16 || p == 24)) g_phase_clock[8 + p / 8] = clock64() - t_phase;
 #endif
 		NNRT_ACC(acc_trail);

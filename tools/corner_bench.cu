@@ -7,6 +7,8 @@
 #include <vector>
 #include <random>
 __device__ long long g_phase_clock[16];
+__device__ long long g_warp_clock[32];
+__device__ long long g_warp_abs[128];
 #include "../dynamicfuion_python_b200/csrc/solver_kernels.cu"
 namespace nnrt_b200 { void set_last_error(const char*, ...) {} }
 using namespace nnrt_b200;
@@ -60,6 +62,10 @@ int main(int argc, char** argv) {
 	const char* names[] = {"stage S", "panels", "trailing", "backsub", "stem backsub", "node update"};
 	for (int k = 0; k < 6; k++) printf("  %-14s %8lld cycles\n", names[k], ph[k]);
 	printf("  trailing at p=0/8/16/24: %lld %lld %lld %lld   pure step B at p=0 (thread 0): %lld\n", ph[8], ph[9], ph[10], ph[11], ph[12]);
+	{ long long wc[32]; cudaMemcpyFromSymbol(wc, g_warp_clock, sizeof(wc)); printf("  step B at p=0, per warp:"); for (int w = 0; w < 16; w++) printf(" %lld", wc[w]); printf("\n"); }
+	{ long long wa[128]; cudaMemcpyFromSymbol(wa, g_warp_abs, sizeof(wa)); long long t0 = wa[0]; for (int w = 0; w < 15; w++) t0 = wa[w] < t0 ? wa[w] : t0;
+	  printf("  p=0 per warp [B start, B end, barrier arrive, barrier exit] relative to first start:\n");
+	  for (int w = 0; w < 16; w++) printf("   w%-2d %6lld %6lld %6lld %6lld\n", w, wa[w] ? wa[w] - t0 : -1, wa[32 + w] ? wa[32 + w] - t0 : -1, wa[64 + w] - t0, wa[96 + w] - t0); }
 	// check against dense double solve
 	std::vector<float> hx((size_t) N * 6); cudaMemcpy(hx.data(), x, sizeof(float) * N * 6, cudaMemcpyDeviceToHost);
 	const int M = N * 6; std::vector<double> A((size_t) M * M, 0.0), bb(M);
