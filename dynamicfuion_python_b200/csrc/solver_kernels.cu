@@ -567,21 +567,86 @@ __device__ __forceinline__ float negate_bits(float v) { return __int_as_float(__
 // The trailing matrix never round-trips through shared memory: thread t owns ONE 8 x 8 tile (bi, bj), bi >= bj, of the
 // augmented lower triangle (rhs = row n) in 64 registers for the whole factorisation. Tiles are handed out by descending
 // block column, so at panel p the live tiles are exactly threads [0, live(p)) and finished warps fall through to the barriers.
-//   panel p, step A: the threads of block column p (one warp's worth) factor the raw diagonal tile published by its owner
-//                    (redundantly, in registers), solve their own 8 rows against it, publish the strip to PT[c][row] and the
-//                    final rows to the packed factor Lf (read by the back substitution only).
+//   panel p, step A: one thread per ROW of block column p (up to 8 warps) forward-substitutes its row, read from the raw strip
+//                    RAW that the column's tile owners published at the end of the previous step B, against the factored
+//                    diagonal tile; the row goes to PT[c][row] and to the packed factor Lf (read by the back substitution).
+//                    The diagonal tile itself is factored one panel AHEAD by warp 0 (which owns the block-column-0 tiles
+//                    only and is otherwise idle), concurrently with step B: see lookahead_factor.
 //   panel p, step B: every live tile with bj > p does its rank-8 update from PT: 32 LDS.128 per 512 FMAs.
 // Shared-memory traffic per panel is the panel strip only; the smem-resident variant above moves every trailing element twice.
 __host__ __device__ inline size_t regtile_corner_floats(int n) {
 	const int tr = (n + 1 + kTile - 1) / kTile, prow = tr * kTile;
-	return (size_t) aligned_row_start(prow) + (size_t) kTile * prow /*PT*/ + 64 /*raw diag*/ + (size_t) tr * 64 /*W*/ + (size_t) prow + 32 /*xs*/ +
+	return (size_t) aligned_row_start(prow) + (size_t) kTile * prow /*PT*/ + (size_t) tr * 72 /*raw strip*/ + 128 + 144 /*look-ahead tiles*/ + (size_t) prow + 32 /*xs*/ +
 	       (size_t) ((n + 31) / 32) * 1024 /*Dinv*/ + (size_t) prow /*inv_diag*/ + 64;
 }
 __host__ __device__ inline bool regtile_corner_fits(int n) {
 	const int tr = (n + 1 + kTile - 1) / kTile, tc = (n + kTile - 1) / kTile;
-	// tiles (bi >= bj): sum over bj of (tr - bj)
+	// tiles (bi >= bj): sum over bj of (tr - bj); block column 0 takes warp 0, the rest start at thread 32
 	const int tiles = tc * tr - tc * (tc - 1) / 2;
-	return n > 0 && n + 1 <= kRegTileMaxRows && tiles <= kCornerThreads && regtile_corner_floats(n) * sizeof(float) <= 227 * 1024;
+	return n > 0 && n + 1 <= kRegTileMaxRows && 32 + tiles - tr <= kCornerThreads && regtile_corner_floats(n) * sizeof(float) <= 227 * 1024;
+}
+
+// Look-ahead factorisation of one 8 x 8 diagonal tile by a single warp, run while the other warps do the trailing update of the
+// previous panel. Lane l holds entries (l / 8, l % 8) and (l / 8 + 4, l % 8); `current` is the tile after all updates but the last,
+// `strip` (PT + 8 q, or nullptr for the first tile) supplies that last rank-8 update with the owner's exact operation order.
+// Writes the Cholesky factor (strict lower triangle) to fac[0..63], the reciprocal diagonal to fac[64..71] and inv_diag.
+__device__ __forceinline__ void lookahead_factor(const float* current, const float* strip, int prow, int nb, float* fac,
+                                                 float* inv_diag, int* flags) {
+	const int lane = threadIdx.x & 31, r = lane >> 3, c = lane & 7;
+	float d0 = current[r * kTile + c], d1 = current[(r + 4) * kTile + c];
+	if (strip != nullptr) {
+#pragma unroll
+		for (int k = 0; k < kTile; k++) {
+			const float* col = strip + k * prow;
+			const float pc = col[c];
+			d0 = fmaf(-col[r], pc, d0);
+			d1 = fmaf(-col[r + 4], pc, d1);
+		}
+	}
+	// exchange through fac so that every lane holds the whole updated tile, then factor it redundantly in registers: the
+	// dependent chain per column is FMA -> MUFU -> FMUL -> FMA, no shuffles (a lane-parallel factor was 2 x slower)
+	fac[r * kTile + c] = d0;
+	fac[(r + 4) * kTile + c] = d1;
+	__syncwarp();
+	float d[kTile][kTile], inv[kTile];
+	{
+		const float4* F = reinterpret_cast<const float4*>(fac);
+#pragma unroll
+		for (int i = 0; i < kTile; i++) {
+			const float4 lo = F[i * 2], hi = (i >= 4) ? F[i * 2 + 1] : make_float4(0.f, 0.f, 0.f, 0.f);
+			const float row[kTile] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+#pragma unroll
+			for (int k = 0; k <= i; k++) d[i][k] = (i < nb) ? row[k] : (i == k ? 1.f : 0.f);   // identity below a partial last block
+		}
+	}
+	__syncwarp();
+	bool ok = true;
+#pragma unroll
+	for (int k = 0; k < kTile; k++) {
+		const float pivot = d[k][k];
+		if (!(pivot > 0.f)) ok = false;
+		asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(inv[k]) : "f"(pivot));
+#pragma unroll
+		for (int i = k + 1; i < kTile; i++) d[i][k] *= inv[k];
+#pragma unroll
+		for (int i = k + 1; i < kTile; i++)
+#pragma unroll
+			for (int m = k + 1; m <= i; m++) d[i][m] = fmaf(-d[i][k], d[m][k], d[i][m]);
+	}
+	if (lane == 0) {
+		float4* F = reinterpret_cast<float4*>(fac);
+#pragma unroll
+		for (int i = 1; i < kTile; i++) {
+			F[i * 2] = make_float4(d[i][0], i > 1 ? d[i][1] : 0.f, i > 2 ? d[i][2] : 0.f, i > 3 ? d[i][3] : 0.f);
+			if (i > 4) F[i * 2 + 1] = make_float4(d[i][4], i > 5 ? d[i][5] : 0.f, i > 6 ? d[i][6] : 0.f, 0.f);
+		}
+		F[16] = make_float4(inv[0], inv[1], inv[2], inv[3]);
+		F[17] = make_float4(inv[4], inv[5], inv[6], inv[7]);
+#pragma unroll
+		for (int i = 0; i < kTile; i++)
+			if (i < nb) inv_diag[i] = inv[i];
+		if (!ok) atomicExch(flags + 2, 1);
+	}
 }
 
 __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(ArrowheadSystem sys, float* __restrict__ x,
@@ -593,9 +658,11 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 	const int tr = (n + 1 + kTile - 1) / kTile, tc = (n + kTile - 1) / kTile, prow = tr * kTile;
 	float* Lf = smem;                                         // final factor, aligned-packed rows (back substitution)
 	float* PT = Lf + aligned_row_start(prow);                 // [8][prow] current panel strip, transposed
-	float* D11 = PT + kTile * prow;                           // [64] raw diagonal tile of the next panel
-	float* W = D11 + 64;                                      // [tr][64] inverse of each factored diagonal block (lower, row-major 8x8)
-	float* xs = W + tr * 64;                                  // [prow + 32] corner solution
+	const int raw_plane = tr * 9;                             // float4 slots per column half; row r of the strip sits at r + r / 8
+	float4* RAW = reinterpret_cast<float4*>(PT + kTile * prow);  // [2][tr * 9] raw (updated, unfactored) strip of the next panel
+	float* DN = PT + kTile * prow + 2 * raw_plane * 4;        // [2][64] diagonal tiles q = p + 1, p + 2 before their last update
+	float* FAC = DN + 128;                                    // [2][72] factored diagonal tile + reciprocal diagonal, by panel parity
+	float* xs = FAC + 144;                                    // [prow + 32] corner solution
 	float* Dinv = xs + prow + 32;                             // [groups][32][32] inverses of the 32 x 32 diagonal blocks of L
 	float* inv_diag = Dinv + ((n + 31) / 32) * 1024;          // [prow] 1 / L_jj
 #ifdef NNRT_PHASE_TIMING
@@ -603,9 +670,11 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 #endif
 	// ---- tile assignment: block columns in descending order, rows ascending inside a column
 	int bi = -1, bj = -1;
-	{
-		int offset = 0;
-		for (int b = tc - 1; b >= 0; b--) {
+	if (tid < 32) {
+		if (tid < tr) { bj = 0; bi = tid; }
+	} else {
+		int offset = 32;
+		for (int b = tc - 1; b >= 1; b--) {
 			const int count = tr - b;
 			if (tid >= offset && tid < offset + count) { bj = b; bi = b + (tid - offset); }
 			offset += count;
@@ -613,13 +682,13 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 	}
 	const bool has_tile = bj >= 0;
 	float a[kTile][kTile];
-	// ---- load this thread's tile: the stem kernel accumulated S and the rhs row directly in tile-packed order, so the tile is
-	// 16 coalesced 128-bit loads; the buffer is zeroed behind the load for the next iteration's accumulation
+	// ---- load this thread's tile: the stem kernel accumulated S and the rhs row directly in warp-interleaved tile order, so the
+	// tile is 16 fully coalesced 128-bit loads; the buffer is zeroed behind the load for the next iteration's accumulation
 	if (has_tile) {
-		float4* tile = reinterpret_cast<float4*>(sys.schur) + (int64_t) tid * 16;
+		float4* tile = reinterpret_cast<float4*>(sys.schur) + (tid >> 5) * 512 + (tid & 31);
 		float4 v[16];
 #pragma unroll
-		for (int q = 0; q < 16; q++) v[q] = __ldcg(tile + q);
+		for (int q = 0; q < 16; q++) v[q] = __ldcg(tile + q * 32);
 #pragma unroll
 		for (int r = 0; r < kTile; r++) {
 			a[r][0] = v[2 * r].x; a[r][1] = v[2 * r].y; a[r][2] = v[2 * r].z; a[r][3] = v[2 * r].w;
@@ -627,88 +696,68 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 		}
 		if (clear_corner) {
 #pragma unroll
-			for (int q = 0; q < 16; q++) tile[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+			for (int q = 0; q < 16; q++) tile[q * 32] = make_float4(0.f, 0.f, 0.f, 0.f);
 		}
-		if (bi == 0 && bj == 0) {
+		if (bj == 0) {
+			float4* dst = RAW + bi * 9;
 #pragma unroll
-			for (int r = 0; r < kTile; r++)
-#pragma unroll
-				for (int c = 0; c < kTile; c++) D11[r * kTile + c] = a[r][c];
+			for (int r = 0; r < kTile; r++) {
+				dst[r] = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
+				dst[raw_plane + r] = make_float4(a[r][4], a[r][5], a[r][6], a[r][7]);
+			}
 		}
 	}
+	if (has_tile && bi == bj && bj < 2) {
+#pragma unroll
+		for (int r = 0; r < kTile; r++)
+#pragma unroll
+			for (int c = 0; c < kTile; c++) DN[bj * 64 + r * kTile + c] = a[r][c];
+	}
+	const bool lookahead_warp = tid < 32;   // warp 0: oldest warp of the CTA, so the scheduler does not starve the critical chain
+	__syncthreads();
+	if (lookahead_warp) lookahead_factor(DN, nullptr, prow, min(kTile, n), FAC, inv_diag, sys.flags);
 	__syncthreads();
 	NNRT_STAMP(0);
 	for (int p = 0; p < tc; p++) {
 		const int j = p * kTile, nb = min(kTile, n - j);
-		if (bj == p) {
-			// ---- step A: factor the diagonal tile (redundantly), then finish this thread's rows
+		if (tid < prow - j) {
+			// ---- step A, one thread per row of block column p: forward-substitute the row against the diagonal factor the
+			// look-ahead warp left in FAC. Rows of the diagonal block itself fall out of the same recurrence.
 			float d[kTile][kTile], inv[kTile];
+			{
+				const float4* F = reinterpret_cast<const float4*>(FAC + (p & 1) * 72);
 #pragma unroll
-			for (int r = 0; r < kTile; r++)
+				for (int c = 1; c < kTile; c++) {
+					const float4 lo = F[c * 2], hi = (c > 4) ? F[c * 2 + 1] : make_float4(0.f, 0.f, 0.f, 0.f);
+					const float row[kTile] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
 #pragma unroll
-				for (int c = 0; c <= r; c++) d[r][c] = (r < nb) ? D11[r * kTile + c] : (r == c ? 1.f : 0.f);
-			bool ok = true;
+					for (int k = 0; k < c; k++) d[c][k] = row[k];
+				}
+				const float4 i0 = F[16], i1 = F[17];
+				inv[0] = i0.x; inv[1] = i0.y; inv[2] = i0.z; inv[3] = i0.w; inv[4] = i1.x; inv[5] = i1.y; inv[6] = i1.z; inv[7] = i1.w;
+			}
+			const int lr = tid, pos = lr + (lr >> 3), row = j + lr;
+			const float4 v0 = RAW[pos], v1 = RAW[raw_plane + pos];
+			float w[kTile] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
 			for (int c = 0; c < kTile; c++) {
-				float v = d[c][c];
+				float acc = w[c];
 #pragma unroll
-				for (int k = 0; k < c; k++) v = fmaf(-d[c][k], d[c][k], v);
-				if (!(v > 0.f)) ok = false;
-				inv[c] = rsqrtf(v);
-				d[c][c] = v * inv[c];
-#pragma unroll
-				for (int r = c + 1; r < kTile; r++) {
-					float w = d[r][c];
-#pragma unroll
-					for (int k = 0; k < c; k++) w = fmaf(-d[r][k], d[c][k], w);
-					d[r][c] = w * inv[c];
-				}
+				for (int k = 0; k < c; k++) acc = fmaf(-w[k], d[c][k], acc);
+				w[c] = acc * inv[c];
 			}
-			if (bi == p) {
-				if (!ok) atomicExch(sys.flags + 2, 1);
-				// final rows of the diagonal block
+			float* Lr = Lf + aligned_row_start(row) + j;
+			if (lr >= kTile && nb == kTile) {
 #pragma unroll
-				for (int r = 0; r < kTile; r++) {
-					float* Lr = Lf + aligned_row_start(j + r) + j;
-					if (r < nb) {
-						inv_diag[j + r] = inv[r];
-#pragma unroll
-						for (int c = 0; c <= r; c++) Lr[c] = d[r][c];
-					} else {
-						// rows below a partial last block (the rhs row among them): forward-substitute against the block
-#pragma unroll
-						for (int c = 0; c < kTile; c++) {
-							float w = a[r][c];
-#pragma unroll
-							for (int k = 0; k < c; k++) w = fmaf(-a[r][k], d[c][k], w);
-							a[r][c] = w * inv[c];
-							if (c < nb) Lr[c] = a[r][c];
-						}
-					}
-				}
+				for (int c = 0; c < kTile; c++) PT[c * prow + row] = w[c];
+				*reinterpret_cast<float4*>(Lr) = make_float4(w[0], w[1], w[2], w[3]);
+				*reinterpret_cast<float4*>(Lr + 4) = make_float4(w[4], w[5], w[6], w[7]);
 			} else {
+				// a row of the diagonal block (columns up to the diagonal), or a row below a partial last block (its nb columns)
+				const int last = lr < nb ? lr : nb - 1;
 #pragma unroll
-				for (int r = 0; r < kTile; r++) {
-#pragma unroll
-					for (int c = 0; c < kTile; c++) {
-						float w = a[r][c];
-#pragma unroll
-						for (int k = 0; k < c; k++) w = fmaf(-a[r][k], d[c][k], w);
-						a[r][c] = w * inv[c];
-					}
-				}
-				const int row0 = bi * kTile;
-#pragma unroll
-				for (int c = 0; c < kTile; c++) {
-					*reinterpret_cast<float4*>(PT + c * prow + row0) = make_float4(a[0][c], a[1][c], a[2][c], a[3][c]);
-					*reinterpret_cast<float4*>(PT + c * prow + row0 + 4) = make_float4(a[4][c], a[5][c], a[6][c], a[7][c]);
-				}
-#pragma unroll
-				for (int r = 0; r < kTile; r++) {
-					float* Lr = Lf + aligned_row_start(row0 + r) + j;
-					*reinterpret_cast<float4*>(Lr) = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
-					*reinterpret_cast<float4*>(Lr + 4) = make_float4(a[r][4], a[r][5], a[r][6], a[r][7]);
-				}
+				for (int c = 0; c < kTile; c++)
+					if (c <= last) Lr[c] = w[c];
 			}
 		}
 		__syncthreads();
@@ -716,9 +765,6 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 		if (bj > p) {
 			// ---- step B: rank-8 update of the register tile
 			const int row0 = bi * kTile, col0 = bj * kTile;
-#ifdef NNRT_PHASE_TIMING
-			const long long tb0 = clock64();
-#endif
 			// c-loop kept rolled (two steps per trip, operands of the next step prefetched) so the body stays inside the L0
 			// instruction cache; the fully unrolled form is fetch-bound (measured 2.3 cycles / instruction)
 			const float* pr_base = PT + row0;
@@ -753,30 +799,39 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 						for (int cc = 0; cc < kTile; cc++) a[r][cc] = fmaf(-pr[r], pk[cc], a[r][cc]);
 				}
 			}
-#ifdef NNRT_PHASE_TIMING
-			if (p == 0) {  // per-warp completion time of step B, forced after the accumulators by data dependence
-				long long tend;
-				asm volatile("mov.u64 %0, %%clock64;" : "=l"(tend) : "f"(a[0][0]), "f"(a[7][7]), "f"(a[3][4]), "f"(a[4][3]));
-				if ((tid & 31) == 0) { g_warp_clock[tid >> 5] = tend - tb0; g_warp_abs[tid >> 5] = tb0; g_warp_abs[32 + (tid >> 5)] = tend; }
-				if (tid == 0) g_phase_clock[12] = tend - tb0;
+			if (bi == bj && bj == p + 2) {
+				// diagonal tile two panels ahead: the look-ahead warp applies its last update and factors it during the next step B
+				float4* dst = reinterpret_cast<float4*>(DN + (p & 1) * 64);
+#pragma unroll
+				for (int r = 0; r < kTile; r++) {
+					dst[2 * r] = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
+					dst[2 * r + 1] = make_float4(a[r][4], a[r][5], a[r][6], a[r][7]);
+				}
 			}
-#endif
-			if (bi == p + 1 && bj == p + 1) {
+			if (bj == p + 1) {
+				// raw strip of the next panel: step A reads it back row by row
+				float4* dst = RAW + (bi - bj) * 9;
 #pragma unroll
-				for (int r = 0; r < kTile; r++)
-#pragma unroll
-					for (int c = 0; c < kTile; c++) D11[r * kTile + c] = a[r][c];
+				for (int r = 0; r < kTile; r++) {
+					dst[r] = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
+					dst[raw_plane + r] = make_float4(a[r][4], a[r][5], a[r][6], a[r][7]);
+				}
 			}
 		}
 #ifdef NNRT_PHASE_TIMING
-		if (p == 0 && (tid & 31) == 0) g_warp_abs[64 + (tid >> 5)] = clock64();
+		const long long tl0 = clock64();
+#endif
+		if (lookahead_warp && p + 1 < tc)
+			lookahead_factor(DN + ((p + 1) & 1) * 64, PT + (p + 1) * kTile, prow, min(kTile, n - (p + 1) * kTile), FAC + ((p + 1) & 1) * 72,
+			                 inv_diag + (p + 1) * kTile, sys.flags);
+#ifdef NNRT_PHASE_TIMING
+		if (lookahead_warp && (tid & 31) == 0 && (p == 0 || p == 12 || p == 24)) g_phase_clock[13 + p / 12] = clock64() - tl0 + (long long) (FAC[((p + 1) & 1) * 72] == 12345.f);
 #endif
 		__syncthreads();
-#ifdef NNRT_PHASE_TIMING
-		if (p == 0 && (tid & 31) == 0) g_warp_abs[96 + (tid >> 5)] = clock64();
-		if (tid == 0 && (p == 0 || p == 8 || p == 16 || p == 24)) g_phase_clock[8 + p / 8] = clock64() - t_phase;
-#endif
 		NNRT_ACC(acc_trail);
+#ifdef NNRT_PHASE_TIMING
+		if (tid == 64) g_warp_abs[p] = clock64() + (long long) (((volatile float*) PT)[0] == 12345.f);
+#endif
 	}
 #ifdef NNRT_PHASE_TIMING
 	if (tid == 0) { g_phase_clock[1] = acc_panel; g_phase_clock[2] = acc_trail; }
@@ -808,6 +863,9 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 		}
 		float y = (tid < n) ? Lf[aligned_row_start(n) + tid] : 0.f;
 		__syncthreads();
+#ifdef NNRT_PHASE_TIMING
+		if (tid == 0) { const long long now = clock64() + (long long) (((volatile float*) Dinv)[0] == 12345.f); g_phase_clock[6] = now - t_phase; t_phase = now; }
+#endif
 		for (int g = groups - 1; g >= 0; g--) {
 			const int base = g << 5;
 			if (warp == g) {
@@ -818,11 +876,29 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 				xs[base + lane] = acc;
 			}
 			__syncthreads();
+#ifdef NNRT_PHASE_TIMING
+			if (tid == 0) g_warp_abs[32 + g] = clock64() + (long long) (((volatile float*) xs)[base] == 12345.f);
+#endif
 			if (tid < base) {
-#pragma unroll 8
-				for (int c = 0; c < 32; c++)
-					if (base + c < n) y = fmaf(-Lf[aligned_row_start(base + c) + tid], xs[base + c], y);
+				// unconditional, fully unrolled so the 64 loads are issued ahead of the FMA chain: columns >= n of the last group
+				// have x = 0 (their Dinv columns are zero) and read the rhs row instead of running past the factor
+				float4 xg[8];
+#pragma unroll
+				for (int q = 0; q < 8; q++) xg[q] = *reinterpret_cast<const float4*>(xs + base + 4 * q);
+				float l[32];
+#pragma unroll
+				for (int c = 0; c < 32; c++) l[c] = Lf[aligned_row_start(min(base + c, n)) + tid];
+#pragma unroll
+				for (int q = 0; q < 8; q++) {
+					y = fmaf(-l[4 * q], xg[q].x, y);
+					y = fmaf(-l[4 * q + 1], xg[q].y, y);
+					y = fmaf(-l[4 * q + 2], xg[q].z, y);
+					y = fmaf(-l[4 * q + 3], xg[q].w, y);
+				}
 			}
+#ifdef NNRT_PHASE_TIMING
+			if (tid == 0) { long long now; asm volatile("mov.u64 %0, %%clock64;" : "=l"(now) : "f"(y)); g_warp_abs[48 + g] = now; }
+#endif
 		}
 		__syncthreads();
 		for (int k = tid; k < n; k += T) x[sys.arrow_base * 6 + k] = xs[k];
@@ -858,7 +934,7 @@ size_t corner_scratch_bytes(int corner_blocks) {
 }
 bool corner_uses_tile_packed_schur(int corner_blocks) { return regtile_corner_fits(corner_blocks * 6); }
 size_t corner_schur_floats(int corner_blocks) {
-	const size_t n = (size_t) corner_blocks * 6, dense = n * n, packed = (size_t) corner_tile_count((int) n) * 64;
+	const size_t n = (size_t) corner_blocks * 6, dense = n * n, packed = (size_t) corner_tile_floats((int) n);
 	return (dense > packed ? dense : packed) + 64;
 }
 bool corner_needs_global_scratch(int corner_blocks) { return blocked_corner_floats(corner_blocks * 6) * sizeof(float) > 227 * 1024; }

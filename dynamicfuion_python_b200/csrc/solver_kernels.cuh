@@ -27,7 +27,7 @@ struct ArrowheadSystem {
 	float* wing_x;                  // [W,36]  D^-1 B
 	float* schur;                   // dense [(6Nc)^2], or tile-packed lower triangle + rhs row (schur_tile_packed); zero on entry
 	float* corner_rhs;              // [6Nc], must be zero on entry (unused when schur_tile_packed)
-	int schur_tile_packed;          // 1: the register-tiled corner kernel consumes `schur` as [tile][8][8] (see corner_tile_index)
+	int schur_tile_packed;          // 1: the register-tiled corner kernel consumes `schur` as warp-interleaved 8 x 8 tiles (see corner_tile_index)
 	int* flags;                     // flags[2] set when a block is not positive definite
 };
 
@@ -44,14 +44,22 @@ __host__ __device__ __forceinline__ int corner_tile_count(int n) {
 	const int tr = corner_tile_rows(n), tc = corner_tile_cols(n);
 	return tc * tr - tc * (tc - 1) / 2;
 }
+// Block column 0 (never updated, only factored) belongs to warp 0, which doubles as the look-ahead warp; the other block columns
+// follow from thread 32 on in DESCENDING order, rows ascending inside a column.
 __host__ __device__ __forceinline__ int corner_tile_id(int n, int bi, int bj) {
+	if (bj == 0) return bi;
 	const int tr = corner_tile_rows(n), tc = corner_tile_cols(n), m = tc - 1 - bj;
-	return m * tr - (bj + tc) * m / 2 + (bi - bj);
+	return 32 + m * tr - (bj + tc) * m / 2 + (bi - bj);
 }
-// offset of element (row, col), row in [0, n], col in [0, n), row / 8 >= col / 8
+__host__ __device__ __forceinline__ int corner_tile_slots(int n) { return 32 + corner_tile_count(n) - corner_tile_rows(n); }
+// offset of element (row, col), row in [0, n], col in [0, n), row / 8 >= col / 8. Tiles are interleaved in groups of 32 (one
+// warp of the corner kernel): 128-bit quad q = 2 * (row % 8) + (col % 8) / 4 of tile t sits at quad ((t / 32) * 16 + q) * 32 + t % 32,
+// so a warp's q-th load instruction reads 512 contiguous bytes and every lane receives its own tile directly.
 __host__ __device__ __forceinline__ int corner_tile_index(int n, int row, int col) {
-	return corner_tile_id(n, row >> 3, col >> 3) * 64 + (row & 7) * kTile + (col & 7);
+	const int t = corner_tile_id(n, row >> 3, col >> 3), q = ((row & 7) << 1) | ((col & 7) >> 2);
+	return ((((t >> 5) << 4) + q) * 32 + (t & 31)) * 4 + (col & 3);
 }
+__host__ __device__ __forceinline__ int corner_tile_floats(int n) { return ((corner_tile_slots(n) + 31) / 32) * 32 * 64; }
 // where the stem kernel accumulates S(row, col): -1 = not stored in this layout (strict upper tile triangle)
 __device__ __forceinline__ int64_t schur_slot(const ArrowheadSystem& sys, int n, int row, int col) {
 	if (!sys.schur_tile_packed) return (int64_t) row * n + col;

@@ -61,11 +61,12 @@ int main(int argc, char** argv) {
 	long long ph[16]; cudaMemcpyFromSymbol(ph, g_phase_clock, sizeof(ph));
 	const char* names[] = {"stage S", "panels", "trailing", "backsub", "stem backsub", "node update"};
 	for (int k = 0; k < 6; k++) printf("  %-14s %8lld cycles\n", names[k], ph[k]);
-	printf("  trailing at p=0/8/16/24: %lld %lld %lld %lld   pure step B at p=0 (thread 0): %lld\n", ph[8], ph[9], ph[10], ph[11], ph[12]);
-	{ long long wc[32]; cudaMemcpyFromSymbol(wc, g_warp_clock, sizeof(wc)); printf("  step B at p=0, per warp:"); for (int w = 0; w < 16; w++) printf(" %lld", wc[w]); printf("\n"); }
-	{ long long wa[128]; cudaMemcpyFromSymbol(wa, g_warp_abs, sizeof(wa)); long long t0 = wa[0]; for (int w = 0; w < 15; w++) t0 = wa[w] < t0 ? wa[w] : t0;
-	  printf("  p=0 per warp [B start, B end, barrier arrive, barrier exit] relative to first start:\n");
-	  for (int w = 0; w < 16; w++) printf("   w%-2d %6lld %6lld %6lld %6lld\n", w, wa[w] ? wa[w] - t0 : -1, wa[32 + w] ? wa[32 + w] - t0 : -1, wa[64 + w] - t0, wa[96 + w] - t0); }
+	printf("  backsub split: block inverses %lld, group sweep %lld\n", ph[6], ph[3]);
+	printf("  look-ahead factor at p=0/12/24: %lld %lld %lld cycles\n", ph[13], ph[14], ph[15]);
+	{ long long wa[128]; cudaMemcpyFromSymbol(wa, g_warp_abs, sizeof(wa));
+	  printf("  back substitution, per group [x_g ready, fold done] since previous fold:"); for (int g = 6; g >= 0; g--) printf(" [%lld %lld]", wa[32 + g] - wa[48 + g + 1], wa[48 + g] - wa[48 + g + 1]); printf("\n");
+	  printf("  cycles per panel (A + B):"); for (int q = 1; q < (n + 7) / 8; q++) printf(" %lld", wa[q] - wa[q - 1]); printf("\n"); }
+
 	// check against dense double solve
 	std::vector<float> hx((size_t) N * 6); cudaMemcpy(hx.data(), x, sizeof(float) * N * 6, cudaMemcpyDeviceToHost);
 	const int M = N * 6; std::vector<double> A((size_t) M * M, 0.0), bb(M);
