@@ -131,34 +131,65 @@ __device__ __forceinline__ float3 row_times_skew(float3 r, float3 s) {
 	return make_float3(sum3(r.x * 0.f, r.y * s.z, r.z * -s.y), sum3(r.x * -s.z, r.y * 0.f, r.z * s.x), sum3(r.x * s.y, r.y * -s.x, r.z * 0.f));
 }
 
-// K6. One thread per pixel (16x16 tile per CTA, 8x4 pixels per warp). Replaces InterpolateVertexAttributes, the
+__device__ __forceinline__ void cp_async_16(void* shared_dst, const void* global_src) {
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned) __cvta_generic_to_shared(shared_dst)), "l"(global_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_8(void* shared_dst, const void* global_src) {
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned) __cvta_generic_to_shared(shared_dst)), "l"(global_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+constexpr int kAssembleThreads = 128;
+__host__ __device__ constexpr size_t assemble_shared_bytes(int anchor_count) {
+	return (size_t) kAssembleThreads * 3 * anchor_count * 2 * sizeof(float4);
+}
+
+// K6. One thread per pixel (16x8 tile per CTA, 8x4 pixels per warp). Replaces InterpolateVertexAttributes, the
 // per-iteration unprojection, ComputePointToPlaneDistances, masking, RasterizedSurfaceJacobians,
 // PixelVertexAnchorJacobiansAndNodeAssociations and both *_UnorderedNodePixels reductions
-// (cpp/alignment/DeformableMeshToImageFitter.cpp:133-220): everything per pixel stays in registers, per-node sums are
+// (cpp/alignment/DeformableMeshToImageFitter.cpp:133-220): everything per pixel stays on chip, per-node sums are
 // formed by a warp-level reduction keyed on node id and flushed with one float atomic per (warp, node, entry).
+// The kernel is bound by the latency of its dependent gathers (key -> face -> vertices -> anchor records), so every load
+// that hangs off the face index is issued in one burst: the 3A vertex-anchor records and the face's node table travel
+// global -> shared with cp.async while the residual and the barycentric chain are computed from registers; the node-voting
+// loop then touches shared memory only.
 template<int A>
-__global__ void __launch_bounds__(256) assemble_kernel(FitterDeviceData d, DataTermParams p) {
-	constexpr int kMaxEntries = 3 * A;
-	__shared__ int s_nodes[256][kMaxEntries + 1];  // +1: bank-conflict padding
-	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	const int tile_x = blockIdx.x * 16 + (warp & 1) * 8, tile_y = blockIdx.y * 16 + (warp >> 1) * 4;
+__global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDeviceData d, DataTermParams p) {
+	constexpr int kMaxEntries = 3 * A, T = kAssembleThreads;
+	extern __shared__ __align__(16) unsigned char assemble_smem[];
+	float4* s_rec = reinterpret_cast<float4*>(assemble_smem);  // [3A * 2][T]: anchor records, then J contributions (+ node id)
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	// tiles are visited in a scrambled order (multiplication by a prime modulo the tile count): the surface covers a compact
+	// part of the image, and in raster order its expensive tiles would reach the SMs as one late clump
+	const unsigned tile_count = gridDim.x * gridDim.y, linear = blockIdx.y * gridDim.x + blockIdx.x;
+	const unsigned tile = (tile_count % 1009u) ? (unsigned) (((unsigned long long) linear * 1009ull) % tile_count) : linear;
+	const int tile_x = (int) (tile % gridDim.x) * 16 + (warp & 1) * 8, tile_y = (int) (tile / gridDim.x) * 8 + (warp >> 1) * 4;
 	const int u = tile_x + (lane & 7), v = tile_y + (lane >> 3);
 	const bool in_image = u < p.width && v < p.height;
 	const int64_t px = (int64_t) v * p.width + u;
 	unsigned long long key = kEmptyKey;
-	if (in_image) {
-		key = d.keys[px];
-		d.keys[px] = kEmptyKey;  // leave the key buffer clean for the next iteration's scatter
-	}
+	if (in_image) key = d.keys[px];
 	const bool covered = key != kEmptyKey;
-	int face = -1, entry_count = 0;
+	int face = -1;
 	float residual = 0.f;
-	bool contributes = false, residual_mask = false;
-	float dr_dV[9], dr_dN[9];
-	int4 tri = make_int4(0, 0, 0, 0);
+	bool residual_mask = false;
+	unsigned pending = 0u;     // bit q = fvi * A + slot: that (face vertex, anchor slot) pair still has to be accumulated
+	int nodes[kMaxEntries];
+#pragma unroll
+	for (int q = 0; q < kMaxEntries; q++) nodes[q] = -1;
 	if (covered) {
+		d.keys[px] = kEmptyKey;  // leave the key buffer clean for the next iteration's scatter
 		face = (int) (key & 0xFFFFFFFFull);
-		tri = d.triangles[face];
+		const int4 tri = d.triangles[face];
+		{
+#pragma unroll
+			for (int fvi = 0; fvi < 3; fvi++) {
+				const int vi = fvi == 0 ? tri.x : fvi == 1 ? tri.y : tri.z;
+				const float4* rec = d.vertex_jacobians + (int64_t) vi * A * 2;
+#pragma unroll
+				for (int q = 0; q < 2 * A; q++) cp_async_16(s_rec + (fvi * 2 * A + q) * T + tid, rec + q);
+			}
+		}
 		float3 fv[3], fn[3];
 		{
 			const float4 a = d.warped_positions[tri.x], b = d.warped_positions[tri.y], c = d.warped_positions[tri.z];
@@ -166,6 +197,7 @@ __global__ void __launch_bounds__(256) assemble_kernel(FitterDeviceData d, DataT
 			const float4 na = d.warped_normals[tri.x], nb = d.warped_normals[tri.y], nc = d.warped_normals[tri.z];
 			fn[0] = make_float3(na.x, na.y, na.z); fn[1] = make_float3(nb.x, nb.y, nb.z); fn[2] = make_float3(nc.x, nc.y, nc.z);
 		}
+		const float4 ref = d.reference_points[px];
 		const float2 ray = make_float2(pixel_to_ndc(u, p.width, p.height), pixel_to_ndc(v, p.height, p.width));
 		FaceNdc fndc;
 		fndc.v0 = project(p.ndc, fv[0]); fndc.v1 = project(p.ndc, fv[1]); fndc.v2 = project(p.ndc, fv[2]);
@@ -183,12 +215,11 @@ __global__ void __launch_bounds__(256) assemble_kernel(FitterDeviceData d, DataT
 		const bool rendered_valid = depth > 0 && depth < p.max_depth;
 		float3 wl = make_float3(0.f, 0.f, 0.f);
 		if (rendered_valid) wl = make_float3(((float) u - p.pinhole.cx) * depth / p.pinhole.fx, ((float) v - p.pinhole.cy) * depth / p.pinhole.fy, depth);
-		const float4 ref = d.reference_points[px];
 		const bool mask = rendered_valid && ref.w != 0.f;
 		const float3 pm = make_float3(wl.x - ref.x, wl.y - ref.y, wl.z - ref.z);
 		const float r_raw = dot3(nl.x, nl.y, nl.z, pm.x, pm.y, pm.z);
 		residual = mask ? r_raw : 0.f;
-		contributes = mask;
+		bool contributes = mask;
 		residual_mask = mask;
 		float3 dr_dnl = pm, dr_dwl = nl;
 		if (p.use_tukey) {
@@ -205,6 +236,7 @@ __global__ void __launch_bounds__(256) assemble_kernel(FitterDeviceData d, DataT
 			dr_dwl = psi * nl;
 			residual = rt;
 		}
+		float dr_dV[9], dr_dN[9];
 		if (contributes) {
 			BaryJacobian J;
 			barycentric_jacobian(J, ray, fv, p.ndc, p.perspective_correct != 0, rho);
@@ -218,7 +250,27 @@ __global__ void __launch_bounds__(256) assemble_kernel(FitterDeviceData d, DataT
 				dr_dV[c] = a + b;
 				dr_dN[c] = (c % 3 == 0 ? dr_dnl.x : c % 3 == 1 ? dr_dnl.y : dr_dnl.z) * rho[c / 3];
 			}
-			entry_count = d.face_anchor_counts[face];
+		}
+		cp_async_wait_all();
+		if (contributes) {
+			// turn every (face vertex, anchor slot) record into its 1 x 6 Jacobian contribution, in place
+#pragma unroll
+			for (int fvi = 0; fvi < 3; fvi++) {
+				const float3 dv = make_float3(dr_dV[fvi * 3], dr_dV[fvi * 3 + 1], dr_dV[fvi * 3 + 2]);
+				const float3 dn = make_float3(dr_dN[fvi * 3], dr_dN[fvi * 3 + 1], dr_dN[fvi * 3 + 2]);
+#pragma unroll
+				for (int slot = 0; slot < A; slot++) {
+					float4* r = s_rec + ((fvi * A + slot) * 2) * T + tid;
+					const float4 rec0 = r[0], rec1 = r[T];
+					const float3 a = row_times_skew(dv, make_float3(rec0.x, rec0.y, rec0.z));
+					const float3 b = row_times_skew(dn, make_float3(rec1.x, rec1.y, rec1.z));
+					r[0] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, dv.x * rec0.w);
+					r[T] = make_float4(dv.y * rec0.w, dv.z * rec0.w, 0.f, rec1.w);
+					const int node = __float_as_int(rec1.w);
+					nodes[fvi * A + slot] = node;
+					if (node >= 0) pending |= 1u << (fvi * A + slot);
+				}
+			}
 		}
 	}
 	if (in_image) {
@@ -226,40 +278,30 @@ __global__ void __launch_bounds__(256) assemble_kernel(FitterDeviceData d, DataT
 		d.diag_residuals[px] = residual;
 		d.diag_mask[px] = residual_mask ? 1 : 0;
 	}
-	// stage this pixel's node list
-	for (int k = 0; k < entry_count; k++) s_nodes[threadIdx.x][k] = d.face_anchor_entries[(int64_t) face * kMaxEntries + k].x;
-	__syncwarp();
-	unsigned pending = entry_count > 0 ? ((1u << entry_count) - 1u) : 0u;
+	// node voting: the leader's first pending node is taken up by every lane that has it among its pairs; a node appears at most
+	// once per face vertex, and the pairs are summed in face-vertex order like the reference's per-pixel accumulation
 	while (true) {
 		const unsigned active = __ballot_sync(0xFFFFFFFFu, pending != 0u);
 		if (active == 0u) break;
 		const int leader = __ffs(active) - 1;
 		int my_first_node = -1;
-		if (pending) my_first_node = s_nodes[threadIdx.x][__ffs(pending) - 1];
+		if (pending) my_first_node = __float_as_int(s_rec[((__ffs(pending) - 1) * 2 + 1) * T + tid].w);
 		const int node = __shfl_sync(0xFFFFFFFFu, my_first_node, leader);
-		int k_found = -1;
-		for (int k = 0; k < entry_count; k++)
-			if (((pending >> k) & 1u) && s_nodes[threadIdx.x][k] == node) k_found = k;
+		unsigned match = 0u;
+#pragma unroll
+		for (int q = 0; q < kMaxEntries; q++) match |= (nodes[q] == node ? 1u : 0u) << q;
+		match &= pending;
+		pending &= ~match;
 		float vals[32];
 #pragma unroll
 		for (int i = 0; i < 32; i++) vals[i] = 0.f;
-		if (k_found >= 0) {
-			pending &= ~(1u << k_found);
-			const unsigned packed = (unsigned) d.face_anchor_entries[(int64_t) face * kMaxEntries + k_found].y;
+		if (match) {
 			float3 Jr = make_float3(0.f, 0.f, 0.f), Jt = make_float3(0.f, 0.f, 0.f);
-#pragma unroll
-			for (int fvi = 0; fvi < 3; fvi++) {
-				const unsigned slot = (packed >> (8 * fvi)) & 0xFFu;
-				if (slot == 0xFFu) continue;
-				const int vi = fvi == 0 ? tri.x : fvi == 1 ? tri.y : tri.z;
-				const float4 rec0 = d.vertex_jacobians[((int64_t) vi * A + slot) * 2];
-				const float4 rec1 = d.vertex_jacobians[((int64_t) vi * A + slot) * 2 + 1];
-				const float3 dv = make_float3(dr_dV[fvi * 3], dr_dV[fvi * 3 + 1], dr_dV[fvi * 3 + 2]);
-				const float3 dn = make_float3(dr_dN[fvi * 3], dr_dN[fvi * 3 + 1], dr_dN[fvi * 3 + 2]);
-				Jt.x += dv.x * rec0.w; Jt.y += dv.y * rec0.w; Jt.z += dv.z * rec0.w;
-				const float3 a = row_times_skew(dv, make_float3(rec0.x, rec0.y, rec0.z));
-				const float3 b = row_times_skew(dn, make_float3(rec1.x, rec1.y, rec1.z));
-				Jr.x += a.x + b.x; Jr.y += a.y + b.y; Jr.z += a.z + b.z;
+			for (unsigned m = match; m; m &= m - 1u) {
+				const float4* r = s_rec + ((__ffs(m) - 1) * 2) * T + tid;
+				const float4 c0 = r[0], c1 = r[T];
+				Jr.x += c0.x; Jr.y += c0.y; Jr.z += c0.z;
+				Jt.x += c0.w; Jt.y += c1.x; Jt.z += c1.y;
 			}
 			const float J6[6] = {Jr.x, Jr.y, Jr.z, Jt.x, Jt.y, Jt.z};
 			int o = 0;
@@ -296,10 +338,22 @@ void launch_band_raster(const FitterDeviceData& d, const DataTermParams& p, cons
 	band_raster_kernel<<<148 * 2, 256, 0, s>>>(d, p, cam);
 }
 
+template<int A>
+static int launch_assemble_for(const FitterDeviceData& d, const DataTermParams& p, cudaStream_t s) {
+	constexpr size_t bytes = assemble_shared_bytes(A);
+	static bool attribute_set = false;
+	if (bytes > 48 * 1024 && !attribute_set) {
+		if (cudaFuncSetAttribute(assemble_kernel<A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bytes) != cudaSuccess) return kCudaError;
+		attribute_set = true;
+	}
+	const dim3 grid((p.width + 15) / 16, (p.height + 7) / 8);
+	assemble_kernel<A><<<grid, kAssembleThreads, bytes, s>>>(d, p);
+	return kOk;
+}
+
 int launch_assemble(const FitterDeviceData& d, const DataTermParams& p, cudaStream_t s) {
-	const dim3 grid((p.width + 15) / 16, (p.height + 15) / 16);
 	switch (d.anchor_count) {
-#define NNRT_CASE(A_) case A_: assemble_kernel<A_><<<grid, 256, 0, s>>>(d, p); break;
+#define NNRT_CASE(A_) case A_: return launch_assemble_for<A_>(d, p, s);
 		NNRT_CASE(1) NNRT_CASE(2) NNRT_CASE(3) NNRT_CASE(4) NNRT_CASE(5) NNRT_CASE(6) NNRT_CASE(7) NNRT_CASE(8)
 #undef NNRT_CASE
 		default: return kInvalidArgument;
