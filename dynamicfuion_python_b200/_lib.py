@@ -32,6 +32,8 @@ _SIGNATURES = {
     "nnrt_b200_fitter_destroy": (None, [P]),
     "nnrt_b200_fitter_workspace_bytes": (I64, [P]),
     "nnrt_b200_fitter_set_model": (C.c_int, [P, P, P, P, P, P, I32, P, P, I32, P, P, P, P]),
+    "nnrt_b200_fitter_set_graph": (C.c_int, [P, P, P, I32, P, P, I32, P, P]),
+    "nnrt_b200_fitter_set_mesh": (C.c_int, [P, P, P, P, P, P, P]),
     "nnrt_b200_fitter_set_reference_points": (C.c_int, [P, P, P, P]),
     "nnrt_b200_fitter_set_reference_depth": (C.c_int, [P, P, I32, P, F32, P, P]),
     "nnrt_b200_fitter_fit": (C.c_int, [P, P, P, P, P, I32, P]),

@@ -39,32 +39,6 @@ __global__ void __launch_bounds__(256) reference_from_depth_kernel(const TDepth*
 	}
 	dst[i] = out;
 }
-// compact AssociateFacesWithAnchors (cpp/alignment/functional/kernel/AssociateFacesWithAnchorsImpl.h:69-106)
-__global__ void __launch_bounds__(256) face_anchor_table_kernel(const int4* __restrict__ triangles, int64_t face_count,
-                                                                 const int32_t* __restrict__ anchors, int anchor_count,
-                                                                 int2* __restrict__ entries, uint8_t* __restrict__ counts) {
-	const int64_t f = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-	if (f >= face_count) return;
-	const int max_entries = 3 * anchor_count;
-	int2* e = entries + f * max_entries;
-	const int4 tri = triangles[f];
-	int count = 0;
-	for (int fv = 0; fv < 3; fv++) {
-		const int vi = fv == 0 ? tri.x : fv == 1 ? tri.y : tri.z;
-		for (int a = 0; a < anchor_count; a++) {
-			const int node = anchors[(int64_t) vi * anchor_count + a];
-			if (node == -1) continue;
-			int k = 0;
-			while (k < count && e[k].x != node) k++;
-			if (k == count) { e[k] = make_int2(node, (int) 0xFFFFFFFF); count++; }
-			const unsigned packed = (unsigned) e[k].y;
-			e[k].y = (int) ((packed & ~(0xFFu << (8 * fv))) | ((unsigned) a << (8 * fv)));
-		}
-	}
-	for (int k = count; k < max_entries; k++) e[k] = make_int2(-1, (int) 0xFFFFFFFF);
-	counts[f] = (uint8_t) count;
-}
-
 // ---- per-iteration: ARAP term + data term -> block-sparse arrowhead system ---------------------------------------
 struct GraphDeviceData {
 	const float* nodes; int node_count; int arrow_base;
@@ -366,7 +340,7 @@ struct nnrt_b200_fitter {
 	nnrt_b200_fitter_options opt;
 	int64_t V, F, E; int N, A, H, W;
 	int arrow_base = 0, corner_blocks = 0;
-	bool model_set = false, reference_set = false, fused_stem = true;
+	bool graph_set = false, mesh_set = false, reference_set = false, fused_stem = true;
 	// arena
 	char* arena = nullptr; size_t arena_bytes = 0, arena_used = 0;
 	int* host_flags = nullptr;  // pinned
@@ -375,7 +349,7 @@ struct nnrt_b200_fitter {
 	nnrt_b200::GraphDeviceData g{};
 	nnrt_b200::ArrowheadSystem sys{};
 	float4 *positions, *normals, *wpos, *wnrm, *vjac, *refpts;
-	int4* tris; int2* fa_entries; uint8_t* fa_counts;
+	int4* tris;
 	int32_t* anchors; float* weights; float* nodes;
 	int2* edges; float *ew_res, *ew_jac; int *out_offsets, *out_edges, *in_offsets, *in_edges, *wing_columns;
 	float *accum, *sys_diag, *sys_rhs, *wing, *dinv, *stem_y, *wing_x, *schur, *corner_rhs, *x, *corner_scratch;
@@ -404,7 +378,7 @@ static size_t layout(nnrt_b200_fitter* f, bool assign) {
 	(void) assign;
 	f->positions = f->take<float4>(V); f->normals = f->take<float4>(V);
 	f->wpos = f->take<float4>(V); f->wnrm = f->take<float4>(V); f->vjac = f->take<float4>(V * A * 2);
-	f->tris = f->take<int4>(F); f->fa_entries = f->take<int2>(F * 3 * A); f->fa_counts = f->take<uint8_t>(F);
+	f->tris = f->take<int4>(F);
 	f->anchors = f->take<int32_t>(V * A); f->weights = f->take<float>(V * A); f->nodes = f->take<float>((int64_t) N * 3);
 	f->edges = f->take<int2>(E + 1); f->ew_res = f->take<float>(E + 1); f->ew_jac = f->take<float>(E + 1);
 	f->out_offsets = f->take<int>(N + 2); f->out_edges = f->take<int>(E + 1);
@@ -475,18 +449,14 @@ extern "C" void nnrt_b200_fitter_destroy(nnrt_b200_fitter* f) {
 extern "C" int64_t nnrt_b200_fitter_workspace_bytes(const nnrt_b200_fitter* f) { return f ? (int64_t) f->arena_bytes : 0; }
 extern "C" int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter* f) { return (f && !f->fused_stem) ? 7 : 6; }
 
-extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vertex_positions, const float* vertex_normals,
-                                          const int64_t* triangles, const float* nodes, const int32_t* edges, int32_t arrow_base,
+extern "C" int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* f, const float* nodes, const int32_t* edges, int32_t arrow_base,
                                           const int8_t* edge_layer_indices, const float* layer_decimation_radii, int32_t layer_count,
-                                          const float* node_coverage_weights, const int32_t* anchors, const float* anchor_weights,
-                                          void* stream) {
-	NNRT_CHECK_ARG(f, "fitter_set_model: null fitter");
-	NNRT_CHECK_ARG(vertex_positions && triangles && nodes && anchors && anchor_weights, "fitter_set_model: null pointer argument");
-	// cpp/alignment/DeformableMeshToImageFitter.cpp:346-348
-	NNRT_CHECK_ARG(vertex_normals, "Input warped mesh needs to have normals defined; it doesn't.");
+                                          const float* node_coverage_weights, void* stream) {
+	NNRT_CHECK_ARG(f && nodes, "fitter_set_graph: null pointer argument");
 	auto s = (cudaStream_t) stream;
-	const int64_t V = f->V, F = f->F, E = f->E;
-	const int N = f->N, A = f->A;
+	const int64_t E = f->E;
+	const int N = f->N;
+	bool fused_stem = true;
 	if (E > 0) {
 		NNRT_CHECK_ARG(edges, "fitter_set_model: edge_count > 0 but edges is null");
 		NNRT_CHECK_ARG((edge_layer_indices && layer_decimation_radii && layer_count > 0) || node_coverage_weights,
@@ -494,17 +464,8 @@ extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vert
 		NNRT_CHECK_ARG(arrow_base >= 1 && arrow_base <= N, "first_layer_node_count (currently, %d) must be in [1, node_count = %d].", arrow_base, N);
 	} else {
 		arrow_base = N;  // no regularisation edges: block-diagonal system (DeformableMeshToImageFitter.cpp:248-254)
-		f->fused_stem = true;
 	}
-	pack_float4_kernel<<<blocks_for(V, 256), 256, 0, s>>>(vertex_positions, V, f->positions);
-	pack_float4_kernel<<<blocks_for(V, 256), 256, 0, s>>>(vertex_normals, V, f->normals);
-	pack_triangles_kernel<<<blocks_for(F, 256), 256, 0, s>>>(triangles, F, f->tris);
-	NNRT_CUDA(cudaMemcpyAsync(f->anchors, anchors, sizeof(int32_t) * V * A, cudaMemcpyDeviceToDevice, s));
-	NNRT_CUDA(cudaMemcpyAsync(f->weights, anchor_weights, sizeof(float) * V * A, cudaMemcpyDeviceToDevice, s));
 	NNRT_CUDA(cudaMemcpyAsync(f->nodes, nodes, sizeof(float) * N * 3, cudaMemcpyDeviceToDevice, s));
-	face_anchor_table_kernel<<<blocks_for(F, 256), 256, 0, s>>>(f->tris, F, f->anchors, A, f->fa_entries, f->fa_counts);
-	NNRT_LAUNCH_CHECK();
-
 	// graph topology is static for the fit: build CSR + per-edge weights on the host once (the reference re-derives them per iteration)
 	std::vector<int32_t> h_edges((size_t) E * 2);
 	std::vector<int> out_off(N + 2, 0), in_off(N + 2, 0), out_e((size_t) E + 1), in_e((size_t) E + 1), wcol((size_t) E + 1);
@@ -541,7 +502,7 @@ extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vert
 		}
 		int max_degree = 0;
 		for (int i = 0; i < arrow_base; i++) max_degree = out_off[i + 1] > max_degree ? out_off[i + 1] : max_degree;
-		f->fused_stem = max_degree <= kMaxStemDegree;
+		fused_stem = max_degree <= kMaxStemDegree;
 		for (int i = 0; i < arrow_base; i++) out_off[i + 1] += out_off[i];
 		for (int c = 0; c < nc; c++) in_off[c + 1] += in_off[c];
 		std::vector<int> oc(out_off.begin(), out_off.end()), ic(in_off.begin(), in_off.end());
@@ -566,7 +527,9 @@ extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vert
 
 	// dense corner buffers (size depends on arrow_base)
 	const int corner_blocks = N - arrow_base;
+	bool reallocated = false;
 	if (corner_blocks != f->corner_blocks || f->schur == nullptr) {
+		reallocated = true;
 		if (f->schur) { cudaFree(f->schur); f->schur = nullptr; }
 		const size_t n = (size_t) corner_blocks * 6;
 		const size_t scratch = corner_scratch_bytes(corner_blocks);
@@ -577,11 +540,48 @@ extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vert
 		f->corner_rhs = f->schur + schur_floats;
 		f->corner_scratch = corner_needs_global_scratch(corner_blocks) ? f->corner_rhs + n + 16 : nullptr;
 	}
-	f->arrow_base = arrow_base; f->corner_blocks = corner_blocks;
-	f->model_set = true;
-	if (f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
+	// the captured iteration graph bakes in the arrowhead shape and the corner buffers: keep it unless one of them moved
+	if (f->graph_exec && (arrow_base != f->arrow_base || fused_stem != f->fused_stem || reallocated)) {
+		cudaGraphExecDestroy(f->graph_exec);
+		f->graph_exec = nullptr;
+	}
+	f->arrow_base = arrow_base; f->corner_blocks = corner_blocks; f->fused_stem = fused_stem;
+	f->graph_set = true;
 	return kOk;
 }
+
+extern "C" int nnrt_b200_fitter_set_mesh(nnrt_b200_fitter* f, const float* vertex_positions, const float* vertex_normals,
+                                         const int64_t* triangles, const int32_t* anchors, const float* anchor_weights, void* stream) {
+	NNRT_CHECK_ARG(f, "fitter_set_mesh: null fitter");
+	NNRT_CHECK_ARG(vertex_positions && triangles && anchors && anchor_weights, "fitter_set_mesh: null pointer argument");
+	// cpp/alignment/DeformableMeshToImageFitter.cpp:346-348
+	NNRT_CHECK_ARG(vertex_normals, "Input warped mesh needs to have normals defined; it doesn't.");
+	auto s = (cudaStream_t) stream;
+	const int64_t V = f->V, F = f->F;
+	const int A = f->A;
+	pack_float4_kernel<<<blocks_for(V, 256), 256, 0, s>>>(vertex_positions, V, f->positions);
+	pack_float4_kernel<<<blocks_for(V, 256), 256, 0, s>>>(vertex_normals, V, f->normals);
+	pack_triangles_kernel<<<blocks_for(F, 256), 256, 0, s>>>(triangles, F, f->tris);
+	NNRT_CUDA(cudaMemcpyAsync(f->anchors, anchors, sizeof(int32_t) * V * A, cudaMemcpyDeviceToDevice, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->weights, anchor_weights, sizeof(float) * V * A, cudaMemcpyDeviceToDevice, s));
+	NNRT_LAUNCH_CHECK();
+
+	f->mesh_set = true;
+	return kOk;
+}
+
+extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vertex_positions, const float* vertex_normals,
+                                          const int64_t* triangles, const float* nodes, const int32_t* edges, int32_t arrow_base,
+                                          const int8_t* edge_layer_indices, const float* layer_decimation_radii, int32_t layer_count,
+                                          const float* node_coverage_weights, const int32_t* anchors, const float* anchor_weights,
+                                          void* stream) {
+	NNRT_CHECK_ARG(f, "fitter_set_model: null fitter");
+	NNRT_CHECK_ARG(vertex_positions && triangles && nodes && anchors && anchor_weights, "fitter_set_model: null pointer argument");
+	const int rc = nnrt_b200_fitter_set_mesh(f, vertex_positions, vertex_normals, triangles, anchors, anchor_weights, stream);
+	if (rc != kOk) return rc;
+	return nnrt_b200_fitter_set_graph(f, nodes, edges, arrow_base, edge_layer_indices, layer_decimation_radii, layer_count, node_coverage_weights, stream);
+}
+
 
 extern "C" int nnrt_b200_fitter_set_reference_points(nnrt_b200_fitter* f, const float* reference_points, const uint8_t* reference_mask,
                                                      void* stream) {
@@ -619,7 +619,6 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	IterationContext c{};
 	c.d.positions = f->positions; c.d.normals = f->normals; c.d.triangles = f->tris; c.d.vertex_count = f->V; c.d.face_count = f->F;
 	c.d.anchors = f->anchors; c.d.anchor_weights = f->weights; c.d.anchor_count = f->A;
-	c.d.face_anchor_entries = f->fa_entries; c.d.face_anchor_counts = f->fa_counts;
 	c.d.nodes = f->nodes; c.d.node_count = f->N; c.d.arrow_base = f->arrow_base;
 	c.d.warped_positions = f->wpos; c.d.warped_normals = f->wnrm; c.d.vertex_jacobians = f->vjac;
 	c.d.keys = f->keys; c.d.band_queue = f->queue; c.d.counters = f->counters; c.d.band_queue_capacity = (int) (f->F + 65536);
@@ -678,7 +677,7 @@ static int enqueue_iteration(nnrt_b200_fitter* f, const IterationContext& c, flo
 extern "C" int nnrt_b200_fitter_fit(nnrt_b200_fitter* f, float* node_rotations, float* node_translations, const double* intrinsics_host,
                                     const double* extrinsics_host, int32_t iteration_count, void* stream) {
 	NNRT_CHECK_ARG(f && node_rotations && node_translations && intrinsics_host, "fitter_fit: null pointer argument");
-	NNRT_CHECK_ARG(f->model_set, "fitter_fit: set_model has not been called");
+	NNRT_CHECK_ARG(f->graph_set && f->mesh_set, "fitter_fit: set_model has not been called");
 	NNRT_CHECK_ARG(f->reference_set, "fitter_fit: no reference observation set");
 	if (iteration_count <= 0) iteration_count = f->opt.max_iteration_count;
 	auto s = (cudaStream_t) stream;
@@ -741,7 +740,7 @@ extern "C" int nnrt_b200_fitter_get_diagnostics(nnrt_b200_fitter* f, float* hess
 extern "C" int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* f, float* node_rotations, float* node_translations,
                                                   const double* intrinsics_host, const double* extrinsics_host, float* stage_ms7, void* stream) {
 	NNRT_CHECK_ARG(f && node_rotations && node_translations && intrinsics_host && stage_ms7, "fitter_profile_iteration: null pointer argument");
-	NNRT_CHECK_ARG(f->model_set && f->reference_set, "fitter_profile_iteration: model / reference not set");
+	NNRT_CHECK_ARG(f->graph_set && f->mesh_set && f->reference_set, "fitter_profile_iteration: model / reference not set");
 	static const double I4[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
 	auto s = (cudaStream_t) stream;
 	const IterationContext c = make_context(f, intrinsics_host, extrinsics_host ? extrinsics_host : I4);

@@ -33,7 +33,6 @@ struct FitterDeviceData {
 	// mesh
 	const float4* positions; const float4* normals; const int4* triangles; int64_t vertex_count; int64_t face_count;
 	const int32_t* anchors; const float* anchor_weights; int anchor_count;
-	const int2* face_anchor_entries; const uint8_t* face_anchor_counts;
 	// graph
 	const float* nodes; int node_count; int arrow_base;
 	// per-iteration buffers

@@ -86,8 +86,15 @@ class DeformableMeshToImageFitter:
             else:
                 ncw = warp_field.node_coverage_weights
         base = getattr(warp_field, "first_layer_node_count", n)
-        T.call("nnrt_b200_fitter_set_model", self._handle, T.ptr(mesh.positions), T.ptr(mesh.normals), T.ptr(mesh.triangles),
-               T.ptr(warp_field.nodes), T.ptr(edges) if e > 0 else None, int(base), T.ptr(eli), T.ptr(radii), int(layer_count), T.ptr(ncw),
+        # The graph belongs to the warp field and is the same object frame after frame; its upload (host-side validation, one
+        # stream synchronisation) is redone only when one of its tensors was replaced or written to (torch version counters).
+        graph_key = (int(base), layer_count) + tuple(None if x is None else (x.data_ptr(), x._version, tuple(x.shape))
+                                                     for x in (warp_field.nodes, edges if e > 0 else None, eli, radii, ncw))
+        if graph_key != self._model_key:
+            T.call("nnrt_b200_fitter_set_graph", self._handle, T.ptr(warp_field.nodes), T.ptr(edges) if e > 0 else None, int(base),
+                   T.ptr(eli), T.ptr(radii), int(layer_count), T.ptr(ncw), T.stream())
+            self._model_key, self._graph_tensors = graph_key, (warp_field.nodes, edges, eli, radii, ncw)  # keep the key's pointers alive
+        T.call("nnrt_b200_fitter_set_mesh", self._handle, T.ptr(mesh.positions), T.ptr(mesh.normals), T.ptr(mesh.triangles),
                T.ptr(anchors), T.ptr(anchor_weights), T.stream())
 
     def _fit(self, warp_field, intrinsic_matrix, extrinsic_matrix, iteration_count=None):

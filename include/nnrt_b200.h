@@ -156,6 +156,16 @@ int nnrt_b200_fitter_set_model(nnrt_b200_fitter* fitter, const float* vertex_pos
                                const int8_t* edge_layer_indices, const float* layer_decimation_radii, int32_t layer_count,
                                const float* node_coverage_weights, const int32_t* anchors, const float* anchor_weights,
                                void* stream);
+/* The two halves of set_model, for callers that track a sequence: the warp field's graph (nodes, edges, edge weights) is
+ * fixed while the canonical mesh changes with every frame (HierarchicalGraphWarpField owns the edges,
+ * geometry/HierarchicalGraphWarpField.h:40-78; FitToImage receives the same field each frame). set_graph validates the
+ * topology on the host (one stream synchronisation) and keeps the captured iteration graph when the arrowhead shape is
+ * unchanged; set_mesh is fully asynchronous. set_model == set_mesh + set_graph. */
+int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* fitter, const float* nodes, const int32_t* edges, int32_t arrow_base,
+                               const int8_t* edge_layer_indices, const float* layer_decimation_radii, int32_t layer_count,
+                               const float* node_coverage_weights, void* stream);
+int nnrt_b200_fitter_set_mesh(nnrt_b200_fitter* fitter, const float* vertex_positions, const float* vertex_normals,
+                              const int64_t* triangles, const int32_t* anchors, const float* anchor_weights, void* stream);
 /* Reference observation: reference_points [H*W,3] f32 + reference_mask [H*W] u8 (FitToImage overload .cpp:85-94),
  * or a depth image (overload .cpp:278-314: depth / depth_scale, unprojected with the camera intrinsics, optional user mask). */
 int nnrt_b200_fitter_set_reference_points(nnrt_b200_fitter* fitter, const float* reference_points, const uint8_t* reference_mask,
