@@ -164,13 +164,27 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
                                                                       float* __restrict__ diag, float* __restrict__ rhs) {
 	__shared__ float s_H[kStemWarps][36], s_b[kStemWarps][8], s_dinv[kStemWarps][36], s_dE[kStemWarps][20];
 	__shared__ float s_B[kStemWarps][kMaxStemDegree][36], s_X[kStemWarps][kMaxStemDegree][36];
-	__shared__ int s_col[kStemWarps][kMaxStemDegree];
+	__shared__ int s_col[kStemWarps][kMaxStemDegree], s_edge[kStemWarps][kMaxStemDegree];
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const int node = blockIdx.x * kStemWarps + wib;
 	if (node >= g.node_count) return;
 	const int nc = sys.node_count - sys.arrow_base, n = nc * 6;
 	float* H = s_H[wib];
 	float* b = s_b[wib];
+	// ---- stem node: lane q fetches and evaluates outgoing edge q, so the dependent loads of all edges (edge list -> endpoints ->
+	// node state) are in flight together and overlap the accumulator read below; the blocks are then summed in edge order
+	int e0 = 0, deg = 0, my_edge = 0, my_col = 0;
+	float3 my_sk = make_float3(0.f, 0.f, 0.f), my_r = make_float3(0.f, 0.f, 0.f);
+	float my_a = 0.f;
+	if (node < g.arrow_base) {
+		e0 = g.out_offsets[node];
+		deg = min(g.out_offsets[node + 1] - e0, kMaxStemDegree);
+		if (lane < deg) {
+			my_edge = g.out_edges[e0 + lane];
+			my_col = g.edges[my_edge].y;
+			arap_edge(g, rotations, translations, my_edge, my_sk, my_a, my_r);
+		}
+	}
 	// ---- data term from the pixel accumulators (21 upper-triangular + 6), cleaned for the next iteration
 	{
 		float* acc = accumulators + (int64_t) node * kAccumStride;
@@ -189,14 +203,13 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 	}
 	__syncwarp();
 	if (node < g.arrow_base) {
-		const int e0 = g.out_offsets[node], deg = min(g.out_offsets[node + 1] - e0, kMaxStemDegree);
+		if (lane < deg) { s_col[wib][lane] = my_col; s_edge[wib][lane] = my_edge; }
 		for (int q = 0; q < deg; q++) {
-			const int e = g.out_edges[e0 + q];
-			float3 sk, r; float a;
-			arap_edge(g, rotations, translations, e, sk, a, r);
+			const float3 sk = make_float3(__shfl_sync(0xFFFFFFFFu, my_sk.x, q), __shfl_sync(0xFFFFFFFFu, my_sk.y, q), __shfl_sync(0xFFFFFFFFu, my_sk.z, q));
+			const float3 r = make_float3(__shfl_sync(0xFFFFFFFFu, my_r.x, q), __shfl_sync(0xFFFFFFFFu, my_r.y, q), __shfl_sync(0xFFFFFFFFu, my_r.z, q));
+			const float a = __shfl_sync(0xFFFFFFFFu, my_a, q);
 			// dE_i (3 x 6) = [skew(s) | a I] staged per warp
 			if (lane < 18) { const int rr = lane / 6, c = lane % 6; s_dE[wib][lane] = c < 3 ? skew_entry(sk, rr, c) : (rr == c - 3 ? a : 0.f); }
-			if (lane == 0) s_col[wib][q] = g.edges[e].y;
 			__syncwarp();
 			const float* dE = s_dE[wib];
 			const float bj = -a;
@@ -268,7 +281,7 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 #pragma unroll
 			for (int m = 0; m < 6; m++) acc += Dinv[rr * 6 + m] * s_B[wib][q][m * 6 + c];
 			s_X[wib][q][k] = acc;
-			sys.wing_x[(int64_t) g.out_edges[e0 + q] * 36 + k] = acc;
+			sys.wing_x[(int64_t) s_edge[wib][q] * 36 + k] = acc;
 		}
 		__syncwarp();
 		// S[c1, c2] -= B_e1^T X_e2 ; with the tile-packed layout only block pairs on or below the diagonal are stored

@@ -320,10 +320,10 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 }
 
 void launch_warp_vertices(const FitterDeviceData& d, const float* rotations, const float* translations, const Rigid& extrinsics, cudaStream_t s) {
-	const unsigned grid = blocks_for(d.vertex_count, 256);
+	const unsigned grid = blocks_for(d.vertex_count, 64);  // small CTAs: the mesh fills the GPU barely once, latency hiding needs every SM
 	if (grid == 0) return;
 	switch (d.anchor_count) {
-#define NNRT_CASE(A_) case A_: warp_vertices_kernel<A_><<<grid, 256, 0, s>>>(d, rotations, translations, extrinsics); break;
+#define NNRT_CASE(A_) case A_: warp_vertices_kernel<A_><<<grid, 64, 0, s>>>(d, rotations, translations, extrinsics); break;
 		NNRT_CASE(1) NNRT_CASE(2) NNRT_CASE(3) NNRT_CASE(4) NNRT_CASE(5) NNRT_CASE(6) NNRT_CASE(7) NNRT_CASE(8)
 #undef NNRT_CASE
 	}
@@ -331,7 +331,7 @@ void launch_warp_vertices(const FitterDeviceData& d, const float* rotations, con
 
 void launch_face_raster(const FitterDeviceData& d, const DataTermParams& p, const NdcCamera& cam, cudaStream_t s) {
 	if (d.face_count == 0) return;
-	face_raster_kernel<<<blocks_for(d.face_count, 256), 256, 0, s>>>(d, p, cam);
+	face_raster_kernel<<<blocks_for(d.face_count, 64), 64, 0, s>>>(d, p, cam);
 }
 
 void launch_band_raster(const FitterDeviceData& d, const DataTermParams& p, const NdcCamera& cam, cudaStream_t s) {
