@@ -32,6 +32,7 @@ _SIGNATURES = {
     "nnrt_b200_fitter_destroy": (None, [P]),
     "nnrt_b200_fitter_workspace_bytes": (I64, [P]),
     "nnrt_b200_fitter_set_model": (C.c_int, [P, P, P, P, P, P, I32, P, P, I32, P, P, P, P]),
+    "nnrt_b200_fitter_set_iteration_modes": (C.c_int, [P, P, I32]),
     "nnrt_b200_fitter_set_graph": (C.c_int, [P, P, P, I32, P, P, I32, P, P]),
     "nnrt_b200_fitter_set_mesh": (C.c_int, [P, P, P, P, P, P, P]),
     "nnrt_b200_fitter_set_reference_points": (C.c_int, [P, P, P, P]),

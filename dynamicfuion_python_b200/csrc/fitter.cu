@@ -48,6 +48,7 @@ struct GraphDeviceData {
 	const int* out_offsets; const int* out_edges;  // CSR: edges by stem node i (== wing rows)
 	const int* in_offsets; const int* in_edges;    // CSR: edges by corner node j
 	float arap_weight; float lm_factor; int use_huber; float huber_constant;
+	int iteration_mode;  // IterationMode of this iteration: 0 ALL, 1 TRANSLATION_ONLY, 2 ROTATION_ONLY (non-ALL: edge-free fits only)
 };
 
 __device__ __forceinline__ void arap_edge(const GraphDeviceData& g, const float* __restrict__ rotations, const float* __restrict__ translations,
@@ -223,6 +224,18 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 		}
 		if (lane < 6 && g.lm_factor > 0.f) H[lane * 7] += g.lm_factor;
 		__syncwarp();
+		if (g.iteration_mode != 0) {
+			// TRANSLATION_ONLY / ROTATION_ONLY (DeformableMeshToImageFitter.cpp:198, 262-272): the reference solves the 3 x 3 block of the
+			// active half. Decoupling the other half (identity block, zero right-hand side) makes the 6 x 6 factorisation perform the
+			// same operations on the active block and adds exact zeros elsewhere.
+			const int lo = g.iteration_mode == 1 ? 0 : 3;  // first row of the inactive half
+			for (int k = lane; k < 36; k += 32) {
+				const int rr = k / 6, c = k % 6;
+				if ((rr >= lo && rr < lo + 3) || (c >= lo && c < lo + 3)) H[k] = rr == c ? 1.f : 0.f;
+			}
+			if (lane >= lo && lane < lo + 3) b[lane] = 0.f;
+			__syncwarp();
+		}
 		for (int k = lane; k < 36; k += 32) diag[(int64_t) node * 36 + k] = H[k];
 		if (lane < 6) rhs[node * 6 + lane] = b[lane];
 		// ---- D^-1: every one of six lanes factors H (redundantly) and solves for its unit column
@@ -354,6 +367,7 @@ struct nnrt_b200_fitter {
 	int64_t V, F, E; int N, A, H, W;
 	int arrow_base = 0, corner_blocks = 0;
 	bool graph_set = false, mesh_set = false, reference_set = false, fused_stem = true;
+	std::vector<int> modes{0};  // IterationMode sequence, cycled by iteration index (DeformableMeshToImageFitter.cpp:112)
 	// arena
 	char* arena = nullptr; size_t arena_bytes = 0, arena_used = 0;
 	int* host_flags = nullptr;  // pinned
@@ -659,7 +673,11 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 }
 
 // One GN/LM iteration = 7 launches. `ev` (optional, 8 events = 7 stages) brackets the stages for profile_iteration.
-static int enqueue_iteration(nnrt_b200_fitter* f, const IterationContext& c, float* R, float* t, cudaStream_t s, cudaEvent_t* ev) {
+static int enqueue_iteration(nnrt_b200_fitter* f, const IterationContext& base, int iteration_mode, float* R, float* t, cudaStream_t s,
+                             cudaEvent_t* ev) {
+	IterationContext c = base;
+	c.g.iteration_mode = iteration_mode;
+	c.sys.update_mode = iteration_mode;
 	if (ev) cudaEventRecord(ev[0], s);
 	launch_warp_vertices(c.d, R, t, c.extrinsics, s);
 	if (ev) cudaEventRecord(ev[1], s);
@@ -687,12 +705,25 @@ static int enqueue_iteration(nnrt_b200_fitter* f, const IterationContext& c, flo
 
 }  // namespace nnrt_b200
 
+extern "C" int nnrt_b200_fitter_set_iteration_modes(nnrt_b200_fitter* f, const int32_t* modes_host, int32_t mode_count) {
+	NNRT_CHECK_ARG(f && modes_host && mode_count > 0, "fitter_set_iteration_modes: need at least one mode");
+	std::vector<int> modes(modes_host, modes_host + mode_count);
+	for (int m : modes) NNRT_CHECK_ARG(m >= 0 && m <= 2, "iteration mode %d is not one of ALL (0), TRANSLATION_ONLY (1), ROTATION_ONLY (2)", m);
+	if (modes != f->modes && f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
+	f->modes = modes;
+	return kOk;
+}
+
 extern "C" int nnrt_b200_fitter_fit(nnrt_b200_fitter* f, float* node_rotations, float* node_translations, const double* intrinsics_host,
                                     const double* extrinsics_host, int32_t iteration_count, void* stream) {
 	NNRT_CHECK_ARG(f && node_rotations && node_translations && intrinsics_host, "fitter_fit: null pointer argument");
 	NNRT_CHECK_ARG(f->graph_set && f->mesh_set, "fitter_fit: set_model has not been called");
 	NNRT_CHECK_ARG(f->reference_set, "fitter_fit: no reference observation set");
 	if (iteration_count <= 0) iteration_count = f->opt.max_iteration_count;
+	if (f->E > 0)
+		for (int m : f->modes)
+			NNRT_CHECK_ARG(m == 0, "TRANSLATION_ONLY / ROTATION_ONLY iterations need a warp field without regularisation edges: the reference's ARAP "
+			                       "Hessian has 6 x 6 blocks only (ArapHessianImpl.h:54-56) and cannot be added to the 3 x 3 depth blocks of those modes");
 	auto s = (cudaStream_t) stream;
 	static const double I4[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
 	const double* T = extrinsics_host ? extrinsics_host : I4;
@@ -706,7 +737,8 @@ extern "C" int nnrt_b200_fitter_fit(nnrt_b200_fitter* f, float* node_rotations, 
 		NNRT_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
 		NNRT_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
 		int rc = kOk;
-		for (int it = 0; it < iteration_count && rc == kOk; it++) rc = enqueue_iteration(f, c, node_rotations, node_translations, cs, nullptr);
+		for (int it = 0; it < iteration_count && rc == kOk; it++)
+			rc = enqueue_iteration(f, c, f->modes[(size_t) it % f->modes.size()], node_rotations, node_translations, cs, nullptr);
 		cudaGraph_t graph = nullptr;
 		const cudaError_t end = cudaStreamEndCapture(cs, &graph);
 		cudaStreamDestroy(cs);
@@ -759,7 +791,7 @@ extern "C" int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* f, float* no
 	const IterationContext c = make_context(f, intrinsics_host, extrinsics_host ? extrinsics_host : I4);
 	cudaEvent_t ev[8];
 	for (auto& e : ev) NNRT_CUDA(cudaEventCreate(&e));
-	const int rc = enqueue_iteration(f, c, node_rotations, node_translations, s, ev);
+	const int rc = enqueue_iteration(f, c, f->modes[0], node_rotations, node_translations, s, ev);
 	NNRT_CUDA(cudaStreamSynchronize(s));
 	for (int k = 0; k < 7; k++) cudaEventElapsedTime(stage_ms7 + k, ev[k], ev[k + 1]);
 	for (auto& e : ev) cudaEventDestroy(e);

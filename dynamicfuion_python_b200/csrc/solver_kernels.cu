@@ -148,22 +148,29 @@ __device__ void rodrigues(const float* __restrict__ w, float* __restrict__ R) {
 
 
 // node update (DeformableMeshToImageFitter.cpp:258-273, HierarchicalGraphWarpField.cpp:261-284): t += dt, R <- R * Rodrigues(dw)
-__device__ __forceinline__ void apply_node_update(const float* __restrict__ dlt, float* __restrict__ rotation, float* __restrict__ translation) {
-	float dR[9], R[9];
-	rodrigues(dlt, dR);
+// `mode` follows IterationMode (DeformableMeshToImageFitter.cpp:258-273): TRANSLATION_ONLY (1) never evaluates Rodrigues (a zero
+// rotation update would be 0 / 0 there), ROTATION_ONLY (2) leaves the translations untouched.
+__device__ __forceinline__ void apply_node_update(const float* __restrict__ dlt, float* __restrict__ rotation, float* __restrict__ translation,
+                                                  int mode) {
+	if (mode != 1) {
+		float dR[9], R[9];
+		rodrigues(dlt, dR);
 #pragma unroll
-	for (int k = 0; k < 9; k++) R[k] = rotation[k];
+		for (int k = 0; k < 9; k++) R[k] = rotation[k];
 #pragma unroll
-	for (int r = 0; r < 3; r++)
+		for (int r = 0; r < 3; r++)
 #pragma unroll
-		for (int c = 0; c < 3; c++) {
-			float acc = 0.f;
+			for (int c = 0; c < 3; c++) {
+				float acc = 0.f;
 #pragma unroll
-			for (int k = 0; k < 3; k++) acc += R[r * 3 + k] * dR[k * 3 + c];
-			rotation[r * 3 + c] = acc;
-		}
+				for (int k = 0; k < 3; k++) acc += R[r * 3 + k] * dR[k * 3 + c];
+				rotation[r * 3 + c] = acc;
+			}
+	}
+	if (mode != 2) {
 #pragma unroll
-	for (int c = 0; c < 3; c++) translation[c] = translation[c] + dlt[3 + c];
+		for (int c = 0; c < 3; c++) translation[c] = translation[c] + dlt[3 + c];
+	}
 }
 
 template<bool kSharedScratch>
@@ -242,25 +249,7 @@ __global__ void __launch_bounds__(1024) corner_solve_kernel(ArrowheadSystem sys,
 	if (rotations == nullptr) return;
 	__syncthreads();
 	__threadfence_block();
-	// node update (DeformableMeshToImageFitter.cpp:258-273, HierarchicalGraphWarpField.cpp:261-284): t += dt, R <- R * Rodrigues(dw)
-	for (int node = tid; node < sys.node_count; node += T) {
-		const float* dlt = x + node * 6;
-		float dR[9], R[9];
-		rodrigues(dlt, dR);
-#pragma unroll
-		for (int k = 0; k < 9; k++) R[k] = rotations[node * 9 + k];
-#pragma unroll
-		for (int r = 0; r < 3; r++)
-#pragma unroll
-			for (int c = 0; c < 3; c++) {
-				float acc = 0.f;
-#pragma unroll
-				for (int k = 0; k < 3; k++) acc += R[r * 3 + k] * dR[k * 3 + c];
-				rotations[node * 9 + r * 3 + c] = acc;
-			}
-#pragma unroll
-		for (int c = 0; c < 3; c++) translations[node * 3 + c] = translations[node * 3 + c] + dlt[3 + c];
-	}
+	for (int node = tid; node < sys.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3, sys.update_mode);
 }
 
 
@@ -547,7 +536,7 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_blocked_kernel(Ar
 	__syncthreads();
 	NNRT_STAMP(4);
 	__threadfence_block();
-	for (int node = tid; node < sys.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3);
+	for (int node = tid; node < sys.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3, sys.update_mode);
 #ifdef NNRT_PHASE_TIMING
 	__syncthreads();
 	NNRT_STAMP(5);
@@ -921,7 +910,7 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 	__syncthreads();
 	NNRT_STAMP(4);
 	__threadfence_block();
-	for (int node = tid; node < sys.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3);
+	for (int node = tid; node < sys.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3, sys.update_mode);
 #ifdef NNRT_PHASE_TIMING
 	__syncthreads();
 	NNRT_STAMP(5);

@@ -29,6 +29,7 @@ struct ArrowheadSystem {
 	float* corner_rhs;              // [6Nc], must be zero on entry (unused when schur_tile_packed)
 	int schur_tile_packed;          // 1: the register-tiled corner kernel consumes `schur` as warp-interleaved 8 x 8 tiles (see corner_tile_index)
 	int* flags;                     // flags[2] set when a block is not positive definite
+	int update_mode;                // node update applied by the corner kernels: 0 rotation + translation, 1 translation only, 2 rotation only
 };
 
 // ---- corner layouts ---------------------------------------------------------------------------------------------------------

@@ -26,8 +26,6 @@ class DeformableMeshToImageFitter:
             raise RuntimeError("`preconditioning_dampening_factor` should be a small non-negative value between 0 and 1. "
                                f"Got {preconditioning_dampening_factor}.")
         modes = [IterationMode(m) for m in iteration_mode_sequence]
-        if any(m != IterationMode.ALL for m in modes):
-            raise RuntimeError("this build implements IterationMode.ALL; TRANSLATION_ONLY / ROTATION_ONLY are not built yet")
         self.max_iteration_count = int(max_iteration_count)
         self.iteration_mode_sequence = modes
         self.min_update_threshold = float(minimal_update_threshold)  # the reference never updates `maximum_update` (:100,111): unused
@@ -56,6 +54,8 @@ class DeformableMeshToImageFitter:
         v, f, n, e, a, h, w = shape
         _lib.check(_lib.lib().nnrt_b200_fitter_create(C.byref(self.options), v, f, n, e, a, h, w, C.byref(handle)))
         self._handle, self._shape, self._model_key = handle, shape, None
+        modes = (C.c_int32 * len(self.iteration_mode_sequence))(*[int(m) for m in self.iteration_mode_sequence])
+        _lib.check(_lib.lib().nnrt_b200_fitter_set_iteration_modes(handle, modes, len(self.iteration_mode_sequence)))
 
     def workspace_bytes(self):
         return 0 if self._handle is None else _lib.lib().nnrt_b200_fitter_workspace_bytes(self._handle)

@@ -166,6 +166,10 @@ int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* fitter, const float* nodes, con
                                const float* node_coverage_weights, void* stream);
 int nnrt_b200_fitter_set_mesh(nnrt_b200_fitter* fitter, const float* vertex_positions, const float* vertex_normals,
                               const int64_t* triangles, const int32_t* anchors, const float* anchor_weights, void* stream);
+/* IterationMode sequence (alignment/IterationMode.h:24-28: 0 ALL, 1 TRANSLATION_ONLY, 2 ROTATION_ONLY), host array, cycled by
+ * iteration % count (DeformableMeshToImageFitter.cpp:112). Default {ALL}. Non-ALL modes solve the 3 x 3 block of the active half
+ * (.cpp:198, 262-272) and are defined for edge-free warp fields only, as in the reference (fit returns an error otherwise). */
+int nnrt_b200_fitter_set_iteration_modes(nnrt_b200_fitter* fitter, const int32_t* modes_host, int32_t mode_count);
 /* Reference observation: reference_points [H*W,3] f32 + reference_mask [H*W] u8 (FitToImage overload .cpp:85-94),
  * or a depth image (overload .cpp:278-314: depth / depth_scale, unprojected with the camera intrinsics, optional user mask). */
 int nnrt_b200_fitter_set_reference_points(nnrt_b200_fitter* fitter, const float* reference_points, const uint8_t* reference_mask,

@@ -65,6 +65,9 @@ struct OracleFitParams {
 	float* trace_hessian_diag; float* trace_negative_gradient; float* trace_deltas;
 	int64_t* last_pixel_faces; float* last_residuals; uint8_t* last_residual_mask;
 	double* stage_seconds;  // optional [8]: warp, faces, raster, residual, jacobians, assembly, arap, solve+update
+	// IterationMode sequence (cpp/alignment/IterationMode.h: 0 ALL, 1 TRANSLATION_ONLY, 2 ROTATION_ONLY), cycled by
+	// iteration % count (DeformableMeshToImageFitter.cpp:112); null / 0 = {ALL}
+	const int32_t* iteration_modes; int32_t iteration_mode_count;
 };
 
 #include <chrono>
@@ -99,6 +102,11 @@ ORACLE_API int oracle_fit_to_image(OracleFitParams* p) {
 	double st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
 	for (int iteration = 0; iteration < p->iteration_count; iteration++) {
+		const int mode = (p->iteration_modes && p->iteration_mode_count > 0) ? p->iteration_modes[iteration % p->iteration_mode_count] : 0;
+		// The reference's ARAP Hessian only exists for 6 x 6 blocks (ArapHessianImpl.h:54-56) while the depth blocks of a
+		// TRANSLATION_ONLY / ROTATION_ONLY iteration are 3 x 3 (.cpp:198, kernel/DeformableMeshToImageFitterImpl.h:219-226): their sum
+		// at .cpp:235 cannot be formed, so those modes are defined without regularisation edges only.
+		if (mode != 0 && use_edges) return -3;
 		double t0 = now_s();
 		oracle_warp_points_normals(p->vertex_positions, p->vertex_normals, V, p->nodes, p->node_rotations, p->node_translations,
 		                           p->anchors, p->anchor_weights, A, 0, p->extrinsics, wpos.data(), wnrm.data());
@@ -187,16 +195,49 @@ ORACLE_API int oracle_fit_to_image(OracleFitParams* p) {
 			failures = oracle_solve_arrowhead_cholesky(Hdiag.data(), N, p->arrow_base, wing.data(), wing_coord.data(), E, nullptr, nullptr, 0,
 			                                           g.data(), delta.data());
 			if (p->trace_hessian_diag) std::copy(Hdiag.begin(), Hdiag.end(), p->trace_hessian_diag + (size_t) iteration * N * 36);
-		} else {
+		} else if (mode == 0) {
 			if (p->levenberg_marquardt_factor > 0.f) oracle_precondition_diagonal_blocks(Hd.data(), N, 6, p->levenberg_marquardt_factor);
 			t7 = now_s();
 			failures = oracle_solve_block_diagonal_cholesky(Hd.data(), g.data(), N, 6, delta.data());
 			if (p->trace_hessian_diag) std::copy(Hd.begin(), Hd.end(), p->trace_hessian_diag + (size_t) iteration * N * 36);
+		} else {
+			// 3-wide pixel Jacobians hold exactly the translation (resp. rotation) half of the 6-wide ones
+			// (PixelVertexAnchorJacobiansImpl.h:278-330: same addends, same order), and every block entry is its own sum over the node's
+			// pixel list (kernel/DeformableMeshToImageFitterImpl.h:264-284), so the 3 x 3 blocks and 3-vectors are sub-blocks of Hd and g.
+			const int off = mode == 1 ? 3 : 0;
+			std::vector<float> H3((size_t) N * 9), g3((size_t) N * 3), d3((size_t) N * 3);
+			for (int n = 0; n < N; n++)
+				for (int r = 0; r < 3; r++) {
+					g3[n * 3 + r] = g[n * 6 + off + r];
+					for (int c = 0; c < 3; c++) H3[n * 9 + r * 3 + c] = Hd[(size_t) n * 36 + (off + r) * 6 + off + c];
+				}
+			if (p->levenberg_marquardt_factor > 0.f) oracle_precondition_diagonal_blocks(H3.data(), N, 3, p->levenberg_marquardt_factor);
+			t7 = now_s();
+			failures = oracle_solve_block_diagonal_cholesky(H3.data(), g3.data(), N, 3, d3.data());
+			// traces keep the 6-wide layout: the inactive half is reported as zero
+			std::fill(delta.begin(), delta.end(), 0.f);
+			std::vector<float> Ht((size_t) N * 36, 0.f), gt((size_t) N * 6, 0.f);
+			for (int n = 0; n < N; n++)
+				for (int r = 0; r < 3; r++) {
+					delta[n * 6 + off + r] = d3[n * 3 + r];
+					gt[n * 6 + off + r] = g3[n * 3 + r];
+					for (int c = 0; c < 3; c++) Ht[(size_t) n * 36 + (off + r) * 6 + off + c] = H3[n * 9 + r * 3 + c];
+				}
+			g = gt;
+			if (p->trace_hessian_diag) std::copy(Ht.begin(), Ht.end(), p->trace_hessian_diag + (size_t) iteration * N * 36);
 		}
 		(void) failures;
 		if (p->trace_negative_gradient) std::copy(g.begin(), g.end(), p->trace_negative_gradient + (size_t) iteration * N * 6);
 		if (p->trace_deltas) std::copy(delta.begin(), delta.end(), p->trace_deltas + (size_t) iteration * N * 6);
-		oracle_apply_node_updates(delta.data(), N, p->node_rotations, p->node_translations);
+		if (mode == 0) {
+			oracle_apply_node_updates(delta.data(), N, p->node_rotations, p->node_translations);
+		} else if (mode == 1) {  // .cpp:266-268: TranslateNodes only
+			for (int i = 0; i < N * 3; i++) p->node_translations[i] = p->node_translations[i] + delta[(i / 3) * 6 + 3 + i % 3];
+		} else {                 // .cpp:269-272: Rodrigues + RotateNodes only
+			std::vector<float> saved(p->node_translations, p->node_translations + (size_t) N * 3);
+			oracle_apply_node_updates(delta.data(), N, p->node_rotations, p->node_translations);
+			std::copy(saved.begin(), saved.end(), p->node_translations);
+		}
 		st[7] += now_s() - t7;
 	}
 	if (p->last_pixel_faces) std::copy(pix_face.begin(), pix_face.end(), p->last_pixel_faces);

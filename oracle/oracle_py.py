@@ -272,6 +272,7 @@ class _FitParams(C.Structure):
         ("trace_hessian_diag", C.c_void_p), ("trace_negative_gradient", C.c_void_p), ("trace_deltas", C.c_void_p),
         ("last_pixel_faces", C.c_void_p), ("last_residuals", C.c_void_p), ("last_residual_mask", C.c_void_p),
         ("stage_seconds", C.c_void_p),
+        ("iteration_modes", C.c_void_p), ("iteration_mode_count", C.c_int32),
     ]
 
 
@@ -279,7 +280,7 @@ def fit_to_image(positions, normals, triangles, nodes, edges, arrow_base, anchor
                  height, width, K, extrinsics=None, rotations=None, translations=None, iteration_count=10,
                  use_perspective_correction=True, max_depth=10.0, use_tukey=False, tukey_cutoff=0.01, lm_factor=0.0,
                  arap_term_weight=200.0, use_huber=False, huber_constant=1e-4, edge_layer_indices=None, layer_radii=None,
-                 node_coverage_weights=None, max_pixels_per_node=0, parallel=False, trace=True):
+                 node_coverage_weights=None, max_pixels_per_node=0, parallel=False, trace=True, iteration_modes=None):
     """The reference GN loop on the CPU. Returns dict with final rotations/translations and per-iteration traces."""
     positions, normals, triangles = _f32(positions), _f32(normals), _i64(triangles)
     nodes = _f32(nodes)
@@ -305,6 +306,7 @@ def fit_to_image(positions, normals, triangles, nodes, edges, arrow_base, anchor
     last_res = np.empty(PX, np.float32)
     last_mask = np.empty(PX, np.uint8)
     stage = np.zeros(8, np.float64)
+    modes = None if iteration_modes is None else np.ascontiguousarray([int(m) for m in iteration_modes], np.int32)  # 0 ALL, 1 TRANSLATION_ONLY, 2 ROTATION_ONLY
     p = _FitParams(
         _p(positions), _p(normals), _p(triangles), positions.shape[0], triangles.shape[0],
         _p(nodes), N, _p(edges), edges.shape[0], arrow_base, _p(eli), _p(radii), _p(ncw),
@@ -312,7 +314,8 @@ def fit_to_image(positions, normals, triangles, nodes, edges, arrow_base, anchor
         _p(ref_pts), _p(ref_mask), height, width, _p(Kd), _p(ext),
         iteration_count, int(use_perspective_correction), max_depth, int(use_tukey), tukey_cutoff, lm_factor,
         arap_term_weight, int(use_huber), huber_constant, max_pixels_per_node, int(parallel),
-        _p(R), _p(t), _p(tr_H), _p(tr_g), _p(tr_d), _p(last_faces), _p(last_res), _p(last_mask), _p(stage))
+        _p(R), _p(t), _p(tr_H), _p(tr_g), _p(tr_d), _p(last_faces), _p(last_res), _p(last_mask), _p(stage),
+        _p(modes), 0 if modes is None else len(modes))
     rc = lib().oracle_fit_to_image(C.byref(p))
     if rc != 0:
         raise RuntimeError(f"oracle_fit_to_image failed: {rc}")

@@ -187,3 +187,55 @@ def test_fitter_argument_errors(nnrt):
         nnrt.alignment.DeformableMeshToImageFitter(preconditioning_dampening_factor=1.5)
     with pytest.raises(RuntimeError):
         nnrt.geometry.GraphWarpField(np.zeros((2, 3), np.float32), anchor_count=4)
+
+
+def test_iteration_mode_sequence(nnrt, oracle):
+    """IterationMode sequence (ALL, TRANSLATION_ONLY, ROTATION_ONLY) cycled by iteration index on an edge-free warp field
+    (cpp/alignment/DeformableMeshToImageFitter.cpp:112,198,258-273): each iteration is checked against the oracle started from the
+    GPU's state, the inactive half of the update is exactly zero and the corresponding node state is left bit-identical."""
+    s = scene_with_target(oracle, "C1", 120, 160)
+    assert len(s["edges"]) == 0
+    A = nnrt.alignment
+    modes = [A.IterationMode.ALL, A.IterationMode.TRANSLATION_ONLY, A.IterationMode.ROTATION_ONLY]
+    G = nnrt.geometry
+    wf = G.HierarchicalGraphWarpField(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+                                      G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
+    mesh = (s["positions"], s["normals"], s["triangles"])
+    for it, mode in enumerate(modes):
+        fitter = A.DeformableMeshToImageFitter(max_iteration_count=1, iteration_mode_sequence=[mode],
+                                               preconditioning_dampening_factor=s["lm_factor"], arap_term_weight=s["arap_term_weight"])
+        R0, t0 = _np(wf.node_rotations).copy(), _np(wf.node_translations).copy()
+        fitter.fit_to_image(wf, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]),
+                            anchors=s["anchors"], anchor_weights=s["anchor_weights"])
+        fitter.check_status()
+        ref = oracle_fit(oracle, s, 1, rotations=R0, translations=t0, iteration_modes=[int(mode)])
+        d = _np(fitter.diagnostics()["deltas"])
+        ok, worst = rel_close(d, ref["deltas"][0], 1e-3, floor_scale=1e-2)
+        assert ok, f"mode {mode.name}: deltas {worst}"
+        if mode == A.IterationMode.TRANSLATION_ONLY:
+            assert np.all(d[:, :3] == 0) and np.array_equal(_np(wf.node_rotations), R0)
+        if mode == A.IterationMode.ROTATION_ONLY:
+            assert np.all(d[:, 3:] == 0) and np.array_equal(_np(wf.node_translations), t0)
+        np.testing.assert_allclose(_np(wf.node_translations), ref["translations"], rtol=1e-3, atol=1e-6)
+        np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
+    # the same sequence inside one captured graph: three iterations, modes cycled by iteration index
+    wf2 = G.HierarchicalGraphWarpField(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+                                       G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
+    fitter = A.DeformableMeshToImageFitter(max_iteration_count=3, iteration_mode_sequence=modes,
+                                           preconditioning_dampening_factor=s["lm_factor"], arap_term_weight=s["arap_term_weight"])
+    fitter.fit_to_image(wf2, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]),
+                        anchors=s["anchors"], anchor_weights=s["anchor_weights"])
+    fitter.check_status()
+    ref = oracle_fit(oracle, s, 3, iteration_modes=[int(m) for m in modes])
+    # free-running: two fp32 implementations drift apart slowly (see test_ten_iterations_free_running)
+    assert np.abs(_np(wf2.node_translations) - ref["translations"]).max() <= 1e-2 * np.abs(ref["translations"]).max()
+    assert np.abs(_np(wf2.node_rotations) - ref["rotations"]).max() <= 1e-3
+
+
+def test_iteration_modes_need_edge_free_field(nnrt, oracle):
+    """With regularisation edges the reference cannot form H = ARAP (6 x 6) + depth (3 x 3): both sides refuse."""
+    s = scene_with_target(oracle, "tinyr", 120, 160)
+    with pytest.raises(RuntimeError):
+        _gpu_fit(nnrt, s, 1, iteration_mode_sequence=[nnrt.alignment.IterationMode.TRANSLATION_ONLY])
+    with pytest.raises(RuntimeError):
+        oracle_fit(oracle, s, 1, iteration_modes=[1])
