@@ -33,6 +33,10 @@ _SIGNATURES = {
     "nnrt_b200_fitter_workspace_bytes": (I64, [P]),
     "nnrt_b200_fitter_set_model": (C.c_int, [P, P, P, P, P, P, I32, P, P, I32, P, P, P, P]),
     "nnrt_b200_fitter_set_iteration_modes": (C.c_int, [P, P, I32]),
+    "nnrt_b200_fitter_set_pixel_rows": (C.c_int, [P, I32, I32]),
+    "nnrt_b200_fitter_accumulators": (P, [P, P]),
+    "nnrt_b200_fitter_iteration_data_term": (C.c_int, [P, P, P, P, P, P]),
+    "nnrt_b200_fitter_iteration_solve": (C.c_int, [P, P, P, P, P, I32, P]),
     "nnrt_b200_fitter_set_graph": (C.c_int, [P, P, P, I32, P, P, I32, P, P]),
     "nnrt_b200_fitter_set_mesh": (C.c_int, [P, P, P, P, P, P, P]),
     "nnrt_b200_fitter_set_reference_points": (C.c_int, [P, P, P, P]),

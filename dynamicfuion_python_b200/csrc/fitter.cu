@@ -367,6 +367,7 @@ struct nnrt_b200_fitter {
 	int64_t V, F, E; int N, A, H, W;
 	int arrow_base = 0, corner_blocks = 0;
 	bool graph_set = false, mesh_set = false, reference_set = false, fused_stem = true;
+	int row_begin = 0, row_end = 0;  // pixel band of a pixel-sharded fit; row_end == 0: whole image
 	std::vector<int> modes{0};  // IterationMode sequence, cycled by iteration index (DeformableMeshToImageFitter.cpp:112)
 	// arena
 	char* arena = nullptr; size_t arena_bytes = 0, arena_used = 0;
@@ -668,16 +669,24 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	c.p.tukey_cutoff = f->opt.tukey_penalty_cutoff;
 	// RasterizeNdcTriangles(..., blur 0.5 px, ...) (DeformableMeshToImageFitter.cpp:124-127); ImageSpaceDistanceToNdc
 	c.p.blur_radius = 0.5f / (fminf((float) f->H, (float) f->W) / 2.0f);
+	c.p.row_begin = f->row_begin; c.p.row_end = f->row_end > 0 ? f->row_end : f->H;
 	c.extrinsics = rigid_from_host(T);
 	return c;
 }
 
 // One GN/LM iteration = 7 launches. `ev` (optional, 8 events = 7 stages) brackets the stages for profile_iteration.
+static int enqueue_data_term(const IterationContext& c, float* R, float* t, cudaStream_t s, cudaEvent_t* ev);
+static int enqueue_solve(nnrt_b200_fitter* f, const IterationContext& base, int iteration_mode, float* R, float* t, cudaStream_t s,
+                         cudaEvent_t* ev);
+
 static int enqueue_iteration(nnrt_b200_fitter* f, const IterationContext& base, int iteration_mode, float* R, float* t, cudaStream_t s,
                              cudaEvent_t* ev) {
-	IterationContext c = base;
-	c.g.iteration_mode = iteration_mode;
-	c.sys.update_mode = iteration_mode;
+	const int rc = enqueue_data_term(base, R, t, s, ev);
+	return rc != kOk ? rc : enqueue_solve(f, base, iteration_mode, R, t, s, ev);
+}
+
+// first half of an iteration: warp, rasterise, residual + Jacobian + per-node J^T J / J^T r sums into the accumulators
+static int enqueue_data_term(const IterationContext& c, float* R, float* t, cudaStream_t s, cudaEvent_t* ev) {
 	if (ev) cudaEventRecord(ev[0], s);
 	launch_warp_vertices(c.d, R, t, c.extrinsics, s);
 	if (ev) cudaEventRecord(ev[1], s);
@@ -687,6 +696,16 @@ static int enqueue_iteration(nnrt_b200_fitter* f, const IterationContext& base, 
 	if (ev) cudaEventRecord(ev[3], s);
 	if (launch_assemble(c.d, c.p, s) != kOk) return kInvalidArgument;
 	if (ev) cudaEventRecord(ev[4], s);
+	NNRT_LAUNCH_CHECK();
+	return kOk;
+}
+
+// second half: ARAP term + system, arrowhead solve, node update (consumes and clears the accumulators)
+static int enqueue_solve(nnrt_b200_fitter* f, const IterationContext& base, int iteration_mode, float* R, float* t, cudaStream_t s,
+                         cudaEvent_t* ev) {
+	IterationContext c = base;
+	c.g.iteration_mode = iteration_mode;
+	c.sys.update_mode = iteration_mode;
 	if (f->fused_stem) {
 		system_stem_kernel<<<(f->N + kStemWarps - 1) / kStemWarps, kStemWarps * 32, 0, s>>>(c.g, c.sys, R, t, f->accum, f->sys_diag, f->sys_rhs);
 		if (ev) { cudaEventRecord(ev[5], s); cudaEventRecord(ev[6], s); }
@@ -712,6 +731,43 @@ extern "C" int nnrt_b200_fitter_set_iteration_modes(nnrt_b200_fitter* f, const i
 	if (modes != f->modes && f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
 	f->modes = modes;
 	return kOk;
+}
+
+extern "C" int nnrt_b200_fitter_set_pixel_rows(nnrt_b200_fitter* f, int32_t row_begin, int32_t row_end) {
+	NNRT_CHECK_ARG(f, "fitter_set_pixel_rows: null fitter");
+	NNRT_CHECK_ARG(row_begin >= 0 && row_begin < row_end && row_end <= f->H, "pixel rows [%d, %d) must lie inside the image (height %d)", row_begin, row_end, f->H);
+	if ((row_begin != f->row_begin || row_end != f->row_end) && f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
+	f->row_begin = row_begin; f->row_end = row_end;
+	return kOk;
+}
+
+extern "C" float* nnrt_b200_fitter_accumulators(nnrt_b200_fitter* f, int64_t* float_count) {
+	if (f == nullptr) return nullptr;
+	if (float_count) *float_count = (int64_t) f->N * kAccumStride;
+	return f->accum;
+}
+
+extern "C" int nnrt_b200_fitter_iteration_data_term(nnrt_b200_fitter* f, float* node_rotations, float* node_translations,
+                                                    const double* intrinsics_host, const double* extrinsics_host, void* stream) {
+	NNRT_CHECK_ARG(f && node_rotations && node_translations && intrinsics_host, "fitter_iteration_data_term: null pointer argument");
+	NNRT_CHECK_ARG(f->graph_set && f->mesh_set && f->reference_set, "fitter_iteration_data_term: model / reference not set");
+	static const double I4[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+	const IterationContext c = make_context(f, intrinsics_host, extrinsics_host ? extrinsics_host : I4);
+	return enqueue_data_term(c, node_rotations, node_translations, (cudaStream_t) stream, nullptr);
+}
+
+extern "C" int nnrt_b200_fitter_iteration_solve(nnrt_b200_fitter* f, float* node_rotations, float* node_translations,
+                                                const double* intrinsics_host, const double* extrinsics_host, int32_t iteration_index,
+                                                void* stream) {
+	NNRT_CHECK_ARG(f && node_rotations && node_translations && intrinsics_host && iteration_index >= 0, "fitter_iteration_solve: bad argument");
+	NNRT_CHECK_ARG(f->graph_set && f->mesh_set && f->reference_set, "fitter_iteration_solve: model / reference not set");
+	static const double I4[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+	const IterationContext c = make_context(f, intrinsics_host, extrinsics_host ? extrinsics_host : I4);
+	const int mode = f->modes[(size_t) iteration_index % f->modes.size()];
+	NNRT_CHECK_ARG(mode == 0 || f->E == 0, "TRANSLATION_ONLY / ROTATION_ONLY iterations need a warp field without regularisation edges");
+	const int rc = enqueue_solve(f, c, mode, node_rotations, node_translations, (cudaStream_t) stream, nullptr);
+	if (rc == kOk) NNRT_CUDA(cudaMemcpyAsync(f->host_flags, f->counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t) stream));
+	return rc;
 }
 
 extern "C" int nnrt_b200_fitter_fit(nnrt_b200_fitter* f, float* node_rotations, float* node_translations, const double* intrinsics_host,

@@ -90,6 +90,9 @@ __global__ void __launch_bounds__(256) face_raster_kernel(FitterDeviceData d, Da
 	const RasterParams rp = raster_params(p);
 	PixelBox box;
 	if (!face_pixel_box(face, rp, box)) return;
+	box.v0 = max(box.v0, p.row_begin);  // pixel-sharded fits: this GPU's band of rows only
+	box.v1 = min(box.v1, p.row_end - 1);
+	if (box.v0 > box.v1) return;
 	int rows_per_band;
 	const int bands = raster_face_or_count_bands(face, (int) f, rp, box, d.keys, nullptr, rows_per_band);
 	if (bands > 0) push_bands((int) f, box, rows_per_band, bands, d.band_queue, d.counters, d.band_queue_capacity, d.counters + 1);
@@ -163,9 +166,9 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 	// part of the image, and in raster order its expensive tiles would reach the SMs as one late clump
 	const unsigned tile_count = gridDim.x * gridDim.y, linear = blockIdx.y * gridDim.x + blockIdx.x;
 	const unsigned tile = (tile_count % 1009u) ? (unsigned) (((unsigned long long) linear * 1009ull) % tile_count) : linear;
-	const int tile_x = (int) (tile % gridDim.x) * 16 + (warp & 1) * 8, tile_y = (int) (tile / gridDim.x) * 8 + (warp >> 1) * 4;
+	const int tile_x = (int) (tile % gridDim.x) * 16 + (warp & 1) * 8, tile_y = p.row_begin + (int) (tile / gridDim.x) * 8 + (warp >> 1) * 4;
 	const int u = tile_x + (lane & 7), v = tile_y + (lane >> 3);
-	const bool in_image = u < p.width && v < p.height;
+	const bool in_image = u < p.width && v < p.row_end;
 	const int64_t px = (int64_t) v * p.width + u;
 	unsigned long long key = kEmptyKey;
 	if (in_image) key = d.keys[px];
@@ -346,7 +349,7 @@ static int launch_assemble_for(const FitterDeviceData& d, const DataTermParams& 
 		if (cudaFuncSetAttribute(assemble_kernel<A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bytes) != cudaSuccess) return kCudaError;
 		attribute_set = true;
 	}
-	const dim3 grid((p.width + 15) / 16, (p.height + 7) / 8);
+	const dim3 grid((p.width + 15) / 16, (p.row_end - p.row_begin + 7) / 8);
 	assemble_kernel<A><<<grid, kAssembleThreads, bytes, s>>>(d, p);
 	return kOk;
 }

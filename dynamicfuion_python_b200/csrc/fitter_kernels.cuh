@@ -27,6 +27,7 @@ struct DataTermParams {
 	int use_tukey;
 	float tukey_cutoff;
 	float blur_radius;    // NDC
+	int row_begin, row_end;  // image rows [row_begin, row_end) this GPU rasterises and assembles (whole image unless pixel-sharded)
 };
 
 struct FitterDeviceData {

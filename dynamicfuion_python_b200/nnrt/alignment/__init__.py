@@ -5,7 +5,7 @@ import enum
 
 import torch
 
-from ... import _lib
+from ... import _lib, pixel_shard
 from .. import _tensor as T
 from ..geometry import WarpNodeCoverageComputationMethod
 from . import functional
@@ -34,6 +34,7 @@ class DeformableMeshToImageFitter:
                                           float(preconditioning_dampening_factor), float(arap_term_weight),
                                           int(bool(use_huber_penalty_for_arap_term)), float(huber_penalty_constant))
         self._handle = None
+        self._pixel_shard = None
         self._shape = None
         self._model_key = None
         self._keep = None
@@ -56,6 +57,13 @@ class DeformableMeshToImageFitter:
         self._handle, self._shape, self._model_key = handle, shape, None
         modes = (C.c_int32 * len(self.iteration_mode_sequence))(*[int(m) for m in self.iteration_mode_sequence])
         _lib.check(_lib.lib().nnrt_b200_fitter_set_iteration_modes(handle, modes, len(self.iteration_mode_sequence)))
+
+    def shard_pixels(self, rank, world_size, group=None):
+        """Pixel-sharded single-frame mode (dynamicfuion_python_b200.pixel_shard): this process fits rows
+        pixel_rows(rank, world_size, height) and all-reduces the per-node sums over `group` once per iteration. world_size 1 turns it off."""
+        self._pixel_shard = None if world_size <= 1 else (int(rank), int(world_size), group)
+        if self._handle is not None and self._pixel_shard is None:
+            T.call("nnrt_b200_fitter_set_pixel_rows", self._handle, 0, self._shape[5])
 
     def workspace_bytes(self):
         return 0 if self._handle is None else _lib.lib().nnrt_b200_fitter_workspace_bytes(self._handle)
@@ -104,7 +112,23 @@ class DeformableMeshToImageFitter:
         if not (R.is_contiguous() and t.is_contiguous() and R.is_cuda and t.is_cuda):
             raise RuntimeError("warp field node rotations / translations must be contiguous CUDA tensors")
         iters = self.max_iteration_count if iteration_count is None else int(iteration_count)
-        T.call("nnrt_b200_fitter_fit", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), iters, T.stream())
+        if iters <= 0:
+            iters = self.max_iteration_count
+        if self._pixel_shard is None:
+            T.call("nnrt_b200_fitter_fit", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), iters, T.stream())
+        else:
+            # pixel-sharded: this rank's band of rows, one all-reduce of the per-node sums per iteration, replicated solve
+            rank, world, group = self._pixel_shard
+            begin, end = pixel_shard.pixel_rows(rank, world, self._shape[5])
+            T.call("nnrt_b200_fitter_set_pixel_rows", self._handle, begin, end)
+            count = C.c_int64()
+            pointer = _lib.lib().nnrt_b200_fitter_accumulators(self._handle, C.byref(count))
+            acc = pixel_shard.DeviceBuffer(pointer, count.value).tensor(R.device)
+            for it in range(iters):
+                T.call("nnrt_b200_fitter_iteration_data_term", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), T.stream())
+                pixel_shard.all_reduce_sum(acc, group)
+                T.call("nnrt_b200_fitter_iteration_solve", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), it, T.stream())
+                pixel_shard.broadcast_node_state(R, t, group)
         self._keep = (K, ext)
 
     def check_status(self):

@@ -170,6 +170,18 @@ int nnrt_b200_fitter_set_mesh(nnrt_b200_fitter* fitter, const float* vertex_posi
  * iteration % count (DeformableMeshToImageFitter.cpp:112). Default {ALL}. Non-ALL modes solve the 3 x 3 block of the active half
  * (.cpp:198, 262-272) and are defined for edge-free warp fields only, as in the reference (fit returns an error otherwise). */
 int nnrt_b200_fitter_set_iteration_modes(nnrt_b200_fitter* fitter, const int32_t* modes_host, int32_t mode_count);
+/* Pixel-sharded single frame (one exchange per iteration): every GPU holds the whole mesh and graph, rasterises and assembles
+ * only image rows [row_begin, row_end), and the per-node J^T J / J^T r partial sums (the accumulator buffer, node_count x 32 f32:
+ * 21 upper-triangular entries + 6 gradient entries + padding) are summed across GPUs by the caller (ncclAllReduce) between
+ * iteration_data_term and iteration_solve; the solve is replicated. The reference has no multi-GPU path; the sums being
+ * exchanged are those of ComputeDepthHessianApproximationBlocks_UnorderedNodePixels / ComputeNegativeDepthGradient_...
+ * (alignment/kernel/DeformableMeshToImageFitterImpl.h:199-420). iteration_index selects the IterationMode of the sequence. */
+int nnrt_b200_fitter_set_pixel_rows(nnrt_b200_fitter* fitter, int32_t row_begin, int32_t row_end);
+float* nnrt_b200_fitter_accumulators(nnrt_b200_fitter* fitter, int64_t* float_count);
+int nnrt_b200_fitter_iteration_data_term(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,
+                                         const double* intrinsics_host, const double* extrinsics_host, void* stream);
+int nnrt_b200_fitter_iteration_solve(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,
+                                     const double* intrinsics_host, const double* extrinsics_host, int32_t iteration_index, void* stream);
 /* Reference observation: reference_points [H*W,3] f32 + reference_mask [H*W] u8 (FitToImage overload .cpp:85-94),
  * or a depth image (overload .cpp:278-314: depth / depth_scale, unprojected with the camera intrinsics, optional user mask). */
 int nnrt_b200_fitter_set_reference_points(nnrt_b200_fitter* fitter, const float* reference_points, const uint8_t* reference_mask,

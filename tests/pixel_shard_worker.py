@@ -1,0 +1,52 @@
+"""Worker of test_two_gpu_pixel_sharded_fit_matches_single_gpu (run under torchrun, one rank per GPU)."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from dynamicfuion_python_b200 import nnrt
+    from oracle import oracle_py as oracle
+    from util import scene_with_target
+    s = scene_with_target(oracle, "tinyr", 120, 160)
+    G = nnrt.geometry
+    mesh = (s["positions"], s["normals"], s["triangles"])
+
+    def fit(shard):
+        wf = G.HierarchicalGraphWarpField(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
+                                          G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
+        fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=3, preconditioning_dampening_factor=s["lm_factor"],
+                                                            arap_term_weight=s["arap_term_weight"])
+        if shard:
+            fitter.shard_pixels(rank, world)
+        fitter.fit_to_image(wf, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]),
+                            anchors=s["anchors"], anchor_weights=s["anchor_weights"])
+        fitter.check_status()
+        return wf.node_rotations.clone(), wf.node_translations.clone()
+
+    R1, t1 = fit(False)
+    R2, t2 = fit(True)
+    scale = float(t1.abs().max())
+    assert float((t2 - t1).abs().max()) <= 1e-3 * scale, float((t2 - t1).abs().max())
+    assert float((R2 - R1).abs().max()) <= 1e-4
+    # identical state on every rank (replicated solve on all-reduced sums)
+    gathered = [torch.zeros_like(t2) for _ in range(world)]
+    dist.all_gather(gathered, t2)
+    assert all(torch.equal(g, gathered[0]) for g in gathered)
+    dist.barrier()
+    if rank == 0:
+        print("PIXEL_SHARD_OK")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

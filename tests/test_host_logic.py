@@ -98,3 +98,18 @@ def test_frame_batch_two_ranks_gloo():
         assert out[r]["log"] == [(s, f) for s in out[r]["seqs"] for f in range(3)]
         assert out[r]["total"] == 18 and out[r]["slowest"] == 200.0
         assert abs(out[r]["fps"] - 18 / 0.2) < 1e-9
+
+
+def test_pixel_rows_partition_the_image():
+    """Bands of the pixel-sharded mode: disjoint, cover every row, multiples of the 8-row assembly tile except the last."""
+    from dynamicfuion_python_b200.pixel_shard import pixel_rows
+    for height in (120, 480, 1080, 2160):
+        for world in (1, 2, 4, 8):
+            rows = [pixel_rows(r, world, height) for r in range(world)]
+            assert rows[0][0] == 0 and rows[-1][1] == height
+            for (b0, e0), (b1, e1) in zip(rows, rows[1:]):
+                assert e0 == b1 and b0 < e0 and b0 % 8 == 0
+    with pytest.raises(ValueError):
+        pixel_rows(2, 2, 480)
+    with pytest.raises(ValueError):
+        pixel_rows(0, 64, 120)
