@@ -117,7 +117,7 @@ STAGES = ["warp_vertices", "face_raster", "band_raster", "assemble", "build_syst
 STAGE_KERNEL = {"warp_vertices": "warp_vertices_kernel<4>", "face_raster": "face_raster_kernel", "band_raster": "band_raster_kernel",
                 "assemble": "assemble_kernel<4>", "build_system": "system_stem_kernel", "stem_eliminate": "(fused into system_stem_kernel)",
                 "corner_solve_update": "corner_solve_regtile_kernel"}
-SETUP_LAUNCHES = 6  # anchors, 3 pack kernels, face-anchor table, reference unprojection
+SETUP_LAUNCHES = 5  # anchors, 3 pack kernels, reference unprojection
 
 
 def run_b200(args):
