@@ -92,9 +92,20 @@ struct Fragment {
 	float3 bary;
 };
 
-// Per-pixel face test (UpdateQueueIfPixelInsideFace without the queue). Returns false if rejected.
+// True when every point of the face's blur-expanded bounding box is closer (squared distance, as the reference compares it) than
+// blur_radius to a vertex, hence to an edge: the reference's outside-pixel test `dist >= blur_radius` can then never reject a
+// pixel of the box, and the three point-segment distances need not be evaluated to reproduce its decision. With the reference's
+// blur radius (0.5 px) compared against a SQUARED distance this holds for every face smaller than about 10 pixels.
+__device__ __forceinline__ bool face_box_within_blur(const FaceNdc& f, float blur_radius) {
+	const float dx = (fmax3(f.v0.x, f.v1.x, f.v2.x) - fmin3(f.v0.x, f.v1.x, f.v2.x)) + 2.f * blur_radius;
+	const float dy = (fmax3(f.v0.y, f.v1.y, f.v2.y) - fmin3(f.v0.y, f.v1.y, f.v2.y)) + 2.f * blur_radius;
+	return (dx * dx + dy * dy) * 1.01f < blur_radius;  // 1 % margin over the fp32 rounding of both sides
+}
+
+// Per-pixel face test (UpdateQueueIfPixelInsideFace without the queue). Returns false if rejected. `within_blur`: the caller
+// knows the distance test cannot reject this pixel (face_box_within_blur, or a pixel that already passed); out.distance is then 0.
 __device__ __forceinline__ bool shade_pixel(const FaceNdc& f, float2 pixel, float blur_radius, bool perspective_correct,
-                                            bool clip_bary, bool cull_back_faces, Fragment& out) {
+                                            bool clip_bary, bool cull_back_faces, Fragment& out, bool within_blur = false) {
 	const float face_area = edge_fn(f.v0, f.v1, f.v2);
 	const bool is_back_face = face_area < 0.f;
 	const bool zero_area = (face_area <= kEps && face_area >= -1.f * kEps);
@@ -121,13 +132,15 @@ __device__ __forceinline__ bool shade_pixel(const FaceNdc& f, float2 pixel, floa
 	}
 	const float depth = bc.x * f.z0 + bc.y * f.z1 + bc.z * f.z2;
 	if (depth < 0.f) return false;
+	out.depth = depth;
+	out.bary = bc;
+	out.distance = 0.f;
+	if (within_blur) return true;
 	const float dist = fmin3(point_segment_sq_distance(pixel, f.v0, f.v1), point_segment_sq_distance(pixel, f.v0, f.v2),
 	                         point_segment_sq_distance(pixel, f.v1, f.v2));
 	const bool inside = bary.x > 0.f && bary.y > 0.f && bary.z > 0.f;
 	if (!inside && dist >= blur_radius) return false;  // sic: squared distance against the radius
-	out.depth = depth;
 	out.distance = inside ? -dist : dist;
-	out.bary = bc;
 	return true;
 }
 

@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 		fndc.v0 = project(p.ndc, fv[0]); fndc.v1 = project(p.ndc, fv[1]); fndc.v2 = project(p.ndc, fv[2]);
 		fndc.z0 = fv[0].z; fndc.z1 = fv[1].z; fndc.z2 = fv[2].z;
 		Fragment frag;
-		shade_pixel(fndc, ray, p.blur_radius, p.perspective_correct != 0, false, true, frag);
+		shade_pixel(fndc, ray, p.blur_radius, p.perspective_correct != 0, false, true, frag, true);  // the raster pass accepted this pixel
 		const float rho[3] = {frag.bary.x, frag.bary.y, frag.bary.z};
 		const float depth = frag.depth;
 		// rendered normal (InterpolateFaceAttributesImpl.h:56-62: acc = 0; acc += w*attr)

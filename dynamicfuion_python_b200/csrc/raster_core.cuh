@@ -55,10 +55,11 @@ __device__ __forceinline__ bool face_pixel_box(const FaceNdc& f, const RasterPar
 }
 
 __device__ __forceinline__ void raster_pixel(const FaceNdc& f, int face, int u, int v, const RasterParams& rp,
-                                             unsigned long long* __restrict__ keys, const unsigned long long* __restrict__ floor_keys) {
+                                             unsigned long long* __restrict__ keys, const unsigned long long* __restrict__ floor_keys,
+                                             bool within_blur) {
 	const float2 pixel = make_float2(pixel_to_ndc(u, rp.width, rp.height), pixel_to_ndc(v, rp.height, rp.width));
 	Fragment frag;
-	if (!shade_pixel(f, pixel, rp.blur_radius, rp.perspective_correct != 0, rp.clip_bary != 0, rp.cull_back_faces != 0, frag)) return;
+	if (!shade_pixel(f, pixel, rp.blur_radius, rp.perspective_correct != 0, rp.clip_bary != 0, rp.cull_back_faces != 0, frag, within_blur)) return;
 	const unsigned long long key = pack_key(frag.depth, face);
 	const int64_t p = (int64_t) v * rp.width + u;
 	if (floor_keys) {  // depth peeling: strictly after the previous layer's winner
@@ -74,8 +75,9 @@ __device__ __forceinline__ int raster_face_or_count_bands(const FaceNdc& f, int 
                                                           const unsigned long long* __restrict__ floor_keys, int& rows_per_band) {
 	const int bw = box.u1 - box.u0 + 1, bh = box.v1 - box.v0 + 1;
 	if (bw * bh <= kSmallBoxPixels) {
+		const bool within_blur = face_box_within_blur(f, rp.blur_radius);
 		for (int v = box.v0; v <= box.v1; v++)
-			for (int u = box.u0; u <= box.u1; u++) raster_pixel(f, face, u, v, rp, keys, floor_keys);
+			for (int u = box.u0; u <= box.u1; u++) raster_pixel(f, face, u, v, rp, keys, floor_keys, within_blur);
 		return 0;
 	}
 	rows_per_band = max(1, kBandPixels / bw);
@@ -109,7 +111,8 @@ __device__ __forceinline__ void drain_band_queue(const BandItem* __restrict__ qu
 		if (!face_pixel_box(f, rp, box)) continue;
 		const int bw = box.u1 - box.u0 + 1;
 		const int total = bw * (it.y1 - it.y0 + 1);
-		for (int k = lane; k < total; k += 32) raster_pixel(f, it.face, box.u0 + k % bw, it.y0 + k / bw, rp, keys, floor_keys);
+		const bool within_blur = face_box_within_blur(f, rp.blur_radius);
+		for (int k = lane; k < total; k += 32) raster_pixel(f, it.face, box.u0 + k % bw, it.y0 + k / bw, rp, keys, floor_keys, within_blur);
 	}
 }
 
