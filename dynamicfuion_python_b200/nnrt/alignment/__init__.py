@@ -44,7 +44,10 @@ class DeformableMeshToImageFitter:
 
     def _release(self):
         if getattr(self, "_handle", None):
-            _lib.lib().nnrt_b200_fitter_destroy(self._handle)
+            try:
+                _lib.lib().nnrt_b200_fitter_destroy(self._handle)
+            except TypeError:  # interpreter shutdown: the module globals are already torn down, the process frees the workspace
+                pass
             self._handle = None
 
     def _ensure(self, shape):
