@@ -162,11 +162,17 @@ def run_b200(args):
     eye = torch.eye(3, device=dev).repeat(N, 1, 1).contiguous()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
+    host_R = torch.empty((N, 3, 3), dtype=torch.float32).pin_memory()
+    host_t = torch.empty((N, 3), dtype=torch.float32).pin_memory()
+
     def step(depth, read_back):
         wf.node_rotations.copy_(eye); wf.node_translations.zero_()
         fitter.fit_to_image(wf, mesh, None, depth, None, K, ext, 1.0)
-        if read_back:
-            return wf.node_rotations.cpu(), wf.node_translations.cpu()
+        if read_back:  # result of the step back on the host: two asynchronous copies into pinned buffers, one synchronisation
+            host_R.copy_(wf.node_rotations, non_blocking=True)
+            host_t.copy_(wf.node_translations, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return host_R, host_t
         return None
 
     def barrier():

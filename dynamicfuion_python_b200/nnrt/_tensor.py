@@ -11,9 +11,15 @@ import torch
 from .. import _lib
 
 
+_cuda_checked = False
+
+
 def device():
-    if not torch.cuda.is_available():
-        raise RuntimeError("nnrt (B200 build) needs a CUDA device; there is no CPU path")
+    global _cuda_checked
+    if not _cuda_checked:  # the availability probe costs ~5 us per call (environment lookups); once per process is enough
+        if not torch.cuda.is_available():
+            raise RuntimeError("nnrt (B200 build) needs a CUDA device; there is no CPU path")
+        _cuda_checked = True
     return torch.device("cuda", torch.cuda.current_device())
 
 
@@ -29,9 +35,13 @@ def to_torch(x):
 
 def cuda(x, dtype):
     t = to_torch(x)
+    if t.is_cuda and t.dtype == dtype and t.is_contiguous():  # the common case on the hot path: already where and what it must be
+        return t
     if t.dtype == torch.bool and dtype == torch.uint8:
         t = t.to(torch.uint8)
-    return t.to(device=device(), dtype=dtype).contiguous()
+    # a pinned host tensor is uploaded asynchronously on the current stream (stream order protects the consumer kernels; the caller
+    # must not rewrite the pinned buffer before the stream has passed the copy, as with any cudaMemcpyAsync)
+    return t.to(device=device(), dtype=dtype, non_blocking=(not t.is_cuda) and t.is_pinned()).contiguous()
 
 
 def host_f64(x, shape):
@@ -47,7 +57,8 @@ def ptr(t):
 
 
 def stream():
-    return torch.cuda.current_stream().cuda_stream
+    """Raw handle of torch's current stream on the current device (the C ABI takes a cudaStream_t as void*)."""
+    return torch._C._cuda_getCurrentRawStream(torch.cuda.current_device())
 
 
 def empty(shape, dtype):
