@@ -298,16 +298,26 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 		}
 		__syncwarp();
 		// S[c1, c2] -= B_e1^T X_e2 ; with the tile-packed layout only block pairs on or below the diagonal are stored
-		for (int idx = lane; idx < deg * deg * 36; idx += 32) {
-			const int pair = idx / 36, k = idx % 36, rr = k / 6, c = k % 6;
-			const int q1 = pair / deg, q2 = pair % deg;
+		// one 6 x 6 product per edge pair: entries 0..31 of a pair go to the 32 lanes, the four tail entries (32..35) of eight pairs
+		// are gathered into one more pass; no per-item division by the runtime degree
+		auto schur_entry = [&](int q1, int q2, int rr, int c) {
 			const int c1 = s_col[wib][q1] - sys.arrow_base, c2 = s_col[wib][q2] - sys.arrow_base;
-			if (sys.schur_tile_packed && c1 < c2) continue;
+			if (sys.schur_tile_packed && c1 < c2) return;
 			float acc = 0.f;
 #pragma unroll
 			for (int m = 0; m < 6; m++) acc += s_B[wib][q1][m * 6 + rr] * s_X[wib][q2][m * 6 + c];
 			const int64_t slot = schur_slot(sys, n, c1 * 6 + rr, c2 * 6 + c);
 			if (slot >= 0) atomicAdd(sys.schur + slot, -acc);
+		};
+		{
+			const int rr = lane / 6, c = lane % 6;
+			for (int q1 = 0; q1 < deg; q1++)
+				for (int q2 = 0; q2 < deg; q2++) schur_entry(q1, q2, rr, c);
+			const int tail = 32 + (lane & 3), tail_rr = tail / 6, tail_c = tail % 6;
+			for (int first = 0; first < deg * deg; first += 8) {
+				const int pair = first + (lane >> 2);
+				if (pair < deg * deg) schur_entry(pair / deg, pair % deg, tail_rr, tail_c);
+			}
 		}
 		// b_C[c] -= X_e^T b
 		for (int idx = lane; idx < deg * 6; idx += 32) {
