@@ -40,18 +40,18 @@ __device__ __forceinline__ float3 operator*(float s, float3 a) { return make_flo
 
 __device__ __forceinline__ float ndc_range(int dim1, int dim2) {
 	float range = 2.0f;
-	if (dim1 > dim2) range = ((float) dim1 * range) / (float) dim2;
+	if (dim1 > dim2) range = __fdiv_rn(__fmul_rn((float) dim1, range), (float) dim2);
 	return range;
 }
 // pixel centre -> NDC along one dimension (ImageSpacePixelAlongDimensionToNdc)
 __device__ __forceinline__ float pixel_to_ndc(int i, int dim1, int dim2) {
 	const float range = ndc_range(dim1, dim2);
-	const float offset = range / 2.0f;
-	return -offset + (range * (float) i + offset) / (float) dim1;
+	const float offset = __fmul_rn(range, 0.5f);  // == range / 2 exactly
+	return __fadd_rn(-offset, __fdiv_rn(__fadd_rn(__fmul_rn(range, (float) i), offset), (float) dim1));
 }
 __device__ __forceinline__ float2 project(const Intrinsics& k, float3 p) {
-	const float inv_z = 1.0f / p.z;
-	return make_float2(k.fx * p.x * inv_z + k.cx, k.fy * p.y * inv_z + k.cy);
+	const float inv_z = __fdiv_rn(1.0f, p.z);
+	return make_float2(__fadd_rn(__fmul_rn(__fmul_rn(k.fx, p.x), inv_z), k.cx), __fadd_rn(__fmul_rn(__fmul_rn(k.fy, p.y), inv_z), k.cy));
 }
 __device__ __forceinline__ float3 rigid_transform(const Rigid& t, float3 p) {
 	return make_float3(p.x * t.e[0] + p.y * t.e[1] + p.z * t.e[2] + t.e[3], p.x * t.e[4] + p.y * t.e[5] + p.z * t.e[6] + t.e[7],
@@ -62,8 +62,10 @@ __device__ __forceinline__ float3 rigid_rotate(const Rigid& t, float3 p) {
 	                   p.x * t.e[8] + p.y * t.e[9] + p.z * t.e[10]);
 }
 // signed parallelogram area, clockwise-front convention
+// (written with round-to-nearest intrinsics, like the rest of the per-pixel face test below: its results decide coverage and must
+// not depend on the translation unit's -fmad / -prec-div settings)
 __device__ __forceinline__ float edge_fn(float2 p, float2 v0, float2 v1) {
-	return (p.x - v0.x) * (v0.y - v1.y) - (p.y - v0.y) * (v0.x - v1.x);
+	return __fsub_rn(__fmul_rn(__fsub_rn(p.x, v0.x), __fsub_rn(v0.y, v1.y)), __fmul_rn(__fsub_rn(p.y, v0.y), __fsub_rn(v0.x, v1.x)));
 }
 __device__ __forceinline__ float fmin3(float a, float b, float c) { return fminf(fminf(a, b), c); }
 __device__ __forceinline__ float fmax3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
@@ -114,15 +116,15 @@ __device__ __forceinline__ bool shade_pixel(const FaceNdc& f, float2 pixel, floa
 	const bool z_invalid = fmax3(f.z0, f.z1, f.z2) < kEps;
 	if (pixel.x > x_max || pixel.x < x_min || pixel.y > y_max || pixel.y < y_min || z_invalid) return false;
 	if ((cull_back_faces && is_back_face) || zero_area) return false;
-	const float area_eps = face_area + kEps;
-	float3 bary = make_float3(edge_fn(pixel, f.v1, f.v2) / area_eps, edge_fn(pixel, f.v2, f.v0) / area_eps,
-	                          edge_fn(pixel, f.v0, f.v1) / area_eps);
+	const float area_eps = __fadd_rn(face_area, kEps);
+	float3 bary = make_float3(__fdiv_rn(edge_fn(pixel, f.v1, f.v2), area_eps), __fdiv_rn(edge_fn(pixel, f.v2, f.v0), area_eps),
+	                          __fdiv_rn(edge_fn(pixel, f.v0, f.v1), area_eps));
 	if (perspective_correct) {
-		const float n0 = bary.x * f.z1 * f.z2;
-		const float n1 = f.z0 * bary.y * f.z2;
-		const float n2 = f.z0 * f.z1 * bary.z;
-		const float den = fmaxf(n0 + n1 + n2, kEps);
-		bary = make_float3(n0 / den, n1 / den, n2 / den);
+		const float n0 = __fmul_rn(__fmul_rn(bary.x, f.z1), f.z2);
+		const float n1 = __fmul_rn(__fmul_rn(f.z0, bary.y), f.z2);
+		const float n2 = __fmul_rn(__fmul_rn(f.z0, f.z1), bary.z);
+		const float den = fmaxf(__fadd_rn(__fadd_rn(n0, n1), n2), kEps);
+		bary = make_float3(__fdiv_rn(n0, den), __fdiv_rn(n1, den), __fdiv_rn(n2, den));
 	}
 	float3 bc = bary;
 	if (clip_bary) {
@@ -130,7 +132,7 @@ __device__ __forceinline__ bool shade_pixel(const FaceNdc& f, float2 pixel, floa
 		const float n2 = sum3(bc.x * bc.x, bc.y * bc.y, bc.z * bc.z);
 		if (n2 > 0.f) { const float n = sqrtf(n2); bc = make_float3(bc.x / n, bc.y / n, bc.z / n); }
 	}
-	const float depth = bc.x * f.z0 + bc.y * f.z1 + bc.z * f.z2;
+	const float depth = __fadd_rn(__fadd_rn(__fmul_rn(bc.x, f.z0), __fmul_rn(bc.y, f.z1)), __fmul_rn(bc.z, f.z2));
 	if (depth < 0.f) return false;
 	out.depth = depth;
 	out.bary = bc;
