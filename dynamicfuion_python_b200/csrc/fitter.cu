@@ -625,6 +625,8 @@ extern "C" int nnrt_b200_fitter_set_reference_points(nnrt_b200_fitter* f, const 
                                                      void* stream) {
 	NNRT_CHECK_ARG(f && reference_points, "fitter_set_reference_points: null pointer argument");
 	const int64_t px = (int64_t) f->H * f->W;
+	// a new observation starts a new fit: its status must not inherit the overflow / not-positive-definite flags of an earlier one
+	NNRT_CUDA(cudaMemsetAsync(f->counters + 1, 0, 2 * sizeof(int), (cudaStream_t) stream));
 	pack_reference_kernel<<<blocks_for(px, 256), 256, 0, (cudaStream_t) stream>>>(reference_points, reference_mask, px, f->refpts);
 	NNRT_LAUNCH_CHECK();
 	f->reference_set = true;
@@ -638,6 +640,7 @@ extern "C" int nnrt_b200_fitter_set_reference_depth(nnrt_b200_fitter* f, const v
 	const int64_t px = (int64_t) f->H * f->W;
 	const Intrinsics k = intrinsics_from_host(intrinsics_host);
 	auto s = (cudaStream_t) stream;
+	NNRT_CUDA(cudaMemsetAsync(f->counters + 1, 0, 2 * sizeof(int), s));  // see set_reference_points
 	if (depth_dtype == 0)
 		reference_from_depth_kernel<float><<<blocks_for(px, 256), 256, 0, s>>>((const float*) depth, user_mask, f->H, f->W, k, depth_scale, f->opt.max_depth, f->refpts);
 	else

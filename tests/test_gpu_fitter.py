@@ -242,3 +242,24 @@ def test_iteration_modes_need_edge_free_field(nnrt, oracle):
         _gpu_fit(nnrt, s, 1, iteration_mode_sequence=[nnrt.alignment.IterationMode.TRANSLATION_ONLY])
     with pytest.raises(RuntimeError):
         oracle_fit(oracle, s, 1, iteration_modes=[1])
+
+
+def test_status_flags_do_not_leak_into_the_next_fit(nnrt, oracle):
+    """A fit that meets a non-positive-definite block (no damping, no pixels: all-zero Hessians) reports it; the next fit of the same
+    fitter on a proper observation reports success."""
+    s = scene_with_target(oracle, "C1", 120, 160)
+    G = nnrt.geometry
+    wf = G.HierarchicalGraphWarpField(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+                                      G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
+    fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=1, preconditioning_dampening_factor=0.0)
+    mesh = (s["positions"], s["normals"], s["triangles"])
+    call = dict(anchors=s["anchors"], anchor_weights=s["anchor_weights"])
+    empty_mask = np.zeros_like(np.asarray(s["reference_mask"]))
+    fitter.fit_to_image(wf, mesh, None, s["reference_points"], empty_mask, s["K"], np.eye(4), (s["height"], s["width"]), **call)
+    with pytest.raises(RuntimeError, match="positive definite"):
+        fitter.check_status()
+    wf2 = G.HierarchicalGraphWarpField(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+                                       G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
+    fitter.fit_to_image(wf2, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]), **call)
+    fitter.check_status()
+    assert np.isfinite(_np(wf2.node_translations)).all()
