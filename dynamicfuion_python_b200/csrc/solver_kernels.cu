@@ -917,6 +917,199 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 #endif
 }
 
+// ---- multi-kernel corner solve for corners beyond one SM (n > 246 unknowns) -----------------------------------------------------
+// Right-looking blocked Cholesky of the DENSE Schur buffer, in place (lower triangle), panels of 32 columns, the right-hand side
+// carried as row n of the augmented system. Per panel: one launch factors the diagonal block (every CTA redundantly, in shared
+// memory) and forward-substitutes 64 rows per CTA; one launch applies the rank-32 update with one CTA per 64 x 64 tile of the
+// lower triangle. The matrix (<= tens of MB) stays in L2 between the launches; all launches are captured in the fit's graph.
+constexpr int kWide = 32;
+
+__device__ __forceinline__ float* augmented_row(const ArrowheadSystem& sys, int n, int r) {
+	return r < n ? sys.schur + (int64_t) r * n : sys.corner_rhs;
+}
+
+__global__ void __launch_bounds__(64) corner_wide_panel_kernel(ArrowheadSystem sys, int n, int j) {
+	__shared__ float D[kWide][kWide + 1];
+	__shared__ float inv_diag[kWide];
+	const int tid = threadIdx.x, nb = min(kWide, n - j);
+	for (int idx = tid; idx < nb * nb; idx += 64) {
+		const int r = idx / nb, c = idx - r * nb;
+		if (c <= r) D[r][c] = sys.schur[(int64_t) (j + r) * n + j + c];
+	}
+	__syncthreads();
+	if (tid < 32) {
+		// lane r keeps row r of the block in registers; column c of the factor travels by shuffle
+		const int lane = tid;
+		float d[kWide];
+#pragma unroll
+		for (int k = 0; k < kWide; k++) d[k] = (lane < nb && k <= lane) ? D[lane][k] : (k == lane ? 1.f : 0.f);
+		bool ok = true;
+#pragma unroll
+		for (int c = 0; c < kWide; c++) {
+			const float pivot = __shfl_sync(0xFFFFFFFFu, d[c], c);
+			if (c < nb && !(pivot > 0.f)) ok = false;
+			const float inv = rsqrtf(pivot);
+			if (lane == c) inv_diag[c] = inv;
+			const float lc = d[c] * inv;  // L(lane, c) for lane >= c
+			d[c] = lc;
+#pragma unroll
+			for (int k = c + 1; k < kWide; k++) {
+				const float lk = __shfl_sync(0xFFFFFFFFu, lc, k);  // L(k, c)
+				if (k <= lane) d[k] = fmaf(-lc, lk, d[k]);
+			}
+		}
+		if (!ok && lane == 0 && blockIdx.x == 0) atomicExch(sys.flags + 2, 1);
+#pragma unroll
+		for (int k = 0; k < kWide; k++)
+			if (lane < nb && k <= lane) D[lane][k] = d[k];
+	}
+	__syncthreads();
+	if (blockIdx.x == 0)
+		for (int idx = tid; idx < nb * nb; idx += 64) {
+			const int r = idx / nb, c = idx - r * nb;
+			if (c <= r) sys.schur[(int64_t) (j + r) * n + j + c] = D[r][c];
+		}
+	const int i = j + nb + blockIdx.x * 64 + tid;
+	if (i > n) return;
+	float* row = augmented_row(sys, n, i) + j;
+	float w[kWide];
+#pragma unroll
+	for (int c = 0; c < kWide; c++) w[c] = c < nb ? row[c] : 0.f;
+#pragma unroll
+	for (int c = 0; c < kWide; c++) {
+		if (c < nb) {
+			float acc = w[c];
+#pragma unroll
+			for (int k = 0; k < c; k++) acc = fmaf(-w[k], D[c][k], acc);
+			w[c] = acc * inv_diag[c];
+		}
+	}
+#pragma unroll
+	for (int c = 0; c < kWide; c++)
+		if (c < nb) row[c] = w[c];
+}
+
+__global__ void __launch_bounds__(256) corner_wide_trailing_kernel(ArrowheadSystem sys, int n, int j) {
+	if (blockIdx.x > blockIdx.y) return;  // lower triangle of tiles: blockIdx.y = row tile, blockIdx.x = column tile
+	__shared__ float Lr[64][kWide + 1], Lc[64][kWide + 1];
+	const int tid = threadIdx.x, nb = min(kWide, n - j), first = j + nb;
+	const int row0 = first + blockIdx.y * 64, col0 = first + blockIdx.x * 64;
+	for (int idx = tid; idx < 64 * kWide; idx += 256) {
+		const int r = idx / kWide, c = idx - r * kWide;
+		const int i = row0 + r, k = col0 + r;
+		Lr[r][c] = (i <= n && c < nb) ? augmented_row(sys, n, i)[j + c] : 0.f;
+		Lc[r][c] = (k < n && c < nb) ? sys.schur[(int64_t) k * n + j + c] : 0.f;
+	}
+	__syncthreads();
+	const int tx = tid & 15, ty = tid >> 4;
+	float acc[4][4] = {};
+#pragma unroll 8
+	for (int c = 0; c < kWide; c++) {
+		float a[4], b[4];
+#pragma unroll
+		for (int q = 0; q < 4; q++) { a[q] = Lr[ty * 4 + q][c]; b[q] = Lc[tx * 4 + q][c]; }
+#pragma unroll
+		for (int q = 0; q < 4; q++)
+#pragma unroll
+			for (int m = 0; m < 4; m++) acc[q][m] = fmaf(a[q], b[m], acc[q][m]);
+	}
+#pragma unroll
+	for (int q = 0; q < 4; q++) {
+		const int i = row0 + ty * 4 + q;
+		if (i > n) continue;
+		float* row = augmented_row(sys, n, i);
+#pragma unroll
+		for (int m = 0; m < 4; m++) {
+			const int k = col0 + tx * 4 + m;
+			if (k < n && k <= i) row[k] -= acc[q][m];
+		}
+	}
+}
+
+// Back substitution L^T x = y (y = the forward-substituted right-hand side), stem back substitution and node update: one CTA.
+__global__ void __launch_bounds__(1024) corner_wide_finish_kernel(ArrowheadSystem sys, int n, float* __restrict__ x, float* __restrict__ rotations,
+                                                                   float* __restrict__ translations) {
+	extern __shared__ float y[];  // [n]
+	const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31;
+	for (int k = tid; k < n; k += T) y[k] = sys.corner_rhs[k];
+	__syncthreads();
+	for (int jb = ((n - 1) / kWide) * kWide; jb >= 0; jb -= kWide) {
+		const int nb = min(kWide, n - jb);
+		if (tid < 32) {
+			// lane l holds column l of the diagonal block, L(jb + c, jb + l) for c >= l: all loads issued before the dependent chain
+			float Lcol[kWide];
+#pragma unroll
+			for (int c = 0; c < kWide; c++) Lcol[c] = (c < nb && lane <= c) ? sys.schur[(int64_t) (jb + c) * n + jb + lane] : 1.f;
+			float yl = lane < nb ? y[jb + lane] : 0.f;
+#pragma unroll
+			for (int c = kWide - 1; c >= 0; c--) {
+				if (c >= nb) continue;
+				const float xc = __shfl_sync(0xFFFFFFFFu, yl / Lcol[c], c);  // lane c divides by the diagonal entry L(c, c)
+				if (lane < c) yl = fmaf(-Lcol[c], xc, yl);
+				if (lane == c) yl = xc;
+			}
+			if (lane < nb) y[jb + lane] = yl;
+		}
+		__syncthreads();
+		for (int k = tid; k < jb; k += T) {
+			float acc = y[k];
+			if (nb == kWide) {
+				float l[kWide];
+#pragma unroll
+				for (int c = 0; c < kWide; c++) l[c] = sys.schur[(int64_t) (jb + c) * n + k];
+#pragma unroll
+				for (int c = 0; c < kWide; c++) acc = fmaf(-l[c], y[jb + c], acc);
+			} else {
+				for (int c = 0; c < nb; c++) acc = fmaf(-sys.schur[(int64_t) (jb + c) * n + k], y[jb + c], acc);
+			}
+			y[k] = acc;
+		}
+		__syncthreads();
+	}
+	for (int k = tid; k < n; k += T) x[sys.arrow_base * 6 + k] = y[k];
+	for (int idx = tid; idx < sys.arrow_base * 6; idx += T) {
+		const int i = idx / 6, r = idx - i * 6;
+		float acc = sys.stem_y[idx];
+		for (int e = sys.row_offsets[i]; e < sys.row_offsets[i + 1]; e++) {
+			const int w = sys.row_blocks[e];
+			const float* X = sys.wing_x + (int64_t) w * 36 + r * 6;
+			const float* xv = y + (sys.wing_columns[w] - sys.arrow_base) * 6;
+#pragma unroll
+			for (int k = 0; k < 6; k++) acc = fmaf(-X[k], xv[k], acc);
+		}
+		x[idx] = acc;
+	}
+	if (rotations == nullptr) return;
+	__syncthreads();
+	__threadfence_block();
+	for (int node = tid; node < sys.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3, sys.update_mode);
+}
+
+static int launch_corner_solve_wide(const ArrowheadSystem& sys, int n, float* x, float* node_rotations, float* node_translations, bool clear_corner,
+                                    cudaStream_t s) {
+	if ((size_t) n * sizeof(float) > 160 * 1024) return kUnsupported;
+	for (int j = 0; j < n; j += kWide) {
+		const int nb = n - j < kWide ? n - j : kWide;
+		const int rows_below = n - (j + nb) + 1;  // the right-hand side row is always there
+		corner_wide_panel_kernel<<<(rows_below + 63) / 64, 64, 0, s>>>(sys, n, j);
+		if (j + nb < n) {
+			const int tiles = (rows_below + 63) / 64;
+			corner_wide_trailing_kernel<<<dim3(tiles, tiles), 256, 0, s>>>(sys, n, j);
+		}
+	}
+	static bool attribute_set = false;
+	if (!attribute_set) {
+		if (cudaFuncSetAttribute(corner_wide_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024) != cudaSuccess) return kCudaError;
+		attribute_set = true;
+	}
+	corner_wide_finish_kernel<<<1, 1024, (size_t) n * sizeof(float), s>>>(sys, n, x, node_rotations, node_translations);
+	if (clear_corner) {
+		if (cudaMemsetAsync(sys.schur, 0, (size_t) n * n * sizeof(float), s) != cudaSuccess) return kCudaError;
+		if (cudaMemsetAsync(sys.corner_rhs, 0, (size_t) n * sizeof(float), s) != cudaSuccess) return kCudaError;
+	}
+	return kOk;
+}
+
 size_t corner_scratch_bytes(int corner_blocks) {
 	const int64_t n = (int64_t) corner_blocks * 6;
 	return (size_t) (((n + 1) * (n + 2) / 2 + (n + 1)) * sizeof(float));
@@ -957,10 +1150,9 @@ int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotati
 		corner_solve_blocked_kernel<<<1, kCornerThreads, blocked_bytes, s>>>(sys, x, node_rotations, node_translations, clear_corner ? 1 : 0);
 		return kOk;
 	}
-	// corners too large for one SM's shared memory: unblocked kernel on a global scratch
-	if (scratch_global == nullptr) return kUnsupported;
-	corner_solve_kernel<false><<<1, 1024, 0, s>>>(sys, x, node_rotations, node_translations, clear_corner ? 1 : 0, scratch_global);
-	return kOk;
+	// corners too large for one SM's shared memory: multi-kernel blocked factorisation of the dense Schur buffer, in place
+	(void) scratch_global;
+	return launch_corner_solve_wide(sys, n, x, node_rotations, node_translations, clear_corner, s);
 }
 
 }  // namespace nnrt_b200
