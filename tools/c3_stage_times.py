@@ -63,6 +63,25 @@ for rep in range(reps):
     torch.cuda.synchronize()
     stage += np.array(fitter.profile_iteration(wf, K, ext))
 stage /= reps
+# whole iterations inside the captured graph: (10-iteration frame - 1-iteration frame) / 9
+graph_ms = {}
+for iters in (1, 10):
+    def frame():
+        wf.set_node_rotations(np.tile(np.eye(3, dtype=np.float32), (N, 1, 1))); wf.set_node_translations(np.zeros((N, 3), np.float32))
+        fitter.fit_to_image(wf, mesh, None, depth, None, K, ext, 1.0, anchors=anchors, anchor_weights=weights, iteration_count=iters)
+    for _ in range(2):
+        frame()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(5):
+        frame()
+    b.record(); torch.cuda.synchronize()
+    graph_ms[iters] = a.elapsed_time(b) / 5
+try:
+    fitter.check_status(); status10 = "ok"
+except RuntimeError as error:
+    status10 = str(error)
 V, F, PX = pos.shape[0], tris.shape[0], H * W
 names = ["warp_vertices", "face_raster", "band_raster", "assemble", "build_system", "stem_eliminate", "corner_solve_update"]
 bytes_by = {"warp_vertices": 80 * V, "raster": 97 * F + 28 * PX, "assemble": 41 * PX + 168 * N}
@@ -70,6 +89,8 @@ data_ms = float(stage[:4].sum())
 print(json.dumps({"config": "C3", "V": V, "F": F, "nodes": N, "stem": base, "corner": N - base, "edges": E, "image": f"{W}x{H}",
                   "coverage": float((depth > 0).float().mean()), "status_first_fit": status,
                   "stage_ms": dict(zip(names, [float(x) for x in stage])),
+                  "ms_per_iteration_in_graph": (graph_ms[10] - graph_ms[1]) / 9, "ms_per_frame_10_iterations": graph_ms[10], "status_10_iterations": status10,
+                  "iteration_algorithmic_bytes": int(80 * V + 97 * F + 69 * PX + 168 * N + 300 * E),
                   "data_term_ms": data_ms, "data_term_algorithmic_bytes": int(sum(bytes_by.values())),
                   "data_term_achieved_gbs": sum(bytes_by.values()) / (data_ms * 1e-3) / 1e9,
                   "warp_gbs": bytes_by["warp_vertices"] / (stage[0] * 1e-3) / 1e9,
