@@ -390,7 +390,7 @@ struct nnrt_b200_fitter {
 	int4* tris;
 	int32_t* anchors; float* weights; float* nodes;
 	int2* edges; float *ew_res, *ew_jac; int *out_offsets, *out_edges, *in_offsets, *in_edges, *wing_columns;
-	float *accum, *sys_diag, *sys_rhs, *wing, *dinv, *stem_y, *wing_x, *schur, *corner_rhs, *x, *corner_scratch;
+	float *accum, *sys_diag, *sys_rhs, *wing, *dinv, *stem_y, *wing_x, *schur, *corner_rhs, *x;
 	unsigned long long* keys; nnrt_b200::BandItem* queue; int* counters;
 	int32_t* diag_faces; float* diag_res; uint8_t* diag_mask;
 	// cached graph
@@ -467,7 +467,7 @@ extern "C" int nnrt_b200_fitter_create(const nnrt_b200_fitter_options* options, 
 	layout(f, true);
 	if (cudaMallocHost(&f->host_flags, 4 * sizeof(int)) != cudaSuccess) { cudaFree(f->arena); delete f; return kCudaError; }
 	memset(f->host_flags, 0, 4 * sizeof(int));
-	f->schur = nullptr; f->corner_rhs = nullptr; f->corner_scratch = nullptr;
+	f->schur = nullptr; f->corner_rhs = nullptr;
 	cudaMemset(f->arena, 0, bytes);
 	launch_fill_keys(f->keys, (int64_t) f->H * f->W, nullptr);
 	if (cudaDeviceSynchronize() != cudaSuccess) { set_last_error("fitter_create: workspace initialisation failed"); return kCudaError; }
@@ -570,13 +570,11 @@ extern "C" int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* f, const float* node
 		reallocated = true;
 		if (f->schur) { cudaFree(f->schur); f->schur = nullptr; }
 		const size_t n = (size_t) corner_blocks * 6;
-		const size_t scratch = corner_scratch_bytes(corner_blocks);
 		const size_t schur_floats = corner_schur_floats(corner_blocks);
-		const size_t total = (schur_floats + n + 16) * sizeof(float) + (corner_needs_global_scratch(corner_blocks) ? scratch : 0);
+		const size_t total = (schur_floats + n + 16) * sizeof(float);
 		NNRT_CUDA(cudaMalloc(&f->schur, total));
 		NNRT_CUDA(cudaMemset(f->schur, 0, total));
 		f->corner_rhs = f->schur + schur_floats;
-		f->corner_scratch = corner_needs_global_scratch(corner_blocks) ? f->corner_rhs + n + 16 : nullptr;
 	}
 	// the captured iteration graph bakes in the arrowhead shape and the corner buffers: keep it unless one of them moved
 	if (f->graph_exec && (arrow_base != f->arrow_base || fused_stem != f->fused_stem || reallocated)) {
@@ -728,7 +726,7 @@ static int enqueue_solve(nnrt_b200_fitter* f, const IterationContext& base, int 
 		launch_stem_eliminate(c.sys, s);
 		if (ev) cudaEventRecord(ev[6], s);
 	}
-	const int rc = launch_corner_solve(c.sys, f->x, R, t, true, f->corner_scratch, s);
+	const int rc = launch_corner_solve(c.sys, f->x, R, t, true, s);
 	if (ev) cudaEventRecord(ev[7], s);
 	if (rc != kOk) return rc;
 	NNRT_LAUNCH_CHECK();

@@ -82,7 +82,6 @@ __global__ void __launch_bounds__(128) matmul3x3_kernel(const float* __restrict_
 struct ExplicitArrowhead {
 	ArrowheadSystem sys{};
 	char* buffer = nullptr;
-	float* scratch = nullptr;
 };
 
 static int prepare_explicit(ExplicitArrowhead& ws, const float* diag, int N, int base, const float* wing, const int32_t* coords, int64_t W,
@@ -104,13 +103,11 @@ static int prepare_explicit(ExplicitArrowhead& ws, const float* diag, int N, int
 	for (int i = 0; i < base; i++) off[i + 1] += off[i];
 	std::vector<int> cur(off.begin(), off.end());
 	for (int64_t w = 0; w < W; w++) blocks[cur[h[w * 2]]++] = (int) w;
-	const size_t scratch_bytes = corner_scratch_bytes(nc);
-	const bool need_global = corner_needs_global_scratch(nc);
 	auto al = [](size_t v) { return (v + 255) & ~size_t(255); };
 	const size_t sz_off = al(sizeof(int) * (base + 2)), sz_blk = al(sizeof(int) * (W + 1)), sz_dinv = al(sizeof(float) * (size_t) (base + 1) * 36),
 	             sz_y = al(sizeof(float) * (size_t) (base + 1) * 6), sz_x = al(sizeof(float) * (size_t) (W + 1) * 36), sz_s = al(sizeof(float) * corner_schur_floats(nc)),
-	             sz_r = al(sizeof(float) * (n + 1)), sz_flags = 256, sz_scr = need_global ? al(scratch_bytes) : 0;
-	const size_t total = sz_off + 2 * sz_blk + sz_dinv + sz_y + sz_x + sz_s + sz_r + sz_flags + sz_scr;
+	             sz_r = al(sizeof(float) * (n + 1)), sz_flags = 256;
+	const size_t total = sz_off + 2 * sz_blk + sz_dinv + sz_y + sz_x + sz_s + sz_r + sz_flags;
 	NNRT_CUDA(cudaMallocAsync(&ws.buffer, total, s));
 	char* p = ws.buffer;
 	int* d_off = (int*) p; p += sz_off;
@@ -122,7 +119,6 @@ static int prepare_explicit(ExplicitArrowhead& ws, const float* diag, int N, int
 	ws.sys.schur = (float*) p; p += sz_s;
 	ws.sys.corner_rhs = (float*) p; p += sz_r;
 	ws.sys.flags = (int*) p; p += sz_flags;
-	ws.scratch = need_global ? (float*) p : nullptr;
 	NNRT_CUDA(cudaMemsetAsync(ws.sys.schur, 0, sz_s + sz_r + sz_flags, s));
 	NNRT_CUDA(cudaMemcpyAsync(d_off, off.data(), sizeof(int) * (base + 2), cudaMemcpyHostToDevice, s));
 	NNRT_CUDA(cudaMemcpyAsync(d_blk, blocks.data(), sizeof(int) * (W + 1), cudaMemcpyHostToDevice, s));
@@ -165,7 +161,7 @@ extern "C" int nnrt_b200_solve_block_sparse_arrowhead_cholesky(const float* diag
 	if (rc != kOk) { if (ws.buffer) cudaFreeAsync(ws.buffer, s); return rc; }
 	ws.sys.schur_tile_packed = corner_uses_tile_packed_schur(diagonal_block_count - arrow_base) ? 1 : 0;
 	launch_stem_eliminate(ws.sys, s);
-	rc = launch_corner_solve(ws.sys, x, nullptr, nullptr, false, ws.scratch, s);
+	rc = launch_corner_solve(ws.sys, x, nullptr, nullptr, false, s);
 	int flags[3] = {0, 0, 0};
 	cudaMemcpyAsync(flags, ws.sys.flags, sizeof(flags), cudaMemcpyDeviceToHost, s);
 	cudaStreamSynchronize(s);

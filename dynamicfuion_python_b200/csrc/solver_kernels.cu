@@ -129,8 +129,6 @@ __global__ void __launch_bounds__(256) corner_upper_scatter_kernel(ArrowheadSyst
 	if (lower >= 0) atomicAdd(sys.schur + lower, v);
 }
 
-__device__ __forceinline__ int64_t packed_index(int i, int k) { return (int64_t) i * (i + 1) / 2 + k; }
-
 // core::linalg::AxisAngleVectorsToMatricesRodrigues (cpp/core/linalg/RodriguesImpl.h:66-100), no small-angle guard (as the reference)
 __device__ void rodrigues(const float* __restrict__ w, float* __restrict__ R) {
 	const float angle = sqrtf(sum3(w[0] * w[0], w[1] * w[1], w[2] * w[2]));
@@ -172,86 +170,6 @@ __device__ __forceinline__ void apply_node_update(const float* __restrict__ dlt,
 		for (int c = 0; c < 3; c++) translation[c] = translation[c] + dlt[3 + c];
 	}
 }
-
-template<bool kSharedScratch>
-__global__ void __launch_bounds__(1024) corner_solve_kernel(ArrowheadSystem sys, float* __restrict__ x, float* __restrict__ rotations,
-                                                             float* __restrict__ translations, int clear_corner,
-                                                             float* __restrict__ scratch_global) {
-	extern __shared__ float smem[];
-	const int tid = threadIdx.x, T = blockDim.x;
-	const int nc = sys.node_count - sys.arrow_base, n = nc * 6;
-	const int64_t packed_count = (int64_t) (n + 1) * (n + 2) / 2;
-	float* L = kSharedScratch ? smem : scratch_global;                      // packed lower triangle, row n = rhs
-	float* col = kSharedScratch ? smem + packed_count : scratch_global + packed_count;  // [n+1]
-	if (n > 0) {
-		for (int64_t q = tid; q < (int64_t) n * n; q += T) {
-			const int i = (int) (q / n), k = (int) (q % n);
-			if (k <= i) L[packed_index(i, k)] = sys.schur[q];
-			if (clear_corner) sys.schur[q] = 0.f;
-		}
-		for (int k = tid; k < n; k += T) {
-			L[packed_index(n, k)] = sys.corner_rhs[k];
-			if (clear_corner) sys.corner_rhs[k] = 0.f;
-		}
-		__syncthreads();
-		const int tx = tid & 31, ty = tid >> 5, TY = T >> 5;
-		for (int j = 0; j < n; j++) {
-			if (tid == 0) {
-				float dj = L[packed_index(j, j)];
-				if (!(dj > 0.f)) atomicExch(sys.flags + 2, 1);
-				L[packed_index(j, j)] = sqrtf(dj);
-			}
-			__syncthreads();
-			const float dj = L[packed_index(j, j)];
-			for (int i = j + 1 + tid; i <= n; i += T) {
-				const float v = L[packed_index(i, j)] / dj;
-				L[packed_index(i, j)] = v;
-				col[i] = v;
-			}
-			__syncthreads();
-			for (int i = j + 1 + ty; i <= n; i += TY) {
-				const float ci = col[i];
-				const int k_end = min(i, n - 1);
-				float* Li = L + packed_index(i, 0);
-				for (int k = j + 1 + tx; k <= k_end; k += 32) Li[k] -= ci * col[k];
-			}
-			__syncthreads();
-		}
-		// back substitution L^T x = y with y = row n, one warp
-		if (tid < 32) {
-			float* y = L + packed_index(n, 0);
-			for (int j = n - 1; j >= 0; j--) {
-				const float xj = y[j] / L[packed_index(j, j)];
-				__syncwarp();
-				if (tid == 0) y[j] = xj;
-				const float* Lj = L + packed_index(j, 0);
-				for (int k = tid; k < j; k += 32) y[k] -= Lj[k] * xj;
-				__syncwarp();
-			}
-		}
-		__syncthreads();
-		for (int k = tid; k < n; k += T) x[sys.arrow_base * 6 + k] = L[packed_index(n, k)];
-	}
-	// stem back-substitution: x_i = y_i - sum_e X_e x_C[col(e)]
-	const float* xc = L + packed_index(n, 0);
-	for (int idx = tid; idx < sys.arrow_base * 6; idx += T) {
-		const int i = idx / 6, r = idx % 6;
-		float acc = sys.stem_y[idx];
-		for (int e = sys.row_offsets[i]; e < sys.row_offsets[i + 1]; e++) {
-			const int w = sys.row_blocks[e];
-			const float* X = sys.wing_x + (int64_t) w * 36 + r * 6;
-			const float* xv = xc + (sys.wing_columns[w] - sys.arrow_base) * 6;
-#pragma unroll
-			for (int k = 0; k < 6; k++) acc -= X[k] * xv[k];
-		}
-		x[idx] = acc;
-	}
-	if (rotations == nullptr) return;
-	__syncthreads();
-	__threadfence_block();
-	for (int node = tid; node < sys.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3, sys.update_mode);
-}
-
 
 // ---- blocked single-CTA corner solve ------------------------------------------------------------------------------------
 // Right-looking Cholesky in shared memory, panels of kPanel = 8 columns, the right-hand side carried as row n (forward
@@ -542,15 +460,6 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_blocked_kernel(Ar
 	NNRT_STAMP(5);
 #endif
 }
-
-// Blackwell packed fp32 FMA (FFMA2): two independent IEEE fp32 fused multiply-adds per lane per instruction.
-__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
-	unsigned long long ra, rb, rc, rd;
-	ra = *reinterpret_cast<unsigned long long*>(&a); rb = *reinterpret_cast<unsigned long long*>(&b); rc = *reinterpret_cast<unsigned long long*>(&c);
-	asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
-	return *reinterpret_cast<float2*>(&rd);
-}
-__device__ __forceinline__ float negate_bits(float v) { return __int_as_float(__float_as_int(v) ^ (int) 0x80000000u); }  // ALU pipe, not FMA
 
 // ---- register-tiled single-CTA corner solve (n + 1 <= 256) ---------------------------------------------------------------
 // The trailing matrix never round-trips through shared memory: thread t owns ONE 8 x 8 tile (bi, bj), bi >= bj, of the
@@ -1110,16 +1019,11 @@ static int launch_corner_solve_wide(const ArrowheadSystem& sys, int n, float* x,
 	return kOk;
 }
 
-size_t corner_scratch_bytes(int corner_blocks) {
-	const int64_t n = (int64_t) corner_blocks * 6;
-	return (size_t) (((n + 1) * (n + 2) / 2 + (n + 1)) * sizeof(float));
-}
 bool corner_uses_tile_packed_schur(int corner_blocks) { return regtile_corner_fits(corner_blocks * 6); }
 size_t corner_schur_floats(int corner_blocks) {
 	const size_t n = (size_t) corner_blocks * 6, dense = n * n, packed = (size_t) corner_tile_floats((int) n);
 	return (dense > packed ? dense : packed) + 64;
 }
-bool corner_needs_global_scratch(int corner_blocks) { return blocked_corner_floats(corner_blocks * 6) * sizeof(float) > 227 * 1024; }
 
 void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s) {
 	if (sys.node_count > 0) stem_eliminate_kernel<<<(sys.node_count + 3) / 4, 128, 0, s>>>(sys);
@@ -1127,7 +1031,7 @@ void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s) {
 }
 
 int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotations, float* node_translations, bool clear_corner,
-                        float* scratch_global, cudaStream_t s) {
+                        cudaStream_t s) {
 	const int n = (sys.node_count - sys.arrow_base) * 6;
 	constexpr size_t kMaxShared = 227 * 1024;
 	const size_t blocked_bytes = blocked_corner_floats(n) * sizeof(float);
@@ -1151,7 +1055,6 @@ int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotati
 		return kOk;
 	}
 	// corners too large for one SM's shared memory: multi-kernel blocked factorisation of the dense Schur buffer, in place
-	(void) scratch_global;
 	return launch_corner_solve_wide(sys, n, x, node_rotations, node_translations, clear_corner, s);
 }
 

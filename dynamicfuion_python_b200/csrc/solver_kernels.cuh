@@ -3,9 +3,10 @@
 //   stem_eliminate: one warp per block row. Stem rows: 6x6 Cholesky inverse D^-1, y = D^-1 b, X_e = D^-1 B_e for the row's wing
 //                   blocks, Schur update S -= B_e1^T X_e2 and rhs update b_C -= X_e^T b (float atomics into the dense corner).
 //                   Corner rows: S_diag += C_jj, b_C += b_j.
-//   corner_solve:   single CTA; packed lower-triangular Cholesky of S in shared memory with the right-hand side carried as an
-//                   extra row (forward substitution for free), warp-level back substitution, stem back-substitution
-//                   x_i = y_i - sum_e X_e x_C, optional fused node update (Rodrigues, R <- R dR, t += dt).
+//   corner_solve:   Cholesky of S with the right-hand side carried as an extra row (forward substitution for free), back
+//                   substitution, stem back-substitution x_i = y_i - sum_e X_e x_C, optional fused node update (Rodrigues,
+//                   R <- R dR, t += dt). Up to 246 unknowns: one CTA, one 8 x 8 tile per thread in registers; up to what one SM's
+//                   shared memory holds: one CTA, blocked in shared memory; beyond: per-panel launches over the dense buffer.
 // This replaces cuSOLVER potrfBatched + MAGMA potrs_batched + 5 cuBLAS gemmBatched + potrf + 2 trsm + their host syncs.
 #pragma once
 #include "host_util.h"
@@ -70,10 +71,8 @@ __device__ __forceinline__ int64_t schur_slot(const ArrowheadSystem& sys, int n,
 void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s);
 // x [6N]; if node_rotations != nullptr the update is applied in place; clear_corner zeroes schur / corner_rhs after reading.
 int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotations, float* node_translations, bool clear_corner,
-                        float* scratch_global, cudaStream_t s);
-size_t corner_scratch_bytes(int corner_blocks);
+                        cudaStream_t s);
 bool corner_uses_tile_packed_schur(int corner_blocks);   // true when launch_corner_solve will pick the register-tiled kernel
 size_t corner_schur_floats(int corner_blocks);            // allocation size of `schur` valid for either layout
-bool corner_needs_global_scratch(int corner_blocks);  // corner too large for the single-SM shared-memory kernel
 
 }  // namespace nnrt_b200

@@ -40,7 +40,7 @@ int main(int argc, char** argv) {
 	float ms_stem = 0, ms_corner = 0; const int reps = 20;
 	for (int rep = 0; rep < reps + 3; rep++) {
 		cudaEventRecord(e0); launch_stem_eliminate(sys, 0); cudaEventRecord(e1);
-		int rc = launch_corner_solve(sys, x, R, t, true, nullptr, 0); cudaEventRecord(e2); cudaEventSynchronize(e2);
+		int rc = launch_corner_solve(sys, x, R, t, true, 0); cudaEventRecord(e2); cudaEventSynchronize(e2);
 		if (rc) { printf("launch rc %d\n", rc); return 1; }
 		float a, b; cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);
 		if (rep >= 3) { ms_stem += a; ms_corner += b; }
@@ -49,7 +49,7 @@ int main(int argc, char** argv) {
 		std::vector<float> first((size_t) N * 6), cur((size_t) N * 6);
 		int bad = 0;
 		for (int rep = 0; rep < 300; rep++) {
-			launch_stem_eliminate(sys, 0); launch_corner_solve(sys, x, R, t, true, nullptr, 0);
+			launch_stem_eliminate(sys, 0); launch_corner_solve(sys, x, R, t, true, 0);
 			cudaMemcpy(cur.data(), x, sizeof(float) * N * 6, cudaMemcpyDeviceToHost);
 			if (rep == 0) first = cur;
 			double worst = 0; for (int i = 0; i < N * 6; i++) { double d = fabs((double) cur[i] - first[i]); if (!(d <= 1e-4)) worst = 1e9; else worst = fmax(worst, d); }
