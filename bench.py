@@ -1,8 +1,11 @@
 """bench.py — dense-depth GN iteration benchmark (BASELINE.json metric: ms per GN iteration @640x480; frames/s box-wide).
 
-A "step" is one frame fit of configuration C2 (bunny-scale relief mesh, ~82k triangles, 249 nodes = 208 stem + 41 corner,
-832 edges, 640x480 depth): the reference's once-per-fit setup (anchors, face-anchor association, reference unprojection;
-DeformableMeshToImageFitter.cpp:96-106,293-307) plus ITERATIONS_PER_FRAME Gauss-Newton iterations (:111-275).
+A frame fit of configuration C2 (bunny-scale relief mesh, ~82k triangles, 249 nodes = 208 stem + 41 corner, 832 edges, 640x480
+depth) is the reference's once-per-fit setup (anchors, face-anchor association, reference unprojection;
+DeformableMeshToImageFitter.cpp:96-106,293-307) plus ITERATIONS_PER_FRAME Gauss-Newton iterations (:111-275). A "step" is one frame
+of each of `--sequences` independent sequences resident on the GPU (BASELINE.json configs[4]; each sequence has its own fitter, warp
+field and CUDA stream, frames inside a sequence are serial). The single-sequence latency (ms per GN iteration, the <= 1 ms target)
+is measured in a separate leg and reported as `ms_per_iteration` / `latency`.
 
   python bench.py --gpus N --steps K --warmup W              our sm_100a path (one process per GPU; frames are sharded, no collective)
   python bench.py --impl reference --gpus N --steps K ...    the reference algorithm's CPU path (oracle restatement, OpenMP, all host threads)
@@ -156,24 +159,34 @@ def run_b200(args):
     frames_host = [f.cpu().pin_memory() for f in frames_dev]
     coverage = float((frames_dev[0] > 0).float().mean())
 
-    wf = new_field()
-    fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=ITERATIONS_PER_FRAME, preconditioning_dampening_factor=s["lm_factor"],
-                                                        arap_term_weight=s["arap_term_weight"])
+    from dynamicfuion_python_b200 import frame_batch
+    S = args.sequences
     eye = torch.eye(3, device=dev).repeat(N, 1, 1).contiguous()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    # one warp field + fitter + stream + pinned result buffers per resident sequence (BASELINE.json configs[4]: independent sequences)
+    seqs = [dict(wf=new_field(),
+                 fitter=nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=ITERATIONS_PER_FRAME,
+                                                                   preconditioning_dampening_factor=s["lm_factor"],
+                                                                   arap_term_weight=s["arap_term_weight"]),
+                 host_R=torch.empty((N, 3, 3), dtype=torch.float32).pin_memory(),
+                 host_t=torch.empty((N, 3), dtype=torch.float32).pin_memory()) for _ in range(S)]
+    pool = frame_batch.SequenceStreams(S, dev)
+    wf, fitter = seqs[0]["wf"], seqs[0]["fitter"]
 
-    host_R = torch.empty((N, 3, 3), dtype=torch.float32).pin_memory()
-    host_t = torch.empty((N, 3), dtype=torch.float32).pin_memory()
+    def fit(q, depth, read_back):
+        q["wf"].node_rotations.copy_(eye); q["wf"].node_translations.zero_()
+        q["fitter"].fit_to_image(q["wf"], mesh, None, depth, None, K, ext, 1.0)
+        if read_back:  # result of the frame back on the host: two asynchronous copies into pinned buffers on the sequence's stream
+            q["host_R"].copy_(q["wf"].node_rotations, non_blocking=True)
+            q["host_t"].copy_(q["wf"].node_translations, non_blocking=True)
 
-    def step(depth, read_back):
-        wf.node_rotations.copy_(eye); wf.node_translations.zero_()
-        fitter.fit_to_image(wf, mesh, None, depth, None, K, ext, 1.0)
-        if read_back:  # result of the step back on the host: two asynchronous copies into pinned buffers, one synchronisation
-            host_R.copy_(wf.node_rotations, non_blocking=True)
-            host_t.copy_(wf.node_translations, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-            return host_R, host_t
-        return None
+    def step(frames, index, read_back):
+        """One frame of every resident sequence, each on its own stream. With read_back the host holds a sequence's previous result
+        (stream synchronised) before that sequence's next frame is enqueued."""
+        for k, q in enumerate(seqs):
+            if read_back:
+                pool.synchronize(k)
+            pool.run(k, fit, q, frames[(first + index + k) % FRAME_POOL], read_back)
 
     def barrier():
         torch.cuda.synchronize()
@@ -183,41 +196,56 @@ def run_b200(args):
 
     first = rank % FRAME_POOL
     for i in range(args.warmup):
-        step(frames_dev[(first + i) % FRAME_POOL], False)
-    fitter.check_status()
+        step(frames_dev, i, False)
+    torch.cuda.synchronize()
+    for q in seqs:
+        q["fitter"].check_status()
 
-    # ---- value: inputs resident in HBM, CUDA events per step on the launching stream, L2 flushed between steps
+    # ---- value: inputs resident in HBM, one CUDA event pair on the launching stream around the K steps (sequence streams forked from /
+    # joined into it); the resident sequences' working sets (S x workspace) exceed L2, so a sequence finds its data evicted each frame
     sampler = ClockSampler(local)
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     if rank == 0:
         sampler.start()
+    start.record()
+    pool.fork()
     for i in range(args.steps):
-        flush.fill_(i & 0xFF)
-        starts[i].record()
-        step(frames_dev[(first + i) % FRAME_POOL], False)
-        ends[i].record()
+        step(frames_dev, i, False)
+    pool.join()
+    end.record()
     barrier()
-    dev_ms = sum(a.elapsed_time(b) for a, b in zip(starts, ends))
-    fitter.check_status()
-    final_t = wf.node_translations.cpu().numpy()
-    if not np.isfinite(final_t).all():
-        raise RuntimeError("bench: fit diverged (non-finite node translations)")
+    dev_ms = start.elapsed_time(end)
+    for q in seqs:
+        q["fitter"].check_status()
+        if not bool(torch.isfinite(q["wf"].node_translations).all()):
+            raise RuntimeError("bench: fit diverged (non-finite node translations)")
 
     # ---- e2e: public API call with the depth frame in pinned host memory + D2H of the node state, wall clock around K steps
     for i in range(min(args.warmup, 3)):
-        step(frames_host[(first + i) % FRAME_POOL], True)
+        step(frames_host, i, True)
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        step(frames_host[(first + i) % FRAME_POOL], True)
+        step(frames_host, i, True)
+    pool.synchronize()
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
 
-    from dynamicfuion_python_b200 import frame_batch
-    dev_ms, e2e_ms = frame_batch.max_over_ranks([dev_ms, e2e_ms], dev)  # frames are sharded, no data-path collective: only the clock is reduced
+    # ---- latency: ONE sequence alone on the GPU, L2 flushed between frames, CUDA events per frame (the <= 1 ms / iteration target)
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    barrier()
+    for i in range(args.steps):
+        flush.fill_(i & 0xFF)
+        starts[i].record()
+        fit(seqs[0], frames_dev[(first + i) % FRAME_POOL], False)
+        ends[i].record()
+    barrier()
+    latency_ms = sum(a.elapsed_time(b) for a, b in zip(starts, ends)) / args.steps
+
+    dev_ms, e2e_ms, latency_ms = frame_batch.max_over_ranks([dev_ms, e2e_ms, latency_ms], dev)  # frames are sharded, no data-path collective: only the clock is reduced
 
     # ---- per-kernel stage times (CUDA events between the 7 launches of an iteration, outside the graph) for the roofline
     stage_ms = np.zeros(7)
@@ -233,8 +261,8 @@ def run_b200(args):
         stage_ms /= profiled
     out = None
     if rank == 0:
-        out = dict(dev_ms=dev_ms, e2e_ms=e2e_ms, stage_ms=stage_ms.tolist(), clocks=clocks, coverage=coverage, dims=(V, F, PX, N, E),
-                   world=world, launches=int(fitter.launches_per_iteration()), workspace=int(fitter.workspace_bytes()))
+        out = dict(dev_ms=dev_ms, e2e_ms=e2e_ms, latency_ms=latency_ms, sequences=S, stage_ms=stage_ms.tolist(), clocks=clocks, coverage=coverage, dims=(V, F, PX, N, E),
+                   world=world, launches=int(fitter.launches_per_iteration()), workspace=int(fitter.workspace_bytes()) * S)
     if world > 1:
         dist.destroy_process_group()
     return out
@@ -324,8 +352,9 @@ def run_reference(args):
     sample = (f"each step = per-fit setup + {iters} of {ITERATIONS_PER_FRAME} GN iterations of {WORKLOAD} @640x480, extrapolated to a full frame; "
               f"{threads} threads on '{cpu_model()}'")
     return {"impl": "reference", "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": frame_s * 1e3, "ms_per_iteration": per_iter * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": bench_config(args.gpus),
+            "ms_per_step": frame_s * 1e3 * args.sequences * args.gpus, "frames_per_step": args.sequences * args.gpus, "ms_per_frame": frame_s * 1e3,
+            "ms_per_iteration": per_iter * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": bench_config(args.gpus, args.sequences),
             "cpu_baseline": {"value": value, "unit": "frames/s", "cores": host_cores(), "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
 
@@ -333,11 +362,14 @@ def run_reference(args):
 METRIC = "frames/s box-wide (frame = per-fit setup + 10 dense-depth GN iterations @640x480); ms per GN iteration in ms_per_iteration"
 
 
-def bench_config(gpus):
+def bench_config(gpus, sequences):
     return {"workload": f"{WORKLOAD}: relief mesh V=41209 F=81608, 249 nodes (208 stem + 41 corner, 1494x1494 arrowhead system), 832 edges, "
-                        f"{WIDTH}x{HEIGHT} depth, {ITERATIONS_PER_FRAME} GN iterations/frame (BASELINE.json configs[1])",
-            "parallelism": f"frame-batch x{gpus} (independent frames per GPU, no collective)",
-            "l2": "256 MiB device fill between timed steps (outside the per-step CUDA events); working set < L2 within a step by nature of the path",
+                        f"{WIDTH}x{HEIGHT} depth, {ITERATIONS_PER_FRAME} GN iterations/frame (BASELINE.json configs[1]); a step = one frame of each "
+                        f"of {sequences} independent sequences per GPU (configs[4])",
+            "parallelism": f"frame-batch: {gpus} GPU(s) x {sequences} resident sequences, one fitter + CUDA stream per sequence, no collective",
+            "sequences_per_gpu": sequences,
+            "l2": f"throughput legs: the {sequences} resident sequences' working sets ({sequences} x 23 MB) exceed the 126 MB L2, every sequence "
+                  "finds its data evicted at its next frame; latency leg: 256 MiB device fill between frames (outside the per-frame CUDA events)",
             "frames": f"{FRAME_POOL} distinct synthetic target depth frames cycled"}
 
 
@@ -356,6 +388,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--sequences", type=int, default=16, help="independent sequences resident per GPU, each on its own stream")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the bounded CPU sample (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 0)
@@ -369,7 +402,8 @@ def main():
         return
     V, F, PX, N, E = r["dims"]
     world = r["world"]
-    frames = args.steps * world
+    S = r["sequences"]
+    frames = args.steps * world * S
     value = frames / (r["dev_ms"] * 1e-3)
     e2e_value = frames / (r["e2e_ms"] * 1e-3)
     ms_per_step = r["dev_ms"] / args.steps
@@ -393,11 +427,15 @@ def main():
                 "stage_ms": stage_ms, "iteration_algorithmic_bytes": bytes_by["total"],
                 "iteration_achieved_gbs": bytes_by["total"] / (iter_ms_profiled * 1e-3) / 1e9 if iter_ms_profiled else None}
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "ms_per_iteration": ms_per_step / ITERATIONS_PER_FRAME, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": bench_config(world),
-            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": PX * 4, "d2h_bytes_per_step": N * 12 * 4,
-                    "ms_per_step": r["e2e_ms"] / args.steps, "timing": "wall clock around K fit_to_image calls, synchronize + barrier on both sides, max over ranks"},
-            "gpu_launches": args.steps * (SETUP_LAUNCHES + ITERATIONS_PER_FRAME * r["launches"]),
+            "ms_per_step": ms_per_step, "frames_per_step": S * world, "ms_per_iteration": r["latency_ms"] / ITERATIONS_PER_FRAME,
+            "latency": {"ms_per_frame": r["latency_ms"], "ms_per_iteration": r["latency_ms"] / ITERATIONS_PER_FRAME,
+                        "frames_per_s_one_sequence": 1e3 / r["latency_ms"],
+                        "note": "one sequence alone on the GPU, L2 flushed between frames, CUDA events per frame (per-fit setup included)"},
+            "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": bench_config(world, S),
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": PX * 4 * S, "d2h_bytes_per_step": N * 12 * 4 * S,
+                    "ms_per_step": r["e2e_ms"] / args.steps, "timing": "wall clock around K steps of fit_to_image calls (one per resident sequence), synchronize + barrier on both sides, max over ranks"},
+            "gpu_launches": args.steps * S * (SETUP_LAUNCHES + ITERATIONS_PER_FRAME * r["launches"]),
             "clocks": r["clocks"], "roofline": roofline, "coverage": r["coverage"], "workspace_bytes": r["workspace"]}
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_sample(make_bench_scene(), 3)

@@ -46,3 +46,42 @@ def run_sequences(sequence_ids, frames_per_sequence, fit_frame):
             fit_frame(seq, frame)
             count += 1
     return count
+
+
+class SequenceStreams:
+    """One CUDA stream per sequence resident on this GPU. A fit is a chain of dependent launches that ends in a single-CTA corner
+    solve, so one sequence leaves most SMs idle; independent sequences (configs[4]) fill them when each has its own fitter, warp field
+    and stream. Nothing is shared between sequences, so no cross-stream ordering is needed beyond fork() / join() with the caller's
+    stream."""
+
+    def __init__(self, count, device=None):
+        if count < 1:
+            raise ValueError("at least one sequence")
+        if not torch.cuda.is_available():
+            raise RuntimeError("SequenceStreams needs a CUDA device; there is no CPU fallback")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.streams = [torch.cuda.Stream(self.device) for _ in range(count)]
+
+    def __len__(self):
+        return len(self.streams)
+
+    def fork(self):
+        """Every sequence stream waits for the work already enqueued on the caller's current stream."""
+        event = torch.cuda.current_stream(self.device).record_event()
+        for stream in self.streams:
+            stream.wait_event(event)
+
+    def join(self):
+        """The caller's current stream waits for every sequence stream (no host synchronisation)."""
+        current = torch.cuda.current_stream(self.device)
+        for stream in self.streams:
+            current.wait_event(stream.record_event())
+
+    def run(self, sequence, fn, *args, **kwargs):
+        """Calls fn(*args, **kwargs) with sequence's stream current, so everything it enqueues lands on that stream."""
+        with torch.cuda.stream(self.streams[sequence]):
+            return fn(*args, **kwargs)
+
+    def synchronize(self, sequence=None):
+        for stream in (self.streams if sequence is None else [self.streams[sequence]]):
+            stream.synchronize()

@@ -13,9 +13,10 @@ def rel_close(a, b, rtol, floor_scale=1e-6):
     return not bad.any(), float((np.abs(a - b) / np.maximum(np.maximum(np.abs(a), np.abs(b)), floor)).max())
 
 
-def scene_with_target(oracle, config, height, width):
+def scene_with_target(oracle, config, height, width, translation_scale=1.0):
     """Scene + anchors (oracle) + target reference points rendered by the oracle from the ground-truth motion."""
     s = synthetic.make_scene(config, height, width)
+    s["translations_gt"] = (s["translations_gt"] * translation_scale).astype(s["translations_gt"].dtype)
     anchors, weights = oracle.compute_anchors(s["positions"], s["nodes"], 4, 0, s["node_coverage"])
     wp, wn = oracle.warp(s["positions"], s["normals"], s["nodes"], s["rotations_gt"], s["translations_gt"], anchors, weights)
     fv, mask = oracle.face_vertices_ndc(wp, s["triangles"], s["K"], height, width, 0.0, 10.0)
