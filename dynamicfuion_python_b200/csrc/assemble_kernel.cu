@@ -22,9 +22,10 @@ __device__ __forceinline__ float warp_transpose_reduce(float (&vals)[32], int la
 	return vals[0];
 }
 
-// row-vector times skew(s):  r * [[0,-sz,sy],[sz,0,-sx],[-sy,sx,0]]
+// row-vector times skew(s):  r * [[0,-sz,sy],[sz,0,-sx],[-sy,sx,0]]. The products with the matrix's zeros are left out: they add
+// +-0 to a sum, which changes nothing but the sign of an exact zero.
 __device__ __forceinline__ float3 row_times_skew(float3 r, float3 s) {
-	return make_float3(sum3(r.x * 0.f, r.y * s.z, r.z * -s.y), sum3(r.x * -s.z, r.y * 0.f, r.z * s.x), sum3(r.x * s.y, r.y * -s.x, r.z * 0.f));
+	return make_float3(r.y * s.z + r.z * -s.y, r.x * -s.z + r.z * s.x, r.x * s.y + r.y * -s.x);
 }
 
 __device__ __forceinline__ void cp_async_16(void* shared_dst, const void* global_src) {
@@ -58,7 +59,7 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 	// tiles are visited in a scrambled order (multiplication by a prime modulo the tile count): the surface covers a compact
 	// part of the image, and in raster order its expensive tiles would reach the SMs as one late clump
 	const unsigned tile_count = gridDim.x * gridDim.y, linear = blockIdx.y * gridDim.x + blockIdx.x;
-	const unsigned tile = (tile_count % 1009u) ? (unsigned) (((unsigned long long) linear * 1009ull) % tile_count) : linear;
+	const unsigned tile = (tile_count % 1009u) && tile_count < (1u << 22) ? (linear * 1009u) % tile_count : linear;  // 32-bit: no overflow below 2^22 tiles
 	const int tile_x = (int) (tile % gridDim.x) * 16 + (warp & 1) * 8, tile_y = p.row_begin + (int) (tile / gridDim.x) * 8 + (warp >> 1) * 4;
 	const int u = tile_x + (lane & 7), v = tile_y + (lane >> 3);
 	const bool in_image = u < p.width && v < p.row_end;
@@ -173,7 +174,7 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 			}
 		}
 	}
-	if (in_image) {
+	if (in_image && p.write_diagnostics) {
 		d.diag_pixel_faces[px] = face;
 		d.diag_residuals[px] = residual;
 		d.diag_mask[px] = residual_mask ? 1 : 0;
@@ -222,11 +223,8 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 template<int A>
 static int launch_assemble_for(const FitterDeviceData& d, const DataTermParams& p, cudaStream_t s) {
 	constexpr size_t bytes = assemble_shared_bytes(A);
-	static bool attribute_set = false;
-	if (bytes > 48 * 1024 && !attribute_set) {
-		if (cudaFuncSetAttribute(assemble_kernel<A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bytes) != cudaSuccess) return kCudaError;
-		attribute_set = true;
-	}
+	static SharedMemoryOptIn opt_in;
+	if (bytes > 48 * 1024 && opt_in.ensure(assemble_kernel<A>, bytes) != kOk) return kCudaError;
 	const dim3 grid((p.width + 15) / 16, (p.row_end - p.row_begin + 7) / 8);
 	assemble_kernel<A><<<grid, kAssembleThreads, bytes, s>>>(d, p);
 	return kOk;

@@ -395,7 +395,7 @@ struct nnrt_b200_fitter {
 	int32_t* diag_faces; float* diag_res; uint8_t* diag_mask;
 	// cached graph
 	cudaGraphExec_t graph_exec = nullptr;
-	struct GraphKey { float* R; float* t; double K[9]; double T[16]; int iters; cudaStream_t stream; } graph_key{};
+	struct GraphKey { float* R; float* t; double K[9]; double T[16]; int iters; } graph_key{};  // an instantiated graph launches into any stream
 
 	template<typename T> T* take(size_t count) {
 		const size_t bytes = (count * sizeof(T) + 255) & ~size_t(255);
@@ -681,6 +681,7 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	// RasterizeNdcTriangles(..., blur 0.5 px, ...) (DeformableMeshToImageFitter.cpp:124-127); ImageSpaceDistanceToNdc
 	c.p.blur_radius = 0.5f / (fminf((float) f->H, (float) f->W) / 2.0f);
 	c.p.row_begin = f->row_begin; c.p.row_end = f->row_end > 0 ? f->row_end : f->H;
+	c.p.write_diagnostics = 1;
 	c.extrinsics = rigid_from_host(T);
 	return c;
 }
@@ -795,7 +796,7 @@ extern "C" int nnrt_b200_fitter_fit(nnrt_b200_fitter* f, float* node_rotations, 
 	static const double I4[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
 	const double* T = extrinsics_host ? extrinsics_host : I4;
 	nnrt_b200_fitter::GraphKey key{};
-	key.R = node_rotations; key.t = node_translations; key.iters = iteration_count; key.stream = s;
+	key.R = node_rotations; key.t = node_translations; key.iters = iteration_count;
 	memcpy(key.K, intrinsics_host, sizeof(key.K)); memcpy(key.T, T, sizeof(key.T));
 	if (f->graph_exec == nullptr || memcmp(&key, &f->graph_key, sizeof(key)) != 0) {
 		if (f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
@@ -804,8 +805,11 @@ extern "C" int nnrt_b200_fitter_fit(nnrt_b200_fitter* f, float* node_rotations, 
 		NNRT_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
 		NNRT_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
 		int rc = kOk;
-		for (int it = 0; it < iteration_count && rc == kOk; it++)
-			rc = enqueue_iteration(f, c, f->modes[(size_t) it % f->modes.size()], node_rotations, node_translations, cs, nullptr);
+		for (int it = 0; it < iteration_count && rc == kOk; it++) {
+			IterationContext ci = c;
+			ci.p.write_diagnostics = it == iteration_count - 1 ? 1 : 0;  // get_diagnostics reports the last iteration
+			rc = enqueue_iteration(f, ci, f->modes[(size_t) it % f->modes.size()], node_rotations, node_translations, cs, nullptr);
+		}
 		cudaGraph_t graph = nullptr;
 		const cudaError_t end = cudaStreamEndCapture(cs, &graph);
 		cudaStreamDestroy(cs);

@@ -28,6 +28,7 @@ struct DataTermParams {
 	float tukey_cutoff;
 	float blur_radius;    // NDC
 	int row_begin, row_end;  // image rows [row_begin, row_end) this GPU rasterises and assembles (whole image unless pixel-sharded)
+	int write_diagnostics;   // per-pixel face / residual / mask of this iteration are kept (the last iteration of a fit; every split or profiled one)
 };
 
 struct FitterDeviceData {

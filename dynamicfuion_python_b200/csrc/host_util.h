@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstdarg>
 #include <cstdint>
+#include <atomic>
 #include "common.cuh"
 
 namespace nnrt_b200 {
@@ -28,6 +29,22 @@ void set_last_error(const char* fmt, ...);
 	} while (0)
 
 #define NNRT_LAUNCH_CHECK() NNRT_CUDA(cudaGetLastError())
+
+// Opt-in to more than 48 KB of dynamic shared memory. The attribute belongs to the (kernel, device) pair, so one flag per call site is
+// kept per device ordinal; fitters of different devices or threads may reach a launcher at the same time.
+struct SharedMemoryOptIn {
+	std::atomic<unsigned long long> done{0};
+	template<typename Kernel>
+	int ensure(Kernel kernel, size_t bytes) {
+		int device = 0;
+		if (cudaGetDevice(&device) != cudaSuccess) return kCudaError;
+		const unsigned long long bit = 1ull << (device & 63);
+		if (done.load(std::memory_order_acquire) & bit) return kOk;
+		if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bytes) != cudaSuccess) return kCudaError;
+		done.fetch_or(bit, std::memory_order_release);
+		return kOk;
+	}
+};
 
 inline unsigned blocks_for(int64_t n, int threads) { return (unsigned) ((n + threads - 1) / threads); }
 

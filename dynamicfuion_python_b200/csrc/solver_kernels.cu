@@ -1006,11 +1006,8 @@ static int launch_corner_solve_wide(const ArrowheadSystem& sys, int n, float* x,
 			corner_wide_trailing_kernel<<<dim3(tiles, tiles), 256, 0, s>>>(sys, n, j);
 		}
 	}
-	static bool attribute_set = false;
-	if (!attribute_set) {
-		if (cudaFuncSetAttribute(corner_wide_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024) != cudaSuccess) return kCudaError;
-		attribute_set = true;
-	}
+	static SharedMemoryOptIn finish_opt_in;
+	if (finish_opt_in.ensure(corner_wide_finish_kernel, 160 * 1024) != kOk) return kCudaError;
 	corner_wide_finish_kernel<<<1, 1024, (size_t) n * sizeof(float), s>>>(sys, n, x, node_rotations, node_translations);
 	if (clear_corner) {
 		if (cudaMemsetAsync(sys.schur, 0, (size_t) n * n * sizeof(float), s) != cudaSuccess) return kCudaError;
@@ -1037,20 +1034,14 @@ int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotati
 	const size_t blocked_bytes = blocked_corner_floats(n) * sizeof(float);
 	if (sys.schur_tile_packed) {
 		if (!regtile_corner_fits(n)) return kInvalidArgument;
-		static bool regtile_attribute_set = false;
-		if (!regtile_attribute_set) {
-			if (cudaFuncSetAttribute(corner_solve_regtile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kMaxShared) != cudaSuccess) return kCudaError;
-			regtile_attribute_set = true;
-		}
+		static SharedMemoryOptIn regtile_opt_in;
+		if (regtile_opt_in.ensure(corner_solve_regtile_kernel, kMaxShared) != kOk) return kCudaError;
 		corner_solve_regtile_kernel<<<1, kCornerThreads, regtile_corner_floats(n) * sizeof(float), s>>>(sys, x, node_rotations, node_translations, clear_corner ? 1 : 0);
 		return kOk;
 	}
 	if (blocked_bytes <= kMaxShared) {
-		static bool blocked_attribute_set = false;
-		if (!blocked_attribute_set) {
-			if (cudaFuncSetAttribute(corner_solve_blocked_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kMaxShared) != cudaSuccess) return kCudaError;
-			blocked_attribute_set = true;
-		}
+		static SharedMemoryOptIn blocked_opt_in;
+		if (blocked_opt_in.ensure(corner_solve_blocked_kernel, kMaxShared) != kOk) return kCudaError;
 		corner_solve_blocked_kernel<<<1, kCornerThreads, blocked_bytes, s>>>(sys, x, node_rotations, node_translations, clear_corner ? 1 : 0);
 		return kOk;
 	}
