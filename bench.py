@@ -142,7 +142,7 @@ def run_b200(args):
     V, F, N, E, PX = s["positions"].shape[0], s["triangles"].shape[0], s["nodes"].shape[0], s["edges"].shape[0], HEIGHT * WIDTH
 
     def new_field():
-        return G.HierarchicalGraphWarpField(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
+        return G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
                                             G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
 
     # target depth frames rendered by the CUDA rasteriser from scaled ground-truth motion (synthetic data, seeded)

@@ -79,7 +79,10 @@ class DeformableMeshToImageFitter:
         if mesh.triangles is None:
             raise RuntimeError("Argument mesh needs to have both triangle vertex indices and vertex positions.")
         if anchors is None:  # warp_field.PrecomputeAnchorsAndWeights(canonical_mesh, true), DeformableMeshToImageFitter.cpp:96-97
-            anchors, anchor_weights = warp_field.precompute_anchors_and_weights(mesh)
+            if hasattr(warp_field, "node_indices"):  # hierarchical field: anchors must index the virtual order the solver works in
+                anchors, anchor_weights = warp_field.precompute_anchors_and_weights(mesh, use_virtual_ordering=True)
+            else:
+                anchors, anchor_weights = warp_field.precompute_anchors_and_weights(mesh)
         anchors, anchor_weights = T.cuda(anchors, torch.int32), T.cuda(anchor_weights, torch.float32)
         edges = getattr(warp_field, "edges", None)
         e = 0 if edges is None else int(edges.shape[0])

@@ -130,3 +130,16 @@ def unproject_raster_depth_without_filtering(depth, intrinsics, extrinsics=None,
     if preserve_pixel_layout:
         return pts.reshape(rows, cols, 3), mask.reshape(rows, cols)
     return pts, mask
+
+
+def median_grid_subsample_3d_points(points, grid_cell_size):
+    """MedianGridSubsample3dPoints (cpp/pybind/geometry/functional/functional.cpp:152-154; cpp/geometry/functional/GeometrySampling.cpp:61-68):
+    int64 indices of the per-grid-cell median points (smallest sum of distances to the cell's points), cells in order of their first point."""
+    import ctypes as C
+    pts = T.cuda(points, torch.float32)
+    if pts.dim() != 2 or pts.shape[1] != 3:
+        raise RuntimeError(f"points must have shape [N, 3], got {tuple(pts.shape)}")
+    sample = T.empty((pts.shape[0],), torch.int64)
+    count = C.c_int64()
+    T.call("nnrt_b200_median_grid_subsample_3d_points", T.ptr(pts), pts.shape[0], float(grid_cell_size), T.ptr(sample), C.byref(count), T.stream())
+    return sample[:count.value]

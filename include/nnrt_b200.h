@@ -201,6 +201,43 @@ int nnrt_b200_fitter_get_diagnostics(nnrt_b200_fitter* fitter, float* hessian_di
 int nnrt_b200_fitter_status(nnrt_b200_fitter* fitter, void* stream);
 /* Number of kernel launches one iteration issues (for bench.py's gpu_launches). */
 int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter* fitter);
+/* ---- Warp-field construction (the once-per-fit setup in front of the loop) ----
+ * The reference numbers grid cells by hash-map buffer index and fills a cell's point list in arrival order, so its bin order and
+ * (for exact distance-sum ties) its choice are run-dependent; its tests compare sets. These entry points resolve every such rule
+ * by ascending point index (the reference's single-thread CPU result) and are reproducible. */
+
+/* geometry::functional::MedianGridSubsample3dPoints (geometry/functional/GeometrySampling.cpp:61-68;
+ * kernel/GeometrySamplingGridBinning.h:30-52, kernel/GeometrySamplingMedian.h:36-285): for every occupied cell of a grid with
+ * the given cell size, the index of the point with the smallest sum of distances to the cell's points. sample: int64, capacity
+ * point_count; cells in order of their first point. Synchronises the stream once (the count is a host value, as in the reference). */
+int nnrt_b200_median_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample,
+                                              int64_t* sample_count_host, void* stream);
+
+/* core::KdTree::FindKNearestToPoints (core/KdTree.cpp:52-90; kernel/SearchKdTreeImpl.h:118-146, PLAIN
+ * strategy), brute force: indexed points are visited in ascending order, which fixes the slot order the kd-tree leaves to its
+ * traversal; sort_output != 0 orders each row by ascending distance. nearest_indices [Q,k] int32 (-1 where fewer than k points
+ * exist), nearest_distances [Q,k] f32 (may be NULL). k <= 8. */
+int nnrt_b200_find_k_nearest_to_points(const float* indexed_points, int32_t indexed_count, const float* query_points,
+                                       int64_t query_count, int32_t k, int32_t sort_output, int32_t* nearest_indices,
+                                       float* nearest_distances, void* stream);
+
+/* geometry::WarpField::RecomputeNodeCoverageWeights (geometry/WarpField.cpp:249-262): squared distance to the nearest other node
+ * (node_coverage itself for a single node). */
+int nnrt_b200_node_coverage_weights(const float* nodes, int32_t node_count, float node_coverage, float* node_coverage_weights,
+                                    void* stream);
+
+/* geometry::HierarchicalGraphWarpField::RebuildRegularizationLayers (geometry/HierarchicalGraphWarpField.cpp:74-195;
+ * kernel/HierarchicalGraphWarpFieldImpl.h:218-296 AdjacencyArrayToEdges). layer_decimation_radii_host [L]: entry i >= 1 is the
+ * caller's compute_layer_decimation_radius(i, node_coverage) (entry 0 unused: the finest layer holds every node).
+ * Outputs: node_indices [N] int64 (virtual -> original index, layers fine to coarse), layer_node_counts_host [L],
+ * edges [<= N * max_vertex_degree, 2] int32 in virtual indices (layer pairs coarse to fine, sources descending, each source's
+ * targets descending), edge_layer_indices [same count] int8 (layer of the targets), edge_count_host. max_vertex_degree <= 8.
+ * One stream synchronisation per layer beyond the first. Fails like the reference when a layer cannot be decimated. */
+int nnrt_b200_build_regularization_layers(const float* nodes, int32_t node_count, const float* layer_decimation_radii_host,
+                                          int32_t layer_count, int32_t max_vertex_degree, int64_t* node_indices,
+                                          int32_t* layer_node_counts_host, int32_t* edges, int8_t* edge_layer_indices,
+                                          int64_t* edge_count_host, void* stream);
+
 /* Per-stage device time of one iteration measured with CUDA events outside graph capture (ms):
  * [warp_vertices, face_raster, band_raster, assemble, build_system, stem_eliminate, corner_solve_update]. */
 int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,

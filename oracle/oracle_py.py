@@ -322,3 +322,65 @@ def fit_to_image(positions, normals, triangles, nodes, edges, arrow_base, anchor
     return dict(rotations=R, translations=t, hessian_diag=tr_H, negative_gradient=tr_g, deltas=tr_d,
                 pixel_faces=last_faces.reshape(height, width), residuals=last_res.reshape(height, width),
                 residual_mask=last_mask.reshape(height, width).astype(bool), stage_seconds=stage)
+
+
+# --- warp-field construction -----------------------------------------------------------------------
+def median_grid_subsample_3d_points(points, grid_cell_size):
+    """Indices (int64, bins in order of first occurrence) of the per-cell median points."""
+    points = _f32(points)
+    sample = np.empty(points.shape[0], np.int64)
+    lib().oracle_median_grid_subsample_3d_points.restype = C.c_int64
+    count = lib().oracle_median_grid_subsample_3d_points(_p(points), C.c_int64(points.shape[0]), C.c_float(grid_cell_size), _p(sample))
+    return sample[:count].copy()
+
+
+def find_k_nearest(indexed_points, query_points, k):
+    indexed_points, query_points = _f32(indexed_points), _f32(query_points)
+    idx = np.empty((query_points.shape[0], k), np.int32)
+    dist = np.empty((query_points.shape[0], k), np.float32)
+    lib().oracle_find_k_nearest(_p(indexed_points), C.c_int(indexed_points.shape[0]), _p(query_points), C.c_int64(query_points.shape[0]),
+                                C.c_int(k), _p(idx), _p(dist))
+    return idx, dist
+
+
+def node_coverage_weights(nodes, node_coverage):
+    nodes = _f32(nodes)
+    out = np.empty(nodes.shape[0], np.float32)
+    lib().oracle_node_coverage_weights(_p(nodes), C.c_int(nodes.shape[0]), C.c_float(node_coverage), _p(out))
+    return out
+
+
+def adjacency_array_to_edges(adjacency, source_indices, target_indices, flip_source_order):
+    adjacency, source_indices, target_indices = _i32(adjacency), _i32(source_indices), _i32(target_indices)
+    edges = np.empty((adjacency.size, 2), np.int32)
+    lib().oracle_adjacency_array_to_edges.restype = C.c_int64
+    count = lib().oracle_adjacency_array_to_edges(_p(adjacency), C.c_int64(adjacency.shape[0]), C.c_int(adjacency.shape[1]), _p(source_indices),
+                                                  _p(target_indices), C.c_int(int(flip_source_order)), _p(edges))
+    return edges[:count].copy()
+
+
+def layer_decimation_radii(node_coverage, layer_count, compute_layer_decimation_radius=None):
+    """radius(0) = node_coverage; radius(i) = compute_layer_decimation_radius(i, node_coverage), default (i + 1) * node_coverage in fp32
+    (cpp/geometry/HierarchicalGraphWarpField.h:46-47)."""
+    c = np.float32(node_coverage)
+    fn = compute_layer_decimation_radius or (lambda i, cov: np.float32(i + 1) * np.float32(cov))
+    return np.array([c] + [np.float32(fn(i, c)) for i in range(1, layer_count)], np.float32)
+
+
+def build_regularization_layers(nodes, node_coverage, layer_count, max_vertex_degree, compute_layer_decimation_radius=None):
+    """dict(node_indices [N] int64, layer_node_counts [L], edges [E,2] int32 (virtual indices), edge_layer_indices [E] int8,
+    layer_decimation_radii [L])."""
+    nodes = _f32(nodes)
+    n = nodes.shape[0]
+    radii = layer_decimation_radii(node_coverage, layer_count, compute_layer_decimation_radius)
+    node_indices = np.empty(n, np.int64)
+    counts = np.empty(layer_count, np.int32)
+    edges = np.empty((max(n * max_vertex_degree, 1), 2), np.int32)
+    eli = np.empty(max(n * max_vertex_degree, 1), np.int8)
+    lib().oracle_build_regularization_layers.restype = C.c_int64
+    e = lib().oracle_build_regularization_layers(_p(nodes), C.c_int(n), _p(radii), C.c_int(layer_count), C.c_int(max_vertex_degree),
+                                                 _p(node_indices), _p(counts), _p(edges), _p(eli))
+    if e < 0:
+        raise RuntimeError(f"Attempting to generate a coarser layer (layer {-e}) out of a finer layer of the same size, which is not possible.")
+    return dict(node_indices=node_indices, layer_node_counts=counts, edges=edges[:e].copy(), edge_layer_indices=eli[:e].copy(),
+                layer_decimation_radii=radii)

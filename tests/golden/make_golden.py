@@ -5,6 +5,8 @@ vectors) and sub-samples one of its binary fixtures, and stores them as numpy ar
   reference_kats.npz   inline vectors of cpp/tests/test_{anchor_computation,rodrigues,unproject_3d_points,linalg_cholesky,matmul3d}.cpp
   mesh_warp_219.npz    every 8th vertex of tests/test_data/mesh_warping/test_{input,gt}_mesh.ply + nodes/rotations/translations.npy
   oracle_fit_tinyr.npz one full GN iteration of the ORACLE on the seeded 'tinyr' scene (regression pin of the oracle itself)
+  warp_field_kats.npz  inline vectors of cpp/tests/test_sampling.cpp (median grid subsampling) and
+                       cpp/tests/test_graph_warp_field.cpp (HierarchicalGraphWarpField constructor: layers, edges, virtual order)
 """
 import os
 import re
@@ -34,6 +36,19 @@ def inline_tensor(cpp_text, name, occurrence=0):
     if "bool" in m.group(1):
         return np.array([1.0 if t == "true" else 0.0 for t in re.findall(r"true|false", body)])
     return np.array([float(t) for t in _NUM.findall(re.sub(r"(?<=[\d.])f\b", "", body))])
+
+
+def braces_after(cpp_text, name, occurrence=0):
+    """Numbers of the first `{ ... }` initialiser that follows the given occurrence of `name` (comments stripped)."""
+    text = re.sub(r"//[^\n]*", "", cpp_text)
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    start = [m.end() for m in re.finditer(r"\b" + re.escape(name) + r"\b", text)][occurrence]
+    i = text.index("{", start)
+    depth, j = 1, i + 1
+    while depth:
+        depth += {"{": 1, "}": -1}.get(text[j], 0)
+        j += 1
+    return np.array([float(t) for t in _NUM.findall(re.sub(r"(?<=[\d.])f\b", "", text[i + 1:j - 1]))])
 
 
 def read(path):
@@ -79,6 +94,28 @@ def main():
             pass
     np.savez_compressed(os.path.join(HERE, "reference_kats.npz"), **out)
     print("reference_kats.npz:", {k: v.shape for k, v in out.items()})
+
+    wf = {}
+    t = read("cpp/tests/test_sampling.cpp")
+    t = t[t.index("void TestGridMedianDownsampling"):]
+    wf["median/points"] = braces_after(t, "point_data").reshape(10, 3).astype(np.float32)
+    wf["median/cell_size"] = np.float32(1.0)
+    wf["median/required"] = np.array([2, 4])                    # REQUIRE(find(2)), REQUIRE(find(4))
+    wf["median/either"] = np.array([[6, 7], [8, 9]])            # REQUIRE(find(6) || find(7)), REQUIRE(find(8) || find(9))
+    t = read("cpp/tests/test_graph_warp_field.cpp")
+    t = t[t.index("void TestHierarchicalGraphWarpFieldConstructor"):]
+    wf["hgwf/nodes"] = braces_after(t, "node_data").reshape(33, 3).astype(np.float32)
+    wf["hgwf/node_coverage"] = np.float32(0.25)                 # hgwf(nodes, 0.25, false, 4, 0, FIXED_NODE_COVERAGE, 3, 4, 2^i * coverage)
+    wf["hgwf/layer_count"], wf["hgwf/max_vertex_degree"] = np.int32(3), np.int32(4)
+    for i in range(3):
+        wf[f"hgwf/layer_{i}"] = braces_after(t, f"ground_truth_layer_{i}").astype(np.int64)
+    wf["hgwf/edge_sources_virtual"] = braces_after(t, "edge_source_virtual_node_indices_gt").astype(np.int32)
+    wf["hgwf/edge_node_indices_sorted"] = braces_after(t, "edge_node_indices_gt").reshape(116, 2).astype(np.int64)
+    wf["hgwf/virtual_node_indices"] = braces_after(t, "virtual_node_indices_gt").astype(np.int64)
+    np.savez_compressed(os.path.join(HERE, "warp_field_kats.npz"), **wf)
+    print("warp_field_kats.npz:", {k: v.shape for k, v in wf.items()})
+    if "--warp-field-only" in sys.argv:
+        return
 
     d = os.path.join(REF, "tests/test_data/mesh_warping")
     vin, nin = read_ply_vertices(os.path.join(d, "test_input_mesh.ply"))

@@ -91,7 +91,7 @@ def test_block_diagonal_and_precondition(nnrt, oracle):
 def _gpu_fit(nnrt, s, iterations, **opts):
     G = nnrt.geometry
     has_edges = len(s["edges"]) > 0
-    wf = G.HierarchicalGraphWarpField(s["nodes"], s["edges"] if has_edges else None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+    wf = G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"] if has_edges else None, s["arrow_base"], s["node_coverage"], False, 4, 0,
                                       G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
     args = dict(max_iteration_count=iterations, preconditioning_dampening_factor=s["lm_factor"], arap_term_weight=s["arap_term_weight"])
     args.update(opts)
@@ -135,7 +135,7 @@ def test_ten_consecutive_iterations_parity(nnrt, oracle):
     iteration): deltas within 1e-3 relative (BASELINE.json), face indices within the reference's own 20-pixel tolerance."""
     s = scene_with_target(oracle, "tinyr", 120, 160)
     G = nnrt.geometry
-    wf = G.HierarchicalGraphWarpField(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
+    wf = G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
                                       G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
     fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=1, preconditioning_dampening_factor=s["lm_factor"],
                                                         arap_term_weight=s["arap_term_weight"])
@@ -203,7 +203,7 @@ def test_iteration_mode_sequence(nnrt, oracle):
     A = nnrt.alignment
     modes = [A.IterationMode.ALL, A.IterationMode.TRANSLATION_ONLY, A.IterationMode.ROTATION_ONLY]
     G = nnrt.geometry
-    wf = G.HierarchicalGraphWarpField(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+    wf = G.HierarchicalGraphWarpField.from_graph(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
                                       G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
     mesh = (s["positions"], s["normals"], s["triangles"])
     for it, mode in enumerate(modes):
@@ -224,7 +224,7 @@ def test_iteration_mode_sequence(nnrt, oracle):
         np.testing.assert_allclose(_np(wf.node_translations), ref["translations"], rtol=1e-3, atol=1e-6)
         np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
     # the same sequence inside one captured graph: three iterations, modes cycled by iteration index
-    wf2 = G.HierarchicalGraphWarpField(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+    wf2 = G.HierarchicalGraphWarpField.from_graph(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
                                        G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
     fitter = A.DeformableMeshToImageFitter(max_iteration_count=3, iteration_mode_sequence=modes,
                                            preconditioning_dampening_factor=s["lm_factor"], arap_term_weight=s["arap_term_weight"])
@@ -251,7 +251,7 @@ def test_status_flags_do_not_leak_into_the_next_fit(nnrt, oracle):
     fitter on a proper observation reports success."""
     s = scene_with_target(oracle, "C1", 120, 160)
     G = nnrt.geometry
-    wf = G.HierarchicalGraphWarpField(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+    wf = G.HierarchicalGraphWarpField.from_graph(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
                                       G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
     fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=1, preconditioning_dampening_factor=0.0)
     mesh = (s["positions"], s["normals"], s["triangles"])
@@ -260,7 +260,7 @@ def test_status_flags_do_not_leak_into_the_next_fit(nnrt, oracle):
     fitter.fit_to_image(wf, mesh, None, s["reference_points"], empty_mask, s["K"], np.eye(4), (s["height"], s["width"]), **call)
     with pytest.raises(RuntimeError, match="positive definite"):
         fitter.check_status()
-    wf2 = G.HierarchicalGraphWarpField(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+    wf2 = G.HierarchicalGraphWarpField.from_graph(s["nodes"], None, s["arrow_base"], s["node_coverage"], False, 4, 0,
                                        G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
     fitter.fit_to_image(wf2, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]), **call)
     fitter.check_status()

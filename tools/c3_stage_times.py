@@ -34,7 +34,7 @@ mesh = (torch.tensor(pos, device=dev), torch.tensor(nrm, device=dev), torch.tens
 
 
 def field():
-    return G.HierarchicalGraphWarpField(nodes, edges, base, coverage, False, 4, 0, G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4,
+    return G.HierarchicalGraphWarpField.from_graph(nodes, edges, base, coverage, False, 4, 0, G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4,
                                         np.zeros(max(E, N), np.int8), np.array([0.015, 0.03], np.float32))
 
 

@@ -14,7 +14,7 @@ for config in ("C1", "C1e", "C2r"):
     N, E = s["nodes"].shape[0], len(s["edges"])
 
     def field():
-        return G.HierarchicalGraphWarpField(s["nodes"], s["edges"] if E else None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+        return G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"] if E else None, s["arrow_base"], s["node_coverage"], False, 4, 0,
                                             G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
     wf = field()
     anchors, weights = wf.precompute_anchors_and_weights(mesh)

@@ -13,7 +13,7 @@ H, W = (480, 640) if len(sys.argv) < 4 else (int(sys.argv[2]), int(sys.argv[3]))
 s = scene_with_target(oracle, cfg, H, W)
 G = nnrt.geometry
 for iters in (1, 2, 3):
-    wf = G.HierarchicalGraphWarpField(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
+    wf = G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
                                       G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
     fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=iters, preconditioning_dampening_factor=s["lm_factor"],
                                                         arap_term_weight=s["arap_term_weight"])

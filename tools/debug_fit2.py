@@ -12,7 +12,7 @@ H, W = (480, 640) if len(sys.argv) < 4 else (int(sys.argv[2]), int(sys.argv[3]))
 s = scene_with_target(oracle, cfg, H, W)
 G = nnrt.geometry
 def field():
-    return G.HierarchicalGraphWarpField(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
+    return G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
                                         G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
 def fit(wf, fitter):
     fitter.fit_to_image(wf, (s["positions"], s["normals"], s["triangles"]), None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4),

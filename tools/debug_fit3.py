@@ -11,7 +11,7 @@ s = scene_with_target(oracle, "C2r", 480, 640)
 G = nnrt.geometry
 f = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=1, preconditioning_dampening_factor=s["lm_factor"], arap_term_weight=s["arap_term_weight"])
 for trial in range(6):
-    wf = G.HierarchicalGraphWarpField(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
+    wf = G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
                                       G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
     for it in range(10):
         f.fit_to_image(wf, (s["positions"], s["normals"], s["triangles"]), None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4),

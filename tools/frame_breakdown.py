@@ -12,7 +12,7 @@ G = nnrt.geometry
 K, ext = s["K"], np.eye(4)
 mesh = (torch.tensor(s["positions"], device=dev), torch.tensor(s["normals"], device=dev), torch.tensor(s["triangles"], device=dev))
 N = s["nodes"].shape[0]
-wf = G.HierarchicalGraphWarpField(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
+wf = G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
                                   G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
 anchors, weights = wf.precompute_anchors_and_weights(mesh)
 R, t = bench.scaled_motion(s, s["frame_scales"][0])

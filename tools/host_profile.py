@@ -9,7 +9,7 @@ s = bench.make_bench_scene()
 G = nnrt.geometry
 K, ext = s["K"], np.eye(4)
 mesh = (torch.tensor(s["positions"], device=dev), torch.tensor(s["normals"], device=dev), torch.tensor(s["triangles"], device=dev))
-wf = G.HierarchicalGraphWarpField(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
+wf = G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
                                   G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
 depth = torch.rand((480, 640), device=dev) * 0 + 0.6
 fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=1, preconditioning_dampening_factor=1.0, arap_term_weight=200.0)
