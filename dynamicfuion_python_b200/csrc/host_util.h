@@ -46,6 +46,27 @@ struct SharedMemoryOptIn {
 	}
 };
 
+// Stream-ordered scratch for the stage-level entry points. The device's default memory pool hands its memory back to the driver at
+// every synchronisation unless a release threshold is set, which makes each call pay for mapping fresh pages (measured: ~0.3 ms per
+// call of the warp-field construction); the threshold is raised once per device so freed scratch stays in the pool.
+template<typename T>
+inline cudaError_t scratch_malloc_async(T** pointer, size_t bytes, cudaStream_t stream) {
+	static std::atomic<unsigned long long> retained{0};
+	int device = 0;
+	cudaError_t err = cudaGetDevice(&device);
+	if (err != cudaSuccess) return err;
+	const unsigned long long bit = 1ull << (device & 63);
+	if (!(retained.load(std::memory_order_acquire) & bit)) {
+		cudaMemPool_t pool;
+		if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+			unsigned long long threshold = ~0ull;
+			cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+		}
+		retained.fetch_or(bit, std::memory_order_release);
+	}
+	return cudaMallocAsync((void**) pointer, bytes, stream);
+}
+
 inline unsigned blocks_for(int64_t n, int threads) { return (unsigned) ((n + threads - 1) / threads); }
 
 inline Intrinsics intrinsics_from_host(const double* K) { return Intrinsics{(float) K[0], (float) K[4], (float) K[2], (float) K[5]}; }

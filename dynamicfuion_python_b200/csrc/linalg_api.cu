@@ -108,7 +108,7 @@ static int prepare_explicit(ExplicitArrowhead& ws, const float* diag, int N, int
 	             sz_y = al(sizeof(float) * (size_t) (base + 1) * 6), sz_x = al(sizeof(float) * (size_t) (W + 1) * 36), sz_s = al(sizeof(float) * corner_schur_floats(nc)),
 	             sz_r = al(sizeof(float) * (n + 1)), sz_flags = 256;
 	const size_t total = sz_off + 2 * sz_blk + sz_dinv + sz_y + sz_x + sz_s + sz_r + sz_flags;
-	NNRT_CUDA(cudaMallocAsync(&ws.buffer, total, s));
+	NNRT_CUDA(scratch_malloc_async(&ws.buffer, total, s));
 	char* p = ws.buffer;
 	int* d_off = (int*) p; p += sz_off;
 	int* d_blk = (int*) p; p += sz_blk;
@@ -183,7 +183,7 @@ extern "C" int nnrt_b200_arrowhead_schur_complement(const float* diagonal_blocks
 	auto s = (cudaStream_t) stream;
 	const int64_t n = (int64_t) (diagonal_block_count - arrow_base) * 6;
 	float* zero_rhs = nullptr;
-	NNRT_CUDA(cudaMallocAsync(&zero_rhs, sizeof(float) * (size_t) diagonal_block_count * 6, s));
+	NNRT_CUDA(scratch_malloc_async(&zero_rhs, sizeof(float) * (size_t) diagonal_block_count * 6, s));
 	NNRT_CUDA(cudaMemsetAsync(zero_rhs, 0, sizeof(float) * (size_t) diagonal_block_count * 6, s));
 	ExplicitArrowhead ws;
 	rc = prepare_explicit(ws, diagonal_blocks, diagonal_block_count, arrow_base, upper_wing_blocks, upper_wing_coordinates, upper_wing_count,

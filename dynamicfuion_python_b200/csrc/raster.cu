@@ -225,9 +225,9 @@ extern "C" int nnrt_b200_rasterize_ndc_triangles(const float* face_vertices_ndc,
 	unsigned long long* keys = nullptr;
 	BandItem* queue = nullptr;
 	int* counters = nullptr;
-	NNRT_CUDA(cudaMallocAsync(&keys, sizeof(unsigned long long) * px * 2, s));
-	NNRT_CUDA(cudaMallocAsync(&queue, sizeof(BandItem) * queue_capacity, s));
-	NNRT_CUDA(cudaMallocAsync(&counters, sizeof(int) * 2, s));
+	NNRT_CUDA(scratch_malloc_async(&keys, sizeof(unsigned long long) * px * 2, s));
+	NNRT_CUDA(scratch_malloc_async(&queue, sizeof(BandItem) * queue_capacity, s));
+	NNRT_CUDA(scratch_malloc_async(&counters, sizeof(int) * 2, s));
 	unsigned long long* cur = keys;
 	unsigned long long* prev = keys + px;
 	int overflow_host = 0;

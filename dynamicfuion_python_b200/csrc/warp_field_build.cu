@@ -97,10 +97,37 @@ __global__ void __launch_bounds__(kThreads) scan_apply_kernel(const int* in, int
 	}
 }
 
+// up to kSmallScan items (warp-field sizes): one CTA, one launch
+constexpr int kSmallScan = 1024 * kScanItems;
+__global__ void __launch_bounds__(1024) scan_small_kernel(const int* in, int* out, int n) {
+	__shared__ int warp_totals[32];
+	const int base = threadIdx.x * kScanItems;
+	int items[kScanItems];
+	int sum = 0;
+#pragma unroll
+	for (int k = 0; k < kScanItems; k++) {
+		items[k] = base + k < n ? in[base + k] : 0;
+		sum += items[k];
+	}
+	int total;
+	int running = block_exclusive_scan(sum, warp_totals, &total);
+#pragma unroll
+	for (int k = 0; k < kScanItems; k++) {
+		if (base + k < n) out[base + k] = running;
+		running += items[k];
+	}
+	if (threadIdx.x == 0) out[n] = total;
+}
+
 // scratch: ceil(n / kScanTile) ints; out needs n + 1 ints
 int exclusive_scan(const int* in, int* out, int64_t n, int* tile_scratch, cudaStream_t s) {
 	const int tiles = (int) ((n + kScanTile - 1) / kScanTile);
 	if (tiles == 0) { NNRT_CUDA(cudaMemsetAsync(out, 0, sizeof(int), s)); return kOk; }
+	if (n <= kSmallScan) {
+		scan_small_kernel<<<1, 1024, 0, s>>>(in, out, (int) n);
+		NNRT_LAUNCH_CHECK();
+		return kOk;
+	}
 	scan_tile_sums_kernel<<<tiles, kThreads, 0, s>>>(in, n, tile_scratch);
 	scan_tile_offsets_kernel<<<1, 1024, 0, s>>>(tile_scratch, tiles, out + n);
 	scan_apply_kernel<<<tiles, kThreads, 0, s>>>(in, out, n, tile_scratch);
@@ -218,17 +245,18 @@ struct SubsampleWorkspace {
 		const size_t ints = (size_t) n + 2;
 		table_size = table_for(n);
 		auto take = [&p](size_t b) { char* r = p; p += align(b); return r; };
+		// [owner | best] are filled with 0xFF and [bin_counts | bin_fill] with zeros by one memset each (sizes are multiples of 256 bytes)
 		owner = (int*) take(sizeof(int) * table_size);
+		best = (unsigned long long*) take(sizeof(unsigned long long) * ints);
 		slot_min = (int*) take(sizeof(int) * table_size);
+		bin_counts = (int*) take(sizeof(int) * ints);
+		bin_fill = (int*) take(sizeof(int) * ints);
 		slot_of_point = (int*) take(sizeof(int) * ints);
 		rank = (int*) take(sizeof(int) * ints);
 		bin_of_point = (int*) take(sizeof(int) * ints);
-		bin_counts = (int*) take(sizeof(int) * ints);
-		bin_fill = (int*) take(sizeof(int) * ints);
 		members = (int*) take(sizeof(int) * ints);
 		sorted_members = (int*) take(sizeof(int) * ints);
 		scan_scratch = (int*) take(sizeof(int) * (size_t) scan_scratch_ints(n + 1));
-		best = (unsigned long long*) take(sizeof(unsigned long long) * ints);
 	}
 };
 
@@ -236,11 +264,10 @@ struct SubsampleWorkspace {
 // bin count sizes the last launch and the result).
 int median_subsample(const float* points, int64_t n, float cell_size, SubsampleWorkspace& w, int64_t* sample, int* bin_count_host, cudaStream_t s) {
 	const unsigned blocks = blocks_for(n, kThreads);
-	NNRT_CUDA(cudaMemsetAsync(w.owner, 0xFF, sizeof(int) * w.table_size, s));
+	const size_t ints = (size_t) n + 2;
+	NNRT_CUDA(cudaMemsetAsync(w.owner, 0xFF, SubsampleWorkspace::align(sizeof(int) * w.table_size) + sizeof(unsigned long long) * ints, s));  // owner, best
 	NNRT_CUDA(cudaMemsetAsync(w.slot_min, 0x7F, sizeof(int) * w.table_size, s));
-	NNRT_CUDA(cudaMemsetAsync(w.bin_counts, 0, sizeof(int) * (size_t) (n + 1), s));
-	NNRT_CUDA(cudaMemsetAsync(w.bin_fill, 0, sizeof(int) * (size_t) (n + 1), s));
-	NNRT_CUDA(cudaMemsetAsync(w.best, 0xFF, sizeof(unsigned long long) * (size_t) (n + 1), s));
+	NNRT_CUDA(cudaMemsetAsync(w.bin_counts, 0, SubsampleWorkspace::align(sizeof(int) * ints) + sizeof(int) * ints, s));  // bin_counts, bin_fill
 	bin_insert_kernel<<<blocks, kThreads, 0, s>>>(points, n, cell_size, w.owner, w.slot_min, w.table_size - 1, w.slot_of_point);
 	flag_first_points_kernel<<<blocks, kThreads, 0, s>>>(w.slot_of_point, w.slot_min, n, w.rank);
 	NNRT_LAUNCH_CHECK();
@@ -330,34 +357,87 @@ __global__ void __launch_bounds__(kThreads) find_k_nearest_kernel(const float* _
 	}
 }
 
-// One finer-layer node per thread: K nearest coarser nodes, indices sorted descending, written straight into the edge list
-// (geometry/kernel/HierarchicalGraphWarpFieldImpl.h:218-296 with flip_source_order: row S-1-i; every row holds the same number
-// min(K, coarser count) of valid targets, so dropping the -1 slots leaves a dense [S, valid] table and needs no compaction pass).
+// One finer-layer node per WARP: every lane keeps the K nearest of its stride of the coarser nodes (same replace-current-maximum rule,
+// indices ascending within a lane), then K rounds of a warp-wide minimum over (distance, index) pick the K nearest overall. That set
+// equals the sequential rule's: a later candidate replaces only when strictly closer, so ties go to the smaller index. The set is then
+// sorted by index, largest first, and written straight into the edge list (geometry/kernel/HierarchicalGraphWarpFieldImpl.h:218-296
+// with flip_source_order: row S-1-i; every row holds the same number min(K, coarser count) of valid targets, so dropping the -1 slots
+// leaves a dense [S, valid] table and needs no compaction pass). A thread per node left 126 of 148 SMs idle at 5000 nodes.
+constexpr int kEdgeWarps = kThreads / 32;
+
 template<int K>
 __global__ void __launch_bounds__(kThreads) layer_edges_kernel(const float* __restrict__ coarser, int coarser_count, const float* __restrict__ finer,
                                                                int finer_count, int first_virtual_finer, int first_virtual_coarser, int layer,
                                                                int32_t* __restrict__ edges, int8_t* __restrict__ edge_layers) {
 	__shared__ float4 tile[kKnnTile];
-	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	const int lane = threadIdx.x & 31;
+	const int i = blockIdx.x * kEdgeWarps + (threadIdx.x >> 5);
 	const bool active = i < finer_count;
 	float query[3] = {0.f, 0.f, 0.f};
 	if (active) { query[0] = finer[i * 3]; query[1] = finer[i * 3 + 1]; query[2] = finer[i * 3 + 2]; }
 	int idx[K];
 	float dist[K];
-	k_nearest<K>(coarser, coarser_count, query, active, tile, kKnnTile, idx, dist);
-	if (!active) return;
+#pragma unroll
+	for (int a = 0; a < K; a++) { idx[a] = -1; dist[a] = INFINITY; }
+	int max_at = 0;
+	float max_distance = INFINITY;
+	for (int base = 0; base < coarser_count; base += kKnnTile) {
+		const int count = min(kKnnTile, coarser_count - base);
+		__syncthreads();
+		for (int k = threadIdx.x; k < count; k += blockDim.x)
+			tile[k] = make_float4(coarser[(base + k) * 3], coarser[(base + k) * 3 + 1], coarser[(base + k) * 3 + 2], 0.f);
+		__syncthreads();
+		if (!active) continue;
+		for (int k = lane; k < count; k += 32) {
+			const float4 g = tile[k];
+			const float dx = g.x - query[0], dy = g.y - query[1], dz = g.z - query[2];
+			const float d = sqrtf(sum3(dx * dx, dy * dy, dz * dz));
+			if (max_distance > d) {
+#pragma unroll
+				for (int a = 0; a < K; a++)
+					if (a == max_at) { dist[a] = d; idx[a] = base + k; }
+				max_at = 0;
+				max_distance = dist[0];
+#pragma unroll
+				for (int a = 1; a < K; a++)
+					if (dist[a] > max_distance) { max_at = a; max_distance = dist[a]; }
+			}
+		}
+	}
+	if (!active) return;  // whole warps leave together
+	// (distance bits, index) keys order like (distance, index): distances are non-negative, empty slots (inf, -1) sort last
+	unsigned long long keys[K];
+#pragma unroll
+	for (int a = 0; a < K; a++) keys[a] = ((unsigned long long) __float_as_uint(dist[a]) << 32) | (unsigned) idx[a];
+	int chosen[K];
+#pragma unroll
+	for (int round = 0; round < K; round++) {
+		unsigned long long mine = keys[0];
+#pragma unroll
+		for (int a = 1; a < K; a++) mine = min(mine, keys[a]);
+		unsigned long long best = mine;
+#pragma unroll
+		for (int offset = 16; offset > 0; offset >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, offset));
+		chosen[round] = (int) (unsigned) (best & 0xffffffffull);  // -1 when fewer than K coarser nodes exist
+		if (mine == best && (unsigned) (best & 0xffffffffull) != 0xffffffffu) {  // indices are unique: exactly one lane owns the key
+#pragma unroll
+			for (int a = 0; a < K; a++)
+				if (keys[a] == best) keys[a] = ~0ull;
+		}
+	}
+	if (lane != 0) return;
 #pragma unroll
 	for (int a = 1; a < K; a++)  // insertion sort, descending (-1 sinks to the end)
 #pragma unroll
 		for (int b = a; b > 0; b--)
-			if (idx[b] > idx[b - 1]) { const int t = idx[b]; idx[b] = idx[b - 1]; idx[b - 1] = t; }
+			if (chosen[b] > chosen[b - 1]) { const int t = chosen[b]; chosen[b] = chosen[b - 1]; chosen[b - 1] = t; }
 	const int valid = min(K, coarser_count);
 	const int64_t row = (int64_t) (finer_count - 1 - i) * valid;
 #pragma unroll
 	for (int a = 0; a < K; a++) {
 		if (a >= valid) break;
 		edges[(row + a) * 2] = first_virtual_finer + i;
-		edges[(row + a) * 2 + 1] = first_virtual_coarser + idx[a];
+		edges[(row + a) * 2 + 1] = first_virtual_coarser + chosen[a];
 		edge_layers[row + a] = (int8_t) layer;
 	}
 }
@@ -450,7 +530,7 @@ extern "C" int nnrt_b200_median_grid_subsample_3d_points(const float* points, in
 	NNRT_CHECK_ARG(grid_cell_size > 0.f, "grid_cell_size must be positive, got %f", grid_cell_size);
 	cudaStream_t s = (cudaStream_t) stream;
 	char* buffer = nullptr;
-	NNRT_CUDA(cudaMallocAsync(&buffer, SubsampleWorkspace::bytes(point_count), s));
+	NNRT_CUDA(scratch_malloc_async(&buffer, SubsampleWorkspace::bytes(point_count), s));
 	SubsampleWorkspace w;
 	w.carve(buffer, point_count);
 	int bins = 0;
@@ -505,7 +585,7 @@ extern "C" int nnrt_b200_build_regularization_layers(const float* nodes, int32_t
 	const size_t flag_bytes = SubsampleWorkspace::align(sizeof(int) * ((size_t) n + 2));
 	const size_t total = (size_t) (2 * L) * (idx_bytes + pos_bytes) + flag_bytes + idx_bytes + SubsampleWorkspace::bytes(n);
 	char* buffer = nullptr;
-	NNRT_CUDA(cudaMallocAsync(&buffer, total, s));
+	NNRT_CUDA(scratch_malloc_async(&buffer, total, s));
 	char* p = buffer;
 	std::vector<int64_t*> layer_indices(2 * L);
 	std::vector<float*> layer_positions(2 * L);
@@ -580,7 +660,7 @@ extern "C" int nnrt_b200_build_regularization_layers(const float* nodes, int32_t
 		int32_t* edges_out = edges + edge_count * 2;
 		int8_t* layers_out = edge_layer_indices + edge_count;
 		dispatch_k(max_vertex_degree, [&](auto K) {
-			layer_edges_kernel<decltype(K)::value><<<blocks_for(finer_count, kThreads), kThreads, 0, s>>>(coarser_positions, coarser_count, finer_positions, finer_count,
+			layer_edges_kernel<decltype(K)::value><<<blocks_for(finer_count, kEdgeWarps), kThreads, 0, s>>>(coarser_positions, coarser_count, finer_positions, finer_count,
 			                                                                                            first_finer, first_coarser, l, edges_out, layers_out);
 		});
 		NNRT_LAYERS_CUDA(cudaGetLastError());

@@ -178,7 +178,7 @@ class HierarchicalGraphWarpField(GraphWarpField):
         self.layer_node_counts = list(counts)
         self.node_indices = node_indices
         original_nodes = self.nodes
-        self._set_order(node_indices)
+        self._set_order(node_indices, identity=layer_count == 1)
         self.nodes = original_nodes[node_indices].contiguous()
         if self.node_coverage_weights is not None:
             self.node_coverage_weights = self.node_coverage_weights[node_indices].contiguous()
@@ -201,12 +201,15 @@ class HierarchicalGraphWarpField(GraphWarpField):
                                                                   self.nodes[first:first + count], layer_edges))
             first += count
 
-    def _set_order(self, node_indices):
-        n = node_indices.shape[0]
-        identity = torch.arange(n, device=node_indices.device)
-        self._identity_order = bool(torch.equal(node_indices, identity))
-        self._original_to_virtual = torch.empty_like(node_indices)
-        self._original_to_virtual[node_indices] = identity
+    def _set_order(self, node_indices, identity):
+        """`identity`: the virtual order is the original order (one layer, or an explicit graph); with more layers the sampled nodes
+        move behind the finer layer and the accessors gather."""
+        self._identity_order = bool(identity)
+        if identity:
+            self._original_to_virtual = node_indices
+        else:
+            self._original_to_virtual = torch.empty_like(node_indices)
+            self._original_to_virtual[node_indices] = torch.arange(node_indices.shape[0], device=node_indices.device)
 
     @classmethod
     def from_graph(cls, nodes, edges=None, first_layer_node_count=None, node_coverage=0.05, threshold_nodes_by_distance=False,
@@ -229,7 +232,7 @@ class HierarchicalGraphWarpField(GraphWarpField):
             layer_decimation_radii = [self.node_coverage * (i + 1) for i in range(2)]  # radius(i) = (i+1) * node_coverage
         self.layer_decimation_radii = T.cuda(torch.as_tensor(layer_decimation_radii, dtype=torch.float32), torch.float32)
         self.node_indices = torch.arange(n, device=self.nodes.device)
-        self._set_order(self.node_indices)
+        self._set_order(self.node_indices, identity=True)
         self.layer_node_counts = [self.first_layer_node_count, n - self.first_layer_node_count] if self.first_layer_node_count < n else [n]
         self.regularization_layers = None
         return self
