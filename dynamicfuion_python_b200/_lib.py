@@ -31,6 +31,10 @@ _SIGNATURES = {
     "nnrt_b200_find_k_nearest_to_points": (C.c_int, [P, I32, P, I64, I32, I32, P, P, P]),
     "nnrt_b200_node_coverage_weights": (C.c_int, [P, I32, F32, P, P]),
     "nnrt_b200_build_regularization_layers": (C.c_int, [P, I32, P, I32, I32, P, P, P, P, P, P]),
+    "nnrt_b200_compute_triangle_normals": (C.c_int, [P, I64, P, I64, I32, P, P]),
+    "nnrt_b200_compute_vertex_normals": (C.c_int, [P, I64, P, I64, I32, P, P]),
+    "nnrt_b200_normalize_vectors_3d": (C.c_int, [P, I64, P]),
+    "nnrt_b200_compute_ordered_point_cloud_normals": (C.c_int, [P, I32, I32, P, P]),
     "nnrt_b200_fitter_default_options": (None, [P]),
     "nnrt_b200_fitter_create": (C.c_int, [P, I64, I64, I32, I64, I32, I32, I32, P]),
     "nnrt_b200_fitter_destroy": (None, [P]),

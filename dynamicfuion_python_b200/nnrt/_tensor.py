@@ -74,16 +74,22 @@ class MeshView:
 
     def __init__(self, mesh):
         pos = nrm = tri = None
+        self.triangle_normals = None
         if isinstance(mesh, MeshView):
             pos, nrm, tri = mesh.positions, mesh.normals, mesh.triangles
+            self.triangle_normals = mesh.triangle_normals
         elif isinstance(mesh, (tuple, list)):
             pos, nrm, tri = (list(mesh) + [None, None])[:3]
         elif isinstance(mesh, dict):
             pos, nrm, tri = mesh.get("positions"), mesh.get("normals"), mesh.get("triangles", mesh.get("indices"))
+            if mesh.get("triangle_normals") is not None:
+                self.triangle_normals = cuda(mesh["triangle_normals"], torch.float32)
         elif hasattr(mesh, "vertex") and hasattr(mesh, "triangle"):
             pos = mesh.vertex["positions"]
             nrm = mesh.vertex["normals"] if "normals" in mesh.vertex else None
             tri = mesh.triangle["indices"] if "indices" in mesh.triangle else None
+            if "normals" in mesh.triangle:
+                self.triangle_normals = cuda(mesh.triangle["normals"], torch.float32)
         else:
             raise RuntimeError("mesh must be an Open3D t.geometry.TriangleMesh-like object, a dict or a (positions, normals, triangles) tuple")
         if pos is None:
@@ -94,7 +100,7 @@ class MeshView:
 
     def with_vertices(self, positions, normals):
         out = MeshView.__new__(MeshView)
-        out.positions, out.normals, out.triangles = positions, normals, self.triangles
+        out.positions, out.normals, out.triangles, out.triangle_normals = positions, normals, self.triangles, None
         return out
 
     # minimal Open3D-like accessors so results can be consumed the same way
@@ -107,4 +113,24 @@ class MeshView:
 
     @property
     def triangle(self):
-        return {} if self.triangles is None else {"indices": self.triangles}
+        d = {} if self.triangles is None else {"indices": self.triangles}
+        if self.triangle_normals is not None:
+            d["normals"] = self.triangle_normals
+        return d
+
+
+def store_mesh_attribute(mesh, group, name, value):
+    """Writes a computed attribute back into the caller's mesh the way the reference's in-place operations do: a MeshView attribute,
+    a dict key, or `mesh.vertex[name]` / `mesh.triangle[name]` of an Open3D-like object (converted through DLPack when Open3D is
+    importable). Tuples are immutable: the caller uses the returned tensor."""
+    if isinstance(mesh, MeshView):
+        setattr(mesh, "normals" if group == "vertex" else "triangle_normals", value)
+    elif isinstance(mesh, dict):
+        mesh["normals" if group == "vertex" else "triangle_normals"] = value
+    elif hasattr(mesh, group) and not isinstance(mesh, (tuple, list)):
+        try:
+            import open3d
+            value = open3d.core.Tensor.from_dlpack(torch.utils.dlpack.to_dlpack(value))
+        except ImportError:
+            pass
+        getattr(mesh, group)[name] = value

@@ -143,3 +143,48 @@ def median_grid_subsample_3d_points(points, grid_cell_size):
     count = C.c_int64()
     T.call("nnrt_b200_median_grid_subsample_3d_points", T.ptr(pts), pts.shape[0], float(grid_cell_size), T.ptr(sample), C.byref(count), T.stream())
     return sample[:count.value]
+
+
+def compute_triangle_normals(mesh, normalized=True):
+    """ComputeTriangleNormals (cpp/geometry/functional/NormalsOperations.cpp:36-46): sets the mesh's triangle normals (where the mesh
+    argument is mutable) and returns them, [F,3] f32."""
+    view = T.MeshView(mesh)
+    if view.triangles is None:
+        raise RuntimeError("Mesh needs to have both vertex positions and triangle indices to compute triangle normals. "
+                           "Vertex positions: present. Triangle indices: absent.")
+    normals = T.empty((view.triangles.shape[0], 3), torch.float32)
+    T.call("nnrt_b200_compute_triangle_normals", T.ptr(view.positions), view.positions.shape[0], T.ptr(view.triangles), view.triangles.shape[0],
+           int(bool(normalized)), T.ptr(normals), T.stream())
+    T.store_mesh_attribute(mesh, "triangle", "normals", normals)
+    return normals
+
+
+def compute_vertex_normals(mesh, normalized=True):
+    """ComputeVertexNormals (cpp/geometry/functional/NormalsOperations.cpp:52-67): uses the mesh's triangle normals if it has them,
+    otherwise computes (and stores) un-normalised ones; sets the mesh's vertex normals and returns them, [V,3] f32."""
+    view = T.MeshView(mesh)
+    if view.triangles is None:
+        raise RuntimeError("Mesh needs to have both vertex positions and triangle indices to compute triangle normals. "
+                           "Vertex positions: present. Triangle indices: absent.")
+    triangle_normals = view.triangle_normals
+    if triangle_normals is None:
+        triangle_normals = compute_triangle_normals(mesh, False)
+    normals = T.empty((view.positions.shape[0], 3), torch.float32)
+    T.call("nnrt_b200_compute_vertex_normals", T.ptr(view.triangles), view.triangles.shape[0], T.ptr(triangle_normals), view.positions.shape[0],
+           int(bool(normalized)), T.ptr(normals), T.stream())
+    T.store_mesh_attribute(mesh, "vertex", "normals", normals)
+    return normals
+
+
+def compute_ordered_point_cloud_normals(point_cloud, source_image_size):
+    """ComputeOrderedPointCloudNormals (cpp/geometry/functional/NormalsOperations.cpp:73-93) -> normals [H*W,3] f32."""
+    if len(source_image_size) != 2:
+        raise RuntimeError(f"Source image size must have two dimensions. Got {len(source_image_size)}.")
+    pts = point_cloud.point["positions"] if hasattr(point_cloud, "point") else point_cloud
+    pts = T.cuda(pts, torch.float32).reshape(-1, 3)
+    h, w = int(source_image_size[0]), int(source_image_size[1])
+    if pts.shape[0] != h * w:
+        raise RuntimeError(f"Point cloud point count (got {pts.shape[0]}) must equal the multiple of dimensions (got {h} * {w} = {h * w}).")
+    normals = T.empty((h * w, 3), torch.float32)
+    T.call("nnrt_b200_compute_ordered_point_cloud_normals", T.ptr(pts), h, w, T.ptr(normals), T.stream())
+    return normals

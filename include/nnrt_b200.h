@@ -238,6 +238,25 @@ int nnrt_b200_build_regularization_layers(const float* nodes, int32_t node_count
                                           int32_t* layer_node_counts_host, int32_t* edges, int8_t* edge_layer_indices,
                                           int64_t* edge_count_host, void* stream);
 
+/* ---- Normals (nnrt.geometry.functional.compute_*_normals, pybind/geometry/functional/functional.cpp:112-114) ---- */
+
+/* geometry::ComputeTriangleNormals (geometry/functional/NormalsOperations.cpp:36-46; kernel/NormalsOperationsImpl.h:38-93):
+ * (v1 - v0) x (v2 - v0) per face, normalised if `normalized` (a NaN result becomes (0, 0, 1), as in the reference).
+ * triangles [F,3] int64, triangle_normals [F,3] f32. */
+int nnrt_b200_compute_triangle_normals(const float* vertex_positions, int64_t vertex_count, const int64_t* triangles,
+                                       int64_t face_count, int32_t normalized, float* triangle_normals, void* stream);
+/* geometry::ComputeVertexNormals (NormalsOperations.cpp:52-67; kernel/NormalsOperationsImpl.h:96-165): per vertex, the sum of the
+ * given normals of the triangles referencing it, normalised if `normalized`. The reference adds with float atomics (order depends on
+ * scheduling); here the addends are taken in ascending face order, which is its single-thread CPU result. */
+int nnrt_b200_compute_vertex_normals(const int64_t* triangles, int64_t face_count, const float* triangle_normals, int64_t vertex_count,
+                                     int32_t normalized, float* vertex_normals, void* stream);
+/* geometry::NormalizeVectors3d (NormalsOperations.cpp:48-50), in place. */
+int nnrt_b200_normalize_vectors_3d(float* vectors, int64_t count, void* stream);
+/* geometry::ComputeOrderedPointCloudNormals (NormalsOperations.cpp:73-93; kernel/NormalsOperationsImpl.h:172-214): central
+ * differences over the source image grid, zero on the border, flipped towards the camera (z <= 0). */
+int nnrt_b200_compute_ordered_point_cloud_normals(const float* point_positions, int32_t image_height, int32_t image_width,
+                                                  float* normals, void* stream);
+
 /* Per-stage device time of one iteration measured with CUDA events outside graph capture (ms):
  * [warp_vertices, face_raster, band_raster, assemble, build_system, stem_eliminate, corner_solve_update]. */
 int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,

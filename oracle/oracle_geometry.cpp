@@ -166,3 +166,54 @@ ORACLE_API void oracle_warped_surface_jacobians(
 		store3(out_normal_jacobians + wi * 3, scale(-w, matvec(R, load3(vertex_normals + v * 3))));
 	}
 }
+
+// ---- normals: cpp/geometry/functional/NormalsOperations.cpp:36-93, kernel/NormalsOperationsImpl.h:38-214 --------------------------
+namespace {
+inline V3 cross3(const V3& a, const V3& b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+// Eigen MatrixBase::normalize()/normalized() (Eigen/src/Core/Dot.h:119-148): divide by sqrt(squaredNorm) when squaredNorm > 0
+inline V3 normalized3(const V3& v) {
+	float z = dot3(v, v);
+	if (z > 0.f) { float n = sqrtf(z); return {v.x / n, v.y / n, v.z / n}; }
+	return v;
+}
+inline V3 normalize_or_up(V3 v) {  // NormalizeVectors3d, NormalsOperationsImpl.h:72-93
+	v = normalized3(v);
+	if (std::isnan(v.x)) v = {0.f, 0.f, 1.f};
+	return v;
+}
+}  // namespace
+
+ORACLE_API void oracle_compute_triangle_normals(const float* positions, const int64_t* triangles, int64_t face_count, int normalized, float* normals) {
+	for (int64_t f = 0; f < face_count; f++) {
+		V3 v0 = load3(positions + triangles[f * 3] * 3), v1 = load3(positions + triangles[f * 3 + 1] * 3), v2 = load3(positions + triangles[f * 3 + 2] * 3);
+		V3 n = cross3(sub(v1, v0), sub(v2, v0));
+		store3(normals + f * 3, normalized ? normalize_or_up(n) : n);
+	}
+}
+
+// triangles visited in index order (ParallelFor on one thread): every vertex receives its addends in ascending face order
+ORACLE_API void oracle_compute_vertex_normals(const int64_t* triangles, int64_t face_count, const float* triangle_normals, int64_t vertex_count,
+                                              int normalized, float* vertex_normals) {
+	for (int64_t i = 0; i < vertex_count * 3; i++) vertex_normals[i] = 0.f;
+	for (int64_t f = 0; f < face_count; f++)
+		for (int k = 0; k < 3; k++) {
+			float* out = vertex_normals + triangles[f * 3 + k] * 3;
+			out[0] += triangle_normals[f * 3]; out[1] += triangle_normals[f * 3 + 1]; out[2] += triangle_normals[f * 3 + 2];
+		}
+	if (normalized)
+		for (int64_t v = 0; v < vertex_count; v++) store3(vertex_normals + v * 3, normalize_or_up(load3(vertex_normals + v * 3)));
+}
+
+ORACLE_API void oracle_compute_ordered_point_cloud_normals(const float* points, int height, int width, float* normals) {
+	for (int64_t i = 0; i < (int64_t) height * width; i++) {
+		int64_t y = i / width, x = i % width;
+		V3 n = {0.f, 0.f, 0.f};
+		if (!(x == 0 || x == width - 1 || y == 0 || y == height - 1)) {
+			V3 d_horizontal = sub(load3(points + (i + 1) * 3), load3(points + (i - 1) * 3));
+			V3 d_vertical = sub(load3(points + (i - width) * 3), load3(points + (i + width) * 3));
+			n = normalized3(cross3(d_horizontal, d_vertical));
+			if (n.z > 0) n = {-n.x, -n.y, -n.z};
+		}
+		store3(normals + i * 3, n);
+	}
+}

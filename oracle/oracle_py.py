@@ -384,3 +384,27 @@ def build_regularization_layers(nodes, node_coverage, layer_count, max_vertex_de
         raise RuntimeError(f"Attempting to generate a coarser layer (layer {-e}) out of a finer layer of the same size, which is not possible.")
     return dict(node_indices=node_indices, layer_node_counts=counts, edges=edges[:e].copy(), edge_layer_indices=eli[:e].copy(),
                 layer_decimation_radii=radii)
+
+
+# --- normals (cpp/geometry/functional/NormalsOperations.cpp) -------------------------------------------------------------------
+def compute_triangle_normals(positions, triangles, normalized=True):
+    positions, triangles = _f32(positions), _i64(triangles)
+    out = np.empty((triangles.shape[0], 3), np.float32)
+    lib().oracle_compute_triangle_normals(_p(positions), _p(triangles), C.c_int64(triangles.shape[0]), C.c_int(int(normalized)), _p(out))
+    return out
+
+
+def compute_vertex_normals(positions, triangles, normalized=True, triangle_normals=None):
+    """As ComputeVertexNormals: un-normalised triangle normals are computed when the mesh has none."""
+    positions, triangles = _f32(positions), _i64(triangles)
+    tn = compute_triangle_normals(positions, triangles, False) if triangle_normals is None else _f32(triangle_normals)
+    out = np.empty((positions.shape[0], 3), np.float32)
+    lib().oracle_compute_vertex_normals(_p(triangles), C.c_int64(triangles.shape[0]), _p(tn), C.c_int64(positions.shape[0]), C.c_int(int(normalized)), _p(out))
+    return out
+
+
+def compute_ordered_point_cloud_normals(points, height, width):
+    points = _f32(points)
+    out = np.empty((height * width, 3), np.float32)
+    lib().oracle_compute_ordered_point_cloud_normals(_p(points), C.c_int(height), C.c_int(width), _p(out))
+    return out

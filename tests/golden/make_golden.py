@@ -5,6 +5,8 @@ vectors) and sub-samples one of its binary fixtures, and stores them as numpy ar
   reference_kats.npz   inline vectors of cpp/tests/test_{anchor_computation,rodrigues,unproject_3d_points,linalg_cholesky,matmul3d}.cpp
   mesh_warp_219.npz    every 8th vertex of tests/test_data/mesh_warping/test_{input,gt}_mesh.ply + nodes/rotations/translations.npy
   oracle_fit_tinyr.npz one full GN iteration of the ORACLE on the seeded 'tinyr' scene (regression pin of the oracle itself)
+  normals_kat.npz      96 x 96 crop of cpp/tests/test_data/images/red_shorts_200_depth.png with the matching crop of
+                       arrays/red_shorts_200_normals.npy (ground truth of cpp/tests/test_normals_operations.cpp:118-140)
   warp_field_kats.npz  inline vectors of cpp/tests/test_sampling.cpp (median grid subsampling) and
                        cpp/tests/test_graph_warp_field.cpp (HierarchicalGraphWarpField constructor: layers, edges, virtual order)
 """
@@ -114,6 +116,17 @@ def main():
     wf["hgwf/virtual_node_indices"] = braces_after(t, "virtual_node_indices_gt").astype(np.int64)
     np.savez_compressed(os.path.join(HERE, "warp_field_kats.npz"), **wf)
     print("warp_field_kats.npz:", {k: v.shape for k, v in wf.items()})
+    # ordered point-cloud normals: a 96 x 96 crop of the reference's depth frame with the ground truth its own test compares against
+    # (cpp/tests/test_normals_operations.cpp:118-140: red_shorts_200_depth.png, red_shorts_intrinsics.txt, red_shorts_200_normals.npy)
+    import cv2
+    data = os.path.join(REF, "cpp/tests/test_data")
+    depth = cv2.imread(os.path.join(data, "images/red_shorts_200_depth.png"), cv2.IMREAD_UNCHANGED)
+    normals_gt = np.load(os.path.join(data, "arrays/red_shorts_200_normals.npy"))
+    K = np.loadtxt(os.path.join(data, "intrinsics/red_shorts_intrinsics.txt"))
+    y0, x0, size = 200, 280, 96
+    np.savez_compressed(os.path.join(HERE, "normals_kat.npz"), depth_u16=depth[y0:y0 + size, x0:x0 + size], origin=np.array([y0, x0]),
+                        normals_gt=normals_gt[y0:y0 + size, x0:x0 + size], intrinsics=K[:3, :3])
+    print("normals_kat.npz:", depth[y0:y0 + size, x0:x0 + size].shape, "valid", int((depth[y0:y0 + size, x0:x0 + size] > 0).sum()))
     if "--warp-field-only" in sys.argv:
         return
 
