@@ -177,9 +177,158 @@ __global__ void __launch_bounds__(256) warped_surface_jacobians_kernel(
 	jn[wi * 3] = outn.x; jn[wi * 3 + 1] = outn.y; jn[wi * 3 + 2] = outn.z;
 }
 
+
+// Shortest-path anchors (core/kernel/KnnUtilities_PriorityQueue.h:102-160, geometry/functional/kernel/WarpUtilities.h:344-375): per
+// point, Dijkstra over the node graph seeded with the nearest node that is not an anchor yet (re-seeded when a component is used
+// up), first `anchor_count` nodes settled. One thread per point. The 40-entry priority queue lives in shared memory, slot-major
+// ([slot][thread]: conflict-free), and follows libstdc++'s std::push_heap / std::pop_heap (the reference's CPU heap,
+// core/heap/CPU/DeviceHeapCPU.h) move for move, so equal path lengths settle in the same order; inserts into a full queue are
+// dropped, as there. anchors must be pre-filled with -1 (the exclusion scan reads all `anchor_count` slots, as the reference's does).
+constexpr int kPathQueueCapacity = 40;
+constexpr int kPathThreads = 64;
+
+struct PathQueue {
+	float* keys;  // [kPathQueueCapacity][kPathThreads]
+	int* nodes;
+	int size;
+	__device__ __forceinline__ float& key(int i) { return keys[i * kPathThreads]; }
+	__device__ __forceinline__ int& node(int i) { return nodes[i * kPathThreads]; }
+	// std::__push_heap with comp(a, b) = a.key > b.key
+	__device__ __forceinline__ void sift_up(int hole, int top, float value_key, int value_node) {
+		int parent = (hole - 1) / 2;
+		while (hole > top && key(parent) > value_key) {
+			key(hole) = key(parent); node(hole) = node(parent);
+			hole = parent;
+			parent = (hole - 1) / 2;
+		}
+		key(hole) = value_key; node(hole) = value_node;
+	}
+	__device__ __forceinline__ void insert(float k, int n) {
+		if (size >= kPathQueueCapacity) return;
+		size++;
+		sift_up(size - 1, 0, k, n);
+	}
+	// std::pop_heap followed by taking the last element: returns the minimum
+	__device__ __forceinline__ void pop(float& out_key, int& out_node) {
+		out_key = key(0); out_node = node(0);
+		size--;
+		if (size == 0) return;
+		const float value_key = key(size);
+		const int value_node = node(size);
+		const int len = size;  // std::__adjust_heap(first, 0, len, value)
+		int hole = 0, child = 0;
+		while (child < (len - 1) / 2) {
+			child = 2 * (child + 1);
+			if (key(child) > key(child - 1)) child--;
+			key(hole) = key(child); node(hole) = node(child);
+			hole = child;
+		}
+		if ((len & 1) == 0 && child == (len - 2) / 2) {
+			child = 2 * (child + 1);
+			key(hole) = key(child - 1); node(hole) = node(child - 1);
+			hole = child - 1;
+		}
+		sift_up(hole, 0, value_key, value_node);
+	}
+};
+
+template<int A>
+__global__ void __launch_bounds__(kPathThreads) anchors_shortest_path_kernel(const float* __restrict__ points, int64_t point_count, const float* __restrict__ nodes,
+                                                                             int node_count, const float* __restrict__ node_weights, float fixed_c2,
+                                                                             const int32_t* __restrict__ edges, int graph_degree,
+                                                                             int32_t* __restrict__ anchors, float* __restrict__ weights) {
+	__shared__ float queue_keys[kPathQueueCapacity * kPathThreads];
+	__shared__ int queue_nodes[kPathQueueCapacity * kPathThreads];
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= point_count) return;
+	const float px = points[i * 3], py = points[i * 3 + 1], pz = points[i * 3 + 2];
+	PathQueue queue{queue_keys + threadIdx.x, queue_nodes + threadIdx.x, 0};
+	int idx[A];
+	float dist[A];
+#pragma unroll
+	for (int a = 0; a < A; a++) { idx[a] = -1; dist[a] = 0.f; }
+	int discovered = 0;
+	while (discovered < A) {
+		int closest = -1;
+		float closest_d2 = INFINITY;
+		for (int n = 0; n < node_count; n++) {
+			bool excluded = false;
+#pragma unroll
+			for (int a = 0; a < A; a++) excluded |= idx[a] == n;
+			if (excluded) continue;
+			const float dx = __ldg(nodes + n * 3) - px, dy = __ldg(nodes + n * 3 + 1) - py, dz = __ldg(nodes + n * 3 + 2) - pz;
+			const float d2 = sum3(dx * dx, dy * dy, dz * dz);
+			if (d2 < closest_d2) { closest_d2 = d2; closest = n; }
+		}
+		if (closest == -1) break;
+		queue.insert(sqrtf(closest_d2), closest);
+		while (queue.size > 0 && discovered < A) {
+			float source_key;
+			int source;
+			queue.pop(source_key, source);
+			bool processed = false;
+#pragma unroll
+			for (int a = 0; a < A; a++) processed |= a < discovered && idx[a] == source;
+			if (processed) continue;
+#pragma unroll
+			for (int a = 0; a < A; a++)
+				if (a == discovered) { dist[a] = source_key; idx[a] = source; }
+			discovered++;
+			if (discovered >= A) break;
+			const float sx = __ldg(nodes + source * 3), sy = __ldg(nodes + source * 3 + 1), sz = __ldg(nodes + source * 3 + 2);
+			for (int e = 0; e < graph_degree; e++) {
+				const int target = __ldg(edges + (int64_t) source * graph_degree + e);
+				if (target > -1) {
+					const float dx = __ldg(nodes + target * 3) - sx, dy = __ldg(nodes + target * 3 + 1) - sy, dz = __ldg(nodes + target * 3 + 2) - sz;
+					queue.insert(source_key + sqrtf(sum3(dx * dx, dy * dy, dz * dz)), target);
+				}
+			}
+		}
+	}
+	// weights from PATH lengths (not squared: WarpUtilities.h:61-64,84-87), normalised over all anchors
+	float w[A];
+	float weight_sum = 0.0f;
+#pragma unroll
+	for (int a = 0; a < A; a++) {
+		const float square_distance = dist[a] * dist[a];
+		const float c2 = node_weights ? node_weights[max(idx[a], 0)] : fixed_c2;
+		w[a] = expf(-square_distance / (2 * c2));
+		weight_sum += w[a];
+	}
+#pragma unroll
+	for (int a = 0; a < A; a++) {
+		anchors[i * A + a] = idx[a];
+		weights[i * A + a] = weight_sum > 0.0f ? w[a] / weight_sum : 1.0f / (float) A;
+	}
+}
+
 }  // namespace nnrt_b200
 
 using namespace nnrt_b200;
+
+extern "C" int nnrt_b200_compute_anchors_shortest_path(const float* points, int64_t point_count, const float* nodes, int32_t node_count,
+                                                       const float* node_weights, float node_coverage, const int32_t* edges, int32_t graph_degree,
+                                                       int32_t anchor_count, int32_t* anchors, float* weights, void* stream) {
+	NNRT_CHECK_ARG(points && nodes && edges && anchors && weights, "compute_anchors_shortest_path: null pointer argument");
+	NNRT_CHECK_ARG(anchor_count >= 1 && anchor_count <= kMaxAnchors, "anchor_count must be in [1, %d], got %d", kMaxAnchors, anchor_count);
+	NNRT_CHECK_ARG(graph_degree >= 1, "edges must have shape [node_count, degree] with degree >= 1, got degree %d", graph_degree);
+	// with fewer nodes than anchors the reference reads never-written distances and node_weights[-1]
+	NNRT_CHECK_ARG(node_count >= anchor_count, "node count (%d) must be at least anchor_count (%d)", node_count, anchor_count);
+	NNRT_CHECK_ARG(point_count >= 0, "negative point count");
+	if (point_count == 0) return kOk;
+	auto s = (cudaStream_t) stream;
+	const float c2 = node_coverage * node_coverage;
+	const unsigned grid = blocks_for(point_count, kPathThreads);
+#define NNRT_PATH_CASE(A_) \
+	case A_: anchors_shortest_path_kernel<A_><<<grid, kPathThreads, 0, s>>>(points, point_count, nodes, node_count, node_weights, c2, edges, graph_degree, anchors, weights); break;
+	switch (anchor_count) {
+		NNRT_PATH_CASE(1) NNRT_PATH_CASE(2) NNRT_PATH_CASE(3) NNRT_PATH_CASE(4)
+		NNRT_PATH_CASE(5) NNRT_PATH_CASE(6) NNRT_PATH_CASE(7) NNRT_PATH_CASE(8)
+	}
+#undef NNRT_PATH_CASE
+	NNRT_LAUNCH_CHECK();
+	return kOk;
+}
 
 extern "C" int nnrt_b200_compute_anchors_euclidean(const float* points, int64_t point_count, const float* nodes, int32_t node_count,
                                                    const float* node_weights, float node_coverage, int32_t anchor_count,

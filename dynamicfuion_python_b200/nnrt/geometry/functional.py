@@ -32,6 +32,45 @@ def compute_anchors_and_weights_euclidean_variable_node_weight(points, nodes, no
     return _anchors(points, nodes, node_coverage_weights, 0.0, anchor_count, minimum_valid_anchor_count)
 
 
+def _anchors_shortest_path(points, nodes, node_weights, node_coverage, edges, anchor_count):
+    pts = T.cuda(points, torch.float32)
+    shape = pts.shape
+    if pts.dim() < 2 or pts.dim() > 3:  # WarpAnchorComputation.cpp:41-44
+        raise RuntimeError(f"`points` needs to have 2 or 3 dimensions. Got: {pts.dim()} dimensions.")
+    if shape[-1] != 3:
+        raise RuntimeError(f"points must have shape [..., 3], got {tuple(shape)}")
+    if anchor_count < 1:
+        raise RuntimeError(f"anchor_count needs to be greater than one. Got: {anchor_count}.")
+    flat = pts.reshape(-1, 3)
+    nd = T.cuda(nodes, torch.float32)
+    e = T.to_torch(edges)
+    if e.dtype != torch.int32:  # o3c::AssertTensorDtype(edges, Int32), WarpAnchorComputation.cpp:169,197
+        raise RuntimeError(f"edges must be Int32, got {e.dtype}")
+    e = T.cuda(e, torch.int32)
+    if e.dim() != 2 or e.shape[0] != nd.shape[0]:
+        raise RuntimeError(f"edges must have shape [node_count, degree], got {tuple(e.shape)}")
+    nw = None if node_weights is None else T.cuda(node_weights, torch.float32)
+    if nw is not None and nw.numel() != nd.shape[0]:
+        raise RuntimeError("node_coverage_weights must have one entry per node")
+    anchors = T.empty((flat.shape[0], anchor_count), torch.int32)
+    weights = T.empty((flat.shape[0], anchor_count), torch.float32)
+    T.call("nnrt_b200_compute_anchors_shortest_path", T.ptr(flat), flat.shape[0], T.ptr(nd), nd.shape[0], T.ptr(nw), float(node_coverage),
+           T.ptr(e), e.shape[1], int(anchor_count), T.ptr(anchors), T.ptr(weights), T.stream())
+    out_shape = tuple(shape[:-1]) + (anchor_count,)
+    return anchors.reshape(out_shape), weights.reshape(out_shape)
+
+
+def compute_anchors_and_weights_shortest_path_fixed_node_weight(points, nodes, edges, anchor_count, node_coverage_weight):
+    """ComputeAnchorsAndWeights_ShortestPath_FixedNodeWeight (cpp/geometry/functional/WarpAnchorComputation.cpp:191-214);
+    edges [N, degree] int32 adjacency, -1 = none."""
+    return _anchors_shortest_path(points, nodes, None, node_coverage_weight, edges, anchor_count)
+
+
+def compute_anchors_and_weights_shortest_path_variable_node_weight(points, nodes, node_coverage_weights, edges, anchor_count):
+    """ComputeAnchorsAndWeights_ShortestPath_VariableNodeWeight (cpp/geometry/functional/WarpAnchorComputation.cpp:158-189)."""
+    return _anchors_shortest_path(points, nodes, node_coverage_weights, 0.0, edges, anchor_count)
+
+
 def _warp(points, normals, nodes, node_rotations, node_translations, anchors, anchor_weights, minimum_valid_anchor_count, extrinsics):
     nd = T.cuda(nodes, torch.float32)
     R = T.cuda(node_rotations, torch.float32)

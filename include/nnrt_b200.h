@@ -33,6 +33,16 @@ int nnrt_b200_compute_anchors_euclidean(const float* points, int64_t point_count
                                         const float* node_weights, float node_coverage, int32_t anchor_count,
                                         int32_t minimum_valid_anchor_count, int32_t* anchors, float* weights, void* stream);
 
+/* geometry::functional::ComputeAnchorsAndWeights_ShortestPath_{Fixed,Variable}NodeWeight
+ * (geometry/functional/WarpAnchorComputation.cpp:158-214; kernel/WarpAnchorComputationImpl.h:146-240;
+ * core/kernel/KnnUtilities_PriorityQueue.h:102-160). edges [N, graph_degree] int32 adjacency (-1 = no neighbour). Anchors are the
+ * first anchor_count nodes settled by Dijkstra from the point's nearest node (re-seeded per connected component), weights come
+ * from the path lengths. The 40-entry queue and its std::push_heap / std::pop_heap tie order are the reference's (CPU path).
+ * node_weights == NULL selects the fixed-coverage variant. Needs node_count >= anchor_count. */
+int nnrt_b200_compute_anchors_shortest_path(const float* points, int64_t point_count, const float* nodes, int32_t node_count,
+                                            const float* node_weights, float node_coverage, const int32_t* edges, int32_t graph_degree,
+                                            int32_t anchor_count, int32_t* anchors, float* weights, void* stream);
+
 /* geometry::functional::WarpTriangleMeshUsingSuppliedAnchors / WarpPointCloud (geometry/functional/Warping.cpp:169-263;
  * kernel/Warp3dPointsAndNormalsImpl.h:334-438). normals / warped_normals may be NULL (points only).
  * extrinsics_host: 4x4 row-major f64 on the host (as in the reference API). */

@@ -217,3 +217,77 @@ ORACLE_API void oracle_compute_ordered_point_cloud_normals(const float* points, 
 		store3(normals + i * 3, n);
 	}
 }
+
+// ---- shortest-path anchors: cpp/core/kernel/KnnUtilities_PriorityQueue.h:102-160, cpp/core/kernel/KnnUtilities.h:119-142,
+// cpp/core/heap/CPU/DeviceHeapCPU.h (std::push_heap / std::pop_heap on a 40-entry array, inserts beyond capacity dropped),
+// cpp/geometry/functional/kernel/WarpUtilities.h:36-92,344-375, kernel/WarpAnchorComputationImpl.h:146-240 ----------------------
+namespace {
+struct DistanceIndexPair { float key; int32_t index; };
+constexpr int SHORTEST_PATH_QUEUE_CAPACITY = 40;
+}  // namespace
+
+// edges [node_count, graph_degree] int32 adjacency (-1 = none). node_weights == nullptr -> fixed coverage.
+// Requires node_count >= anchor_count (the reference reads uninitialised distances / node_weights[-1] otherwise).
+ORACLE_API void oracle_compute_anchors_shortest_path(const float* points, int64_t point_count, const float* nodes, int node_count,
+                                                     const float* node_weights, float node_coverage, const int32_t* edges, int graph_degree,
+                                                     int anchor_count, int32_t* anchors, float* weights) {
+	auto compare = [](const DistanceIndexPair& first, const DistanceIndexPair& second) { return first.key > second.key; };  // MinHeapKeyCompare
+	const float fixed_c2 = node_coverage * node_coverage;
+	for (int64_t i = 0; i < point_count; i++) {
+		int32_t* idx = anchors + i * anchor_count;
+		float* dist = weights + i * anchor_count;
+		for (int a = 0; a < anchor_count; a++) idx[a] = -1;
+		V3 p = load3(points + i * 3);
+		DistanceIndexPair queue[SHORTEST_PATH_QUEUE_CAPACITY];
+		int size = 0;
+		auto insert = [&](DistanceIndexPair e) {
+			if (size >= SHORTEST_PATH_QUEUE_CAPACITY) return;
+			queue[size++] = e;
+			std::push_heap(queue, queue + size, compare);
+		};
+		int discovered = 0;
+		while (discovered < anchor_count) {
+			// nearest node not yet among the anchors (k = 1 brute force, strict <, ascending index)
+			int closest = -1;
+			float closest_d2 = INFINITY;
+			for (int n = 0; n < node_count; n++) {
+				bool excluded = false;
+				for (int a = 0; a < anchor_count; a++) if (idx[a] == n) excluded = true;
+				if (excluded) continue;
+				V3 d = sub(load3(nodes + n * 3), p);
+				float d2 = dot3(d, d);
+				if (d2 < closest_d2) { closest_d2 = d2; closest = n; }
+			}
+			if (closest == -1) break;
+			insert({sqrtf(closest_d2), closest});
+			while (size > 0 && discovered < anchor_count) {
+				std::pop_heap(queue, queue + size, compare);
+				DistanceIndexPair source = queue[--size];
+				bool processed = false;
+				for (int a = 0; a < discovered && !processed; a++) if (idx[a] == source.index) processed = true;
+				if (processed) continue;
+				dist[discovered] = source.key;
+				idx[discovered] = source.index;
+				discovered++;
+				if (discovered >= anchor_count) break;
+				for (int e = 0; e < graph_degree; e++) {
+					int32_t target = edges[(int64_t) source.index * graph_degree + e];
+					if (target > -1) {
+						V3 d = sub(load3(nodes + target * 3), load3(nodes + source.index * 3));
+						insert({source.key + sqrtf(dot3(d, d)), target});
+					}
+				}
+			}
+		}
+		float weight_sum = 0.0f;
+		for (int a = 0; a < anchor_count; a++) {
+			float square_distance = dist[a] * dist[a];
+			float c2 = node_weights ? node_weights[idx[a]] : fixed_c2;
+			float weight = expf(-square_distance / (2 * c2));
+			weight_sum += weight;
+			dist[a] = weight;
+		}
+		if (weight_sum > 0.0f) for (int a = 0; a < anchor_count; a++) dist[a] /= weight_sum;
+		else for (int a = 0; a < anchor_count; a++) dist[a] = 1.0f / (float) anchor_count;
+	}
+}

@@ -408,3 +408,17 @@ def compute_ordered_point_cloud_normals(points, height, width):
     out = np.empty((height * width, 3), np.float32)
     lib().oracle_compute_ordered_point_cloud_normals(_p(points), C.c_int(height), C.c_int(width), _p(out))
     return out
+
+
+def compute_anchors_shortest_path(points, nodes, edges, anchor_count, node_coverage=0.05, node_weights=None):
+    """compute_anchors_and_weights_shortest_path_{fixed,variable}_node_weight; edges [N, degree] int32 adjacency (-1 = none)."""
+    points, nodes, edges = _f32(points), _f32(nodes), _i32(edges)
+    if nodes.shape[0] < anchor_count:
+        raise RuntimeError("node count must be at least anchor_count")
+    nw = None if node_weights is None else _f32(node_weights)
+    anchors = np.empty((points.shape[0], anchor_count), np.int32)
+    weights = np.empty((points.shape[0], anchor_count), np.float32)
+    lib().oracle_compute_anchors_shortest_path(_p(points), C.c_int64(points.shape[0]), _p(nodes), C.c_int(nodes.shape[0]), _p(nw),
+                                               C.c_float(node_coverage), _p(edges), C.c_int(edges.shape[1]), C.c_int(anchor_count),
+                                               _p(anchors), _p(weights))
+    return anchors, weights

@@ -5,6 +5,7 @@ vectors) and sub-samples one of its binary fixtures, and stores them as numpy ar
   reference_kats.npz   inline vectors of cpp/tests/test_{anchor_computation,rodrigues,unproject_3d_points,linalg_cholesky,matmul3d}.cpp
   mesh_warp_219.npz    every 8th vertex of tests/test_data/mesh_warping/test_{input,gt}_mesh.ply + nodes/rotations/translations.npy
   oracle_fit_tinyr.npz one full GN iteration of the ORACLE on the seeded 'tinyr' scene (regression pin of the oracle itself)
+  shortest_path_kat.npz inline data + ground truth of tests/test_compute_anchors.py:57-185 (shortest-path anchors, 11 nodes, 2 vertices)
   normals_kat.npz      96 x 96 crop of cpp/tests/test_data/images/red_shorts_200_depth.png with the matching crop of
                        arrays/red_shorts_200_normals.npy (ground truth of cpp/tests/test_normals_operations.cpp:118-140)
   warp_field_kats.npz  inline vectors of cpp/tests/test_sampling.cpp (median grid subsampling) and
@@ -116,6 +117,19 @@ def main():
     wf["hgwf/virtual_node_indices"] = braces_after(t, "virtual_node_indices_gt").astype(np.int64)
     np.savez_compressed(os.path.join(HERE, "warp_field_kats.npz"), **wf)
     print("warp_field_kats.npz:", {k: v.shape for k, v in wf.items()})
+    # shortest-path anchors: the inline data of the reference's python test, obtained by executing ONLY that data-building function
+    # (tests/test_compute_anchors.py:57-146, numpy + math) -- nothing of it is stored as source
+    import ast
+    import math
+    tree = ast.parse(read("tests/test_compute_anchors.py"))
+    fn = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "prepare_test_data_anchor_computation_manual"][0]
+    scope = {"np": np, "math": math}
+    exec(compile(ast.Module([fn], []), "reference_kat", "exec"), scope)
+    vertices, nodes, edges, anchors_gt, weights_s0, weights_s1 = scope["prepare_test_data_anchor_computation_manual"](1.0)
+    np.savez_compressed(os.path.join(HERE, "shortest_path_kat.npz"), vertices=vertices, nodes=nodes, edges=edges, anchors_gt=anchors_gt,
+                        weights_gt=np.stack([weights_s0, weights_s1]), anchor_count=np.int32(8), node_coverage=np.float32(1.0))
+    print("shortest_path_kat.npz:", vertices.shape, nodes.shape, edges.shape)
+
     # ordered point-cloud normals: a 96 x 96 crop of the reference's depth frame with the ground truth its own test compares against
     # (cpp/tests/test_normals_operations.cpp:118-140: red_shorts_200_depth.png, red_shorts_intrinsics.txt, red_shorts_200_normals.npy)
     import cv2
