@@ -115,6 +115,47 @@ __global__ void __launch_bounds__(256) interpolate_attributes_kernel(const int64
 	}
 }
 
+// rendering::kernel::ShadeEdgesFlat (rendering/kernel/FlatEdgeShaderImpl.h:30-99): the nearest fragment's squared edge distance against
+// the squared NDC line width, linear fall-off; pixels without a fragment stay black. One thread per pixel, 3 bytes out.
+__global__ void __launch_bounds__(256) shade_edges_flat_kernel(const int64_t* __restrict__ faces, const float* __restrict__ distances, int64_t pixel_count,
+                                                               int faces_per_pixel, float ndc_line_width_squared, float r, float g, float b,
+                                                               uint8_t* __restrict__ pixels) {
+	const int64_t px = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (px >= pixel_count) return;
+	uint8_t out[3] = {0, 0, 0};
+	if (faces[px * faces_per_pixel] != -1) {
+		const float distance = fabsf(distances[px * faces_per_pixel]);
+		if (distance < ndc_line_width_squared) {
+			const float factor = __fdiv_rn(ndc_line_width_squared - distance, ndc_line_width_squared);
+			out[0] = (uint8_t) (int) (255.f * r * factor);
+			out[1] = (uint8_t) (int) (255.f * g * factor);
+			out[2] = (uint8_t) (int) (255.f * b * factor);
+		}
+	}
+	pixels[px * 3] = out[0]; pixels[px * 3 + 1] = out[1]; pixels[px * 3 + 2] = out[2];
+}
+
+// rendering::VertexColorShader::ShadeMeshes (rendering/VertexColorShader.cpp:29-59): barycentric interpolation of the nearest
+// fragment's face-vertex colours (InterpolateFaceAttributesImpl.h:31-71, same summation order), times 255, truncated to 8 bits —
+// the reference's gather + interpolate over all K fragments + Slice + multiply + To(UInt8) in one pass over the pixels.
+__global__ void __launch_bounds__(256) shade_vertex_colors_kernel(const int64_t* __restrict__ faces, const float* __restrict__ bary, int64_t pixel_count,
+                                                                  int faces_per_pixel, const float* __restrict__ face_vertex_colors,
+                                                                  uint8_t* __restrict__ pixels) {
+	const int64_t px = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (px >= pixel_count) return;
+	const int64_t f = faces[px * faces_per_pixel];
+#pragma unroll
+	for (int c = 0; c < 3; c++) {
+		float acc = 0.0f;
+		if (f >= 0) {
+#pragma unroll
+			for (int tv = 0; tv < 3; tv++) acc += bary[px * faces_per_pixel * 3 + tv] * face_vertex_colors[f * 9 + tv * 3 + c];
+		}
+		pixels[px * 3 + c] = (uint8_t) (int) (acc * 255.f);  // low byte of the truncated value: what the x86 reference build's cast yields
+		                                                      // for colours pushed outside [0, 255] by barycentrics of blurred (outside-the-face) fragments
+	}
+}
+
 __global__ void __launch_bounds__(128) rasterized_surface_jacobians_kernel(
 		const float* __restrict__ positions, const float* __restrict__ normals, const int64_t* __restrict__ triangles,
 		const int64_t* __restrict__ pixel_faces, const float* __restrict__ pixel_bary, int height, int width, int faces_per_pixel,
@@ -295,6 +336,32 @@ extern "C" int nnrt_b200_associate_faces_with_anchors(const int64_t* triangles, 
 	if (face_count == 0) return kOk;
 	associate_faces_kernel<<<blocks_for(face_count, 256), 256, 0, (cudaStream_t) stream>>>(triangles, face_count, vertex_anchors, anchor_count,
 	                                                                                       face_anchor_entries, face_anchor_counts);
+	NNRT_LAUNCH_CHECK();
+	return kOk;
+}
+
+extern "C" int nnrt_b200_shade_edges_flat(const int64_t* pixel_face_indices, const float* pixel_face_distances, int32_t image_height, int32_t image_width,
+                                          int32_t faces_per_pixel, float pixel_line_width, const float* line_color_host, uint8_t* pixels, void* stream) {
+	NNRT_CHECK_ARG(pixel_face_indices && pixel_face_distances && line_color_host && pixels, "shade_edges_flat: null pointer argument");
+	NNRT_CHECK_ARG(image_height > 0 && image_width > 0 && faces_per_pixel >= 1, "shade_edges_flat: bad image size or faces_per_pixel");
+	// kernel::ImageSpaceDistanceToNdc (rendering/kernel/CoordinateSystemConversions.h:97-101)
+	const float ndc_line_width = pixel_line_width / ((float) (image_height < image_width ? image_height : image_width) / 2.0f);
+	NNRT_CHECK_ARG(ndc_line_width > 0.f, "Expecting a non-zero, positive ndc_line_width. Got: %f.", ndc_line_width);
+	const int64_t px = (int64_t) image_height * image_width;
+	shade_edges_flat_kernel<<<blocks_for(px, 256), 256, 0, (cudaStream_t) stream>>>(pixel_face_indices, pixel_face_distances, px, faces_per_pixel,
+	                                                                              ndc_line_width * ndc_line_width, line_color_host[0], line_color_host[1],
+	                                                                              line_color_host[2], pixels);
+	NNRT_LAUNCH_CHECK();
+	return kOk;
+}
+
+extern "C" int nnrt_b200_shade_vertex_colors(const int64_t* pixel_face_indices, const float* pixel_barycentric, int32_t image_height, int32_t image_width,
+                                             int32_t faces_per_pixel, const float* face_vertex_colors, uint8_t* pixels, void* stream) {
+	NNRT_CHECK_ARG(pixel_face_indices && pixel_barycentric && face_vertex_colors && pixels, "shade_vertex_colors: null pointer argument");
+	NNRT_CHECK_ARG(image_height > 0 && image_width > 0 && faces_per_pixel >= 1, "shade_vertex_colors: bad image size or faces_per_pixel");
+	const int64_t px = (int64_t) image_height * image_width;
+	shade_vertex_colors_kernel<<<blocks_for(px, 256), 256, 0, (cudaStream_t) stream>>>(pixel_face_indices, pixel_barycentric, px, faces_per_pixel,
+	                                                                                 face_vertex_colors, pixels);
 	NNRT_LAUNCH_CHECK();
 	return kOk;
 }

@@ -267,6 +267,20 @@ int nnrt_b200_normalize_vectors_3d(float* vectors, int64_t count, void* stream);
 int nnrt_b200_compute_ordered_point_cloud_normals(const float* point_positions, int32_t image_height, int32_t image_width,
                                                   float* normals, void* stream);
 
+/* ---- Shaders over rasteriser fragments (headless: 8-bit RGB device buffers) ---- */
+
+/* rendering::FlatEdgeShader::ShadeMeshes (rendering/FlatEdgeShader.cpp:32-50; kernel/FlatEdgeShaderImpl.h:30-99): triangle edges
+ * drawn from the nearest fragment's face distance, `pixel_line_width` in pixels, line_color_host = 3 floats in [0, 1].
+ * pixels [H,W,3] u8. */
+int nnrt_b200_shade_edges_flat(const int64_t* pixel_face_indices, const float* pixel_face_distances, int32_t image_height,
+                               int32_t image_width, int32_t faces_per_pixel, float pixel_line_width, const float* line_color_host,
+                               uint8_t* pixels, void* stream);
+/* rendering::VertexColorShader::ShadeMeshes (rendering/VertexColorShader.cpp:29-59): face_vertex_colors [F,3,3] f32 in [0, 1]
+ * (vertex colours gathered by triangle, meshes concatenated in rasterisation order); pixels [H,W,3] u8. */
+int nnrt_b200_shade_vertex_colors(const int64_t* pixel_face_indices, const float* pixel_barycentric, int32_t image_height,
+                                  int32_t image_width, int32_t faces_per_pixel, const float* face_vertex_colors, uint8_t* pixels,
+                                  void* stream);
+
 /* Per-stage device time of one iteration measured with CUDA events outside graph capture (ms):
  * [warp_vertices, face_raster, band_raster, assemble, build_system, stem_eliminate, corner_solve_update]. */
 int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,

@@ -422,3 +422,19 @@ def compute_anchors_shortest_path(points, nodes, edges, anchor_count, node_cover
                                                C.c_float(node_coverage), _p(edges), C.c_int(edges.shape[1]), C.c_int(anchor_count),
                                                _p(anchors), _p(weights))
     return anchors, weights
+
+
+def shade_edges_flat(pixel_face_indices, pixel_face_distances, pixel_line_width, line_color):
+    faces, dist = _i64(pixel_face_indices), _f32(pixel_face_distances)
+    h, w, k = faces.shape
+    out = np.empty((h, w, 3), np.uint8)
+    lib().oracle_shade_edges_flat(_p(faces), _p(dist), C.c_int(h), C.c_int(w), C.c_int(k), C.c_float(pixel_line_width), _p(_f32(line_color)), _p(out))
+    return out
+
+
+def shade_vertex_colors(pixel_face_indices, pixel_barycentric, face_vertex_colors):
+    faces, bary, colors = _i64(pixel_face_indices), _f32(pixel_barycentric), _f32(face_vertex_colors)
+    h, w, k = faces.shape
+    out = np.empty((h, w, 3), np.uint8)
+    lib().oracle_shade_vertex_colors(_p(faces), _p(bary), C.c_int(h), C.c_int(w), C.c_int(k), _p(colors), _p(out))
+    return out

@@ -271,3 +271,29 @@ ORACLE_API void oracle_interpolate_vertex_attributes(
 		}
 	}
 }
+
+// ---- shaders: cpp/rendering/kernel/FlatEdgeShaderImpl.h:30-99, cpp/rendering/VertexColorShader.cpp:29-59 ----------------------------
+ORACLE_API void oracle_shade_edges_flat(const int64_t* pixel_face_indices, const float* pixel_face_distances, int height, int width, int faces_per_pixel,
+                                        float pixel_line_width, const float* color, uint8_t* pixels) {
+	// ImageSpaceDistanceToNdc, cpp/rendering/kernel/CoordinateSystemConversions.h:97-101
+	const float ndc_line_width = pixel_line_width / (fminf((float) height, (float) width) / 2.0f);
+	const float w2 = ndc_line_width * ndc_line_width;
+	memset(pixels, 0, (size_t) height * width * 3);
+	for (int64_t px = 0; px < (int64_t) height * width; px++) {
+		if (pixel_face_indices[px * faces_per_pixel] == -1) continue;
+		float distance = fabsf(pixel_face_distances[px * faces_per_pixel]);
+		if (distance < w2) {
+			float factor = (w2 - distance) / w2;
+			for (int c = 0; c < 3; c++) pixels[px * 3 + c] = (uint8_t) (int32_t) (255.f * color[c] * factor);
+		}
+	}
+}
+
+ORACLE_API void oracle_shade_vertex_colors(const int64_t* pixel_face_indices, const float* pixel_bary, int height, int width, int faces_per_pixel,
+                                           const float* face_vertex_colors, uint8_t* pixels) {
+	const int64_t pixel_count = (int64_t) height * width;
+	std::vector<float> interpolated((size_t) pixel_count * faces_per_pixel * 3);
+	oracle_interpolate_vertex_attributes(pixel_face_indices, pixel_bary, pixel_count, faces_per_pixel, face_vertex_colors, 3, interpolated.data());
+	for (int64_t px = 0; px < pixel_count; px++)  // .Slice(2, 0, 1) * 255.f, To(UInt8)
+		for (int c = 0; c < 3; c++) pixels[px * 3 + c] = (uint8_t) (int32_t) (interpolated[px * faces_per_pixel * 3 + c] * 255.f);  // x86 cvttss2si + low byte
+}
