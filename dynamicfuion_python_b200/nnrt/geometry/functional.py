@@ -227,3 +227,67 @@ def compute_ordered_point_cloud_normals(point_cloud, source_image_size):
     normals = T.empty((h * w, 3), torch.float32)
     T.call("nnrt_b200_compute_ordered_point_cloud_normals", T.ptr(pts), h, w, T.ptr(normals), T.stream())
     return normals
+
+
+def integrate_non_rigid_voxel_blocks(block_indices, block_keys, block_values, block_resolution, voxel_size, warp_field, depth, color,
+                                     depth_normals, depth_intrinsics, color_intrinsics=None, extrinsics=None, depth_scale=1000.0, depth_max=3.0,
+                                     truncation_voxel_multiplier=2.0):
+    """The voxel kernel of NonRigidSurfaceVoxelBlockGrid.integrate_non_rigid (cpp/geometry/NonRigidSurfaceVoxelBlockGrid.cpp:32-74;
+    kernel/NonRigidSurfaceVoxelBlockGridImpl.h:50-229) over a voxel block grid's own tensors: `block_indices` [B] the active buffer
+    indices, `block_keys` [capacity,3] int32 the hash map's key tensor, `block_values` a dict with "tsdf" [capacity,R,R,R] f32,
+    "weight" (f32 or uint16) and optionally "color" [capacity,R,R,R,3] f32 — CUDA tensors updated IN PLACE (with Open3D present:
+    `torch.utils.dlpack.from_dlpack(grid.attribute("tsdf").to_dlpack())`). `warp_field` is a GraphWarpField; its
+    minimum_valid_anchor_count and coverage mode apply (WarpField::ComputeAnchorsForPoint<threshold = true>).
+    Returns cos_voxel_ray_to_normal [H,W] f32."""
+    from . import WarpNodeCoverageComputationMethod
+    idx = T.cuda(block_indices, torch.int64)
+    keys = T.cuda(block_keys, torch.int32)
+    tsdf, weight = block_values["tsdf"], block_values["weight"]
+    voxel_color = block_values.get("color")
+    for name, tensor in (("tsdf", tsdf), ("weight", weight), ("color", voxel_color)):
+        if tensor is not None and not (isinstance(tensor, torch.Tensor) and tensor.is_cuda and tensor.is_contiguous()):
+            raise RuntimeError(f"block_values['{name}'] must be a contiguous CUDA tensor (it is updated in place)")
+    if tsdf.dtype != torch.float32 or (voxel_color is not None and voxel_color.dtype != torch.float32):
+        raise RuntimeError("tsdf and color voxel attributes must be Float32")
+    if weight.dtype == torch.float32:
+        weight_code = 0
+    elif weight.dtype in (torch.uint16, torch.int16):
+        weight_code = 1
+    else:
+        raise RuntimeError("weight voxel attribute must be Float32 or UInt16")
+    d = T.to_torch(depth.as_tensor() if hasattr(depth, "as_tensor") else depth)
+    if d.dim() == 3:
+        d = d[..., 0]
+    if d.dtype in (torch.uint16, torch.int16):
+        d, depth_code = T.cuda(d.view(torch.int16) if d.dtype == torch.uint16 else d, torch.int16), 1
+    elif d.dtype == torch.float32:
+        d, depth_code = T.cuda(d, torch.float32), 0
+    else:
+        raise RuntimeError("depth must be UInt16 or Float32")
+    h, w = d.shape
+    c = None
+    color_code, ch, cw = 0, 0, 0
+    if color is not None and voxel_color is not None:
+        c = T.to_torch(color.as_tensor() if hasattr(color, "as_tensor") else color)
+        if c.numel() == 0:
+            c = None
+        else:
+            color_code = 0 if c.dtype == torch.float32 else 1
+            c = T.cuda(c, torch.float32 if color_code == 0 else torch.uint8)
+            ch, cw = int(c.shape[0]), int(c.shape[1])
+    normals = T.cuda(depth_normals, torch.float32)
+    if normals.numel() != h * w * 3:
+        raise RuntimeError("depth_normals must have shape [H,W,3]")
+    Kd = T.host_f64(depth_intrinsics, (3, 3))
+    Kc = T.host_f64(depth_intrinsics if color_intrinsics is None else color_intrinsics, (3, 3))
+    ext = T.host_f64(torch.eye(4, dtype=torch.float64) if extrinsics is None else extrinsics, (4, 4))
+    fixed = warp_field.warp_node_coverage_computation_method == WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE
+    ncw = None if fixed else warp_field.node_coverage_weights
+    cos = T.empty((h, w), torch.float32)
+    T.call("nnrt_b200_integrate_non_rigid", T.ptr(idx), idx.shape[0], T.ptr(keys), T.ptr(tsdf), T.ptr(weight), weight_code,
+           T.ptr(voxel_color) if c is not None else None, int(block_resolution), float(voxel_size), float(voxel_size) * float(truncation_voxel_multiplier),
+           T.ptr(d), depth_code, T.ptr(c), color_code, T.ptr(normals), h, w, ch, cw, Kd.data_ptr(), Kc.data_ptr(), ext.data_ptr(),
+           T.ptr(warp_field.nodes), T.ptr(warp_field.node_rotations), T.ptr(warp_field.node_translations), warp_field.nodes.shape[0], T.ptr(ncw),
+           float(warp_field.node_coverage), warp_field.anchor_count, warp_field.minimum_valid_anchor_count, float(depth_scale), float(depth_max),
+           T.ptr(cos), T.stream())
+    return cos

@@ -438,3 +438,34 @@ def shade_vertex_colors(pixel_face_indices, pixel_barycentric, face_vertex_color
     out = np.empty((h, w, 3), np.uint8)
     lib().oracle_shade_vertex_colors(_p(faces), _p(bary), C.c_int(h), C.c_int(w), C.c_int(k), _p(colors), _p(out))
     return out
+
+
+# --- non-rigid TSDF integration (cpp/geometry/kernel/NonRigidSurfaceVoxelBlockGridImpl.h:50-229) ---------------------------------
+def integrate_non_rigid(block_indices, block_keys, tsdf, weight, voxel_color, block_resolution, voxel_size, sdf_truncation_distance, depth, color,
+                        depth_normals, depth_intrinsics, color_intrinsics, extrinsics, nodes, node_rotations, node_translations, node_coverage,
+                        anchor_count, minimum_valid_anchor_count, depth_scale, depth_max, node_coverage_weights=None):
+    """Updates tsdf (and voxel_color) in place; returns cos_voxel_ray_to_normal [H,W]."""
+    block_indices, block_keys = _i64(block_indices), _i32(block_keys)
+    assert tsdf.dtype == np.float32 and tsdf.flags.c_contiguous
+    weight_dtype = 0 if weight.dtype == np.float32 else 1
+    depth = np.ascontiguousarray(depth)
+    depth_dtype = 0 if depth.dtype == np.float32 else 1
+    h, w = depth.shape
+    ch = cw = 0
+    color_dtype = 0
+    if color is not None:
+        color = np.ascontiguousarray(color)
+        color_dtype = 0 if color.dtype == np.float32 else 1
+        ch, cw = color.shape[:2]
+    normals = _f32(depth_normals)
+    nodes, R, t = _f32(nodes), _f32(node_rotations), _f32(node_translations)
+    ncw = None if node_coverage_weights is None else _f32(node_coverage_weights)
+    cos = np.empty((h, w), np.float32)
+    lib().oracle_integrate_non_rigid(
+        _p(block_indices), C.c_int64(block_indices.shape[0]), _p(block_keys), _p(tsdf), _p(weight), C.c_int(weight_dtype),
+        None if voxel_color is None else _p(voxel_color), C.c_int(block_resolution), C.c_float(voxel_size), C.c_float(sdf_truncation_distance),
+        _p(depth), C.c_int(depth_dtype), None if color is None else _p(color), C.c_int(color_dtype), _p(normals), C.c_int(h), C.c_int(w),
+        C.c_int(ch), C.c_int(cw), _p(_f64(depth_intrinsics)), _p(_f64(color_intrinsics)), _p(_f64(extrinsics)), _p(nodes), _p(R), _p(t),
+        C.c_int(nodes.shape[0]), _p(ncw), C.c_float(node_coverage), C.c_int(anchor_count), C.c_int(minimum_valid_anchor_count),
+        C.c_float(depth_scale), C.c_float(depth_max), _p(cos))
+    return cos
