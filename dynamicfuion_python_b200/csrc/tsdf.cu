@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(Integrate
 #pragma unroll
 	for (int a = 0; a < A; a++) { idx[a] = -1; w[a] = INFINITY; c2s[a] = p.node_weights ? p.node_weights[0] : p.fixed_c2; }
 	int max_at = 0;
-	float max_distance = INFINITY;
+	float max_distance = INFINITY, skip_above = INFINITY;
 	for (int base = 0; base < p.node_count; base += kNodeTile) {
 		const int count = min(kNodeTile, p.node_count - base);
 		__syncthreads();
@@ -70,7 +70,9 @@ __global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(Integrate
 		for (int k = 0; k < count; k++) {
 			const float4 g = tile[k];
 			const float dx = g.x - voxel.x, dy = g.y - voxel.y, dz = g.z - voxel.z;
-			const float distance = sqrtf(sum3(dx * dx, dy * dy, dz * dz));
+			const float d2 = sum3(dx * dx, dy * dy, dz * dz);
+			if (d2 > skip_above) continue;  // screened on the squared distance: sqrt(d2) >= max_distance for certain (see below)
+			const float distance = sqrtf(d2);
 			if (max_distance > distance) {
 #pragma unroll
 				for (int a = 0; a < A; a++)
@@ -80,6 +82,9 @@ __global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(Integrate
 #pragma unroll
 				for (int a = 1; a < A; a++)
 					if (w[a] > max_distance) { max_at = a; max_distance = w[a]; }
+				// m * m * (1 + 1e-6) exceeds the exact m^2 whatever the roundings do; above it the correctly rounded root cannot be
+				// below m, so only the few candidates near the current k-th distance pay for the IEEE square root
+				skip_above = max_distance * max_distance * 1.000001f;
 			}
 		}
 	}

@@ -27,6 +27,12 @@ __device__ __forceinline__ float distance3(const float* __restrict__ a, const fl
 	return sqrtf(sum3(dx * dx, dy * dy, dz * dz));
 }
 
+// The reference compares DISTANCES (sqrt of the squared norm). The IEEE square root costs several instructions and almost every
+// candidate is far outside the current k-th distance, so candidates are first screened on the squared distance: above
+// m * m * (1 + 1e-6) (which exceeds the exact m^2 whatever the two roundings do) the correctly rounded root cannot be below m, and
+// the exact comparison `m > sqrtf(d2)` is only evaluated for the rest. Decisions are unchanged.
+__device__ __forceinline__ float squared_upper_bound(float m) { return m * m * 1.000001f; }
+
 // ---------------------------------------------------------------------------------------------------------------------------
 // Median-grid subsampling (geometry/functional/kernel/GeometrySamplingGridBinning.h:30-52, GeometrySamplingMedian.h:36-285)
 
@@ -190,7 +196,7 @@ __device__ __forceinline__ void k_nearest(const float* __restrict__ indexed, int
 #pragma unroll
 	for (int a = 0; a < K; a++) { idx[a] = -1; dist[a] = INFINITY; }
 	int max_at = 0;
-	float max_distance = INFINITY;
+	float max_distance = INFINITY, skip_above = INFINITY;
 	for (int base = 0; base < indexed_count; base += tile_capacity) {
 		const int count = min(tile_capacity, indexed_count - base);
 		__syncthreads();
@@ -201,7 +207,9 @@ __device__ __forceinline__ void k_nearest(const float* __restrict__ indexed, int
 		for (int k = 0; k < count; k++) {
 			const float4 g = tile[k];
 			const float dx = g.x - query[0], dy = g.y - query[1], dz = g.z - query[2];
-			const float d = sqrtf(sum3(dx * dx, dy * dy, dz * dz));
+			const float d2 = sum3(dx * dx, dy * dy, dz * dz);
+			if (d2 > skip_above) continue;  // sqrt(d2) >= max_distance for certain: the exact test below would fail
+			const float d = sqrtf(d2);
 			if (max_distance > d) {
 #pragma unroll
 				for (int a = 0; a < K; a++)
@@ -211,6 +219,7 @@ __device__ __forceinline__ void k_nearest(const float* __restrict__ indexed, int
 #pragma unroll
 				for (int a = 1; a < K; a++)
 					if (dist[a] > max_distance) { max_at = a; max_distance = dist[a]; }
+				skip_above = squared_upper_bound(max_distance);
 			}
 		}
 	}
@@ -271,7 +280,7 @@ __global__ void __launch_bounds__(kThreads) layer_edges_kernel(const float* __re
 #pragma unroll
 	for (int a = 0; a < K; a++) { idx[a] = -1; dist[a] = INFINITY; }
 	int max_at = 0;
-	float max_distance = INFINITY;
+	float max_distance = INFINITY, skip_above = INFINITY;
 	for (int base = 0; base < coarser_count; base += kKnnTile) {
 		const int count = min(kKnnTile, coarser_count - base);
 		__syncthreads();
@@ -282,7 +291,9 @@ __global__ void __launch_bounds__(kThreads) layer_edges_kernel(const float* __re
 		for (int k = lane; k < count; k += 32) {
 			const float4 g = tile[k];
 			const float dx = g.x - query[0], dy = g.y - query[1], dz = g.z - query[2];
-			const float d = sqrtf(sum3(dx * dx, dy * dy, dz * dz));
+			const float d2 = sum3(dx * dx, dy * dy, dz * dz);
+			if (d2 > skip_above) continue;  // sqrt(d2) >= max_distance for certain: the exact test below would fail
+			const float d = sqrtf(d2);
 			if (max_distance > d) {
 #pragma unroll
 				for (int a = 0; a < K; a++)
@@ -292,6 +303,7 @@ __global__ void __launch_bounds__(kThreads) layer_edges_kernel(const float* __re
 #pragma unroll
 				for (int a = 1; a < K; a++)
 					if (dist[a] > max_distance) { max_at = a; max_distance = dist[a]; }
+				skip_above = squared_upper_bound(max_distance);
 			}
 		}
 	}
@@ -340,7 +352,7 @@ __global__ void __launch_bounds__(kThreads) node_coverage_weights_kernel(const f
 	const bool active = i < node_count;
 	float p[3] = {0.f, 0.f, 0.f};
 	if (active) { p[0] = nodes[i * 3]; p[1] = nodes[i * 3 + 1]; p[2] = nodes[i * 3 + 2]; }
-	float nearest = INFINITY;
+	float nearest_d2 = INFINITY;
 	for (int base = 0; base < node_count; base += kKnnTile) {
 		const int count = min(kKnnTile, node_count - base);
 		__syncthreads();
@@ -352,10 +364,10 @@ __global__ void __launch_bounds__(kThreads) node_coverage_weights_kernel(const f
 			if (base + k == i) continue;
 			const float4 g = tile[k];
 			const float dx = g.x - p[0], dy = g.y - p[1], dz = g.z - p[2];
-			nearest = fminf(nearest, sqrtf(sum3(dx * dx, dy * dy, dz * dz)));
+			nearest_d2 = fminf(nearest_d2, sum3(dx * dx, dy * dy, dz * dz));  // sqrt is monotone: the nearest node has the smallest d2
 		}
 	}
-	if (active) weights[i] = nearest * nearest;
+	if (active) { const float nearest = sqrtf(nearest_d2); weights[i] = nearest * nearest; }
 }
 
 // --- layer bookkeeping -----------------------------------------------------------------------------------------------------
