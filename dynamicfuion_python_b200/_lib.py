@@ -14,6 +14,7 @@ _SIGNATURES = {
     "nnrt_b200_compute_anchors_euclidean": (C.c_int, [P, I64, P, I32, P, F32, I32, I32, P, P, P]),
     "nnrt_b200_compute_anchors_shortest_path": (C.c_int, [P, I64, P, I32, P, F32, P, I32, I32, P, P, P]),
     "nnrt_b200_warp_points_normals": (C.c_int, [P, P, I64, P, P, P, I32, P, P, I32, I32, P, P, P, P]),
+    "nnrt_b200_warp_points_normals_dual_quaternion": (C.c_int, [P, P, I64, P, P, P, I32, P, P, I32, I32, P, P, P, P]),
     "nnrt_b200_face_vertices_ndc": (C.c_int, [P, I64, P, I64, P, I32, I32, F32, F32, P, P, P]),
     "nnrt_b200_rasterize_ndc_triangles": (C.c_int, [P, P, I64, I32, I32, F32, I32, I32, I32, I32, I32, I32, P, P, P, P, P]),
     "nnrt_b200_interpolate_vertex_attributes": (C.c_int, [P, P, I64, I32, P, I32, P, P]),

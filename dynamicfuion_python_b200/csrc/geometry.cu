@@ -127,6 +127,85 @@ __global__ void __launch_bounds__(256) warp_points_kernel(const float* __restric
 	if (normals && warped_normals) { warped_normals[i * 3] = wn.x; warped_normals[i * 3 + 1] = wn.y; warped_normals[i * 3 + 2] = wn.z; }
 }
 
+// Dual-quaternion blending (BASELINE.json north_star names it next to linear blending; the reference has no implementation of it —
+// cpp/geometry/TransformationMode.h only distinguishes how rotations are STORED — so this follows the published algorithm, Kavan et al.,
+// "Geometric Skinning with Approximate Dual Quaternion Blending", 2008): each anchor's rigid motion x -> R (x - g) + g + t becomes a
+// unit dual quaternion, the weighted sum (signs aligned with the first valid anchor) is normalised, and the blended rigid motion
+// is applied to the point and its rotation to the normal. Same inputs, validity rules and extrinsics handling as warp_points_kernel.
+struct Quat { float w, x, y, z; };
+__device__ __forceinline__ Quat quat_mul(Quat a, Quat b) {
+	return Quat{a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z, a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y,
+	            a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x, a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w};
+}
+// rotation matrix (row-major) -> unit quaternion, Shepperd's method (largest of the four squared components first)
+__device__ __forceinline__ Quat quat_from_matrix(const float* __restrict__ R) {
+	const float trace = R[0] + R[4] + R[8];
+	Quat q;
+	if (trace > 0.f) {
+		const float s = sqrtf(trace + 1.f) * 2.f;
+		q = Quat{0.25f * s, (R[7] - R[5]) / s, (R[2] - R[6]) / s, (R[3] - R[1]) / s};
+	} else if (R[0] > R[4] && R[0] > R[8]) {
+		const float s = sqrtf(1.f + R[0] - R[4] - R[8]) * 2.f;
+		q = Quat{(R[7] - R[5]) / s, 0.25f * s, (R[1] + R[3]) / s, (R[2] + R[6]) / s};
+	} else if (R[4] > R[8]) {
+		const float s = sqrtf(1.f + R[4] - R[0] - R[8]) * 2.f;
+		q = Quat{(R[2] - R[6]) / s, (R[1] + R[3]) / s, 0.25f * s, (R[5] + R[7]) / s};
+	} else {
+		const float s = sqrtf(1.f + R[8] - R[0] - R[4]) * 2.f;
+		q = Quat{(R[3] - R[1]) / s, (R[2] + R[6]) / s, (R[5] + R[7]) / s, 0.25f * s};
+	}
+	const float n = sqrtf(q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z);
+	return Quat{q.w / n, q.x / n, q.y / n, q.z / n};
+}
+
+__global__ void __launch_bounds__(256) warp_points_dqb_kernel(const float* __restrict__ points, const float* __restrict__ normals,
+                                                               int64_t point_count, const float* __restrict__ nodes,
+                                                               const float* __restrict__ rotations, const float* __restrict__ translations,
+                                                               const int32_t* __restrict__ anchors, const float* __restrict__ anchor_weights,
+                                                               int anchor_count, int min_valid, Rigid extrinsics,
+                                                               float* __restrict__ warped_points, float* __restrict__ warped_normals) {
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= point_count) return;
+	const float3 pc = rigid_transform(extrinsics, make_float3(points[i * 3], points[i * 3 + 1], points[i * 3 + 2]));
+	float3 nc = make_float3(0.f, 0.f, 0.f);
+	if (normals) nc = rigid_rotate(extrinsics, make_float3(normals[i * 3], normals[i * 3 + 1], normals[i * 3 + 2]));
+	float3 wp = make_float3(0.f, 0.f, 0.f), wn = make_float3(0.f, 0.f, 0.f);
+	int valid = 0;
+	for (int a = 0; a < anchor_count; a++) valid += anchors[i * anchor_count + a] != -1;
+	if (valid > 0 && !(min_valid > 0 && valid < min_valid)) {
+		Quat real{0.f, 0.f, 0.f, 0.f}, dual{0.f, 0.f, 0.f, 0.f}, pivot{1.f, 0.f, 0.f, 0.f};
+		bool first = true;
+		for (int a = 0; a < anchor_count; a++) {
+			const int n = anchors[i * anchor_count + a];
+			if (n == -1) continue;
+			float weight = anchor_weights[i * anchor_count + a];
+			const float* R = rotations + (int64_t) n * 9;
+			const float3 g = make_float3(nodes[n * 3], nodes[n * 3 + 1], nodes[n * 3 + 2]);
+			const float3 t = make_float3(translations[n * 3], translations[n * 3 + 1], translations[n * 3 + 2]);
+			const float3 tau = (g + t) - matvec3(R, g);  // x -> R x + tau
+			const Quat q = quat_from_matrix(R);
+			const Quat d = quat_mul(Quat{0.f, 0.5f * tau.x, 0.5f * tau.y, 0.5f * tau.z}, q);
+			if (first) { pivot = q; first = false; }
+			if (q.w * pivot.w + q.x * pivot.x + q.y * pivot.y + q.z * pivot.z < 0.f) weight = -weight;  // q and -q are the same rotation
+			real = Quat{real.w + weight * q.w, real.x + weight * q.x, real.y + weight * q.y, real.z + weight * q.z};
+			dual = Quat{dual.w + weight * d.w, dual.x + weight * d.x, dual.y + weight * d.y, dual.z + weight * d.z};
+		}
+		const float norm = sqrtf(real.w * real.w + real.x * real.x + real.y * real.y + real.z * real.z);
+		if (norm > 0.f) {
+			const Quat q{real.w / norm, real.x / norm, real.y / norm, real.z / norm};
+			const Quat d{dual.w / norm, dual.x / norm, dual.y / norm, dual.z / norm};
+			const Quat tq = quat_mul(d, Quat{q.w, -q.x, -q.y, -q.z});  // translation = 2 * vector part of d * conj(q)
+			const float Rb[9] = {1.f - 2.f * (q.y * q.y + q.z * q.z), 2.f * (q.x * q.y - q.w * q.z), 2.f * (q.x * q.z + q.w * q.y),
+			                     2.f * (q.x * q.y + q.w * q.z), 1.f - 2.f * (q.x * q.x + q.z * q.z), 2.f * (q.y * q.z - q.w * q.x),
+			                     2.f * (q.x * q.z - q.w * q.y), 2.f * (q.y * q.z + q.w * q.x), 1.f - 2.f * (q.x * q.x + q.y * q.y)};
+			wp = matvec3(Rb, pc) + make_float3(2.f * tq.x, 2.f * tq.y, 2.f * tq.z);
+			wn = matvec3(Rb, nc);
+		}
+	}
+	warped_points[i * 3] = wp.x; warped_points[i * 3 + 1] = wp.y; warped_points[i * 3 + 2] = wp.z;
+	if (normals && warped_normals) { warped_normals[i * 3] = wn.x; warped_normals[i * 3 + 1] = wn.y; warped_normals[i * 3 + 2] = wn.z; }
+}
+
 template<typename TDepth>
 __global__ void __launch_bounds__(256) unproject_kernel(const TDepth* __restrict__ depth, int rows, int cols, Intrinsics k, Rigid pose,
                                                          float depth_scale, float depth_max, float* __restrict__ points,
@@ -362,6 +441,23 @@ extern "C" int nnrt_b200_warp_points_normals(const float* points, const float* n
 	(void) node_count;
 	if (point_count == 0) return kOk;
 	warp_points_kernel<<<blocks_for(point_count, 256), 256, 0, (cudaStream_t) stream>>>(
+			points, normals, point_count, nodes, node_rotations, node_translations, anchors, anchor_weights, anchor_count,
+			minimum_valid_anchor_count, rigid_from_host(extrinsics_host), warped_points, warped_normals);
+	NNRT_LAUNCH_CHECK();
+	return kOk;
+}
+
+extern "C" int nnrt_b200_warp_points_normals_dual_quaternion(const float* points, const float* normals, int64_t point_count, const float* nodes,
+                                                             const float* node_rotations, const float* node_translations, int32_t node_count,
+                                                             const int32_t* anchors, const float* anchor_weights, int32_t anchor_count,
+                                                             int32_t minimum_valid_anchor_count, const double* extrinsics_host, float* warped_points,
+                                                             float* warped_normals, void* stream) {
+	NNRT_CHECK_ARG(points && nodes && node_rotations && node_translations && anchors && anchor_weights && warped_points,
+	               "warp_points_normals_dual_quaternion: null pointer argument");
+	NNRT_CHECK_ARG(anchor_count >= 1 && anchor_count <= kMaxAnchors, "anchor_count must be in [1, %d], got %d", kMaxAnchors, anchor_count);
+	(void) node_count;
+	if (point_count == 0) return kOk;
+	warp_points_dqb_kernel<<<blocks_for(point_count, 256), 256, 0, (cudaStream_t) stream>>>(
 			points, normals, point_count, nodes, node_rotations, node_translations, anchors, anchor_weights, anchor_count,
 			minimum_valid_anchor_count, rigid_from_host(extrinsics_host), warped_points, warped_normals);
 	NNRT_LAUNCH_CHECK();

@@ -569,6 +569,7 @@ extern "C" int nnrt_b200_build_regularization_layers(const float* nodes, int32_t
 		NNRT_LAYERS_CUDA(cudaGetLastError());
 		edge_count += (int64_t) finer_count * (max_vertex_degree < coarser_count ? max_vertex_degree : coarser_count);
 	}
+	NNRT_LAYERS_CUDA(cudaGetLastError());
 #undef NNRT_LAYERS_CUDA
 	*edge_count_host = edge_count;
 	cudaFreeAsync(buffer, s);

@@ -71,7 +71,8 @@ def compute_anchors_and_weights_shortest_path_variable_node_weight(points, nodes
     return _anchors_shortest_path(points, nodes, node_coverage_weights, 0.0, edges, anchor_count)
 
 
-def _warp(points, normals, nodes, node_rotations, node_translations, anchors, anchor_weights, minimum_valid_anchor_count, extrinsics):
+def _warp(points, normals, nodes, node_rotations, node_translations, anchors, anchor_weights, minimum_valid_anchor_count, extrinsics,
+          dual_quaternion=False):
     nd = T.cuda(nodes, torch.float32)
     R = T.cuda(node_rotations, torch.float32)
     t = T.cuda(node_translations, torch.float32)
@@ -84,7 +85,7 @@ def _warp(points, normals, nodes, node_rotations, node_translations, anchors, an
     ext = T.host_f64(torch.eye(4, dtype=torch.float64) if extrinsics is None else extrinsics, (4, 4))
     wp = torch.empty_like(points)
     wn = None if normals is None else torch.empty_like(normals)
-    T.call("nnrt_b200_warp_points_normals", T.ptr(points), T.ptr(normals), points.shape[0], T.ptr(nd), T.ptr(R), T.ptr(t), nd.shape[0],
+    T.call("nnrt_b200_warp_points_normals_dual_quaternion" if dual_quaternion else "nnrt_b200_warp_points_normals", T.ptr(points), T.ptr(normals), points.shape[0], T.ptr(nd), T.ptr(R), T.ptr(t), nd.shape[0],
            T.ptr(a), T.ptr(w), a.shape[1], int(minimum_valid_anchor_count), ext.data_ptr(), T.ptr(wp), T.ptr(wn), T.stream())
     return wp, wn
 
@@ -291,3 +292,21 @@ def integrate_non_rigid_voxel_blocks(block_indices, block_keys, block_values, bl
            float(warp_field.node_coverage), warp_field.anchor_count, warp_field.minimum_valid_anchor_count, float(depth_scale), float(depth_max),
            T.ptr(cos), T.stream())
     return cos
+
+
+def warp_triangle_mesh_dual_quaternion(input_mesh, nodes, node_rotations, node_translations, anchors, anchor_weights,
+                                       minimum_valid_anchor_count=0, extrinsics=None):
+    """Dual-quaternion blended counterpart of warp_triangle_mesh with supplied anchors (no reference implementation exists; Kavan et
+    al. 2008 on the node motions x -> R (x - g) + g + t). Volume-preserving where linear blending of distinct rotations shrinks."""
+    mesh = T.MeshView(input_mesh)
+    wp, wn = _warp(mesh.positions, mesh.normals, nodes, node_rotations, node_translations, anchors, anchor_weights, minimum_valid_anchor_count,
+                   extrinsics, dual_quaternion=True)
+    return mesh.with_vertices(wp, wn)
+
+
+def warp_point_cloud_dual_quaternion(input_point_cloud, nodes, node_rotations, node_translations, anchors, anchor_weights,
+                                     minimum_valid_anchor_count=0, extrinsics=None):
+    pts = input_point_cloud.point["positions"] if hasattr(input_point_cloud, "point") else input_point_cloud
+    pts = T.cuda(pts, torch.float32)
+    wp, _ = _warp(pts, None, nodes, node_rotations, node_translations, anchors, anchor_weights, minimum_valid_anchor_count, extrinsics, dual_quaternion=True)
+    return wp

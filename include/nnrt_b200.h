@@ -52,6 +52,16 @@ int nnrt_b200_warp_points_normals(const float* points, const float* normals, int
                                   int32_t minimum_valid_anchor_count, const double* extrinsics_host, float* warped_points,
                                   float* warped_normals, void* stream);
 
+/* Dual-quaternion blended warp with the arguments of nnrt_b200_warp_points_normals. BASELINE.json names dual-quaternion warping next
+ * to linear blending; the reference has no implementation (geometry/TransformationMode.h only selects how rotations are stored), so
+ * this follows Kavan et al. 2008: per anchor the rigid motion x -> R (x - g) + g + t as a unit dual quaternion, weighted sum with
+ * signs aligned to the first valid anchor, normalisation, blended rigid motion applied to the point (its rotation to the normal). */
+int nnrt_b200_warp_points_normals_dual_quaternion(const float* points, const float* normals, int64_t point_count, const float* nodes,
+                                                  const float* node_rotations, const float* node_translations, int32_t node_count,
+                                                  const int32_t* anchors, const float* anchor_weights, int32_t anchor_count,
+                                                  int32_t minimum_valid_anchor_count, const double* extrinsics_host,
+                                                  float* warped_points, float* warped_normals, void* stream);
+
 /* rendering::functional::GetMeshNdcFaceVerticesAndClipMask (rendering/functional/ExtractFaceVertices.cpp:56-85;
  * kernel/ExtractClippedFaceVerticesImpl.h:33-194). triangles int64 [F,3]; out face_vertices_ndc [F,3,3] f32
  * (zeros for masked faces), clip_mask [F] u8 (1 = keep). */
