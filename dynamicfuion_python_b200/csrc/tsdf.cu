@@ -11,6 +11,7 @@
 // single-thread result.
 #include "host_util.h"
 #include "../../include/nnrt_b200.h"
+#include <cfloat>
 
 namespace nnrt_b200 {
 namespace {
@@ -18,14 +19,18 @@ namespace {
 constexpr int kThreads = 128;
 constexpr int kNodeTile = 1024;
 
+// the warp field as the kernels see it
+struct NodeField {
+	const float *nodes, *rotations, *translations; int node_count; const float* node_weights; float fixed_c2; int min_valid;
+};
+
 struct IntegrateParams {
 	const int64_t* block_indices; const int32_t* block_keys; float* tsdf; const void* weight; int weight_dtype; float* voxel_color;
 	int block_resolution; float voxel_size, truncation;
 	const void* depth; int depth_dtype; const void* color; int color_dtype; const float* normals;
 	int height, width, color_height, color_width;
 	Intrinsics depth_k, color_k; Rigid extrinsics;
-	const float *nodes, *rotations, *translations; int node_count; const float* node_weights; float fixed_c2;
-	int min_valid; float depth_scale, depth_max;
+	NodeField field; float depth_scale, depth_max;
 	unsigned long long* cos_keys; int64_t voxel_count;
 };
 
@@ -33,24 +38,13 @@ __device__ __forceinline__ bool in_boundary(float x, float y, int rows, int cols
 	return y >= 0 && x >= 0 && y <= rows - 1.0f && x <= cols - 1.0f;
 }
 
+// WarpField::ComputeAnchorsForPoint<threshold = true> + WarpPoint (geometry/WarpField.h:77-122) for one point per thread; every thread
+// of the CTA must call it (the node tiles are staged cooperatively). Returns false when fewer than min_valid anchors survive the
+// distance threshold; with `warp_anyway` the point is then still blended with the raw, un-normalised weights of the surviving
+// anchors, which is what a caller that ignores ComputeAnchorsForPoint's result gets (GetBoundingBoxesOfWarpedBlocks).
 template<int A>
-__global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(IntegrateParams p) {
-	__shared__ float4 tile[kNodeTile];
-	const int64_t workload = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-	const bool active = workload < p.voxel_count;
-	const int r = p.block_resolution;
-	const int64_t r3 = (int64_t) r * r * r;
-	int64_t block_index = 0, voxel_in_block = 0;
-	float3 voxel = make_float3(0.f, 0.f, 0.f);
-	if (active) {
-		block_index = p.block_indices[workload / r3];
-		voxel_in_block = workload % r3;
-		const int32_t* key = p.block_keys + block_index * 3;
-		const int xl = (int) (voxel_in_block % r), yl = (int) ((voxel_in_block / r) % r), zl = (int) (voxel_in_block / ((int64_t) r * r));
-		const float3 metric = make_float3((float) (key[0] * r + xl) * p.voxel_size, (float) (key[1] * r + yl) * p.voxel_size,
-		                                  (float) (key[2] * r + zl) * p.voxel_size);
-		voxel = rigid_transform(p.extrinsics, metric);
-	}
+__device__ __forceinline__ bool warp_thresholded(const NodeField& p, float3 voxel, bool active, float4* tile, bool warp_anyway, float3& warped_out) {
+	warped_out = make_float3(0.f, 0.f, 0.f);
 	// --- K nearest nodes by distance (norm), replace-current-maximum in ascending node order
 	int idx[A];
 	float w[A], c2s[A];
@@ -88,7 +82,7 @@ __global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(Integrate
 			}
 		}
 	}
-	if (!active) return;
+	if (!active) return false;
 	// --- thresholded weights (geometry/functional/kernel/WarpUtilities.h:95-153, distances not squared) and normalisation (:36-46)
 	float weight_sum = 0.0f;
 	int valid = 0;
@@ -101,8 +95,11 @@ __global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(Integrate
 		w[a] = anchor_weight;
 		valid++;
 	}
-	if (valid < p.min_valid) return;
-	if (weight_sum > 0.0f) {
+	const bool enough = valid >= p.min_valid;
+	if (!enough && !warp_anyway) return false;
+	if (!enough) {
+		// weights stay raw
+	} else if (weight_sum > 0.0f) {
 #pragma unroll
 		for (int a = 0; a < A; a++) w[a] = __fdiv_rn(w[a], weight_sum);
 	} else if (valid > 0) {
@@ -119,6 +116,31 @@ __global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(Integrate
 		const float3 t = make_float3(p.translations[n * 3], p.translations[n * 3 + 1], p.translations[n * 3 + 2]);
 		warped = warped + w[a] * ((g + matvec3(p.rotations + (int64_t) n * 9, voxel - g)) + t);
 	}
+	warped_out = warped;
+	return enough;
+}
+
+template<int A>
+__global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(IntegrateParams p) {
+	__shared__ float4 tile[kNodeTile];
+	const int64_t workload = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	const bool active = workload < p.voxel_count;
+	const int r = p.block_resolution;
+	const int64_t r3 = (int64_t) r * r * r;
+	int64_t block_index = 0, voxel_in_block = 0;
+	float3 voxel = make_float3(0.f, 0.f, 0.f);
+	if (active) {
+		block_index = p.block_indices[workload / r3];
+		voxel_in_block = workload % r3;
+		const int32_t* key = p.block_keys + block_index * 3;
+		const int xl = (int) (voxel_in_block % r), yl = (int) ((voxel_in_block / r) % r), zl = (int) (voxel_in_block / ((int64_t) r * r));
+		const float3 metric = make_float3((float) (key[0] * r + xl) * p.voxel_size, (float) (key[1] * r + yl) * p.voxel_size,
+		                                  (float) (key[2] * r + zl) * p.voxel_size);
+		voxel = rigid_transform(p.extrinsics, metric);
+	}
+	float3 warped;
+	const bool warp_ok = warp_thresholded<A>(p.field, voxel, active, tile, false, warped);
+	if (!active || !warp_ok) return;
 	if (warped.z < 0) return;
 	const float2 uv = project(p.depth_k, warped);
 	if (!in_boundary(uv.x, uv.y, p.height, p.width)) return;
@@ -156,6 +178,118 @@ __global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(Integrate
 			}
 		}
 	}
+}
+
+// GetBoundingBoxesOfWarpedBlocks (geometry/kernel/NonRigidSurfaceVoxelBlockGridImpl.h:289-363): axis-aligned box of the 8 warped
+// corners of every block, 8 lanes per block (one corner each; the corner warps are the expensive part). Kept as the reference has them:
+// the corner is `block key + block side length` (key in blocks, side in metres), anchors always use the FIXED coverage, a corner with
+// too few valid anchors is blended with its raw weights (the reference ignores ComputeAnchorsForPoint's result), and the bounds are
+// updated corner by corner with `if (min > x) min = x; else if (max < x) max = x;` (so max can stay -FLT_MAX).
+template<int A>
+__global__ void __launch_bounds__(kThreads) warped_block_boxes_kernel(const int32_t* __restrict__ block_keys, int64_t block_count, NodeField field,
+                                                                      float block_side_length, Rigid extrinsics, float* __restrict__ boxes) {
+	__shared__ float4 tile[kNodeTile];
+	const int64_t block = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+	const int corner = threadIdx.x & 7;
+	const bool active = block < block_count;
+	float3 point = make_float3(0.f, 0.f, 0.f);
+	if (active) {
+		// corner order of the reference: 000, 001, 010, 100, 011, 101, 110, 111 as (x, y, z)
+		const int bx = (0xE8 >> corner) & 1, by = (0xD4 >> corner) & 1, bz = (0xB2 >> corner) & 1;
+		const float x0 = (float) block_keys[block * 3], y0 = (float) block_keys[block * 3 + 1], z0 = (float) block_keys[block * 3 + 2];
+		point = rigid_transform(extrinsics, make_float3(bx ? x0 + block_side_length : x0, by ? y0 + block_side_length : y0, bz ? z0 + block_side_length : z0));
+	}
+	float3 warped;
+	warp_thresholded<A>(field, point, active, tile, true, warped);
+	// the 8 lanes of a block stay together (active is uniform over them): lane 0 of the group replays the sequential update
+	float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+	const unsigned group_mask = 0xFFu << (threadIdx.x & 24);
+#pragma unroll
+	for (int c = 0; c < 8; c++) {
+		const int src = (threadIdx.x & 24) + c;
+		const float v[3] = {__shfl_sync(group_mask, warped.x, src), __shfl_sync(group_mask, warped.y, src), __shfl_sync(group_mask, warped.z, src)};
+#pragma unroll
+		for (int k = 0; k < 3; k++) {
+			if (lo[k] > v[k]) lo[k] = v[k];
+			else if (hi[k] < v[k]) hi[k] = v[k];
+		}
+	}
+	if (active && corner == 0) {
+#pragma unroll
+		for (int k = 0; k < 3; k++) { boxes[block * 6 + k] = lo[k]; boxes[block * 6 + 3 + k] = hi[k]; }
+	}
+}
+
+// GetAxisAlignedBoxesInterceptingSurfaceMask (NonRigidSurfaceVoxelBlockGridImpl.h:365-435; geometry/kernel/Segment.h:27-73): mask[b] =
+// some strided pixel's truncation segment (its ray between depth -+ truncation) intersects box b (slab test, as written there).
+// The reference materialises all segments and tests every (segment, box) pair. Here a warp takes a box and visits only the strided
+// pixels inside the box's projected rectangle (+-1 pixel): a segment lies on its pixel's ray, and a ray outside that rectangle cannot
+// meet a box in front of the camera. Boxes that reach behind the camera or are inverted (the quirk above) fall back to every pixel.
+// Stops at the first hit. Identical masks except where the slab test meets 0 * inf (a ray exactly on a box face through the optical axis).
+__device__ __forceinline__ bool segment_intersects_box(float3 origin, float3 end, const float* __restrict__ box) {
+	const float3 v = end - origin;
+	const float3 inv = make_float3(__fdiv_rn(1.f, v.x), __fdiv_rn(1.f, v.y), __fdiv_rn(1.f, v.z));
+	const int sx = inv.x < 0, sy = inv.y < 0, sz = inv.z < 0;
+	float t_min = (box[sx ? 3 : 0] - origin.x) * inv.x, t_max = (box[sx ? 0 : 3] - origin.x) * inv.x;
+	const float ty_min = (box[sy ? 4 : 1] - origin.y) * inv.y, ty_max = (box[sy ? 1 : 4] - origin.y) * inv.y;
+	if ((t_min > ty_max) || (ty_min > t_max)) return false;
+	if (ty_min > t_min) t_min = ty_min;
+	if (ty_max < t_max) t_max = ty_max;
+	const float tz_min = (box[sz ? 5 : 2] - origin.z) * inv.z, tz_max = (box[sz ? 2 : 5] - origin.z) * inv.z;
+	if ((t_min > tz_max) || (tz_min > t_max)) return false;
+	if (tz_min > t_min) t_min = tz_min;
+	if (tz_max < t_max) t_max = tz_max;
+	return !(t_max < 0.0f || t_min > 1.0f);
+}
+
+__global__ void __launch_bounds__(kThreads) boxes_intersecting_surface_kernel(const float* __restrict__ boxes, int64_t box_count, Intrinsics k, const void* __restrict__ depth,
+                                                                              int depth_dtype, int height, int width, float depth_scale, float depth_max, int stride,
+                                                                              float truncation, uint8_t* __restrict__ mask) {
+	const int64_t b = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (b >= box_count) return;  // whole warps
+	float box[6];
+#pragma unroll
+	for (int c = 0; c < 6; c++) box[c] = boxes[b * 6 + c];
+	const int rows = height / stride, cols = width / stride;
+	int row0 = 0, row1 = rows - 1, col0 = 0, col1 = cols - 1;
+	if (box[2] > 0.f && box[0] <= box[3] && box[1] <= box[4] && box[2] <= box[5]) {
+		// x / z and y / z over the box are extremal at its corners
+		float x_lo = INFINITY, x_hi = -INFINITY, y_lo = INFINITY, y_hi = -INFINITY;
+#pragma unroll
+		for (int c = 0; c < 4; c++) {
+			const float z = (c & 1) ? box[5] : box[2];
+			const float x = (c & 2) ? box[3] : box[0], y = (c & 2) ? box[4] : box[1];
+			x_lo = fminf(x_lo, x / z); x_hi = fmaxf(x_hi, x / z); y_lo = fminf(y_lo, y / z); y_hi = fmaxf(y_hi, y / z);
+		}
+		const float u_lo = fminf(k.fx * x_lo, k.fx * x_hi) + k.cx - 1.f, u_hi = fmaxf(k.fx * x_lo, k.fx * x_hi) + k.cx + 1.f;
+		const float v_lo = fminf(k.fy * y_lo, k.fy * y_hi) + k.cy - 1.f, v_hi = fmaxf(k.fy * y_lo, k.fy * y_hi) + k.cy + 1.f;
+		// strided pixel index i covers pixel i * stride
+		col0 = max(0, (int) floorf(fmaxf(u_lo, 0.f) / (float) stride)); col1 = min(cols - 1, (int) fminf(ceilf(u_hi / (float) stride), (float) cols));
+		row0 = max(0, (int) floorf(fmaxf(v_lo, 0.f) / (float) stride)); row1 = min(rows - 1, (int) fminf(ceilf(v_hi / (float) stride), (float) rows));
+		if (u_hi < 0.f || v_hi < 0.f) { col1 = -1; row1 = -1; }
+	}
+	bool hit = false;
+	const int span = col1 - col0 + 1;
+	const int64_t candidates = (row1 >= row0 && span > 0) ? (int64_t) (row1 - row0 + 1) * span : 0;
+	for (int64_t base = 0; base < candidates && !hit; base += 32) {
+		const int64_t i = base + lane;
+		bool mine = false;
+		if (i < candidates) {
+			const int v = (row0 + (int) (i / span)) * stride, u = (col0 + (int) (i % span)) * stride;
+			const int64_t px = (int64_t) v * width + u;
+			const float d = __fdiv_rn(depth_dtype == 0 ? ((const float*) depth)[px] : (float) ((const uint16_t*) depth)[px], depth_scale);
+			if (d > 0 && d < depth_max) {
+				const float d0 = d - truncation, d1 = d + truncation;
+				// TransformIndexer::Unproject: x = (u - cx) * d / fx
+				const float3 start = make_float3(__fdiv_rn(((float) u - k.cx) * d0, k.fx), __fdiv_rn(((float) v - k.cy) * d0, k.fy), d0);
+				const float3 end = make_float3(__fdiv_rn(((float) u - k.cx) * d1, k.fx), __fdiv_rn(((float) v - k.cy) * d1, k.fy), d1);
+				mine = segment_intersects_box(start, end, box);
+			}
+		}
+		hit = __any_sync(0xFFFFFFFFu, mine);
+	}
+	if (lane == 0) mask[b] = hit ? 1 : 0;
 }
 
 __global__ void __launch_bounds__(256) resolve_cosines_kernel(const unsigned long long* __restrict__ keys, int64_t pixel_count, float* __restrict__ cosines) {
@@ -199,9 +333,8 @@ extern "C" int nnrt_b200_integrate_non_rigid(
 	p.depth_k = intrinsics_from_host(depth_intrinsics_host);
 	p.color_k = color ? intrinsics_from_host(color_intrinsics_host) : p.depth_k;
 	p.extrinsics = rigid_from_host(extrinsics_host);
-	p.nodes = nodes; p.rotations = node_rotations; p.translations = node_translations; p.node_count = node_count;
-	p.node_weights = node_coverage_weights; p.fixed_c2 = node_coverage * node_coverage;
-	p.min_valid = minimum_valid_anchor_count; p.depth_scale = depth_scale; p.depth_max = depth_max;
+	p.field = NodeField{nodes, node_rotations, node_translations, node_count, node_coverage_weights, node_coverage * node_coverage, minimum_valid_anchor_count};
+	p.depth_scale = depth_scale; p.depth_max = depth_max;
 	p.cos_keys = keys; p.voxel_count = voxel_count;
 	if (voxel_count > 0) {
 		const unsigned grid = blocks_for(voxel_count, kThreads);
@@ -215,5 +348,41 @@ extern "C" int nnrt_b200_integrate_non_rigid(
 	const cudaError_t err = cudaGetLastError();
 	cudaFreeAsync(keys, s);
 	if (err != cudaSuccess) { set_last_error("integrate_non_rigid: launch failed: %s", cudaGetErrorString(err)); return kCudaError; }
+	return kOk;
+}
+
+extern "C" int nnrt_b200_bounding_boxes_of_warped_blocks(const int32_t* block_keys, int64_t block_count, const float* nodes, const float* node_rotations,
+                                                         const float* node_translations, int32_t node_count, float node_coverage, int32_t anchor_count,
+                                                         int32_t minimum_valid_anchor_count, float voxel_size, int32_t block_resolution,
+                                                         const double* extrinsics_host, float* bounding_boxes, void* stream) {
+	if (block_count == 0) return kOk;
+	NNRT_CHECK_ARG(block_keys && nodes && node_rotations && node_translations && bounding_boxes, "bounding_boxes_of_warped_blocks: null pointer argument");
+	NNRT_CHECK_ARG(anchor_count >= 1 && anchor_count <= kMaxAnchors, "anchor_count must be in [1, %d], got %d", kMaxAnchors, anchor_count);
+	NNRT_CHECK_ARG(block_count > 0 && node_count > 0 && block_resolution >= 1, "bounding_boxes_of_warped_blocks: bad sizes");
+	cudaStream_t s = (cudaStream_t) stream;
+	const NodeField field{nodes, node_rotations, node_translations, node_count, nullptr, node_coverage * node_coverage, minimum_valid_anchor_count};
+	const float side = (float) block_resolution * voxel_size;
+	const Rigid extrinsics = rigid_from_host(extrinsics_host);
+	const unsigned grid = blocks_for(block_count * 8, kThreads);
+#define NNRT_BOX_CASE(A_) case A_: warped_block_boxes_kernel<A_><<<grid, kThreads, 0, s>>>(block_keys, block_count, field, side, extrinsics, bounding_boxes); break;
+	switch (anchor_count) {
+		NNRT_BOX_CASE(1) NNRT_BOX_CASE(2) NNRT_BOX_CASE(3) NNRT_BOX_CASE(4) NNRT_BOX_CASE(5) NNRT_BOX_CASE(6) NNRT_BOX_CASE(7) NNRT_BOX_CASE(8)
+	}
+#undef NNRT_BOX_CASE
+	NNRT_LAUNCH_CHECK();
+	return kOk;
+}
+
+extern "C" int nnrt_b200_boxes_intersecting_surface_mask(const float* boxes, int64_t box_count, const double* intrinsics_host, const void* depth,
+                                                         int32_t depth_dtype, int32_t image_height, int32_t image_width, float depth_scale, float depth_max,
+                                                         int32_t stride, float truncation_distance, uint8_t* mask, void* stream) {
+	if (box_count == 0) return kOk;
+	NNRT_CHECK_ARG(boxes && intrinsics_host && depth && mask, "boxes_intersecting_surface_mask: null pointer argument");
+	NNRT_CHECK_ARG(box_count > 0 && image_height > 0 && image_width > 0 && stride >= 1, "boxes_intersecting_surface_mask: bad sizes");
+	NNRT_CHECK_ARG(depth_dtype == 0 || depth_dtype == 1, "depth dtype must be float32 (0) or uint16 (1)");
+	boxes_intersecting_surface_kernel<<<blocks_for(box_count * 32, kThreads), kThreads, 0, (cudaStream_t) stream>>>(
+			boxes, box_count, intrinsics_from_host(intrinsics_host), depth, depth_dtype, image_height, image_width, depth_scale, depth_max, stride,
+			truncation_distance, mask);
+	NNRT_LAUNCH_CHECK();
 	return kOk;
 }

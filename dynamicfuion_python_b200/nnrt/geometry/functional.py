@@ -310,3 +310,38 @@ def warp_point_cloud_dual_quaternion(input_point_cloud, nodes, node_rotations, n
     pts = T.cuda(pts, torch.float32)
     wp, _ = _warp(pts, None, nodes, node_rotations, node_translations, anchors, anchor_weights, minimum_valid_anchor_count, extrinsics, dual_quaternion=True)
     return wp
+
+
+def bounding_boxes_of_warped_blocks(block_keys, warp_field, voxel_size, block_resolution, extrinsics=None):
+    """NonRigidSurfaceVoxelBlockGrid.GetBoundingBoxesOfWarpedBlocks (cpp/geometry/NonRigidSurfaceVoxelBlockGrid.cpp:120-130) -> [B,6] f32."""
+    keys = T.cuda(block_keys, torch.int32)
+    if keys.dim() != 2 or keys.shape[1] != 3:
+        raise RuntimeError(f"block_keys must have shape [B, 3], got {tuple(keys.shape)}")
+    ext = T.host_f64(torch.eye(4, dtype=torch.float64) if extrinsics is None else extrinsics, (4, 4))
+    boxes = T.empty((keys.shape[0], 6), torch.float32)
+    T.call("nnrt_b200_bounding_boxes_of_warped_blocks", T.ptr(keys), keys.shape[0], T.ptr(warp_field.nodes), T.ptr(warp_field.node_rotations),
+           T.ptr(warp_field.node_translations), warp_field.nodes.shape[0], float(warp_field.node_coverage), warp_field.anchor_count,
+           warp_field.minimum_valid_anchor_count, float(voxel_size), int(block_resolution), ext.data_ptr(), T.ptr(boxes), T.stream())
+    return boxes
+
+
+def axis_aligned_boxes_intersecting_surface_mask(boxes, depth, intrinsics, depth_scale, depth_max, downsampling_factor, truncation_distance):
+    """NonRigidSurfaceVoxelBlockGrid.GetAxisAlignedBoxesIntersectingSurfaceMask (cpp/geometry/NonRigidSurfaceVoxelBlockGrid.cpp:132-148);
+    `truncation_distance` = voxel_size * truncation_voxel_multiplier. Returns a bool mask [B]."""
+    b = T.cuda(boxes, torch.float32)
+    if b.dim() != 2 or b.shape[1] != 6:
+        raise RuntimeError(f"boxes must have shape [B, 6], got {tuple(b.shape)}")
+    d = T.to_torch(depth.as_tensor() if hasattr(depth, "as_tensor") else depth)
+    if d.dim() == 3:
+        d = d[..., 0]
+    if d.dtype in (torch.uint16, torch.int16):
+        d, code = T.cuda(d.view(torch.int16) if d.dtype == torch.uint16 else d, torch.int16), 1
+    elif d.dtype == torch.float32:
+        d, code = T.cuda(d, torch.float32), 0
+    else:
+        raise RuntimeError("depth must be UInt16 or Float32")
+    K = T.host_f64(intrinsics, (3, 3))
+    mask = T.empty((b.shape[0],), torch.uint8)
+    T.call("nnrt_b200_boxes_intersecting_surface_mask", T.ptr(b), b.shape[0], K.data_ptr(), T.ptr(d), code, int(d.shape[0]), int(d.shape[1]),
+           float(depth_scale), float(depth_max), int(downsampling_factor), float(truncation_distance), T.ptr(mask), T.stream())
+    return mask.to(torch.bool)

@@ -311,6 +311,22 @@ int nnrt_b200_integrate_non_rigid(const int64_t* block_indices, int64_t block_co
                                   float node_coverage, int32_t anchor_count, int32_t minimum_valid_anchor_count, float depth_scale,
                                   float depth_max, float* cos_voxel_ray_to_normal, void* stream);
 
+/* geometry::NonRigidSurfaceVoxelBlockGrid::GetBoundingBoxesOfWarpedBlocks (geometry/NonRigidSurfaceVoxelBlockGrid.cpp:120-130;
+ * kernel/NonRigidSurfaceVoxelBlockGridImpl.h:289-363): bounding_boxes [B,6] f32 (min xyz, max xyz) of the warped corners of each block
+ * key [B,3] int32. Fixed node coverage, as the reference's kernel. Its quirks are kept (see csrc/tsdf.cu). */
+int nnrt_b200_bounding_boxes_of_warped_blocks(const int32_t* block_keys, int64_t block_count, const float* nodes,
+                                              const float* node_rotations, const float* node_translations, int32_t node_count,
+                                              float node_coverage, int32_t anchor_count, int32_t minimum_valid_anchor_count,
+                                              float voxel_size, int32_t block_resolution, const double* extrinsics_host,
+                                              float* bounding_boxes, void* stream);
+/* geometry::NonRigidSurfaceVoxelBlockGrid::GetAxisAlignedBoxesIntersectingSurfaceMask (NonRigidSurfaceVoxelBlockGrid.cpp:132-148;
+ * kernel/NonRigidSurfaceVoxelBlockGridImpl.h:365-435; kernel/Segment.h): mask [B] u8 = the box is met by the truncation segment
+ * (depth -+ truncation_distance along the pixel ray) of some pixel sampled with `stride`. Together with the call above this is the
+ * device work of FindBlocksIntersectingTruncationRegion (NonRigidSurfaceVoxelBlockGrid.cpp:150-178). */
+int nnrt_b200_boxes_intersecting_surface_mask(const float* boxes, int64_t box_count, const double* intrinsics_host, const void* depth,
+                                              int32_t depth_dtype, int32_t image_height, int32_t image_width, float depth_scale,
+                                              float depth_max, int32_t stride, float truncation_distance, uint8_t* mask, void* stream);
+
 /* Per-stage device time of one iteration measured with CUDA events outside graph capture (ms):
  * [warp_vertices, face_raster, band_raster, assemble, build_system, stem_eliminate, corner_solve_update]. */
 int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,

@@ -469,3 +469,24 @@ def integrate_non_rigid(block_indices, block_keys, tsdf, weight, voxel_color, bl
         C.c_int(nodes.shape[0]), _p(ncw), C.c_float(node_coverage), C.c_int(anchor_count), C.c_int(minimum_valid_anchor_count),
         C.c_float(depth_scale), C.c_float(depth_max), _p(cos))
     return cos
+
+
+def bounding_boxes_of_warped_blocks(block_keys, nodes, node_rotations, node_translations, node_coverage, anchor_count, minimum_valid_anchor_count,
+                                    voxel_size, block_resolution, extrinsics):
+    keys = _i32(block_keys)
+    nodes, R, t = _f32(nodes), _f32(node_rotations), _f32(node_translations)
+    boxes = np.empty((keys.shape[0], 6), np.float32)
+    lib().oracle_bounding_boxes_of_warped_blocks(_p(keys), C.c_int64(keys.shape[0]), _p(nodes), _p(R), _p(t), C.c_int(nodes.shape[0]), C.c_float(node_coverage),
+                                                 C.c_int(anchor_count), C.c_int(minimum_valid_anchor_count), C.c_float(voxel_size), C.c_int(block_resolution),
+                                                 _p(_f64(extrinsics)), _p(boxes))
+    return boxes
+
+
+def boxes_intersecting_surface_mask(boxes, intrinsics, depth, depth_scale, depth_max, stride, truncation_distance):
+    boxes = _f32(boxes)
+    depth = np.ascontiguousarray(depth)
+    mask = np.empty(boxes.shape[0], np.uint8)
+    lib().oracle_boxes_intersecting_surface_mask(_p(boxes), C.c_int64(boxes.shape[0]), _p(_f64(intrinsics)), _p(depth), C.c_int(0 if depth.dtype == np.float32 else 1),
+                                                 C.c_int(depth.shape[0]), C.c_int(depth.shape[1]), C.c_float(depth_scale), C.c_float(depth_max), C.c_int(stride),
+                                                 C.c_float(truncation_distance), _p(mask))
+    return mask.astype(bool)

@@ -116,3 +116,105 @@ ORACLE_API void oracle_integrate_non_rigid(
 		}
 	}
 }
+
+#include <cfloat>
+
+// cpp/geometry/kernel/NonRigidSurfaceVoxelBlockGridImpl.h:289-363 (GetBoundingBoxesOfWarpedBlocks), quirks included: corner = block key
+// (in blocks) + block side (in metres); fixed coverage always; ComputeAnchorsForPoint's result ignored (a corner with too few valid
+// anchors is blended with raw weights); `if (min > x) min = x; else if (max < x) max = x`.
+ORACLE_API void oracle_bounding_boxes_of_warped_blocks(const int32_t* block_keys, int64_t block_count, const float* nodes, const float* node_rotations,
+                                                       const float* node_translations, int node_count, float node_coverage, int anchor_count,
+                                                       int minimum_valid_anchor_count, float voxel_size, int block_resolution, const double* extrinsics,
+                                                       float* boxes) {
+	TransformIndexer transform(IDENTITY3, extrinsics, 1.0f);
+	const float side = (float) block_resolution * voxel_size;
+	const float c2 = node_coverage * node_coverage;
+	static const int corner_bits[8][3] = {{0, 0, 0}, {0, 0, 1}, {0, 1, 0}, {1, 0, 0}, {0, 1, 1}, {1, 0, 1}, {1, 1, 0}, {1, 1, 1}};
+	for (int64_t b = 0; b < block_count; b++) {
+		const float x0 = (float) block_keys[b * 3], y0 = (float) block_keys[b * 3 + 1], z0 = (float) block_keys[b * 3 + 2];
+		float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+		for (int c = 0; c < 8; c++) {
+			V3 corner;
+			transform.RigidTransform(corner_bits[c][0] ? x0 + side : x0, corner_bits[c][1] ? y0 + side : y0, corner_bits[c][2] ? z0 + side : z0,
+			                         &corner.x, &corner.y, &corner.z);
+			int32_t idx[MAX_ANCHOR_COUNT];
+			float w[MAX_ANCHOR_COUNT];
+			for (int a = 0; a < anchor_count; a++) { idx[a] = -1; w[a] = INFINITY; }
+			int max_at = 0;
+			float max_distance = INFINITY;
+			for (int n = 0; n < node_count; n++) {
+				V3 d = sub(load3(nodes + n * 3), corner);
+				float distance = sqrtf(dot3(d, d));
+				if (max_distance > distance) {
+					w[max_at] = distance; idx[max_at] = n;
+					max_at = 0; max_distance = w[0];
+					for (int a = 1; a < anchor_count; a++) if (w[a] > max_distance) { max_at = a; max_distance = w[a]; }
+				}
+			}
+			float weight_sum = 0.0f;
+			int valid = 0;
+			for (int a = 0; a < anchor_count; a++) {
+				float square_distance = w[a] * w[a];
+				if (square_distance > 4 * c2) { idx[a] = -1; continue; }
+				float anchor_weight = expf(-square_distance / (2 * c2));
+				weight_sum += anchor_weight; w[a] = anchor_weight; valid++;
+			}
+			if (valid >= minimum_valid_anchor_count) {
+				if (weight_sum > 0.0f) { for (int a = 0; a < anchor_count; a++) w[a] /= weight_sum; }
+				else if (valid > 0) { for (int a = 0; a < anchor_count; a++) w[a] = 1.0f / (float) valid; }
+			}
+			V3 warped = {0.f, 0.f, 0.f};
+			for (int a = 0; a < anchor_count; a++) {
+				int n = idx[a];
+				if (n == -1) continue;
+				V3 g = load3(nodes + n * 3), t = load3(node_translations + n * 3);
+				warped = add(warped, scale(w[a], add(add(g, matvec(node_rotations + n * 9, sub(corner, g))), t)));
+			}
+			const float v[3] = {warped.x, warped.y, warped.z};
+			for (int k = 0; k < 3; k++) {
+				if (lo[k] > v[k]) lo[k] = v[k];
+				else if (hi[k] < v[k]) hi[k] = v[k];
+			}
+		}
+		for (int k = 0; k < 3; k++) { boxes[b * 6 + k] = lo[k]; boxes[b * 6 + 3 + k] = hi[k]; }
+	}
+}
+
+// cpp/geometry/kernel/NonRigidSurfaceVoxelBlockGridImpl.h:365-435 + cpp/geometry/kernel/Segment.h:27-73: every (segment, box) pair
+ORACLE_API void oracle_boxes_intersecting_surface_mask(const float* boxes, int64_t box_count, const double* intrinsics, const void* depth, int depth_dtype,
+                                                       int height, int width, float depth_scale, float depth_max, int stride, float truncation,
+                                                       uint8_t* mask) {
+	TransformIndexer transform(intrinsics, IDENTITY4, 1.0f);
+	struct Segment { V3 origin, inv; int sign[3]; };
+	std::vector<Segment> segments;
+	const int rows = height / stride, cols = width / stride;
+	for (int64_t i = 0; i < (int64_t) rows * cols; i++) {
+		int v = (int) (i / cols) * stride, u = (int) (i % cols) * stride;
+		float d = (depth_dtype == 0 ? ((const float*) depth)[(int64_t) v * width + u] : (float) ((const uint16_t*) depth)[(int64_t) v * width + u]) / depth_scale;
+		if (d > 0 && d < depth_max) {
+			V3 start, end;
+			transform.Unproject((float) u, (float) v, d - truncation, &start.x, &start.y, &start.z);
+			transform.Unproject((float) u, (float) v, d + truncation, &end.x, &end.y, &end.z);
+			V3 vec = sub(end, start);
+			Segment s{start, {1.f / vec.x, 1.f / vec.y, 1.f / vec.z}, {0, 0, 0}};
+			s.sign[0] = s.inv.x < 0; s.sign[1] = s.inv.y < 0; s.sign[2] = s.inv.z < 0;
+			segments.push_back(s);
+		}
+	}
+	for (int64_t b = 0; b < box_count; b++) {
+		const float* box = boxes + b * 6;
+		mask[b] = 0;
+		for (const Segment& s : segments) {
+			float t_min = (box[s.sign[0] ? 3 : 0] - s.origin.x) * s.inv.x, t_max = (box[s.sign[0] ? 0 : 3] - s.origin.x) * s.inv.x;
+			float ty_min = (box[s.sign[1] ? 4 : 1] - s.origin.y) * s.inv.y, ty_max = (box[s.sign[1] ? 1 : 4] - s.origin.y) * s.inv.y;
+			if ((t_min > ty_max) || (ty_min > t_max)) continue;
+			if (ty_min > t_min) t_min = ty_min;
+			if (ty_max < t_max) t_max = ty_max;
+			float tz_min = (box[s.sign[2] ? 5 : 2] - s.origin.z) * s.inv.z, tz_max = (box[s.sign[2] ? 2 : 5] - s.origin.z) * s.inv.z;
+			if ((t_min > tz_max) || (tz_min > t_max)) continue;
+			if (tz_min > t_min) t_min = tz_min;
+			if (tz_max < t_max) t_max = tz_max;
+			if (!(t_max < 0.0f || t_min > 1.0f)) { mask[b] = 1; break; }
+		}
+	}
+}

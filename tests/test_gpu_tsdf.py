@@ -96,3 +96,37 @@ def test_integrate_non_rigid_matches_oracle(nnrt, oracle, depth_u16, with_color,
         assert color_off.sum() <= 1e-3 * both.sum()
         assert (color_o != c["voxel_color"]).any()
     assert np.array_equal(values["weight"].cpu().numpy(), weight_t.cpu().numpy())  # weights are read only, as in the reference
+
+
+def test_block_selection_matches_oracle(nnrt, oracle):
+    """The device work of FindBlocksIntersectingTruncationRegion: bounding boxes of warped blocks (quirks of the reference included) and
+    the box / truncation-segment mask, which visits only the pixels inside a box's projected rectangle yet must equal the reference's
+    all-pairs result."""
+    c = _scene(oracle, False, False, False)
+    s = c["s"]
+    G = nnrt.geometry
+    f = G.functional
+    ext = np.eye(4)
+    ext[:3, 3] = [0.002, -0.001, 0.003]
+    for min_valid, coverage in ((0, 0.3), (2, 0.2), (3, 0.05)):
+        # the reference adds a side in metres to a key in blocks: keys near the surface's metric coordinates keep the test meaningful
+        rng = np.random.default_rng(min_valid)
+        keys = np.concatenate([rng.integers(-1, 1, (300, 3)), np.array([[0, 0, 0], [-1, -1, 0], [5, 5, 5]])]).astype(np.int32)
+        wf = G.GraphWarpField(s["nodes"], coverage, True, 4, min_valid, G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE)
+        wf.set_node_rotations(s["rotations_gt"])
+        wf.set_node_translations(s["translations_gt"])
+        boxes = f.bounding_boxes_of_warped_blocks(keys, wf, c["voxel_size"], c["R"], ext)
+        want = oracle.bounding_boxes_of_warped_blocks(keys, s["nodes"], s["rotations_gt"], s["translations_gt"], coverage, 4, min_valid, c["voxel_size"], c["R"], ext)
+        np.testing.assert_allclose(boxes.cpu().numpy(), want, rtol=1e-5, atol=1e-6)
+    # boxes around the surface, in front of the camera, behind it, inverted (max < min) and far off to the side
+    rng = np.random.default_rng(5)
+    centres = np.concatenate([s["positions"][rng.choice(len(s["positions"]), 400)] + rng.normal(0, 0.03, (400, 3)), rng.uniform(-1, 1, (200, 3)) * [1.0, 1.0, 2.0]])
+    half = rng.uniform(0.002, 0.05, (600, 3))
+    boxes = np.concatenate([centres - half, centres + half], 1).astype(np.float32)
+    boxes[-20:] = np.concatenate([boxes[-20:, 3:], boxes[-20:, :3]], 1)  # inverted
+    boxes[-40:-20, 2] = -0.5  # reach behind the camera
+    for depth, scale, stride in ((c["depth"], 1.0, 4), (np.round(c["depth"] * 1000).astype(np.uint16), 1000.0, 1), (c["depth"], 1.0, 7)):
+        got = f.axis_aligned_boxes_intersecting_surface_mask(boxes, depth, s["K"], scale, 3.0, stride, 2 * c["voxel_size"])
+        want = oracle.boxes_intersecting_surface_mask(boxes, s["K"], depth, scale, 3.0, stride, 2 * c["voxel_size"])
+        assert 20 < want.sum() < 580
+        assert np.array_equal(got.cpu().numpy(), want)

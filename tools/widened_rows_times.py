@@ -116,6 +116,24 @@ def main():
            12 * voxels + 16 * H * W, cpu, bound="issue (N distance evaluations per voxel)", oracle_note=f"extrapolated from {len(sample)} blocks",
            voxel_node_pairs_per_s=round(voxels * N / ms * 1e3 / 1e9, 1))
 
+    # block selection of FindBlocksIntersectingTruncationRegion: 27 neighbours of every block; 12 B key in, 24 B box out, then 24 B box in, 1 B out
+    neighbours = np.unique((keys[:, None, :] + np.stack(np.meshgrid(*[np.arange(-1, 2)] * 3, indexing="ij"), -1).reshape(1, 27, 3)).reshape(-1, 3), axis=0).astype(np.int32)
+    keys_t = torch.as_tensor(neighbours).cuda()
+    ms = gpu_ms(lambda: f.bounding_boxes_of_warped_blocks(keys_t, wf, voxel, R))
+    report("bounding_boxes_of_warped_blocks", f"{len(neighbours)} block keys x 8 corners, {N} nodes", ms, 36 * len(neighbours),
+           cpu_ms(lambda: oracle.bounding_boxes_of_warped_blocks(neighbours, s["nodes"], s["rotations_gt"], s["translations_gt"], 0.02, 4, 1, voxel, R, np.eye(4))),
+           bound="issue (N distance evaluations per corner)")
+    centres = (neighbours.astype(np.float32) + 0.5) * block  # metric boxes of the same blocks (the reference's own boxes mix units)
+    metric_boxes = np.concatenate([centres - block / 2, centres + block / 2], 1).astype(np.float32)
+    boxes_t, depth_t = torch.as_tensor(metric_boxes).cuda(), torch.as_tensor(depth_img).cuda()
+    ms = gpu_ms(lambda: f.axis_aligned_boxes_intersecting_surface_mask(boxes_t, depth_t, s["K"], 1.0, 3.0, 4, 2 * voxel))
+    segments = int((depth_img[::4, ::4] > 0).sum())
+    hits = int(oracle.boxes_intersecting_surface_mask(metric_boxes, s["K"], depth_img, 1.0, 3.0, 4, 2 * voxel).sum())
+    report("axis_aligned_boxes_intersecting_surface_mask", f"{len(metric_boxes)} boxes x {segments} segments ({W}x{H}, stride 4), {hits} hits", ms,
+           25 * len(metric_boxes) + 4 * (H // 4) * (W // 4),
+           cpu_ms(lambda: oracle.boxes_intersecting_surface_mask(metric_boxes, s["K"], depth_img, 1.0, 3.0, 4, 2 * voxel)),
+           bound="latency (a warp per box over its projected pixel rectangle)", reference_pairs=len(metric_boxes) * segments)
+
 
 if __name__ == "__main__":
     main()
