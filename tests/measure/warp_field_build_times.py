@@ -8,10 +8,10 @@ import time
 import numpy as np
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from dynamicfuion_python_b200 import nnrt, synthetic  # noqa: E402
-from oracle import oracle_py as oracle  # noqa: E402  (CPU baseline of this tool only)
+from oracle import oracle_py as oracle  # noqa: E402  (CPU baseline; measurement scripts live under tests/ because only tests may use the oracle)
 
 
 def timed(fn, repeats=20):

@@ -30,13 +30,14 @@ def test_c_abi_exports_every_declared_symbol():
 
 
 def test_no_cpu_fallback_in_product_path():
-    """The product package never imports the oracle, and asking for a device without CUDA raises instead of falling back."""
-    pkg = os.path.join(ROOT, "dynamicfuion_python_b200")
-    for dirpath, _, files in os.walk(pkg):
-        for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".h")):
-                text = open(os.path.join(dirpath, f)).read()
-                assert "oracle_py" not in text and "liboracle" not in text, f"{f} references the oracle"
+    """Neither the product package nor tools/ ever imports the oracle (measurement scripts that time it live under tests/measure),
+    and asking for a device without CUDA raises instead of falling back."""
+    for top in ("dynamicfuion_python_b200", "tools", "include"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, top)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".h", ".sh")):
+                    text = open(os.path.join(dirpath, f)).read()
+                    assert "oracle_py" not in text and "liboracle" not in text, f"{top}/{f} references the oracle"
     if not torch.cuda.is_available():
         from dynamicfuion_python_b200.nnrt import _tensor
         with pytest.raises(RuntimeError):
