@@ -41,6 +41,8 @@ _SIGNATURES = {
     "nnrt_b200_shade_vertex_colors": (C.c_int, [P, P, I32, I32, I32, P, P, P]),
     "nnrt_b200_integrate_non_rigid": (C.c_int, [P, I64, P, P, P, I32, P, I32, F32, F32, P, I32, P, I32, P, I32, I32, I32, I32, P, P, P, P, P, P, I32, P,
                                                 F32, I32, I32, F32, F32, P, P]),
+    "nnrt_b200_integrate_non_rigid_full_scan": (C.c_int, [P, I64, P, P, P, I32, P, I32, F32, F32, P, I32, P, I32, P, I32, I32, I32, I32, P, P, P, P, P, P, I32, P,
+                                                F32, I32, I32, F32, F32, P, P]),
     "nnrt_b200_bounding_boxes_of_warped_blocks": (C.c_int, [P, I64, P, P, P, I32, F32, I32, I32, F32, I32, P, P, P]),
     "nnrt_b200_boxes_intersecting_surface_mask": (C.c_int, [P, I64, P, P, I32, I32, I32, F32, F32, I32, F32, P, P]),
     "nnrt_b200_fitter_default_options": (None, [P]),

@@ -265,6 +265,7 @@ __global__ void __launch_bounds__(256) warped_surface_jacobians_kernel(
 // dropped, as there. anchors must be pre-filled with -1 (the exclusion scan reads all `anchor_count` slots, as the reference's does).
 constexpr int kPathQueueCapacity = 40;
 constexpr int kPathThreads = 64;
+constexpr int kPathNodeCache = 1536;  // 18 KB next to the 20 KB of queues
 
 struct PathQueue {
 	float* keys;  // [kPathQueueCapacity][kPathThreads]
@@ -318,6 +319,13 @@ __global__ void __launch_bounds__(kPathThreads) anchors_shortest_path_kernel(con
                                                                              int32_t* __restrict__ anchors, float* __restrict__ weights) {
 	__shared__ float queue_keys[kPathQueueCapacity * kPathThreads];
 	__shared__ int queue_nodes[kPathQueueCapacity * kPathThreads];
+	// node positions are read N times per point by the seeding scan and again along every edge: staged in shared memory when they fit
+	__shared__ float s_nodes[kPathNodeCache * 3];
+	const bool cached = node_count <= kPathNodeCache;
+	if (cached)
+		for (int k = threadIdx.x; k < node_count * 3; k += blockDim.x) s_nodes[k] = nodes[k];
+	__syncthreads();
+	const float* __restrict__ node_xyz = cached ? s_nodes : nodes;
 	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= point_count) return;
 	const float px = points[i * 3], py = points[i * 3 + 1], pz = points[i * 3 + 2];
@@ -335,7 +343,7 @@ __global__ void __launch_bounds__(kPathThreads) anchors_shortest_path_kernel(con
 #pragma unroll
 			for (int a = 0; a < A; a++) excluded |= idx[a] == n;
 			if (excluded) continue;
-			const float dx = __ldg(nodes + n * 3) - px, dy = __ldg(nodes + n * 3 + 1) - py, dz = __ldg(nodes + n * 3 + 2) - pz;
+			const float dx = node_xyz[n * 3] - px, dy = node_xyz[n * 3 + 1] - py, dz = node_xyz[n * 3 + 2] - pz;
 			const float d2 = sum3(dx * dx, dy * dy, dz * dz);
 			if (d2 < closest_d2) { closest_d2 = d2; closest = n; }
 		}
@@ -354,11 +362,11 @@ __global__ void __launch_bounds__(kPathThreads) anchors_shortest_path_kernel(con
 				if (a == discovered) { dist[a] = source_key; idx[a] = source; }
 			discovered++;
 			if (discovered >= A) break;
-			const float sx = __ldg(nodes + source * 3), sy = __ldg(nodes + source * 3 + 1), sz = __ldg(nodes + source * 3 + 2);
+			const float sx = node_xyz[source * 3], sy = node_xyz[source * 3 + 1], sz = node_xyz[source * 3 + 2];
 			for (int e = 0; e < graph_degree; e++) {
 				const int target = __ldg(edges + (int64_t) source * graph_degree + e);
 				if (target > -1) {
-					const float dx = __ldg(nodes + target * 3) - sx, dy = __ldg(nodes + target * 3 + 1) - sy, dz = __ldg(nodes + target * 3 + 2) - sz;
+					const float dx = node_xyz[target * 3] - sx, dy = node_xyz[target * 3 + 1] - sy, dz = node_xyz[target * 3 + 2] - sz;
 					queue.insert(source_key + sqrtf(sum3(dx * dx, dy * dy, dz * dz)), target);
 				}
 			}

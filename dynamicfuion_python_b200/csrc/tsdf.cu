@@ -38,20 +38,88 @@ __device__ __forceinline__ bool in_boundary(float x, float y, int rows, int cols
 	return y >= 0 && x >= 0 && y <= rows - 1.0f && x <= cols - 1.0f;
 }
 
-// WarpField::ComputeAnchorsForPoint<threshold = true> + WarpPoint (geometry/WarpField.h:77-122) for one point per thread; every thread
-// of the CTA must call it (the node tiles are staged cooperatively). Returns false when fewer than min_valid anchors survive the
-// distance threshold; with `warp_anyway` the point is then still blended with the raw, un-normalised weights of the surviving
-// anchors, which is what a caller that ignores ComputeAnchorsForPoint's result gets (GetBoundingBoxesOfWarpedBlocks).
+// K nearest nodes by DISTANCE (norm), replace-current-maximum in the order the candidates are offered (core/kernel/KnnUtilities.h:144-218
+// without the kd-tree). Candidates are screened on the squared distance: m * m * (1 + 1e-6) exceeds the exact m^2 whatever the
+// roundings do; above it the correctly rounded root cannot be below m, so only the few candidates near the current k-th distance pay
+// for the IEEE square root the comparison is defined on.
 template<int A>
-__device__ __forceinline__ bool warp_thresholded(const NodeField& p, float3 voxel, bool active, float4* tile, bool warp_anyway, float3& warped_out) {
-	warped_out = make_float3(0.f, 0.f, 0.f);
-	// --- K nearest nodes by distance (norm), replace-current-maximum in ascending node order
+struct NearestNodes {
 	int idx[A];
 	float w[A], c2s[A];
+	int max_at;
+	float max_distance, skip_above;
+	__device__ __forceinline__ void init(float default_c2) {
 #pragma unroll
-	for (int a = 0; a < A; a++) { idx[a] = -1; w[a] = INFINITY; c2s[a] = p.node_weights ? p.node_weights[0] : p.fixed_c2; }
-	int max_at = 0;
-	float max_distance = INFINITY, skip_above = INFINITY;
+		for (int a = 0; a < A; a++) { idx[a] = -1; w[a] = INFINITY; c2s[a] = default_c2; }
+		max_at = 0;
+		max_distance = INFINITY;
+		skip_above = INFINITY;
+	}
+	__device__ __forceinline__ void offer(float4 g, int index, float3 point) {
+		const float dx = g.x - point.x, dy = g.y - point.y, dz = g.z - point.z;
+		const float d2 = sum3(dx * dx, dy * dy, dz * dz);
+		if (d2 > skip_above) return;
+		const float distance = sqrtf(d2);
+		if (max_distance > distance) {
+#pragma unroll
+			for (int a = 0; a < A; a++)
+				if (a == max_at) { w[a] = distance; idx[a] = index; c2s[a] = g.w; }
+			max_at = 0;
+			max_distance = w[0];
+#pragma unroll
+			for (int a = 1; a < A; a++)
+				if (w[a] > max_distance) { max_at = a; max_distance = w[a]; }
+			skip_above = max_distance * max_distance * 1.000001f;
+		}
+	}
+	// thresholded weights (geometry/functional/kernel/WarpUtilities.h:95-153, distances not squared), normalisation (:36-46) and blend
+	// warp (:428-445). Returns false when fewer than min_valid anchors survive; with `warp_anyway` the point is then still blended with
+	// the raw, un-normalised weights of the surviving anchors (what a caller that ignores ComputeAnchorsForPoint's result gets).
+	__device__ __forceinline__ bool finish(const NodeField& p, float3 point, bool warp_anyway, float3& warped_out) {
+		float weight_sum = 0.0f;
+		int valid = 0;
+#pragma unroll
+		for (int a = 0; a < A; a++) {
+			const float square_distance = w[a] * w[a];
+			if (square_distance > 4 * c2s[a]) { idx[a] = -1; continue; }
+			const float anchor_weight = expf(-square_distance / (2 * c2s[a]));
+			weight_sum += anchor_weight;
+			w[a] = anchor_weight;
+			valid++;
+		}
+		const bool enough = valid >= p.min_valid;
+		warped_out = make_float3(0.f, 0.f, 0.f);
+		if (!enough && !warp_anyway) return false;
+		if (!enough) {
+			// weights stay raw
+		} else if (weight_sum > 0.0f) {
+#pragma unroll
+			for (int a = 0; a < A; a++) w[a] = __fdiv_rn(w[a], weight_sum);
+		} else if (valid > 0) {
+#pragma unroll
+			for (int a = 0; a < A; a++) w[a] = 1.0f / (float) valid;
+		}
+		float3 warped = make_float3(0.f, 0.f, 0.f);
+#pragma unroll
+		for (int a = 0; a < A; a++) {
+			const int n = idx[a];
+			if (n == -1) continue;
+			const float3 g = make_float3(p.nodes[n * 3], p.nodes[n * 3 + 1], p.nodes[n * 3 + 2]);
+			const float3 t = make_float3(p.translations[n * 3], p.translations[n * 3 + 1], p.translations[n * 3 + 2]);
+			warped = warped + w[a] * ((g + matvec3(p.rotations + (int64_t) n * 9, point - g)) + t);
+		}
+		warped_out = warped;
+		return enough;
+	}
+};
+
+// WarpField::ComputeAnchorsForPoint<threshold = true> + WarpPoint (geometry/WarpField.h:77-122) for one point per thread over ALL nodes,
+// staged through shared memory in tiles; every thread of the CTA must call it.
+template<int A>
+__device__ __forceinline__ bool warp_thresholded(const NodeField& p, float3 point, bool active, float4* tile, bool warp_anyway, float3& warped_out) {
+	warped_out = make_float3(0.f, 0.f, 0.f);
+	NearestNodes<A> nearest;
+	nearest.init(p.node_weights ? p.node_weights[0] : p.fixed_c2);
 	for (int base = 0; base < p.node_count; base += kNodeTile) {
 		const int count = min(kNodeTile, p.node_count - base);
 		__syncthreads();
@@ -61,86 +129,15 @@ __device__ __forceinline__ bool warp_thresholded(const NodeField& p, float3 voxe
 		}
 		__syncthreads();
 		if (!active) continue;
-		for (int k = 0; k < count; k++) {
-			const float4 g = tile[k];
-			const float dx = g.x - voxel.x, dy = g.y - voxel.y, dz = g.z - voxel.z;
-			const float d2 = sum3(dx * dx, dy * dy, dz * dz);
-			if (d2 > skip_above) continue;  // screened on the squared distance: sqrt(d2) >= max_distance for certain (see below)
-			const float distance = sqrtf(d2);
-			if (max_distance > distance) {
-#pragma unroll
-				for (int a = 0; a < A; a++)
-					if (a == max_at) { w[a] = distance; idx[a] = base + k; c2s[a] = g.w; }
-				max_at = 0;
-				max_distance = w[0];
-#pragma unroll
-				for (int a = 1; a < A; a++)
-					if (w[a] > max_distance) { max_at = a; max_distance = w[a]; }
-				// m * m * (1 + 1e-6) exceeds the exact m^2 whatever the roundings do; above it the correctly rounded root cannot be
-				// below m, so only the few candidates near the current k-th distance pay for the IEEE square root
-				skip_above = max_distance * max_distance * 1.000001f;
-			}
-		}
+		for (int k = 0; k < count; k++) nearest.offer(tile[k], base + k, point);
 	}
 	if (!active) return false;
-	// --- thresholded weights (geometry/functional/kernel/WarpUtilities.h:95-153, distances not squared) and normalisation (:36-46)
-	float weight_sum = 0.0f;
-	int valid = 0;
-#pragma unroll
-	for (int a = 0; a < A; a++) {
-		const float square_distance = w[a] * w[a];
-		if (square_distance > 4 * c2s[a]) { idx[a] = -1; continue; }
-		const float anchor_weight = expf(-square_distance / (2 * c2s[a]));
-		weight_sum += anchor_weight;
-		w[a] = anchor_weight;
-		valid++;
-	}
-	const bool enough = valid >= p.min_valid;
-	if (!enough && !warp_anyway) return false;
-	if (!enough) {
-		// weights stay raw
-	} else if (weight_sum > 0.0f) {
-#pragma unroll
-		for (int a = 0; a < A; a++) w[a] = __fdiv_rn(w[a], weight_sum);
-	} else if (valid > 0) {
-#pragma unroll
-		for (int a = 0; a < A; a++) w[a] = 1.0f / (float) valid;
-	}
-	// --- blend warp (WarpUtilities.h:428-445)
-	float3 warped = make_float3(0.f, 0.f, 0.f);
-#pragma unroll
-	for (int a = 0; a < A; a++) {
-		const int n = idx[a];
-		if (n == -1) continue;
-		const float3 g = make_float3(p.nodes[n * 3], p.nodes[n * 3 + 1], p.nodes[n * 3 + 2]);
-		const float3 t = make_float3(p.translations[n * 3], p.translations[n * 3 + 1], p.translations[n * 3 + 2]);
-		warped = warped + w[a] * ((g + matvec3(p.rotations + (int64_t) n * 9, voxel - g)) + t);
-	}
-	warped_out = warped;
-	return enough;
+	return nearest.finish(p, point, warp_anyway, warped_out);
 }
 
-template<int A>
-__global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(IntegrateParams p) {
-	__shared__ float4 tile[kNodeTile];
-	const int64_t workload = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-	const bool active = workload < p.voxel_count;
-	const int r = p.block_resolution;
-	const int64_t r3 = (int64_t) r * r * r;
-	int64_t block_index = 0, voxel_in_block = 0;
-	float3 voxel = make_float3(0.f, 0.f, 0.f);
-	if (active) {
-		block_index = p.block_indices[workload / r3];
-		voxel_in_block = workload % r3;
-		const int32_t* key = p.block_keys + block_index * 3;
-		const int xl = (int) (voxel_in_block % r), yl = (int) ((voxel_in_block / r) % r), zl = (int) (voxel_in_block / ((int64_t) r * r));
-		const float3 metric = make_float3((float) (key[0] * r + xl) * p.voxel_size, (float) (key[1] * r + yl) * p.voxel_size,
-		                                  (float) (key[2] * r + zl) * p.voxel_size);
-		voxel = rigid_transform(p.extrinsics, metric);
-	}
-	float3 warped;
-	const bool warp_ok = warp_thresholded<A>(p.field, voxel, active, tile, false, warped);
-	if (!active || !warp_ok) return;
+// everything after the warp: projection, depth / normal lookup, gates, running averages (NonRigidSurfaceVoxelBlockGridImpl.h:160-226)
+__device__ __forceinline__ void integrate_warped_voxel(const IntegrateParams& p, int64_t workload, int64_t block_index, int64_t voxel_in_block, int64_t r3,
+                                                       float3 warped) {
 	if (warped.z < 0) return;
 	const float2 uv = project(p.depth_k, warped);
 	if (!in_boundary(uv.x, uv.y, p.height, p.width)) return;
@@ -177,6 +174,127 @@ __global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(Integrate
 				p.voxel_color[linear * 3 + c] = (voxel_weight * p.voxel_color[linear * 3 + c] + in * multiplier) * inverted_weight_sum;
 			}
 		}
+	}
+}
+
+__device__ __forceinline__ float3 voxel_camera_position(const IntegrateParams& p, int64_t block_index, int64_t voxel_in_block) {
+	const int r = p.block_resolution;
+	const int32_t* key = p.block_keys + block_index * 3;
+	const int xl = (int) (voxel_in_block % r), yl = (int) ((voxel_in_block / r) % r), zl = (int) (voxel_in_block / ((int64_t) r * r));
+	return rigid_transform(p.extrinsics, make_float3((float) (key[0] * r + xl) * p.voxel_size, (float) (key[1] * r + yl) * p.voxel_size,
+	                                                 (float) (key[2] * r + zl) * p.voxel_size));
+}
+
+// Full-scan form: one thread per voxel, every node offered to every voxel. Kept as the yardstick the shortlist kernel below must equal
+// bit for bit (nnrt_b200_integrate_non_rigid_full_scan).
+template<int A>
+__global__ void __launch_bounds__(kThreads) integrate_non_rigid_kernel(IntegrateParams p) {
+	__shared__ float4 tile[kNodeTile];
+	const int64_t workload = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	const bool active = workload < p.voxel_count;
+	const int64_t r3 = (int64_t) p.block_resolution * p.block_resolution * p.block_resolution;
+	int64_t block_index = 0, voxel_in_block = 0;
+	float3 voxel = make_float3(0.f, 0.f, 0.f);
+	if (active) {
+		block_index = p.block_indices[workload / r3];
+		voxel_in_block = workload % r3;
+		voxel = voxel_camera_position(p, block_index, voxel_in_block);
+	}
+	float3 warped;
+	const bool warp_ok = warp_thresholded<A>(p.field, voxel, active, tile, false, warped);
+	if (!active || !warp_ok) return;
+	integrate_warped_voxel(p, workload, block_index, voxel_in_block, r3, warped);
+}
+
+// Shortlist form: one CTA per voxel block. A node can enter a voxel's anchor slots only while it is closer to that voxel than the
+// voxel's current A-th distance. With c the block centre and r the half diagonal, every voxel v of the block has
+// |n - v| >= |n - c| - r and (A-th distance of v among the nodes before n) <= U + r, where U is the A-th smallest distance to c among
+// nodes before n. So a node with |n - c| >= U + 2r is never inserted for any voxel of the block and may be left out of the scan without
+// changing a single slot — provided U is the RUNNING bound over the node order (a node that no voxel keeps in the end can still sit in a
+// slot for a while and decide where later nodes land). Warp 0 walks the nodes in chunks of 32 in index order, tests each chunk against
+// the bound of the chunks before it (a superset of the nodes before n gives a smaller U, so the chunk-level bound is only more
+// conservative), appends the survivors to the shortlist in order and folds the chunk into the running A smallest distances. The voxels
+// then scan the shortlist instead of all N nodes: same slots, same weights, same sums (checked bit for bit against the full scan).
+constexpr int kShortlist = kNodeTile;  // entries; a block whose shortlist overflows falls back to the full scan
+constexpr int kBlockThreads = 256;
+
+template<int A>
+__global__ void __launch_bounds__(kBlockThreads) integrate_blocks_kernel(IntegrateParams p) {
+	__shared__ float4 s_node[kShortlist];  // doubles as the tile buffer of the fallback
+	__shared__ int s_index[kShortlist];
+	__shared__ int s_count;
+	const int r = p.block_resolution;
+	const int64_t r3 = (int64_t) r * r * r;
+	const int64_t block_index = p.block_indices[blockIdx.x];
+	const NodeField& f = p.field;
+	if (threadIdx.x < 32) {
+		const int lane = threadIdx.x;
+		const int32_t* key = p.block_keys + block_index * 3;
+		const float half = 0.5f * (float) (r - 1);
+		const float3 centre = rigid_transform(p.extrinsics, make_float3(((float) (key[0] * r) + half) * p.voxel_size, ((float) (key[1] * r) + half) * p.voxel_size,
+		                                                              ((float) (key[2] * r) + half) * p.voxel_size));
+		// half diagonal of the cube of voxel centres, padded for the fp32 rounding of voxel and centre positions
+		const float reach = 2.f * (half * p.voxel_size * 1.7320509f * 1.0001f + 1e-6f);
+		float smallest[A];  // running A smallest distances to the centre, ascending, identical in every lane
+#pragma unroll
+		for (int a = 0; a < A; a++) smallest[a] = INFINITY;
+		int count = 0;
+		for (int base = 0; base < f.node_count; base += 32) {
+			const int n = base + lane;
+			float distance = INFINITY;
+			float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+			if (n < f.node_count) {
+				g = make_float4(f.nodes[n * 3], f.nodes[n * 3 + 1], f.nodes[n * 3 + 2], f.node_weights ? f.node_weights[n] : f.fixed_c2);
+				const float dx = g.x - centre.x, dy = g.y - centre.y, dz = g.z - centre.z;
+				distance = sqrtf(sum3(dx * dx, dy * dy, dz * dz));
+			}
+			const float bound = (smallest[A - 1] + reach) * 1.00001f;  // inf while fewer than A nodes have been seen
+			const bool keep = n < f.node_count && distance < bound;
+			const unsigned kept = __ballot_sync(0xFFFFFFFFu, keep);
+			const int slot = count + __popc(kept & ((1u << lane) - 1u));
+			if (keep && slot < kShortlist) { s_node[slot] = g; s_index[slot] = n; }
+			count += __popc(kept);
+			if (count > kShortlist) break;  // uniform: falls back
+			// fold the chunk into the running A smallest: repeated warp minimum over the chunk, merged into the sorted list
+			float mine = distance;
+			while (__any_sync(0xFFFFFFFFu, mine < smallest[A - 1])) {
+				float best = mine;
+#pragma unroll
+				for (int offset = 16; offset > 0; offset >>= 1) best = fminf(best, __shfl_xor_sync(0xFFFFFFFFu, best, offset));
+				const unsigned owners = __ballot_sync(0xFFFFFFFFu, mine == best);
+				if (lane == __ffs(owners) - 1) mine = INFINITY;  // one lane gives up its value per round (duplicates stay for the next)
+				float carry = best;  // insertion into the ascending list
+#pragma unroll
+				for (int a = 0; a < A; a++) {
+					const float lower = fminf(smallest[a], carry);
+					carry = fmaxf(smallest[a], carry);
+					smallest[a] = lower;
+				}
+			}
+		}
+		if (lane == 0) s_count = count;
+	}
+	__syncthreads();
+	const int count = s_count;
+	const bool fallback = count > kShortlist;
+	for (int64_t base = 0; base < r3; base += kBlockThreads) {
+		const int64_t voxel_in_block = base + threadIdx.x;
+		const bool active = voxel_in_block < r3;
+		const float3 voxel = active ? voxel_camera_position(p, block_index, voxel_in_block) : make_float3(0.f, 0.f, 0.f);
+		float3 warped;
+		bool warp_ok;
+		if (fallback) {
+			warp_ok = warp_thresholded<A>(f, voxel, active, s_node, false, warped);
+		} else {
+			NearestNodes<A> nearest;
+			nearest.init(f.node_weights ? f.node_weights[0] : f.fixed_c2);
+			warp_ok = false;
+			if (active) {
+				for (int k = 0; k < count; k++) nearest.offer(s_node[k], s_index[k], voxel);
+				warp_ok = nearest.finish(f, voxel, false, warped);
+			}
+		}
+		if (active && warp_ok) integrate_warped_voxel(p, (int64_t) blockIdx.x * r3 + voxel_in_block, block_index, voxel_in_block, r3, warped);
 	}
 }
 
@@ -302,7 +420,8 @@ __global__ void __launch_bounds__(256) resolve_cosines_kernel(const unsigned lon
 
 using namespace nnrt_b200;
 
-extern "C" int nnrt_b200_integrate_non_rigid(
+static int integrate_non_rigid_impl(bool full_scan,
+		
 		const int64_t* block_indices, int64_t block_count, const int32_t* block_keys, float* tsdf, const void* weight, int32_t weight_dtype,
 		float* voxel_color, int32_t block_resolution, float voxel_size, float sdf_truncation_distance, const void* depth, int32_t depth_dtype,
 		const void* color, int32_t color_dtype, const float* depth_normals, int32_t image_height, int32_t image_width, int32_t color_height,
@@ -337,8 +456,12 @@ extern "C" int nnrt_b200_integrate_non_rigid(
 	p.depth_scale = depth_scale; p.depth_max = depth_max;
 	p.cos_keys = keys; p.voxel_count = voxel_count;
 	if (voxel_count > 0) {
-		const unsigned grid = blocks_for(voxel_count, kThreads);
-#define NNRT_TSDF_CASE(A_) case A_: integrate_non_rigid_kernel<A_><<<grid, kThreads, 0, s>>>(p); break;
+		const unsigned scan_grid = blocks_for(voxel_count, kThreads);
+#define NNRT_TSDF_CASE(A_)                                                                          \
+	case A_:                                                                                        \
+		if (full_scan) integrate_non_rigid_kernel<A_><<<scan_grid, kThreads, 0, s>>>(p);            \
+		else integrate_blocks_kernel<A_><<<(unsigned) block_count, kBlockThreads, 0, s>>>(p);      \
+		break;
 		switch (anchor_count) {
 			NNRT_TSDF_CASE(1) NNRT_TSDF_CASE(2) NNRT_TSDF_CASE(3) NNRT_TSDF_CASE(4) NNRT_TSDF_CASE(5) NNRT_TSDF_CASE(6) NNRT_TSDF_CASE(7) NNRT_TSDF_CASE(8)
 		}
@@ -349,6 +472,34 @@ extern "C" int nnrt_b200_integrate_non_rigid(
 	cudaFreeAsync(keys, s);
 	if (err != cudaSuccess) { set_last_error("integrate_non_rigid: launch failed: %s", cudaGetErrorString(err)); return kCudaError; }
 	return kOk;
+}
+
+extern "C" int nnrt_b200_integrate_non_rigid(
+		const int64_t* block_indices, int64_t block_count, const int32_t* block_keys, float* tsdf, const void* weight, int32_t weight_dtype,
+		float* voxel_color, int32_t block_resolution, float voxel_size, float sdf_truncation_distance, const void* depth, int32_t depth_dtype,
+		const void* color, int32_t color_dtype, const float* depth_normals, int32_t image_height, int32_t image_width, int32_t color_height,
+		int32_t color_width, const double* depth_intrinsics_host, const double* color_intrinsics_host, const double* extrinsics_host,
+		const float* nodes, const float* node_rotations, const float* node_translations, int32_t node_count, const float* node_coverage_weights,
+		float node_coverage, int32_t anchor_count, int32_t minimum_valid_anchor_count, float depth_scale, float depth_max,
+		float* cos_voxel_ray_to_normal, void* stream) {
+	return integrate_non_rigid_impl(false, block_indices, block_count, block_keys, tsdf, weight, weight_dtype, voxel_color, block_resolution, voxel_size, sdf_truncation_distance, depth, depth_dtype,
+	                                 color, color_dtype, depth_normals, image_height, image_width, color_height, color_width, depth_intrinsics_host, color_intrinsics_host,
+	                                 extrinsics_host, nodes, node_rotations, node_translations, node_count, node_coverage_weights, node_coverage, anchor_count,
+	                                 minimum_valid_anchor_count, depth_scale, depth_max, cos_voxel_ray_to_normal, stream);
+}
+
+extern "C" int nnrt_b200_integrate_non_rigid_full_scan(
+		const int64_t* block_indices, int64_t block_count, const int32_t* block_keys, float* tsdf, const void* weight, int32_t weight_dtype,
+		float* voxel_color, int32_t block_resolution, float voxel_size, float sdf_truncation_distance, const void* depth, int32_t depth_dtype,
+		const void* color, int32_t color_dtype, const float* depth_normals, int32_t image_height, int32_t image_width, int32_t color_height,
+		int32_t color_width, const double* depth_intrinsics_host, const double* color_intrinsics_host, const double* extrinsics_host,
+		const float* nodes, const float* node_rotations, const float* node_translations, int32_t node_count, const float* node_coverage_weights,
+		float node_coverage, int32_t anchor_count, int32_t minimum_valid_anchor_count, float depth_scale, float depth_max,
+		float* cos_voxel_ray_to_normal, void* stream) {
+	return integrate_non_rigid_impl(true, block_indices, block_count, block_keys, tsdf, weight, weight_dtype, voxel_color, block_resolution, voxel_size, sdf_truncation_distance, depth, depth_dtype,
+	                                 color, color_dtype, depth_normals, image_height, image_width, color_height, color_width, depth_intrinsics_host, color_intrinsics_host,
+	                                 extrinsics_host, nodes, node_rotations, node_translations, node_count, node_coverage_weights, node_coverage, anchor_count,
+	                                 minimum_valid_anchor_count, depth_scale, depth_max, cos_voxel_ray_to_normal, stream);
 }
 
 extern "C" int nnrt_b200_bounding_boxes_of_warped_blocks(const int32_t* block_keys, int64_t block_count, const float* nodes, const float* node_rotations,

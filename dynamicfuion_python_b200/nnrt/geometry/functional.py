@@ -232,7 +232,7 @@ def compute_ordered_point_cloud_normals(point_cloud, source_image_size):
 
 def integrate_non_rigid_voxel_blocks(block_indices, block_keys, block_values, block_resolution, voxel_size, warp_field, depth, color,
                                      depth_normals, depth_intrinsics, color_intrinsics=None, extrinsics=None, depth_scale=1000.0, depth_max=3.0,
-                                     truncation_voxel_multiplier=2.0):
+                                     truncation_voxel_multiplier=2.0, _full_scan=False):
     """The voxel kernel of NonRigidSurfaceVoxelBlockGrid.integrate_non_rigid (cpp/geometry/NonRigidSurfaceVoxelBlockGrid.cpp:32-74;
     kernel/NonRigidSurfaceVoxelBlockGridImpl.h:50-229) over a voxel block grid's own tensors: `block_indices` [B] the active buffer
     indices, `block_keys` [capacity,3] int32 the hash map's key tensor, `block_values` a dict with "tsdf" [capacity,R,R,R] f32,
@@ -285,7 +285,7 @@ def integrate_non_rigid_voxel_blocks(block_indices, block_keys, block_values, bl
     fixed = warp_field.warp_node_coverage_computation_method == WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE
     ncw = None if fixed else warp_field.node_coverage_weights
     cos = T.empty((h, w), torch.float32)
-    T.call("nnrt_b200_integrate_non_rigid", T.ptr(idx), idx.shape[0], T.ptr(keys), T.ptr(tsdf), T.ptr(weight), weight_code,
+    T.call("nnrt_b200_integrate_non_rigid_full_scan" if _full_scan else "nnrt_b200_integrate_non_rigid", T.ptr(idx), idx.shape[0], T.ptr(keys), T.ptr(tsdf), T.ptr(weight), weight_code,
            T.ptr(voxel_color) if c is not None else None, int(block_resolution), float(voxel_size), float(voxel_size) * float(truncation_voxel_multiplier),
            T.ptr(d), depth_code, T.ptr(c), color_code, T.ptr(normals), h, w, ch, cw, Kd.data_ptr(), Kc.data_ptr(), ext.data_ptr(),
            T.ptr(warp_field.nodes), T.ptr(warp_field.node_rotations), T.ptr(warp_field.node_translations), warp_field.nodes.shape[0], T.ptr(ncw),

@@ -299,8 +299,20 @@ int nnrt_b200_shade_vertex_colors(const int64_t* pixel_face_indices, const float
  * 1 = u16), color [Hc,Wc,3] or NULL (color_dtype 0 = f32 in [0,1], 1 = u8), depth_normals [H,W,3]; the warp field as nodes /
  * rotations / translations with node_coverage_weights (NULL = fixed node_coverage), anchor_count, minimum_valid_anchor_count.
  * Output cos_voxel_ray_to_normal [H,W] f32 (0 where no voxel projected; the highest voxel index wins a pixel). The k nearest nodes
- * are found by brute force in ascending node order (the reference's kd-tree yields the same set in its traversal order). */
+ * are found by brute force in ascending node order (the reference's kd-tree yields the same set in its traversal order), over a
+ * per-block shortlist of the nodes that can reach a slot of some voxel of the block (csrc/tsdf.cu). */
 int nnrt_b200_integrate_non_rigid(const int64_t* block_indices, int64_t block_count, const int32_t* block_keys, float* tsdf,
+                                  const void* weight, int32_t weight_dtype, float* voxel_color, int32_t block_resolution,
+                                  float voxel_size, float sdf_truncation_distance, const void* depth, int32_t depth_dtype,
+                                  const void* color, int32_t color_dtype, const float* depth_normals, int32_t image_height,
+                                  int32_t image_width, int32_t color_height, int32_t color_width,
+                                  const double* depth_intrinsics_host, const double* color_intrinsics_host,
+                                  const double* extrinsics_host, const float* nodes, const float* node_rotations,
+                                  const float* node_translations, int32_t node_count, const float* node_coverage_weights,
+                                  float node_coverage, int32_t anchor_count, int32_t minimum_valid_anchor_count, float depth_scale,
+                                  float depth_max, float* cos_voxel_ray_to_normal, void* stream);
+/* The same with every node offered to every voxel (no per-block shortlist): the yardstick the default entry point equals bit for bit. */
+int nnrt_b200_integrate_non_rigid_full_scan(const int64_t* block_indices, int64_t block_count, const int32_t* block_keys, float* tsdf,
                                   const void* weight, int32_t weight_dtype, float* voxel_color, int32_t block_resolution,
                                   float voxel_size, float sdf_truncation_distance, const void* depth, int32_t depth_dtype,
                                   const void* color, int32_t color_dtype, const float* depth_normals, int32_t image_height,

@@ -39,7 +39,7 @@ def cpu_ms(fn):
 def report(op, case, ms, algorithmic_bytes, oracle_ms, **extra):
     gbs = algorithmic_bytes / ms / 1e6
     line = dict(op=op, case=case, gpu_ms=round(ms, 4), algorithmic_mb=round(algorithmic_bytes / 1e6, 2), gbs=round(gbs, 1),
-                frac_of_measured_hbm=None if PEAK is None else round(gbs / PEAK, 4), oracle_cpu_ms=round(oracle_ms, 2), **extra)
+                frac_of_measured_hbm=None if PEAK is None else round(gbs / PEAK, 4), oracle_cpu_ms=None if oracle_ms != oracle_ms else round(oracle_ms, 2), **extra)
     print(json.dumps(line), flush=True)
 
 
@@ -108,14 +108,25 @@ def main():
     args = (torch.as_tensor(active).cuda(), torch.as_tensor(keys).cuda(), values, R, voxel, wf, torch.as_tensor(depth_img).cuda(), None,
             torch.as_tensor(normals).cuda(), s["K"], s["K"], None, 1.0, 3.0, 2.0)
     ms = gpu_ms(lambda: f.integrate_non_rigid_voxel_blocks(*args), 20)
+    ms_full = gpu_ms(lambda: f.integrate_non_rigid_voxel_blocks(*args, _full_scan=True), 20)
     voxels = B * R ** 3
     sample = active[:max(1, B // 50)]
     cpu = cpu_ms(lambda: oracle.integrate_non_rigid(sample, keys, tsdf.copy(), weight, None, R, voxel, 2 * voxel, depth_img, None, normals, s["K"], s["K"], np.eye(4),
                                                     s["nodes"], s["rotations_gt"], s["translations_gt"], 0.02, 4, 1, 1.0, 3.0)) * (B / len(sample))
     report("integrate_non_rigid_voxel_blocks", f"{B} blocks of 8^3 voxels ({voxels} voxels) around the C2r surface, {N} nodes, A=4, {W}x{H} depth", ms,
-           12 * voxels + 16 * H * W, cpu, bound="issue (N distance evaluations per voxel)", oracle_note=f"extrapolated from {len(sample)} blocks",
-           voxel_node_pairs_per_s=round(voxels * N / ms * 1e3 / 1e9, 1))
-
+           12 * voxels + 16 * H * W, cpu, bound="issue (shortlisted node distances per voxel)", oracle_note=f"extrapolated from {len(sample)} blocks",
+           full_scan_ms=round(ms_full, 4), full_scan_voxel_node_pairs_per_s=round(voxels * N / ms_full * 1e3 / 1e9, 1))
+    # the same blocks against a 2000-node field (C3-scale graph): most nodes are far from any one block
+    rng2 = np.random.default_rng(5)
+    many = np.concatenate([s["positions"][rng2.choice(V, 1000, replace=False)], rng2.uniform(-1, 1, (1000, 3)) + [0, 0, 0.6]]).astype(np.float32)
+    many = rng2.permutation(many)
+    wf2 = G.GraphWarpField(many, 0.01, True, 4, 1, G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE)
+    args2 = args[:5] + (wf2,) + args[6:]
+    ms2 = gpu_ms(lambda: f.integrate_non_rigid_voxel_blocks(*args2), 20)
+    ms2_full = gpu_ms(lambda: f.integrate_non_rigid_voxel_blocks(*args2, _full_scan=True), 20)
+    report("integrate_non_rigid_voxel_blocks", f"{B} blocks ({voxels} voxels), 2000 nodes, A=4", ms2, 12 * voxels + 16 * H * W, float("nan"),
+           bound="issue (shortlisted node distances per voxel)", full_scan_ms=round(ms2_full, 4),
+           full_scan_voxel_node_pairs_per_s=round(voxels * 2000 / ms2_full * 1e3 / 1e9, 1))
     # block selection of FindBlocksIntersectingTruncationRegion: 27 neighbours of every block; 12 B key in, 24 B box out, then 24 B box in, 1 B out
     neighbours = np.unique((keys[:, None, :] + np.stack(np.meshgrid(*[np.arange(-1, 2)] * 3, indexing="ij"), -1).reshape(1, 27, 3)).reshape(-1, 3), axis=0).astype(np.int32)
     keys_t = torch.as_tensor(neighbours).cuda()

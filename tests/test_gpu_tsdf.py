@@ -130,3 +130,39 @@ def test_block_selection_matches_oracle(nnrt, oracle):
         want = oracle.boxes_intersecting_surface_mask(boxes, s["K"], depth, scale, 3.0, stride, 2 * c["voxel_size"])
         assert 20 < want.sum() < 580
         assert np.array_equal(got.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("node_count,coverage,variable,min_valid", [(30, 0.03, False, 0), (2500, 0.012, False, 1), (2500, 0.01, True, 2), (1500, 0.5, False, 0)])
+def test_block_shortlist_equals_full_scan_bit_for_bit(nnrt, oracle, node_count, coverage, variable, min_valid):
+    """The default entry point scans a per-block shortlist of nodes; the full scan over every node is the yardstick. They must agree in
+    every bit of tsdf, colour and cosine — the pruning argument (running A-th distance + block diameter) leaves no slot different.
+    (1500 nodes packed into the surface's neighbourhood with a huge coverage overflow the 1024-entry shortlist: the fallback path.)"""
+    c = _scene(oracle, False, True, variable)
+    s = c["s"]
+    rng = np.random.default_rng(node_count)
+    if node_count == 30:
+        nodes = s["nodes"]
+    elif node_count == 1500:
+        nodes = (s["positions"][rng.choice(len(s["positions"]), node_count, replace=False)] + rng.normal(0, 0.002, (node_count, 3))).astype(np.float32)
+    else:  # many nodes: most of them far from any one block
+        near = s["positions"][rng.choice(len(s["positions"]), node_count // 2, replace=False)] + rng.normal(0, 0.01, (node_count // 2, 3))
+        far = rng.uniform(-1, 1, (node_count - node_count // 2, 3)) + [0, 0, 0.6]
+        nodes = rng.permutation(np.concatenate([near, far])).astype(np.float32)
+    rotations, translations = synthetic.smooth_node_motion(nodes, 3.0, 0.005, np.random.default_rng(1))
+    G = nnrt.geometry
+    method = G.WarpNodeCoverageComputationMethod
+    outputs = []
+    for full_scan in (False, True):
+        wf = G.GraphWarpField(nodes, coverage, True, 4, min_valid, method.MINIMAL_K_NEIGHBOR_NODE_DISTANCE if variable else method.FIXED_NODE_COVERAGE)
+        if variable:
+            wf.node_coverage_weights = torch.as_tensor((rng.uniform(0.5, 1.5, len(nodes)) * coverage).astype(np.float32) ** 2).cuda() if not outputs else weights_used
+            weights_used = wf.node_coverage_weights
+        wf.set_node_rotations(rotations)
+        wf.set_node_translations(translations)
+        values = dict(tsdf=torch.as_tensor(c["tsdf"]).cuda(), weight=torch.as_tensor(c["weight"]).cuda(), color=torch.as_tensor(c["voxel_color"]).cuda())
+        cos = G.functional.integrate_non_rigid_voxel_blocks(c["active"], c["keys"], values, c["R"], c["voxel_size"], wf, c["depth"], c["color"], c["normals"],
+                                                            s["K"], s["K"], None, c["depth_scale"], 3.0, 2.0, _full_scan=full_scan)
+        outputs.append((values["tsdf"].cpu().numpy(), values["color"].cpu().numpy(), cos.cpu().numpy()))
+    (tsdf_a, color_a, cos_a), (tsdf_b, color_b, cos_b) = outputs
+    assert (tsdf_b != c["tsdf"]).sum() > 500
+    assert np.array_equal(tsdf_a, tsdf_b) and np.array_equal(color_a, color_b) and np.array_equal(cos_a, cos_b)
