@@ -157,9 +157,9 @@ struct SubsampleWorkspace {
 	}
 };
 
-// Enqueues the whole subsample on `s`; sample[0 .. *bin_count) is valid once the stream has passed. ONE host synchronisation (the
-// bin count sizes the last launch and the result).
-int median_subsample(const float* points, int64_t n, float cell_size, SubsampleWorkspace& w, int64_t* sample, int* bin_count_host, cudaStream_t s) {
+// Bins the points into grid cells and leaves every bin's members in ascending point order: bin_of_point, bin_counts (= CSR starts,
+// n + 2 entries) and sorted_members are valid on the stream afterwards; *bin_count_host after its ONE host synchronisation.
+int bin_points_sorted(const float* points, int64_t n, float cell_size, SubsampleWorkspace& w, int* bin_count_host, cudaStream_t s) {
 	const unsigned blocks = blocks_for(n, kThreads);
 	const size_t ints = (size_t) n + 2;
 	NNRT_CUDA(cudaMemsetAsync(w.owner, 0xFF, SubsampleWorkspace::align(sizeof(int) * w.table_size) + sizeof(unsigned long long) * ints, s));  // owner, best
@@ -178,12 +178,48 @@ int median_subsample(const float* points, int64_t n, float cell_size, SubsampleW
 	if (rc != kOk) return rc;
 	scatter_members_kernel<<<blocks, kThreads, 0, s>>>(w.bin_of_point, w.bin_counts, n, w.bin_fill, w.members);
 	rank_members_kernel<<<blocks, kThreads, 0, s>>>(w.bin_of_point, w.bin_counts, w.members, n, w.sorted_members);
-	median_sums_kernel<<<blocks, kThreads, 0, s>>>(points, w.bin_of_point, w.bin_counts, w.sorted_members, n, w.best);
+	NNRT_LAUNCH_CHECK();
+	return kOk;
+}
+
+// Enqueues the whole median subsample on `s`; sample[0 .. *bin_count) is valid once the stream has passed.
+int median_subsample(const float* points, int64_t n, float cell_size, SubsampleWorkspace& w, int64_t* sample, int* bin_count_host, cudaStream_t s) {
+	const int rc = bin_points_sorted(points, n, cell_size, w, bin_count_host, s);
+	if (rc != kOk) return rc;
+	median_sums_kernel<<<blocks_for(n, kThreads), kThreads, 0, s>>>(points, w.bin_of_point, w.bin_counts, w.sorted_members, n, w.best);
 	NNRT_LAUNCH_CHECK();
 	NNRT_CUDA(cudaStreamSynchronize(s));
 	emit_sample_kernel<<<blocks_for(*bin_count_host, kThreads), kThreads, 0, s>>>(w.best, *bin_count_host, sample);
 	NNRT_LAUNCH_CHECK();
 	return kOk;
+}
+
+// Mean of every bin's points (geometry/functional/kernel/GeometrySamplingMean.h:37-92): the reference adds with float atomics; here
+// the members are added in ascending point order (its single-thread result), then divided by the count. One thread per bin.
+__global__ void __launch_bounds__(kThreads) bin_means_kernel(const float* __restrict__ points, const int* __restrict__ bin_starts,
+                                                             const int* __restrict__ sorted_members, int bins, float* __restrict__ means) {
+	const int b = blockIdx.x * blockDim.x + threadIdx.x;
+	if (b >= bins) return;
+	const int begin = bin_starts[b], end = bin_starts[b + 1];
+	float x = 0.f, y = 0.f, z = 0.f;
+	for (int k = begin; k < end; k++) {
+		const int64_t i = sorted_members[k];
+		x += points[i * 3]; y += points[i * 3 + 1]; z += points[i * 3 + 2];
+	}
+	const float count = (float) (end - begin);
+	means[b * 3] = __fdiv_rn(x, count); means[b * 3 + 1] = __fdiv_rn(y, count); means[b * 3 + 2] = __fdiv_rn(z, count);
+}
+
+// FindClosestInBins (GeometrySamplingMean.h:189-212): per bin the point with the smallest squared distance to the bin mean, the
+// smallest index among equals (strict `>` in the reference's compare-and-swap loop)
+__global__ void __launch_bounds__(kThreads) closest_to_mean_kernel(const float* __restrict__ points, const int* __restrict__ bin_of_point,
+                                                                   const float* __restrict__ means, int64_t n, unsigned long long* __restrict__ best) {
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const int b = bin_of_point[i];
+	const float dx = means[b * 3] - points[i * 3], dy = means[b * 3 + 1] - points[i * 3 + 1], dz = means[b * 3 + 2] - points[i * 3 + 2];
+	const float d2 = sum3(dx * dx, dy * dy, dz * dz);
+	atomicMin(best + b, ((unsigned long long) __float_as_uint(d2) << 32) | (unsigned) i);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------------
@@ -442,6 +478,48 @@ extern "C" int nnrt_b200_median_grid_subsample_3d_points(const float* points, in
 	if (rc != kOk) return rc;
 	*sample_count_host = bins;
 	return kOk;
+}
+
+// mode 0: means [bins,3] f32 into `out`; mode 1: indices of the points closest to their bin's mean, int64, into `out`
+static int grid_mean_impl(int mode, const float* points, int64_t point_count, float grid_cell_size, void* out, int64_t* count_host, void* stream) {
+	NNRT_CHECK_ARG(count_host, "count_host must not be NULL");
+	*count_host = 0;
+	if (point_count == 0) return kOk;
+	NNRT_CHECK_ARG(points && out, "points and the output must not be NULL");
+	NNRT_CHECK_ARG(point_count > 0 && point_count < (1ll << 30), "point_count must be in [0, 2^30), got %lld", (long long) point_count);
+	NNRT_CHECK_ARG(grid_cell_size > 0.f, "grid_cell_size must be positive, got %f", grid_cell_size);
+	cudaStream_t s = (cudaStream_t) stream;
+	char* buffer = nullptr;
+	const size_t mean_bytes = mode == 1 ? SubsampleWorkspace::align(sizeof(float) * 3 * (size_t) point_count) : 0;
+	NNRT_CUDA(scratch_malloc_async(&buffer, SubsampleWorkspace::bytes(point_count) + mean_bytes, s));
+	SubsampleWorkspace w;
+	w.carve(buffer, point_count);
+	float* means = mode == 1 ? (float*) (buffer + SubsampleWorkspace::bytes(point_count)) : (float*) out;
+	int bins = 0;
+	int rc = bin_points_sorted(points, point_count, grid_cell_size, w, &bins, s);
+	if (rc == kOk && cudaStreamSynchronize(s) != cudaSuccess) rc = kCudaError;
+	if (rc == kOk) {
+		bin_means_kernel<<<blocks_for(bins, kThreads), kThreads, 0, s>>>(points, w.bin_counts, w.sorted_members, bins, means);
+		if (mode == 1) {
+			closest_to_mean_kernel<<<blocks_for(point_count, kThreads), kThreads, 0, s>>>(points, w.bin_of_point, means, point_count, w.best);
+			emit_sample_kernel<<<blocks_for(bins, kThreads), kThreads, 0, s>>>(w.best, bins, (int64_t*) out);
+		}
+		if (cudaGetLastError() != cudaSuccess) { set_last_error("grid mean: kernel launch failed"); rc = kCudaError; }
+	}
+	cudaFreeAsync(buffer, s);
+	if (rc != kOk) return rc;
+	*count_host = bins;
+	return kOk;
+}
+
+extern "C" int nnrt_b200_mean_grid_downsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float* downsampled_points,
+                                                        int64_t* downsampled_count_host, void* stream) {
+	return grid_mean_impl(0, points, point_count, grid_cell_size, downsampled_points, downsampled_count_host, stream);
+}
+
+extern "C" int nnrt_b200_closest_to_mean_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample,
+                                                                  int64_t* sample_count_host, void* stream) {
+	return grid_mean_impl(1, points, point_count, grid_cell_size, sample, sample_count_host, stream);
 }
 
 extern "C" int nnrt_b200_find_k_nearest_to_points(const float* indexed_points, int32_t indexed_count, const float* query_points, int64_t query_count,

@@ -345,3 +345,29 @@ def axis_aligned_boxes_intersecting_surface_mask(boxes, depth, intrinsics, depth
     T.call("nnrt_b200_boxes_intersecting_surface_mask", T.ptr(b), b.shape[0], K.data_ptr(), T.ptr(d), code, int(d.shape[0]), int(d.shape[1]),
            float(depth_scale), float(depth_max), int(downsampling_factor), float(truncation_distance), T.ptr(mask), T.stream())
     return mask.to(torch.bool)
+
+
+def mean_grid_downsample_3d_points(points, grid_cell_size):
+    """MeanGridDownsample3dPoints (cpp/pybind/geometry/functional/functional.cpp:143-145): [bins,3] f32 means of the occupied grid cells,
+    cells in order of their first point."""
+    import ctypes as C
+    pts = T.cuda(points, torch.float32)
+    if pts.dim() != 2 or pts.shape[1] != 3:
+        raise RuntimeError(f"points must have shape [N, 3], got {tuple(pts.shape)}")
+    out = T.empty((pts.shape[0], 3), torch.float32)
+    count = C.c_int64()
+    T.call("nnrt_b200_mean_grid_downsample_3d_points", T.ptr(pts), pts.shape[0], float(grid_cell_size), T.ptr(out), C.byref(count), T.stream())
+    return out[:count.value]
+
+
+def closest_to_mean_grid_subsample_3d_points(points, grid_cell_size):
+    """ClosestToGridMeanSubsample3dPoints (cpp/pybind/geometry/functional/functional.cpp:146-148): int64 indices of the points closest to
+    the mean of their grid cell."""
+    import ctypes as C
+    pts = T.cuda(points, torch.float32)
+    if pts.dim() != 2 or pts.shape[1] != 3:
+        raise RuntimeError(f"points must have shape [N, 3], got {tuple(pts.shape)}")
+    out = T.empty((pts.shape[0],), torch.int64)
+    count = C.c_int64()
+    T.call("nnrt_b200_closest_to_mean_grid_subsample_3d_points", T.ptr(pts), pts.shape[0], float(grid_cell_size), T.ptr(out), C.byref(count), T.stream())
+    return out[:count.value]

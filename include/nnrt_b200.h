@@ -233,6 +233,16 @@ int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter* fitter);
 int nnrt_b200_median_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample,
                                               int64_t* sample_count_host, void* stream);
 
+/* geometry::functional::MeanGridDownsample3dPoints (geometry/functional/GeometrySampling.cpp:27-37; kernel/GeometrySamplingMean.h):
+ * mean of the points of every occupied grid cell, downsampled_points [<= point_count, 3] f32, cells in order of their first point;
+ * members are added in ascending point order (the reference's float atomics are scheduling-dependent). */
+int nnrt_b200_mean_grid_downsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float* downsampled_points,
+                                             int64_t* downsampled_count_host, void* stream);
+/* geometry::functional::ClosestToGridMeanSubsample3dPoints (GeometrySampling.cpp:40-47; kernel/GeometrySamplingMean.h:189-236):
+ * per occupied cell the index (int64) of the point closest to the cell's mean, the smallest index among equals. */
+int nnrt_b200_closest_to_mean_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample,
+                                                       int64_t* sample_count_host, void* stream);
+
 /* core::KdTree::FindKNearestToPoints (core/KdTree.cpp:52-90; kernel/SearchKdTreeImpl.h:118-146, PLAIN
  * strategy), brute force: indexed points are visited in ascending order, which fixes the slot order the kd-tree leaves to its
  * traversal; sort_output != 0 orders each row by ascending distance. nearest_indices [Q,k] int32 (-1 where fewer than k points

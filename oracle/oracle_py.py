@@ -490,3 +490,19 @@ def boxes_intersecting_surface_mask(boxes, intrinsics, depth, depth_scale, depth
                                                  C.c_int(depth.shape[0]), C.c_int(depth.shape[1]), C.c_float(depth_scale), C.c_float(depth_max), C.c_int(stride),
                                                  C.c_float(truncation_distance), _p(mask))
     return mask.astype(bool)
+
+
+def mean_grid_downsample_3d_points(points, grid_cell_size):
+    points = _f32(points)
+    out = np.empty((points.shape[0], 3), np.float32)
+    lib().oracle_grid_mean.restype = C.c_int64
+    bins = lib().oracle_grid_mean(_p(points), C.c_int64(points.shape[0]), C.c_float(grid_cell_size), C.c_int(0), _p(out), None)
+    return out[:bins].copy()
+
+
+def closest_to_mean_grid_subsample_3d_points(points, grid_cell_size):
+    points = _f32(points)
+    out = np.empty(points.shape[0], np.int64)
+    lib().oracle_grid_mean.restype = C.c_int64
+    bins = lib().oracle_grid_mean(_p(points), C.c_int64(points.shape[0]), C.c_float(grid_cell_size), C.c_int(1), None, _p(out))
+    return out[:bins].copy()

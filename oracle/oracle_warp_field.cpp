@@ -189,3 +189,47 @@ ORACLE_API int64_t oracle_build_regularization_layers(const float* nodes, int no
 	}
 	return edge_count;
 }
+
+// cpp/geometry/functional/kernel/GeometrySamplingMean.h:37-92,159-236 (grid binning as above): bin means with the members added in
+// ascending point order, and per bin the point closest to the mean (squared distance, strict `>` replacement: first among equals).
+// mode 0: out_points [bins,3]; mode 1: out_indices [bins]. Returns the bin count.
+ORACLE_API int64_t oracle_grid_mean(const float* points, int64_t point_count, float grid_cell_size, int mode, float* out_points, int64_t* out_indices) {
+	std::map<std::array<int32_t, 3>, int32_t> bin_of_cell;
+	std::vector<int32_t> point_bin(point_count);
+	std::vector<std::array<float, 3>> sums;
+	std::vector<int32_t> counts;
+	for (int64_t i = 0; i < point_count; i++) {
+		std::array<int32_t, 3> cell;
+		for (int c = 0; c < 3; c++) cell[c] = (int32_t) floorf(points[i * 3 + c] / grid_cell_size + 0.0f);
+		auto found = bin_of_cell.find(cell);
+		int32_t bin;
+		if (found == bin_of_cell.end()) {
+			bin = (int32_t) sums.size();
+			bin_of_cell.emplace(cell, bin);
+			sums.push_back({0.f, 0.f, 0.f});
+			counts.push_back(0);
+		} else {
+			bin = found->second;
+		}
+		point_bin[i] = bin;
+		for (int c = 0; c < 3; c++) sums[bin][c] += points[i * 3 + c];
+		counts[bin]++;
+	}
+	const int64_t bins = (int64_t) sums.size();
+	for (int64_t b = 0; b < bins; b++)
+		for (int c = 0; c < 3; c++) sums[b][c] /= (float) counts[b];
+	if (mode == 0) {
+		for (int64_t b = 0; b < bins; b++)
+			for (int c = 0; c < 3; c++) out_points[b * 3 + c] = sums[b][c];
+		return bins;
+	}
+	std::vector<float> best(bins, INFINITY);
+	for (int64_t b = 0; b < bins; b++) out_indices[b] = -1;
+	for (int64_t i = 0; i < point_count; i++) {
+		const int32_t b = point_bin[i];
+		V3 d = sub(V3{sums[b][0], sums[b][1], sums[b][2]}, load3(points + i * 3));
+		float d2 = dot3(d, d);
+		if (best[b] > d2) { best[b] = d2; out_indices[b] = i; }
+	}
+	return bins;
+}

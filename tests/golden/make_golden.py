@@ -105,6 +105,15 @@ def main():
     wf["median/cell_size"] = np.float32(1.0)
     wf["median/required"] = np.array([2, 4])                    # REQUIRE(find(2)), REQUIRE(find(4))
     wf["median/either"] = np.array([[6, 7], [8, 9]])            # REQUIRE(find(6) || find(7)), REQUIRE(find(8) || find(9))
+    t = read("cpp/tests/test_sampling.cpp")
+    g = t[t.index("void TestGridDownsampling_Generic"):]
+    wf["mean/points"] = braces_after(g, "point_data").reshape(30, 3).astype(np.float32)
+    wf["mean/cell_size"] = np.float32(5.0)                      # downsample(points, 5.0)
+    wf["mean/points_gt_sorted_by_x"] = braces_after(g, "downsampled_points_gt_data").reshape(4, 3).astype(np.float32)
+    g = t[t.index("void TestClosestToMeanSampling"):]
+    wf["closest/points"] = braces_after(g, "point_data").reshape(17, 3).astype(np.float32)
+    wf["closest/cell_size"] = np.float32(2.0)
+    wf["closest/sample_gt"] = braces_after(g, "sample_gt").astype(np.int64)  # AllEqual: order included
     t = read("cpp/tests/test_graph_warp_field.cpp")
     t = t[t.index("void TestHierarchicalGraphWarpFieldConstructor"):]
     wf["hgwf/nodes"] = braces_after(t, "node_data").reshape(33, 3).astype(np.float32)

@@ -188,3 +188,19 @@ def test_fit_with_constructed_warp_field_matches_oracle(nnrt, oracle):
     np.testing.assert_allclose(t_virtual, ref["translations"], rtol=1e-3, atol=1e-6)
     np.testing.assert_allclose(_np(wf.get_node_rotations(True)), ref["rotations"], rtol=1e-3, atol=1e-6)
     assert np.array_equal(_np(wf.get_node_translations())[built["node_indices"]], t_virtual)
+
+
+@pytest.mark.parametrize("count,extent,cell", [(30, 5.0, 5.0), (2000, 1.0, 0.2), (100000, 2.0, 0.07)])
+def test_mean_grid_ops_bit_exact(nnrt, oracle, count, extent, cell):
+    """mean_grid_downsample_3d_points / closest_to_mean_grid_subsample_3d_points: the reference's KATs, and random clouds against the
+    oracle — means summed in ascending point order on both sides, so bit-exact."""
+    kat = np.load(GOLDEN)
+    f = nnrt.geometry.functional
+    if count == 30:
+        means = _np(f.mean_grid_downsample_3d_points(kat["mean/points"], float(kat["mean/cell_size"])))
+        np.testing.assert_allclose(means[np.argsort(means[:, 0])], kat["mean/points_gt_sorted_by_x"], atol=1e-6)
+        assert np.array_equal(_np(f.closest_to_mean_grid_subsample_3d_points(kat["closest/points"], float(kat["closest/cell_size"]))), kat["closest/sample_gt"])
+    rng = np.random.default_rng(count)
+    pts = rng.uniform(-extent, extent, (count, 3)).astype(np.float32)
+    assert np.array_equal(_np(f.mean_grid_downsample_3d_points(pts, cell)), oracle.mean_grid_downsample_3d_points(pts, cell))
+    assert np.array_equal(_np(f.closest_to_mean_grid_subsample_3d_points(pts, cell)), oracle.closest_to_mean_grid_subsample_3d_points(pts, cell))

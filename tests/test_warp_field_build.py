@@ -81,3 +81,13 @@ def test_oracle_layer_that_cannot_be_decimated_is_an_error(oracle):
     nodes = np.array([[0, 0, 0], [10, 0, 0], [0, 10, 0]], np.float32)  # every node alone in its cell
     with pytest.raises(RuntimeError):
         oracle.build_regularization_layers(nodes, 0.05, 2, 4)
+
+
+def test_oracle_mean_grid_kats(oracle):
+    """cpp/tests/test_sampling.cpp:70-118 (mean of 30 points in 5 m cells, compared after sorting by x) and :179-215 (closest to the cell
+    mean: AllEqual to [2, 13], order included)."""
+    kat = np.load(GOLDEN)
+    means = oracle.mean_grid_downsample_3d_points(kat["mean/points"], float(kat["mean/cell_size"]))
+    means = means[np.argsort(means[:, 0])]
+    np.testing.assert_allclose(means, kat["mean/points_gt_sorted_by_x"], atol=1e-6)
+    assert np.array_equal(oracle.closest_to_mean_grid_subsample_3d_points(kat["closest/points"], float(kat["closest/cell_size"])), kat["closest/sample_gt"])
