@@ -29,9 +29,9 @@ _SIGNATURES = {
     "nnrt_b200_precondition_diagonal_blocks": (C.c_int, [P, I32, I32, F32, P]),
     "nnrt_b200_rodrigues": (C.c_int, [P, I32, P, P]),
     "nnrt_b200_matmul3d_3x3": (C.c_int, [P, P, I32, P, P]),
-    "nnrt_b200_median_grid_subsample_3d_points": (C.c_int, [P, I64, F32, P, P, P]),
-    "nnrt_b200_mean_grid_downsample_3d_points": (C.c_int, [P, I64, F32, P, P, P]),
-    "nnrt_b200_closest_to_mean_grid_subsample_3d_points": (C.c_int, [P, I64, F32, P, P, P]),
+    "nnrt_b200_median_grid_subsample_3d_points": (C.c_int, [P, I64, F32, F32, P, P, P]),
+    "nnrt_b200_mean_grid_downsample_3d_points": (C.c_int, [P, I64, F32, F32, P, P, P]),
+    "nnrt_b200_closest_to_mean_grid_subsample_3d_points": (C.c_int, [P, I64, F32, F32, P, P, P]),
     "nnrt_b200_find_k_nearest_to_points": (C.c_int, [P, I32, P, I64, I32, I32, P, P, P]),
     "nnrt_b200_node_coverage_weights": (C.c_int, [P, I32, F32, P, P]),
     "nnrt_b200_build_regularization_layers": (C.c_int, [P, I32, P, I32, I32, P, P, P, P, P, P]),

@@ -37,10 +37,11 @@ __device__ __forceinline__ float squared_upper_bound(float m) { return m * m * 1
 // Median-grid subsampling (geometry/functional/kernel/GeometrySamplingGridBinning.h:30-52, GeometrySamplingMedian.h:36-285)
 
 struct Cell { int x, y, z; };
-__device__ __forceinline__ Cell cell_of(const float* __restrict__ p, float cell_size) {
-	// Open3D: points / grid_cell_size + offset (0), Floor(), To(Int32)
-	return Cell{(int) floorf(__fdiv_rn(p[0], cell_size) + 0.0f), (int) floorf(__fdiv_rn(p[1], cell_size) + 0.0f),
-	            (int) floorf(__fdiv_rn(p[2], cell_size) + 0.0f)};
+__device__ __forceinline__ Cell cell_of(const float* __restrict__ p, float cell_size, float offset) {
+	// Open3D: points / grid_cell_size + grid_offset (the same on all three axes: 0, or 0.5 for the second pass of the radius variants),
+	// Floor(), To(Int32)
+	return Cell{(int) floorf(__fdiv_rn(p[0], cell_size) + offset), (int) floorf(__fdiv_rn(p[1], cell_size) + offset),
+	            (int) floorf(__fdiv_rn(p[2], cell_size) + offset)};
 }
 __device__ __forceinline__ unsigned hash_cell(Cell c) {
 	unsigned h = (unsigned) c.x * 73856093u ^ (unsigned) c.y * 19349663u ^ (unsigned) c.z * 83492791u;
@@ -50,16 +51,16 @@ __device__ __forceinline__ unsigned hash_cell(Cell c) {
 
 // Open-addressing table over cells. A slot is claimed by the first point that reaches it (owner = its index); later points compare
 // their cell with the owner's, recomputed from the immutable point array, so no key is stored. slot_min = smallest index in the cell.
-__global__ void __launch_bounds__(kThreads) bin_insert_kernel(const float* __restrict__ points, int64_t n, float cell_size, int* __restrict__ owner,
+__global__ void __launch_bounds__(kThreads) bin_insert_kernel(const float* __restrict__ points, int64_t n, float cell_size, float offset, int* __restrict__ owner,
                                                               int* __restrict__ slot_min, unsigned mask, int* __restrict__ slot_of_point) {
 	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
-	const Cell c = cell_of(points + i * 3, cell_size);
+	const Cell c = cell_of(points + i * 3, cell_size, offset);
 	unsigned slot = hash_cell(c) & mask;
 	while (true) {
 		const int previous = atomicCAS(owner + slot, -1, (int) i);
 		if (previous == -1) break;
-		const Cell other = cell_of(points + (int64_t) previous * 3, cell_size);
+		const Cell other = cell_of(points + (int64_t) previous * 3, cell_size, offset);
 		if (other.x == c.x && other.y == c.y && other.z == c.z) break;
 		slot = (slot + 1) & mask;
 	}
@@ -159,13 +160,13 @@ struct SubsampleWorkspace {
 
 // Bins the points into grid cells and leaves every bin's members in ascending point order: bin_of_point, bin_counts (= CSR starts,
 // n + 2 entries) and sorted_members are valid on the stream afterwards; *bin_count_host after its ONE host synchronisation.
-int bin_points_sorted(const float* points, int64_t n, float cell_size, SubsampleWorkspace& w, int* bin_count_host, cudaStream_t s) {
+int bin_points_sorted(const float* points, int64_t n, float cell_size, float offset, SubsampleWorkspace& w, int* bin_count_host, cudaStream_t s) {
 	const unsigned blocks = blocks_for(n, kThreads);
 	const size_t ints = (size_t) n + 2;
 	NNRT_CUDA(cudaMemsetAsync(w.owner, 0xFF, SubsampleWorkspace::align(sizeof(int) * w.table_size) + sizeof(unsigned long long) * ints, s));  // owner, best
 	NNRT_CUDA(cudaMemsetAsync(w.slot_min, 0x7F, sizeof(int) * w.table_size, s));
 	NNRT_CUDA(cudaMemsetAsync(w.bin_counts, 0, SubsampleWorkspace::align(sizeof(int) * ints) + sizeof(int) * ints, s));  // bin_counts, bin_fill
-	bin_insert_kernel<<<blocks, kThreads, 0, s>>>(points, n, cell_size, w.owner, w.slot_min, w.table_size - 1, w.slot_of_point);
+	bin_insert_kernel<<<blocks, kThreads, 0, s>>>(points, n, cell_size, offset, w.owner, w.slot_min, w.table_size - 1, w.slot_of_point);
 	flag_first_points_kernel<<<blocks, kThreads, 0, s>>>(w.slot_of_point, w.slot_min, n, w.rank);
 	NNRT_LAUNCH_CHECK();
 	int rc = exclusive_scan(w.rank, w.rank, n, w.scan_scratch, s);  // rank[n] = bin count
@@ -183,8 +184,9 @@ int bin_points_sorted(const float* points, int64_t n, float cell_size, Subsample
 }
 
 // Enqueues the whole median subsample on `s`; sample[0 .. *bin_count) is valid once the stream has passed.
-int median_subsample(const float* points, int64_t n, float cell_size, SubsampleWorkspace& w, int64_t* sample, int* bin_count_host, cudaStream_t s) {
-	const int rc = bin_points_sorted(points, n, cell_size, w, bin_count_host, s);
+int median_subsample(const float* points, int64_t n, float cell_size, float offset, SubsampleWorkspace& w, int64_t* sample, int* bin_count_host,
+                     cudaStream_t s) {
+	const int rc = bin_points_sorted(points, n, cell_size, offset, w, bin_count_host, s);
 	if (rc != kOk) return rc;
 	median_sums_kernel<<<blocks_for(n, kThreads), kThreads, 0, s>>>(points, w.bin_of_point, w.bin_counts, w.sorted_members, n, w.best);
 	NNRT_LAUNCH_CHECK();
@@ -459,8 +461,8 @@ int dispatch_k(int k, Launch&& launch) {
 
 using namespace nnrt_b200;
 
-extern "C" int nnrt_b200_median_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample,
-                                                         int64_t* sample_count_host, void* stream) {
+extern "C" int nnrt_b200_median_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float grid_offset,
+                                                         int64_t* sample, int64_t* sample_count_host, void* stream) {
 	NNRT_CHECK_ARG(sample_count_host, "sample_count_host must not be NULL");
 	*sample_count_host = 0;
 	if (point_count == 0) return kOk;
@@ -473,7 +475,7 @@ extern "C" int nnrt_b200_median_grid_subsample_3d_points(const float* points, in
 	SubsampleWorkspace w;
 	w.carve(buffer, point_count);
 	int bins = 0;
-	const int rc = median_subsample(points, point_count, grid_cell_size, w, sample, &bins, s);
+	const int rc = median_subsample(points, point_count, grid_cell_size, grid_offset, w, sample, &bins, s);
 	cudaFreeAsync(buffer, s);
 	if (rc != kOk) return rc;
 	*sample_count_host = bins;
@@ -481,7 +483,8 @@ extern "C" int nnrt_b200_median_grid_subsample_3d_points(const float* points, in
 }
 
 // mode 0: means [bins,3] f32 into `out`; mode 1: indices of the points closest to their bin's mean, int64, into `out`
-static int grid_mean_impl(int mode, const float* points, int64_t point_count, float grid_cell_size, void* out, int64_t* count_host, void* stream) {
+static int grid_mean_impl(int mode, const float* points, int64_t point_count, float grid_cell_size, float grid_offset, void* out, int64_t* count_host,
+                          void* stream) {
 	NNRT_CHECK_ARG(count_host, "count_host must not be NULL");
 	*count_host = 0;
 	if (point_count == 0) return kOk;
@@ -496,7 +499,7 @@ static int grid_mean_impl(int mode, const float* points, int64_t point_count, fl
 	w.carve(buffer, point_count);
 	float* means = mode == 1 ? (float*) (buffer + SubsampleWorkspace::bytes(point_count)) : (float*) out;
 	int bins = 0;
-	int rc = bin_points_sorted(points, point_count, grid_cell_size, w, &bins, s);
+	int rc = bin_points_sorted(points, point_count, grid_cell_size, grid_offset, w, &bins, s);
 	if (rc == kOk && cudaStreamSynchronize(s) != cudaSuccess) rc = kCudaError;
 	if (rc == kOk) {
 		bin_means_kernel<<<blocks_for(bins, kThreads), kThreads, 0, s>>>(points, w.bin_counts, w.sorted_members, bins, means);
@@ -512,14 +515,14 @@ static int grid_mean_impl(int mode, const float* points, int64_t point_count, fl
 	return kOk;
 }
 
-extern "C" int nnrt_b200_mean_grid_downsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float* downsampled_points,
-                                                        int64_t* downsampled_count_host, void* stream) {
-	return grid_mean_impl(0, points, point_count, grid_cell_size, downsampled_points, downsampled_count_host, stream);
+extern "C" int nnrt_b200_mean_grid_downsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float grid_offset,
+                                                        float* downsampled_points, int64_t* downsampled_count_host, void* stream) {
+	return grid_mean_impl(0, points, point_count, grid_cell_size, grid_offset, downsampled_points, downsampled_count_host, stream);
 }
 
-extern "C" int nnrt_b200_closest_to_mean_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample,
-                                                                  int64_t* sample_count_host, void* stream) {
-	return grid_mean_impl(1, points, point_count, grid_cell_size, sample, sample_count_host, stream);
+extern "C" int nnrt_b200_closest_to_mean_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float grid_offset,
+                                                                  int64_t* sample, int64_t* sample_count_host, void* stream) {
+	return grid_mean_impl(1, points, point_count, grid_cell_size, grid_offset, sample, sample_count_host, stream);
 }
 
 extern "C" int nnrt_b200_find_k_nearest_to_points(const float* indexed_points, int32_t indexed_count, const float* query_points, int64_t query_count,
@@ -600,7 +603,7 @@ extern "C" int nnrt_b200_build_regularization_layers(const float* nodes, int32_t
 		int sample_count = 0;
 		const float cell = layer_decimation_radii_host[l] * 2;
 		if (!(cell > 0.f)) { set_last_error("layer %d: decimation radius must be positive, got %f", l, layer_decimation_radii_host[l]); return fail(kInvalidArgument); }
-		rc = median_subsample(layer_positions[finer], finer_count, cell, w, sample, &sample_count, s);
+		rc = median_subsample(layer_positions[finer], finer_count, cell, 0.f, w, sample, &sample_count, s);
 		if (rc != kOk) return fail(rc);
 		if (sample_count == finer_count) {
 			set_last_error("Attempting to generate a coarser layer of size %d out of a finer layer of the same size, which is not possible."

@@ -172,7 +172,7 @@ def unproject_raster_depth_without_filtering(depth, intrinsics, extrinsics=None,
     return pts, mask
 
 
-def median_grid_subsample_3d_points(points, grid_cell_size):
+def median_grid_subsample_3d_points(points, grid_cell_size, _grid_offset=0.0):
     """MedianGridSubsample3dPoints (cpp/pybind/geometry/functional/functional.cpp:152-154; cpp/geometry/functional/GeometrySampling.cpp:61-68):
     int64 indices of the per-grid-cell median points (smallest sum of distances to the cell's points), cells in order of their first point."""
     import ctypes as C
@@ -181,7 +181,7 @@ def median_grid_subsample_3d_points(points, grid_cell_size):
         raise RuntimeError(f"points must have shape [N, 3], got {tuple(pts.shape)}")
     sample = T.empty((pts.shape[0],), torch.int64)
     count = C.c_int64()
-    T.call("nnrt_b200_median_grid_subsample_3d_points", T.ptr(pts), pts.shape[0], float(grid_cell_size), T.ptr(sample), C.byref(count), T.stream())
+    T.call("nnrt_b200_median_grid_subsample_3d_points", T.ptr(pts), pts.shape[0], float(grid_cell_size), float(_grid_offset), T.ptr(sample), C.byref(count), T.stream())
     return sample[:count.value]
 
 
@@ -347,7 +347,7 @@ def axis_aligned_boxes_intersecting_surface_mask(boxes, depth, intrinsics, depth
     return mask.to(torch.bool)
 
 
-def mean_grid_downsample_3d_points(points, grid_cell_size):
+def mean_grid_downsample_3d_points(points, grid_cell_size, _grid_offset=0.0):
     """MeanGridDownsample3dPoints (cpp/pybind/geometry/functional/functional.cpp:143-145): [bins,3] f32 means of the occupied grid cells,
     cells in order of their first point."""
     import ctypes as C
@@ -356,7 +356,7 @@ def mean_grid_downsample_3d_points(points, grid_cell_size):
         raise RuntimeError(f"points must have shape [N, 3], got {tuple(pts.shape)}")
     out = T.empty((pts.shape[0], 3), torch.float32)
     count = C.c_int64()
-    T.call("nnrt_b200_mean_grid_downsample_3d_points", T.ptr(pts), pts.shape[0], float(grid_cell_size), T.ptr(out), C.byref(count), T.stream())
+    T.call("nnrt_b200_mean_grid_downsample_3d_points", T.ptr(pts), pts.shape[0], float(grid_cell_size), float(_grid_offset), T.ptr(out), C.byref(count), T.stream())
     return out[:count.value]
 
 
@@ -369,5 +369,28 @@ def closest_to_mean_grid_subsample_3d_points(points, grid_cell_size):
         raise RuntimeError(f"points must have shape [N, 3], got {tuple(pts.shape)}")
     out = T.empty((pts.shape[0],), torch.int64)
     count = C.c_int64()
-    T.call("nnrt_b200_closest_to_mean_grid_subsample_3d_points", T.ptr(pts), pts.shape[0], float(grid_cell_size), T.ptr(out), C.byref(count), T.stream())
+    T.call("nnrt_b200_closest_to_mean_grid_subsample_3d_points", T.ptr(pts), pts.shape[0], float(grid_cell_size), 0.0, T.ptr(out), C.byref(count), T.stream())
     return out[:count.value]
+
+
+def _extended_cell(radius):
+    import numpy as np
+    r = np.float32(radius)
+    return float(np.sqrt(np.float32(2) * (r * r), dtype=np.float32) * np.float32(2))  # sqrtf(2 * (radius * radius)) * 2
+
+
+def fast_mean_radius_downsample_3d_points(points, radius):
+    """FastMeanRadiusDownsample3dPoints (cpp/geometry/functional/kernel/GeometrySamplingImpl.h:47-59): cell means on a grid of
+    2 * sqrt(2) * radius, merged again on the same grid shifted by half a cell."""
+    cell = _extended_cell(radius)
+    return mean_grid_downsample_3d_points(mean_grid_downsample_3d_points(points, cell), cell, _grid_offset=0.5)
+
+
+def fast_median_radius_subsample_3d_points(points, radius):
+    """FastMedianRadiusSubsample3dPoints (GeometrySamplingImpl.h:78-91): cell medians, then the medians of those on the shifted grid;
+    int64 indices into `points`."""
+    cell = _extended_cell(radius)
+    pts = T.cuda(points, torch.float32)
+    stage1 = median_grid_subsample_3d_points(pts, cell)
+    stage2 = median_grid_subsample_3d_points(pts[stage1].contiguous(), cell, _grid_offset=0.5)
+    return stage1[stage2]

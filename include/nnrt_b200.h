@@ -229,19 +229,21 @@ int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter* fitter);
 /* geometry::functional::MedianGridSubsample3dPoints (geometry/functional/GeometrySampling.cpp:61-68;
  * kernel/GeometrySamplingGridBinning.h:30-52, kernel/GeometrySamplingMedian.h:36-285): for every occupied cell of a grid with
  * the given cell size, the index of the point with the smallest sum of distances to the cell's points. sample: int64, capacity
- * point_count; cells in order of their first point. Synchronises the stream once (the count is a host value, as in the reference). */
-int nnrt_b200_median_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample,
-                                              int64_t* sample_count_host, void* stream);
+ * point_count; cells in order of their first point. grid_offset (in cells, the same on all axes) is 0 except in the second pass of
+ * FastMedianRadiusSubsample3dPoints / FastMeanRadiusDownsample3dPoints (kernel/GeometrySamplingImpl.h:47-91), which merge the first pass's
+ * result on a grid shifted by 0.5. Synchronises the stream once (the count is a host value, as in the reference). */
+int nnrt_b200_median_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float grid_offset,
+                                              int64_t* sample, int64_t* sample_count_host, void* stream);
 
 /* geometry::functional::MeanGridDownsample3dPoints (geometry/functional/GeometrySampling.cpp:27-37; kernel/GeometrySamplingMean.h):
  * mean of the points of every occupied grid cell, downsampled_points [<= point_count, 3] f32, cells in order of their first point;
  * members are added in ascending point order (the reference's float atomics are scheduling-dependent). */
-int nnrt_b200_mean_grid_downsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float* downsampled_points,
-                                             int64_t* downsampled_count_host, void* stream);
+int nnrt_b200_mean_grid_downsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float grid_offset,
+                                             float* downsampled_points, int64_t* downsampled_count_host, void* stream);
 /* geometry::functional::ClosestToGridMeanSubsample3dPoints (GeometrySampling.cpp:40-47; kernel/GeometrySamplingMean.h:189-236):
  * per occupied cell the index (int64) of the point closest to the cell's mean, the smallest index among equals. */
-int nnrt_b200_closest_to_mean_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample,
-                                                       int64_t* sample_count_host, void* stream);
+int nnrt_b200_closest_to_mean_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float grid_offset,
+                                                       int64_t* sample, int64_t* sample_count_host, void* stream);
 
 /* core::KdTree::FindKNearestToPoints (core/KdTree.cpp:52-90; kernel/SearchKdTreeImpl.h:118-146, PLAIN
  * strategy), brute force: indexed points are visited in ascending order, which fixes the slot order the kd-tree leaves to its

@@ -325,12 +325,12 @@ def fit_to_image(positions, normals, triangles, nodes, edges, arrow_base, anchor
 
 
 # --- warp-field construction -----------------------------------------------------------------------
-def median_grid_subsample_3d_points(points, grid_cell_size):
+def median_grid_subsample_3d_points(points, grid_cell_size, grid_offset=0.0):
     """Indices (int64, bins in order of first occurrence) of the per-cell median points."""
     points = _f32(points)
     sample = np.empty(points.shape[0], np.int64)
     lib().oracle_median_grid_subsample_3d_points.restype = C.c_int64
-    count = lib().oracle_median_grid_subsample_3d_points(_p(points), C.c_int64(points.shape[0]), C.c_float(grid_cell_size), _p(sample))
+    count = lib().oracle_median_grid_subsample_3d_points(_p(points), C.c_int64(points.shape[0]), C.c_float(grid_cell_size), C.c_float(grid_offset), _p(sample))
     return sample[:count].copy()
 
 
@@ -492,11 +492,11 @@ def boxes_intersecting_surface_mask(boxes, intrinsics, depth, depth_scale, depth
     return mask.astype(bool)
 
 
-def mean_grid_downsample_3d_points(points, grid_cell_size):
+def mean_grid_downsample_3d_points(points, grid_cell_size, grid_offset=0.0):
     points = _f32(points)
     out = np.empty((points.shape[0], 3), np.float32)
     lib().oracle_grid_mean.restype = C.c_int64
-    bins = lib().oracle_grid_mean(_p(points), C.c_int64(points.shape[0]), C.c_float(grid_cell_size), C.c_int(0), _p(out), None)
+    bins = lib().oracle_grid_mean(_p(points), C.c_int64(points.shape[0]), C.c_float(grid_cell_size), C.c_float(grid_offset), C.c_int(0), _p(out), None)
     return out[:bins].copy()
 
 
@@ -504,5 +504,25 @@ def closest_to_mean_grid_subsample_3d_points(points, grid_cell_size):
     points = _f32(points)
     out = np.empty(points.shape[0], np.int64)
     lib().oracle_grid_mean.restype = C.c_int64
-    bins = lib().oracle_grid_mean(_p(points), C.c_int64(points.shape[0]), C.c_float(grid_cell_size), C.c_int(1), None, _p(out))
+    bins = lib().oracle_grid_mean(_p(points), C.c_int64(points.shape[0]), C.c_float(grid_cell_size), C.c_float(0.0), C.c_int(1), None, _p(out))
     return out[:bins].copy()
+
+
+def _extended_cell(radius):
+    r = np.float32(radius)
+    return float(np.sqrt(np.float32(2) * (r * r), dtype=np.float32) * np.float32(2))
+
+
+def fast_mean_radius_downsample_3d_points(points, radius):
+    """cpp/geometry/functional/kernel/GeometrySamplingImpl.h:47-59"""
+    cell = _extended_cell(radius)
+    return mean_grid_downsample_3d_points(mean_grid_downsample_3d_points(points, cell), cell, 0.5)
+
+
+def fast_median_radius_subsample_3d_points(points, radius):
+    """cpp/geometry/functional/kernel/GeometrySamplingImpl.h:78-91"""
+    cell = _extended_cell(radius)
+    points = _f32(points)
+    stage1 = median_grid_subsample_3d_points(points, cell)
+    stage2 = median_grid_subsample_3d_points(points[stage1], cell, 0.5)
+    return stage1[stage2]

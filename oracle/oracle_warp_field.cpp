@@ -21,13 +21,13 @@ inline float distance3(const float* a, const float* b) {
 
 // cpp/geometry/functional/kernel/GeometrySamplingGridBinning.h:30-52 (points / cell + offset, Floor, To(Int32); bin index =
 // hash-map buffer index, here: order of first occurrence) + GeometrySamplingMedian.h:36-190,254-285.
-int64_t median_grid_subsample(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample) {
+int64_t median_grid_subsample(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample, float grid_offset = 0.0f) {
 	std::map<std::array<int32_t, 3>, int32_t> bin_of_cell;
 	std::vector<int32_t> point_bin(point_count);
 	std::vector<std::vector<int32_t>> bin_points;  // ascending point index = bin-sorted order of a sequential run
 	for (int64_t i = 0; i < point_count; i++) {
 		std::array<int32_t, 3> cell;
-		for (int c = 0; c < 3; c++) cell[c] = (int32_t) floorf(points[i * 3 + c] / grid_cell_size + 0.0f);
+		for (int c = 0; c < 3; c++) cell[c] = (int32_t) floorf(points[i * 3 + c] / grid_cell_size + grid_offset);
 		auto found = bin_of_cell.find(cell);
 		int32_t bin;
 		if (found == bin_of_cell.end()) {
@@ -82,8 +82,8 @@ void find_k_nearest(const float* indexed_points, int indexed_count, const float*
 
 }  // namespace
 
-ORACLE_API int64_t oracle_median_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, int64_t* sample) {
-	return median_grid_subsample(points, point_count, grid_cell_size, sample);
+ORACLE_API int64_t oracle_median_grid_subsample_3d_points(const float* points, int64_t point_count, float grid_cell_size, float grid_offset, int64_t* sample) {
+	return median_grid_subsample(points, point_count, grid_cell_size, sample, grid_offset);
 }
 
 ORACLE_API void oracle_find_k_nearest(const float* indexed_points, int indexed_count, const float* query_points, int64_t query_count,
@@ -193,14 +193,15 @@ ORACLE_API int64_t oracle_build_regularization_layers(const float* nodes, int no
 // cpp/geometry/functional/kernel/GeometrySamplingMean.h:37-92,159-236 (grid binning as above): bin means with the members added in
 // ascending point order, and per bin the point closest to the mean (squared distance, strict `>` replacement: first among equals).
 // mode 0: out_points [bins,3]; mode 1: out_indices [bins]. Returns the bin count.
-ORACLE_API int64_t oracle_grid_mean(const float* points, int64_t point_count, float grid_cell_size, int mode, float* out_points, int64_t* out_indices) {
+ORACLE_API int64_t oracle_grid_mean(const float* points, int64_t point_count, float grid_cell_size, float grid_offset, int mode, float* out_points,
+                                    int64_t* out_indices) {
 	std::map<std::array<int32_t, 3>, int32_t> bin_of_cell;
 	std::vector<int32_t> point_bin(point_count);
 	std::vector<std::array<float, 3>> sums;
 	std::vector<int32_t> counts;
 	for (int64_t i = 0; i < point_count; i++) {
 		std::array<int32_t, 3> cell;
-		for (int c = 0; c < 3; c++) cell[c] = (int32_t) floorf(points[i * 3 + c] / grid_cell_size + 0.0f);
+		for (int c = 0; c < 3; c++) cell[c] = (int32_t) floorf(points[i * 3 + c] / grid_cell_size + grid_offset);
 		auto found = bin_of_cell.find(cell);
 		int32_t bin;
 		if (found == bin_of_cell.end()) {

@@ -114,6 +114,9 @@ def main():
     wf["closest/points"] = braces_after(g, "point_data").reshape(17, 3).astype(np.float32)
     wf["closest/cell_size"] = np.float32(2.0)
     wf["closest/sample_gt"] = braces_after(g, "sample_gt").astype(np.int64)  # AllEqual: order included
+    # TestRadiusDownsampling (cpp/tests/test_sampling.cpp:131-141): the reference's 100-point cloud; REQUIRE(min pairwise distance >= radius)
+    wf["radius/points"] = np.load(os.path.join(REF, "cpp/tests/test_data/arrays/downsampling_source.npy")).astype(np.float32)
+    wf["radius/radius"] = np.float32(10.0)
     t = read("cpp/tests/test_graph_warp_field.cpp")
     t = t[t.index("void TestHierarchicalGraphWarpFieldConstructor"):]
     wf["hgwf/nodes"] = braces_after(t, "node_data").reshape(33, 3).astype(np.float32)

@@ -204,3 +204,21 @@ def test_mean_grid_ops_bit_exact(nnrt, oracle, count, extent, cell):
     pts = rng.uniform(-extent, extent, (count, 3)).astype(np.float32)
     assert np.array_equal(_np(f.mean_grid_downsample_3d_points(pts, cell)), oracle.mean_grid_downsample_3d_points(pts, cell))
     assert np.array_equal(_np(f.closest_to_mean_grid_subsample_3d_points(pts, cell)), oracle.closest_to_mean_grid_subsample_3d_points(pts, cell))
+
+
+def test_fast_radius_variants_bit_exact(nnrt, oracle):
+    """fast_mean_radius_downsample_3d_points / fast_median_radius_subsample_3d_points (two grid passes, the second shifted by half a
+    cell): the reference's cloud and property (cpp/tests/test_sampling.cpp:131-141), and random clouds against the oracle."""
+    kat = np.load(GOLDEN)
+    f = nnrt.geometry.functional
+    rng = np.random.default_rng(17)
+    for pts, radius in ((kat["radius/points"], float(kat["radius/radius"])), (rng.uniform(-1, 1, (20000, 3)).astype(np.float32), 0.05),
+                        (rng.normal(0, 0.3, (5000, 3)).astype(np.float32), 0.011)):
+        means = _np(f.fast_mean_radius_downsample_3d_points(pts, radius))
+        assert np.array_equal(means, oracle.fast_mean_radius_downsample_3d_points(pts, radius))
+        sample = _np(f.fast_median_radius_subsample_3d_points(pts, radius))
+        assert np.array_equal(sample, oracle.fast_median_radius_subsample_3d_points(pts, radius))
+    means = _np(f.fast_mean_radius_downsample_3d_points(kat["radius/points"], 10.0))
+    d = np.linalg.norm(means[:, None].astype(np.float64) - means[None].astype(np.float64), axis=2)
+    np.fill_diagonal(d, np.inf)
+    assert d.min() >= 10.0

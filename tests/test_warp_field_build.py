@@ -91,3 +91,15 @@ def test_oracle_mean_grid_kats(oracle):
     means = means[np.argsort(means[:, 0])]
     np.testing.assert_allclose(means, kat["mean/points_gt_sorted_by_x"], atol=1e-6)
     assert np.array_equal(oracle.closest_to_mean_grid_subsample_3d_points(kat["closest/points"], float(kat["closest/cell_size"])), kat["closest/sample_gt"])
+
+
+def test_oracle_fast_radius_downsampling_reference_property(oracle):
+    """cpp/tests/test_sampling.cpp:131-141 on the reference's own cloud: after FastMeanRadiusDownsample3dPoints(points, 10) no two
+    points are closer than the radius."""
+    kat = np.load(GOLDEN)
+    out = oracle.fast_mean_radius_downsample_3d_points(kat["radius/points"], float(kat["radius/radius"]))
+    d = np.linalg.norm(out[:, None].astype(np.float64) - out[None].astype(np.float64), axis=2)
+    np.fill_diagonal(d, np.inf)
+    assert 1 < len(out) < 100 and d.min() >= float(kat["radius/radius"])
+    sample = oracle.fast_median_radius_subsample_3d_points(kat["radius/points"], float(kat["radius/radius"]))
+    assert len(set(sample.tolist())) == len(sample) and 1 < len(sample) < 100
