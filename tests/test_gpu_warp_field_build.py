@@ -222,3 +222,17 @@ def test_fast_radius_variants_bit_exact(nnrt, oracle):
     d = np.linalg.norm(means[:, None].astype(np.float64) - means[None].astype(np.float64), axis=2)
     np.fill_diagonal(d, np.inf)
     assert d.min() >= 10.0
+
+
+def test_fitter_refuses_edges_between_coarse_layers(nnrt, oracle):
+    """A hierarchy with more than two layers has edges between coarser layers; the reference's ARAP Hessian is only defined for edges
+    from the first layer (anything else writes out of bounds there), so the fitter refuses such a field with an error."""
+    s = synthetic.make_scene("tinyr", 120, 160)
+    nodes = s["positions"][oracle.median_grid_subsample_3d_points(s["positions"], 0.03)]
+    G = nnrt.geometry
+    wf = G.HierarchicalGraphWarpField(nodes, 0.015, False, 4, 0, G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 3, 3)
+    assert wf.get_regularization_level_count() == 3 and wf.layer_node_counts[2] > 0
+    fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=1, preconditioning_dampening_factor=1.0)
+    reference_points = np.zeros((120 * 160, 3), np.float32)
+    with pytest.raises(RuntimeError, match="first-layer node"):
+        fitter.fit_to_image(wf, (s["positions"], s["normals"], s["triangles"]), None, reference_points, None, s["K"], np.eye(4), (120, 160))
