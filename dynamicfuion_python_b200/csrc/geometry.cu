@@ -327,8 +327,28 @@ __global__ void __launch_bounds__(kPathThreads) anchors_shortest_path_kernel(con
 	__syncthreads();
 	const float* __restrict__ node_xyz = cached ? s_nodes : nodes;
 	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= point_count) return;
-	const float px = points[i * 3], py = points[i * 3 + 1], pz = points[i * 3 + 2];
+	const bool active = i < point_count;
+	const float px = active ? points[i * 3] : 0.f, py = active ? points[i * 3 + 1] : 0.f, pz = active ? points[i * 3 + 2] : 0.f;
+	// With more nodes than the cache holds, the FIRST seeding scan (no anchor excluded yet, and the bulk of the work) still goes
+	// through shared memory: all threads of the CTA run it together, tile by tile. Later re-seeds (a graph component used up) are rare
+	// and read the nodes from global memory.
+	int first_seed = -1;
+	float first_seed_d2 = INFINITY;
+	if (!cached) {
+		constexpr int kTile = kPathNodeCache;
+		for (int base = 0; base < node_count; base += kTile) {
+			const int count = min(kTile, node_count - base);
+			__syncthreads();
+			for (int k = threadIdx.x; k < count * 3; k += blockDim.x) s_nodes[k] = nodes[(int64_t) base * 3 + k];
+			__syncthreads();
+			for (int k = 0; k < count; k++) {
+				const float dx = s_nodes[k * 3] - px, dy = s_nodes[k * 3 + 1] - py, dz = s_nodes[k * 3 + 2] - pz;
+				const float d2 = sum3(dx * dx, dy * dy, dz * dz);
+				if (d2 < first_seed_d2) { first_seed_d2 = d2; first_seed = base + k; }
+			}
+		}
+	}
+	if (!active) return;
 	PathQueue queue{queue_keys + threadIdx.x, queue_nodes + threadIdx.x, 0};
 	int idx[A];
 	float dist[A];
@@ -338,14 +358,19 @@ __global__ void __launch_bounds__(kPathThreads) anchors_shortest_path_kernel(con
 	while (discovered < A) {
 		int closest = -1;
 		float closest_d2 = INFINITY;
-		for (int n = 0; n < node_count; n++) {
-			bool excluded = false;
+		if (first_seed >= 0) {
+			closest = first_seed; closest_d2 = first_seed_d2;
+			first_seed = -1;
+		} else {
+			for (int n = 0; n < node_count; n++) {
+				bool excluded = false;
 #pragma unroll
-			for (int a = 0; a < A; a++) excluded |= idx[a] == n;
-			if (excluded) continue;
-			const float dx = node_xyz[n * 3] - px, dy = node_xyz[n * 3 + 1] - py, dz = node_xyz[n * 3 + 2] - pz;
-			const float d2 = sum3(dx * dx, dy * dy, dz * dz);
-			if (d2 < closest_d2) { closest_d2 = d2; closest = n; }
+				for (int a = 0; a < A; a++) excluded |= idx[a] == n;
+				if (excluded) continue;
+				const float dx = node_xyz[n * 3] - px, dy = node_xyz[n * 3 + 1] - py, dz = node_xyz[n * 3 + 2] - pz;
+				const float d2 = sum3(dx * dx, dy * dy, dz * dz);
+				if (d2 < closest_d2) { closest_d2 = d2; closest = n; }
+			}
 		}
 		if (closest == -1) break;
 		queue.insert(sqrtf(closest_d2), closest);

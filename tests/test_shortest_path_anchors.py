@@ -78,7 +78,7 @@ def test_reference_kat_on_device(nnrt):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", ["knn4", "lattice_ties", "dense_full_queue", "variable_weights", "image_shaped"])
+@pytest.mark.parametrize("case", ["knn4", "lattice_ties", "dense_full_queue", "variable_weights", "image_shaped", "many_nodes"])
 def test_bit_exact_against_oracle(nnrt, oracle, case):
     rng = np.random.default_rng(len(case))
     f = nnrt.geometry.functional
@@ -92,6 +92,12 @@ def test_bit_exact_against_oracle(nnrt, oracle, case):
         edges = knn_graph(nodes, 8)
         points = rng.uniform(-1, 1, (3000, 3)).astype(np.float32)
         anchor_count, coverage = 8, 0.4
+    elif case == "many_nodes":  # more nodes than the kernel's shared-memory cache: tiled first seeding scan, re-seeds from global memory
+        nodes = rng.uniform(-0.5, 0.5, (4000, 3)).astype(np.float32)
+        edges = knn_graph(nodes, 3)
+        edges[rng.random(edges.shape) < 0.5] = -1  # sparse: components get used up, forcing re-seeds
+        points = rng.uniform(-0.5, 0.5, (3000, 3)).astype(np.float32)
+        anchor_count, coverage = 6, 0.05
     else:
         nodes = rng.uniform(-0.5, 0.5, (250, 3)).astype(np.float32)
         edges = knn_graph(nodes, 4)
