@@ -93,16 +93,83 @@ __global__ void __launch_bounds__(kThreads) scatter_members_kernel(const int* __
 	members[bin_starts[bin] + atomicAdd(bin_fill + bin, 1)] = (int) i;
 }
 
-// arrival order -> ascending index order inside every bin (rank by counting, the same O(m) per point as the distance sums)
+// arrival order -> ascending index order inside every bin. Light bins (<= kHeavyBin members): every point ranks itself by counting
+// the smaller indices of its bin. Heavy bins: their first arrival enlists the bin, and one CTA per enlisted bin sorts its member list
+// in shared memory (bitonic, up to kSortCapacity members; larger bins are ranked by counting with the CTA's threads). For the median
+// the same CTA then stages the bin's positions in shared memory and forms every member's distance sum from there (ascending order,
+// broadcast reads) instead of one thread per point gathering its whole bin from global memory: a 1200-point bin is 1.4 M distances.
+constexpr int kHeavyBin = 64, kSortCapacity = 2048;
+
 __global__ void __launch_bounds__(kThreads) rank_members_kernel(const int* __restrict__ bin_of_point, const int* __restrict__ bin_starts,
-                                                                const int* __restrict__ members, int64_t n, int* __restrict__ sorted_members) {
+                                                                const int* __restrict__ members, int64_t n, int* __restrict__ sorted_members,
+                                                                int* __restrict__ heavy_bins, int* __restrict__ heavy_count) {
 	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
 	const int bin = bin_of_point[i];
 	const int begin = bin_starts[bin], end = bin_starts[bin + 1];
+	if (end - begin > kHeavyBin) {
+		if (members[begin] == (int) i) heavy_bins[atomicAdd(heavy_count, 1)] = bin;
+		return;
+	}
 	int rank = 0;
 	for (int k = begin; k < end; k++) rank += members[k] < (int) i;
 	sorted_members[begin + rank] = (int) i;
+}
+
+__global__ void __launch_bounds__(kThreads) sort_heavy_bins_kernel(const int* __restrict__ heavy_bins, const int* __restrict__ heavy_count,
+                                                                   const int* __restrict__ bin_starts, const int* __restrict__ members,
+                                                                   int* __restrict__ sorted_members, const float* __restrict__ median_points,
+                                                                   unsigned long long* __restrict__ best) {
+	__shared__ int s_values[kSortCapacity];
+	__shared__ float s_x[kSortCapacity], s_y[kSortCapacity], s_z[kSortCapacity];
+	if ((int) blockIdx.x >= *heavy_count) return;
+	const int bin = heavy_bins[blockIdx.x];
+	const int begin = bin_starts[bin], m = bin_starts[bin + 1] - begin;
+	if (m > kSortCapacity) {
+		for (int k = threadIdx.x; k < m; k += blockDim.x) {
+			const int value = members[begin + k];
+			int rank = 0;
+			for (int j = 0; j < m; j++) rank += members[begin + j] < value;
+			sorted_members[begin + rank] = value;
+		}
+		return;  // its distance sums are left to median_sums_kernel
+	}
+	int padded = 1;
+	while (padded < m) padded <<= 1;
+	for (int k = threadIdx.x; k < padded; k += blockDim.x) s_values[k] = k < m ? members[begin + k] : 0x7fffffff;
+	__syncthreads();
+	for (int span = 2; span <= padded; span <<= 1) {
+		for (int stride = span >> 1; stride > 0; stride >>= 1) {
+			for (int t = threadIdx.x; t < padded; t += blockDim.x) {
+				const int partner = t ^ stride;
+				if (partner > t) {
+					const int a = s_values[t], b = s_values[partner];
+					if ((a > b) == ((t & span) == 0)) { s_values[t] = b; s_values[partner] = a; }
+				}
+			}
+			__syncthreads();
+		}
+	}
+	for (int k = threadIdx.x; k < m; k += blockDim.x) {
+		const int i = s_values[k];
+		sorted_members[begin + k] = i;
+		if (median_points) { s_x[k] = median_points[(int64_t) i * 3]; s_y[k] = median_points[(int64_t) i * 3 + 1]; s_z[k] = median_points[(int64_t) i * 3 + 2]; }
+	}
+	if (!median_points) return;
+	__syncthreads();
+	unsigned long long mine = kEmptyKey;
+	for (int k = threadIdx.x; k < m; k += blockDim.x) {
+		const float sx = s_x[k], sy = s_y[k], sz = s_z[k];
+		float sum = 0.f;
+		for (int j = 0; j < m; j++) {
+			const float dx = s_x[j] - sx, dy = s_y[j] - sy, dz = s_z[j] - sz;
+			sum += sqrtf(sum3(dx * dx, dy * dy, dz * dz));
+		}
+		if (sum < FLT_MAX) mine = min(mine, ((unsigned long long) __float_as_uint(sum) << 32) | (unsigned) s_values[k]);
+	}
+#pragma unroll
+	for (int offset = 16; offset > 0; offset >>= 1) mine = min(mine, __shfl_xor_sync(0xFFFFFFFFu, mine, offset));
+	if ((threadIdx.x & 31) == 0 && mine != kEmptyKey) atomicMin(best + bin, mine);
 }
 
 __global__ void __launch_bounds__(kThreads) median_sums_kernel(const float* __restrict__ points, const int* __restrict__ bin_of_point,
@@ -112,6 +179,7 @@ __global__ void __launch_bounds__(kThreads) median_sums_kernel(const float* __re
 	if (i >= n) return;
 	const int bin = bin_of_point[i];
 	const int begin = bin_starts[bin], end = bin_starts[bin + 1];
+	if (end - begin > kHeavyBin && end - begin <= kSortCapacity) return;  // summed by the bin's own CTA (sort_heavy_bins_kernel)
 	const float* source = points + i * 3;
 	float sum = 0.f;
 	for (int k = begin; k < end; k++) sum += distance3(points + (int64_t) sorted_members[k] * 3, source);
@@ -160,7 +228,8 @@ struct SubsampleWorkspace {
 
 // Bins the points into grid cells and leaves every bin's members in ascending point order: bin_of_point, bin_counts (= CSR starts,
 // n + 2 entries) and sorted_members are valid on the stream afterwards; *bin_count_host after its ONE host synchronisation.
-int bin_points_sorted(const float* points, int64_t n, float cell_size, float offset, SubsampleWorkspace& w, int* bin_count_host, cudaStream_t s) {
+int bin_points_sorted(const float* points, int64_t n, float cell_size, float offset, SubsampleWorkspace& w, int* bin_count_host, bool median_sums,
+                      cudaStream_t s) {
 	const unsigned blocks = blocks_for(n, kThreads);
 	const size_t ints = (size_t) n + 2;
 	NNRT_CUDA(cudaMemsetAsync(w.owner, 0xFF, SubsampleWorkspace::align(sizeof(int) * w.table_size) + sizeof(unsigned long long) * ints, s));  // owner, best
@@ -178,7 +247,13 @@ int bin_points_sorted(const float* points, int64_t n, float cell_size, float off
 	rc = exclusive_scan(w.bin_counts, w.bin_counts, n + 1, w.scan_scratch, s);
 	if (rc != kOk) return rc;
 	scatter_members_kernel<<<blocks, kThreads, 0, s>>>(w.bin_of_point, w.bin_counts, n, w.bin_fill, w.members);
-	rank_members_kernel<<<blocks, kThreads, 0, s>>>(w.bin_of_point, w.bin_counts, w.members, n, w.sorted_members);
+	// the first-point ranks are consumed (assign_bins) and so is the fill counter array: reused as the heavy-bin list and its counter
+	// (bin_fill[n + 1] was zeroed with the rest and no bin id reaches it)
+	int* heavy_bins = w.rank;
+	int* heavy_count = w.bin_fill + n + 1;
+	rank_members_kernel<<<blocks, kThreads, 0, s>>>(w.bin_of_point, w.bin_counts, w.members, n, w.sorted_members, heavy_bins, heavy_count);
+	sort_heavy_bins_kernel<<<(unsigned) (n / (kHeavyBin + 1) + 1), kThreads, 0, s>>>(heavy_bins, heavy_count, w.bin_counts, w.members, w.sorted_members,
+	                                                                               median_sums ? points : nullptr, w.best);
 	NNRT_LAUNCH_CHECK();
 	return kOk;
 }
@@ -186,7 +261,7 @@ int bin_points_sorted(const float* points, int64_t n, float cell_size, float off
 // Enqueues the whole median subsample on `s`; sample[0 .. *bin_count) is valid once the stream has passed.
 int median_subsample(const float* points, int64_t n, float cell_size, float offset, SubsampleWorkspace& w, int64_t* sample, int* bin_count_host,
                      cudaStream_t s) {
-	const int rc = bin_points_sorted(points, n, cell_size, offset, w, bin_count_host, s);
+	const int rc = bin_points_sorted(points, n, cell_size, offset, w, bin_count_host, true, s);
 	if (rc != kOk) return rc;
 	median_sums_kernel<<<blocks_for(n, kThreads), kThreads, 0, s>>>(points, w.bin_of_point, w.bin_counts, w.sorted_members, n, w.best);
 	NNRT_LAUNCH_CHECK();
@@ -499,7 +574,7 @@ static int grid_mean_impl(int mode, const float* points, int64_t point_count, fl
 	w.carve(buffer, point_count);
 	float* means = mode == 1 ? (float*) (buffer + SubsampleWorkspace::bytes(point_count)) : (float*) out;
 	int bins = 0;
-	int rc = bin_points_sorted(points, point_count, grid_cell_size, grid_offset, w, &bins, s);
+	int rc = bin_points_sorted(points, point_count, grid_cell_size, grid_offset, w, &bins, false, s);
 	if (rc == kOk && cudaStreamSynchronize(s) != cudaSuccess) rc = kCudaError;
 	if (rc == kOk) {
 		bin_means_kernel<<<blocks_for(bins, kThreads), kThreads, 0, s>>>(points, w.bin_counts, w.sorted_members, bins, means);

@@ -25,10 +25,10 @@ def test_median_grid_subsample_kat(nnrt):
 
 
 @pytest.mark.parametrize("count,extent,cell", [(1, 1.0, 0.3), (10, 1.0, 0.5), (1000, 1.0, 0.25), (5000, 1.0, 0.013), (3000, 0.05, 1.0),
-                                               (60000, 2.0, 0.11), (300000, 3.0, 0.05)])
+                                               (60000, 2.0, 0.11), (300000, 3.0, 0.05), (40000, 0.05, 1.0)])
 def test_median_grid_subsample_bit_exact(nnrt, oracle, count, extent, cell):
     """Singletons (cell much smaller than the spacing), eight bins of ~375 points each (3000 points around the origin, unit cells), negative coordinates,
-    sizes across several scan tiles."""
+    sizes across several scan tiles, eight bins of ~5000 points (beyond the shared-memory sort's capacity)."""
     rng = np.random.default_rng(count)
     pts = rng.uniform(-extent, extent, (count, 3)).astype(np.float32)
     got = _np(nnrt.geometry.functional.median_grid_subsample_3d_points(pts, cell))
