@@ -114,6 +114,13 @@ def main():
     wf["closest/points"] = braces_after(g, "point_data").reshape(17, 3).astype(np.float32)
     wf["closest/cell_size"] = np.float32(2.0)
     wf["closest/sample_gt"] = braces_after(g, "sample_gt").astype(np.int64)  # AllEqual: order included
+    # Test3DKnnSearch (cpp/tests/test_kdtree.cpp:243-276): 15 points, 3 queries, k = 4, neighbours sorted by distance
+    t = read("cpp/tests/test_kdtree.cpp")
+    t = t[t.index("void Test3DKnnSearch"):]
+    wf["knn/points"] = braces_after(t, "point_data").reshape(15, 3).astype(np.float32)
+    wf["knn/queries"] = braces_after(t, "query_point_data").reshape(3, 3).astype(np.float32)
+    wf["knn/indices_gt"] = braces_after(t, "gt_nn_indices_data").reshape(3, 4).astype(np.int32)
+    wf["knn/distances_gt"] = braces_after(t, "gt_nn_distances_data").reshape(3, 4).astype(np.float32)
     # TestRadiusDownsampling (cpp/tests/test_sampling.cpp:131-141): the reference's 100-point cloud; REQUIRE(min pairwise distance >= radius)
     wf["radius/points"] = np.load(os.path.join(REF, "cpp/tests/test_data/arrays/downsampling_source.npy")).astype(np.float32)
     wf["radius/radius"] = np.float32(10.0)

@@ -236,3 +236,11 @@ def test_fitter_refuses_edges_between_coarse_layers(nnrt, oracle):
     reference_points = np.zeros((120 * 160, 3), np.float32)
     with pytest.raises(RuntimeError, match="first-layer node"):
         fitter.fit_to_image(wf, (s["positions"], s["normals"], s["triangles"]), None, reference_points, None, s["K"], np.eye(4), (120, 160))
+
+
+def test_kdtree_reference_kat(nnrt):
+    """cpp/tests/test_kdtree.cpp:243-276 through nnrt.core.KDTree(points).find_k_nearest_to_points(queries, 4, sort_output=True)."""
+    kat = np.load(GOLDEN)
+    idx, dist = nnrt.core.KDTree(kat["knn/points"]).find_k_nearest_to_points(kat["knn/queries"], 4, sort_output=True)
+    assert np.array_equal(_np(idx), kat["knn/indices_gt"])
+    np.testing.assert_allclose(_np(dist), kat["knn/distances_gt"], atol=1e-5)

@@ -103,3 +103,12 @@ def test_oracle_fast_radius_downsampling_reference_property(oracle):
     assert 1 < len(out) < 100 and d.min() >= float(kat["radius/radius"])
     sample = oracle.fast_median_radius_subsample_3d_points(kat["radius/points"], float(kat["radius/radius"]))
     assert len(set(sample.tolist())) == len(sample) and 1 < len(sample) < 100
+
+
+def test_oracle_knn_reference_kat(oracle):
+    """cpp/tests/test_kdtree.cpp:243-276: neighbours of 3 queries among 15 points, k = 4, compared after sorting by distance."""
+    kat = np.load(GOLDEN)
+    idx, dist = oracle.find_k_nearest(kat["knn/points"], kat["knn/queries"], 4)
+    order = np.argsort(dist, axis=1, kind="stable")
+    assert np.array_equal(np.take_along_axis(idx, order, 1), kat["knn/indices_gt"])
+    np.testing.assert_allclose(np.take_along_axis(dist, order, 1), kat["knn/distances_gt"], atol=1e-5)
