@@ -526,3 +526,134 @@ def fast_median_radius_subsample_3d_points(points, radius):
     stage1 = median_grid_subsample_3d_points(points, cell)
     stage2 = median_grid_subsample_3d_points(points[stage1], cell, 0.5)
     return stage1[stage2]
+
+
+# --- un-fused assembly stages ------------------------------------------------------------------------
+def pixel_vertex_anchor_jacobians(rasterized_vertex_position_jacobians, rasterized_vertex_normal_jacobians, warped_vertex_position_jacobians,
+                                  warped_vertex_normal_jacobians, point_map_vectors, rasterized_normals, residual_mask, pixel_faces,
+                                  face_anchors, face_anchor_counts, node_count, use_tukey=False, tukey_cutoff=0.01, max_pixels_per_node=0):
+    """PixelVertexAnchorJacobiansAndNodeAssociations (cap lifted unless max_pixels_per_node > 0). Returns
+    (pixel_jacobians [PX,3A,6], pixel_node_jacobian_counts [PX], node_pixel_lists [N,cap], node_pixel_counts [N], dropped)."""
+    rv, rn = _f32(rasterized_vertex_position_jacobians), _f32(rasterized_vertex_normal_jacobians)
+    wv, wn = _f32(warped_vertex_position_jacobians), _f32(warped_vertex_normal_jacobians)
+    pm, nl = _f32(point_map_vectors).reshape(-1, 3), _f32(rasterized_normals).reshape(-1, 3)
+    mask = np.ascontiguousarray(residual_mask, np.uint8).reshape(-1)
+    pf = _i64(pixel_faces).reshape(mask.shape[0], -1)
+    fa, fc = _i32(face_anchors), _i32(face_anchor_counts)
+    PX, A, K = mask.shape[0], wv.shape[1], pf.shape[1]
+    counts = np.zeros(node_count, np.int64)
+    for px in np.nonzero(mask)[0]:
+        f = pf[px, 0]
+        for k in range(fc[f]):
+            counts[fa[f, k, 0]] += 1
+    cap = int(max(1, counts.max() if node_count else 1, max_pixels_per_node + 1 if max_pixels_per_node > 0 else 1))
+    pj = np.empty((PX, 3 * A, 6), np.float32)
+    pc = np.empty(PX, np.int32)
+    lists = np.empty((node_count, cap), np.int32)
+    nc = np.empty(node_count, np.int32)
+    dropped = lib().oracle_pixel_vertex_anchor_jacobians(_p(rv), _p(rn), _p(wv), _p(wn), _p(pm), _p(nl), _p(mask), _p(pf), C.c_int(K), _p(fa), _p(fc),
+                                                         C.c_int64(PX), C.c_int(A), C.c_int(node_count), C.c_int(use_tukey), C.c_float(tukey_cutoff),
+                                                         C.c_int64(cap), C.c_int(max_pixels_per_node), _p(pj), _p(pc), _p(lists), _p(nc))
+    return pj, pc, lists, nc, int(dropped)
+
+
+def depth_hessian_and_gradient(pixel_jacobians, node_pixel_lists, node_pixel_counts, residuals, residual_mask, anchor_count):
+    """ComputeDepthHessianApproximationBlocks_UnorderedNodePixels + ComputeNegativeDepthGradient_UnorderedNodePixels."""
+    pj, lists, nc = _f32(pixel_jacobians), _i32(node_pixel_lists), _i32(node_pixel_counts)
+    N, cap = lists.shape
+    H = np.empty((N, 6, 6), np.float32)
+    g = np.empty(N * 6, np.float32)
+    res = _f32(residuals).reshape(-1)
+    mask = np.ascontiguousarray(residual_mask, np.uint8).reshape(-1)
+    lib().oracle_depth_hessian_blocks(_p(pj), _p(lists), _p(nc), C.c_int(N), C.c_int64(cap), C.c_int(0), _p(H))
+    lib().oracle_negative_depth_gradient(_p(res), _p(mask), _p(pj), _p(lists), _p(nc), C.c_int(N), C.c_int64(cap), C.c_int(anchor_count), C.c_int(0), _p(g))
+    return H, g
+
+
+# --- generic block-sparse routines (oracle_blocks.cpp) ----------------------------------------------------------------------------
+def matmul_block_sparse_row_wise(a_blocks, b_blocks, b_coordinates, padded=False):
+    a, b, bc = _f32(a_blocks), _f32(b_blocks), _i32(b_coordinates)
+    s = a.shape[1]
+    c = np.empty_like(b)
+    lib().oracle_matmul_block_sparse_row_wise_padded(_p(a), C.c_int(a.shape[0]), _p(b), _p(bc), C.c_int(b.shape[0]), C.c_int(s), _p(c))
+    if padded:
+        return c
+    keep = bc[:, 0] < a.shape[0]
+    return c[keep], bc[keep]
+
+
+def matmul_block_sparse(a_blocks, a_breadboard, transpose_a, b_blocks, b_breadboard, transpose_b):
+    a, b = _f32(a_blocks), _f32(b_blocks)
+    ab, bb = np.ascontiguousarray(a_breadboard, np.int16), np.ascontiguousarray(b_breadboard, np.int16)
+    s = a.shape[1]
+    out_rows = ab.shape[1] if transpose_a else ab.shape[0]
+    out_cols = bb.shape[0] if transpose_b else bb.shape[1]
+    blocks = np.empty((out_rows * out_cols, s, s), np.float32)
+    mask = np.empty(out_rows * out_cols, np.uint8)
+    lib().oracle_matmul_block_sparse(_p(a), _p(ab), C.c_int(ab.shape[0]), C.c_int(ab.shape[1]), C.c_int(transpose_a), _p(b), _p(bb),
+                                     C.c_int(bb.shape[0]), C.c_int(bb.shape[1]), C.c_int(transpose_b), C.c_int(s), _p(blocks), _p(mask))
+    keep = mask.astype(bool)
+    coords = np.stack(np.divmod(np.arange(out_rows * out_cols), out_cols), 1).astype(np.int32)
+    return blocks[keep], coords[keep]
+
+
+def block_sparse_and_vector_product(blocks, m, coordinates, offset, transpose, vector_b):
+    a, co, b = _f32(blocks), _i32(coordinates), _f32(vector_b)
+    c = np.empty(m, np.float32)
+    lib().oracle_block_sparse_and_vector_product(_p(a), _p(co), C.c_int(a.shape[0]), C.c_int(a.shape[1]), C.c_int(m), C.c_int(transpose),
+                                                 C.c_int(offset[0]), C.c_int(offset[1]), _p(b), _p(c))
+    return c
+
+
+def diagonal_block_sparse_and_vector_product(blocks, vector_b):
+    a, b = _f32(blocks), _f32(vector_b)
+    c = np.empty_like(b)
+    lib().oracle_diagonal_block_sparse_and_vector_product(_p(a), C.c_int(a.shape[0]), C.c_int(a.shape[1]), _p(b), _p(c))
+    return c
+
+
+def invert_positive_semidefinite_blocks(blocks):
+    a = _f32(blocks)
+    out = np.zeros_like(a)
+    fails = lib().oracle_invert_positive_semidefinite_blocks(_p(a), C.c_int(a.shape[0]), C.c_int(a.shape[1]), _p(out))
+    return out, int(fails)
+
+
+def invert_triangular_blocks(blocks, upper):
+    a = _f32(blocks)
+    out = np.empty_like(a)
+    lib().oracle_invert_triangular_blocks(_p(a), C.c_int(a.shape[0]), C.c_int(a.shape[1]), C.c_int(upper), _p(out))
+    return out
+
+
+def transpose_blocks(blocks):
+    a = _f32(blocks).copy()
+    lib().oracle_transpose_blocks_in_place(_p(a), C.c_int(a.shape[0]), C.c_int(a.shape[1]))
+    return a
+
+
+def fill_in_diagonal_blocks(matrix, blocks):
+    m, b = _f32(matrix).copy(), _f32(blocks)
+    lib().oracle_fill_in_diagonal_blocks(_p(m), C.c_int(m.shape[0]), _p(b), C.c_int(b.shape[0]), C.c_int(b.shape[1]))
+    return m
+
+
+def get_diagonal_blocks(matrix, block_size):
+    m = _f32(matrix)
+    out = np.empty((m.shape[0] // block_size, block_size, block_size), np.float32)
+    lib().oracle_get_diagonal_blocks(_p(m), C.c_int(m.shape[0]), C.c_int(block_size), _p(out))
+    return out
+
+
+def fill_in_sparse_blocks(matrix, blocks, coordinates, offset=(0, 0), transpose=False):
+    m, b, co = _f32(matrix).copy(), _f32(blocks), _i32(coordinates)
+    lib().oracle_fill_in_sparse_blocks(_p(m), C.c_int(m.shape[0]), C.c_int(m.shape[1]), _p(b), _p(co), C.c_int(b.shape[0]), C.c_int(b.shape[1]),
+                                       C.c_int(offset[0]), C.c_int(offset[1]), C.c_int(transpose))
+    return m
+
+
+def get_sparse_blocks(matrix, block_size, coordinates):
+    m, co = _f32(matrix), _i32(coordinates)
+    out = np.empty((co.shape[0], block_size, block_size), np.float32)
+    lib().oracle_get_sparse_blocks(_p(m), C.c_int(m.shape[1]), C.c_int(block_size), _p(co), C.c_int(co.shape[0]), _p(out))
+    return out
