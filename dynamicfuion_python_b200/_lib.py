@@ -47,6 +47,16 @@ _SIGNATURES = {
                                                 F32, I32, I32, F32, F32, P, P]),
     "nnrt_b200_bounding_boxes_of_warped_blocks": (C.c_int, [P, I64, P, P, P, I32, F32, I32, I32, F32, I32, P, P, P]),
     "nnrt_b200_boxes_intersecting_surface_mask": (C.c_int, [P, I64, P, P, I32, I32, I32, F32, F32, I32, F32, P, P]),
+    "nnrt_b200_pixel_vertex_anchor_jacobians": (C.c_int, [P, P, P, P, P, P, P, P, I32, P, P, P, I64, I32, I32, I32, I32, F32, P, P, P, P]),
+    "nnrt_b200_arap_term": (C.c_int, [P, I64, P, P, P, P, P, P, I32, F32, I32, F32, P, P, P, P, P, P, P]),
+    "nnrt_b200_matmul_block_sparse_row_wise_padded": (C.c_int, [P, I32, P, P, I32, I32, P, P]),
+    "nnrt_b200_matmul_block_sparse": (C.c_int, [P, P, I32, I32, I32, P, P, I32, I32, I32, I32, P, P, P]),
+    "nnrt_b200_block_sparse_and_vector_product": (C.c_int, [P, P, I32, I32, I32, I32, I32, I32, P, P, P]),
+    "nnrt_b200_diagonal_block_sparse_and_vector_product": (C.c_int, [P, I32, I32, P, P, P]),
+    "nnrt_b200_invert_positive_semidefinite_blocks": (C.c_int, [P, I32, I32, P, P, P]),
+    "nnrt_b200_invert_triangular_blocks": (C.c_int, [P, I32, I32, I32, P, P]),
+    "nnrt_b200_transpose_blocks_in_place": (C.c_int, [P, I64, I32, P]),
+    "nnrt_b200_dense_matrix_blocks": (C.c_int, [P, I64, I64, P, P, I64, I32, I32, I32, I32, I32, P]),
     "nnrt_b200_fitter_default_options": (None, [P]),
     "nnrt_b200_fitter_create": (C.c_int, [P, I64, I64, I32, I64, I32, I32, I32, P]),
     "nnrt_b200_fitter_destroy": (None, [P]),

@@ -351,6 +351,73 @@ int nnrt_b200_boxes_intersecting_surface_mask(const float* boxes, int64_t box_co
                                               int32_t depth_dtype, int32_t image_height, int32_t image_width, float depth_scale,
                                               float depth_max, int32_t stride, float truncation_distance, uint8_t* mask, void* stream);
 
+/* ---- Un-fused stages of the assembly chain (parity-test entry points; the fitter's iteration fuses them) ----
+ * alignment::functional::PixelVertexAnchorJacobiansAndNodeAssociations (alignment/functional/PixelVertexAnchorJacobians.cpp:29-56;
+ * kernel/PixelVertexAnchorJacobiansImpl.h:40-434). Inputs are the reference's intermediate tensors: rasterized vertex position /
+ * normal Jacobians [PX,3,9] / [PX,3,10] (nnrt_b200_rasterized_surface_jacobians), warped vertex position / normal Jacobians
+ * [V,A,4] / [V,A,3] (nnrt_b200_warped_surface_jacobians), point_map_vectors [PX,3] (rendered point - reference point),
+ * rasterized_normals [PX,3], residual_mask [PX] u8, pixel_faces [PX,K] int64 (k = 0 used), triangles [F,3] int64 and the compact
+ * face-anchor table of nnrt_b200_associate_faces_with_anchors. iteration_mode 0 ALL (S = 6 floats per entry: rotation, translation),
+ * 1 TRANSLATION_ONLY, 2 ROTATION_ONLY (S = 3). Outputs: pixel_jacobians [PX,3A,S] f32 (zero-filled), pixel_node_jacobian_counts
+ * [PX] int32, node_pixel_jacobian_counts [N] int32. The reference's node_pixel_jacobian_indices [N,4000] lists (capped, order
+ * scheduling-dependent) have no counterpart: nothing downstream of this library consumes per-node pixel lists. */
+int nnrt_b200_pixel_vertex_anchor_jacobians(
+		const float* rasterized_vertex_position_jacobians, const float* rasterized_vertex_normal_jacobians,
+		const float* warped_vertex_position_jacobians, const float* warped_vertex_normal_jacobians, const float* point_map_vectors,
+		const float* rasterized_normals, const uint8_t* residual_mask, const int64_t* pixel_faces, int32_t faces_per_pixel,
+		const int64_t* triangles, const int32_t* face_anchor_entries, const int32_t* face_anchor_counts, int64_t pixel_count,
+		int32_t anchor_count, int32_t node_count, int32_t iteration_mode, int32_t use_tukey_penalty, float tukey_penalty_cutoff,
+		float* pixel_jacobians, int32_t* pixel_node_jacobian_counts, int32_t* node_pixel_jacobian_counts, void* stream);
+
+/* The ARAP term as the reference materialises it: ComputeEdgeResiduals (alignment/DeformableMeshToImageFitter.cpp:392-448,
+ * kernel/DeformableMeshToImageFitterImpl.h:644-784; optional Huber), ComputeDenseArapEdgeJacobians (functional/ArapJacobian.cpp:25-72)
+ * -> edge_jacobians [E,5], ComputeArapBlockSparseHessianApproximation (functional/ArapHessian.cpp:30-48) -> ARAP part of the diagonal
+ * blocks [N,6,6], upper wing blocks [E,6,6] + coordinates [E,2] (block id = edge id), ComputeNegativeArapGradient (...Impl.h:464-642)
+ * -> [6N]. edges [E,2] int32 in virtual node order; fixed coverage: edge_layer_indices [max(E,N)] int8 + layer_decimation_radii,
+ * variable coverage: node_coverage_weights [N]. Any output pointer may be NULL. Per-node sums run in ascending edge order. */
+int nnrt_b200_arap_term(const int32_t* edges, int64_t edge_count, const int8_t* edge_layer_indices, const float* layer_decimation_radii,
+                        const float* node_coverage_weights, const float* nodes, const float* node_rotations,
+                        const float* node_translations, int32_t node_count, float arap_term_weight, int32_t use_huber_penalty,
+                        float huber_penalty_constant, float* edge_residuals, float* edge_jacobians, float* hessian_diagonal_blocks,
+                        float* upper_wing_blocks, int32_t* upper_wing_block_coordinates, float* negative_gradient, void* stream);
+
+/* ---- Generic block-sparse routines of core/linalg (block size <= 8), one per reference function; the arrowhead solve above fuses
+ * them. Pinned by the reference's inline known-answer tests (cpp/tests/test_linalg_matmul_block_sparse.cpp,
+ * cpp/tests/test_linalg_block_routines.cpp). ----
+ * core::linalg::MatmulBlockSparseRowWisePadded (core/linalg/MatmulBlockSparseImpl.h:48-150): C_k = A[row(B_k)] B_k, zero where the
+ * row has no A block; MatmulBlockSparseRowWise = the same restricted to rows < a_block_count. */
+int nnrt_b200_matmul_block_sparse_row_wise_padded(const float* blocks_a, int32_t a_block_count, const float* blocks_b,
+                                                  const int32_t* blocks_b_coordinates, int32_t b_block_count, int32_t block_size,
+                                                  float* blocks_c, void* stream);
+/* core::linalg::MatmulBlockSparse (MatmulBlockSparseImpl.h:171-420): op(A) op(B) of two block lists addressed through int16
+ * breadboards [rows, columns] (block index or -1). out_blocks [out_rows*out_columns, s, s] row-major over output positions,
+ * out_block_mask [out_rows*out_columns] = position received a product (the reference returns the masked blocks + coordinates). */
+int nnrt_b200_matmul_block_sparse(const float* blocks_a, const int16_t* a_breadboard, int32_t a_rows, int32_t a_columns, int32_t transpose_a,
+                                  const float* blocks_b, const int16_t* b_breadboard, int32_t b_rows, int32_t b_columns, int32_t transpose_b,
+                                  int32_t block_size, float* out_blocks, uint8_t* out_block_mask, void* stream);
+/* core::linalg::BlockSparseAndVectorProduct (MatmulBlockSparseImpl.h:441-600): c [output_length] = op(A) b. */
+int nnrt_b200_block_sparse_and_vector_product(const float* blocks_a, const int32_t* blocks_a_coordinates, int32_t block_count,
+                                              int32_t block_size, int32_t output_length, int32_t transpose_a, int32_t block_row_offset,
+                                              int32_t block_column_offset, const float* vector_b, float* vector_c, void* stream);
+/* core::linalg::DiagonalBlockSparseAndVectorProduct (MatmulBlockSparseImpl.h:620-700). */
+int nnrt_b200_diagonal_block_sparse_and_vector_product(const float* blocks_d, int32_t block_count, int32_t block_size, const float* vector_b,
+                                                       float* vector_c, void* stream);
+/* core::linalg::InvertPositiveSemidefiniteBlocks (core/linalg/InvertBlocks.cpp:82-127; InvertBlocksCPU.cpp:80-112 potrf + potrs;
+ * InvertBlocksCUDA.cu:96-139). failure_count_device [1] int32 = blocks that were not positive definite (left untouched). */
+int nnrt_b200_invert_positive_semidefinite_blocks(const float* blocks, int32_t block_count, int32_t block_size, float* inverted_blocks,
+                                                  int32_t* failure_count_device, void* stream);
+/* core::linalg::InvertTriangularBlocks (core/linalg/InvertBlocks.cpp:33-80); upper = 0 lower, 1 upper triangular. */
+int nnrt_b200_invert_triangular_blocks(const float* blocks, int32_t block_count, int32_t block_size, int32_t upper, float* inverted_blocks,
+                                       void* stream);
+/* core::linalg::TransposeBlocksInPlace (core/linalg/TransposeBlocks.cpp). */
+int nnrt_b200_transpose_blocks_in_place(float* blocks, int64_t block_count, int32_t block_size, void* stream);
+/* core::linalg::FillInDiagonalBlocks / GetDiagonalBlocks (core/linalg/DiagonalBlocksImpl.h; coordinates == NULL) and FillInSparseBlocks /
+ * GetSparseBlocks (core/linalg/SparseBlocksImpl.h:30-140) on a dense row-major matrix; gather = 0 writes blocks into the matrix (with
+ * `transpose` block k lands transposed at (column, row)), gather = 1 reads them out. */
+int nnrt_b200_dense_matrix_blocks(float* matrix, int64_t matrix_rows, int64_t matrix_columns, float* blocks, const int32_t* coordinates,
+                                  int64_t block_count, int32_t block_size, int32_t block_row_offset, int32_t block_column_offset,
+                                  int32_t transpose, int32_t gather, void* stream);
+
 /* Per-stage device time of one iteration measured with CUDA events outside graph capture (ms):
  * [warp_vertices, face_raster, band_raster, assemble, build_system, stem_eliminate, corner_solve_update]. */
 int nnrt_b200_fitter_profile_iteration(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,
