@@ -3,6 +3,7 @@
 // re-layout of the inputs into 128-bit SoA records, and the GN/LM loop issued as one CUDA graph (7 kernels / iteration,
 // no allocation, no host sync inside the loop).
 #include <vector>
+#include <algorithm>
 #include <cstring>
 #include "fitter_kernels.cuh"
 #include "solver_kernels.cuh"
@@ -144,13 +145,15 @@ __global__ void __launch_bounds__(128) build_system_kernel(GraphDeviceData g, co
 	for (int c = 0; c < 6; c++) rhs[n * 6 + c] = b[c];
 }
 
-// Fused replacement of build_system_kernel + stem_eliminate_kernel on the fitter path: ONE WARP PER NODE.
+// The fitter's system kernel: ONE WARP PER NODE, no atomics (ReducedSystem, solver_kernels.cuh).
 //   stem node  : H = data-term block + sum of its edges' ARAP blocks + lambda I (same summation order as build_system_kernel),
-//                wing blocks B_e kept in shared memory, D^-1 by six lanes (one unit column each), y = D^-1 b, X_e = D^-1 B_e,
-//                Schur update S -= B_e1^T X_e2 and rhs update b_C -= X_e^T b straight into the corner kernel's tile-packed buffer.
-//   corner node: H = data-term block + sum over incoming edges (lanes stride over edges, shuffle reduction) + lambda I, scattered
-//                into the corner buffer together with its right-hand side.
-// Saves one launch, the global round trip of the wing blocks and ~30 us of single-thread-per-node latency per iteration.
+//                D^-1 by six lanes (one unit column each), y = D^-1 b; per out-edge q: G_q = -a_q dE_i(q) (3 x 6, the non-zero
+//                half of the wing block B_q = [0 | G_q^T]), Y_q = D^-1 G_q^T; per ordered edge pair the 3 x 3 Schur contribution
+//                G_q1 Y_q2 and per edge the right-hand-side contribution G_q y, each WRITTEN to its own slot (the corner kernel
+//                gathers them in a fixed order).
+//   corner node: H = data-term block + sum over incoming edges (lanes stride over edges, shuffle reduction) + lambda I; its rotation
+//                block couples to nothing but its own translation and is eliminated here: C' = C - B^T A^-1 B, r' = b_t - B^T A^-1 b_r.
+// Replaces 8 launches + cuSOLVER / MAGMA batched inverses + 2 gemmBatched + atomic block sums of the reference.
 constexpr int kStemWarps = 4;
 
 __device__ __forceinline__ float skew_entry(float3 s, int r, int c) {
@@ -160,21 +163,20 @@ __device__ __forceinline__ float skew_entry(float3 s, int r, int c) {
 	return r == c ? 0.f : (neg ? -v : v);
 }
 
-__global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDeviceData g, ArrowheadSystem sys, const float* __restrict__ rotations,
+__global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDeviceData g, ReducedSystem red, const float* __restrict__ rotations,
                                                                       const float* __restrict__ translations, float* __restrict__ accumulators,
                                                                       float* __restrict__ diag, float* __restrict__ rhs) {
-	__shared__ float s_H[kStemWarps][36], s_b[kStemWarps][8], s_dinv[kStemWarps][36], s_dE[kStemWarps][20];
-	__shared__ float s_B[kStemWarps][kMaxStemDegree][36], s_X[kStemWarps][kMaxStemDegree][36];
-	__shared__ int s_col[kStemWarps][kMaxStemDegree], s_edge[kStemWarps][kMaxStemDegree];
+	__shared__ float s_H[kStemWarps][36], s_b[kStemWarps][8], s_dinv[kStemWarps][36], s_dE[kStemWarps][20], s_y[kStemWarps][8];
+	__shared__ float s_G[kStemWarps][kMaxStemDegree][18], s_Y[kStemWarps][kMaxStemDegree][18];
+	__shared__ int s_edge[kStemWarps][kMaxStemDegree];
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const int node = blockIdx.x * kStemWarps + wib;
 	if (node >= g.node_count) return;
-	const int nc = sys.node_count - sys.arrow_base, n = nc * 6;
 	float* H = s_H[wib];
 	float* b = s_b[wib];
 	// ---- stem node: lane q fetches and evaluates outgoing edge q, so the dependent loads of all edges (edge list -> endpoints ->
 	// node state) are in flight together and overlap the accumulator read below; the blocks are then summed in edge order
-	int e0 = 0, deg = 0, my_edge = 0, my_col = 0;
+	int e0 = 0, deg = 0, my_edge = 0;
 	float3 my_sk = make_float3(0.f, 0.f, 0.f), my_r = make_float3(0.f, 0.f, 0.f);
 	float my_a = 0.f;
 	if (node < g.arrow_base) {
@@ -182,7 +184,6 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 		deg = min(g.out_offsets[node + 1] - e0, kMaxStemDegree);
 		if (lane < deg) {
 			my_edge = g.out_edges[e0 + lane];
-			my_col = g.edges[my_edge].y;
 			arap_edge(g, rotations, translations, my_edge, my_sk, my_a, my_r);
 		}
 	}
@@ -204,7 +205,7 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 	}
 	__syncwarp();
 	if (node < g.arrow_base) {
-		if (lane < deg) { s_col[wib][lane] = my_col; s_edge[wib][lane] = my_edge; }
+		if (lane < deg) s_edge[wib][lane] = my_edge;
 		for (int q = 0; q < deg; q++) {
 			const float3 sk = make_float3(__shfl_sync(0xFFFFFFFFu, my_sk.x, q), __shfl_sync(0xFFFFFFFFu, my_sk.y, q), __shfl_sync(0xFFFFFFFFu, my_sk.z, q));
 			const float3 r = make_float3(__shfl_sync(0xFFFFFFFFu, my_r.x, q), __shfl_sync(0xFFFFFFFFu, my_r.y, q), __shfl_sync(0xFFFFFFFFu, my_r.z, q));
@@ -217,8 +218,8 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 			for (int k = lane; k < 36; k += 32) {
 				const int rr = k / 6, c = k % 6;
 				H[k] += sum3(dE[rr] * dE[c], dE[6 + rr] * dE[6 + c], dE[12 + rr] * dE[12 + c]);
-				s_B[wib][q][k] = c < 3 ? 0.f : sum3(dE[rr] * (c == 3 ? bj : 0.f), dE[6 + rr] * (c == 4 ? bj : 0.f), dE[12 + rr] * (c == 5 ? bj : 0.f));
 			}
+			if (lane < 18) s_G[wib][q][lane] = dE[lane] * bj;  // G_q = dE_j^T-scaled dE_i: wing block B_q = [0 | G_q^T]
 			if (lane < 6) b[lane] -= sum3(dE[lane] * r.x, dE[6 + lane] * r.y, dE[12 + lane] * r.z);
 			__syncwarp();
 		}
@@ -260,7 +261,7 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 					L[i * 6 + j] = v / dj;
 				}
 			}
-			if (!ok && lane == 0) atomicExch(sys.flags + 2, 1);
+			if (!ok && lane == 0) atomicExch(red.flags + 2, 1);
 			float xcol[6];
 #pragma unroll
 			for (int i = 0; i < 6; i++) {
@@ -285,48 +286,37 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 			float acc = 0.f;
 #pragma unroll
 			for (int k = 0; k < 6; k++) acc += Dinv[lane * 6 + k] * b[k];
-			sys.stem_y[node * 6 + lane] = acc;
+			s_y[wib][lane] = acc;
+			red.stem_y[node * 6 + lane] = acc;
 		}
-		// X_e = D^-1 B_e (kept in shared memory for the Schur update, written out for the back substitution)
-		for (int idx = lane; idx < deg * 36; idx += 32) {
-			const int q = idx / 36, k = idx % 36, rr = k / 6, c = k % 6;
+		// Y_q = D^-1 G_q^T (6 x 3): kept in shared memory for the pair products, written out for the back substitution
+		for (int idx = lane; idx < deg * 18; idx += 32) {
+			const int q = idx / 18, k = idx % 18, rr = k / 3, c = k % 3;
 			float acc = 0.f;
 #pragma unroll
-			for (int m = 0; m < 6; m++) acc += Dinv[rr * 6 + m] * s_B[wib][q][m * 6 + c];
-			s_X[wib][q][k] = acc;
-			sys.wing_x[(int64_t) s_edge[wib][q] * 36 + k] = acc;
+			for (int m = 0; m < 6; m++) acc += Dinv[rr * 6 + m] * s_G[wib][q][c * 6 + m];
+			s_Y[wib][q][k] = acc;
+			red.wing_y[(int64_t) s_edge[wib][q] * 18 + k] = acc;
 		}
 		__syncwarp();
-		// S[c1, c2] -= B_e1^T X_e2 ; with the tile-packed layout only block pairs on or below the diagonal are stored
-		// one 6 x 6 product per edge pair: entries 0..31 of a pair go to the 32 lanes, the four tail entries (32..35) of eight pairs
-		// are gathered into one more pass; no per-item division by the runtime degree
-		auto schur_entry = [&](int q1, int q2, int rr, int c) {
-			const int c1 = s_col[wib][q1] - sys.arrow_base, c2 = s_col[wib][q2] - sys.arrow_base;
-			if (sys.schur_tile_packed && c1 < c2) return;
+		// Schur contributions of every ordered edge pair: (G_q1 Y_q2), 3 x 3, one slot each
+		const int* slots = red.pair_slots + red.pair_offsets[node];
+		for (int idx = lane; idx < deg * deg * 9; idx += 32) {
+			const int pair = idx / 9, k = idx % 9, q1 = pair / deg, q2 = pair % deg, rr = k / 3, c = k % 3;
+			const int slot = slots[pair];
+			if (slot < 0) continue;  // col(q1) < col(q2): the mirror image of a stored pair
 			float acc = 0.f;
 #pragma unroll
-			for (int m = 0; m < 6; m++) acc += s_B[wib][q1][m * 6 + rr] * s_X[wib][q2][m * 6 + c];
-			const int64_t slot = schur_slot(sys, n, c1 * 6 + rr, c2 * 6 + c);
-			if (slot >= 0) atomicAdd(sys.schur + slot, -acc);
-		};
-		{
-			const int rr = lane / 6, c = lane % 6;
-			for (int q1 = 0; q1 < deg; q1++)
-				for (int q2 = 0; q2 < deg; q2++) schur_entry(q1, q2, rr, c);
-			const int tail = 32 + (lane & 3), tail_rr = tail / 6, tail_c = tail % 6;
-			for (int first = 0; first < deg * deg; first += 8) {
-				const int pair = first + (lane >> 2);
-				if (pair < deg * deg) schur_entry(pair / deg, pair % deg, tail_rr, tail_c);
-			}
+			for (int m = 0; m < 6; m++) acc += s_G[wib][q1][rr * 6 + m] * s_Y[wib][q2][m * 3 + c];
+			red.pair_blocks[(int64_t) slot * 12 + k] = acc;
 		}
-		// b_C[c] -= X_e^T b
-		for (int idx = lane; idx < deg * 6; idx += 32) {
-			const int q = idx / 6, c = idx % 6;
+		// right-hand-side contributions G_q y
+		for (int idx = lane; idx < deg * 3; idx += 32) {
+			const int q = idx / 3, rr = idx % 3;
 			float acc = 0.f;
 #pragma unroll
-			for (int m = 0; m < 6; m++) acc += s_X[wib][q][m * 6 + c] * b[m];
-			const int col = (s_col[wib][q] - sys.arrow_base) * 6 + c;
-			atomicAdd(sys.schur_tile_packed ? sys.schur + corner_tile_index(n, n, col) : sys.corner_rhs + col, -acc);
+			for (int m = 0; m < 6; m++) acc += s_G[wib][q][rr * 6 + m] * s_y[wib][m];
+			red.edge_rhs[(int64_t) red.in_slots[s_edge[wib][q]] * 4 + rr] = acc;
 		}
 	} else {
 		const int cj = node - g.arrow_base;
@@ -349,14 +339,63 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 		__syncwarp();
 		if (lane < 6 && g.lm_factor > 0.f) H[lane * 7] += g.lm_factor;
 		__syncwarp();
-		for (int k = lane; k < 36; k += 32) {
-			diag[(int64_t) node * 36 + k] = H[k];
-			const int64_t slot = schur_slot(sys, n, cj * 6 + k / 6, cj * 6 + k % 6);
-			if (slot >= 0) atomicAdd(sys.schur + slot, H[k]);
-		}
-		if (lane < 6) {
-			rhs[node * 6 + lane] = b[lane];
-			atomicAdd(sys.schur_tile_packed ? sys.schur + corner_tile_index(n, n, cj * 6 + lane) : sys.corner_rhs + cj * 6 + lane, b[lane]);
+		for (int k = lane; k < 36; k += 32) diag[(int64_t) node * 36 + k] = H[k];
+		if (lane < 6) rhs[node * 6 + lane] = b[lane];
+		if (lane == 0) {
+			// eliminate the node's rotation: A = H[0:3,0:3] = L L^T, [A^-1 B | A^-1 b_r] by two triangular solves per column
+			float L[9];
+			bool ok = true;
+#pragma unroll
+			for (int j = 0; j < 3; j++) {
+				float dj = H[j * 6 + j];
+#pragma unroll
+				for (int k = 0; k < j; k++) dj -= L[j * 3 + k] * L[j * 3 + k];
+				if (!(dj > 0.f)) ok = false;
+				dj = sqrtf(dj);
+				L[j * 3 + j] = dj;
+#pragma unroll
+				for (int i = j + 1; i < 3; i++) {
+					float v = H[i * 6 + j];
+#pragma unroll
+					for (int k = 0; k < j; k++) v -= L[i * 3 + k] * L[j * 3 + k];
+					L[i * 3 + j] = v / dj;
+				}
+			}
+			if (!ok) atomicExch(red.flags + 2, 1);
+			float sol[4][3];  // columns 0..2: A^-1 B, column 3: A^-1 b_r
+#pragma unroll
+			for (int c = 0; c < 4; c++) {
+#pragma unroll
+				for (int i = 0; i < 3; i++) {
+					float v = c < 3 ? H[i * 6 + 3 + c] : b[i];
+#pragma unroll
+					for (int k = 0; k < i; k++) v -= L[i * 3 + k] * sol[c][k];
+					sol[c][i] = v / L[i * 3 + i];
+				}
+#pragma unroll
+				for (int i = 2; i >= 0; i--) {
+					float v = sol[c][i];
+#pragma unroll
+					for (int k = i + 1; k < 3; k++) v -= L[k * 3 + i] * sol[c][k];
+					sol[c][i] = v / L[i * 3 + i];
+				}
+			}
+#pragma unroll
+			for (int rr = 0; rr < 3; rr++) {
+#pragma unroll
+				for (int c = 0; c < 3; c++) {
+					float v = H[(3 + rr) * 6 + 3 + c];
+#pragma unroll
+					for (int k = 0; k < 3; k++) v -= H[k * 6 + 3 + rr] * sol[c][k];  // B^T (A^-1 B)
+					red.corner_c[cj * 9 + rr * 3 + c] = v;
+					red.corner_ainvb[cj * 9 + rr * 3 + c] = sol[c][rr];
+				}
+				float v = b[3 + rr];
+#pragma unroll
+				for (int k = 0; k < 3; k++) v -= H[k * 6 + 3 + rr] * sol[3][k];
+				red.corner_r[cj * 3 + rr] = v;
+				red.corner_zr[cj * 3 + rr] = sol[3][rr];
+			}
 		}
 	}
 }
@@ -391,6 +430,12 @@ struct nnrt_b200_fitter {
 	int32_t* anchors; float* weights; float* nodes;
 	int2* edges; float *ew_res, *ew_jac; int *out_offsets, *out_edges, *in_offsets, *in_edges, *wing_columns;
 	float *accum, *sys_diag, *sys_rhs, *wing, *dinv, *stem_y, *wing_x, *schur, *corner_rhs, *x;
+	// reduced (deterministic) solve: per-producer slots gathered by the corner kernel (solver_kernels.cuh ReducedSystem)
+	float *wing_y, *edge_rhs, *corner_c, *corner_r, *corner_ainvb, *corner_zr;
+	char* graph_buffer = nullptr;  // sized by the graph: pair_offsets, list_offsets, list_items, pair_blocks, dense corner (if beyond one SM)
+	int *pair_offsets = nullptr, *list_offsets = nullptr, *pair_slots = nullptr, *in_slots = nullptr, listed_pairs = 0;
+	int2* block_pairs = nullptr;
+	float *pair_blocks = nullptr, *reduced_packed = nullptr, *reduced_dense = nullptr, *reduced_dense_rhs = nullptr;
 	unsigned long long* keys; nnrt_b200::BandItem* queue; int* counters;
 	int32_t* diag_faces; float* diag_res; uint8_t* diag_mask;
 	// cached graph
@@ -429,6 +474,9 @@ static size_t layout(nnrt_b200_fitter* f, bool assign) {
 	f->dinv = f->take<float>((int64_t) N * 36); f->stem_y = f->take<float>(nmax); f->wing_x = f->take<float>((E + 1) * 36);
 	// dense corner: sized for the worst case the graph can ask for is N blocks; allocate lazily bounded by what set_model needs
 	f->x = f->take<float>(nmax);
+	f->wing_y = f->take<float>((E + 1) * 18); f->edge_rhs = f->take<float>((E + 1) * 4);
+	f->corner_c = f->take<float>((int64_t) N * 9); f->corner_r = f->take<float>((int64_t) N * 3);
+	f->corner_ainvb = f->take<float>((int64_t) N * 9); f->corner_zr = f->take<float>((int64_t) N * 3);
 	f->diag_faces = f->take<int32_t>(PX); f->diag_res = f->take<float>(PX); f->diag_mask = f->take<uint8_t>(PX);
 	return f->arena_used;
 }
@@ -480,6 +528,7 @@ extern "C" void nnrt_b200_fitter_destroy(nnrt_b200_fitter* f) {
 	if (f->graph_exec) cudaGraphExecDestroy(f->graph_exec);
 	cudaFree(f->arena);
 	cudaFree(f->schur);  // corner buffers are allocated by set_model (their size depends on arrow_base)
+	cudaFree(f->graph_buffer);
 	cudaFreeHost(f->host_flags);
 	delete f;
 }
@@ -561,10 +610,87 @@ extern "C" int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* f, const float* node
 	NNRT_CUDA(cudaMemcpyAsync(f->out_edges, out_e.data(), sizeof(int) * (E + 1), cudaMemcpyHostToDevice, s));
 	NNRT_CUDA(cudaMemcpyAsync(f->in_edges, in_e.data(), sizeof(int) * (E + 1), cudaMemcpyHostToDevice, s));
 	NNRT_CUDA(cudaMemcpyAsync(f->wing_columns, wcol.data(), sizeof(int) * (E + 1), cudaMemcpyHostToDevice, s));
+	// ---- reduced solve: slot of every ordered edge pair of a stem node, and per lower corner block pair (c1 >= c2) the list of the
+	// pair slots that contribute to it, in ascending (stem node, q1, q2) order: the corner kernel sums them in exactly this order
+	const int corner_blocks = N - arrow_base;
+	std::vector<int> pair_off((size_t) arrow_base + 1, 0);
+	for (int i = 0; i < arrow_base; i++) {
+		const int deg = out_off[i + 1] - out_off[i];
+		pair_off[i + 1] = pair_off[i] + (fused_stem ? deg * deg : 0);
+	}
+	// listed block pairs: every diagonal pair first (they carry the corner's own block), then the off-diagonal pairs (c1 > c2) that
+	// share at least one stem node, in order of first appearance
+	std::vector<int> pair_c1c2, list_off, pair_slot((size_t) pair_off[arrow_base] + 1, -1), in_slot((size_t) E + 1, 0);
+	if (fused_stem) {
+		std::vector<int> counts;
+		std::vector<std::pair<long long, int>> seen;  // (c1 * Nc + c2, listed index) kept sorted for lookup
+		for (int c = 0; c < corner_blocks; c++) { pair_c1c2.push_back(c); pair_c1c2.push_back(c); counts.push_back(0); }
+		auto find_or_add = [&](int c1, int c2) -> int {
+			if (c1 == c2) return c1;
+			const long long key = (long long) c1 * corner_blocks + c2;
+			auto it = std::lower_bound(seen.begin(), seen.end(), std::make_pair(key, -1));
+			if (it != seen.end() && it->first == key) return it->second;
+			const int idx = (int) counts.size();
+			seen.insert(it, std::make_pair(key, idx));
+			pair_c1c2.push_back(c1); pair_c1c2.push_back(c2); counts.push_back(0);
+			return idx;
+		};
+		std::vector<int> item_pair((size_t) pair_off[arrow_base], -1);
+		for (int i = 0; i < arrow_base; i++) {
+			const int deg = out_off[i + 1] - out_off[i];
+			for (int q1 = 0; q1 < deg; q1++)
+				for (int q2 = 0; q2 < deg; q2++) {
+					const int c1 = wcol[out_e[out_off[i] + q1]] - arrow_base, c2 = wcol[out_e[out_off[i] + q2]] - arrow_base;
+					if (c1 < c2) continue;
+					const int idx = find_or_add(c1, c2);
+					item_pair[pair_off[i] + q1 * deg + q2] = idx;
+					counts[idx]++;
+				}
+		}
+		list_off.assign(counts.size() + 1, 0);
+		for (size_t k = 0; k < counts.size(); k++) list_off[k + 1] = list_off[k] + counts[k];
+		std::vector<int> cursor(list_off.begin(), list_off.end() - 1);
+		for (size_t k = 0; k < item_pair.size(); k++)
+			if (item_pair[k] >= 0) pair_slot[k] = cursor[item_pair[k]]++;
+		for (int c = 0; c < corner_blocks; c++)
+			for (int q = in_off[c]; q < in_off[c + 1]; q++) in_slot[in_e[q]] = q;
+	} else {
+		list_off.assign(1, 0);
+	}
+	const int listed_pairs = (int) list_off.size() - 1;
+	{
+		auto al = [](size_t v) { return (v + 255) & ~size_t(255); };
+		const bool wide = fused_stem && !reduced_corner_fits_one_cta(corner_blocks);
+		const size_t n3 = (size_t) corner_blocks * 3;
+		const size_t sz_po = al(sizeof(int) * pair_off.size()), sz_lo = al(sizeof(int) * list_off.size()), sz_ps = al(sizeof(int) * pair_slot.size()),
+		             sz_is = al(sizeof(int) * in_slot.size()), sz_pc = al(sizeof(int) * (pair_c1c2.size() + 2)),
+		             sz_pb = al(sizeof(float) * ((size_t) list_off[listed_pairs] * 12 + 64)),
+		             sz_pk = wide ? 0 : al(sizeof(float) * reduced_packed_floats(corner_blocks)),
+		             sz_d = wide ? al(sizeof(float) * n3 * n3) : 0, sz_dr = wide ? al(sizeof(float) * (n3 + 16)) : 0;
+		if (f->graph_buffer) { cudaFree(f->graph_buffer); f->graph_buffer = nullptr; }
+		const size_t total = sz_po + sz_lo + sz_ps + sz_is + sz_pc + sz_pb + sz_pk + sz_d + sz_dr;
+		NNRT_CUDA(cudaMalloc(&f->graph_buffer, total));
+		NNRT_CUDA(cudaMemsetAsync(f->graph_buffer, 0, total, s));  // the packed system's never-written entries (padding, strict upper tiles) stay zero
+		char* q = f->graph_buffer;
+		f->pair_offsets = (int*) q; q += sz_po;
+		f->list_offsets = (int*) q; q += sz_lo;
+		f->pair_slots = (int*) q; q += sz_ps;
+		f->in_slots = (int*) q; q += sz_is;
+		f->block_pairs = (int2*) q; q += sz_pc;
+		f->pair_blocks = (float*) q; q += sz_pb;
+		f->reduced_packed = wide ? nullptr : (float*) q; q += sz_pk;
+		f->reduced_dense = wide ? (float*) q : nullptr; q += sz_d;
+		f->reduced_dense_rhs = wide ? (float*) q : nullptr;
+		f->listed_pairs = listed_pairs;
+		NNRT_CUDA(cudaMemcpyAsync(f->pair_offsets, pair_off.data(), sizeof(int) * pair_off.size(), cudaMemcpyHostToDevice, s));
+		NNRT_CUDA(cudaMemcpyAsync(f->list_offsets, list_off.data(), sizeof(int) * list_off.size(), cudaMemcpyHostToDevice, s));
+		NNRT_CUDA(cudaMemcpyAsync(f->pair_slots, pair_slot.data(), sizeof(int) * pair_slot.size(), cudaMemcpyHostToDevice, s));
+		NNRT_CUDA(cudaMemcpyAsync(f->in_slots, in_slot.data(), sizeof(int) * in_slot.size(), cudaMemcpyHostToDevice, s));
+		if (!pair_c1c2.empty()) NNRT_CUDA(cudaMemcpyAsync(f->block_pairs, pair_c1c2.data(), sizeof(int) * pair_c1c2.size(), cudaMemcpyHostToDevice, s));
+	}
 	NNRT_CUDA(cudaStreamSynchronize(s));  // host staging vectors go out of scope
 
-	// dense corner buffers (size depends on arrow_base)
-	const int corner_blocks = N - arrow_base;
+	// dense corner buffers of the unfused fallback (size depends on arrow_base)
 	bool reallocated = false;
 	if (corner_blocks != f->corner_blocks || f->schur == nullptr) {
 		reallocated = true;
@@ -577,7 +703,8 @@ extern "C" int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* f, const float* node
 		f->corner_rhs = f->schur + schur_floats;
 	}
 	// the captured iteration graph bakes in the arrowhead shape and the corner buffers: keep it unless one of them moved
-	if (f->graph_exec && (arrow_base != f->arrow_base || fused_stem != f->fused_stem || reallocated)) {
+	(void) reallocated;
+	if (f->graph_exec) {  // the reduced solve's lists and slots were just reallocated: the captured pointers are stale
 		cudaGraphExecDestroy(f->graph_exec);
 		f->graph_exec = nullptr;
 	}
@@ -651,7 +778,7 @@ extern "C" int nnrt_b200_fitter_set_reference_depth(nnrt_b200_fitter* f, const v
 namespace nnrt_b200 {
 
 struct IterationContext {
-	FitterDeviceData d; GraphDeviceData g; ArrowheadSystem sys; DataTermParams p; NdcCamera cam; Rigid extrinsics;
+	FitterDeviceData d; GraphDeviceData g; ArrowheadSystem sys; ReducedSystem red; DataTermParams p; NdcCamera cam; Rigid extrinsics;
 };
 
 static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const double* T) {
@@ -674,6 +801,13 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	c.sys.inverted_stem = f->dinv; c.sys.stem_y = f->stem_y; c.sys.wing_x = f->wing_x; c.sys.schur = f->schur; c.sys.corner_rhs = f->corner_rhs;
 	c.sys.schur_tile_packed = corner_uses_tile_packed_schur(f->N - f->arrow_base) ? 1 : 0;
 	c.sys.flags = f->counters;
+	c.red.node_count = f->N; c.red.arrow_base = f->arrow_base; c.red.row_offsets = f->out_offsets; c.red.row_blocks = f->out_edges;
+	c.red.wing_columns = f->wing_columns; c.red.in_offsets = f->in_offsets; c.red.in_edges = f->in_edges;
+	c.red.pair_offsets = f->pair_offsets; c.red.pair_slots = f->pair_slots; c.red.list_offsets = f->list_offsets; c.red.in_slots = f->in_slots;
+	c.red.stem_y = f->stem_y; c.red.wing_y = f->wing_y; c.red.pair_blocks = f->pair_blocks; c.red.edge_rhs = f->edge_rhs;
+	c.red.corner_c = f->corner_c; c.red.corner_r = f->corner_r; c.red.corner_ainvb = f->corner_ainvb; c.red.corner_zr = f->corner_zr;
+	c.red.block_pair_count = f->listed_pairs; c.red.block_pairs = f->block_pairs; c.red.packed = f->reduced_packed;
+	c.red.dense = f->reduced_dense; c.red.dense_rhs = f->reduced_dense_rhs; c.red.flags = f->counters;
 	c.cam = ndc_camera_from_host(K, f->H, f->W);
 	c.p.height = f->H; c.p.width = f->W; c.p.pinhole = intrinsics_from_host(K); c.p.ndc = c.cam.k; c.p.max_depth = f->opt.max_depth;
 	c.p.perspective_correct = f->opt.use_perspective_correction; c.p.use_tukey = f->opt.use_tukey_penalty;
@@ -719,8 +853,14 @@ static int enqueue_solve(nnrt_b200_fitter* f, const IterationContext& base, int 
 	c.g.iteration_mode = iteration_mode;
 	c.sys.update_mode = iteration_mode;
 	if (f->fused_stem) {
-		system_stem_kernel<<<(f->N + kStemWarps - 1) / kStemWarps, kStemWarps * 32, 0, s>>>(c.g, c.sys, R, t, f->accum, f->sys_diag, f->sys_rhs);
+		c.red.update_mode = iteration_mode;
+		system_stem_kernel<<<(f->N + kStemWarps - 1) / kStemWarps, kStemWarps * 32, 0, s>>>(c.g, c.red, R, t, f->accum, f->sys_diag, f->sys_rhs);
 		if (ev) { cudaEventRecord(ev[5], s); cudaEventRecord(ev[6], s); }
+		const int rc = launch_reduced_corner_solve(c.red, f->x, R, t, s);
+		if (ev) cudaEventRecord(ev[7], s);
+		if (rc != kOk) return rc;
+		NNRT_LAUNCH_CHECK();
+		return kOk;
 	} else {  // stem rows with more than kMaxStemDegree edges: unfused pair of kernels
 		build_system_kernel<<<(f->N + 127) / 128, 128, 0, s>>>(c.g, R, t, f->accum, f->sys_diag, f->sys_rhs, f->wing);
 		if (ev) cudaEventRecord(ev[5], s);

@@ -461,6 +461,35 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_blocked_kernel(Ar
 #endif
 }
 
+// Reduced fitter system, after the dense solve of the corner translations xt (shared memory, 3 per corner node): corner rotations
+// x_r = A^-1 b_r - (A^-1 B) x_t, stem unknowns x_i = y_i - sum_e Y_e x_t[col(e)]; x is [N, 6] = (rotation, translation) per node.
+__device__ __forceinline__ void reduced_back_substitution(const ReducedSystem& red, const float* __restrict__ xt, float* __restrict__ x, int tid, int T) {
+	const int nc = red.node_count - red.arrow_base;
+	for (int idx = tid; idx < nc * 6; idx += T) {
+		const int c = idx / 6, r = idx - c * 6;
+		float v;
+		if (r >= 3) v = xt[c * 3 + r - 3];
+		else {
+			v = red.corner_zr[c * 3 + r];
+#pragma unroll
+			for (int k = 0; k < 3; k++) v = fmaf(-red.corner_ainvb[c * 9 + r * 3 + k], xt[c * 3 + k], v);
+		}
+		x[(red.arrow_base + c) * 6 + r] = v;
+	}
+	for (int idx = tid; idx < red.arrow_base * 6; idx += T) {
+		const int i = idx / 6, r = idx - i * 6;
+		float acc = red.stem_y[idx];
+		for (int e = red.row_offsets[i]; e < red.row_offsets[i + 1]; e++) {
+			const int w = red.row_blocks[e];
+			const float* Y = red.wing_y + (int64_t) w * 18 + r * 3;
+			const float* xv = xt + (red.wing_columns[w] - red.arrow_base) * 3;
+#pragma unroll
+			for (int k = 0; k < 3; k++) acc = fmaf(-Y[k], xv[k], acc);
+		}
+		x[idx] = acc;
+	}
+}
+
 // ---- register-tiled single-CTA corner solve (n + 1 <= 256) ---------------------------------------------------------------
 // The trailing matrix never round-trips through shared memory: thread t owns ONE 8 x 8 tile (bi, bj), bi >= bj, of the
 // augmented lower triangle (rhs = row n) in 64 registers for the whole factorisation. Tiles are handed out by descending
@@ -547,12 +576,25 @@ __device__ __forceinline__ void lookahead_factor(const float* current, const flo
 	}
 }
 
-__global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(ArrowheadSystem sys, float* __restrict__ x,
+// kReduced: the fitter's deterministic path (ReducedSystem, solver_kernels.cuh): the matrix is the 3 Nc x 3 Nc system over the corner
+// translations, gathered here in a fixed order from the stem kernel's per-node products instead of being read from an
+// atomically accumulated buffer.
+template<bool kReduced>
+__global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(ArrowheadSystem sys, ReducedSystem red, float* __restrict__ x,
                                                                               float* __restrict__ rotations, float* __restrict__ translations,
                                                                               int clear_corner) {
 	extern __shared__ __align__(16) float smem[];
 	const int tid = threadIdx.x, T = blockDim.x;
-	const int nc = sys.node_count - sys.arrow_base, n = nc * 6;
+	const int nc = kReduced ? red.node_count - red.arrow_base : sys.node_count - sys.arrow_base, n = nc * (kReduced ? 3 : 6);
+	int* const flags = kReduced ? red.flags : sys.flags;
+	if (kReduced && n == 0) {  // no corner (edge-free warp field): the stem kernel already solved every block
+		reduced_back_substitution(red, smem, x, tid, T);
+		if (rotations == nullptr) return;
+		__syncthreads();
+		__threadfence_block();
+		for (int node = tid; node < red.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3, red.update_mode);
+		return;
+	}
 	const int tr = (n + 1 + kTile - 1) / kTile, tc = (n + kTile - 1) / kTile, prow = tr * kTile;
 	float* Lf = smem;                                         // final factor, aligned-packed rows (back substitution)
 	float* PT = Lf + aligned_row_start(prow);                 // [8][prow] current panel strip, transposed
@@ -583,7 +625,7 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 	// ---- load this thread's tile: the stem kernel accumulated S and the rhs row directly in warp-interleaved tile order, so the
 	// tile is 16 fully coalesced 128-bit loads; the buffer is zeroed behind the load for the next iteration's accumulation
 	if (has_tile) {
-		float4* tile = reinterpret_cast<float4*>(sys.schur) + (tid >> 5) * 512 + (tid & 31);
+		float4* tile = reinterpret_cast<float4*>(kReduced ? red.packed : sys.schur) + (tid >> 5) * 512 + (tid & 31);
 		float4 v[16];
 #pragma unroll
 		for (int q = 0; q < 16; q++) v[q] = __ldcg(tile + q * 32);
@@ -592,17 +634,17 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 			a[r][0] = v[2 * r].x; a[r][1] = v[2 * r].y; a[r][2] = v[2 * r].z; a[r][3] = v[2 * r].w;
 			a[r][4] = v[2 * r + 1].x; a[r][5] = v[2 * r + 1].y; a[r][6] = v[2 * r + 1].z; a[r][7] = v[2 * r + 1].w;
 		}
-		if (clear_corner) {
+		if (!kReduced && clear_corner) {  // the reduced system is rewritten entry by entry each iteration: nothing accumulates
 #pragma unroll
 			for (int q = 0; q < 16; q++) tile[q * 32] = make_float4(0.f, 0.f, 0.f, 0.f);
 		}
-		if (bj == 0) {
-			float4* dst = RAW + bi * 9;
+	}
+	if (has_tile && bj == 0) {
+		float4* dst = RAW + bi * 9;
 #pragma unroll
-			for (int r = 0; r < kTile; r++) {
-				dst[r] = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
-				dst[raw_plane + r] = make_float4(a[r][4], a[r][5], a[r][6], a[r][7]);
-			}
+		for (int r = 0; r < kTile; r++) {
+			dst[r] = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
+			dst[raw_plane + r] = make_float4(a[r][4], a[r][5], a[r][6], a[r][7]);
 		}
 	}
 	if (has_tile && bi == bj && bj < 2) {
@@ -613,7 +655,7 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 	}
 	const bool lookahead_warp = tid < 32;   // warp 0: oldest warp of the CTA, so the scheduler does not starve the critical chain
 	__syncthreads();
-	if (lookahead_warp) lookahead_factor(DN, nullptr, prow, min(kTile, n), FAC, inv_diag, sys.flags);
+	if (lookahead_warp) lookahead_factor(DN, nullptr, prow, min(kTile, n), FAC, inv_diag, flags);
 	__syncthreads();
 	NNRT_STAMP(0);
 	for (int p = 0; p < tc; p++) {
@@ -721,7 +763,7 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 #endif
 		if (lookahead_warp && p + 1 < tc)
 			lookahead_factor(DN + ((p + 1) & 1) * 64, PT + (p + 1) * kTile, prow, min(kTile, n - (p + 1) * kTile), FAC + ((p + 1) & 1) * 72,
-			                 inv_diag + (p + 1) * kTile, sys.flags);
+			                 inv_diag + (p + 1) * kTile, flags);
 #ifdef NNRT_PHASE_TIMING
 		if (lookahead_warp && (tid & 31) == 0 && (p == 0 || p == 12 || p == 24)) g_phase_clock[13 + p / 12] = clock64() - tl0 + (long long) (FAC[((p + 1) & 1) * 72] == 12345.f);
 #endif
@@ -799,8 +841,22 @@ __global__ void __launch_bounds__(kCornerThreads) corner_solve_regtile_kernel(Ar
 #endif
 		}
 		__syncthreads();
-		for (int k = tid; k < n; k += T) x[sys.arrow_base * 6 + k] = xs[k];
+		if (!kReduced)
+			for (int k = tid; k < n; k += T) x[sys.arrow_base * 6 + k] = xs[k];
 		NNRT_STAMP(3);
+	}
+	if (kReduced) {
+		reduced_back_substitution(red, xs, x, tid, T);
+		if (rotations == nullptr) return;
+		__syncthreads();
+		NNRT_STAMP(4);
+		__threadfence_block();
+		for (int node = tid; node < red.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3, red.update_mode);
+#ifdef NNRT_PHASE_TIMING
+		__syncthreads();
+		NNRT_STAMP(5);
+#endif
+		return;
 	}
 	// stem back-substitution: x_i = y_i - sum_e X_e x_C[col(e)]
 	for (int idx = tid; idx < sys.arrow_base * 6; idx += T) {
@@ -936,8 +992,9 @@ __global__ void __launch_bounds__(256) corner_wide_trailing_kernel(ArrowheadSyst
 }
 
 // Back substitution L^T x = y (y = the forward-substituted right-hand side), stem back substitution and node update: one CTA.
-__global__ void __launch_bounds__(1024) corner_wide_finish_kernel(ArrowheadSystem sys, int n, float* __restrict__ x, float* __restrict__ rotations,
-                                                                   float* __restrict__ translations) {
+template<bool kReduced>
+__global__ void __launch_bounds__(1024) corner_wide_finish_kernel(ArrowheadSystem sys, ReducedSystem red, int n, float* __restrict__ x,
+                                                                   float* __restrict__ rotations, float* __restrict__ translations) {
 	extern __shared__ float y[];  // [n]
 	const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31;
 	for (int k = tid; k < n; k += T) y[k] = sys.corner_rhs[k];
@@ -975,6 +1032,14 @@ __global__ void __launch_bounds__(1024) corner_wide_finish_kernel(ArrowheadSyste
 		}
 		__syncthreads();
 	}
+	if (kReduced) {
+		reduced_back_substitution(red, y, x, tid, T);
+		if (rotations == nullptr) return;
+		__syncthreads();
+		__threadfence_block();
+		for (int node = tid; node < red.node_count; node += T) apply_node_update(x + node * 6, rotations + node * 9, translations + node * 3, red.update_mode);
+		return;
+	}
 	for (int k = tid; k < n; k += T) x[sys.arrow_base * 6 + k] = y[k];
 	for (int idx = tid; idx < sys.arrow_base * 6; idx += T) {
 		const int i = idx / 6, r = idx - i * 6;
@@ -995,7 +1060,7 @@ __global__ void __launch_bounds__(1024) corner_wide_finish_kernel(ArrowheadSyste
 }
 
 static int launch_corner_solve_wide(const ArrowheadSystem& sys, int n, float* x, float* node_rotations, float* node_translations, bool clear_corner,
-                                    cudaStream_t s) {
+                                    cudaStream_t s, const ReducedSystem* red = nullptr) {
 	if ((size_t) n * sizeof(float) > 160 * 1024) return kUnsupported;
 	for (int j = 0; j < n; j += kWide) {
 		const int nb = n - j < kWide ? n - j : kWide;
@@ -1006,14 +1071,103 @@ static int launch_corner_solve_wide(const ArrowheadSystem& sys, int n, float* x,
 			corner_wide_trailing_kernel<<<dim3(tiles, tiles), 256, 0, s>>>(sys, n, j);
 		}
 	}
-	static SharedMemoryOptIn finish_opt_in;
-	if (finish_opt_in.ensure(corner_wide_finish_kernel, 160 * 1024) != kOk) return kCudaError;
-	corner_wide_finish_kernel<<<1, 1024, (size_t) n * sizeof(float), s>>>(sys, n, x, node_rotations, node_translations);
+	static SharedMemoryOptIn finish_opt_in, finish_reduced_opt_in;
+	if (red) {
+		if (finish_reduced_opt_in.ensure(corner_wide_finish_kernel<true>, 160 * 1024) != kOk) return kCudaError;
+		corner_wide_finish_kernel<true><<<1, 1024, (size_t) n * sizeof(float), s>>>(sys, *red, n, x, node_rotations, node_translations);
+		return kOk;  // the dense buffer is rewritten by the next gather: nothing to clear
+	}
+	if (finish_opt_in.ensure(corner_wide_finish_kernel<false>, 160 * 1024) != kOk) return kCudaError;
+	corner_wide_finish_kernel<false><<<1, 1024, (size_t) n * sizeof(float), s>>>(sys, ReducedSystem{}, n, x, node_rotations, node_translations);
 	if (clear_corner) {
 		if (cudaMemsetAsync(sys.schur, 0, (size_t) n * n * sizeof(float), s) != cudaSuccess) return kCudaError;
 		if (cudaMemsetAsync(sys.corner_rhs, 0, (size_t) n * sizeof(float), s) != cudaSuccess) return kCudaError;
 	}
 	return kOk;
+}
+
+// Gather of the reduced corner system: ONE WARP per listed block pair (then one per corner node for the right-hand side). The lanes
+// load the pair's contiguous run of 3 x 3 products (32 at a time), a fixed shuffle tree sums them, the diagonal block is added and
+// the nine entries are written where the corner kernel expects them (tile-packed, or the dense buffer of the multi-kernel path).
+// Nothing is accumulated atomically: the result does not depend on scheduling.
+__global__ void __launch_bounds__(128) reduced_gather_kernel(ReducedSystem red) {
+	const int lane = threadIdx.x & 31, item = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const int nc = red.node_count - red.arrow_base, n = nc * 3;
+	if (item >= red.block_pair_count + nc) return;
+	float v[9];
+#pragma unroll
+	for (int k = 0; k < 9; k++) v[k] = 0.f;
+	const bool is_pair = item < red.block_pair_count;
+	int c1 = 0, c2 = 0, first, last;
+	if (is_pair) {
+		const int2 cc = red.block_pairs[item];
+		c1 = cc.x; c2 = cc.y; first = red.list_offsets[item]; last = red.list_offsets[item + 1];
+	} else {
+		c1 = c2 = item - red.block_pair_count; first = red.in_offsets[c1]; last = red.in_offsets[c1 + 1];
+	}
+	for (int q0 = first; q0 < last; q0 += 32) {
+		float w[9];
+#pragma unroll
+		for (int k = 0; k < 9; k++) w[k] = 0.f;
+		if (q0 + lane < last) {
+			if (is_pair) {
+				const float4* src = reinterpret_cast<const float4*>(red.pair_blocks) + (int64_t) (q0 + lane) * 3;
+				const float4 a = __ldcg(src), b = __ldcg(src + 1), c = __ldcg(src + 2);
+				w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w; w[8] = c.x;
+			} else {
+				const float4 a = __ldcg(reinterpret_cast<const float4*>(red.edge_rhs) + (q0 + lane));
+				w[0] = a.x; w[1] = a.y; w[2] = a.z;
+			}
+		}
+#pragma unroll
+		for (int off = 16; off >= 1; off >>= 1)
+#pragma unroll
+			for (int k = 0; k < 9; k++)
+				if (is_pair || k < 3) w[k] += __shfl_xor_sync(0xFFFFFFFFu, w[k], off);
+#pragma unroll
+		for (int k = 0; k < 9; k++) v[k] += w[k];
+	}
+	if (is_pair) {
+		if (lane < 9) {
+			float total = 0.f;
+#pragma unroll
+			for (int k = 0; k < 9; k++) total = lane == k ? v[k] : total;
+			const float value = (c1 == c2 ? red.corner_c[c1 * 9 + lane] : 0.f) - total;
+			const int row = c1 * 3 + lane / 3, col = c2 * 3 + lane % 3;
+			if (col <= row) {
+				if (red.packed) red.packed[corner_tile_index(n, row, col)] = value;
+				else red.dense[(int64_t) row * n + col] = value;
+			}
+		}
+	} else if (lane < 3) {
+		const float total = lane == 0 ? v[0] : lane == 1 ? v[1] : v[2];
+		const float value = red.corner_r[c1 * 3 + lane] - total;
+		if (red.packed) red.packed[corner_tile_index(n, n, c1 * 3 + lane)] = value;
+		else red.dense_rhs[c1 * 3 + lane] = value;
+	}
+}
+
+bool reduced_corner_fits_one_cta(int corner_blocks) { return corner_blocks == 0 || regtile_corner_fits(corner_blocks * 3); }
+size_t reduced_packed_floats(int corner_blocks) { return corner_blocks == 0 ? 64 : (size_t) corner_tile_floats(corner_blocks * 3) + 64; }
+
+int launch_reduced_corner_solve(const ReducedSystem& red, float* x, float* node_rotations, float* node_translations, cudaStream_t s) {
+	const int nc = red.node_count - red.arrow_base, n = nc * 3;
+	const int items = red.block_pair_count + nc;
+	if (reduced_corner_fits_one_cta(nc)) {
+		if (items > 0) reduced_gather_kernel<<<(items + 3) / 4, 128, 0, s>>>(red);
+		static SharedMemoryOptIn opt_in;
+		if (opt_in.ensure(corner_solve_regtile_kernel<true>, 227 * 1024) != kOk) return kCudaError;
+		corner_solve_regtile_kernel<true><<<1, kCornerThreads, regtile_corner_floats(n > 0 ? n : 1) * sizeof(float), s>>>(ArrowheadSystem{}, red, x, node_rotations,
+		                                                                                                             node_translations, 0);
+		return kOk;
+	}
+	if (red.dense == nullptr) return kInvalidArgument;
+	// the multi-kernel factorisation works in place: the dense buffer is rebuilt (zeros included) every iteration
+	if (cudaMemsetAsync(red.dense, 0, (size_t) n * n * sizeof(float), s) != cudaSuccess) return kCudaError;
+	reduced_gather_kernel<<<(items + 3) / 4, 128, 0, s>>>(red);
+	ArrowheadSystem dense{};
+	dense.schur = red.dense; dense.corner_rhs = red.dense_rhs; dense.flags = red.flags;
+	return launch_corner_solve_wide(dense, n, x, node_rotations, node_translations, false, s, &red);
 }
 
 bool corner_uses_tile_packed_schur(int corner_blocks) { return regtile_corner_fits(corner_blocks * 6); }
@@ -1035,8 +1189,8 @@ int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotati
 	if (sys.schur_tile_packed) {
 		if (!regtile_corner_fits(n)) return kInvalidArgument;
 		static SharedMemoryOptIn regtile_opt_in;
-		if (regtile_opt_in.ensure(corner_solve_regtile_kernel, kMaxShared) != kOk) return kCudaError;
-		corner_solve_regtile_kernel<<<1, kCornerThreads, regtile_corner_floats(n) * sizeof(float), s>>>(sys, x, node_rotations, node_translations, clear_corner ? 1 : 0);
+		if (regtile_opt_in.ensure(corner_solve_regtile_kernel<false>, kMaxShared) != kOk) return kCudaError;
+		corner_solve_regtile_kernel<false><<<1, kCornerThreads, regtile_corner_floats(n) * sizeof(float), s>>>(sys, ReducedSystem{}, x, node_rotations, node_translations, clear_corner ? 1 : 0);
 		return kOk;
 	}
 	if (blocked_bytes <= kMaxShared) {

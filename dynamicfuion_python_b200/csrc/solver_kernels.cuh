@@ -68,6 +68,41 @@ __device__ __forceinline__ int64_t schur_slot(const ArrowheadSystem& sys, int n,
 	return (col > row) ? -1 : corner_tile_index(n, row, col);
 }
 
+// ---- fitter path: deterministic, reduced corner -------------------------------------------------------------------------------
+// In the fitter's system the ARAP residual of an edge (i -> j) depends on R_i, t_i and t_j only (DeformableMeshToImageFitterImpl.h:
+// 697-713) and the data term couples nothing across nodes, so (two-layer graphs) the ROTATION unknowns of a corner node couple to
+// nothing but that node's own translation: they are eliminated block-wise like the stem, which leaves a dense system over the
+// corner TRANSLATIONS only (3 Nc unknowns instead of 6 Nc: an eighth of the Cholesky flops, half its dependency chain). Every sum
+// that the stem elimination used to scatter with float atomics is written once per producer (pair_blocks, edge_rhs) and gathered by
+// the corner kernel in a fixed order through lists built once per graph on the host: bit-identical results run to run.
+struct ReducedSystem {
+	int node_count, arrow_base;
+	const int* row_offsets; const int* row_blocks;   // CSR over out-edges (edge ids) by stem node
+	const int* wing_columns;                          // [E] global index of the edge's corner node
+	const int* in_offsets; const int* in_edges;       // CSR over in-edges by corner node, ascending edge id
+	const int* pair_offsets;                          // [stem + 1] prefix sums of deg_i^2
+	const int* pair_slots;                            // [sum deg^2] slot in pair_blocks of the ordered edge pair (q1, q2) of a stem node, -1: not stored
+	int block_pair_count;                             // lower corner block pairs (c1 >= c2) that receive a product, plus every diagonal pair
+	const int2* block_pairs;                          // [block_pair_count] (c1, c2)
+	const int* list_offsets;                          // [block_pair_count + 1] CONTIGUOUS slot range of each listed block pair
+	const int* in_slots;                              // [E] position of edge e in the in-edge order of its corner node (slot in edge_rhs)
+	float* stem_y;        // [stem, 6]   y_i = D_i^-1 b_i
+	float* wing_y;        // [E, 18]     Y_e = D_i^-1 G_e^T (6 x 3), G_e = -a_e dE_i(e) (3 x 6)
+	float* pair_blocks;   // [slots, 12]  G_q1 Y_q2 (3 x 3 + pad) of the edge pairs of the stem nodes with col(q1) >= col(q2), grouped by block pair
+	float* edge_rhs;      // [E, 4]      G_e y_i (+ pad), grouped by corner node
+	float* corner_c;      // [Nc, 9]     C' = C - B^T A^-1 B (translation block after eliminating the node's rotation)
+	float* corner_r;      // [Nc, 3]     r' = b_t - B^T A^-1 b_r
+	float* corner_ainvb;  // [Nc, 9]     A^-1 B
+	float* corner_zr;     // [Nc, 3]     A^-1 b_r
+	float* packed;        // tile-packed lower triangle + rhs row of the reduced corner system (corner_tile_index with n = 3 Nc): one SM
+	float* dense; float* dense_rhs;  // [(3 Nc)^2], [3 Nc]: corners beyond one SM (multi-kernel path); exactly one of packed / dense is set
+	int* flags;           // flags[2] set when a block is not positive definite
+	int update_mode;
+};
+bool reduced_corner_fits_one_cta(int corner_blocks);
+size_t reduced_packed_floats(int corner_blocks);  // allocation size of ReducedSystem::packed (zero-initialised once)
+int launch_reduced_corner_solve(const ReducedSystem& sys, float* x, float* node_rotations, float* node_translations, cudaStream_t s);
+
 void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s);
 // x [6N]; if node_rotations != nullptr the update is applied in place; clear_corner zeroes schur / corner_rhs after reading.
 int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotations, float* node_translations, bool clear_corner,
