@@ -3,11 +3,16 @@
 // with the oracle at 1e-4 relative and contain heavy cancellation, so it is compiled like the rest with -fmad=false and IEEE
 // division (see build.py for the measured alternative); the residual chain is written with rounding intrinsics regardless.
 #include "fitter_kernels.cuh"
+#include "fixed_accum.cuh"
 #include "jacobian_math.cuh"
 
 namespace nnrt_b200 {
 
 // Transposed warp reduction: every lane passes 32 values, lane l receives the warp-wide sum of value l (31 shuffles).
+// (Measured alternative, round 2: the same per-node Gram matrix M^T M as four k-steps of mma.sync m16n8k8 with a TF32 head / tail split
+// of every operand, fragments exchanged through 1 KB of shared memory per warp. It executes a third of the instructions of this
+// tree but runs 5.6 us SLOWER per launch (44.9 vs 39.3 us): on sm_100a the legacy mma.sync path has a long issue-to-result latency
+// and the kernel is bound by the latency of each warp's dependent chain, not by instruction issue.)
 __device__ __forceinline__ float warp_transpose_reduce(float (&vals)[32], int lane) {
 #pragma unroll
 	for (int half = 16; half >= 1; half >>= 1) {
@@ -214,7 +219,8 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 			for (int c = 0; c < 6; c++) vals[21 + c] = J6[c] * residual;
 		}
 		const float total = warp_transpose_reduce(vals, lane);
-		if (lane < 27) atomicAdd(d.accumulators + (int64_t) node * kAccumStride + lane, total);
+		// integer (fixed-point) atomics: the per-node sums do not depend on the order in which warps arrive (fixed_accum.cuh)
+		if (lane < 27) fixed_accum_add(d.accumulators + ((int64_t) node * kAccumStride + lane) * 2, total, d.counters + 3);
 	}
 	// the band queue was fully drained before this kernel started: reset its counter for the next iteration
 	if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) d.counters[0] = 0;

@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cstring>
 #include "fitter_kernels.cuh"
+#include "fixed_accum.cuh"
 #include "solver_kernels.cuh"
 #include "../../include/nnrt_b200.h"
 
@@ -79,22 +80,22 @@ __device__ __forceinline__ void arap_edge(const GraphDeviceData& g, const float*
 // wing blocks B_e = dE_i^T dE_j of the node's outgoing edges (ArapHessianImpl.h:117-189, ComputeNegativeArapGradient
 // DeformableMeshToImageFitterImpl.h:496-540, PreconditionDiagonalBlocksImpl.h). Replaces 8 launches + float atomics.
 __global__ void __launch_bounds__(128) build_system_kernel(GraphDeviceData g, const float* __restrict__ rotations,
-                                                            const float* __restrict__ translations, float* __restrict__ accumulators,
+                                                            const float* __restrict__ translations, unsigned long long* __restrict__ accumulators,
                                                             float* __restrict__ diag, float* __restrict__ rhs, float* __restrict__ wing) {
 	const int n = blockIdx.x * blockDim.x + threadIdx.x;
 	if (n >= g.node_count) return;
 	float H[36], b[6];
-	float* acc = accumulators + (int64_t) n * kAccumStride;
+	unsigned long long* acc = accumulators + (int64_t) n * kAccumStride * 2;
 	{
 		int o = 0;
 #pragma unroll
 		for (int c0 = 0; c0 < 6; c0++)
 #pragma unroll
-			for (int c1 = c0; c1 < 6; c1++) { const float v = acc[o++]; H[c0 * 6 + c1] = v; H[c1 * 6 + c0] = v; }
+			for (int c1 = c0; c1 < 6; c1++) { const float v = fixed_accum_value(acc[o * 2], acc[o * 2 + 1]); o++; H[c0 * 6 + c1] = v; H[c1 * 6 + c0] = v; }
 #pragma unroll
-		for (int c = 0; c < 6; c++) b[c] = 0.f - acc[21 + c];
+		for (int c = 0; c < 6; c++) b[c] = 0.f - fixed_accum_value(acc[(21 + c) * 2], acc[(21 + c) * 2 + 1]);
 #pragma unroll
-		for (int k = 0; k < 27; k++) acc[k] = 0.f;  // clean for the next iteration's assembly
+		for (int k = 0; k < 54; k++) acc[k] = 0ull;  // clean for the next iteration's assembly
 	}
 	if (g.edge_count > 0) {
 		if (n < g.arrow_base) {
@@ -164,7 +165,7 @@ __device__ __forceinline__ float skew_entry(float3 s, int r, int c) {
 }
 
 __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDeviceData g, ReducedSystem red, const float* __restrict__ rotations,
-                                                                      const float* __restrict__ translations, float* __restrict__ accumulators,
+                                                                      const float* __restrict__ translations, unsigned long long* __restrict__ accumulators,
                                                                       float* __restrict__ diag, float* __restrict__ rhs) {
 	__shared__ float s_H[kStemWarps][36], s_b[kStemWarps][8], s_dinv[kStemWarps][36], s_dE[kStemWarps][20], s_y[kStemWarps][8];
 	__shared__ float s_G[kStemWarps][kMaxStemDegree][18], s_Y[kStemWarps][kMaxStemDegree][18];
@@ -189,10 +190,11 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 	}
 	// ---- data term from the pixel accumulators (21 upper-triangular + 6), cleaned for the next iteration
 	{
-		float* acc = accumulators + (int64_t) node * kAccumStride;
+		ulonglong2* acc = reinterpret_cast<ulonglong2*>(accumulators) + (int64_t) node * kAccumStride;
 		if (lane < 27) {
-			const float v = acc[lane];
-			acc[lane] = 0.f;
+			const ulonglong2 words = acc[lane];
+			acc[lane] = make_ulonglong2(0ull, 0ull);
+			const float v = fixed_accum_value(words.x, words.y);
 			if (lane < 21) {
 				int c0 = 0, o = lane;
 				while (o >= 6 - c0) { o -= 6 - c0; c0++; }
@@ -429,7 +431,8 @@ struct nnrt_b200_fitter {
 	int4* tris;
 	int32_t* anchors; float* weights; float* nodes;
 	int2* edges; float *ew_res, *ew_jac; int *out_offsets, *out_edges, *in_offsets, *in_edges, *wing_columns;
-	float *accum, *sys_diag, *sys_rhs, *wing, *dinv, *stem_y, *wing_x, *schur, *corner_rhs, *x;
+	unsigned long long* accum;
+	float *sys_diag, *sys_rhs, *wing, *dinv, *stem_y, *wing_x, *schur, *corner_rhs, *x;
 	// reduced (deterministic) solve: per-producer slots gathered by the corner kernel (solver_kernels.cuh ReducedSystem)
 	float *wing_y, *edge_rhs, *corner_c, *corner_r, *corner_ainvb, *corner_zr;
 	char* graph_buffer = nullptr;  // sized by the graph: pair_offsets, list_offsets, list_items, pair_blocks, dense corner (if beyond one SM)
@@ -469,7 +472,7 @@ static size_t layout(nnrt_b200_fitter* f, bool assign) {
 	f->refpts = f->take<float4>(PX);
 	f->keys = f->take<unsigned long long>(PX);
 	f->queue = f->take<BandItem>(F + 65536); f->counters = f->take<int>(4);
-	f->accum = f->take<float>((int64_t) N * kAccumStride);
+	f->accum = f->take<unsigned long long>((int64_t) N * kAccumStride * 2);
 	f->sys_diag = f->take<float>((int64_t) N * 36); f->sys_rhs = f->take<float>(nmax); f->wing = f->take<float>((E + 1) * 36);
 	f->dinv = f->take<float>((int64_t) N * 36); f->stem_y = f->take<float>(nmax); f->wing_x = f->take<float>((E + 1) * 36);
 	// dense corner: sized for the worst case the graph can ask for is N blocks; allocate lazily bounded by what set_model needs
@@ -751,7 +754,7 @@ extern "C" int nnrt_b200_fitter_set_reference_points(nnrt_b200_fitter* f, const 
 	NNRT_CHECK_ARG(f && reference_points, "fitter_set_reference_points: null pointer argument");
 	const int64_t px = (int64_t) f->H * f->W;
 	// a new observation starts a new fit: its status must not inherit the overflow / not-positive-definite flags of an earlier one
-	NNRT_CUDA(cudaMemsetAsync(f->counters + 1, 0, 2 * sizeof(int), (cudaStream_t) stream));
+	NNRT_CUDA(cudaMemsetAsync(f->counters + 1, 0, 3 * sizeof(int), (cudaStream_t) stream));
 	pack_reference_kernel<<<blocks_for(px, 256), 256, 0, (cudaStream_t) stream>>>(reference_points, reference_mask, px, f->refpts);
 	NNRT_LAUNCH_CHECK();
 	f->reference_set = true;
@@ -765,7 +768,7 @@ extern "C" int nnrt_b200_fitter_set_reference_depth(nnrt_b200_fitter* f, const v
 	const int64_t px = (int64_t) f->H * f->W;
 	const Intrinsics k = intrinsics_from_host(intrinsics_host);
 	auto s = (cudaStream_t) stream;
-	NNRT_CUDA(cudaMemsetAsync(f->counters + 1, 0, 2 * sizeof(int), s));  // see set_reference_points
+	NNRT_CUDA(cudaMemsetAsync(f->counters + 1, 0, 3 * sizeof(int), s));  // see set_reference_points
 	if (depth_dtype == 0)
 		reference_from_depth_kernel<float><<<blocks_for(px, 256), 256, 0, s>>>((const float*) depth, user_mask, f->H, f->W, k, depth_scale, f->opt.max_depth, f->refpts);
 	else
@@ -893,10 +896,10 @@ extern "C" int nnrt_b200_fitter_set_pixel_rows(nnrt_b200_fitter* f, int32_t row_
 	return kOk;
 }
 
-extern "C" float* nnrt_b200_fitter_accumulators(nnrt_b200_fitter* f, int64_t* float_count) {
+extern "C" int64_t* nnrt_b200_fitter_accumulators(nnrt_b200_fitter* f, int64_t* word_count) {
 	if (f == nullptr) return nullptr;
-	if (float_count) *float_count = (int64_t) f->N * kAccumStride;
-	return f->accum;
+	if (word_count) *word_count = (int64_t) f->N * kAccumStride * 2;
+	return reinterpret_cast<int64_t*>(f->accum);
 }
 
 extern "C" int nnrt_b200_fitter_iteration_data_term(nnrt_b200_fitter* f, float* node_rotations, float* node_translations,
@@ -974,6 +977,7 @@ extern "C" int nnrt_b200_fitter_status(nnrt_b200_fitter* f, void* stream) {
 	NNRT_CUDA(cudaStreamSynchronize((cudaStream_t) stream));
 	if (f->host_flags[1]) { set_last_error("fitter: large-face band queue overflow"); return kQueueOverflow; }
 	if (f->host_flags[2]) { set_last_error("fitter: a Hessian block was not positive definite"); return kNotPositiveDefinite; }
+	if (f->host_flags[3]) { set_last_error("fitter: a data-term sum left the accumulator range (non-finite, or magnitude above 4e12)"); return kNotPositiveDefinite; }
 	return kOk;
 }
 

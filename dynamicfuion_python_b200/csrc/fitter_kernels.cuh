@@ -8,7 +8,7 @@
 //   face-anchor table                         int2   [F, 3A] + u8 count [F]   (node, packed per-vertex anchor slots)
 //   pixel keys                                u64    [H*W]          (depth bits << 32 | face), ~0 = empty
 //   reference points                          float4 [H*W]          (xyz, mask)
-//   node accumulators                         f32    [N, 32]        21 upper-triangular J^T J + 6 J^T r + pad
+//   node accumulators                         2 x u64 [N, 32]       21 upper-triangular J^T J + 6 J^T r + pad, 103-bit fixed point (fixed_accum.cuh)
 #pragma once
 #include "host_util.h"
 #include "raster_core.cuh"
@@ -39,10 +39,10 @@ struct FitterDeviceData {
 	const float* nodes; int node_count; int arrow_base;
 	// per-iteration buffers
 	float4* warped_positions; float4* warped_normals; float4* vertex_jacobians;
-	unsigned long long* keys; BandItem* band_queue; int* counters;  // counters[0] = queue count, [1] = overflow flag, [2] = not-PD flag
+	unsigned long long* keys; BandItem* band_queue; int* counters;  // counters[0] = queue count, [1] = overflow flag, [2] = not-PD flag, [3] = accumulator range flag
 	int band_queue_capacity;
 	const float4* reference_points;
-	float* accumulators;
+	unsigned long long* accumulators;  // [N, kAccumStride, 2] fixed-point words (fixed_accum.cuh)
 	int32_t* diag_pixel_faces; float* diag_residuals; uint8_t* diag_mask;  // diagnostics of the last iteration
 };
 

@@ -134,7 +134,6 @@ class DeformableMeshToImageFitter:
                 T.call("nnrt_b200_fitter_iteration_data_term", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), T.stream())
                 pixel_shard.all_reduce_sum(acc, group)
                 T.call("nnrt_b200_fitter_iteration_solve", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), it, T.stream())
-                pixel_shard.broadcast_node_state(R, t, group)
         self._keep = (K, ext)
 
     def check_status(self):

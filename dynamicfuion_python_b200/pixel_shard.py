@@ -1,12 +1,13 @@
 """Pixel-sharded single-frame mode of the dense-depth fitter (BASELINE.json configs[3]).
 
 The image is cut into one band of rows per GPU. Every GPU holds the whole mesh and graph, warps it redundantly, rasterises and
-assembles its own band, and the per-node partial sums of J^T J and J^T r ([node_count, 32] fp32: 21 + 6 used) are all-reduced once
-per Gauss-Newton iteration; the ARAP term, the arrowhead solve and the node update are replicated. The replicas see identical
-sums but their Schur complements are accumulated with float atomics (order varies run to run), so the updated node state differs
-in the last bits between ranks; rank 0's state is broadcast after every iteration (12 floats per node) to keep the bands
-consistent. fp32 summation order differs from the single-GPU run, hence parity with it is 1e-4 relative, not bit-exact. At 640x480 one band is a few microseconds of work against an all-reduce of tens of
-microseconds: the mode is built for 4K frames and reported as measured.
+assembles its own band, and the per-node partial sums of J^T J and J^T r are all-reduced once per Gauss-Newton iteration; the ARAP
+term, the arrowhead solve and the node update are replicated. The sums live in 103-bit fixed point (two int64 words per entry,
+csrc/fixed_accum.cuh) and are exchanged as int64: integer addition is associative, so every rank holds bit-identical sums whatever
+order NCCL reduces in, they equal the single-GPU sums bit for bit (bands are multiples of the 8-row assembly tile, so every warp sees
+the same 32 pixels as in the unsharded fit), and the replicated solves -- which use no atomics -- keep the node state identical on
+all ranks with no broadcast. At 640x480 one band is a few microseconds of work against an all-reduce of tens of microseconds: the
+mode is built for 4K frames and reported as measured.
 """
 import torch
 import torch.distributed as dist
@@ -26,10 +27,10 @@ def pixel_rows(rank, world_size, height, align=8):
 
 
 class DeviceBuffer:
-    """Zero-copy torch view of a float32 device buffer owned by the C library (CUDA array interface)."""
+    """Zero-copy torch view of an int64 device buffer owned by the C library (CUDA array interface)."""
 
     def __init__(self, pointer, count):
-        self.__cuda_array_interface__ = {"shape": (int(count),), "typestr": "<f4", "data": (int(pointer), False), "version": 2}
+        self.__cuda_array_interface__ = {"shape": (int(count),), "typestr": "<i8", "data": (int(pointer), False), "version": 2}
 
     def tensor(self, device):
         return torch.as_tensor(self, device=device)
@@ -40,10 +41,3 @@ def all_reduce_sum(tensor, group=None):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(tensor, op=dist.ReduceOp.SUM, group=group)
     return tensor
-
-
-def broadcast_node_state(rotations, translations, group=None):
-    """Rank 0's node rotations / translations replace everyone's (see module docstring)."""
-    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-        dist.broadcast(rotations, group=group, group_src=0)
-        dist.broadcast(translations, group=group, group_src=0)

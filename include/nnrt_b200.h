@@ -191,13 +191,17 @@ int nnrt_b200_fitter_set_mesh(nnrt_b200_fitter* fitter, const float* vertex_posi
  * (.cpp:198, 262-272) and are defined for edge-free warp fields only, as in the reference (fit returns an error otherwise). */
 int nnrt_b200_fitter_set_iteration_modes(nnrt_b200_fitter* fitter, const int32_t* modes_host, int32_t mode_count);
 /* Pixel-sharded single frame (one exchange per iteration): every GPU holds the whole mesh and graph, rasterises and assembles
- * only image rows [row_begin, row_end), and the per-node J^T J / J^T r partial sums (the accumulator buffer, node_count x 32 f32:
- * 21 upper-triangular entries + 6 gradient entries + padding) are summed across GPUs by the caller (ncclAllReduce) between
- * iteration_data_term and iteration_solve; the solve is replicated. The reference has no multi-GPU path; the sums being
- * exchanged are those of ComputeDepthHessianApproximationBlocks_UnorderedNodePixels / ComputeNegativeDepthGradient_...
- * (alignment/kernel/DeformableMeshToImageFitterImpl.h:199-420). iteration_index selects the IterationMode of the sequence. */
+ * only image rows [row_begin, row_end) (multiples of 8 rows, the assembly tile), and the per-node J^T J / J^T r partial sums are
+ * summed across GPUs by the caller between iteration_data_term and iteration_solve; the solve is replicated. The accumulator
+ * buffer is node_count x 32 entries (21 upper-triangular + 6 gradient + padding) of two 64-bit words each: a 103-bit FIXED-POINT
+ * number (value = int64 word0 * 2^-20 + uint64 word1 * 2^-60) that the assembly kernel adds to with integer atomics. Integer sums
+ * are order-independent, so an all-reduce of the words as int64 (ncclAllReduce, ncclInt64, ncclSum) gives every rank bit-identical
+ * sums, equal to the single-GPU sums: the replicated solves stay bit-identical without any broadcast. The reference has no
+ * multi-GPU path; the sums being exchanged are those of ComputeDepthHessianApproximationBlocks_UnorderedNodePixels /
+ * ComputeNegativeDepthGradient_... (alignment/kernel/DeformableMeshToImageFitterImpl.h:199-420). iteration_index selects the
+ * IterationMode of the sequence. */
 int nnrt_b200_fitter_set_pixel_rows(nnrt_b200_fitter* fitter, int32_t row_begin, int32_t row_end);
-float* nnrt_b200_fitter_accumulators(nnrt_b200_fitter* fitter, int64_t* float_count);
+int64_t* nnrt_b200_fitter_accumulators(nnrt_b200_fitter* fitter, int64_t* word_count);
 int nnrt_b200_fitter_iteration_data_term(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,
                                          const double* intrinsics_host, const double* extrinsics_host, void* stream);
 int nnrt_b200_fitter_iteration_solve(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,

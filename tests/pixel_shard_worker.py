@@ -35,9 +35,9 @@ def main():
 
     R1, t1 = fit(False)
     R2, t2 = fit(True)
-    scale = float(t1.abs().max())
-    assert float((t2 - t1).abs().max()) <= 1e-3 * scale, float((t2 - t1).abs().max())
-    assert float((R2 - R1).abs().max()) <= 1e-4
+    # integer (fixed-point) sums all-reduced as int64: the sharded fit equals the single-GPU fit bit for bit
+    assert torch.equal(t2, t1), float((t2 - t1).abs().max())
+    assert torch.equal(R2, R1), float((R2 - R1).abs().max())
     # identical state on every rank (replicated solve on all-reduced sums)
     gathered = [torch.zeros_like(t2) for _ in range(world)]
     dist.all_gather(gathered, t2)
