@@ -1,11 +1,15 @@
 """bench.py — dense-depth GN iteration benchmark (BASELINE.json metric: ms per GN iteration @640x480; frames/s box-wide).
 
 A frame fit of configuration C2 (bunny-scale relief mesh, ~82k triangles, 249 nodes = 208 stem + 41 corner, 832 edges, 640x480
-depth) is the reference's once-per-fit setup (anchors, face-anchor association, reference unprojection;
-DeformableMeshToImageFitter.cpp:96-106,293-307) plus ITERATIONS_PER_FRAME Gauss-Newton iterations (:111-275). A "step" is one frame
-of each of `--sequences` independent sequences resident on the GPU (BASELINE.json configs[4]; each sequence has its own fitter, warp
-field and CUDA stream, frames inside a sequence are serial). The single-sequence latency (ms per GN iteration, the <= 1 ms target)
-is measured in a separate leg and reported as `ms_per_iteration` / `latency`.
+depth) is the reference's once-per-fit setup (anchors, reference unprojection; DeformableMeshToImageFitter.cpp:96-106,293-307) plus
+ITERATIONS_PER_FRAME Gauss-Newton iterations (:111-275). A "step" is FRAMES_PER_STEP consecutive frames of each of `--sequences`
+independent sequences resident on the GPU (BASELINE.json configs[4]; each sequence has its own fitter, warp field and CUDA stream;
+frames inside a sequence are serial and warm-started from the previous frame's node translations, the target advancing frame by frame).
+Further legs of the same run, each reported in its own block of the JSON line:
+  latency      one sequence alone on the GPU, L2 flushed between frames (ms per GN iteration, the <= 1 ms target)
+  population   BASELINE.json configs[4] as stated: a FIXED population of 64 sequences shared by the N GPUs (strong scaling)
+  configs      (N = 1) C1 (configs[0]) and C3 (configs[2]) at their stated sizes: ms per iteration, per-stage ms, status, GB/s
+  pixel_shard  (N > 1) configs[3]: one 3840x2160 frame split into row bands over all N ranks, int64 all-reduce per iteration
 
   python bench.py --gpus N --steps K --warmup W              our sm_100a path (one process per GPU; frames are sharded, no collective)
   python bench.py --impl reference --gpus N --steps K ...    the reference algorithm's CPU path (oracle restatement, OpenMP, all host threads)
@@ -101,9 +105,13 @@ def algorithmic_bytes(V, F, PX, N, E):
     }
 
 
-def make_bench_scene():
+FRAMES_PER_STEP = 10   # consecutive frames per resident sequence in one step: a default run's timed region lasts about a second
+POPULATION = 64        # BASELINE.json configs[4]: 64 independent sequences shared by the GPUs of the box
+
+
+def make_bench_scene(config=WORKLOAD, height=HEIGHT, width=WIDTH):
     from dynamicfuion_python_b200 import synthetic
-    s = synthetic.make_scene(WORKLOAD, HEIGHT, WIDTH)
+    s = synthetic.make_scene(config, height, width)
     s["frame_scales"] = [0.5 + 0.5 * (k + 1) / FRAME_POOL for k in range(FRAME_POOL)]
     return s
 
@@ -111,7 +119,8 @@ def make_bench_scene():
 def scaled_motion(s, scale):
     """Ground-truth node motion scaled towards the identity (axis-angle scaling through Rodrigues on the host)."""
     from dynamicfuion_python_b200 import synthetic
-    R, t = synthetic.smooth_node_motion(s["nodes"], max_angle_deg=3.0 * scale, max_translation=0.005 * scale,
+    big = s["config"] in ("C1", "C1e")
+    R, t = synthetic.smooth_node_motion(s["nodes"], max_angle_deg=3.0 * scale, max_translation=(0.05 if big else 0.005) * scale,
                                         rng=np.random.default_rng(synthetic.SEED + 1))
     return R, t
 
@@ -119,8 +128,191 @@ def scaled_motion(s, scale):
 STAGES = ["warp_vertices", "face_raster", "band_raster", "assemble", "build_system", "stem_eliminate", "corner_solve_update"]
 STAGE_KERNEL = {"warp_vertices": "warp_vertices_kernel<4>", "face_raster": "face_raster_kernel", "band_raster": "band_raster_kernel",
                 "assemble": "assemble_kernel<4>", "build_system": "system_stem_kernel", "stem_eliminate": "(fused into system_stem_kernel)",
-                "corner_solve_update": "corner_solve_regtile_kernel"}
+                "corner_solve_update": "reduced_gather_kernel + corner_solve_regtile_kernel<true>"}
+STAGE_BOUND = {"corner_solve_update": "latency: one CTA, 3 Nc-step Cholesky dependency chain (flops and bytes are far from any roof)",
+               "build_system": "latency: warp per node, 6 x 6 factorisations"}
 SETUP_LAUNCHES = 5  # anchors, 3 pack kernels, reference unprojection
+
+
+class Workload:
+    """One scene on this GPU: mesh tensors, FRAME_POOL target depth frames of increasing ground-truth motion (rendered by the CUDA
+    rasteriser, resident in HBM and in pinned host memory), and a factory of sequences (warp field + fitter + pinned result)."""
+
+    def __init__(self, nnrt, torch, dev, config=WORKLOAD, height=HEIGHT, width=WIDTH, iterations=ITERATIONS_PER_FRAME, scene_edit=None):
+        self.nnrt, self.torch, self.dev, self.iterations = nnrt, torch, dev, iterations
+        s = self.s = make_bench_scene(config, height, width)
+        if scene_edit:
+            scene_edit(s)
+        self.K, self.ext, self.size = s["K"], np.eye(4), (height, width)
+        self.mesh = (torch.tensor(s["positions"], device=dev), torch.tensor(s["normals"], device=dev), torch.tensor(s["triangles"], device=dev))
+        self.dims = (s["positions"].shape[0], s["triangles"].shape[0], height * width, s["nodes"].shape[0], s["edges"].shape[0])
+        self.eye = torch.eye(3, device=dev).repeat(self.dims[3], 1, 1).contiguous()
+        wf = self.field()
+        self.anchors, self.weights = wf.precompute_anchors_and_weights(self.mesh)
+        self.frames_dev = []
+        for scale in s["frame_scales"]:
+            R, t = scaled_motion(s, scale)
+            wf.set_node_rotations(R); wf.set_node_translations(t)
+            warped = wf.warp_mesh(self.mesh, self.anchors, self.weights, True, self.ext)
+            fv, mask = nnrt.rendering.functional.get_mesh_ndc_face_vertices_and_clip_mask(warped, self.K, self.size, 0.0, 10.0)
+            _, depth, _, _ = nnrt.rendering.rasterize_ndc_triangles(fv, mask, self.size, 0.0, 1, -1, -1, True, False, True)
+            self.frames_dev.append(torch.where(depth[..., 0] > 0, depth[..., 0], torch.zeros_like(depth[..., 0])).contiguous())
+        self.frames_host = None
+        self.coverage = float((self.frames_dev[0] > 0).float().mean())
+
+    def pin_frames(self):
+        if self.frames_host is None:
+            self.frames_host = [f.cpu().pin_memory() for f in self.frames_dev]
+        return self.frames_host
+
+    def field(self):
+        G, s = self.nnrt.geometry, self.s
+        return G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"] if len(s["edges"]) else None, s["arrow_base"], s["node_coverage"], False, 4, 0,
+                                                       G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
+
+    def sequence(self, first_frame=0):
+        N, torch, s = self.dims[3], self.torch, self.s
+        return dict(wf=self.field(), frame=first_frame,
+                    fitter=self.nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=self.iterations,
+                                                                           preconditioning_dampening_factor=s["lm_factor"],
+                                                                           arap_term_weight=s["arap_term_weight"]),
+                    host_R=torch.empty((N, 3, 3), dtype=torch.float32).pin_memory(), host_t=torch.empty((N, 3), dtype=torch.float32).pin_memory())
+
+    def fit_next(self, q, frames, read_back, supplied_anchors=False):
+        """The next frame of sequence q through the public API: warm start from the previous frame's node state; the sequence starts
+        over from the identity when its target wraps around the frame pool. Per-fit setup (anchors of the canonical mesh, mesh
+        re-layout, reference unprojection) is part of every call unless `supplied_anchors`."""
+        k = q["frame"] % FRAME_POOL
+        # Warm start: node TRANSLATIONS carry over from the previous frame; node rotations restart from the identity every frame. The
+        # reference's iteration is not contractive in the rotations (its ARAP rotation Jacobian has the sign opposite to the derivative
+        # of its own residual, DESIGN.md §5): carried over for 60+ iterations they grow until the fit leaves the image (measured:
+        # max |t| 0.002 -> 0.65 -> 1.56 m at the 7th and 8th warm-started frame), whereas this form tracks the target (error 0.0005-0.0008).
+        q["wf"].node_rotations.copy_(self.eye)
+        if k == 0:
+            q["wf"].node_translations.zero_()
+        extra = dict(anchors=self.anchors, anchor_weights=self.weights) if supplied_anchors else {}
+        q["fitter"].fit_to_image(q["wf"], self.mesh, None, frames[k], None, self.K, self.ext, 1.0, **extra)
+        q["frame"] += 1
+        if read_back:  # result of the frame back on the host: two asynchronous copies into pinned buffers on the sequence's stream
+            q["host_R"].copy_(q["wf"].node_rotations, non_blocking=True)
+            q["host_t"].copy_(q["wf"].node_translations, non_blocking=True)
+
+    def status(self, q):
+        try:
+            q["fitter"].check_status()
+        except RuntimeError as error:
+            return str(error)
+        return "ok" if bool(self.torch.isfinite(q["wf"].node_translations).all()) else "non-finite node state"
+
+
+def throughput_leg(torch, pool, work, seqs, frames, steps, read_back, barrier, wall_clock):
+    """`steps` steps of FRAMES_PER_STEP frames of every sequence in `seqs`, each sequence on its own stream. Device time by one CUDA
+    event pair on the launching stream (sequence streams forked from / joined into it), or wall clock when the host waits for every
+    frame's result (`read_back`: the stream is synchronised before that sequence's next frame is enqueued)."""
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.perf_counter()
+    start.record()
+    pool.fork()
+    for _ in range(steps * FRAMES_PER_STEP):
+        for k, q in enumerate(seqs):
+            if read_back:
+                pool.synchronize(k)
+            pool.run(k, work.fit_next, q, frames, read_back)
+    pool.join()
+    end.record()
+    if read_back:
+        pool.synchronize()
+    barrier()
+    return (time.perf_counter() - t0) * 1e3 if wall_clock else start.elapsed_time(end)
+
+
+def stage_profile(torch, work, q, flush, reps):
+    """Per-kernel stage times of one iteration: CUDA events between the launches of an iteration issued OUTSIDE the captured graph,
+    serialised, L2 flushed before each iteration (so each value carries a few us of launch latency and cold caches)."""
+    stage_ms, count = np.zeros(7), 0
+    for rep in range(reps):
+        q["wf"].node_rotations.copy_(work.eye); q["wf"].node_translations.zero_()
+        for it in range(work.iterations):
+            flush.fill_(it)
+            torch.cuda.synchronize()
+            stage_ms += np.array(q["fitter"].profile_iteration(q["wf"], work.K, work.ext))
+            count += 1
+    return (stage_ms / count).tolist()
+
+
+def config_block(torch, nnrt, dev, flush, config, height, width, frames, peak):
+    """One BASELINE.json config at its stated size on this GPU alone: ms per GN iteration inside the captured graph (CUDA events
+    around `frames` frames of 10 iterations, one sequence), per-stage ms, fit status, achieved algorithmic GB/s."""
+    work = Workload(nnrt, torch, dev, config, height, width)
+    q = work.sequence()
+    for _ in range(2):
+        work.fit_next(q, work.frames_dev, False, supplied_anchors=True)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(frames):
+        work.fit_next(q, work.frames_dev, False, supplied_anchors=True)
+    b.record()
+    torch.cuda.synchronize()
+    status = work.status(q)
+    ms_iter = a.elapsed_time(b) / frames / work.iterations
+    stages = dict(zip(STAGES, stage_profile(torch, work, q, flush, 1)))
+    V, F, PX, N, E = work.dims
+    total = algorithmic_bytes(V, F, PX, N, E)["total"]
+    gbs = total / (ms_iter * 1e-3) / 1e9
+    out = {"workload": f"{config}: V={V} F={F} nodes={N} (stem {work.s['arrow_base']} + corner {N - work.s['arrow_base']}) edges={E} {width}x{height}, "
+                       f"{work.iterations} GN iterations/frame, one sequence, anchors supplied",
+           "status": status, "ms_per_iteration": ms_iter, "stage_ms": stages, "coverage": work.coverage,
+           "iteration_algorithmic_bytes": total, "iteration_achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
+    del q, work
+    torch.cuda.empty_cache()
+    return out
+
+
+def pixel_shard_leg(torch, dist, nnrt, dev, rank, world, frames):
+    """BASELINE.json configs[3]: the C2 mesh and graph fitted to ONE 3840x2160 frame, rows split into one band per rank, the per-node
+    sums all-reduced as int64 once per iteration. Timed with CUDA events (max over ranks) next to the same fit unsharded on one GPU."""
+    from dynamicfuion_python_b200 import frame_batch
+    height, width = 2160, 3840
+    ratio = height * width / float(HEIGHT * WIDTH)
+
+    def edit(s):  # the data term grows with the pixel count: keep its balance with the ARAP term of the 640x480 scene
+        s["arap_term_weight"] *= ratio ** 0.5
+    work = Workload(nnrt, torch, dev, WORKLOAD, height, width, scene_edit=edit)
+    results, states = {}, {}
+    for label, shard in (("one_gpu", False), ("sharded", True)):
+        q = work.sequence()
+        if shard:
+            q["fitter"].shard_pixels(rank, world)
+
+        def frame():
+            q["frame"] = FRAME_POOL - 1  # always the same (last) target frame, from the identity: the two runs do identical work
+            q["wf"].node_rotations.copy_(work.eye); q["wf"].node_translations.zero_()
+            work.fit_next(q, work.frames_dev, False, supplied_anchors=True)
+        for _ in range(2):
+            frame()
+        torch.cuda.synchronize(); dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(frames):
+            frame()
+        b.record()
+        torch.cuda.synchronize(); dist.barrier()
+        ms = frame_batch.max_over_ranks([a.elapsed_time(b) / frames / work.iterations], dev)[0]
+        results[label] = ms
+        states[label] = (q["wf"].node_rotations.clone(), q["wf"].node_translations.clone(), work.status(q))
+    (R1, t1, s1), (R2, t2, s2) = states["one_gpu"], states["sharded"]
+    gathered = [torch.zeros_like(t2) for _ in range(world)]
+    dist.all_gather(gathered, t2)
+    return {"image": f"{width}x{height}", "workload": "C2r mesh and graph (configs[3]), 10 GN iterations from the identity state, anchors supplied",
+            "nranks": world, "ms_per_iteration": results["sharded"], "ms_per_iteration_1gpu": results["one_gpu"],
+            "speedup": results["one_gpu"] / results["sharded"], "status": [s1, s2],
+            "parity_vs_1gpu": {"bit_identical": bool(torch.equal(R1, R2) and torch.equal(t1, t2)),
+                               "max_abs_translation_difference": float((t1 - t2).abs().max()),
+                               "identical_on_all_ranks": bool(all(torch.equal(g, gathered[0]) for g in gathered))},
+            "collective": "int64 all-reduce (NCCL) of node_count x 32 x 2 fixed-point words per iteration; replicated deterministic solve, no broadcast",
+            "coverage": work.coverage}
 
 
 def run_b200(args):
@@ -133,60 +325,16 @@ def run_b200(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    from dynamicfuion_python_b200 import nnrt
+    from dynamicfuion_python_b200 import frame_batch, nnrt
     dev = torch.device("cuda", local)
-    s = make_bench_scene()
-    G = nnrt.geometry
-    K, ext = s["K"], np.eye(4)
-    mesh = (torch.tensor(s["positions"], device=dev), torch.tensor(s["normals"], device=dev), torch.tensor(s["triangles"], device=dev))
-    V, F, N, E, PX = s["positions"].shape[0], s["triangles"].shape[0], s["nodes"].shape[0], s["edges"].shape[0], HEIGHT * WIDTH
-
-    def new_field():
-        return G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
-                                            G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
-
-    # target depth frames rendered by the CUDA rasteriser from scaled ground-truth motion (synthetic data, seeded)
-    wf = new_field()
-    anchors, weights = wf.precompute_anchors_and_weights(mesh)
-    frames_dev = []
-    for scale in s["frame_scales"]:
-        R, t = scaled_motion(s, scale)
-        wf.set_node_rotations(R); wf.set_node_translations(t)
-        warped = wf.warp_mesh(mesh, anchors, weights, True, ext)
-        fv, mask = nnrt.rendering.functional.get_mesh_ndc_face_vertices_and_clip_mask(warped, K, (HEIGHT, WIDTH), 0.0, 10.0)
-        _, depth, _, _ = nnrt.rendering.rasterize_ndc_triangles(fv, mask, (HEIGHT, WIDTH), 0.0, 1, -1, -1, True, False, True)
-        frames_dev.append(torch.where(depth[..., 0] > 0, depth[..., 0], torch.zeros_like(depth[..., 0])).contiguous())
-    frames_host = [f.cpu().pin_memory() for f in frames_dev]
-    coverage = float((frames_dev[0] > 0).float().mean())
-
-    from dynamicfuion_python_b200 import frame_batch
-    S = args.sequences
-    eye = torch.eye(3, device=dev).repeat(N, 1, 1).contiguous()
+    work = Workload(nnrt, torch, dev)
+    frames_host = work.pin_frames()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    # one warp field + fitter + stream + pinned result buffers per resident sequence (BASELINE.json configs[4]: independent sequences)
-    seqs = [dict(wf=new_field(),
-                 fitter=nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=ITERATIONS_PER_FRAME,
-                                                                   preconditioning_dampening_factor=s["lm_factor"],
-                                                                   arap_term_weight=s["arap_term_weight"]),
-                 host_R=torch.empty((N, 3, 3), dtype=torch.float32).pin_memory(),
-                 host_t=torch.empty((N, 3), dtype=torch.float32).pin_memory()) for _ in range(S)]
-    pool = frame_batch.SequenceStreams(S, dev)
-    wf, fitter = seqs[0]["wf"], seqs[0]["fitter"]
-
-    def fit(q, depth, read_back):
-        q["wf"].node_rotations.copy_(eye); q["wf"].node_translations.zero_()
-        q["fitter"].fit_to_image(q["wf"], mesh, None, depth, None, K, ext, 1.0)
-        if read_back:  # result of the frame back on the host: two asynchronous copies into pinned buffers on the sequence's stream
-            q["host_R"].copy_(q["wf"].node_rotations, non_blocking=True)
-            q["host_t"].copy_(q["wf"].node_translations, non_blocking=True)
-
-    def step(frames, index, read_back):
-        """One frame of every resident sequence, each on its own stream. With read_back the host holds a sequence's previous result
-        (stream synchronised) before that sequence's next frame is enqueued."""
-        for k, q in enumerate(seqs):
-            if read_back:
-                pool.synchronize(k)
-            pool.run(k, fit, q, frames[(first + index + k) % FRAME_POOL], read_back)
+    S = args.sequences
+    resident = max(S, POPULATION // world)
+    # one warp field + fitter + stream + pinned result buffers per resident sequence; sequences start at different frames of the pool
+    seqs = [work.sequence(first_frame=(rank + k) % FRAME_POOL) for k in range(resident)]
+    pool = frame_batch.SequenceStreams(resident, dev)
 
     def barrier():
         torch.cuda.synchronize()
@@ -194,76 +342,69 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    first = rank % FRAME_POOL
-    for i in range(args.warmup):
-        step(frames_dev, i, False)
+    weak = seqs[:S]
+    for _ in range(args.warmup):
+        for k, q in enumerate(weak):
+            pool.run(k, work.fit_next, q, work.frames_dev, False)
     torch.cuda.synchronize()
-    for q in seqs:
-        q["fitter"].check_status()
+    status = sorted({work.status(q) for q in weak})
 
-    # ---- value: inputs resident in HBM, one CUDA event pair on the launching stream around the K steps (sequence streams forked from /
-    # joined into it); the resident sequences' working sets (S x workspace) exceed L2, so a sequence finds its data evicted each frame
+    # ---- value: inputs resident in HBM; the resident sequences' working sets (S x workspace) exceed L2, so a sequence finds its data
+    # evicted at its next frame
     sampler = ClockSampler(local)
-    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
     if rank == 0:
         sampler.start()
-    start.record()
-    pool.fork()
-    for i in range(args.steps):
-        step(frames_dev, i, False)
-    pool.join()
-    end.record()
-    barrier()
-    dev_ms = start.elapsed_time(end)
-    for q in seqs:
-        q["fitter"].check_status()
-        if not bool(torch.isfinite(q["wf"].node_translations).all()):
-            raise RuntimeError("bench: fit diverged (non-finite node translations)")
-
-    # ---- e2e: public API call with the depth frame in pinned host memory + D2H of the node state, wall clock around K steps
-    for i in range(min(args.warmup, 3)):
-        step(frames_host, i, True)
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        step(frames_host, i, True)
-    pool.synchronize()
-    barrier()
-    e2e_ms = (time.perf_counter() - t0) * 1e3
+    dev_ms = throughput_leg(torch, pool, work, weak, work.frames_dev, args.steps, False, barrier, False)
+    status = sorted(set(status) | {work.status(q) for q in weak})
+    # ---- e2e: the public API call with the depth frame in pinned host memory + D2H of the node state awaited before that sequence's
+    # next frame; wall clock
+    for _ in range(min(args.warmup, 3)):
+        for k, q in enumerate(weak):
+            pool.run(k, work.fit_next, q, frames_host, True)
+    e2e_ms = throughput_leg(torch, pool, work, weak, frames_host, args.steps, True, barrier, True)
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---- population: BASELINE.json configs[4] as stated -- 64 sequences in total, 64 / N resident per GPU (strong scaling)
+    pop = seqs[:POPULATION // world]
+    pop_steps = max(1, args.steps // 4)
+    for k, q in enumerate(pop):
+        pool.run(k, work.fit_next, q, work.frames_dev, False)
+    pop_ms = throughput_leg(torch, pool, work, pop, work.frames_dev, pop_steps, False, barrier, False)
+
     # ---- latency: ONE sequence alone on the GPU, L2 flushed between frames, CUDA events per frame (the <= 1 ms / iteration target)
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    lat_frames = 2 * FRAME_POOL
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(lat_frames)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(lat_frames)]
     barrier()
     with torch.cuda.stream(pool.streams[0]):  # the stream this sequence's graph was captured for
-        for i in range(args.steps):
+        for i in range(lat_frames):
             flush.fill_(i & 0xFF)
             starts[i].record()
-            fit(seqs[0], frames_dev[(first + i) % FRAME_POOL], False)
+            work.fit_next(seqs[0], work.frames_dev, False)
             ends[i].record()
     barrier()
-    latency_ms = sum(a.elapsed_time(b) for a, b in zip(starts, ends)) / args.steps
+    latency_ms = sum(a.elapsed_time(b) for a, b in zip(starts, ends)) / lat_frames
+    dev_ms, e2e_ms, pop_ms, latency_ms = frame_batch.max_over_ranks([dev_ms, e2e_ms, pop_ms, latency_ms], dev)  # no data-path collective: only the clock is reduced
 
-    dev_ms, e2e_ms, latency_ms = frame_batch.max_over_ranks([dev_ms, e2e_ms, latency_ms], dev)  # frames are sharded, no data-path collective: only the clock is reduced
-
-    # ---- per-kernel stage times (CUDA events between the 7 launches of an iteration, outside the graph) for the roofline
-    stage_ms = np.zeros(7)
-    profiled = 0
-    if rank == 0:
-        for rep in range(4):
-            wf.node_rotations.copy_(eye); wf.node_translations.zero_()
-            for it in range(ITERATIONS_PER_FRAME):
-                flush.fill_(it)
-                torch.cuda.synchronize()
-                stage_ms += np.array(fitter.profile_iteration(wf, K, ext))
-                profiled += 1
-        stage_ms /= profiled
     out = None
     if rank == 0:
-        out = dict(dev_ms=dev_ms, e2e_ms=e2e_ms, latency_ms=latency_ms, sequences=S, stage_ms=stage_ms.tolist(), clocks=clocks, coverage=coverage, dims=(V, F, PX, N, E),
-                   world=world, launches=int(fitter.launches_per_iteration()), workspace=int(fitter.workspace_bytes()) * S)
+        peak, _ = load_peaks()
+        out = dict(dev_ms=dev_ms, e2e_ms=e2e_ms, latency_ms=latency_ms, sequences=S, stage_ms=stage_profile(torch, work, seqs[0], flush, 4), clocks=clocks,
+                   coverage=work.coverage, dims=work.dims, world=world, launches=int(seqs[0]["fitter"].launches_per_iteration()),
+                   workspace=int(seqs[0]["fitter"].workspace_bytes()) * S, status=status,
+                   population=dict(sequences=POPULATION, resident_per_gpu=len(pop), steps=pop_steps, ms_per_step=pop_ms / pop_steps,
+                                   frames_per_s=pop_steps * FRAMES_PER_STEP * POPULATION / (pop_ms * 1e-3)))
+    del seqs, weak, pop, pool
+    torch.cuda.empty_cache()
+    if world > 1:
+        shard = pixel_shard_leg(torch, dist, nnrt, dev, rank, world, 5)
+        if rank == 0:
+            out["pixel_shard"] = shard
+    elif not args.no_configs:
+        peak, _ = load_peaks()
+        out["configs"] = {"C1": config_block(torch, nnrt, dev, flush, "C1", HEIGHT, WIDTH, 20, peak),
+                          "C1e": config_block(torch, nnrt, dev, flush, "C1e", HEIGHT, WIDTH, 20, peak),
+                          "C3": config_block(torch, nnrt, dev, flush, "C3", 1080, 1920, 3, peak)}
     if world > 1:
         dist.destroy_process_group()
     return out
@@ -329,7 +470,10 @@ def cpu_baseline_sample(s, iterations):
 
 
 def run_reference(args):
-    """--impl reference: the reference algorithm's CPU path (oracle port; the reference itself needs Open3D 0.17 and cannot be built here)."""
+    """--impl reference: the reference algorithm's CPU path, timed on this box's host cores. The reference itself needs Open3D 0.17 and
+    cannot be built here, so this is the flat-array C++ restatement in oracle/ (cpu_baseline.kind = "port"), OpenMP over all host
+    threads. ONE host, whatever --gpus says: under torchrun rank 0 alone runs it. A step is ONE frame (per-fit setup + as many of the
+    10 GN iterations as fit the time budget, the rest extrapolated in `value` only); `ms_per_step` is the measured time of a step."""
     rank = _env_int("RANK", 0)
     if rank != 0:
         return None
@@ -344,17 +488,20 @@ def run_reference(args):
     for _ in range(args.warmup):
         oracle_frame(oracle, s, depth, iters)
     total_setup = total_iter = 0.0
+    t0 = time.perf_counter()
     for _ in range(args.steps):
         a, b = oracle_frame(oracle, s, depth, iters)
         total_setup += a; total_iter += b
+    measured_ms_per_step = (time.perf_counter() - t0) * 1e3 / args.steps
     per_iter = total_iter / (args.steps * iters)
     frame_s = total_setup / args.steps + per_iter * ITERATIONS_PER_FRAME
     value = 1.0 / frame_s
-    sample = (f"each step = per-fit setup + {iters} of {ITERATIONS_PER_FRAME} GN iterations of {WORKLOAD} @640x480, extrapolated to a full frame; "
-              f"{threads} threads on '{cpu_model()}'")
+    sample = (f"each step = ONE frame: per-fit setup + {iters} of {ITERATIONS_PER_FRAME} GN iterations of {WORKLOAD} @640x480 measured "
+              f"(value extrapolates the remaining iterations at the measured per-iteration time); {threads} threads on ONE host ('{cpu_model()}'), "
+              "independent of --gpus")
     return {"impl": "reference", "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": frame_s * 1e3 * args.sequences * args.gpus, "frames_per_step": args.sequences * args.gpus, "ms_per_frame": frame_s * 1e3,
-            "ms_per_iteration": per_iter * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": measured_ms_per_step, "frames_per_step": 1, "iterations_measured_per_step": iters, "ms_per_frame": frame_s * 1e3,
+            "ms_per_iteration": per_iter * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "single_host": True,
             "dtype": "f32", "data": "synthetic", "config": bench_config(args.gpus, args.sequences),
             "cpu_baseline": {"value": value, "unit": "frames/s", "cores": host_cores(), "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
@@ -365,13 +512,14 @@ METRIC = "frames/s box-wide (frame = per-fit setup + 10 dense-depth GN iteration
 
 def bench_config(gpus, sequences):
     return {"workload": f"{WORKLOAD}: relief mesh V=41209 F=81608, 249 nodes (208 stem + 41 corner, 1494x1494 arrowhead system), 832 edges, "
-                        f"{WIDTH}x{HEIGHT} depth, {ITERATIONS_PER_FRAME} GN iterations/frame (BASELINE.json configs[1]); a step = one frame of each "
-                        f"of {sequences} independent sequences per GPU (configs[4])",
+                        f"{WIDTH}x{HEIGHT} depth, {ITERATIONS_PER_FRAME} GN iterations/frame (BASELINE.json configs[1]); a step = {FRAMES_PER_STEP} "
+                        f"consecutive warm-started frames of each of {sequences} independent sequences per GPU (configs[4])",
             "parallelism": f"frame-batch: {gpus} GPU(s) x {sequences} resident sequences, one fitter + CUDA stream per sequence, no collective",
-            "sequences_per_gpu": sequences,
+            "sequences_per_gpu": sequences, "frames_per_sequence_per_step": FRAMES_PER_STEP,
             "l2": f"throughput legs: the {sequences} resident sequences' working sets ({sequences} x 23 MB) exceed the 126 MB L2, every sequence "
                   "finds its data evicted at its next frame; latency leg: 256 MiB device fill between frames (outside the per-frame CUDA events)",
-            "frames": f"{FRAME_POOL} distinct synthetic target depth frames cycled"}
+            "frames": f"{FRAME_POOL} synthetic target depth frames of increasing motion per sequence; node translations warm-start frame to frame (rotations "
+                      "restart from the identity: the reference iteration is not contractive in them), restart at the wrap"}
 
 
 def load_peaks():
@@ -389,8 +537,9 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--sequences", type=int, default=16, help="independent sequences resident per GPU, each on its own stream")
+    ap.add_argument("--sequences", type=int, default=16, help="independent sequences resident per GPU in the weak-scaling legs, each on its own stream")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the bounded CPU sample (profiling runs)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 config blocks (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 0)
     if args.impl == "reference":
@@ -402,16 +551,16 @@ def main():
     if r is None:
         return
     V, F, PX, N, E = r["dims"]
-    world = r["world"]
-    S = r["sequences"]
-    frames = args.steps * world * S
+    world, S = r["world"], r["sequences"]
+    frames = args.steps * FRAMES_PER_STEP * world * S
     value = frames / (r["dev_ms"] * 1e-3)
     e2e_value = frames / (r["e2e_ms"] * 1e-3)
     ms_per_step = r["dev_ms"] / args.steps
     stage_ms = dict(zip(STAGES, r["stage_ms"]))
     bytes_by = algorithmic_bytes(V, F, PX, N, E)
+    nc = N - 208
     stage_bytes = {"warp_vertices": bytes_by["warp"], "face_raster": bytes_by["raster"], "band_raster": 0, "assemble": bytes_by["assemble"],
-                   "build_system": 168 * N + 144 * E, "stem_eliminate": 156 * E + 168 * N, "corner_solve_update": 4 * (6 * (N - 208)) ** 2 + 72 * N}
+                   "build_system": 168 * N + 300 * E, "stem_eliminate": 0, "corner_solve_update": 4 * (3 * nc) ** 2 + 48 * E * 10 // 4 + 72 * N}
     dominant = max(STAGES, key=lambda k: stage_ms[k])
     peak, peak_kind = load_peaks()
     achieved = stage_bytes[dominant] / (stage_ms[dominant] * 1e-3) / 1e9 if stage_ms[dominant] > 0 else 0.0
@@ -419,25 +568,37 @@ def main():
     traffic = None
     try:  # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (profiles/ncu_traffic.json)
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
-            traffic = json.load(fh).get(STAGE_KERNEL[dominant].split("(")[0], {}).get("dram_bytes_per_launch")
+            traffic = json.load(fh).get(STAGE_KERNEL[dominant].split("(")[0].split(" ")[0], {}).get("dram_bytes_per_launch")
     except (OSError, ValueError):
         pass
+    iter_ms_throughput = ms_per_step / (FRAMES_PER_STEP * ITERATIONS_PER_FRAME * S)
     roofline = {"bound": "hbm", "kernel": STAGE_KERNEL[dominant], "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": stage_bytes[dominant],
-                "avg_launch_ms": stage_ms[dominant], "share_of_iteration": stage_ms[dominant] / iter_ms_profiled if iter_ms_profiled else None,
+                "limiter": STAGE_BOUND.get(dominant, "latency of each warp's dependent chain at this size (one wave of work); HBM is the roof it is measured against"),
+                "avg_launch_ms": stage_ms[dominant], "avg_launch_ms_source": "separate serialised leg after the timed region: un-captured launches, CUDA events "
+                "between them, L2 flushed before every iteration (each value carries a few us of launch latency); NOT the timed region, where "
+                "16 sequences overlap", "share_of_iteration": stage_ms[dominant] / iter_ms_profiled if iter_ms_profiled else None,
                 "stage_ms": stage_ms, "iteration_algorithmic_bytes": bytes_by["total"],
-                "iteration_achieved_gbs": bytes_by["total"] / (iter_ms_profiled * 1e-3) / 1e9 if iter_ms_profiled else None}
+                "iteration_achieved_gbs": bytes_by["total"] / (iter_ms_profiled * 1e-3) / 1e9 if iter_ms_profiled else None,
+                "iteration_throughput": {"ms_per_iteration_with_resident_sequences": iter_ms_throughput,
+                                         "achieved_gbs": bytes_by["total"] / (iter_ms_throughput * 1e-3) / 1e9,
+                                         "frac": bytes_by["total"] / (iter_ms_throughput * 1e-3) / 1e9 / peak}}
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "frames_per_step": S * world, "ms_per_iteration": r["latency_ms"] / ITERATIONS_PER_FRAME,
+            "ms_per_step": ms_per_step, "frames_per_step": FRAMES_PER_STEP * S * world, "ms_per_iteration": r["latency_ms"] / ITERATIONS_PER_FRAME,
             "latency": {"ms_per_frame": r["latency_ms"], "ms_per_iteration": r["latency_ms"] / ITERATIONS_PER_FRAME,
                         "frames_per_s_one_sequence": 1e3 / r["latency_ms"],
                         "note": "one sequence alone on the GPU, L2 flushed between frames, CUDA events per frame (per-fit setup included)"},
-            "higher_is_better": True, "scaling": "weak",
+            "higher_is_better": True, "scaling": "weak", "status": r["status"],
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": bench_config(world, S),
-            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": PX * 4 * S, "d2h_bytes_per_step": N * 12 * 4 * S,
-                    "ms_per_step": r["e2e_ms"] / args.steps, "timing": "wall clock around K steps of fit_to_image calls (one per resident sequence), synchronize + barrier on both sides, max over ranks"},
-            "gpu_launches": args.steps * S * (SETUP_LAUNCHES + ITERATIONS_PER_FRAME * r["launches"]),
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": PX * 4 * S * FRAMES_PER_STEP, "d2h_bytes_per_step": N * 12 * 4 * S * FRAMES_PER_STEP,
+                    "ms_per_step": r["e2e_ms"] / args.steps, "timing": "wall clock around K steps of fit_to_image calls (one per frame of every resident "
+                    "sequence), synchronize + barrier on both sides, max over ranks"},
+            "gpu_launches": args.steps * FRAMES_PER_STEP * S * (SETUP_LAUNCHES + ITERATIONS_PER_FRAME * r["launches"]),
+            "population": dict(r["population"], scaling="strong", note="BASELINE.json configs[4]: 64 sequences in total, 64 / n_gpus resident per GPU"),
             "clocks": r["clocks"], "roofline": roofline, "coverage": r["coverage"], "workspace_bytes": r["workspace"]}
+    for key in ("configs", "pixel_shard"):
+        if key in r:
+            line[key] = r[key]
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_sample(make_bench_scene(), 3)
     print(json.dumps(line), flush=True)

@@ -537,7 +537,7 @@ extern "C" void nnrt_b200_fitter_destroy(nnrt_b200_fitter* f) {
 }
 
 extern "C" int64_t nnrt_b200_fitter_workspace_bytes(const nnrt_b200_fitter* f) { return f ? (int64_t) f->arena_bytes : 0; }
-extern "C" int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter* f) { return (f && !f->fused_stem) ? 7 : 6; }
+extern "C" int32_t nnrt_b200_fitter_launches_per_iteration(const nnrt_b200_fitter* f) { return 7; (void) f; }
 
 extern "C" int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* f, const float* nodes, const int32_t* edges, int32_t arrow_base,
                                           const int8_t* edge_layer_indices, const float* layer_decimation_radii, int32_t layer_count,

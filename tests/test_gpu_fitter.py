@@ -130,10 +130,12 @@ def test_single_iteration_parity(nnrt, oracle, config, h, w):
     np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
 
 
-def test_ten_consecutive_iterations_parity(nnrt, oracle):
+@pytest.mark.parametrize("config,h,w", [("tinyr", 120, 160), ("C1", 480, 640), ("C1e", 480, 640), ("C2r", 480, 640)])
+def test_ten_consecutive_iterations_parity(nnrt, oracle, config, h, w):
     """Ten consecutive GN iterations, each checked against the oracle started from the SAME state (the GPU's state before that
-    iteration): deltas within 1e-3 relative (BASELINE.json), face indices within the reference's own 20-pixel tolerance."""
-    s = scene_with_target(oracle, "tinyr", 120, 160)
+    iteration): face indices and coverage BIT-EXACT (identical inputs), deltas within 1e-3 relative (BASELINE.json). C1 / C1e
+    (BASELINE.json configs[0], "10 GN iterations") and C2r (configs[1]) run at their stated 640 x 480."""
+    s = scene_with_target(oracle, config, h, w)
     G = nnrt.geometry
     wf = G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
                                       G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
@@ -147,19 +149,33 @@ def test_ten_consecutive_iterations_parity(nnrt, oracle):
         ref = oracle_fit(oracle, s, 1, rotations=R0, translations=t0)
         d = fitter.diagnostics()
         mismatch = int((_np(d["pixel_face_indices"]) != ref["pixel_faces"]).sum())
-        assert mismatch <= 20, (it, mismatch)  # cpp/tests/test_rasterize.cpp:281,300
-        if mismatch == 0:
-            # entries below 0.1 % of the largest are sums with heavy cancellation: both fp32 summation orders (oracle: sequential
-            # over the node's pixel list; GPU: warp tree + atomics) carry more than 1e-4 of such an entry
-            ok, worst = rel_close(_np(d["hessian_diagonal"]), ref["hessian_diag"][0], 1e-4, floor_scale=1e-3)
-            assert ok, f"iteration {it}: J^T J {worst}"
-        ok, worst = rel_close(_np(d["deltas"]), ref["deltas"][0], 1e-3, floor_scale=1e-2)
+        assert mismatch == 0, (it, mismatch)
+        assert np.array_equal(_np(d["residual_mask"]), ref["residual_mask"])
+        # The GPU's per-node sums are exact sums of per-warp totals (fixed point); the ORACLE adds a node's pixel list sequentially in
+        # fp32, whose rounding grows with the list length (C1 at 640 x 480: ~56 000 addends per node, against ~1 700 at C2r): beyond
+        # 5 000 addends per node the 1e-4 / 1e-3 bars are widened by sqrt(addends / 5000).
+        addends = 4.0 * float(ref["residual_mask"].sum()) / len(s["nodes"])
+        widen = max(1.0, addends / 5000.0) ** 0.5
+        ok, worst = rel_close(_np(d["hessian_diagonal"]), ref["hessian_diag"][0], 1e-4 * widen, floor_scale=1e-3)
+        assert ok, f"iteration {it}: J^T J {worst}"
+        if len(s["edges"]) == 0 and widen > 1.0:
+            # C1: a plane leaves each node's in-plane translation and its rotation about the normal to the damping alone (lambda = 1
+            # against data entries of 1e3..1e4), so a block's solution amplifies the 3e-4 the oracle's own sums carry by its condition
+            # number. The update is therefore checked where that cancels: as the solution of the ORACLE's system, block by block
+            # (|H d - g| <= 1e-3 (|H| |d| + |g|)), and norm-wise against the oracle's update.
+            H, g, dg = ref["hessian_diag"][0].astype(np.float64), ref["negative_gradient"][0].astype(np.float64), _np(d["deltas"]).astype(np.float64)
+            resid = np.abs(np.einsum("nij,nj->ni", H, dg) - g)
+            bound = 1e-3 * widen * (np.einsum("nij,nj->ni", np.abs(H), np.abs(dg)) + np.abs(g))
+            assert np.all(resid <= bound), f"iteration {it}: backward error {float((resid / bound).max())}"
+            assert np.abs(dg - ref["deltas"][0]).max() <= 1e-2 * np.abs(ref["deltas"][0]).max()
+            continue
+        ok, worst = rel_close(_np(d["deltas"]), ref["deltas"][0], 1e-3 * widen, floor_scale=1e-2)
         assert ok, f"iteration {it}: deltas {worst}"
-        np.testing.assert_allclose(_np(wf.node_translations), ref["translations"], rtol=1e-3, atol=1e-6)
-        np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
+        np.testing.assert_allclose(_np(wf.node_translations), ref["translations"], rtol=1e-3 * widen, atol=1e-6 * widen)
+        np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3 * widen, atol=1e-6 * widen)
 
 
-@pytest.mark.parametrize("config,h,w,converges", [("tinyr", 120, 160, False), ("C2r", 240, 320, True)])
+@pytest.mark.parametrize("config,h,w,converges", [("tinyr", 120, 160, False), ("C2r", 240, 320, True), ("C1", 480, 640, True), ("C1e", 480, 640, True)])
 def test_ten_iterations_free_running(nnrt, oracle, config, h, w, converges):
     """Ten free-running iterations in one graph launch stay close to the oracle's free-running state (two fp32 implementations of
     the iteration drift apart slowly; per-iteration parity is tested above). On the bench scene (C2r) the reference's iteration is
@@ -171,6 +187,7 @@ def test_ten_iterations_free_running(nnrt, oracle, config, h, w, converges):
     assert np.abs(_np(wf.node_translations) - ref["translations"]).max() <= 5e-2 * scale
     assert np.abs(_np(wf.node_rotations) - ref["rotations"]).max() <= 1e-2
     if converges:
+        fitter.check_status()
         err = np.abs(_np(wf.node_translations) - s["translations_gt"]).max()
         assert err < 0.5 * np.abs(s["translations_gt"]).max()
 

@@ -1,5 +1,5 @@
 #!/bin/bash
-python bench.py --steps 10 --warmup 3 --no-cpu-baseline 2>gpurun_out/bench_only.err | python -c "
+python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-configs 2>gpurun_out/bench_only.err | python -c "
 import json,sys
 t=sys.stdin.read()
 try:

@@ -3,7 +3,7 @@
 # usage: tools/gpu_check.sh <tag> [pytest args...]
 tag=${1:-check}; shift
 python -m pytest tests -m gpu -x -q "$@" 2>&1 | tail -15
-python bench.py --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/${tag}.json 2> gpurun_out/${tag}.err || tail -c 1500 gpurun_out/${tag}.err
+python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-configs > gpurun_out/${tag}.json 2> gpurun_out/${tag}.err || tail -c 1500 gpurun_out/${tag}.err
 python - <<PY
 import json
 try:
