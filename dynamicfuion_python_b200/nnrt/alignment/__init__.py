@@ -35,6 +35,7 @@ class DeformableMeshToImageFitter:
                                           int(bool(use_huber_penalty_for_arap_term)), float(huber_penalty_constant))
         self._handle = None
         self._pixel_shard = None
+        self._shard_graphs, self._shard_seen, self._shard_keep = {}, None, None
         self._shape = None
         self._model_key = None
         self._keep = None
@@ -123,17 +124,38 @@ class DeformableMeshToImageFitter:
         if self._pixel_shard is None:
             T.call("nnrt_b200_fitter_fit", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), iters, T.stream())
         else:
-            # pixel-sharded: this rank's band of rows, one all-reduce of the per-node sums per iteration, replicated solve
+            # pixel-sharded: this rank's band of rows, one int64 all-reduce of the per-node sums per iteration, replicated solve.
+            # The loop (2 launches groups + 1 NCCL collective per iteration) is recorded ONCE into a CUDA graph per (node state, camera,
+            # iteration count, band) and replayed; the first call of a key runs eagerly (it also brings up the NCCL communicator, which
+            # cannot happen under capture).
             rank, world, group = self._pixel_shard
             begin, end = pixel_shard.pixel_rows(rank, world, self._shape[5])
             T.call("nnrt_b200_fitter_set_pixel_rows", self._handle, begin, end)
             count = C.c_int64()
             pointer = _lib.lib().nnrt_b200_fitter_accumulators(self._handle, C.byref(count))
             acc = pixel_shard.DeviceBuffer(pointer, count.value).tensor(R.device)
-            for it in range(iters):
-                T.call("nnrt_b200_fitter_iteration_data_term", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), T.stream())
-                pixel_shard.all_reduce_sum(acc, group)
-                T.call("nnrt_b200_fitter_iteration_solve", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), it, T.stream())
+
+            def loop():
+                for it in range(iters):
+                    T.call("nnrt_b200_fitter_iteration_data_term", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), T.stream())
+                    pixel_shard.all_reduce_sum(acc, group)
+                    T.call("nnrt_b200_fitter_iteration_solve", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), it, T.stream())
+            key = (R.data_ptr(), t.data_ptr(), K.numpy().tobytes(), ext.numpy().tobytes(), iters, begin, end, world, id(group), self._handle.value)
+            graph = self._shard_graphs.get(key)
+            if graph is None:
+                if self._shard_seen == key and pixel_shard.GRAPH_CAPTURE:
+                    graph = torch.cuda.CUDAGraph()
+                    Kc, extc = K, ext  # the captured launches read the host matrices at capture time only (by value)
+                    with torch.cuda.graph(graph):
+                        loop()
+                    self._shard_graphs = {key: graph}  # one graph kept: a new key (new warp field, camera ...) replaces it
+                    self._shard_keep = (Kc, extc, acc)
+                    graph.replay()
+                else:
+                    self._shard_seen = key
+                    loop()
+            else:
+                graph.replay()
         self._keep = (K, ext)
 
     def check_status(self):

@@ -9,8 +9,13 @@ the same 32 pixels as in the unsharded fit), and the replicated solves -- which 
 all ranks with no broadcast. At 640x480 one band is a few microseconds of work against an all-reduce of tens of microseconds: the
 mode is built for 4K frames and reported as measured.
 """
+import os
+
 import torch
 import torch.distributed as dist
+
+# the sharded Gauss-Newton loop is replayed from a CUDA graph (NCCL collective inside) from the second fit of a key on; NNRT_B200_SHARD_GRAPH=0 keeps it eager
+GRAPH_CAPTURE = os.environ.get("NNRT_B200_SHARD_GRAPH", "1") != "0"
 
 
 def pixel_rows(rank, world_size, height, align=8):

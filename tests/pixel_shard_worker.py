@@ -31,7 +31,18 @@ def main():
         fitter.fit_to_image(wf, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]),
                             anchors=s["anchors"], anchor_weights=s["anchor_weights"])
         fitter.check_status()
-        return wf.node_rotations.clone(), wf.node_translations.clone()
+        first = (wf.node_rotations.clone(), wf.node_translations.clone())
+        if shard:
+            # the second fit of the same key records the loop (NCCL all-reduce included) into a CUDA graph and replays it, the third replays
+            for _ in range(2):
+                wf.node_rotations.copy_(torch.eye(3, device=wf.node_rotations.device).expand_as(wf.node_rotations))
+                wf.node_translations.zero_()
+                fitter.fit_to_image(wf, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]),
+                                    anchors=s["anchors"], anchor_weights=s["anchor_weights"])
+                fitter.check_status()
+                assert torch.equal(wf.node_rotations, first[0]) and torch.equal(wf.node_translations, first[1]), "graph replay differs from the eager loop"
+            assert len(fitter._shard_graphs) == 1, "the sharded loop was not captured"
+        return first
 
     R1, t1 = fit(False)
     R2, t2 = fit(True)
