@@ -146,6 +146,42 @@ __global__ void __launch_bounds__(128) build_system_kernel(GraphDeviceData g, co
 	for (int c = 0; c < 6; c++) rhs[n * 6 + c] = b[c];
 }
 
+// Edges between two coarser-layer nodes (hierarchies of more than two layers; general path only): the edge's ARAP blocks are added
+// to both endpoints' diagonal blocks and right-hand sides (already formed by build_system_kernel) and dE_i^T dE_j becomes a
+// corner_upper block. The reference writes these out of bounds (ArapHessianImpl.h:144-150); this is the intended arithmetic.
+__global__ void __launch_bounds__(64) corner_edges_kernel(GraphDeviceData g, const int* __restrict__ edge_ids, int count, const float* __restrict__ rotations,
+                                                           const float* __restrict__ translations, float* __restrict__ diag, float* __restrict__ rhs,
+                                                           float* __restrict__ upper_blocks, int* __restrict__ upper_coordinates) {
+	const int k = blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= count) return;
+	const int e = edge_ids[k];
+	const int2 ij = g.edges[e];
+	float3 s, r; float a;
+	arap_edge(g, rotations, translations, e, s, a, r);
+	const float S[9] = {0.f, -s.z, s.y, s.z, 0.f, -s.x, -s.y, s.x, 0.f};
+	float dEi[18];
+#pragma unroll
+	for (int rr = 0; rr < 3; rr++)
+#pragma unroll
+		for (int c = 0; c < 3; c++) { dEi[rr * 6 + c] = S[rr * 3 + c]; dEi[rr * 6 + 3 + c] = rr == c ? a : 0.f; }
+	const float bj = -a;
+	const float rv[3] = {r.x, r.y, r.z};
+	const bool upper = ij.x < ij.y;  // block (i, j) sits in the upper triangle as is, otherwise its transpose at (j, i)
+	upper_coordinates[k * 2] = upper ? ij.x : ij.y;
+	upper_coordinates[k * 2 + 1] = upper ? ij.y : ij.x;
+	for (int rr = 0; rr < 6; rr++)
+		for (int c = 0; c < 6; c++) {
+			atomicAdd(diag + (int64_t) ij.x * 36 + rr * 6 + c, sum3(dEi[rr] * dEi[c], dEi[6 + rr] * dEi[6 + c], dEi[12 + rr] * dEi[12 + c]));
+			const float b = c < 3 ? 0.f : sum3(dEi[rr] * (c == 3 ? bj : 0.f), dEi[6 + rr] * (c == 4 ? bj : 0.f), dEi[12 + rr] * (c == 5 ? bj : 0.f));
+			upper_blocks[(int64_t) k * 36 + (upper ? rr * 6 + c : c * 6 + rr)] = b;
+		}
+	for (int c = 0; c < 6; c++) atomicAdd(rhs + ij.x * 6 + c, -sum3(dEi[c] * rv[0], dEi[6 + c] * rv[1], dEi[12 + c] * rv[2]));
+	for (int c = 0; c < 3; c++) {
+		atomicAdd(diag + (int64_t) ij.y * 36 + (3 + c) * 7, bj * bj);
+		atomicAdd(rhs + ij.y * 6 + 3 + c, -bj * rv[c]);
+	}
+}
+
 // The fitter's system kernel: ONE WARP PER NODE, no atomics (ReducedSystem, solver_kernels.cuh).
 //   stem node  : H = data-term block + sum of its edges' ARAP blocks + lambda I (same summation order as build_system_kernel),
 //                D^-1 by six lanes (one unit column each), y = D^-1 b; per out-edge q: G_q = -a_q dE_i(q) (3 x 6, the non-zero
@@ -438,6 +474,8 @@ struct nnrt_b200_fitter {
 	char* graph_buffer = nullptr;  // sized by the graph: pair_offsets, list_offsets, list_items, pair_blocks, dense corner (if beyond one SM)
 	int *pair_offsets = nullptr, *list_offsets = nullptr, *pair_slots = nullptr, *in_slots = nullptr, listed_pairs = 0;
 	int2* block_pairs = nullptr;
+	int *corner_edge_ids = nullptr, *corner_upper_coords = nullptr, corner_edge_count = 0;
+	float* corner_upper = nullptr;
 	float *pair_blocks = nullptr, *reduced_packed = nullptr, *reduced_dense = nullptr, *reduced_dense_rhs = nullptr;
 	unsigned long long* keys; nnrt_b200::BandItem* queue; int* counters;
 	int32_t* diag_faces; float* diag_res; uint8_t* diag_mask;
@@ -521,7 +559,7 @@ extern "C" int nnrt_b200_fitter_create(const nnrt_b200_fitter_options* options, 
 	f->schur = nullptr; f->corner_rhs = nullptr;
 	cudaMemset(f->arena, 0, bytes);
 	launch_fill_keys(f->keys, (int64_t) f->H * f->W, nullptr);
-	if (cudaDeviceSynchronize() != cudaSuccess) { set_last_error("fitter_create: workspace initialisation failed"); return kCudaError; }
+	if (cudaDeviceSynchronize() != cudaSuccess) { nnrt_b200_fitter_destroy(f); set_last_error("fitter_create: workspace initialisation failed"); return kCudaError; }
 	*out_fitter = f;
 	return kOk;
 }
@@ -560,6 +598,7 @@ extern "C" int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* f, const float* node
 	std::vector<int32_t> h_edges((size_t) E * 2);
 	std::vector<int> out_off(N + 2, 0), in_off(N + 2, 0), out_e((size_t) E + 1), in_e((size_t) E + 1), wcol((size_t) E + 1);
 	std::vector<float> ew_res((size_t) E + 1, 0.f), ew_jac((size_t) E + 1, 0.f);
+	std::vector<int> corner_edges;  // edges between two coarser-layer nodes
 	if (E > 0) {
 		NNRT_CUDA(cudaMemcpyAsync(h_edges.data(), edges, sizeof(int32_t) * E * 2, cudaMemcpyDeviceToHost, s));
 		std::vector<int8_t> h_layers;
@@ -577,11 +616,14 @@ extern "C" int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* f, const float* node
 		const int nc = N - arrow_base;
 		for (int64_t e = 0; e < E; e++) {
 			const int i = h_edges[e * 2], j = h_edges[e * 2 + 1];
-			// the only regime in which the reference's ARAP Hessian is defined: every edge is a wing block
-			NNRT_CHECK_ARG(i >= 0 && i < arrow_base && j >= arrow_base && j < N,
-			               "edge %lld = (%d, %d) must connect a first-layer node (< %d) to a coarser-layer node (>= %d)", (long long) e, i, j, arrow_base, arrow_base);
-			out_off[i + 1]++; in_off[j - arrow_base + 1]++;
+			// An edge from a first-layer node to a coarser node is a wing block: the only regime in which the reference's ARAP Hessian is
+			// defined. An edge between two coarser nodes (hierarchies of more than two layers) is out of bounds
+			// there; here it gets the evidently intended semantics: its blocks go to the corner (diagonal + corner_upper block).
+			NNRT_CHECK_ARG(i >= 0 && i < N && j >= arrow_base && j < N && i != j,
+			               "edge %lld = (%d, %d) must lead from any node to a different node of a coarser layer (>= %d)", (long long) e, i, j, arrow_base);
 			wcol[e] = j;
+			if (i >= arrow_base) corner_edges.push_back((int) e);
+			else { out_off[i + 1]++; in_off[j - arrow_base + 1]++; }
 			if (!h_layers.empty()) {
 				const int lr = h_layers[j], lj = h_layers[e];  // sic: residual indexes the layer table by node j (…FitterImpl.h:708), Jacobian by edge
 				NNRT_CHECK_ARG(lr >= 0 && lr < layer_count && lj >= 0 && lj < layer_count, "edge layer index out of range");
@@ -592,11 +634,12 @@ extern "C" int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* f, const float* node
 		}
 		int max_degree = 0;
 		for (int i = 0; i < arrow_base; i++) max_degree = out_off[i + 1] > max_degree ? out_off[i + 1] : max_degree;
-		fused_stem = max_degree <= kMaxStemDegree;
+		fused_stem = max_degree <= kMaxStemDegree && corner_edges.empty();  // coarse-to-coarse edges take the general (6 Nc, corner_upper) path
 		for (int i = 0; i < arrow_base; i++) out_off[i + 1] += out_off[i];
 		for (int c = 0; c < nc; c++) in_off[c + 1] += in_off[c];
 		std::vector<int> oc(out_off.begin(), out_off.end()), ic(in_off.begin(), in_off.end());
 		for (int64_t e = 0; e < E; e++) {
+			if (h_edges[e * 2] >= arrow_base) continue;
 			out_e[oc[h_edges[e * 2]]++] = (int) e;
 			in_e[ic[h_edges[e * 2 + 1] - arrow_base]++] = (int) e;
 		}
@@ -670,8 +713,9 @@ extern "C" int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* f, const float* node
 		             sz_pb = al(sizeof(float) * ((size_t) list_off[listed_pairs] * 12 + 64)),
 		             sz_pk = wide ? 0 : al(sizeof(float) * reduced_packed_floats(corner_blocks)),
 		             sz_d = wide ? al(sizeof(float) * n3 * n3) : 0, sz_dr = wide ? al(sizeof(float) * (n3 + 16)) : 0;
+		const size_t ce = corner_edges.size(), sz_ce = al(sizeof(int) * (ce + 1)), sz_cu = al(sizeof(float) * (ce * 36 + 36)), sz_cc = al(sizeof(int) * (ce * 2 + 2));
 		if (f->graph_buffer) { cudaFree(f->graph_buffer); f->graph_buffer = nullptr; }
-		const size_t total = sz_po + sz_lo + sz_ps + sz_is + sz_pc + sz_pb + sz_pk + sz_d + sz_dr;
+		const size_t total = sz_po + sz_lo + sz_ps + sz_is + sz_pc + sz_pb + sz_pk + sz_d + sz_dr + sz_ce + sz_cu + sz_cc;
 		NNRT_CUDA(cudaMalloc(&f->graph_buffer, total));
 		NNRT_CUDA(cudaMemsetAsync(f->graph_buffer, 0, total, s));  // the packed system's never-written entries (padding, strict upper tiles) stay zero
 		char* q = f->graph_buffer;
@@ -683,7 +727,12 @@ extern "C" int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* f, const float* node
 		f->pair_blocks = (float*) q; q += sz_pb;
 		f->reduced_packed = wide ? nullptr : (float*) q; q += sz_pk;
 		f->reduced_dense = wide ? (float*) q : nullptr; q += sz_d;
-		f->reduced_dense_rhs = wide ? (float*) q : nullptr;
+		f->reduced_dense_rhs = wide ? (float*) q : nullptr; q += sz_dr;
+		f->corner_edge_ids = (int*) q; q += sz_ce;
+		f->corner_upper = (float*) q; q += sz_cu;
+		f->corner_upper_coords = (int*) q;
+		f->corner_edge_count = (int) ce;
+		if (ce > 0) NNRT_CUDA(cudaMemcpyAsync(f->corner_edge_ids, corner_edges.data(), sizeof(int) * ce, cudaMemcpyHostToDevice, s));
 		f->listed_pairs = listed_pairs;
 		NNRT_CUDA(cudaMemcpyAsync(f->pair_offsets, pair_off.data(), sizeof(int) * pair_off.size(), cudaMemcpyHostToDevice, s));
 		NNRT_CUDA(cudaMemcpyAsync(f->list_offsets, list_off.data(), sizeof(int) * list_off.size(), cudaMemcpyHostToDevice, s));
@@ -800,7 +849,7 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	c.g.use_huber = f->opt.use_huber_penalty; c.g.huber_constant = f->opt.huber_penalty_constant;
 	c.sys.node_count = f->N; c.sys.arrow_base = f->arrow_base; c.sys.diagonal_blocks = f->sys_diag; c.sys.rhs = f->sys_rhs;
 	c.sys.wing_blocks = f->wing; c.sys.wing_columns = f->wing_columns; c.sys.row_offsets = f->out_offsets; c.sys.row_blocks = f->out_edges;
-	c.sys.corner_upper_blocks = nullptr; c.sys.corner_upper_coordinates = nullptr; c.sys.corner_upper_count = 0;
+	c.sys.corner_upper_blocks = f->corner_upper; c.sys.corner_upper_coordinates = f->corner_upper_coords; c.sys.corner_upper_count = f->corner_edge_count;
 	c.sys.inverted_stem = f->dinv; c.sys.stem_y = f->stem_y; c.sys.wing_x = f->wing_x; c.sys.schur = f->schur; c.sys.corner_rhs = f->corner_rhs;
 	c.sys.schur_tile_packed = corner_uses_tile_packed_schur(f->N - f->arrow_base) ? 1 : 0;
 	c.sys.flags = f->counters;
@@ -866,6 +915,9 @@ static int enqueue_solve(nnrt_b200_fitter* f, const IterationContext& base, int 
 		return kOk;
 	} else {  // stem rows with more than kMaxStemDegree edges: unfused pair of kernels
 		build_system_kernel<<<(f->N + 127) / 128, 128, 0, s>>>(c.g, R, t, f->accum, f->sys_diag, f->sys_rhs, f->wing);
+		if (f->corner_edge_count > 0)
+			corner_edges_kernel<<<(f->corner_edge_count + 63) / 64, 64, 0, s>>>(c.g, f->corner_edge_ids, f->corner_edge_count, R, t, f->sys_diag, f->sys_rhs,
+			                                                                     f->corner_upper, f->corner_upper_coords);
 		if (ev) cudaEventRecord(ev[5], s);
 		launch_stem_eliminate(c.sys, s);
 		if (ev) cudaEventRecord(ev[6], s);

@@ -46,26 +46,60 @@ struct SharedMemoryOptIn {
 	}
 };
 
-// Stream-ordered scratch for the stage-level entry points. The device's default memory pool hands its memory back to the driver at
-// every synchronisation unless a release threshold is set, which makes each call pay for mapping fresh pages (measured: ~0.3 ms per
-// call of the warp-field construction); the threshold is raised once per device so freed scratch stays in the pool.
-template<typename T>
-inline cudaError_t scratch_malloc_async(T** pointer, size_t bytes, cudaStream_t stream) {
-	static std::atomic<unsigned long long> retained{0};
-	int device = 0;
-	cudaError_t err = cudaGetDevice(&device);
-	if (err != cudaSuccess) return err;
-	const unsigned long long bit = 1ull << (device & 63);
-	if (!(retained.load(std::memory_order_acquire) & bit)) {
-		cudaMemPool_t pool;
-		if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-			unsigned long long threshold = ~0ull;
-			cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
-		}
-		retained.fetch_or(bit, std::memory_order_release);
+// Stream-ordered scratch for the stage-level entry points, taken from a PRIVATE memory pool per device (the device's default pool is
+// left untouched: a host application that shares it keeps its own release policy). The pool keeps freed memory (release threshold
+// raised once) because handing it back to the driver at every synchronisation makes each call pay for mapping fresh pages (measured:
+// ~0.3 ms per call of the warp-field construction).
+inline cudaMemPool_t scratch_pool(int device) {
+	static std::atomic<cudaMemPool_t> pools[64];
+	cudaMemPool_t pool = pools[device & 63].load(std::memory_order_acquire);
+	if (pool) return pool;
+	cudaMemPoolProps props{};
+	props.allocType = cudaMemAllocationTypePinned;
+	props.handleTypes = cudaMemHandleTypeNone;
+	props.location.type = cudaMemLocationTypeDevice;
+	props.location.id = device;
+	cudaMemPool_t created = nullptr;
+	if (cudaMemPoolCreate(&created, &props) != cudaSuccess) return nullptr;
+	unsigned long long threshold = ~0ull;
+	cudaMemPoolSetAttribute(created, cudaMemPoolAttrReleaseThreshold, &threshold);
+	cudaMemPool_t expected = nullptr;
+	if (!pools[device & 63].compare_exchange_strong(expected, created, std::memory_order_acq_rel)) {
+		cudaMemPoolDestroy(created);  // another thread won the race
+		return expected;
 	}
-	return cudaMallocAsync((void**) pointer, bytes, stream);
+	return created;
 }
+
+// Scratch of one entry-point call: every allocation is returned to the pool (stream-ordered) when the object goes out of scope, on
+// the error paths as well as on success.
+class Scratch {
+public:
+	explicit Scratch(cudaStream_t stream) : stream_(stream) {}
+	Scratch(const Scratch&) = delete;
+	Scratch& operator=(const Scratch&) = delete;
+	~Scratch() {
+		for (int i = 0; i < count_; i++) cudaFreeAsync(pointers_[i], stream_);
+	}
+	template<typename T>
+	cudaError_t alloc(T** pointer, size_t bytes) {
+		*pointer = nullptr;
+		if (count_ >= kMax) return cudaErrorMemoryAllocation;
+		int device = 0;
+		cudaError_t err = cudaGetDevice(&device);
+		if (err != cudaSuccess) return err;
+		cudaMemPool_t pool = scratch_pool(device);
+		if (pool == nullptr) return cudaErrorMemoryAllocation;
+		err = cudaMallocFromPoolAsync((void**) pointer, bytes > 0 ? bytes : 1, pool, stream_);
+		if (err == cudaSuccess) pointers_[count_++] = *pointer;
+		return err;
+	}
+private:
+	static constexpr int kMax = 8;
+	cudaStream_t stream_;
+	void* pointers_[kMax];
+	int count_ = 0;
+};
 
 inline unsigned blocks_for(int64_t n, int threads) { return (unsigned) ((n + threads - 1) / threads); }
 

@@ -80,8 +80,10 @@ __global__ void __launch_bounds__(128) matmul3x3_kernel(const float* __restrict_
 // Explicit-block arrowhead workspace: CSR over wing rows is built on the host from the coordinate list (the reference
 // also synchronises with the host several times inside this call, see SURVEY.md §3.1 "syncs").
 struct ExplicitArrowhead {
+	explicit ExplicitArrowhead(cudaStream_t stream) : scratch(stream) {}
 	ArrowheadSystem sys{};
 	char* buffer = nullptr;
+	Scratch scratch;  // returns `buffer` to the pool on every path
 };
 
 static int prepare_explicit(ExplicitArrowhead& ws, const float* diag, int N, int base, const float* wing, const int32_t* coords, int64_t W,
@@ -108,7 +110,7 @@ static int prepare_explicit(ExplicitArrowhead& ws, const float* diag, int N, int
 	             sz_y = al(sizeof(float) * (size_t) (base + 1) * 6), sz_x = al(sizeof(float) * (size_t) (W + 1) * 36), sz_s = al(sizeof(float) * corner_schur_floats(nc)),
 	             sz_r = al(sizeof(float) * (n + 1)), sz_flags = 256;
 	const size_t total = sz_off + 2 * sz_blk + sz_dinv + sz_y + sz_x + sz_s + sz_r + sz_flags;
-	NNRT_CUDA(scratch_malloc_async(&ws.buffer, total, s));
+	NNRT_CUDA(ws.scratch.alloc(&ws.buffer, total));
 	char* p = ws.buffer;
 	int* d_off = (int*) p; p += sz_off;
 	int* d_blk = (int*) p; p += sz_blk;
@@ -155,17 +157,16 @@ extern "C" int nnrt_b200_solve_block_sparse_arrowhead_cholesky(const float* diag
 	if (rc != kOk) return rc;
 	NNRT_CHECK_ARG(b && x, "Size of lhs tensor b must be {%d}, matching the leading dimension of rhs matrix a.", diagonal_block_count * 6);
 	auto s = (cudaStream_t) stream;
-	ExplicitArrowhead ws;
+	ExplicitArrowhead ws(s);
 	rc = prepare_explicit(ws, diagonal_blocks, diagonal_block_count, arrow_base, upper_wing_blocks, upper_wing_coordinates, upper_wing_count,
 	                      corner_upper_blocks, corner_upper_coordinates, corner_upper_count, b, s);
-	if (rc != kOk) { if (ws.buffer) cudaFreeAsync(ws.buffer, s); return rc; }
+	if (rc != kOk) return rc;
 	ws.sys.schur_tile_packed = corner_uses_tile_packed_schur(diagonal_block_count - arrow_base) ? 1 : 0;
 	launch_stem_eliminate(ws.sys, s);
 	rc = launch_corner_solve(ws.sys, x, nullptr, nullptr, false, s);
 	int flags[3] = {0, 0, 0};
 	cudaMemcpyAsync(flags, ws.sys.flags, sizeof(flags), cudaMemcpyDeviceToHost, s);
 	cudaStreamSynchronize(s);
-	cudaFreeAsync(ws.buffer, s);
 	if (rc != kOk) return rc;
 	NNRT_LAUNCH_CHECK();
 	if (flags[2]) { set_last_error("solve_block_sparse_arrowhead_cholesky: matrix is not positive definite"); return kNotPositiveDefinite; }
@@ -182,10 +183,10 @@ extern "C" int nnrt_b200_arrowhead_schur_complement(const float* diagonal_blocks
 	NNRT_CHECK_ARG(schur, "arrowhead_schur_complement: null output");
 	auto s = (cudaStream_t) stream;
 	const int64_t n = (int64_t) (diagonal_block_count - arrow_base) * 6;
+	ExplicitArrowhead ws(s);
 	float* zero_rhs = nullptr;
-	NNRT_CUDA(scratch_malloc_async(&zero_rhs, sizeof(float) * (size_t) diagonal_block_count * 6, s));
+	NNRT_CUDA(ws.scratch.alloc(&zero_rhs, sizeof(float) * (size_t) diagonal_block_count * 6));
 	NNRT_CUDA(cudaMemsetAsync(zero_rhs, 0, sizeof(float) * (size_t) diagonal_block_count * 6, s));
-	ExplicitArrowhead ws;
 	rc = prepare_explicit(ws, diagonal_blocks, diagonal_block_count, arrow_base, upper_wing_blocks, upper_wing_coordinates, upper_wing_count,
 	                      corner_upper_blocks, corner_upper_coordinates, corner_upper_count, zero_rhs, s);
 	if (rc == kOk) {
@@ -193,8 +194,6 @@ extern "C" int nnrt_b200_arrowhead_schur_complement(const float* diagonal_blocks
 		if (n > 0) cudaMemcpyAsync(schur, ws.sys.schur, sizeof(float) * n * n, cudaMemcpyDeviceToDevice, s);
 	}
 	cudaStreamSynchronize(s);
-	if (ws.buffer) cudaFreeAsync(ws.buffer, s);
-	cudaFreeAsync(zero_rhs, s);
 	if (rc != kOk) return rc;
 	NNRT_LAUNCH_CHECK();
 	return kOk;

@@ -130,7 +130,8 @@ extern "C" int nnrt_b200_compute_vertex_normals(const int64_t* triangles, int64_
 	const size_t ints = (size_t) vertex_count + 2;
 	const size_t total = 2 * align(sizeof(int) * ints) + align(sizeof(int) * (size_t) (corner_count + 1)) + align(sizeof(int) * (size_t) scan_scratch_ints(vertex_count + 1));
 	char* buffer = nullptr;
-	NNRT_CUDA(scratch_malloc_async(&buffer, total, s));
+	Scratch scratch_guard(s);
+	NNRT_CUDA(scratch_guard.alloc(&buffer, total));
 	int* counts = (int*) buffer;                                   // becomes the CSR starts [V + 1]
 	int* fill = (int*) (buffer + align(sizeof(int) * ints));       // adjacent to counts: one memset clears both
 	int* corners = (int*) (buffer + 2 * align(sizeof(int) * ints));
@@ -145,7 +146,6 @@ extern "C" int nnrt_b200_compute_vertex_normals(const int64_t* triangles, int64_
 		vertex_normals_kernel<<<blocks_for(vertex_count, kThreads), kThreads, 0, s>>>(counts, corners, triangle_normals, vertex_count, normalized != 0, vertex_normals);
 		if (cudaGetLastError() != cudaSuccess) { set_last_error("compute_vertex_normals: kernel launch failed"); rc = kCudaError; }
 	} while (false);
-	cudaFreeAsync(buffer, s);
 	return rc;
 }
 

@@ -266,9 +266,10 @@ extern "C" int nnrt_b200_rasterize_ndc_triangles(const float* face_vertices_ndc,
 	unsigned long long* keys = nullptr;
 	BandItem* queue = nullptr;
 	int* counters = nullptr;
-	NNRT_CUDA(scratch_malloc_async(&keys, sizeof(unsigned long long) * px * 2, s));
-	NNRT_CUDA(scratch_malloc_async(&queue, sizeof(BandItem) * queue_capacity, s));
-	NNRT_CUDA(scratch_malloc_async(&counters, sizeof(int) * 2, s));
+	Scratch scratch(s);
+	NNRT_CUDA(scratch.alloc(&keys, sizeof(unsigned long long) * px * 2));
+	NNRT_CUDA(scratch.alloc(&queue, sizeof(BandItem) * queue_capacity));
+	NNRT_CUDA(scratch.alloc(&counters, sizeof(int) * 2));
 	unsigned long long* cur = keys;
 	unsigned long long* prev = keys + px;
 	int overflow_host = 0;
@@ -291,9 +292,6 @@ extern "C" int nnrt_b200_rasterize_ndc_triangles(const float* face_vertices_ndc,
 		overflow_host |= flag;
 		unsigned long long* t = cur; cur = prev; prev = t;
 	}
-	NNRT_CUDA(cudaFreeAsync(keys, s));
-	NNRT_CUDA(cudaFreeAsync(queue, s));
-	NNRT_CUDA(cudaFreeAsync(counters, s));
 	if (overflow_host) {
 		set_last_error("rasterize: large-face band queue overflow (capacity %d)", queue_capacity);
 		return kQueueOverflow;

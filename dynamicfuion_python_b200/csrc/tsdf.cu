@@ -442,7 +442,8 @@ static int integrate_non_rigid_impl(bool full_scan,
 	cudaStream_t s = (cudaStream_t) stream;
 	const int64_t pixel_count = (int64_t) image_height * image_width;
 	unsigned long long* keys = nullptr;
-	NNRT_CUDA(scratch_malloc_async(&keys, sizeof(unsigned long long) * pixel_count, s));
+	Scratch scratch(s);
+	NNRT_CUDA(scratch.alloc(&keys, sizeof(unsigned long long) * pixel_count));
 	NNRT_CUDA(cudaMemsetAsync(keys, 0, sizeof(unsigned long long) * pixel_count, s));
 	IntegrateParams p{};
 	p.block_indices = block_indices; p.block_keys = block_keys; p.tsdf = tsdf; p.weight = weight; p.weight_dtype = weight_dtype; p.voxel_color = voxel_color;
@@ -469,7 +470,6 @@ static int integrate_non_rigid_impl(bool full_scan,
 	}
 	resolve_cosines_kernel<<<blocks_for(pixel_count, 256), 256, 0, s>>>(keys, pixel_count, cos_voxel_ray_to_normal);
 	const cudaError_t err = cudaGetLastError();
-	cudaFreeAsync(keys, s);
 	if (err != cudaSuccess) { set_last_error("integrate_non_rigid: launch failed: %s", cudaGetErrorString(err)); return kCudaError; }
 	return kOk;
 }

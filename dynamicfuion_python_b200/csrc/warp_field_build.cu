@@ -546,12 +546,12 @@ extern "C" int nnrt_b200_median_grid_subsample_3d_points(const float* points, in
 	NNRT_CHECK_ARG(grid_cell_size > 0.f, "grid_cell_size must be positive, got %f", grid_cell_size);
 	cudaStream_t s = (cudaStream_t) stream;
 	char* buffer = nullptr;
-	NNRT_CUDA(scratch_malloc_async(&buffer, SubsampleWorkspace::bytes(point_count), s));
+	Scratch scratch(s);
+	NNRT_CUDA(scratch.alloc(&buffer, SubsampleWorkspace::bytes(point_count)));
 	SubsampleWorkspace w;
 	w.carve(buffer, point_count);
 	int bins = 0;
 	const int rc = median_subsample(points, point_count, grid_cell_size, grid_offset, w, sample, &bins, s);
-	cudaFreeAsync(buffer, s);
 	if (rc != kOk) return rc;
 	*sample_count_host = bins;
 	return kOk;
@@ -569,7 +569,8 @@ static int grid_mean_impl(int mode, const float* points, int64_t point_count, fl
 	cudaStream_t s = (cudaStream_t) stream;
 	char* buffer = nullptr;
 	const size_t mean_bytes = mode == 1 ? SubsampleWorkspace::align(sizeof(float) * 3 * (size_t) point_count) : 0;
-	NNRT_CUDA(scratch_malloc_async(&buffer, SubsampleWorkspace::bytes(point_count) + mean_bytes, s));
+	Scratch scratch(s);
+	NNRT_CUDA(scratch.alloc(&buffer, SubsampleWorkspace::bytes(point_count) + mean_bytes));
 	SubsampleWorkspace w;
 	w.carve(buffer, point_count);
 	float* means = mode == 1 ? (float*) (buffer + SubsampleWorkspace::bytes(point_count)) : (float*) out;
@@ -584,7 +585,6 @@ static int grid_mean_impl(int mode, const float* points, int64_t point_count, fl
 		}
 		if (cudaGetLastError() != cudaSuccess) { set_last_error("grid mean: kernel launch failed"); rc = kCudaError; }
 	}
-	cudaFreeAsync(buffer, s);
 	if (rc != kOk) return rc;
 	*count_host = bins;
 	return kOk;
@@ -644,7 +644,8 @@ extern "C" int nnrt_b200_build_regularization_layers(const float* nodes, int32_t
 	const size_t flag_bytes = SubsampleWorkspace::align(sizeof(int) * ((size_t) n + 2));
 	const size_t total = (size_t) (2 * L) * (idx_bytes + pos_bytes) + flag_bytes + idx_bytes + SubsampleWorkspace::bytes(n);
 	char* buffer = nullptr;
-	NNRT_CUDA(scratch_malloc_async(&buffer, total, s));
+	Scratch scratch(s);
+	NNRT_CUDA(scratch.alloc(&buffer, total));
 	char* p = buffer;
 	std::vector<int64_t*> layer_indices(2 * L);
 	std::vector<float*> layer_positions(2 * L);
@@ -657,7 +658,7 @@ extern "C" int nnrt_b200_build_regularization_layers(const float* nodes, int32_t
 	SubsampleWorkspace w;
 	std::vector<int> counts(L, 0);
 	int rc = kOk;
-	auto fail = [&](int code) { cudaFreeAsync(buffer, s); return code; };
+	auto fail = [&](int code) { return code; };  // `scratch` returns the buffer
 #define NNRT_LAYERS_CUDA(call)                                                                                                      \
 	do {                                                                                                                            \
 		cudaError_t err__ = (call);                                                                                                 \
@@ -728,6 +729,5 @@ extern "C" int nnrt_b200_build_regularization_layers(const float* nodes, int32_t
 	NNRT_LAYERS_CUDA(cudaGetLastError());
 #undef NNRT_LAYERS_CUDA
 	*edge_count_host = edge_count;
-	cudaFreeAsync(buffer, s);
 	return kOk;
 }

@@ -282,3 +282,55 @@ def test_status_flags_do_not_leak_into_the_next_fit(nnrt, oracle):
     fitter.fit_to_image(wf2, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]), **call)
     fitter.check_status()
     assert np.isfinite(_np(wf2.node_translations)).all()
+
+
+def test_three_layer_hierarchy_uses_corner_upper_blocks(nnrt, oracle):
+    """Edges between two coarser-layer nodes (a hierarchy of more than two layers, the default of HierarchicalGraphWarpField) are out
+    of bounds in the reference's ARAP Hessian (ArapHessianImpl.h:144-150). The fitter gives them the intended semantics (diagonal +
+    corner_upper blocks, general 6 Nc corner path); one iteration is checked against a dense float64 assembly of the same system:
+    data-term blocks and gradient from a fit with the ARAP term switched off, ARAP term of every edge restated here in numpy."""
+    s = scene_with_target(oracle, "tinyr", 120, 160)
+    rng = np.random.default_rng(21)
+    fine = s["nodes"][:s["arrow_base"]]
+    mid, top = s["nodes"][s["arrow_base"]:], s["nodes"].mean(0, keepdims=True) + np.array([[0.03, 0, 0], [-0.03, 0, 0]], np.float32)
+    nodes = np.concatenate([fine, mid, top]).astype(np.float32)
+    nf, nm = len(fine), len(mid)
+    upper = np.array([(nf + a, nf + nm + b) for a in range(nm) for b in range(2)], np.int32)  # mid -> top
+    edges = np.concatenate([s["edges"], upper]).astype(np.int32)
+    N, lam, weight, radius = len(nodes), 1.0, 20.0, float(s["layer_radii"][0])
+    anchors, weights = oracle.compute_anchors(s["positions"], nodes, 4, 0, s["node_coverage"])
+    R0 = oracle.rodrigues((rng.normal(size=(N, 3)) * 0.02).astype(np.float32))
+    t0 = (rng.normal(size=(N, 3)) * 0.002).astype(np.float32)
+    G = nnrt.geometry
+    mesh = (s["positions"], s["normals"], s["triangles"])
+
+    def run(arap):
+        wf = G.HierarchicalGraphWarpField.from_graph(nodes, edges, nf, s["node_coverage"], False, 4, 0, G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4,
+                                                     np.zeros(max(len(edges), N), np.int8), s["layer_radii"])
+        wf.set_node_rotations(R0); wf.set_node_translations(t0)
+        fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=1, preconditioning_dampening_factor=lam, arap_term_weight=arap)
+        fitter.fit_to_image(wf, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]), anchors=anchors,
+                            anchor_weights=weights)
+        fitter.check_status()
+        return fitter.diagnostics()
+    data = run(0.0)
+    H = np.zeros((6 * N, 6 * N))
+    g = _np(data["negative_gradient"]).astype(np.float64).reshape(-1).copy()
+    Hd = _np(data["hessian_diagonal"]).astype(np.float64)
+    for n in range(N):
+        H[6 * n:6 * n + 6, 6 * n:6 * n + 6] = Hd[n]  # data term + lambda I
+    a = weight * radius
+    for i, j in edges:
+        rd = R0[i].astype(np.float64) @ (nodes[i].astype(np.float64) - nodes[j])
+        sk = -a * rd
+        S = np.array([[0, -sk[2], sk[1]], [sk[2], 0, -sk[0]], [-sk[1], sk[0], 0]])
+        dEi, dEj = np.hstack([S, a * np.eye(3)]), np.hstack([np.zeros((3, 3)), -a * np.eye(3)])
+        r = a * ((nodes[i] + t0[i].astype(np.float64)) - (nodes[j] + t0[j]) - rd)
+        J = np.zeros((3, 6 * N)); J[:, 6 * i:6 * i + 6] = dEi; J[:, 6 * j:6 * j + 6] = dEj
+        H += J.T @ J
+        g -= J.T @ r
+    expected = np.linalg.solve(H, g).reshape(N, 6)
+    got = _np(run(weight)["deltas"]).astype(np.float64)
+    assert np.abs(got - expected).max() <= 1e-3 * np.abs(expected).max()
+    ok, worst = rel_close(got, expected, 1e-3, floor_scale=1e-2)
+    assert ok, worst

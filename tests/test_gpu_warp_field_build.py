@@ -224,18 +224,29 @@ def test_fast_radius_variants_bit_exact(nnrt, oracle):
     assert d.min() >= 10.0
 
 
-def test_fitter_refuses_edges_between_coarse_layers(nnrt, oracle):
-    """A hierarchy with more than two layers has edges between coarser layers; the reference's ARAP Hessian is only defined for edges
-    from the first layer (anything else writes out of bounds there), so the fitter refuses such a field with an error."""
+def test_fitter_accepts_a_constructed_three_layer_hierarchy(nnrt, oracle):
+    """A hierarchy built by the reference constructor with more than two layers has edges between coarser layers (out of bounds in
+    the reference's ARAP Hessian). The fitter routes them through corner_upper blocks
+    (test_gpu_fitter.py::test_three_layer_hierarchy_uses_corner_upper_blocks checks the arithmetic): the two classes' defaults work
+    together and a fit to the field's own rendering leaves it where it is."""
     s = synthetic.make_scene("tinyr", 120, 160)
     nodes = s["positions"][oracle.median_grid_subsample_3d_points(s["positions"], 0.03)]
     G = nnrt.geometry
     wf = G.HierarchicalGraphWarpField(nodes, 0.015, False, 4, 0, G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 3, 3)
     assert wf.get_regularization_level_count() == 3 and wf.layer_node_counts[2] > 0
-    fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=1, preconditioning_dampening_factor=1.0)
-    reference_points = np.zeros((120 * 160, 3), np.float32)
-    with pytest.raises(RuntimeError, match="first-layer node"):
-        fitter.fit_to_image(wf, (s["positions"], s["normals"], s["triangles"]), None, reference_points, None, s["K"], np.eye(4), (120, 160))
+    mesh = (s["positions"], s["normals"], s["triangles"])
+    fv, mask = oracle.face_vertices_ndc(s["positions"], s["triangles"], s["K"], 120, 160, 0.0, 10.0)
+    _, depth, _, _, _ = oracle.rasterize(fv, mask, 120, 160, 0.0, 1, perspective_correct=True)
+    depth = np.where(depth[..., 0] > 0, depth[..., 0], 0).astype(np.float32)
+    fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=3, preconditioning_dampening_factor=1.0, arap_term_weight=20.0)
+    fitter.fit_to_image(wf, mesh, None, depth, None, s["K"], np.eye(4), 1.0)
+    fitter.check_status()
+    assert bool(torch.isfinite(wf.get_node_translations()).all()) and float(wf.get_node_translations().abs().max()) < 2e-2
+    with pytest.raises(RuntimeError, match="coarser layer"):  # an edge INTO the first layer is still refused
+        bad = G.HierarchicalGraphWarpField.from_graph(nodes[:6], np.array([[3, 0]], np.int32), 3, 0.015, False, 4, 0,
+                                                      G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4)
+        fitter2 = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=1, preconditioning_dampening_factor=1.0)
+        fitter2.fit_to_image(bad, mesh, None, depth, None, s["K"], np.eye(4), 1.0)
 
 
 def test_kdtree_reference_kat(nnrt):
