@@ -37,6 +37,7 @@ _SIGNATURES = {
     "nnrt_b200_build_regularization_layers": (C.c_int, [P, I32, P, I32, I32, P, P, P, P, P, P]),
     "nnrt_b200_compute_triangle_normals": (C.c_int, [P, I64, P, I64, I32, P, P]),
     "nnrt_b200_compute_vertex_normals": (C.c_int, [P, I64, P, I64, I32, P, P]),
+    "nnrt_b200_compute_vertex_normals_static_scratch": (C.c_int, [P, I64, P, I64, I32, P, P]),
     "nnrt_b200_normalize_vectors_3d": (C.c_int, [P, I64, P]),
     "nnrt_b200_compute_ordered_point_cloud_normals": (C.c_int, [P, I32, I32, P, P]),
     "nnrt_b200_shade_edges_flat": (C.c_int, [P, P, I32, I32, I32, F32, P, P, P]),

@@ -149,6 +149,74 @@ extern "C" int nnrt_b200_compute_vertex_normals(const int64_t* triangles, int64_
 	return rc;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of compute_vertex_normals (no counterpart in the reference; added for
+// callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). The CSR scratch
+// lives in a file-scope device array, so every GPU that loads the library holds kStaticScratchBytes (~4.2 MB) until exit.
+// All calls on one device share the array and it keeps the previous call's contents: the counters are cleared at the start of each
+// call, and two calls that overlap on the GPU (different streams, no ordering between them) race.
+namespace nnrt_b200 {
+namespace {
+constexpr int64_t kStaticMaxVertices = 1 << 17, kStaticMaxFaces = 1 << 18;
+constexpr size_t align256(size_t b) { return (b + 255) & ~(size_t) 255; }
+constexpr size_t kStaticCounterBytes = align256(sizeof(int) * (size_t) (kStaticMaxVertices + 2));
+constexpr size_t kStaticCornerBytes = align256(sizeof(int) * (size_t) (kStaticMaxFaces * 3 + 1));
+constexpr size_t kStaticScanBytes = align256(sizeof(int) * (size_t) ((kStaticMaxVertices + 1 + kScanTile - 1) / kScanTile + 1));
+constexpr size_t kStaticScratchBytes = 2 * kStaticCounterBytes + kStaticCornerBytes + kStaticScanBytes;
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// In host code `g_static_scratch` is only a stand-in for the symbol: the device address is looked up once per device (with that
+// device current) and cached by ordinal.
+int static_scratch_address(char** address) {
+	static std::atomic<char*> cached[64];
+	int device = 0;
+	NNRT_CUDA(cudaGetDevice(&device));
+	NNRT_CHECK_ARG(device >= 0 && device < 64, "compute_vertex_normals_static_scratch: device ordinal %d not supported", device);
+	char* p = cached[device].load(std::memory_order_acquire);
+	if (p == nullptr) {
+		NNRT_CUDA(cudaGetSymbolAddress((void**) &p, g_static_scratch));
+		cached[device].store(p, std::memory_order_release);
+	}
+	*address = p;
+	return kOk;
+}
+}  // namespace
+}  // namespace nnrt_b200
+
+static_assert(kStaticMaxVertices == NNRT_B200_STATIC_SCRATCH_MAX_VERTICES && kStaticMaxFaces == NNRT_B200_STATIC_SCRATCH_MAX_FACES,
+              "include/nnrt_b200.h states the limits of the static scratch");
+
+extern "C" int nnrt_b200_compute_vertex_normals_static_scratch(const int64_t* triangles, int64_t face_count, const float* triangle_normals,
+                                                               int64_t vertex_count, int32_t normalized, float* vertex_normals, void* stream) {
+	if (vertex_count == 0) return kOk;
+	NNRT_CHECK_ARG(vertex_normals && vertex_count > 0, "compute_vertex_normals_static_scratch: bad vertex_normals / vertex_count");
+	NNRT_CHECK_ARG(face_count == 0 || (triangles && triangle_normals), "compute_vertex_normals_static_scratch: null pointer argument");
+	NNRT_CHECK_ARG(face_count >= 0, "compute_vertex_normals_static_scratch: face_count out of range");
+	NNRT_CHECK_ARG(vertex_count <= kStaticMaxVertices && face_count <= kStaticMaxFaces,
+	               "compute_vertex_normals_static_scratch: %lld vertices / %lld faces exceed the static scratch limit of %lld vertices / %lld faces; "
+	               "use compute_vertex_normals for larger meshes",
+	               (long long) vertex_count, (long long) face_count, (long long) kStaticMaxVertices, (long long) kStaticMaxFaces);
+	char* buffer = nullptr;
+	const int rc = static_scratch_address(&buffer);
+	if (rc != kOk) return rc;
+	cudaStream_t s = (cudaStream_t) stream;
+	const int64_t corner_count = face_count * 3;
+	int* counts = (int*) buffer;                                   // becomes the CSR starts [V + 1]
+	int* fill = (int*) (buffer + kStaticCounterBytes);             // adjacent to counts: one memset clears both
+	int* corners = (int*) (buffer + 2 * kStaticCounterBytes);
+	int* scan_tiles = (int*) (buffer + 2 * kStaticCounterBytes + kStaticCornerBytes);
+	// the previous call's counters are still there: clear them (corners and scan tiles are fully rewritten before they are read)
+	NNRT_CUDA(cudaMemsetAsync(counts, 0, kStaticCounterBytes + sizeof(int) * (size_t) (vertex_count + 2), s));
+	if (corner_count > 0) count_corners_kernel<<<blocks_for(corner_count, kThreads), kThreads, 0, s>>>(triangles, corner_count, counts);
+	const int scan_rc = exclusive_scan(counts, counts, vertex_count, scan_tiles, s);
+	if (scan_rc != kOk) return scan_rc;
+	if (corner_count > 0) fill_corners_kernel<<<blocks_for(corner_count, kThreads), kThreads, 0, s>>>(triangles, corner_count, counts, fill, corners);
+	vertex_normals_kernel<<<blocks_for(vertex_count, kThreads), kThreads, 0, s>>>(counts, corners, triangle_normals, vertex_count, normalized != 0, vertex_normals);
+	NNRT_LAUNCH_CHECK();
+	return kOk;
+}
+
 extern "C" int nnrt_b200_normalize_vectors_3d(float* vectors, int64_t count, void* stream) {
 	if (count == 0) return kOk;
 	NNRT_CHECK_ARG(vectors && count > 0, "normalize_vectors_3d: null pointer or negative count");

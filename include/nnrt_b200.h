@@ -286,6 +286,18 @@ int nnrt_b200_compute_triangle_normals(const float* vertex_positions, int64_t ve
  * scheduling); here the addends are taken in ascending face order, which is its single-thread CPU result. */
 int nnrt_b200_compute_vertex_normals(const int64_t* triangles, int64_t face_count, const float* triangle_normals, int64_t vertex_count,
                                      int32_t normalized, float* vertex_normals, void* stream);
+/* Allocation-free variant of nnrt_b200_compute_vertex_normals. It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid allocation). Same arguments and result (bit-identical) as nnrt_b200_compute_vertex_normals; the CSR scratch is a file-scope
+ * __device__ array (about 4.2 MB, held by every GPU that loads the library until exit) instead of a pool allocation, and the call
+ * makes no cudaMalloc / cudaFree / allocating library call. Meshes beyond the limits below are rejected with
+ * NNRT_B200_INVALID_ARGUMENT and a message in nnrt_b200_last_error(). All calls on a device share that array: calls that overlap on
+ * the GPU (different streams without ordering) race; calls ordered on one stream, or by events, are safe. The first call on a device
+ * looks up the array's address (cudaGetSymbolAddress); make that call outside stream capture. */
+#define NNRT_B200_STATIC_SCRATCH_MAX_VERTICES (1 << 17)
+#define NNRT_B200_STATIC_SCRATCH_MAX_FACES (1 << 18)
+int nnrt_b200_compute_vertex_normals_static_scratch(const int64_t* triangles, int64_t face_count, const float* triangle_normals,
+                                                    int64_t vertex_count, int32_t normalized, float* vertex_normals, void* stream);
 /* geometry::NormalizeVectors3d (NormalsOperations.cpp:48-50), in place. */
 int nnrt_b200_normalize_vectors_3d(float* vectors, int64_t count, void* stream);
 /* geometry::ComputeOrderedPointCloudNormals (NormalsOperations.cpp:73-93; kernel/NormalsOperationsImpl.h:172-214): central
