@@ -128,7 +128,7 @@ def scaled_motion(s, scale):
 STAGES = ["warp_vertices", "face_raster", "band_raster", "assemble", "build_system", "stem_eliminate", "corner_solve_update"]
 STAGE_KERNEL = {"warp_vertices": "warp_vertices_kernel<4>", "face_raster": "face_raster_kernel", "band_raster": "band_raster_kernel",
                 "assemble": "assemble_kernel<4>", "build_system": "system_stem_kernel", "stem_eliminate": "(fused into system_stem_kernel)",
-                "corner_solve_update": "reduced_gather_kernel + corner_solve_regtile_kernel<true>"}
+                "corner_solve_update": "reduced_gather_kernel + corner_solve_regtile_kernel<1>"}  # names as ncu prints them (<1> = <true>)
 STAGE_BOUND = {"corner_solve_update": "latency: one CTA, 3 Nc-step Cholesky dependency chain (flops and bytes are far from any roof)",
                "build_system": "latency: warp per node, 6 x 6 factorisations"}
 SETUP_LAUNCHES = 5  # anchors, 3 pack kernels, reference unprojection
@@ -568,7 +568,9 @@ def main():
     traffic = None
     try:  # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (profiles/ncu_traffic.json)
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
-            traffic = json.load(fh).get(STAGE_KERNEL[dominant].split("(")[0].split(" ")[0], {}).get("dram_bytes_per_launch")
+            table = json.load(fh)  # a stage of two kernels ("a + b") reports the sum of both launches
+            parts = [table.get(name.strip(), {}).get("dram_bytes_per_launch") for name in STAGE_KERNEL[dominant].split(" + ")]
+            traffic = sum(parts) if all(p is not None for p in parts) else None
     except (OSError, ValueError):
         pass
     iter_ms_throughput = ms_per_step / (FRAMES_PER_STEP * ITERATIONS_PER_FRAME * S)

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libnnrt_b200.so")
-SOURCES = ["c_api.cu", "geometry.cu", "warp_field_build.cu", "mesh_normals.cu", "tsdf.cu", "raster.cu", "fitter_kernels.cu", "assemble_kernel.cu", "solver_kernels.cu", "linalg_api.cu", "linalg_blocks.cu", "assembly_stages.cu", "fitter.cu"]
+SOURCES = ["c_api.cu", "geometry.cu", "warp_field_build.cu", "mesh_normals.cu", "tsdf.cu", "raster.cu", "fitter_kernels.cu", "assemble_kernel.cu", "solver_kernels.cu", "linalg_api.cu", "linalg_blocks.cu", "assembly_stages.cu", "node_store.cu", "fitter.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-fmad=false", "-std=c++17", "--extended-lambda",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-DNNRT_B200_BUILD"]
 # Per-file overrides of -fmad=false. Empty on purpose: contraction + fast division in assemble_kernel.cu (-fmad=true -prec-div=false)
@@ -61,5 +61,50 @@ def build(force=False, verbose=False):
     return LIB_PATH
 
 
+# ---- pybind11 module `nnrt` (C++ host classes over the C ABI): dynamicfuion_python_b200/pybind/nnrt.<abi>.so ---------------------------
+PYBIND_DIR = os.path.join(HERE, "pybind")
+PYBIND_SOURCES = ["bridge.cpp", "warp_field.cpp", "geometry_bind.cpp", "alignment_bind.cpp", "core_rendering_bind.cpp", "nnrt_module.cpp"]
+
+
+def pybind_module_path():
+    import sysconfig
+    return os.path.join(PYBIND_DIR, "nnrt" + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def build_pybind(force=False):
+    """g++ + pybind11 headers; links libnnrt_b200.so by relative rpath. No CUDA toolkit needed at this step."""
+    import sysconfig
+    import pybind11
+    out = pybind_module_path()
+    deps = [os.path.join(PYBIND_DIR, f) for f in os.listdir(PYBIND_DIR) if f.endswith((".cpp", ".h"))] + [os.path.join(HERE, "..", "include", "nnrt_b200.h")]
+    if not force and os.path.exists(out) and all(os.path.getmtime(d) <= os.path.getmtime(out) for d in deps):
+        return out
+    obj_dir = os.path.join(HERE, "build", "pybind")
+    os.makedirs(obj_dir, exist_ok=True)
+    flags = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-I", pybind11.get_include(), "-I", sysconfig.get_paths()["include"]]
+    procs = []
+    for src in PYBIND_SOURCES:
+        obj = os.path.join(obj_dir, src.replace(".cpp", ".o"))
+        procs.append((src, obj, subprocess.Popen(["g++"] + flags + ["-c", os.path.join(PYBIND_DIR, src), "-o", obj], stdout=subprocess.PIPE,
+                                                 stderr=subprocess.STDOUT, text=True)))
+    objs = []
+    for src, obj, p in procs:
+        text, _ = p.communicate()
+        if p.returncode != 0:
+            raise RuntimeError(f"g++ failed for {src}:\n{text}")
+        objs.append(obj)
+    subprocess.check_call(["g++", "-shared", "-o", out] + objs + ["-L", LIB_DIR, "-lnnrt_b200", "-Wl,-rpath,$ORIGIN/../lib"])
+    return out
+
+
+def import_pybind_module():
+    """`import nnrt` with the in-tree module directory on sys.path (what a user of the reference does after installing its wheel)."""
+    if PYBIND_DIR not in sys.path:
+        sys.path.insert(0, PYBIND_DIR)
+    import nnrt
+    return nnrt
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_pybind(force="--force" in sys.argv))

@@ -1,0 +1,266 @@
+// nnrt.geometry / nnrt.geometry.functional bindings: names, argument order and defaults of cpp/pybind/geometry/geometry.cpp:278-316 and
+// cpp/pybind/geometry/functional/functional.cpp:51-157.
+#include "warp_field.h"
+
+using namespace pybind11::literals;
+
+namespace nnrt {
+
+using namespace geometry;
+
+Mesh as_mesh_or_triangle_mesh(const py::handle& value) { return as_mesh(value); }
+
+static py::tuple pair_to_tuple(const std::pair<Dev, Dev>& p) { return py::make_tuple(p.first.object, p.second.object); }
+
+static void bind_functional(py::module_& m) {
+	m.def("compute_anchors_and_weights_euclidean_fixed_node_weight",
+	      [](const py::object& points, const py::object& nodes, int anchor_count, int minimum_valid_anchor_count, float node_coverage_weight) {
+		      return pair_to_tuple(compute_anchors_euclidean(as_cuda(points, Dtype::Float32), as_cuda(nodes, Dtype::Float32), Dev{}, node_coverage_weight,
+		                                                     anchor_count, minimum_valid_anchor_count));
+	      }, "points"_a, "nodes"_a, "anchor_count"_a, "minimum_valid_anchor_count"_a, "node_coverage_weight"_a);
+	m.def("compute_anchors_and_weights_euclidean_variable_node_weight",
+	      [](const py::object& points, const py::object& nodes, const py::object& node_coverage_weights, int anchor_count, int minimum_valid_anchor_count) {
+		      return pair_to_tuple(compute_anchors_euclidean(as_cuda(points, Dtype::Float32), as_cuda(nodes, Dtype::Float32),
+		                                                     as_cuda(node_coverage_weights, Dtype::Float32), 0.f, anchor_count, minimum_valid_anchor_count));
+	      }, "points"_a, "nodes"_a, "node_coverage_weights"_a, "anchor_count"_a, "minimum_valid_anchor_count"_a);
+
+	auto shortest_path = [](const py::object& points_in, const py::object& nodes_in, const py::object& weights_in, float node_coverage, const py::object& edges_in,
+	                        int anchor_count) {
+		Dev points = as_cuda(points_in, Dtype::Float32), nodes = as_cuda(nodes_in, Dtype::Float32);
+		if (points.dim() < 2 || points.dim() > 3)  // WarpAnchorComputation.cpp:41-44
+			log_error("`points` needs to have 2 or 3 dimensions. Got: " + std::to_string(points.dim()) + " dimensions.");
+		if (points.size(-1) != 3) log_error("points must have shape [..., 3], got " + points.shape_string());
+		if (anchor_count < 1) log_error("anchor_count needs to be greater than one. Got: " + std::to_string(anchor_count) + ".");
+		py::object edges_tensor = to_torch(edges_in);
+		if (!has_dtype(edges_tensor, Torch::get().dtype(Dtype::Int32)))  // o3c::AssertTensorDtype(edges, Int32), :169,197
+			log_error("edges must be Int32, got " + py::str(edges_tensor.attr("dtype")).cast<std::string>());
+		Dev edges = as_cuda(edges_tensor, Dtype::Int32);
+		if (edges.dim() != 2 || edges.size(0) != nodes.size(0)) log_error("edges must have shape [node_count, degree], got " + edges.shape_string());
+		Dev weights_nodes = as_cuda_or_none(weights_in, Dtype::Float32);
+		if (weights_nodes.defined() && weights_nodes.numel() != nodes.size(0)) log_error("node_coverage_weights must have one entry per node");
+		std::vector<int64_t> out_shape(points.shape.begin(), points.shape.end() - 1);
+		out_shape.push_back(anchor_count);
+		Dev anchors = empty(out_shape, Dtype::Int32), weights = empty(out_shape, Dtype::Float32);
+		check(nnrt_b200_compute_anchors_shortest_path(points.data<float>(), points.numel() / 3, nodes.data<float>(), (int32_t) nodes.size(0),
+		                                              weights_nodes.defined() ? weights_nodes.data<float>() : nullptr, node_coverage, edges.data<int32_t>(),
+		                                              (int32_t) edges.size(1), anchor_count, anchors.data<int32_t>(), weights.data<float>(), current_stream()));
+		return py::make_tuple(anchors.object, weights.object);
+	};
+	m.def("compute_anchors_and_weights_shortest_path_fixed_node_weight",
+	      [shortest_path](const py::object& points, const py::object& nodes, const py::object& edges, int anchor_count, float node_coverage_weight) {
+		      return shortest_path(points, nodes, py::none(), node_coverage_weight, edges, anchor_count);
+	      }, "points"_a, "nodes"_a, "edges"_a, "anchor_count"_a, "node_coverage_weight"_a);
+	m.def("compute_anchors_and_weights_shortest_path_variable_node_weight",
+	      [shortest_path](const py::object& points, const py::object& nodes, const py::object& node_coverage_weights, const py::object& edges, int anchor_count) {
+		      return shortest_path(points, nodes, node_coverage_weights, 0.f, edges, anchor_count);
+	      }, "points"_a, "nodes"_a, "node_coverage_weights"_a, "edges"_a, "anchor_count"_a);
+
+	// warp_triangle_mesh, both overloads (functional.cpp:77-93): the fifth / sixth arguments are (anchor_count, node_coverage) or (anchors, anchor_weights)
+	m.def("warp_triangle_mesh",
+	      [](const py::object& input_mesh, const py::object& nodes_in, const py::object& rotations, const py::object& translations, int anchor_count,
+	         float node_coverage, bool threshold_nodes_by_distance, int minimum_valid_anchor_count, const py::object& extrinsics) {
+		      const Mesh mesh = as_mesh(input_mesh);
+		      Dev nodes = as_cuda(nodes_in, Dtype::Float32);
+		      const int min_valid = threshold_nodes_by_distance ? minimum_valid_anchor_count : 0;
+		      auto [anchors, weights] = compute_anchors_euclidean(mesh.positions, nodes, Dev{}, node_coverage, anchor_count, min_valid);
+		      auto [wp, wn] = warp_points_normals(mesh.positions, mesh.normals, nodes, as_cuda(rotations, Dtype::Float32), as_cuda(translations, Dtype::Float32),
+		                                          anchors, weights, min_valid, extrinsics);
+		      return make_mesh(wp, wn, mesh.triangles);
+	      }, "input_mesh"_a, "nodes"_a, "node_rotations"_a, "node_translations"_a, "anchor_count"_a, "node_coverage"_a,
+	      "threshold_nodes_by_distance"_a = false, "minimum_valid_anchor_count"_a = 0, "extrinsics"_a = py::none());
+	m.def("warp_triangle_mesh",
+	      [](const py::object& input_mesh, const py::object& nodes_in, const py::object& rotations, const py::object& translations, const py::object& anchors,
+	         const py::object& anchor_weights, bool threshold_nodes_by_distance, int minimum_valid_anchor_count, const py::object& extrinsics) {
+		      const Mesh mesh = as_mesh(input_mesh);
+		      const int min_valid = threshold_nodes_by_distance ? minimum_valid_anchor_count : 0;
+		      auto [wp, wn] = warp_points_normals(mesh.positions, mesh.normals, as_cuda(nodes_in, Dtype::Float32), as_cuda(rotations, Dtype::Float32),
+		                                          as_cuda(translations, Dtype::Float32), as_cuda(anchors, Dtype::Int32), as_cuda(anchor_weights, Dtype::Float32),
+		                                          min_valid, extrinsics);
+		      return make_mesh(wp, wn, mesh.triangles);
+	      }, "input_mesh"_a, "nodes"_a, "node_rotations"_a, "node_translations"_a, "anchors"_a, "anchor_weights"_a,
+	      "threshold_nodes_by_distance"_a = false, "minimum_valid_anchor_count"_a = 0, "extrinsics"_a = py::none());
+
+	// compute_{triangle,vertex}_normals (functional.cpp:112-113): returns the normals (a tuple / dict mesh cannot be modified in place)
+	m.def("compute_triangle_normals", [](const py::object& mesh_in, bool normalized) {
+		const Mesh mesh = as_mesh(mesh_in);
+		if (!mesh.triangles.defined()) log_error("Argument mesh needs to have both triangle vertex indices and vertex positions.");
+		Dev normals = empty({mesh.triangles.size(0), 3}, Dtype::Float32);
+		check(nnrt_b200_compute_triangle_normals(mesh.positions.data<float>(), mesh.positions.size(0), mesh.triangles.data<int64_t>(), mesh.triangles.size(0),
+		                                         normalized ? 1 : 0, normals.data<float>(), current_stream()));
+		return normals.object;
+	}, "mesh"_a, "normalized"_a = true);
+	m.def("compute_vertex_normals", [](const py::object& mesh_in, bool normalized) {
+		const Mesh mesh = as_mesh(mesh_in);
+		if (!mesh.triangles.defined()) log_error("Argument mesh needs to have both triangle vertex indices and vertex positions.");
+		Dev triangle_normals = mesh.triangle_normals;
+		if (!triangle_normals.defined()) {  // NormalsOperations.cpp:52-60: un-normalised triangle normals are computed when the mesh carries none
+			triangle_normals = empty({mesh.triangles.size(0), 3}, Dtype::Float32);
+			check(nnrt_b200_compute_triangle_normals(mesh.positions.data<float>(), mesh.positions.size(0), mesh.triangles.data<int64_t>(),
+			                                         mesh.triangles.size(0), 0, triangle_normals.data<float>(), current_stream()));
+		}
+		Dev normals = empty(mesh.positions.shape, Dtype::Float32);
+		check(nnrt_b200_compute_vertex_normals(mesh.triangles.data<int64_t>(), mesh.triangles.size(0), triangle_normals.data<float>(), mesh.positions.size(0),
+		                                       normalized ? 1 : 0, normals.data<float>(), current_stream()));
+		return normals.object;
+	}, "mesh"_a, "normalized"_a = true);
+}
+
+void bind_geometry(py::module_& m) {
+	py::enum_<AnchorComputationMethod>(m, "AnchorComputationMethod")
+			.value("EUCLIDEAN", AnchorComputationMethod::EUCLIDEAN)
+			.value("SHORTEST_PATH", AnchorComputationMethod::SHORTEST_PATH)
+			.export_values();
+	py::enum_<WarpNodeCoverageComputationMethod>(m, "WarpNodeCoverageComputationMethod")
+			.value("FIXED_NODE_COVERAGE", WarpNodeCoverageComputationMethod::FIXED_NODE_COVERAGE)
+			.value("MINIMAL_K_NEIGHBOR_NODE_DISTANCE", WarpNodeCoverageComputationMethod::MINIMAL_K_NEIGHBOR_NODE_DISTANCE)
+			.export_values();
+
+	py::class_<TriangleMesh>(m, "TriangleMesh", "Result holder standing in for open3d.t.geometry.TriangleMesh: .vertex / .triangle attribute maps.")
+			.def_readonly("vertex", &TriangleMesh::vertex)
+			.def_readonly("triangle", &TriangleMesh::triangle)
+			.def_property_readonly("positions", [](const TriangleMesh& s) { return s.vertex["positions"]; })
+			.def_property_readonly("normals", [](const TriangleMesh& s) -> py::object { return s.vertex.contains("normals") ? py::object(s.vertex["normals"]) : py::none(); })
+			.def_property_readonly("triangles", [](const TriangleMesh& s) -> py::object { return s.triangle.contains("indices") ? py::object(s.triangle["indices"]) : py::none(); });
+
+	py::class_<WarpField> graph_warp_field(
+			m, "GraphWarpField",
+			"A warp (motion) field represented by a graph: the motion of a point is a weighted function of the motions of the graph nodes close to it.");
+	graph_warp_field.def(py::init([](const py::object& nodes, float node_coverage, bool threshold_nodes_by_distance, int anchor_count, int minimum_valid_anchor_count,
+	                                 WarpNodeCoverageComputationMethod method, int neighbor_count) {
+		                     return new WarpField(nodes, node_coverage, threshold_nodes_by_distance, anchor_count, minimum_valid_anchor_count, method, neighbor_count);
+	                     }),
+	                     "nodes"_a, "node_coverage"_a = 0.05, "threshold_nodes_by_distance"_a = false, "anchor_count"_a = 4, "minimum_valid_anchor_count"_a = 0,
+	                     "warp_node_coverage_computation_method"_a = WarpNodeCoverageComputationMethod::MINIMAL_K_NEIGHBOR_NODE_DISTANCE,
+	                     "warp_node_coverage_neighbor_count"_a = 4);
+	graph_warp_field.def("get_warped_nodes", &WarpField::GetWarpedNodes);
+	graph_warp_field.def("get_node_extent", &WarpField::GetNodeExtent);
+	graph_warp_field.def("warp_mesh",
+	                     [](const WarpField& self, const py::object& input_mesh, bool disable_neighbor_thresholding, const py::object& extrinsics) {
+		                     return self.WarpMesh(input_mesh, py::none(), py::none(), disable_neighbor_thresholding, extrinsics);
+	                     }, "input_mesh"_a, "disable_neighbor_thresholding"_a = true, "extrinsics"_a = py::none());
+	graph_warp_field.def("warp_mesh",
+	                     [](const WarpField& self, const py::object& input_mesh, const py::object& anchors, const py::object& anchor_weights,
+	                        bool disable_neighbor_thresholding, const py::object& extrinsics) {
+		                     return self.WarpMesh(input_mesh, anchors, anchor_weights, disable_neighbor_thresholding, extrinsics);
+	                     }, "input_mesh"_a, "anchors"_a, "anchor_weights"_a, "disable_neighbor_thresholding"_a = true, "extrinsics"_a = py::none());
+	graph_warp_field.def("precompute_anchors_and_weights",
+	                     [](const WarpField& self, const py::object& input_mesh) { return pair_to_tuple(self.PrecomputeAnchorsAndWeights(as_mesh(input_mesh))); },
+	                     "input_mesh"_a);
+	// WarpField::Clone (WarpField.cpp:166-168): node positions are shared (immutable), the motion is copied
+	graph_warp_field.def("clone", [](const WarpField& self) {
+		auto* other = new WarpField(self);
+		other->node_rotations = clone(self.node_rotations);
+		other->node_translations = clone(self.node_translations);
+		if (self.node_coverage_weights.defined()) other->node_coverage_weights = clone(self.node_coverage_weights);
+		return other;
+	});
+	graph_warp_field.def("reset_rotations", &WarpField::ResetRotations);
+	// WarpField::ApplyTransformations (WarpField.cpp:161-164): a new field at the warped node positions, motion reset
+	graph_warp_field.def("apply_transformations", [](const WarpField& self) {
+		return new WarpField(self.GetWarpedNodes(), self.node_coverage, self.threshold_nodes_by_distance_by_default, self.anchor_count,
+		                     self.minimum_valid_anchor_count, self.warp_node_coverage_computation_method, self.warp_node_coverage_neighbor_count);
+	});
+	graph_warp_field.def("get_node_rotations", [](const WarpField& self) { return self.node_rotations.object; });
+	graph_warp_field.def("get_node_translations", [](const WarpField& self) { return self.node_translations.object; });
+	graph_warp_field.def("set_node_rotations", [](WarpField& self, const py::object& r) { self.SetNodeRotations(as_cuda(r, Dtype::Float32)); }, "node_rotations"_a);
+	graph_warp_field.def("set_node_translations", [](WarpField& self, const py::object& t) { self.SetNodeTranslations(as_cuda(t, Dtype::Float32)); },
+	                     "node_translations"_a);
+	graph_warp_field.def("translate_nodes", [](WarpField& self, const py::object& d) { self.TranslateNodes(as_cuda(d, Dtype::Float32)); },
+	                     "node_translation_deltas"_a);
+	graph_warp_field.def("rotate_nodes", [](WarpField& self, const py::object& d) { self.RotateNodes(as_cuda(d, Dtype::Float32)); }, "node_rotation_deltas"_a);
+	graph_warp_field.def_property_readonly("nodes", [](const WarpField& self) { return self.nodes.object; });
+	graph_warp_field.def_property_readonly("node_rotations", [](const WarpField& self) { return self.node_rotations.object; });
+	graph_warp_field.def_property_readonly("node_translations", [](const WarpField& self) { return self.node_translations.object; });
+	graph_warp_field.def_property_readonly("node_coverage_weights", [](const WarpField& self) -> py::object {
+		return self.node_coverage_weights.defined() ? self.node_coverage_weights.object : py::none();
+	});
+	graph_warp_field.def_readonly("node_coverage", &WarpField::node_coverage);
+	graph_warp_field.def_readonly("anchor_count", &WarpField::anchor_count);
+	graph_warp_field.def_readonly("minimum_valid_anchor_count", &WarpField::minimum_valid_anchor_count);
+	graph_warp_field.def_readonly("warp_node_coverage_computation_method", &WarpField::warp_node_coverage_computation_method);
+
+	using H = HierarchicalGraphWarpField;
+	py::class_<H::RegularizationLayer>(m, "RegularizationLayer")
+			.def_readonly("decimation_radius", &H::RegularizationLayer::decimation_radius)
+			.def_readonly("node_indices", &H::RegularizationLayer::node_indices)
+			.def_readonly("node_positions", &H::RegularizationLayer::node_positions)
+			.def_readonly("edges", &H::RegularizationLayer::edges);
+	py::class_<H, WarpField> hierarchical(m, "HierarchicalGraphWarpField",
+	                                      "Warp field with regularisation layers (cpp/geometry/HierarchicalGraphWarpField.h:35-96). Storage is in virtual order "
+	                                      "(layer 0 first); accessors take use_virtual_ordering and default to the original node order.");
+	hierarchical.def(py::init([](const py::object& nodes, float node_coverage, bool threshold, int anchor_count, int minimum_valid_anchor_count,
+	                             WarpNodeCoverageComputationMethod method, int layer_count, int max_vertex_degree, const py::object& radius_function) {
+		                 return new H(nodes, node_coverage, threshold, anchor_count, minimum_valid_anchor_count, method, layer_count, max_vertex_degree, radius_function);
+	                 }),
+	                 "nodes"_a, "node_coverage"_a = 0.05, "threshold_nodes_by_distance_by_default"_a = false, "anchor_count"_a = 4,
+	                 "minimum_valid_anchor_count"_a = 0,
+	                 "warp_node_coverage_computation_method"_a = WarpNodeCoverageComputationMethod::MINIMAL_K_NEIGHBOR_NODE_DISTANCE, "layer_count"_a = 4,
+	                 "max_vertex_degree"_a = 4, "compute_layer_decimation_radius"_a = py::none());
+	hierarchical.def_static("from_graph",
+	                        [](const py::object& nodes, const py::object& edges, const py::object& first_layer_node_count, float node_coverage, bool threshold,
+	                           int anchor_count, int minimum_valid_anchor_count, WarpNodeCoverageComputationMethod method, int neighbor_count,
+	                           const py::object& edge_layer_indices, const py::object& layer_decimation_radii) {
+		                        return new H(nodes, edges, first_layer_node_count, node_coverage, threshold, anchor_count, minimum_valid_anchor_count, method,
+		                                     neighbor_count, edge_layer_indices, layer_decimation_radii);
+	                        },
+	                        "nodes"_a, "edges"_a = py::none(), "first_layer_node_count"_a = py::none(), "node_coverage"_a = 0.05,
+	                        "threshold_nodes_by_distance"_a = false, "anchor_count"_a = 4, "minimum_valid_anchor_count"_a = 0,
+	                        "warp_node_coverage_computation_method"_a = WarpNodeCoverageComputationMethod::MINIMAL_K_NEIGHBOR_NODE_DISTANCE,
+	                        "warp_node_coverage_neighbor_count"_a = 4, "edge_layer_indices"_a = py::none(), "layer_decimation_radii"_a = py::none());
+	hierarchical.def("get_regularization_level", [](const H& self, int i) {
+		if (i < 0 || i >= (int) self.regularization_layers.size()) log_error("regularization level " + std::to_string(i) + " does not exist");
+		return self.regularization_layers[i];
+	}, "i_layer"_a);
+	hierarchical.def("get_regularization_level_count", [](const H& self) { return (int) self.layer_node_counts.size(); });
+	hierarchical.def("get_node_positions", [](const H& self, bool v) { return self.to_original(self.nodes, v).object; }, "use_virtual_ordering"_a = false);
+	hierarchical.def("get_node_rotations", [](const H& self, bool v) { return self.to_original(self.node_rotations, v).object; }, "use_virtual_ordering"_a = false);
+	hierarchical.def("get_node_translations", [](const H& self, bool v) { return self.to_original(self.node_translations, v).object; },
+	                 "use_virtual_ordering"_a = false);
+	hierarchical.def("get_node_coverage_weights", [](const H& self, bool v) -> py::object {
+		return self.node_coverage_weights.defined() ? self.to_original(self.node_coverage_weights, v).object : py::none();
+	}, "use_virtual_ordering"_a = false);
+	hierarchical.def("get_warped_nodes", [](const H& self, bool v) { return self.to_original(wrap(self.GetWarpedNodes()), v).object; },
+	                 "use_virtual_ordering"_a = false);
+	hierarchical.def("get_edges", [](const H& self) { return self.edges.object; });
+	hierarchical.def("get_virtual_node_indices", [](const H& self) { return self.node_indices.object; });
+	hierarchical.def("get_edge_layer_indices", [](const H& self) { return self.edge_layer_indices.object; });
+	hierarchical.def("get_layer_decimation_radii", [](const H& self) { return self.layer_decimation_radii.object; });
+	hierarchical.def("set_node_rotations", [](H& self, const py::object& r, bool v) { self.SetNodeRotations(self.to_virtual(as_cuda(r, Dtype::Float32), v)); },
+	                 "node_rotations"_a, "use_virtual_ordering"_a = false);
+	hierarchical.def("set_node_translations", [](H& self, const py::object& t, bool v) { self.SetNodeTranslations(self.to_virtual(as_cuda(t, Dtype::Float32), v)); },
+	                 "node_translations"_a, "use_virtual_ordering"_a = false);
+	hierarchical.def("translate_nodes", [](H& self, const py::object& d, bool v) { self.TranslateNodes(self.to_virtual(as_cuda(d, Dtype::Float32), v)); },
+	                 "node_translation_deltas"_a, "use_virtual_ordering"_a = false);
+	hierarchical.def("rotate_nodes", [](H& self, const py::object& d, bool v) { self.RotateNodes(self.to_virtual(as_cuda(d, Dtype::Float32), v)); },
+	                 "node_rotation_deltas"_a, "use_virtual_ordering"_a = false);
+	hierarchical.def("precompute_anchors_and_weights", [](const H& self, const py::object& mesh, bool v) {
+		return pair_to_tuple(self.PrecomputeAnchorsAndWeights(as_mesh(mesh), v));
+	}, "input_mesh"_a, "use_virtual_ordering"_a = false);
+	hierarchical.def("warp_mesh", [](const H& self, const py::object& input_mesh, bool disable_neighbor_thresholding, const py::object& extrinsics) {
+		return self.WarpMesh(input_mesh, py::none(), py::none(), disable_neighbor_thresholding, extrinsics);
+	}, "input_mesh"_a, "disable_neighbor_thresholding"_a = true, "extrinsics"_a = py::none());
+	hierarchical.def("warp_mesh", [](const H& self, const py::object& input_mesh, const py::object& anchors, const py::object& anchor_weights,
+	                                 bool disable_neighbor_thresholding, const py::object& extrinsics, bool use_virtual_ordering) {
+		Dev a = as_cuda(anchors, Dtype::Int32);
+		if (!use_virtual_ordering) a = self.anchors_to_virtual(a);  // supplied anchors index the original order unless told otherwise
+		return self.WarpMesh(input_mesh, a.object, anchor_weights, disable_neighbor_thresholding, extrinsics);
+	}, "input_mesh"_a, "anchors"_a, "anchor_weights"_a, "disable_neighbor_thresholding"_a = true, "extrinsics"_a = py::none(), "use_virtual_ordering"_a = false);
+	hierarchical.def("clone", [](const H& self) {
+		auto* other = new H(self);
+		other->node_rotations = clone(self.node_rotations);
+		other->node_translations = clone(self.node_translations);
+		if (self.node_coverage_weights.defined()) other->node_coverage_weights = clone(self.node_coverage_weights);
+		return other;
+	});
+	hierarchical.def_property_readonly("edges", [](const H& self) { return self.edges.object; });
+	hierarchical.def_property_readonly("edge_layer_indices", [](const H& self) { return self.edge_layer_indices.object; });
+	hierarchical.def_property_readonly("layer_decimation_radii", [](const H& self) { return self.layer_decimation_radii.object; });
+	hierarchical.def_property_readonly("node_indices", [](const H& self) { return self.node_indices.object; });
+	hierarchical.def_readonly("first_layer_node_count", &H::first_layer_node_count);
+	hierarchical.def_readonly("layer_node_counts", &H::layer_node_counts);
+
+	py::module_ functional = m.def_submodule("functional", "Stateless functions on geometry (cpp/pybind/geometry/functional/functional.cpp).");
+	bind_functional(functional);
+}
+
+}  // namespace nnrt

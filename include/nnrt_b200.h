@@ -367,6 +367,20 @@ int nnrt_b200_boxes_intersecting_surface_mask(const float* boxes, int64_t box_co
                                               int32_t depth_dtype, int32_t image_height, int32_t image_width, float depth_scale,
                                               float depth_max, int32_t stride, float truncation_distance, uint8_t* mask, void* stream);
 
+/* ---- Node store of the warp field (what the host classes do to node tensors besides the warp) ----
+ * WarpField::GetWarpedNodes / TranslateNodes (geometry/WarpField.cpp:89-91,185-187; HierarchicalGraphWarpField.cpp:261-269): out = a + alpha * b. */
+int nnrt_b200_add_scaled(const float* a, const float* b, float alpha, int64_t count, float* out, void* stream);
+/* WarpField::ResetRotations (geometry/WarpField.cpp:151-159): [count,3,3] identities. */
+int nnrt_b200_fill_identity_rotations(float* rotations, int64_t count, void* stream);
+/* Virtual <-> original node order (HierarchicalGraphWarpField.cpp:197-226, tensor[indices] with an Int64 index tensor): rows of
+ * `row_words` 4-byte words, out[i] = source[indices[i]]. */
+int nnrt_b200_gather_rows(const void* source, int64_t source_rows, int32_t row_words, const int64_t* indices, int64_t count, void* out,
+                          void* stream);
+/* inverse[permutation[i]] = i (original -> virtual index map of HierarchicalGraphWarpField). */
+int nnrt_b200_invert_permutation(const int64_t* permutation, int64_t count, int64_t* inverse, void* stream);
+/* Anchor indices between the two node orders (HierarchicalGraphWarpField.cpp:228-256): out = map[index], -1 (no anchor) kept. */
+int nnrt_b200_remap_indices(const int32_t* indices, int64_t count, const int64_t* map, int64_t map_size, int32_t* out, void* stream);
+
 /* ---- Un-fused stages of the assembly chain (parity-test entry points; the fitter's iteration fuses them) ----
  * alignment::functional::PixelVertexAnchorJacobiansAndNodeAssociations (alignment/functional/PixelVertexAnchorJacobians.cpp:29-56;
  * kernel/PixelVertexAnchorJacobiansImpl.h:40-434). Inputs are the reference's intermediate tensors: rasterized vertex position /

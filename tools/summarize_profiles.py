@@ -56,8 +56,8 @@ def main():
     ours = {k: v for k, v in agg.items() if any(p in k for p in OURS)}
     total = sum(sum(v) for v in ours.values())
     lines = [f"# {tag} — ncu launch list and per-kernel captures",
-             "", f"Launch list: `profiles/{tag}_launches.csv` (`ncu --metrics gpu__time_duration.sum --clock-control none` over `python bench.py --steps 2 "
-             "--warmup 3 --no-cpu-baseline`). Times under ncu are cold-cache and serialised: only the SHARE per kernel is meaningful.",
+             "", f"Launch list: `profiles/{tag}_launches.csv` (`ncu --metrics gpu__time_duration.sum --clock-control none` over `python bench.py --steps 1 "
+             "--warmup 3 --no-cpu-baseline --no-configs`, tools/refresh_profiles.sh). Times under ncu are cold-cache and serialised: only the SHARE per kernel is meaningful.",
              "", "| kernel | launches | total us | avg us | share of our kernels |", "|---|---|---|---|---|"]
     for k, v in sorted(ours.items(), key=lambda kv: -sum(kv[1])):
         lines.append(f"| `{short(k)}` | {len(v)} | {sum(v):.1f} | {sum(v) / len(v):.2f} | {100 * sum(v) / total:.1f} % |")
