@@ -103,6 +103,14 @@ bool reduced_corner_fits_one_cta(int corner_blocks);
 size_t reduced_packed_floats(int corner_blocks);  // allocation size of ReducedSystem::packed (zero-initialised once)
 int launch_reduced_corner_solve(const ReducedSystem& sys, float* x, float* node_rotations, float* node_translations, cudaStream_t s);
 
+// corner_cluster.cu: in-place Cholesky + forward substitution of a dense corner system (lower triangle of schur [n, n], corner_rhs [n])
+// by one thread-block cluster; kUnsupported when the device cannot co-schedule one.
+int launch_corner_cluster_factor(float* schur, float* corner_rhs, int n, int* flags, cudaStream_t s);
+// back substitution with the block inverses the cluster kernel left behind, stem back substitution and node update (one CTA);
+// `red` != nullptr: the fitter's reduced system (sys carries schur / corner_rhs / flags only).
+int launch_corner_cluster_finish(const ArrowheadSystem& sys, const ReducedSystem* red, int n, float* x, float* node_rotations, float* node_translations,
+                                 cudaStream_t s);
+
 void launch_stem_eliminate(const ArrowheadSystem& sys, cudaStream_t s);
 // x [6N]; if node_rotations != nullptr the update is applied in place; clear_corner zeroes schur / corner_rhs after reading.
 int launch_corner_solve(const ArrowheadSystem& sys, float* x, float* node_rotations, float* node_translations, bool clear_corner,

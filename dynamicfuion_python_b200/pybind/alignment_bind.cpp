@@ -109,6 +109,17 @@ public:
 		return out;
 	}
 
+	// one iteration outside the graph with CUDA events between the stages: ms for [warp_vertices, face_raster, band_raster, assemble,
+	// build_system, stem_eliminate, corner_solve_update]
+	std::vector<float> ProfileIteration(WarpField& warp_field, const py::handle& intrinsic_matrix, const py::handle& extrinsic_matrix) {
+		require_handle();
+		const std::vector<double> K = host_matrix(intrinsic_matrix, 3, 3, false), extrinsics = host_matrix(extrinsic_matrix, 4, 4, true);
+		std::vector<float> out(7, 0.f);
+		check(nnrt_b200_fitter_profile_iteration(handle, warp_field.node_rotations.data<float>(), warp_field.node_translations.data<float>(), K.data(),
+		                                         extrinsics.data(), out.data(), current_stream()));
+		return out;
+	}
+
 	int LaunchesPerIteration() {
 		require_handle();
 		return nnrt_b200_fitter_launches_per_iteration(handle);
@@ -269,6 +280,7 @@ void bind_alignment(py::module_& m) {
 	fitter.def("check_status", &DeformableMeshToImageFitter::CheckStatus,
 	           "Waits for the stream and raises if the last fit overflowed its band queue or met a non-positive-definite block.");
 	fitter.def("diagnostics", &DeformableMeshToImageFitter::Diagnostics);
+	fitter.def("profile_iteration", &DeformableMeshToImageFitter::ProfileIteration, "warp_field"_a, "intrinsic_matrix"_a, "extrinsic_matrix"_a = py::none());
 	fitter.def("launches_per_iteration", &DeformableMeshToImageFitter::LaunchesPerIteration);
 	fitter.def("workspace_bytes", &DeformableMeshToImageFitter::WorkspaceBytes);
 	fitter.def_readonly("max_iteration_count", &DeformableMeshToImageFitter::max_iteration_count);

@@ -8,7 +8,12 @@ namespace nnrt {
 
 using namespace geometry;
 
-Mesh as_mesh_or_triangle_mesh(const py::handle& value) { return as_mesh(value); }
+// The reference's compute_*_normals modify the mesh in place (mesh.SetTriangleNormals / SetVertexNormals): a dict mesh gets the key, an
+// Open3D-like mesh its .triangle / .vertex map entry; a tuple is immutable and the caller uses the returned tensor.
+static void store_mesh_attribute(const py::object& mesh, const char* group, const char* dict_key, const py::object& value) {
+	if (py::isinstance<py::dict>(mesh)) mesh[py::str(dict_key)] = value;
+	else if (!py::isinstance<py::tuple>(mesh) && !py::isinstance<py::list>(mesh) && py::hasattr(mesh, group)) mesh.attr(group)[py::str("normals")] = value;
+}
 
 static py::tuple pair_to_tuple(const std::pair<Dev, Dev>& p) { return py::make_tuple(p.first.object, p.second.object); }
 
@@ -87,6 +92,7 @@ static void bind_functional(py::module_& m) {
 		Dev normals = empty({mesh.triangles.size(0), 3}, Dtype::Float32);
 		check(nnrt_b200_compute_triangle_normals(mesh.positions.data<float>(), mesh.positions.size(0), mesh.triangles.data<int64_t>(), mesh.triangles.size(0),
 		                                         normalized ? 1 : 0, normals.data<float>(), current_stream()));
+		store_mesh_attribute(mesh_in, "triangle", "triangle_normals", normals.object);
 		return normals.object;
 	}, "mesh"_a, "normalized"_a = true);
 	m.def("compute_vertex_normals", [](const py::object& mesh_in, bool normalized) {
@@ -101,6 +107,7 @@ static void bind_functional(py::module_& m) {
 		Dev normals = empty(mesh.positions.shape, Dtype::Float32);
 		check(nnrt_b200_compute_vertex_normals(mesh.triangles.data<int64_t>(), mesh.triangles.size(0), triangle_normals.data<float>(), mesh.positions.size(0),
 		                                       normalized ? 1 : 0, normals.data<float>(), current_stream()));
+		store_mesh_attribute(mesh_in, "vertex", "normals", normals.object);
 		return normals.object;
 	}, "mesh"_a, "normalized"_a = true);
 }
@@ -171,9 +178,13 @@ void bind_geometry(py::module_& m) {
 	graph_warp_field.def_property_readonly("nodes", [](const WarpField& self) { return self.nodes.object; });
 	graph_warp_field.def_property_readonly("node_rotations", [](const WarpField& self) { return self.node_rotations.object; });
 	graph_warp_field.def_property_readonly("node_translations", [](const WarpField& self) { return self.node_translations.object; });
-	graph_warp_field.def_property_readonly("node_coverage_weights", [](const WarpField& self) -> py::object {
-		return self.node_coverage_weights.defined() ? self.node_coverage_weights.object : py::none();
-	});
+	graph_warp_field.def_property("node_coverage_weights",
+	                              [](const WarpField& self) -> py::object { return self.node_coverage_weights.defined() ? self.node_coverage_weights.object : py::none(); },
+	                              [](WarpField& self, const py::object& weights) {
+		                              Dev w = as_cuda(weights, Dtype::Float32);
+		                              if (w.numel() != self.node_count()) log_error("node_coverage_weights must have one entry per node");
+		                              self.node_coverage_weights = w;
+	                              });
 	graph_warp_field.def_readonly("node_coverage", &WarpField::node_coverage);
 	graph_warp_field.def_readonly("anchor_count", &WarpField::anchor_count);
 	graph_warp_field.def_readonly("minimum_valid_anchor_count", &WarpField::minimum_valid_anchor_count);
@@ -256,6 +267,7 @@ void bind_geometry(py::module_& m) {
 	hierarchical.def_property_readonly("edge_layer_indices", [](const H& self) { return self.edge_layer_indices.object; });
 	hierarchical.def_property_readonly("layer_decimation_radii", [](const H& self) { return self.layer_decimation_radii.object; });
 	hierarchical.def_property_readonly("node_indices", [](const H& self) { return self.node_indices.object; });
+	hierarchical.def_readonly("_identity_order", &H::identity_order);
 	hierarchical.def_readonly("first_layer_node_count", &H::first_layer_node_count);
 	hierarchical.def_readonly("layer_node_counts", &H::layer_node_counts);
 

@@ -47,7 +47,8 @@ def _dense(diag, wing, coords, cu, cuc):
 
 
 @pytest.mark.parametrize("n_stem,n_corner,degree,cu", [(208, 41, 4, False), (16, 4, 2, False), (30, 8, 3, True), (5, 0, 0, False), (0, 7, 0, True),
-                                                       (300, 64, 4, False), (60, 130, 3, True)])
+                                                       (300, 64, 4, False), (60, 130, 3, True), (300, 200, 4, False), (120, 300, 3, True),
+                                                       (40, 43, 3, False), (10, 75, 2, True)])
 def test_arrowhead_solver(nnrt, oracle, n_stem, n_corner, degree, cu):
     """Shapes of the reference's only solver fixture (249 blocks: stem 208, corner 41; cpp/tests/test_block_sparse_arrowhead_solver.cpp:33-35)
     plus degenerate ones and two corners too large for one SM (384 and 780 unknowns: the multi-kernel blocked factorisation);

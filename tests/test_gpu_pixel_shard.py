@@ -23,7 +23,8 @@ def _field(nnrt, s):
                                         G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
 
 
-def test_two_bands_on_one_gpu_equal_whole_image(nnrt, oracle):
+def test_two_bands_on_one_gpu_equal_whole_image(nnrt_mirror, oracle):
+    nnrt = nnrt_mirror  # drives the split-iteration C ABI through the ctypes fitter handle
     """Rank 0's and rank 1's bands are run one after the other through the split-iteration C ABI with the accumulators summed in
     between (int64 words): J^T J / J^T r and the update must equal the unsharded iteration exactly."""
     from dynamicfuion_python_b200 import _lib, pixel_shard
