@@ -382,6 +382,21 @@ __global__ void __launch_bounds__(kClusterThreads * kGroups) corner_cluster_fact
 	}
 	cluster_barrier();
 	NNRT_CLUSTER_STAMP(0);
+#ifdef NNRT_CLUSTER_TIMING
+	if (threadIdx.x == 0) {  // latency probes: a value another CTA just wrote, the same again, an untouched line, a line of the same row
+		long long t0 = clock64();
+		float v = __ldcg(S + 1 * n + 0);
+		long long t1 = clock64() + (v == 12345.f ? 1 : 0);
+		v = __ldcg(S + 1 * n + 0);
+		long long t2 = clock64() + (v == 12345.f ? 1 : 0);
+		v = __ldcg(S + (n / 2) * n + 3);
+		long long t3 = clock64() + (v == 12345.f ? 1 : 0);
+		v = __ldcg(S + 1 * n + 1);
+		long long t4 = clock64() + (v == 12345.f ? 1 : 0);
+		g_cluster_clock[rank * 16 + 12] = t1 - t0; g_cluster_clock[rank * 16 + 13] = t2 - t1; g_cluster_clock[rank * 16 + 14] = t3 - t2; g_cluster_clock[rank * 16 + 15] = t4 - t3;
+		t_phase = clock64();
+	}
+#endif
 	for (int j0 = 0; j0 < n; j0 += kPanel) {
 		const int nb = min(kPanel, n - j0), first = j0 + nb, step = j0 / kPanel;
 		// ---- A: rows below the diagonal block (and the right-hand side row) times inv(L_jj)^T
