@@ -83,5 +83,6 @@ void bind_core(py::module_& m);
 void bind_geometry(py::module_& m);
 void bind_rendering(py::module_& m);
 void bind_alignment(py::module_& m);
+void bind_io(py::module_& m);
 
 }  // namespace nnrt

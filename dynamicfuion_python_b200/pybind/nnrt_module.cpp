@@ -14,4 +14,6 @@ PYBIND11_MODULE(nnrt, m) {
 	nnrt::bind_rendering(rendering);
 	py::module_ alignment = m.def_submodule("alignment", "Dense-depth mesh-to-image fitter.");
 	nnrt::bind_alignment(alignment);
+	py::module_ io = m.def_submodule("io", "Tensor files in the reference's binary format.");
+	nnrt::bind_io(io);
 }
