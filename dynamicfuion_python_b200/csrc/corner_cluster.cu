@@ -29,11 +29,12 @@ constexpr int kGroups = 2;
 constexpr int kLd = kPanel + 4;  // shared rows of 36 floats: 16-byte aligned for 128-bit loads, conflict-free for the fragment reads
 
 #ifdef NNRT_CLUSTER_TIMING  // developer harness (tools/corner_cluster_bench.cu): cycles per phase, per CTA rank
+__shared__ long long s_cluster_clock[16];  // accumulated in shared memory (a global read-modify-write per stamp costs 0.4 us itself)
 #define NNRT_CLUSTER_STAMP(slot)                                                     \
 	do {                                                                             \
 		if (threadIdx.x == 0) {                                                      \
 			const long long now = clock64();                                         \
-			g_cluster_clock[rank * 16 + (slot)] += now - t_phase;                     \
+			s_cluster_clock[slot] += now - t_phase;                                  \
 			t_phase = now;                                                           \
 		}                                                                            \
 	} while (0)
@@ -294,9 +295,13 @@ struct alignas(16) ClusterShared {
 // inv(L_jj) of the factored diagonal block at (j0, j0): strict lower part from the block's upper triangle (where the owner left its
 // transpose), diagonal as the reciprocal of the factor's diagonal; identity beyond nb.
 __device__ __forceinline__ float load_inverse_entry(const float* __restrict__ S, int n, int j0, int nb, int r, int c) {
-	if (r >= nb || c > r) return 0.f + ((r == c) ? 1.f : 0.f);
-	if (r == c) return 1.f / __ldcg(S + (j0 + r) * n + j0 + r);
-	return __ldcg(S + (j0 + c) * n + j0 + r);
+	// one branch-free load: for r >= c the address (j0 + c, j0 + r) is the diagonal entry itself (r == c) or the transposed inverse
+	// entry above the diagonal (divergent loads would serialise their L2 round trips: measured 1.6 us per call site)
+	const bool stored = r < nb && c <= r;
+	const float v = stored ? __ldcg(S + (j0 + c) * n + j0 + r) : 0.f;
+	const bool diagonal = r == c;
+	const float reciprocal = 1.f / (diagonal && stored ? v : 1.f);  // never divides by the zeros of the unused lanes (slow path of the IEEE division)
+	return diagonal ? reciprocal : v;
 }
 
 // Rows [first, n] x columns [j0, j0 + nb): Y = A inv(L_jj)^T, 64 rows per chunk, chunks dealt round-robin to the CTAs of the cluster.
@@ -368,6 +373,8 @@ __global__ void __launch_bounds__(kClusterThreads * kGroups) corner_cluster_fact
 	const int tid = threadIdx.x & (kClusterThreads - 1), group = threadIdx.x / kClusterThreads;  // group 1 only takes tiles
 	const int rank = (int) cluster_rank(), ctas = (int) cluster_ctas();
 #ifdef NNRT_CLUSTER_TIMING
+	if (threadIdx.x < 16) s_cluster_clock[threadIdx.x] = 0;
+	__syncthreads();
 	long long t_phase = clock64();
 #endif
 	if (rank == 0 && group == 0) {
@@ -382,21 +389,6 @@ __global__ void __launch_bounds__(kClusterThreads * kGroups) corner_cluster_fact
 	}
 	cluster_barrier();
 	NNRT_CLUSTER_STAMP(0);
-#ifdef NNRT_CLUSTER_TIMING
-	if (threadIdx.x == 0) {  // latency probes: a value another CTA just wrote, the same again, an untouched line, a line of the same row
-		long long t0 = clock64();
-		float v = __ldcg(S + 1 * n + 0);
-		long long t1 = clock64() + (v == 12345.f ? 1 : 0);
-		v = __ldcg(S + 1 * n + 0);
-		long long t2 = clock64() + (v == 12345.f ? 1 : 0);
-		v = __ldcg(S + (n / 2) * n + 3);
-		long long t3 = clock64() + (v == 12345.f ? 1 : 0);
-		v = __ldcg(S + 1 * n + 1);
-		long long t4 = clock64() + (v == 12345.f ? 1 : 0);
-		g_cluster_clock[rank * 16 + 12] = t1 - t0; g_cluster_clock[rank * 16 + 13] = t2 - t1; g_cluster_clock[rank * 16 + 14] = t3 - t2; g_cluster_clock[rank * 16 + 15] = t4 - t3;
-		t_phase = clock64();
-	}
-#endif
 	for (int j0 = 0; j0 < n; j0 += kPanel) {
 		const int nb = min(kPanel, n - j0), first = j0 + nb, step = j0 / kPanel;
 		// ---- A: rows below the diagonal block (and the right-hand side row) times inv(L_jj)^T
@@ -466,6 +458,10 @@ __global__ void __launch_bounds__(kClusterThreads * kGroups) corner_cluster_fact
 		cluster_barrier();
 		NNRT_CLUSTER_STAMP(5);
 	}
+#ifdef NNRT_CLUSTER_TIMING
+	if (threadIdx.x == 0)
+		for (int k = 0; k < 16; k++) g_cluster_clock[rank * 16 + k] += s_cluster_clock[k];
+#endif
 }
 
 // Back substitution L^T x = y with the published block inverses, then the stem back substitution and the node update: one CTA of 1024
@@ -485,9 +481,9 @@ __global__ void __launch_bounds__(kFinishThreads) corner_cluster_finish_kernel(A
 		const int nb = min(kPanel, n - j0);
 		{
 			const int c = tid >> 5, r = tid & 31;  // 1024 threads: one entry of the inverse each (lane = row: contiguous in memory)
-			float v = r == c ? 1.f : 0.f;
-			if (r < nb && c <= r) v = r == c ? 1.f / S[(j0 + r) * n + j0 + r] : S[(j0 + c) * n + j0 + r];
-			Linv[r][c] = v;
+			const bool stored = r < nb && c <= r;
+			const float v = stored ? S[(j0 + c) * n + j0 + r] : 0.f;  // diagonal of L for r == c, transposed inverse above it otherwise
+			Linv[r][c] = r == c ? 1.f / (stored ? v : 1.f) : v;
 		}
 		// this thread's column k of the rows of the block, for every pass over k < j0
 		float l[kPanel];

@@ -52,6 +52,5 @@ int main(int argc, char** argv) {
 	long long ph[256]; cudaMemcpyFromSymbol(ph, g_cluster_clock, sizeof(ph));
 	const char* names[] = {"prologue", "substitute", "barrier 1", "owner store", "tiles", "barrier 2", "owner update", "owner factor", "sub:B", "sub:A+wait", "sub:mma", "sub:store"};
 	for (int r = 0; r < 16; r++) { printf("rank %2d:", r); for (int k = 0; k < 12; k++) printf(" %s %6.1f", names[k], ph[r * 16 + k] / (double) reps / 1965.0); printf("\n"); }
-	for (int r = 0; r < 16; r += 5) printf("rank %d load probes (cycles): written-by-rank-0 %lld, again %lld, untouched %lld, neighbour %lld\n", r, ph[r * 16 + 12], ph[r * 16 + 13], ph[r * 16 + 14], ph[r * 16 + 15]);
 	return 0;
 }
