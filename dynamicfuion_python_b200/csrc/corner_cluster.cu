@@ -54,16 +54,20 @@ __device__ __forceinline__ unsigned cluster_ctas() {
 }
 // barrier of one 256-thread group of the CTA (named barrier 1 + group): the two groups run different tiles at the same time
 __device__ __forceinline__ void group_sync(int group) { asm volatile("bar.sync %0, %1;" ::"r"(group + 1), "r"(kClusterThreads) : "memory"); }
+// Every cross-CTA read in this kernel bypasses L1 (ld.global.cg), so the L1 invalidation of an acquiring cluster barrier is not needed
+// (measured: no difference): the L2 traffic is ordered with explicit fences around a relaxed barrier. Arrive and wait are separate so the
+// owner of the next panel can arrive early and keep working.
+__device__ __forceinline__ void cluster_arrive() {
+	__threadfence();
+	asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait() {
+	asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+	__threadfence();
+}
 __device__ __forceinline__ void cluster_barrier() {
-#ifdef NNRT_CLUSTER_ACQUIRE_BARRIER
-	asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-#else
-	// every cross-CTA read in this kernel bypasses L1 (ld.global.cg), so the L1 invalidation an acquiring cluster barrier performs is
-	// not needed: order the L2 traffic with explicit fences around a relaxed barrier
-	__threadfence();
-	asm volatile("barrier.cluster.arrive.relaxed.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
-	__threadfence();
-#endif
+	cluster_arrive();
+	cluster_wait();
 }
 
 // row r of the augmented system: rows < n live in S, row n is the right-hand side (n * n < 2^31: 32-bit offsets)
@@ -304,16 +308,12 @@ __device__ __forceinline__ float load_inverse_entry(const float* __restrict__ S,
 	return diagonal ? reciprocal : v;
 }
 
-// Rows [first, n] x columns [j0, j0 + nb): Y = A inv(L_jj)^T, 64 rows per chunk, chunks dealt round-robin to the CTAs of the cluster.
-__device__ __noinline__ void substitute_chunks(float* __restrict__ S, float* __restrict__ rhs, int n, int j0, int nb, int first, int rank, int ctas,
-                                               ClusterShared& sh, int tid
-#ifdef NNRT_CLUSTER_TIMING
-                                               , long long& t_phase
-#endif
-) {
+// Rows [row_begin, row_end) x columns [j0, j0 + nb): Y = A inv(L_jj)^T, 64 rows per chunk; this caller takes chunks part, part + parts, ...
+__device__ __noinline__ void substitute_rows(float* __restrict__ S, float* __restrict__ rhs, int n, int j0, int nb, int row_begin, int row_end, int part,
+                                             int parts, ClusterShared& sh, int tid) {
 	const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
-	const int chunks = (n + 1 - first + kTrail - 1) / kTrail;
-	if (rank >= chunks) return;
+	const int chunks = (row_end - row_begin + kTrail - 1) / kTrail;
+	if (part >= chunks) return;
 	// column operand: Bt[j][k] = Linv(j, k) (Y(i, j) = sum_k A(i, k) Linv(j, k))
 	{
 		float entry[kPanel / 8];  // all four loads in flight before the first is used
@@ -322,31 +322,28 @@ __device__ __noinline__ void substitute_chunks(float* __restrict__ S, float* __r
 #pragma unroll
 		for (int pass = 0; pass < kPanel / 8; pass++) sh.stage[0].bt[lane][pass * 8 + warp] = entry[pass];
 	}
-	NNRT_CLUSTER_STAMP(8);
 #pragma unroll 1
-	for (int chunk = rank; chunk < chunks; chunk += ctas) {
-		const int row0 = first + chunk * kTrail;
+	for (int chunk = part; chunk < chunks; chunk += parts) {
+		const int row0 = row_begin + chunk * kTrail;
 		{
 			float va[kTrail / 8];
 #pragma unroll
 			for (int pass = 0; pass < kTrail / 8; pass++) {
 				const int i = row0 + pass * 8 + warp;
-				va[pass] = (i <= n && lane < nb) ? __ldcg(augmented(S, rhs, n, i) + j0 + lane) : 0.f;
+				va[pass] = (i < row_end && lane < nb) ? __ldcg(augmented(S, rhs, n, i) + j0 + lane) : 0.f;
 			}
 #pragma unroll
 			for (int pass = 0; pass < kTrail / 8; pass++) sh.stage[0].a[pass * 8 + warp][lane] = va[pass];
 		}
 		group_sync(0);
-		NNRT_CLUSTER_STAMP(9);
 		// warp w: rows [16 (w % 4), +16) x columns [16 (w / 4), +16)
 		const int wr = (warp & 3) * 16, wc = (warp >> 2) * 16;
 		float acc[2][4] = {};
 		warp_mma_32<2>(sh.stage[0], wr, wc, g, t, acc);
-		NNRT_CLUSTER_STAMP(10);
 #pragma unroll
 		for (int half = 0; half < 2; half++) {
 			const int i = row0 + wr + g + half * 8;
-			if (i > n) continue;
+			if (i >= row_end) continue;
 			float* row = augmented(S, rhs, n, i) + j0 + wc + 2 * t;
 #pragma unroll
 			for (int nbk = 0; nbk < 2; nbk++)
@@ -355,7 +352,6 @@ __device__ __noinline__ void substitute_chunks(float* __restrict__ S, float* __r
 					if (wc + nbk * 8 + 2 * t + e < nb) row[nbk * 8 + e] = acc[nbk][half * 2 + e];
 		}
 		group_sync(0);
-		NNRT_CLUSTER_STAMP(11);
 	}
 }
 
@@ -391,25 +387,20 @@ __global__ void __launch_bounds__(kClusterThreads * kGroups) corner_cluster_fact
 	NNRT_CLUSTER_STAMP(0);
 	for (int j0 = 0; j0 < n; j0 += kPanel) {
 		const int nb = min(kPanel, n - j0), first = j0 + nb, step = j0 / kPanel;
-		// ---- A: rows below the diagonal block (and the right-hand side row) times inv(L_jj)^T
-		if (group == 0) {
-#ifdef NNRT_CLUSTER_TIMING
-			substitute_chunks(S, rhs, n, j0, nb, first, rank, ctas, sh, tid, t_phase);
-#else
-			substitute_chunks(S, rhs, n, j0, nb, first, rank, ctas, sh, tid);
-#endif
-		}
-		NNRT_CLUSTER_STAMP(1);
-		cluster_barrier();
-		NNRT_CLUSTER_STAMP(2);
-		if (first >= n) break;  // only the right-hand side row was left: nothing to update
-		// ---- B: rank-nb update of the trailing matrix; the owner of the next panel does the next diagonal block, factors and inverts it
-		const int nb1 = min(kPanel, n - first);
-		const int owner = (step + 1) % ctas;
-		const int tile_rows = (n + 1 - first + kTrail - 1) / kTrail, tiles = tile_rows * (tile_rows + 1) / 2;
-		const bool owner_works_tiles = ctas == 1;
-		if (rank == owner && group == 0) {
-			// P = L[first .. first + nb1, j0 .. j0 + nb] (staged in T's neighbour: the stage area is free here); D = A[next block] - P P^T
+		const bool has_next = first < n;
+		const int nb1 = has_next ? min(kPanel, n - first) : 0;
+		const int owner = (step + 1) % ctas;                 // of panel j + 1
+		const int worker = (rank - owner - 1 + ctas) % ctas;  // position among the other CTAs
+		const bool lone = ctas == 1;
+		// ---- A: rows below the diagonal block (and the right-hand side row) times inv(L_jj)^T. The owner of panel j + 1 takes the nb1 rows
+		// of its diagonal block, arrives at barrier 1 as soon as they are written and runs ahead: next diagonal block, factor, inverse,
+		// publish — the dependency chain of the factorisation — while the others substitute the remaining rows and update the tiles.
+		if (group == 0 && rank == owner && has_next) {
+			substitute_rows(S, rhs, n, j0, nb, first, first + nb1, 0, 1, sh, tid);
+			if (lone) substitute_rows(S, rhs, n, j0, nb, first + nb1, n + 1, 0, 1, sh, tid);
+			NNRT_CLUSTER_STAMP(1);
+			cluster_arrive();
+			// P = L[first .. first + nb1, j0 .. j0 + nb] (this CTA's own writes); D = A[next block] - P P^T on the lower triangle
 			float (*P)[kLd] = sh.stage[0].a;
 #pragma unroll 4
 			for (int idx = tid; idx < kPanel * kPanel; idx += kClusterThreads) {
@@ -439,12 +430,25 @@ __global__ void __launch_bounds__(kClusterThreads * kGroups) corner_cluster_fact
 			publish_block(S, n, first, nb1, sh, tid);
 			group_sync(0);
 			NNRT_CLUSTER_STAMP(3);
+			cluster_wait();
+		} else {
+			if (group == 0 && !has_next) {
+				if (rank == 0) substitute_rows(S, rhs, n, j0, nb, first, n + 1, 0, 1, sh, tid);  // only the right-hand side row is left
+			} else if (group == 0) {
+				substitute_rows(S, rhs, n, j0, nb, first + nb1, n + 1, worker, ctas - 1, sh, tid);
+			}
+			NNRT_CLUSTER_STAMP(1);
+			cluster_arrive();
+			cluster_wait();
 		}
+		NNRT_CLUSTER_STAMP(2);
+		if (!has_next) break;
+		// ---- B: rank-nb update of the trailing matrix (the next diagonal block is the owner's)
 		{
+			const int tile_rows = (n + 1 - first + kTrail - 1) / kTrail, tiles = tile_rows * (tile_rows + 1) / 2;
 			// tiles are dealt to (CTA, group) units: two per worker CTA, one (group 1) on the owner; a lone CTA works them after the factor
-			const int worker = (rank - owner - 1 + ctas) % ctas;
-			const int units = owner_works_tiles ? kGroups : kGroups * (ctas - 1) + 1;
-			const int unit = owner_works_tiles ? group : (rank == owner ? (group == 1 ? kGroups * (ctas - 1) : -1) : worker * kGroups + group);
+			const int units = lone ? kGroups : kGroups * (ctas - 1) + 1;
+			const int unit = lone ? group : (rank == owner ? (group == 1 ? kGroups * (ctas - 1) : -1) : worker * kGroups + group);
 #pragma unroll 1
 			for (int tile = unit < 0 ? tiles : unit; tile < tiles; tile += units) {
 				int a = (int) ((sqrtf(8.f * (float) tile + 1.f) - 1.f) * 0.5f);

@@ -169,6 +169,15 @@ class DeformableMeshToImageFitter:
         fit_to_image(warp_field, canonical_mesh, reference_color_image, reference_point_cloud, reference_point_mask, intrinsic_matrix,
         extrinsic_matrix, rendering_image_size). The colour image is unused by the reference beyond its size and may be None."""
         names = ["reference_color_image", "reference", "reference_mask", "intrinsic_matrix", "extrinsic_matrix", "last"]
+        rgbd = kwargs.pop("reference_image", None)
+        if rgbd is None and args and (hasattr(args[0], "depth") or (isinstance(args[0], (tuple, list)) and len(args[0]) == 2 and len(args) <= 5)):
+            rgbd, args = args[0], args[1:]  # RGB-D overload (.cpp:316-329): reference_image, reference_image_mask, K, extrinsics, depth_scale
+            names = names[2:]
+        if rgbd is not None:
+            color, depth = (rgbd.color, rgbd.depth) if hasattr(rgbd, "depth") else rgbd
+            if names[0] == "reference_color_image":  # passed by keyword: the remaining positionals start at the mask
+                names = names[2:]
+            kwargs.update(reference_color_image=color, reference_depth_image=depth)
         vals = dict(zip(names, args))
         vals.update(kwargs)
         ref = vals.get("reference", vals.get("reference_depth_image", vals.get("reference_point_cloud")))

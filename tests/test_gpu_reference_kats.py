@@ -272,3 +272,32 @@ def test_arap_term_per_edge(nnrt, oracle, fixed_coverage, huber):
     assert np.array_equal(_np(out["upper_wing_blocks"]), wing)
     assert np.array_equal(_np(out["hessian_diagonal_blocks"]), diag)
     assert np.array_equal(_np(out["negative_gradient"]), g)
+
+
+def test_three_fit_to_image_overloads_agree(nnrt, oracle, kats):
+    """FitToImage's RGB-D overload forwards to the depth-image overload, which unprojects and forwards to the point-cloud overload
+    (DeformableMeshToImageFitter.cpp:278-329): the three must leave the warp field in the same state, bit for bit."""
+    import types
+    scenario, angle, mode, iterations, _, _, lm = fitter_case(kats, _CASES[0])
+    s = reference_fitter_scenario(oracle, kats, scenario, angle)
+    G, A = nnrt.geometry, nnrt.alignment
+    mesh = (s["positions"], s["normals"], s["triangles"])
+    color = np.zeros((s["height"], s["width"], 3), np.uint8)
+    results = []
+    for call in ("rgbd_object", "rgbd_pair", "depth", "points"):
+        wf = G.HierarchicalGraphWarpField(s["nodes"], s["node_coverage"], False, s["anchor_count"], 0, G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 1)
+        fitter = A.DeformableMeshToImageFitter(iterations, [A.IterationMode(mode)], 1e-6, True, 10.0, False, 0.01, lm)
+        if call == "rgbd_object":  # anything with .color / .depth, like open3d.t.geometry.RGBDImage
+            fitter.fit_to_image(wf, mesh, types.SimpleNamespace(color=color, depth=s["depth"]), s["depth_mask"], s["K"], np.eye(4), 1.0)
+        elif call == "rgbd_pair":
+            fitter.fit_to_image(wf, mesh, (color, s["depth"]), s["depth_mask"], s["K"], np.eye(4), 1.0)
+        elif call == "depth":
+            fitter.fit_to_image(wf, mesh, color, s["depth"], s["depth_mask"], s["K"], np.eye(4), 1.0)
+        else:
+            fitter.fit_to_image(wf, mesh, color, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]))
+        fitter.check_status()
+        results.append((_np(wf.get_node_rotations()), _np(wf.get_node_translations())))
+    for R, t in results[1:3]:
+        assert np.array_equal(R, results[0][0]) and np.array_equal(t, results[0][1])
+    # the point-cloud overload gets the oracle's unprojection instead of the device's: equal up to that
+    np.testing.assert_allclose(results[3][1], results[0][1], rtol=0, atol=1e-6)
