@@ -53,9 +53,10 @@ public:
 		Dev points = as_cuda(points_object, Dtype::Float32);
 		const int height = (int) rendering_image_size[0], width = (int) rendering_image_size[1];
 		if (points.numel() != (int64_t) height * width * 3) log_error("reference point cloud must hold one point per pixel of the rendering image, got " + points.shape_string());
+		stream = current_stream();
 		set_model(warp_field, canonical_mesh, height, width, anchors, anchor_weights);
 		Dev mask = mask_or_none(reference_point_mask, (int64_t) height * width);
-		check(nnrt_b200_fitter_set_reference_points(handle, points.data<float>(), mask.defined() ? mask.data<uint8_t>() : nullptr, current_stream()));
+		check(nnrt_b200_fitter_set_reference_points(handle, points.data<float>(), mask.defined() ? mask.data<uint8_t>() : nullptr, stream));
 		fit(warp_field, intrinsic_matrix, extrinsic_matrix, iteration_count);
 		keep_reference = {points.object, mask.object};
 	}
@@ -78,11 +79,12 @@ public:
 			depth = as_cuda(depth_object, Dtype::Float32);
 		}
 		const int height = (int) depth.size(0), width = (int) depth.size(1);
+		stream = current_stream();
 		set_model(warp_field, canonical_mesh, height, width, anchors, anchor_weights);
 		Dev mask = mask_or_none(reference_image_mask, (int64_t) height * width);
 		const std::vector<double> K = host_matrix(intrinsic_matrix, 3, 3, false);
 		check(nnrt_b200_fitter_set_reference_depth(handle, depth.pointer, depth_code, mask.defined() ? mask.data<uint8_t>() : nullptr, depth_scale, K.data(),
-		                                           current_stream()));
+		                                           stream));
 		fit(warp_field, intrinsic_matrix, extrinsic_matrix, iteration_count);
 		keep_reference = {depth.object, mask.object};
 	}
@@ -140,7 +142,9 @@ private:
 	}
 	static Dev mask_or_none(const py::handle& mask, int64_t pixel_count) {
 		if (mask.is_none()) return Dev{};
-		Dev m = as_cuda(to_torch(mask).attr("reshape")(-1), Dtype::UInt8);
+		py::object tensor = to_torch(mask);
+		if (tensor.attr("dim")().cast<int>() != 1) tensor = tensor.attr("reshape")(-1);
+		Dev m = as_cuda(tensor, Dtype::UInt8);
 		if (m.numel() != pixel_count) log_error("reference mask must have one entry per pixel, got " + m.shape_string());
 		return m;
 	}
@@ -151,6 +155,7 @@ private:
 		                              (int32_t) wanted[6], &handle));
 		shape = wanted;
 		graph_key.clear();
+		mesh_key.clear();
 		std::vector<int32_t> modes;
 		for (IterationMode m : iteration_mode_sequence) modes.push_back((int32_t) m);
 		check(nnrt_b200_fitter_set_iteration_modes(handle, modes.data(), (int32_t) modes.size()));
@@ -207,26 +212,37 @@ private:
 		if (key != graph_key) {
 			check(nnrt_b200_fitter_set_graph(handle, warp_field.nodes.data<float>(), e > 0 ? edges.data<int32_t>() : nullptr, (int32_t) base,
 			                                 edge_layers.defined() ? edge_layers.data<int8_t>() : nullptr, radii.defined() ? radii.data<float>() : nullptr,
-			                                 layer_count, coverage_weights.defined() ? coverage_weights.data<float>() : nullptr, current_stream()));
+			                                 layer_count, coverage_weights.defined() ? coverage_weights.data<float>() : nullptr, stream));
 			graph_key = key;
 			keep_graph = {warp_field.nodes.object, edges.object, edge_layers.object, radii.object, coverage_weights.object};
 		}
-		check(nnrt_b200_fitter_set_mesh(handle, mesh.positions.data<float>(), mesh.normals.data<float>(), mesh.triangles.data<int64_t>(),
-		                                anchors.data<int32_t>(), weights.data<float>(), current_stream()));
-		keep_mesh = {mesh.positions.object, mesh.normals.object, mesh.triangles.object, anchors.object, weights.object};
+		// the canonical mesh is re-laid out into the workspace only when one of its tensors was replaced or written to
+		std::vector<int64_t> mesh_identity;
+		append_key(mesh_identity, mesh.positions);
+		append_key(mesh_identity, mesh.normals);
+		append_key(mesh_identity, mesh.triangles);
+		append_key(mesh_identity, anchors);
+		append_key(mesh_identity, weights);
+		if (mesh_identity != mesh_key) {
+			check(nnrt_b200_fitter_set_mesh(handle, mesh.positions.data<float>(), mesh.normals.data<float>(), mesh.triangles.data<int64_t>(),
+			                                anchors.data<int32_t>(), weights.data<float>(), stream));
+			mesh_key = mesh_identity;
+			keep_mesh = {mesh.positions.object, mesh.normals.object, mesh.triangles.object, anchors.object, weights.object};
+		}
 	}
 
 	void fit(WarpField& warp_field, const py::handle& intrinsic_matrix, const py::handle& extrinsic_matrix, int iteration_count) {
 		const std::vector<double> K = host_matrix(intrinsic_matrix, 3, 3, false), extrinsics = host_matrix(extrinsic_matrix, 4, 4, true);
 		const int iterations = iteration_count > 0 ? iteration_count : max_iteration_count;
 		check(nnrt_b200_fitter_fit(handle, warp_field.node_rotations.data<float>(), warp_field.node_translations.data<float>(), K.data(), extrinsics.data(),
-		                           iterations, current_stream()));
+		                           iterations, stream));
 	}
 
 	nnrt_b200_fitter_options options;
 	nnrt_b200_fitter* handle = nullptr;
 	std::array<int64_t, 7> shape{};
-	std::vector<int64_t> graph_key;
+	std::vector<int64_t> graph_key, mesh_key;
+	void* stream = nullptr;  // torch's current stream, looked up once per fit_to_image call
 	std::vector<py::object> keep_graph, keep_mesh, keep_reference;  // inputs of work still queued on the stream
 };
 

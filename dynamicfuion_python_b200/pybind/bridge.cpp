@@ -112,7 +112,11 @@ std::vector<double> host_matrix(const py::handle& value, int rows, int cols, boo
 		return m;
 	}
 	Torch& t = Torch::get();
-	py::object host = to_torch(value).attr("detach")().attr("to")(py::arg("device") = "cpu", py::arg("dtype") = t.dtype(Dtype::Float64)).attr("contiguous")();
+	py::object host = to_torch(value);
+	// the common case on the hot path (a float64 CPU tensor, as the reference API prescribes) is read in place
+	if (host.attr("is_cuda").cast<bool>() || !has_dtype(host, t.dtype(Dtype::Float64)) || !host.attr("is_contiguous")().cast<bool>() ||
+	    host.attr("requires_grad").cast<bool>())
+		host = host.attr("detach")().attr("to")(py::arg("device") = "cpu", py::arg("dtype") = t.dtype(Dtype::Float64)).attr("contiguous")();
 	const std::vector<int64_t> shape = shape_of(host);
 	if (shape.size() != 2 || shape[0] != rows || shape[1] != cols) {
 		Dev d;

@@ -1,4 +1,6 @@
 """GPU parity of the arrowhead solver and of whole GN iterations against the CPU oracle."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -51,8 +53,8 @@ def _dense(diag, wing, coords, cu, cuc):
                                                        (40, 43, 3, False), (10, 75, 2, True)])
 def test_arrowhead_solver(nnrt, oracle, n_stem, n_corner, degree, cu):
     """Shapes of the reference's only solver fixture (249 blocks: stem 208, corner 41; cpp/tests/test_block_sparse_arrowhead_solver.cpp:33-35)
-    plus degenerate ones and two corners too large for one SM (384 and 780 unknowns: the multi-kernel blocked factorisation);
-    checked against the oracle and a dense float64 solve with the reference's tolerance AllClose(1e-4, 1e-5)."""
+    plus degenerate ones and corners too large for one SM (258, 384, 450, 780, 1200 and 1800 unknowns: the thread-block-cluster
+    factorisation of csrc/corner_cluster.cu, with partial last panels); checked against the oracle and a dense float64 solve with the reference's tolerance AllClose(1e-4, 1e-5)."""
     rng = np.random.default_rng(11)
     diag, wing, coords, cub, cuc, b = _random_arrowhead(rng, n_stem, n_corner, degree, cu)
     L = nnrt.core.linalg
@@ -129,6 +131,27 @@ def test_single_iteration_parity(nnrt, oracle, config, h, w):
     assert np.abs(_np(d["deltas"]) - ref["deltas"][0]).max() <= 1e-3 * np.abs(ref["deltas"][0]).max()
     np.testing.assert_allclose(_np(wf.node_translations), ref["translations"], rtol=1e-3, atol=1e-6)
     np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
+
+
+@pytest.mark.skipif(bool(os.environ.get("NNRT_B200_SKIP_SLOW_TESTS")), reason="slow (about a minute on the 16-core GPU box: the oracle at 4.45 M triangles)")
+def test_single_iteration_parity_at_c3_size(nnrt_mirror, oracle):
+    """BASELINE.json configs[2] (4.45 M triangles, 1920 x 1080, 1681 + 289 nodes: the cluster corner kernel on 867 unknowns): one GN
+    iteration against the oracle. Face indices and coverage bit-exact, residuals / J^T J / J^T r within 1e-4, deltas within 1e-3."""
+    s = scene_with_target(oracle, "C3", 1080, 1920)
+    ref = oracle_fit(oracle, s, 1)
+    wf, fitter = _gpu_fit(nnrt_mirror, s, 1)
+    d = fitter.diagnostics()
+    assert np.array_equal(_np(d["pixel_face_indices"]), ref["pixel_faces"])
+    assert np.array_equal(_np(d["residual_mask"]), ref["residual_mask"])
+    ok, worst = rel_close(_np(d["residuals"]), ref["residuals"], 1e-4)
+    assert ok, f"residuals {worst}"
+    ok, worst = rel_close(_np(d["hessian_diagonal"]), ref["hessian_diag"][0], 1e-4, floor_scale=1e-3)
+    assert ok, f"J^T J {worst}"
+    ok, worst = rel_close(_np(d["negative_gradient"]), ref["negative_gradient"][0], 1e-4, floor_scale=1e-4)
+    assert ok, f"J^T r {worst}"
+    ok, worst = rel_close(_np(d["deltas"]), ref["deltas"][0], 1e-3, floor_scale=1e-2)
+    assert ok, f"deltas {worst}"
+    assert np.abs(_np(d["deltas"]) - ref["deltas"][0]).max() <= 1e-3 * np.abs(ref["deltas"][0]).max()
 
 
 @pytest.mark.parametrize("config,h,w", [("tinyr", 120, 160), ("C1", 480, 640), ("C1e", 480, 640), ("C2r", 480, 640)])

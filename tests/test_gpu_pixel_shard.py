@@ -23,14 +23,18 @@ def _field(nnrt, s):
                                         G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
 
 
-def test_two_bands_on_one_gpu_equal_whole_image(nnrt_mirror, oracle):
+@pytest.mark.parametrize("config,h,w,bands", [("tinyr", 120, 160, 2), ("C2r", 2160, 3840, 2), ("C2r", 2160, 3840, 3)])
+def test_bands_on_one_gpu_equal_whole_image(nnrt_mirror, oracle, config, h, w, bands):
+    """The ranks' bands are run one after the other through the split-iteration C ABI with the accumulators summed in between (int64
+    words): J^T J / J^T r and the update must equal the unsharded iteration exactly. The 3840 x 2160 cases are BASELINE.json configs[3]
+    (the C2 mesh at 4K) split in two and in three uneven bands; their target is rendered on the GPU (the oracle's renderer takes
+    minutes there)."""
     nnrt = nnrt_mirror  # drives the split-iteration C ABI through the ctypes fitter handle
-    """Rank 0's and rank 1's bands are run one after the other through the split-iteration C ABI with the accumulators summed in
-    between (int64 words): J^T J / J^T r and the update must equal the unsharded iteration exactly."""
     from dynamicfuion_python_b200 import _lib, pixel_shard
     from dynamicfuion_python_b200.nnrt import _tensor as T
+    from util import scene_with_gpu_target
     import ctypes as C
-    s = scene_with_target(oracle, "tinyr", 120, 160)
+    s = scene_with_target(oracle, config, h, w) if h <= 480 else scene_with_gpu_target(nnrt, config, h, w)
     mesh = (s["positions"], s["normals"], s["triangles"])
     args = dict(max_iteration_count=1, preconditioning_dampening_factor=s["lm_factor"], arap_term_weight=s["arap_term_weight"])
     call = dict(anchors=s["anchors"], anchor_weights=s["anchor_weights"])
@@ -52,8 +56,8 @@ def test_two_bands_on_one_gpu_equal_whole_image(nnrt_mirror, oracle):
     acc = pixel_shard.DeviceBuffer(pointer, count.value).tensor(R.device)
     total = torch.zeros_like(acc)
     covered = np.zeros((s["height"],), bool)
-    for rank in range(2):
-        begin, end = pixel_shard.pixel_rows(rank, 2, s["height"])
+    for rank in range(bands):
+        begin, end = pixel_shard.pixel_rows(rank, bands, s["height"])
         assert not covered[begin:end].any()
         covered[begin:end] = True
         T.call("nnrt_b200_fitter_set_pixel_rows", fitter._handle, begin, end)

@@ -26,6 +26,26 @@ def scene_with_target(oracle, config, height, width, translation_scale=1.0):
     return s
 
 
+def scene_with_gpu_target(nnrt, config, height, width):
+    """As scene_with_target, with anchors and the target rendered by the CUDA path (already bit-exact against the oracle at test sizes:
+    test_gpu_geometry / test_gpu_raster); for sizes at which the oracle's renderer takes minutes (3840 x 2160)."""
+    import torch
+    s = synthetic.make_scene(config, height, width)
+    G, R = nnrt.geometry.functional, nnrt.rendering
+    anchors, weights = G.compute_anchors_and_weights_euclidean_fixed_node_weight(s["positions"], s["nodes"], 4, 0, s["node_coverage"])
+    warped = G.warp_triangle_mesh((s["positions"], s["normals"], s["triangles"]), s["nodes"], s["rotations_gt"], s["translations_gt"], anchors, weights)
+    fv, mask = R.functional.get_mesh_ndc_face_vertices_and_clip_mask((warped.positions, None, s["triangles"]), s["K"], (height, width), 0.0, 10.0)
+    _, depth, _, _ = R.rasterize_ndc_triangles(fv, mask, (height, width), 0.0, 1, -1, -1, True, False, True)
+    depth = depth[..., 0]
+    # unprojection as PerspectiveProjectionImpl.h:62-150 with depth_scale 1: X = (u - cx) d / fx, Y = (v - cy) d / fy, Z = d
+    K = torch.as_tensor(s["K"], dtype=torch.float32, device=depth.device)
+    v, u = torch.meshgrid(torch.arange(height, device=depth.device, dtype=torch.float32), torch.arange(width, device=depth.device, dtype=torch.float32), indexing="ij")
+    valid = (depth > 0) & (depth < 10.0)
+    points = torch.stack([(u - K[0, 2]) * depth / K[0, 0], (v - K[1, 2]) * depth / K[1, 1], depth], -1) * valid[..., None]
+    s.update(anchors=anchors, anchor_weights=weights, reference_points=points.reshape(-1, 3).contiguous(), reference_mask=valid.reshape(-1), target_depth=depth)
+    return s
+
+
 def oracle_fit(oracle, s, iterations, **kw):
     args = dict(iteration_count=iterations, lm_factor=s["lm_factor"], arap_term_weight=s["arap_term_weight"],
                 edge_layer_indices=s["edge_layer_indices"], layer_radii=s["layer_radii"], parallel=True)
