@@ -58,6 +58,9 @@ _SIGNATURES = {
     "nnrt_b200_invert_triangular_blocks": (C.c_int, [P, I32, I32, I32, P, P]),
     "nnrt_b200_transpose_blocks_in_place": (C.c_int, [P, I64, I32, P]),
     "nnrt_b200_dense_matrix_blocks": (C.c_int, [P, I64, I64, P, P, I64, I32, I32, I32, I32, I32, P]),
+    "nnrt_b200_voxel_block_neighbors": (C.c_int, [P, I64, P, P]),
+    "nnrt_b200_extract_triangle_mesh_prepare": (C.c_int, [I64, P, P, P, I32, I32, F32, P, P, P, P]),
+    "nnrt_b200_extract_triangle_mesh_emit": (C.c_int, [P, I64, P, P, P, I32, F32, P, P, P, P, P, P, P]),
     "nnrt_b200_add_scaled": (C.c_int, [P, P, F32, I64, P, P]),
     "nnrt_b200_fill_identity_rotations": (C.c_int, [P, I64, P]),
     "nnrt_b200_gather_rows": (C.c_int, [P, I64, I32, P, I64, P, P]),

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libnnrt_b200.so")
-SOURCES = ["c_api.cu", "geometry.cu", "warp_field_build.cu", "mesh_normals.cu", "tsdf.cu", "raster.cu", "fitter_kernels.cu", "assemble_kernel.cu", "solver_kernels.cu", "corner_cluster.cu", "linalg_api.cu", "linalg_blocks.cu", "assembly_stages.cu", "node_store.cu", "fitter.cu"]
+SOURCES = ["c_api.cu", "geometry.cu", "warp_field_build.cu", "mesh_normals.cu", "tsdf.cu", "raster.cu", "fitter_kernels.cu", "assemble_kernel.cu", "solver_kernels.cu", "corner_cluster.cu", "linalg_api.cu", "linalg_blocks.cu", "assembly_stages.cu", "node_store.cu", "mesh_extraction.cu", "fitter.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-fmad=false", "-std=c++17", "--extended-lambda",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-DNNRT_B200_BUILD"]
 # Per-file overrides of -fmad=false. Empty on purpose: contraction + fast division in assemble_kernel.cu (-fmad=true -prec-div=false)

@@ -394,3 +394,54 @@ def fast_median_radius_subsample_3d_points(points, radius):
     stage1 = median_grid_subsample_3d_points(pts, cell)
     stage2 = median_grid_subsample_3d_points(pts[stage1].contiguous(), cell, _grid_offset=0.5)
     return stage1[stage2]
+
+
+# --- mesh extraction from TSDF voxel blocks (cpp/geometry/VoxelBlockGrid.cpp:461-484 -> Open3D's kernel) ----------
+def voxel_block_neighbors(block_keys):
+    """The block hash behind VoxelBlockGrid::BufferRadiusNeighbors: for block_keys [B,3] int32 the [B,27] int32 indices of the blocks at
+    key + (dx, dy, dz) (slot (dz + 1) * 9 + (dy + 1) * 3 + (dx + 1)), -1 where no such block exists."""
+    keys = T.cuda(block_keys, torch.int32)
+    if keys.dim() != 2 or keys.shape[1] != 3:
+        raise RuntimeError(f"block_keys must have shape [B, 3], got {tuple(keys.shape)}")
+    out = T.empty((keys.shape[0], 27), torch.int32)
+    T.call("nnrt_b200_voxel_block_neighbors", T.ptr(keys), keys.shape[0], T.ptr(out), T.stream())
+    return out
+
+
+def extract_triangle_mesh(block_keys, block_values, voxel_size, weight_threshold=3.0):
+    """VoxelBlockGrid::ExtractTriangleMesh(weight_threshold) on explicit block tensors: block_keys [B,3] int32, block_values a dict with
+    "tsdf" [B,R,R,R] f32, "weight" (f32 or uint16) and optionally "color" [B,R,R,R,3] f32 (0..255). Returns a mesh (positions,
+    normals = normalised TSDF gradients, triangles int64; `.colors` in [0, 1] when colour is given). Vertices and triangles come in
+    (block, voxel, edge) order, reproducibly."""
+    import ctypes as C
+    keys = T.cuda(block_keys, torch.int32)
+    tsdf = T.cuda(block_values["tsdf"], torch.float32)
+    if tsdf.dim() != 4 or tsdf.shape[1] != tsdf.shape[2] or tsdf.shape[1] != tsdf.shape[3] or tsdf.shape[0] != keys.shape[0]:
+        raise RuntimeError(f"tsdf must have shape [B,R,R,R] with one block per key, got {tuple(tsdf.shape)}")
+    weight = T.to_torch(block_values["weight"])
+    if weight.dtype in (torch.uint16, torch.int16):
+        weight, weight_code = T.cuda(weight.view(torch.int16) if weight.dtype == torch.uint16 else weight, torch.int16), 1
+    elif weight.dtype == torch.float32:
+        weight, weight_code = T.cuda(weight, torch.float32), 0
+    else:
+        raise RuntimeError("weight voxel attribute must be Float32 or UInt16")
+    if tuple(weight.shape) != tuple(tsdf.shape):
+        raise RuntimeError("weight must have the shape of tsdf")
+    color = None if block_values.get("color") is None else T.cuda(block_values["color"], torch.float32)
+    if color is not None and tuple(color.shape) != tuple(tsdf.shape) + (3,):
+        raise RuntimeError("color must have shape [B,R,R,R,3]")
+    b, r = keys.shape[0], tsdf.shape[1]
+    neighbors = voxel_block_neighbors(keys)
+    structure = T.empty((b * r ** 3, 4), torch.int32)
+    offsets = T.empty((b * r ** 3 + 1,), torch.int32)
+    counts = (C.c_int64 * 2)()
+    T.call("nnrt_b200_extract_triangle_mesh_prepare", b, T.ptr(neighbors), T.ptr(tsdf), T.ptr(weight), weight_code, r, float(weight_threshold),
+           T.ptr(structure), T.ptr(offsets), counts, T.stream())
+    vertices, normals = T.empty((counts[0], 3), torch.float32), T.empty((counts[0], 3), torch.float32)
+    colors = None if color is None else T.empty((counts[0], 3), torch.float32)
+    triangles = T.empty((counts[1], 3), torch.int64)
+    T.call("nnrt_b200_extract_triangle_mesh_emit", T.ptr(keys), b, T.ptr(neighbors), T.ptr(tsdf), T.ptr(color), r, float(voxel_size), T.ptr(structure),
+           T.ptr(offsets), T.ptr(vertices), T.ptr(normals), T.ptr(colors), T.ptr(triangles), T.stream())
+    mesh = T.MeshView((vertices, normals, triangles))
+    mesh.colors = colors
+    return mesh

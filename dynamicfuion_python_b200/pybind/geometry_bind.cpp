@@ -110,6 +110,50 @@ static void bind_functional(py::module_& m) {
 		store_mesh_attribute(mesh_in, "vertex", "normals", normals.object);
 		return normals.object;
 	}, "mesh"_a, "normalized"_a = true);
+
+	// mesh extraction from TSDF voxel blocks (cpp/geometry/VoxelBlockGrid.cpp:461-484 -> Open3D's kernel; csrc/mesh_extraction.cu)
+	m.def("voxel_block_neighbors", [](const py::object& block_keys) {
+		Dev keys = as_cuda(block_keys, Dtype::Int32);
+		if (keys.dim() != 2 || keys.size(1) != 3) log_error("block_keys must have shape [B, 3], got " + keys.shape_string());
+		Dev out = empty({keys.size(0), 27}, Dtype::Int32);
+		check(nnrt_b200_voxel_block_neighbors(keys.data<int32_t>(), keys.size(0), out.data<int32_t>(), current_stream()));
+		return out.object;
+	}, "block_keys"_a);
+	m.def("extract_triangle_mesh", [](const py::object& block_keys, const py::dict& block_values, float voxel_size, float weight_threshold) {
+		Dev keys = as_cuda(block_keys, Dtype::Int32), tsdf = as_cuda(block_values["tsdf"], Dtype::Float32);
+		if (tsdf.dim() != 4 || tsdf.size(1) != tsdf.size(2) || tsdf.size(1) != tsdf.size(3) || tsdf.size(0) != keys.size(0))
+			log_error("tsdf must have shape [B,R,R,R] with one block per key, got " + tsdf.shape_string());
+		py::object weight_tensor = to_torch(block_values["weight"]);
+		Torch& t = Torch::get();
+		int weight_code = 0;
+		Dev weight;
+		if (has_dtype(weight_tensor, t.module.attr("uint16")) || has_dtype(weight_tensor, t.dtype(Dtype::Int16))) {
+			weight = as_cuda(has_dtype(weight_tensor, t.module.attr("uint16")) ? py::object(weight_tensor.attr("view")(t.dtype(Dtype::Int16))) : weight_tensor, Dtype::Int16);
+			weight_code = 1;
+		} else if (has_dtype(weight_tensor, t.dtype(Dtype::Float32))) {
+			weight = as_cuda(weight_tensor, Dtype::Float32);
+		} else {
+			log_error("weight voxel attribute must be Float32 or UInt16");
+		}
+		if (weight.shape != tsdf.shape) log_error("weight must have the shape of tsdf");
+		Dev color;
+		if (block_values.contains("color") && !block_values["color"].is_none()) color = as_cuda(block_values["color"], Dtype::Float32);
+		const int64_t b = keys.size(0), r = tsdf.size(1), voxels = b * r * r * r;
+		void* stream = current_stream();
+		Dev neighbors = empty({b, 27}, Dtype::Int32), structure = empty({voxels, 4}, Dtype::Int32), offsets = empty({voxels + 1}, Dtype::Int32);
+		check(nnrt_b200_voxel_block_neighbors(keys.data<int32_t>(), b, neighbors.data<int32_t>(), stream));
+		int64_t counts[2] = {0, 0};
+		check(nnrt_b200_extract_triangle_mesh_prepare(b, neighbors.data<int32_t>(), tsdf.data<float>(), weight.pointer, weight_code, (int32_t) r, weight_threshold,
+		                                              structure.data<int32_t>(), offsets.data<int32_t>(), counts, stream));
+		Dev vertices = empty({counts[0], 3}, Dtype::Float32), normals = empty({counts[0], 3}, Dtype::Float32), triangles = empty({counts[1], 3}, Dtype::Int64), colors;
+		if (color.defined()) colors = empty({counts[0], 3}, Dtype::Float32);
+		check(nnrt_b200_extract_triangle_mesh_emit(keys.data<int32_t>(), b, neighbors.data<int32_t>(), tsdf.data<float>(), color.defined() ? color.data<float>() : nullptr,
+		                                           (int32_t) r, voxel_size, structure.data<int32_t>(), offsets.data<int32_t>(), vertices.data<float>(),
+		                                           normals.data<float>(), color.defined() ? colors.data<float>() : nullptr, triangles.data<int64_t>(), stream));
+		py::object mesh = make_mesh(vertices, normals, triangles);
+		if (color.defined()) mesh.attr("vertex")["colors"] = colors.object;
+		return mesh;
+	}, "block_keys"_a, "block_values"_a, "voxel_size"_a, "weight_threshold"_a = 3.0f);
 }
 
 void bind_geometry(py::module_& m) {

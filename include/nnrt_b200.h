@@ -367,6 +367,31 @@ int nnrt_b200_boxes_intersecting_surface_mask(const float* boxes, int64_t box_co
                                               int32_t depth_dtype, int32_t image_height, int32_t image_width, float depth_scale,
                                               float depth_max, int32_t stride, float truncation_distance, uint8_t* mask, void* stream);
 
+/* ---- Mesh extraction from TSDF voxel blocks (the canonical mesh the fitter consumes) ----
+ * geometry::VoxelBlockGrid::ExtractTriangleMesh (geometry/VoxelBlockGrid.cpp:461-484) calls Open3D's
+ * t::geometry::kernel::voxel_grid::ExtractTriangleMesh over Open3D's device hash map (Open3D v0.17.0-1fix6008, third party, not in
+ * the reference checkout); both are restated from the published algorithm (csrc/mesh_extraction.cu). Parity unpinned by the reference.
+ *
+ * VoxelBlockGrid::BufferRadiusNeighbors (VoxelBlockGrid.cpp:466-468): the block hash. block_keys [B,3] int32 (block coordinates);
+ * neighbor_indices [B,27] int32: index of the block at key + (dx, dy, dz), slot (dz + 1) * 9 + (dy + 1) * 3 + (dx + 1), -1 where absent
+ * (an open-addressing table over the packed keys is built per call; a key listed twice resolves to its first block). */
+int nnrt_b200_voxel_block_neighbors(const int32_t* block_keys, int64_t block_count, int32_t* neighbor_indices, void* stream);
+/* Marching cubes, first half: cube configuration per voxel, one vertex per sign-change edge that lies on a complete cube (all eight
+ * corners present with weight > weight_threshold), numbered by exclusive scans in (block, voxel, x / y / z edge) order.
+ * tsdf [B,R,R,R] f32 (z, y, x major to minor as Open3D's blocks), weight the same shape (weight_dtype 0 = f32, 1 = uint16).
+ * Caller-allocated: mesh_structure [B*R^3, 4] int32 (vertex id of the voxel's x / y / z edge or < 0, cube configuration),
+ * triangle_offsets [B*R^3 + 1] int32. counts_host[0..1] = vertex and triangle counts (one stream synchronisation). */
+int nnrt_b200_extract_triangle_mesh_prepare(int64_t block_count, const int32_t* neighbor_indices, const float* tsdf, const void* weight,
+                                            int32_t weight_dtype, int32_t block_resolution, float weight_threshold,
+                                            int32_t* mesh_structure, int32_t* triangle_offsets, int64_t* counts_host, void* stream);
+/* Second half: vertices [Nv,3] = voxel_size * (global voxel coordinate + ratio along the edge), ratio = -tsdf_o / (tsdf_e - tsdf_o);
+ * normals [Nv,3] = interpolated central-difference TSDF gradients / (norm + 1e-5); colors [Nv,3] = interpolated color / 255 when
+ * color [B,R^3,3] f32 is given (else both NULL); triangles [Nt,3] int64. vertices / triangles may be NULL to skip that part. */
+int nnrt_b200_extract_triangle_mesh_emit(const int32_t* block_keys, int64_t block_count, const int32_t* neighbor_indices,
+                                         const float* tsdf, const float* color, int32_t block_resolution, float voxel_size,
+                                         const int32_t* mesh_structure, const int32_t* triangle_offsets, float* vertices, float* normals,
+                                         float* colors, int64_t* triangles, void* stream);
+
 /* ---- Node store of the warp field (what the host classes do to node tensors besides the warp) ----
  * WarpField::GetWarpedNodes / TranslateNodes (geometry/WarpField.cpp:89-91,185-187; HierarchicalGraphWarpField.cpp:261-269): out = a + alpha * b. */
 int nnrt_b200_add_scaled(const float* a, const float* b, float alpha, int64_t count, float* out, void* stream);

@@ -657,3 +657,27 @@ def get_sparse_blocks(matrix, block_size, coordinates):
     out = np.empty((co.shape[0], block_size, block_size), np.float32)
     lib().oracle_get_sparse_blocks(_p(m), C.c_int(m.shape[1]), C.c_int(block_size), _p(co), C.c_int(co.shape[0]), _p(out))
     return out
+
+
+def voxel_block_neighbors(block_keys):
+    """VoxelBlockGrid::BufferRadiusNeighbors: [B, 27] indices of the blocks around every block, -1 where absent."""
+    keys = np.ascontiguousarray(block_keys, np.int32)
+    out = np.empty((keys.shape[0], 27), np.int32)
+    lib().oracle_voxel_block_neighbors(_p(keys), C.c_int64(keys.shape[0]), _p(out))
+    return out
+
+
+def extract_triangle_mesh(block_keys, tsdf, weight, color=None, voxel_size=0.01, weight_threshold=3.0):
+    """Open3D's ExtractTriangleMesh over voxel blocks [B,R,R,R]: (vertices, normals, colors or None, triangles)."""
+    keys, tsdf, weight = np.ascontiguousarray(block_keys, np.int32), _f32(tsdf), _f32(weight)
+    R = tsdf.shape[1]
+    col = None if color is None else _f32(color)
+    counts = np.zeros(2, np.int64)
+    null = C.c_void_p(None)
+    args = (_p(keys), C.c_int64(keys.shape[0]), _p(tsdf), _p(weight), null if col is None else _p(col), C.c_int(R), C.c_float(voxel_size), C.c_float(weight_threshold))
+    lib().oracle_extract_triangle_mesh(*args, _p(counts), null, null, null, null)
+    vertices, normals = np.empty((counts[0], 3), np.float32), np.empty((counts[0], 3), np.float32)
+    colors = None if col is None else np.empty((counts[0], 3), np.float32)
+    triangles = np.empty((counts[1], 3), np.int64)
+    lib().oracle_extract_triangle_mesh(*args, _p(counts), _p(vertices), _p(normals), null if colors is None else _p(colors), _p(triangles))
+    return vertices, normals, colors, triangles
