@@ -84,5 +84,6 @@ void bind_geometry(py::module_& m);
 void bind_rendering(py::module_& m);
 void bind_alignment(py::module_& m);
 void bind_io(py::module_& m);
+void bind_geometry_functional_more(py::module_& m);  // geometry_functional_bind.cpp, into nnrt.geometry.functional
 
 }  // namespace nnrt
