@@ -84,6 +84,9 @@ void bind_geometry(py::module_& m);
 void bind_rendering(py::module_& m);
 void bind_alignment(py::module_& m);
 void bind_io(py::module_& m);
+void bind_alignment_functional(py::module_& m);      // alignment_functional_bind.cpp
+void bind_shaders(py::module_& m);                   // FlatEdgeShader / VertexColorShader into nnrt.rendering
+void bind_linalg_blocks(py::module_& m);             // linalg_blocks_bind.cpp, into nnrt.core.linalg
 void bind_geometry_functional_more(py::module_& m);  // geometry_functional_bind.cpp, into nnrt.geometry.functional
 
 }  // namespace nnrt

@@ -133,6 +133,7 @@ struct KdTree {
 void bind_core(py::module_& m) {
 	py::module_ linalg = m.def_submodule("linalg", "Contains additional linear algebra functions not defined in open3d.core or its submodules.");
 	core::linalg::bind(linalg);
+	bind_linalg_blocks(linalg);
 	m.def("matmul3d", [](const py::object& a_in, const py::object& b_in) {
 		Dev a = as_cuda(a_in, Dtype::Float32), b = as_cuda(b_in, Dtype::Float32);
 		if (a.dim() != 3 || b.dim() != 3 || a.size(0) != b.size(0) || a.size(2) != b.size(1))

@@ -12,8 +12,11 @@ PYBIND11_MODULE(nnrt, m) {
 	nnrt::bind_geometry(geometry);
 	py::module_ rendering = m.def_submodule("rendering", "Rasterization.");
 	nnrt::bind_rendering(rendering);
+	nnrt::bind_shaders(rendering);
 	py::module_ alignment = m.def_submodule("alignment", "Dense-depth mesh-to-image fitter.");
 	nnrt::bind_alignment(alignment);
+	py::module_ alignment_functional = alignment.def_submodule("functional", "Un-fused stages of the data term.");
+	nnrt::bind_alignment_functional(alignment_functional);
 	py::module_ io = m.def_submodule("io", "Tensor files in the reference's binary format.");
 	nnrt::bind_io(io);
 }
