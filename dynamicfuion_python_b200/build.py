@@ -63,7 +63,7 @@ def build(force=False, verbose=False):
 
 # ---- pybind11 module `nnrt` (C++ host classes over the C ABI): dynamicfuion_python_b200/pybind/nnrt.<abi>.so ---------------------------
 PYBIND_DIR = os.path.join(HERE, "pybind")
-PYBIND_SOURCES = ["bridge.cpp", "warp_field.cpp", "geometry_bind.cpp", "geometry_functional_bind.cpp", "alignment_bind.cpp", "alignment_functional_bind.cpp", "core_rendering_bind.cpp", "linalg_blocks_bind.cpp", "io_bind.cpp", "nnrt_module.cpp"]
+PYBIND_SOURCES = ["bridge.cpp", "warp_field.cpp", "geometry_bind.cpp", "geometry_functional_bind.cpp", "tsdf_bind.cpp", "alignment_bind.cpp", "alignment_functional_bind.cpp", "core_rendering_bind.cpp", "linalg_blocks_bind.cpp", "io_bind.cpp", "nnrt_module.cpp"]
 
 
 def pybind_module_path():

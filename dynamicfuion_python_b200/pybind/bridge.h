@@ -88,5 +88,6 @@ void bind_alignment_functional(py::module_& m);      // alignment_functional_bin
 void bind_shaders(py::module_& m);                   // FlatEdgeShader / VertexColorShader into nnrt.rendering
 void bind_linalg_blocks(py::module_& m);             // linalg_blocks_bind.cpp, into nnrt.core.linalg
 void bind_geometry_functional_more(py::module_& m);  // geometry_functional_bind.cpp, into nnrt.geometry.functional
+void bind_tsdf(py::module_& m);                      // tsdf_bind.cpp, into nnrt.geometry.functional
 
 }  // namespace nnrt

@@ -318,6 +318,7 @@ void bind_geometry(py::module_& m) {
 	py::module_ functional = m.def_submodule("functional", "Stateless functions on geometry (cpp/pybind/geometry/functional/functional.cpp).");
 	bind_functional(functional);
 	bind_geometry_functional_more(functional);
+	bind_tsdf(functional);
 }
 
 }  // namespace nnrt
