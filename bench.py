@@ -9,7 +9,8 @@ Further legs of the same run, each reported in its own block of the JSON line:
   latency      one sequence alone on the GPU, L2 flushed between frames (ms per GN iteration, the <= 1 ms target)
   population   BASELINE.json configs[4] as stated: a FIXED population of 64 sequences shared by the N GPUs (strong scaling)
   configs      (N = 1) C1 (configs[0]) and C3 (configs[2]) at their stated sizes: ms per iteration, per-stage ms, status, GB/s
-  pixel_shard  (N > 1) configs[3]: one 3840x2160 frame split into row bands over all N ranks, int64 all-reduce per iteration
+  pixel_shard  (N > 1) configs[3]: one 3840x2160 frame, rows dealt in stripes to all N ranks, per-node sums gathered over NVLink peer memory
+               by the consuming kernel (NCCL all-reduce forms timed beside it)
 
   python bench.py --gpus N --steps K --warmup W              our sm_100a path (one process per GPU; frames are sharded, no collective)
   python bench.py --impl reference --gpus N --steps K ...    the reference algorithm's CPU path (oracle restatement, OpenMP, all host threads)
@@ -271,8 +272,9 @@ def config_block(torch, nnrt, dev, flush, config, height, width, frames, peak):
 
 
 def pixel_shard_leg(torch, dist, nnrt, dev, rank, world, frames):
-    """BASELINE.json configs[3]: the C2 mesh and graph fitted to ONE 3840x2160 frame, rows split into one band per rank, the per-node
-    sums all-reduced as int64 once per iteration. Timed with CUDA events (max over ranks) next to the same fit unsharded on one GPU."""
+    """BASELINE.json configs[3]: the C2 mesh and graph fitted to ONE 3840x2160 frame, rows split over the ranks, the per-node sums
+    (int64 fixed-point words) summed over the ranks once per iteration. Timed with CUDA events (max over ranks) next to the same fit
+    unsharded on one GPU, in three forms: bands + NCCL all-reduce, stripes + NCCL, stripes + the reduction fused into the stem kernel."""
     from dynamicfuion_python_b200 import frame_batch
     height, width = 2160, 3840
     ratio = height * width / float(HEIGHT * WIDTH)
@@ -280,17 +282,22 @@ def pixel_shard_leg(torch, dist, nnrt, dev, rank, world, frames):
     def edit(s):  # the data term grows with the pixel count: keep its balance with the ARAP term of the 640x480 scene
         s["arap_term_weight"] *= ratio ** 0.5
     work = Workload(nnrt, torch, dev, WORKLOAD, height, width, scene_edit=edit)
-    results, states = {}, {}
-    for label, shard in (("one_gpu", False), ("sharded", True)):
+    from dynamicfuion_python_b200 import pixel_shard
+    variants = [("one_gpu", None),
+                ("bands_nccl", dict(stripe_rows=None, collective="nccl")),  # round-2 first form: contiguous bands, int64 all-reduce
+                ("stripes_nccl", dict(stripe_rows=pixel_shard.STRIPE_ROWS, collective="nccl")),
+                ("stripes_peer", dict(stripe_rows=pixel_shard.STRIPE_ROWS, collective="peer"))]  # the default of shard_pixels
+    results, states, used = {}, {}, {}
+    for label, shard in variants:
         q = work.sequence()
-        if shard:
-            q["fitter"].shard_pixels(rank, world)
+        if shard is not None:
+            q["fitter"].shard_pixels(rank, world, **shard)
 
         def frame():
-            q["frame"] = FRAME_POOL - 1  # always the same (last) target frame, from the identity: the two runs do identical work
+            q["frame"] = FRAME_POOL - 1  # always the same (last) target frame, from the identity: the runs do identical work
             q["wf"].node_rotations.copy_(work.eye); q["wf"].node_translations.zero_()
             work.fit_next(q, work.frames_dev, False, supplied_anchors=True)
-        for _ in range(2):
+        for _ in range(3):
             frame()
         torch.cuda.synchronize(); dist.barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -302,16 +309,28 @@ def pixel_shard_leg(torch, dist, nnrt, dev, rank, world, frames):
         ms = frame_batch.max_over_ranks([a.elapsed_time(b) / frames / work.iterations], dev)[0]
         results[label] = ms
         states[label] = (q["wf"].node_rotations.clone(), q["wf"].node_translations.clone(), work.status(q))
-    (R1, t1, s1), (R2, t2, s2) = states["one_gpu"], states["sharded"]
+        used[label] = None if shard is None else q["fitter"]._shard_collective  # "peer" falls back to "nccl" if a peer cannot be mapped
+        if shard is not None:
+            q["fitter"].shard_pixels(0, 1)  # unmaps the peers' buffers
+        del q
+    R1, t1, s1 = states["one_gpu"]
+    head = "stripes_peer" if used["stripes_peer"] == "peer" else "stripes_nccl"
+    R2, t2, s2 = states[head]
     gathered = [torch.zeros_like(t2) for _ in range(world)]
     dist.all_gather(gathered, t2)
     return {"image": f"{width}x{height}", "workload": "C2r mesh and graph (configs[3]), 10 GN iterations from the identity state, anchors supplied",
-            "nranks": world, "ms_per_iteration": results["sharded"], "ms_per_iteration_1gpu": results["one_gpu"],
-            "speedup": results["one_gpu"] / results["sharded"], "status": [s1, s2],
-            "parity_vs_1gpu": {"bit_identical": bool(torch.equal(R1, R2) and torch.equal(t1, t2)),
-                               "max_abs_translation_difference": float((t1 - t2).abs().max()),
+            "nranks": world, "ms_per_iteration": results[head], "ms_per_iteration_1gpu": results["one_gpu"],
+            "speedup": results["one_gpu"] / results[head], "status": [s1, s2],
+            "parity_vs_1gpu": {"bit_identical": bool(all(torch.equal(R1, states[k][0]) and torch.equal(t1, states[k][1]) for k in states)),
+                               "max_abs_translation_difference": float(max((t1 - states[k][1]).abs().max() for k in states)),
                                "identical_on_all_ranks": bool(all(torch.equal(g, gathered[0]) for g in gathered))},
-            "collective": "int64 all-reduce (NCCL) of node_count x 32 x 2 fixed-point words per iteration; replicated deterministic solve, no broadcast",
+            "split": f"rows dealt in {pixel_shard.STRIPE_ROWS}-row stripes, stripe s to rank s % nranks",
+            "collective": ("none on the iteration: the stem kernel reads every rank's node_count x 32 x 2 fixed-point words over NVLink peer memory (CUDA IPC) "
+                           "and adds them itself; flags + two alternating buffers; the whole fit is one captured graph per rank"
+                           if head == "stripes_peer" else
+                           "int64 all-reduce (NCCL) of node_count x 32 x 2 fixed-point words per iteration") + "; replicated deterministic solve, no broadcast",
+            "variants_ms_per_iteration": {k: results[k] for k in results if k != "one_gpu"}, "variants_collective_used": {k: used[k] for k in used if used[k]},
+            "variants_status": {k: states[k][2] for k in states},
             "coverage": work.coverage}
 
 

@@ -73,6 +73,11 @@ _SIGNATURES = {
     "nnrt_b200_fitter_set_model": (C.c_int, [P, P, P, P, P, P, I32, P, P, I32, P, P, P, P]),
     "nnrt_b200_fitter_set_iteration_modes": (C.c_int, [P, P, I32]),
     "nnrt_b200_fitter_set_pixel_rows": (C.c_int, [P, I32, I32]),
+    "nnrt_b200_fitter_set_pixel_stripes": (C.c_int, [P, I32, I32, I32]),
+    "nnrt_b200_fitter_peer_exchange": (C.c_int, [P, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), P]),
+    "nnrt_b200_fitter_enable_peer_reduce": (C.c_int, [P, I32, I32, C.POINTER(C.c_void_p)]),
+    "nnrt_b200_fitter_enable_peer_reduce_ipc": (C.c_int, [P, I32, I32, P]),
+    "nnrt_b200_fitter_disable_peer_reduce": (C.c_int, [P]),
     "nnrt_b200_fitter_accumulators": (P, [P, P]),
     "nnrt_b200_fitter_iteration_data_term": (C.c_int, [P, P, P, P, P, P]),
     "nnrt_b200_fitter_iteration_solve": (C.c_int, [P, P, P, P, P, I32, P]),

@@ -61,11 +61,17 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 	extern __shared__ __align__(16) unsigned char assemble_smem[];
 	float4* s_rec = reinterpret_cast<float4*>(assemble_smem);  // [3A * 2][T]: anchor records, then J contributions (+ node id)
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	// peer-reduced pixel shard (fitter_kernels.cuh::PeerReduce): two buffers alternate by iteration parity
+	unsigned long long* const accumulators = d.accumulators + (d.accum_epoch ? (long long) (*d.accum_epoch & 1ull) * d.accum_parity_words : 0ll);
 	// tiles are visited in a scrambled order (multiplication by a prime modulo the tile count): the surface covers a compact
 	// part of the image, and in raster order its expensive tiles would reach the SMs as one late clump
 	const unsigned tile_count = gridDim.x * gridDim.y, linear = blockIdx.y * gridDim.x + blockIdx.x;
 	const unsigned tile = (tile_count % 1009u) && tile_count < (1u << 22) ? (linear * 1009u) % tile_count : linear;  // 32-bit: no overflow below 2^22 tiles
-	const int tile_x = (int) (tile % gridDim.x) * 16 + (warp & 1) * 8, tile_y = p.row_begin + (int) (tile / gridDim.x) * 8 + (warp >> 1) * 4;
+	// tile row -> image row: tile rows are numbered over the stripes this GPU owns (fitter_kernels.cuh; 8-row stripes dealt to one GPU = every row)
+	const int tile_row = (int) (tile / gridDim.x), tiles_per_stripe = p.stripe_rows >> 3;
+	const int stripe = p.stripe_index + p.stripe_count * (tile_row / tiles_per_stripe);
+	const int tile_x = (int) (tile % gridDim.x) * 16 + (warp & 1) * 8;
+	const int tile_y = p.row_begin + stripe * p.stripe_rows + (tile_row % tiles_per_stripe) * 8 + (warp >> 1) * 4;
 	const int u = tile_x + (lane & 7), v = tile_y + (lane >> 3);
 	const bool in_image = u < p.width && v < p.row_end;
 	const int64_t px = (int64_t) v * p.width + u;
@@ -220,7 +226,7 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 		}
 		const float total = warp_transpose_reduce(vals, lane);
 		// integer (fixed-point) atomics: the per-node sums do not depend on the order in which warps arrive (fixed_accum.cuh)
-		if (lane < 27) fixed_accum_add(d.accumulators + ((int64_t) node * kAccumStride + lane) * 2, total, d.counters + 3);
+		if (lane < 27) fixed_accum_add(accumulators + ((int64_t) node * kAccumStride + lane) * 2, total, d.counters + 3);
 	}
 	// the band queue was fully drained before this kernel started: reset its counter for the next iteration
 	if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) d.counters[0] = 0;
@@ -231,7 +237,9 @@ static int launch_assemble_for(const FitterDeviceData& d, const DataTermParams& 
 	constexpr size_t bytes = assemble_shared_bytes(A);
 	static SharedMemoryOptIn opt_in;
 	if (bytes > 48 * 1024 && opt_in.ensure(assemble_kernel<A>, bytes) != kOk) return kCudaError;
-	const dim3 grid((p.width + 15) / 16, (p.row_end - p.row_begin + 7) / 8);
+	const int stripes = (p.row_end - p.row_begin + p.stripe_rows - 1) / p.stripe_rows;
+	const int owned = p.stripe_index < stripes ? (stripes - p.stripe_index + p.stripe_count - 1) / p.stripe_count : 0;
+	const dim3 grid((p.width + 15) / 16, max(1, owned * (p.stripe_rows / 8)));  // a GPU that owns nothing still resets the band queue counter
 	assemble_kernel<A><<<grid, kAssembleThreads, bytes, s>>>(d, p);
 	return kOk;
 }

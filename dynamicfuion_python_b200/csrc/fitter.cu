@@ -200,15 +200,63 @@ __device__ __forceinline__ float skew_entry(float3 s, int r, int c) {
 	return r == c ? 0.f : (neg ? -v : v);
 }
 
+// ---- peer reduction of a pixel-sharded fit (fitter_kernels.cuh::PeerReduce), fused into the consumer of the sums -----------------
+// Iteration k on every GPU: assemble_kernel adds into the GPU's own buffer k & 1; system_stem_kernel then (1) tells every peer "my sums
+// of iteration k are complete" (flag k + 1 into the peer's flag row, a release store over NVLink -- the sums were finished by the
+// previous kernel), (2) while that travels, evaluates its ARAP edges, (3) waits for the peers' flags in its OWN memory, (4) reads the
+// node's 27 words from every rank's buffer k & 1 (peer loads) and adds them as integers -- the same total on every GPU, bit for bit,
+// and equal to the single-GPU sums -- and (5) clears its own buffer (k - 1) & 1, which no peer can still be reading: a peer raises
+// flag k + 1 only after its iteration k - 1 kernel has ended. A GPU can run at most one iteration ahead of a peer (it needs the peer's
+// flag to finish an iteration), so two buffers suffice. The iteration counter lives in device memory and is advanced by the last warp
+// of this kernel, so a captured graph replays correctly. Waits are bounded (kPeerWaitNs): a missing peer raises flag 4, never a hang.
+constexpr unsigned long long kPeerWaitNs = 4000000000ull;
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+	asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+	unsigned long long v;
+	asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ ulonglong2 ld_relaxed_sys_v2(const unsigned long long* p) {
+	ulonglong2 v;
+	asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+	unsigned long long t;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+	return t;
+}
+// every warp reports once it no longer needs this iteration's epoch; the last one advances it
+__device__ __forceinline__ void peer_warp_done(const PeerReduce& peer, unsigned long long epoch, int lane) {
+	if (peer.world <= 1 || lane != 0) return;
+	__threadfence();
+	if (atomicAdd(peer.done, 1u) == gridDim.x * (blockDim.x >> 5) - 1u) {
+		*peer.done = 0u;
+		*peer.epoch = epoch + 1ull;
+	}
+}
+
 __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDeviceData g, ReducedSystem red, const float* __restrict__ rotations,
                                                                       const float* __restrict__ translations, unsigned long long* __restrict__ accumulators,
-                                                                      float* __restrict__ diag, float* __restrict__ rhs) {
+                                                                      float* __restrict__ diag, float* __restrict__ rhs, PeerReduce peer) {
 	__shared__ float s_H[kStemWarps][36], s_b[kStemWarps][8], s_dinv[kStemWarps][36], s_dE[kStemWarps][20], s_y[kStemWarps][8];
 	__shared__ float s_G[kStemWarps][kMaxStemDegree][18], s_Y[kStemWarps][kMaxStemDegree][18];
 	__shared__ int s_edge[kStemWarps][kMaxStemDegree];
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const int node = blockIdx.x * kStemWarps + wib;
-	if (node >= g.node_count) return;
+	unsigned long long epoch = 0ull;
+	if (peer.world > 1) {
+		epoch = *reinterpret_cast<volatile unsigned long long*>(peer.epoch);
+		__syncthreads();  // every warp of the CTA holds the epoch before any of them can report
+		if (blockIdx.x == 0 && (int) threadIdx.x < peer.world && (int) threadIdx.x != peer.rank) {
+			__threadfence_system();
+			st_release_sys(peer.peer_flags[threadIdx.x] + peer.rank, epoch + 1ull);
+		}
+	}
+	if (node >= g.node_count) { peer_warp_done(peer, epoch, lane); return; }
 	float* H = s_H[wib];
 	float* b = s_b[wib];
 	// ---- stem node: lane q fetches and evaluates outgoing edge q, so the dependent loads of all edges (edge list -> endpoints ->
@@ -227,9 +275,29 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 	// ---- data term from the pixel accumulators (21 upper-triangular + 6), cleaned for the next iteration
 	{
 		ulonglong2* acc = reinterpret_cast<ulonglong2*>(accumulators) + (int64_t) node * kAccumStride;
-		if (lane < 27) {
-			const ulonglong2 words = acc[lane];
+		ulonglong2 words = make_ulonglong2(0ull, 0ull);
+		if (peer.world > 1) {
+			if (lane < peer.world && lane != peer.rank) {
+				const unsigned long long start = global_timer_ns();
+				while (ld_acquire_sys(peer.flags + lane) < epoch + 1ull)
+					if (global_timer_ns() - start > kPeerWaitNs) { atomicExch(red.flags + 4, 1); break; }
+			}
+			__syncwarp();
+			const long long current = (long long) (epoch & 1ull) * peer.parity_words, previous = (long long) ((epoch & 1ull) ^ 1ull) * peer.parity_words;
+			const long long entry = ((long long) node * kAccumStride + lane) * 2;
+			if (lane < 27) {
+				for (int r = 0; r < peer.world; r++) {
+					const ulonglong2 w = ld_relaxed_sys_v2(peer.peer_accum[r] + current + entry);
+					words.x += w.x; words.y += w.y;  // two's-complement and unsigned words: plain 64-bit adds, any order
+				}
+				*reinterpret_cast<ulonglong2*>(const_cast<unsigned long long*>(peer.peer_accum[peer.rank]) + previous + entry) = make_ulonglong2(0ull, 0ull);
+			}
+			peer_warp_done(peer, epoch, lane);
+		} else if (lane < 27) {
+			words = acc[lane];
 			acc[lane] = make_ulonglong2(0ull, 0ull);
+		}
+		if (lane < 27) {
 			const float v = fixed_accum_value(words.x, words.y);
 			if (lane < 21) {
 				int c0 = 0, o = lane;
@@ -455,6 +523,12 @@ struct nnrt_b200_fitter {
 	int arrow_base = 0, corner_blocks = 0;
 	bool graph_set = false, mesh_set = false, reference_set = false, fused_stem = true;
 	int row_begin = 0, row_end = 0;  // pixel band of a pixel-sharded fit; row_end == 0: whole image
+	int stripe_rows = 8, stripe_index = 0, stripe_count = 1;  // striped pixel shard (fitter_kernels.cuh); 8, 0, 1: every row of the band
+	// peer-reduced pixel shard: accumulators, flags and the iteration counter in a cudaMalloc'ed buffer of its own (it is exported to the
+	// peers by IPC handle, which the arena must not be)
+	char* exchange = nullptr; size_t exchange_bytes = 0;
+	nnrt_b200::PeerReduce peer{};
+	void* peer_mapped[nnrt_b200::kMaxPeers]{};  // bases opened with cudaIpcOpenMemHandle
 	std::vector<int> modes{0};  // IterationMode sequence, cycled by iteration index (DeformableMeshToImageFitter.cpp:112)
 	// arena
 	char* arena = nullptr; size_t arena_bytes = 0, arena_used = 0;
@@ -509,7 +583,7 @@ static size_t layout(nnrt_b200_fitter* f, bool assign) {
 	f->in_offsets = f->take<int>(N + 2); f->in_edges = f->take<int>(E + 1); f->wing_columns = f->take<int>(E + 1);
 	f->refpts = f->take<float4>(PX);
 	f->keys = f->take<unsigned long long>(PX);
-	f->queue = f->take<BandItem>(F + 65536); f->counters = f->take<int>(4);
+	f->queue = f->take<BandItem>(F + 65536); f->counters = f->take<int>(8);
 	f->accum = f->take<unsigned long long>((int64_t) N * kAccumStride * 2);
 	f->sys_diag = f->take<float>((int64_t) N * 36); f->sys_rhs = f->take<float>(nmax); f->wing = f->take<float>((E + 1) * 36);
 	f->dinv = f->take<float>((int64_t) N * 36); f->stem_y = f->take<float>(nmax); f->wing_x = f->take<float>((E + 1) * 36);
@@ -554,8 +628,8 @@ extern "C" int nnrt_b200_fitter_create(const nnrt_b200_fitter_options* options, 
 	if (cudaMalloc(&f->arena, bytes) != cudaSuccess) { delete f; set_last_error("fitter_create: cudaMalloc of %zu bytes failed", bytes); return kCudaError; }
 	f->arena_bytes = bytes;
 	layout(f, true);
-	if (cudaMallocHost(&f->host_flags, 4 * sizeof(int)) != cudaSuccess) { cudaFree(f->arena); delete f; return kCudaError; }
-	memset(f->host_flags, 0, 4 * sizeof(int));
+	if (cudaMallocHost(&f->host_flags, 8 * sizeof(int)) != cudaSuccess) { cudaFree(f->arena); delete f; return kCudaError; }
+	memset(f->host_flags, 0, 8 * sizeof(int));
 	f->schur = nullptr; f->corner_rhs = nullptr;
 	cudaMemset(f->arena, 0, bytes);
 	launch_fill_keys(f->keys, (int64_t) f->H * f->W, nullptr);
@@ -567,6 +641,8 @@ extern "C" int nnrt_b200_fitter_create(const nnrt_b200_fitter_options* options, 
 extern "C" void nnrt_b200_fitter_destroy(nnrt_b200_fitter* f) {
 	if (!f) return;
 	if (f->graph_exec) cudaGraphExecDestroy(f->graph_exec);
+	nnrt_b200_fitter_disable_peer_reduce(f);
+	cudaFree(f->exchange);
 	cudaFree(f->arena);
 	cudaFree(f->schur);  // corner buffers are allocated by set_model (their size depends on arrow_base)
 	cudaFree(f->graph_buffer);
@@ -803,7 +879,7 @@ extern "C" int nnrt_b200_fitter_set_reference_points(nnrt_b200_fitter* f, const 
 	NNRT_CHECK_ARG(f && reference_points, "fitter_set_reference_points: null pointer argument");
 	const int64_t px = (int64_t) f->H * f->W;
 	// a new observation starts a new fit: its status must not inherit the overflow / not-positive-definite flags of an earlier one
-	NNRT_CUDA(cudaMemsetAsync(f->counters + 1, 0, 3 * sizeof(int), (cudaStream_t) stream));
+	NNRT_CUDA(cudaMemsetAsync(f->counters + 1, 0, 4 * sizeof(int), (cudaStream_t) stream));
 	pack_reference_kernel<<<blocks_for(px, 256), 256, 0, (cudaStream_t) stream>>>(reference_points, reference_mask, px, f->refpts);
 	NNRT_LAUNCH_CHECK();
 	f->reference_set = true;
@@ -817,7 +893,7 @@ extern "C" int nnrt_b200_fitter_set_reference_depth(nnrt_b200_fitter* f, const v
 	const int64_t px = (int64_t) f->H * f->W;
 	const Intrinsics k = intrinsics_from_host(intrinsics_host);
 	auto s = (cudaStream_t) stream;
-	NNRT_CUDA(cudaMemsetAsync(f->counters + 1, 0, 3 * sizeof(int), s));  // see set_reference_points
+	NNRT_CUDA(cudaMemsetAsync(f->counters + 1, 0, 4 * sizeof(int), s));  // see set_reference_points
 	if (depth_dtype == 0)
 		reference_from_depth_kernel<float><<<blocks_for(px, 256), 256, 0, s>>>((const float*) depth, user_mask, f->H, f->W, k, depth_scale, f->opt.max_depth, f->refpts);
 	else
@@ -831,6 +907,7 @@ namespace nnrt_b200 {
 
 struct IterationContext {
 	FitterDeviceData d; GraphDeviceData g; ArrowheadSystem sys; ReducedSystem red; DataTermParams p; NdcCamera cam; Rigid extrinsics;
+	PeerReduce peer;
 };
 
 static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const double* T) {
@@ -841,6 +918,11 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	c.d.warped_positions = f->wpos; c.d.warped_normals = f->wnrm; c.d.vertex_jacobians = f->vjac;
 	c.d.keys = f->keys; c.d.band_queue = f->queue; c.d.counters = f->counters; c.d.band_queue_capacity = (int) (f->F + 65536);
 	c.d.reference_points = f->refpts; c.d.accumulators = f->accum;
+	c.peer = f->peer;
+	if (f->peer.world > 1) {  // the sums go to the exported buffer of this iteration's parity
+		c.d.accumulators = reinterpret_cast<unsigned long long*>(f->exchange);
+		c.d.accum_epoch = f->peer.epoch; c.d.accum_parity_words = f->peer.parity_words;
+	}
 	c.d.diag_pixel_faces = f->diag_faces; c.d.diag_residuals = f->diag_res; c.d.diag_mask = f->diag_mask;
 	c.g.nodes = f->nodes; c.g.node_count = f->N; c.g.arrow_base = f->arrow_base; c.g.edges = f->edges; c.g.edge_count = (int) f->E;
 	c.g.edge_weight_residual = f->ew_res; c.g.edge_weight_jacobian = f->ew_jac;
@@ -867,6 +949,7 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	// RasterizeNdcTriangles(..., blur 0.5 px, ...) (DeformableMeshToImageFitter.cpp:124-127); ImageSpaceDistanceToNdc
 	c.p.blur_radius = 0.5f / (fminf((float) f->H, (float) f->W) / 2.0f);
 	c.p.row_begin = f->row_begin; c.p.row_end = f->row_end > 0 ? f->row_end : f->H;
+	c.p.stripe_rows = f->stripe_rows; c.p.stripe_index = f->stripe_index; c.p.stripe_count = f->stripe_count;
 	c.p.write_diagnostics = 1;
 	c.extrinsics = rigid_from_host(T);
 	return c;
@@ -906,7 +989,7 @@ static int enqueue_solve(nnrt_b200_fitter* f, const IterationContext& base, int 
 	c.sys.update_mode = iteration_mode;
 	if (f->fused_stem) {
 		c.red.update_mode = iteration_mode;
-		system_stem_kernel<<<(f->N + kStemWarps - 1) / kStemWarps, kStemWarps * 32, 0, s>>>(c.g, c.red, R, t, f->accum, f->sys_diag, f->sys_rhs);
+		system_stem_kernel<<<(f->N + kStemWarps - 1) / kStemWarps, kStemWarps * 32, 0, s>>>(c.g, c.red, R, t, f->accum, f->sys_diag, f->sys_rhs, c.peer);
 		if (ev) { cudaEventRecord(ev[5], s); cudaEventRecord(ev[6], s); }
 		const int rc = launch_reduced_corner_solve(c.red, f->x, R, t, s);
 		if (ev) cudaEventRecord(ev[7], s);
@@ -914,6 +997,7 @@ static int enqueue_solve(nnrt_b200_fitter* f, const IterationContext& base, int 
 		NNRT_LAUNCH_CHECK();
 		return kOk;
 	} else {  // stem rows with more than kMaxStemDegree edges: unfused pair of kernels
+		if (c.peer.world > 1) { set_last_error("fitter: the peer reduction is fused into the stem kernel, which this graph (a stem row with more than %d edges) does not use; use the all-reduce path", kMaxStemDegree); return kInvalidArgument; }
 		build_system_kernel<<<(f->N + 127) / 128, 128, 0, s>>>(c.g, R, t, f->accum, f->sys_diag, f->sys_rhs, f->wing);
 		if (f->corner_edge_count > 0)
 			corner_edges_kernel<<<(f->corner_edge_count + 63) / 64, 64, 0, s>>>(c.g, f->corner_edge_ids, f->corner_edge_count, R, t, f->sys_diag, f->sys_rhs,
@@ -948,6 +1032,95 @@ extern "C" int nnrt_b200_fitter_set_pixel_rows(nnrt_b200_fitter* f, int32_t row_
 	return kOk;
 }
 
+extern "C" int nnrt_b200_fitter_set_pixel_stripes(nnrt_b200_fitter* f, int32_t stripe_rows, int32_t stripe_index, int32_t stripe_count) {
+	NNRT_CHECK_ARG(f, "fitter_set_pixel_stripes: null fitter");
+	NNRT_CHECK_ARG(stripe_rows > 0 && stripe_rows % 8 == 0, "stripe_rows must be a positive multiple of the 8-row assembly tile, got %d", stripe_rows);
+	NNRT_CHECK_ARG(stripe_count >= 1 && stripe_index >= 0 && stripe_index < stripe_count, "stripe index %d outside [0, %d)", stripe_index, stripe_count);
+	if ((stripe_rows != f->stripe_rows || stripe_index != f->stripe_index || stripe_count != f->stripe_count) && f->graph_exec) {
+		cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr;
+	}
+	f->stripe_rows = stripe_rows; f->stripe_index = stripe_index; f->stripe_count = stripe_count;
+	return kOk;
+}
+
+// ---- peer-reduced pixel shard ---------------------------------------------------------------------------------------------
+static size_t exchange_flags_offset(const nnrt_b200_fitter* f) { return ((size_t) f->N * kAccumStride * 2 * 2 * sizeof(unsigned long long) + 255) & ~size_t(255); }
+
+extern "C" int nnrt_b200_fitter_peer_exchange(nnrt_b200_fitter* f, void** device_pointer, int64_t* byte_count, void* ipc_handle_out) {
+	NNRT_CHECK_ARG(f, "fitter_peer_exchange: null fitter");
+	if (f->exchange == nullptr) {
+		f->exchange_bytes = exchange_flags_offset(f) + 256;
+		if (cudaMalloc(&f->exchange, f->exchange_bytes) != cudaSuccess) { f->exchange = nullptr; set_last_error("fitter_peer_exchange: cudaMalloc of %zu bytes failed", f->exchange_bytes); return kCudaError; }
+	}
+	// a fresh exchange: zero sums, no flags raised, iteration counter 0 (every rank does this before the handles are gathered)
+	NNRT_CUDA(cudaDeviceSynchronize());
+	NNRT_CUDA(cudaMemset(f->exchange, 0, f->exchange_bytes));
+	NNRT_CUDA(cudaDeviceSynchronize());
+	if (device_pointer) *device_pointer = f->exchange;
+	if (byte_count) *byte_count = (int64_t) f->exchange_bytes;
+	if (ipc_handle_out) {
+		static_assert(sizeof(cudaIpcMemHandle_t) == 64, "the C ABI states 64 bytes per IPC handle");
+		cudaIpcMemHandle_t handle;
+		NNRT_CUDA(cudaIpcGetMemHandle(&handle, f->exchange));
+		memcpy(ipc_handle_out, &handle, sizeof(handle));
+	}
+	return kOk;
+}
+
+extern "C" int nnrt_b200_fitter_disable_peer_reduce(nnrt_b200_fitter* f) {
+	if (!f) return kOk;
+	if (f->peer.world > 1 && f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
+	for (int r = 0; r < kMaxPeers; r++)
+		if (f->peer_mapped[r]) { cudaIpcCloseMemHandle(f->peer_mapped[r]); f->peer_mapped[r] = nullptr; }
+	f->peer = PeerReduce{};
+	return kOk;
+}
+
+extern "C" int nnrt_b200_fitter_enable_peer_reduce(nnrt_b200_fitter* f, int32_t rank, int32_t world, void* const* exchange_pointers) {
+	NNRT_CHECK_ARG(f && exchange_pointers, "fitter_enable_peer_reduce: null pointer argument");
+	NNRT_CHECK_ARG(world >= 2 && world <= kMaxPeers && rank >= 0 && rank < world, "peer reduction needs 2..%d ranks and a rank inside them, got rank %d of %d", kMaxPeers, rank, world);
+	NNRT_CHECK_ARG(f->exchange, "fitter_enable_peer_reduce: call fitter_peer_exchange first");
+	NNRT_CHECK_ARG(!f->graph_set || f->fused_stem, "the peer reduction is fused into the stem kernel, which this graph (a stem row with more than %d edges) does not use", kMaxStemDegree);
+	if (f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
+	PeerReduce p{};
+	p.world = world; p.rank = rank; p.parity_words = (long long) f->N * kAccumStride * 2;
+	const size_t flags_at = exchange_flags_offset(f);
+	for (int r = 0; r < world; r++) {
+		char* base = r == rank ? f->exchange : static_cast<char*>(exchange_pointers[r]);
+		NNRT_CHECK_ARG(base, "fitter_enable_peer_reduce: no exchange pointer for rank %d", r);
+		p.peer_accum[r] = reinterpret_cast<const unsigned long long*>(base);
+		p.peer_flags[r] = reinterpret_cast<unsigned long long*>(base + flags_at);
+	}
+	p.flags = p.peer_flags[rank];
+	p.epoch = p.flags + kMaxPeers;
+	p.done = reinterpret_cast<unsigned int*>(p.flags + kMaxPeers + 1);
+	f->peer = p;
+	return kOk;
+}
+
+extern "C" int nnrt_b200_fitter_enable_peer_reduce_ipc(nnrt_b200_fitter* f, int32_t rank, int32_t world, const void* ipc_handles) {
+	NNRT_CHECK_ARG(f && ipc_handles, "fitter_enable_peer_reduce_ipc: null pointer argument");
+	NNRT_CHECK_ARG(world >= 2 && world <= kMaxPeers && rank >= 0 && rank < world, "peer reduction needs 2..%d ranks and a rank inside them, got rank %d of %d", kMaxPeers, rank, world);
+	nnrt_b200_fitter_disable_peer_reduce(f);
+	void* pointers[kMaxPeers] = {};
+	for (int r = 0; r < world; r++) {
+		if (r == rank) continue;
+		cudaIpcMemHandle_t handle;
+		memcpy(&handle, static_cast<const char*>(ipc_handles) + (size_t) r * sizeof(handle), sizeof(handle));
+		const cudaError_t e = cudaIpcOpenMemHandle(&pointers[r], handle, cudaIpcMemLazyEnablePeerAccess);
+		if (e != cudaSuccess) {
+			cudaGetLastError();
+			for (int q = 0; q < r; q++) if (pointers[q]) cudaIpcCloseMemHandle(pointers[q]);
+			set_last_error("fitter_enable_peer_reduce_ipc: cannot map rank %d's exchange buffer (%s)", r, cudaGetErrorString(e));
+			return kCudaError;
+		}
+	}
+	const int rc = nnrt_b200_fitter_enable_peer_reduce(f, rank, world, pointers);
+	if (rc != kOk) { for (int r = 0; r < world; r++) if (pointers[r]) cudaIpcCloseMemHandle(pointers[r]); return rc; }
+	for (int r = 0; r < world; r++) f->peer_mapped[r] = pointers[r];
+	return kOk;
+}
+
 extern "C" int64_t* nnrt_b200_fitter_accumulators(nnrt_b200_fitter* f, int64_t* word_count) {
 	if (f == nullptr) return nullptr;
 	if (word_count) *word_count = (int64_t) f->N * kAccumStride * 2;
@@ -973,7 +1146,7 @@ extern "C" int nnrt_b200_fitter_iteration_solve(nnrt_b200_fitter* f, float* node
 	const int mode = f->modes[(size_t) iteration_index % f->modes.size()];
 	NNRT_CHECK_ARG(mode == 0 || f->E == 0, "TRANSLATION_ONLY / ROTATION_ONLY iterations need a warp field without regularisation edges");
 	const int rc = enqueue_solve(f, c, mode, node_rotations, node_translations, (cudaStream_t) stream, nullptr);
-	if (rc == kOk) NNRT_CUDA(cudaMemcpyAsync(f->host_flags, f->counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t) stream));
+	if (rc == kOk) NNRT_CUDA(cudaMemcpyAsync(f->host_flags, f->counters, 5 * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t) stream));
 	return rc;
 }
 
@@ -1019,7 +1192,7 @@ extern "C" int nnrt_b200_fitter_fit(nnrt_b200_fitter* f, float* node_rotations, 
 		f->graph_key = key;
 	}
 	NNRT_CUDA(cudaGraphLaunch(f->graph_exec, s));
-	NNRT_CUDA(cudaMemcpyAsync(f->host_flags, f->counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, s));
+	NNRT_CUDA(cudaMemcpyAsync(f->host_flags, f->counters, 5 * sizeof(int), cudaMemcpyDeviceToHost, s));
 	return kOk;
 }
 
@@ -1030,6 +1203,7 @@ extern "C" int nnrt_b200_fitter_status(nnrt_b200_fitter* f, void* stream) {
 	if (f->host_flags[1]) { set_last_error("fitter: large-face band queue overflow"); return kQueueOverflow; }
 	if (f->host_flags[2]) { set_last_error("fitter: a Hessian block was not positive definite"); return kNotPositiveDefinite; }
 	if (f->host_flags[3]) { set_last_error("fitter: a data-term sum left the accumulator range (non-finite, or magnitude above 4e12)"); return kNotPositiveDefinite; }
+	if (f->host_flags[4]) { set_last_error("fitter: peer reduction timed out waiting for another rank's sums (ranks out of step, or a peer stopped)"); return kCudaError; }
 	return kOk;
 }
 

@@ -80,21 +80,72 @@ __device__ __forceinline__ RasterParams raster_params(const DataTermParams& p) {
 }
 
 // K3. One thread per face: gather + project (replaces ExtractFaceVertices + the bbox pass + binning), rasterise inline
-// when the pixel box is small, otherwise enqueue row bands.
+// when the pixel box is small, otherwise enqueue row bands. Pixel-sharded fits walk only the rows of this GPU's band / stripes
+// (fitter_kernels.cuh::row_owned); a larger box queues its band items stripe by stripe so that no warp of the drain kernel walks
+// rows of another GPU. Queue slots are reserved with ONE atomic per warp (at 4K nearly every face takes the queue path, and 81 608
+// atomics on one counter were a fixed ~40 us that no amount of sharding removed).
 __global__ void __launch_bounds__(256) face_raster_kernel(FitterDeviceData d, DataTermParams p, NdcCamera cam) {
 	const int64_t f = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-	if (f >= d.face_count) return;
-	FaceNdc face;
-	if (!load_fitter_face(d, cam, (int) f, face)) return;
+	const int lane = threadIdx.x & 31;
 	const RasterParams rp = raster_params(p);
+	FaceNdc face;
 	PixelBox box;
-	if (!face_pixel_box(face, rp, box)) return;
-	box.v0 = max(box.v0, p.row_begin);  // pixel-sharded fits: this GPU's band of rows only
-	box.v1 = min(box.v1, p.row_end - 1);
-	if (box.v0 > box.v1) return;
-	int rows_per_band;
-	const int bands = raster_face_or_count_bands(face, (int) f, rp, box, d.keys, nullptr, rows_per_band);
-	if (bands > 0) push_bands((int) f, box, rows_per_band, bands, d.band_queue, d.counters, d.band_queue_capacity, d.counters + 1);
+	bool valid = f < d.face_count && load_fitter_face(d, cam, (int) f, face) && face_pixel_box(face, rp, box);
+	if (valid) {
+		box.v0 = max(box.v0, p.row_begin);
+		box.v1 = min(box.v1, p.row_end - 1);
+		valid = box.v0 <= box.v1;
+	}
+	const bool striped = p.stripe_count > 1;
+	int items = 0, rows_per_band = 1, first = 0, last = 0;
+	// rows [y0, y1] of the box inside stripe `stripe` (unstriped: the whole box is the one "stripe" 0)
+	auto stripe_rows = [&](int stripe, int& y0, int& y1) {
+		y0 = striped ? max(box.v0, p.row_begin + stripe * p.stripe_rows) : box.v0;
+		y1 = striped ? min(box.v1, p.row_begin + (stripe + 1) * p.stripe_rows - 1) : box.v1;
+	};
+	const int step = striped ? p.stripe_count : 1;
+	if (valid) {
+		const int bw = box.u1 - box.u0 + 1, bh = box.v1 - box.v0 + 1;
+		if (bw * bh <= kSmallBoxPixels) {
+			const bool within_blur = face_box_within_blur(face, rp.blur_radius);
+			for (int v = box.v0; v <= box.v1; v++) {
+				if (!row_owned(p, v)) continue;
+				for (int u = box.u0; u <= box.u1; u++) raster_pixel(face, (int) f, u, v, rp, d.keys, nullptr, within_blur);
+			}
+		} else {
+			rows_per_band = max(1, kBandPixels / bw);
+			if (striped) {
+				const int s0 = (box.v0 - p.row_begin) / p.stripe_rows;
+				last = (box.v1 - p.row_begin) / p.stripe_rows;
+				first = s0 + ((p.stripe_index - s0) % p.stripe_count + p.stripe_count) % p.stripe_count;  // first owned stripe >= s0
+			}
+			for (int stripe = first; stripe <= last; stripe += step) {
+				int y0, y1;
+				stripe_rows(stripe, y0, y1);
+				items += (y1 - y0 + rows_per_band) / rows_per_band;
+			}
+		}
+	}
+	// warp-aggregated reservation: inclusive scan of the item counts, one atomicAdd by the last lane
+	int inclusive = items;
+#pragma unroll
+	for (int offset = 1; offset < 32; offset <<= 1) {
+		const int up = __shfl_up_sync(0xffffffffu, inclusive, offset);
+		if (lane >= offset) inclusive += up;
+	}
+	const int warp_items = __shfl_sync(0xffffffffu, inclusive, 31);
+	if (warp_items == 0) return;
+	int base = 0;
+	if (lane == 31) base = atomicAdd(d.counters, warp_items);
+	base = __shfl_sync(0xffffffffu, base, 31);
+	if (items == 0) return;
+	int slot = base + inclusive - items;
+	if (slot + items > d.band_queue_capacity) { atomicExch(d.counters + 1, 1); return; }
+	for (int stripe = first; stripe <= last; stripe += step) {
+		int y0, y1;
+		stripe_rows(stripe, y0, y1);
+		for (int y = y0; y <= y1; y += rows_per_band) d.band_queue[slot++] = BandItem{(int) f, y, min(y1, y + rows_per_band - 1), 0};
+	}
 }
 
 // K5. One warp per queued row band.

@@ -17,6 +17,21 @@ namespace nnrt_b200 {
 
 constexpr int kAccumStride = 32;
 constexpr int kMaxStemDegree = 8;
+constexpr int kMaxPeers = 16;
+
+// Pixel-sharded fits without a library collective: every GPU's accumulators live in a buffer its peers can read (NVLink peer memory),
+// and the kernel that consumes the sums (system_stem_kernel) gathers and adds the ranks' words itself. Two accumulator buffers
+// alternate by iteration parity so that a GPU one iteration ahead never writes what a peer is still reading; `flags[r]` on every GPU
+// holds 1 + the last iteration rank r has finished assembling. See fitter.cu::system_stem_kernel for the protocol.
+struct PeerReduce {
+	int world, rank;                                  // world <= 1: off
+	long long parity_words;                           // 64-bit words per accumulator buffer = N * kAccumStride * 2
+	unsigned long long* epoch;                        // this GPU's iteration counter (device memory; the kernels read and advance it)
+	unsigned int* done;                               // warps of system_stem_kernel that have read the epoch and the sums
+	unsigned long long* flags;                        // this GPU's flag row [kMaxPeers]
+	unsigned long long* peer_flags[kMaxPeers];        // every rank's flag row, as mapped into this process
+	const unsigned long long* peer_accum[kMaxPeers];  // every rank's [2][parity_words] accumulators, as mapped into this process ([rank] = own)
+};
 
 struct DataTermParams {
 	int height, width;
@@ -28,6 +43,9 @@ struct DataTermParams {
 	float tukey_cutoff;
 	float blur_radius;    // NDC
 	int row_begin, row_end;  // image rows [row_begin, row_end) this GPU rasterises and assembles (whole image unless pixel-sharded)
+	// pixel-sharded fits, balanced form: the rows are cut into stripes of `stripe_rows` (a multiple of the 8-row assembly tile) dealt
+	// round-robin to `stripe_count` GPUs; this GPU owns stripes stripe_index, stripe_index + stripe_count, ... (8, 0, 1 = every row)
+	int stripe_rows, stripe_index, stripe_count;
 	int write_diagnostics;   // per-pixel face / residual / mask of this iteration are kept (the last iteration of a fit; every split or profiled one)
 };
 
@@ -43,8 +61,13 @@ struct FitterDeviceData {
 	int band_queue_capacity;
 	const float4* reference_points;
 	unsigned long long* accumulators;  // [N, kAccumStride, 2] fixed-point words (fixed_accum.cuh)
+	const unsigned long long* accum_epoch; long long accum_parity_words;  // PeerReduce: this iteration's buffer is accumulators + (*accum_epoch & 1) * accum_parity_words
 	int32_t* diag_pixel_faces; float* diag_residuals; uint8_t* diag_mask;  // diagnostics of the last iteration
 };
+
+__host__ __device__ __forceinline__ bool row_owned(const DataTermParams& p, int v) {
+	return p.stripe_count <= 1 || ((v - p.row_begin) / p.stripe_rows) % p.stripe_count == p.stripe_index;
+}
 
 void launch_warp_vertices(const FitterDeviceData& d, const float* rotations, const float* translations, const Rigid& extrinsics, cudaStream_t s);
 void launch_face_raster(const FitterDeviceData& d, const DataTermParams& p, const NdcCamera& cam, cudaStream_t s);

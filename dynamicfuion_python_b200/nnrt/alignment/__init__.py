@@ -35,6 +35,8 @@ class DeformableMeshToImageFitter:
                                           int(bool(use_huber_penalty_for_arap_term)), float(huber_penalty_constant))
         self._handle = None
         self._pixel_shard = None
+        self._stripe_rows = None
+        self._shard_collective, self._peer_ready = "nccl", False
         self._shard_graphs, self._shard_seen, self._shard_keep = {}, None, None
         self._shape = None
         self._model_key = None
@@ -59,15 +61,49 @@ class DeformableMeshToImageFitter:
         v, f, n, e, a, h, w = shape
         _lib.check(_lib.lib().nnrt_b200_fitter_create(C.byref(self.options), v, f, n, e, a, h, w, C.byref(handle)))
         self._handle, self._shape, self._model_key = handle, shape, None
+        self._peer_ready = False  # a new fitter object: its exchange buffer has not been mapped by the peers
         modes = (C.c_int32 * len(self.iteration_mode_sequence))(*[int(m) for m in self.iteration_mode_sequence])
         _lib.check(_lib.lib().nnrt_b200_fitter_set_iteration_modes(handle, modes, len(self.iteration_mode_sequence)))
 
-    def shard_pixels(self, rank, world_size, group=None):
-        """Pixel-sharded single-frame mode (dynamicfuion_python_b200.pixel_shard): this process fits rows
-        pixel_rows(rank, world_size, height) and all-reduces the per-node sums over `group` once per iteration. world_size 1 turns it off."""
+    def shard_pixels(self, rank, world_size, group=None, stripe_rows=pixel_shard.STRIPE_ROWS, collective=None):
+        """Pixel-sharded single-frame mode (dynamicfuion_python_b200.pixel_shard): this process fits its share of the image rows and the
+        per-node sums are summed over the ranks of `group` once per iteration. The rows are dealt in stripes of `stripe_rows` (a multiple
+        of 8), stripe s to rank s % world_size, so that a surface in the middle of the frame loads every GPU alike; stripe_rows=None
+        gives one contiguous band per rank, pixel_rows(rank, world_size, height). `collective`: "peer" (default, NNRT_B200_SHARD_COLLECTIVE)
+        = the consuming kernel reads the ranks' sums over NVLink peer memory itself and the whole fit is one call into the C library;
+        "nccl" = an int64 all-reduce between the two halves of an iteration. world_size 1 turns the mode off."""
+        if stripe_rows is not None and (int(stripe_rows) <= 0 or int(stripe_rows) % 8):
+            raise ValueError(f"stripe_rows must be a positive multiple of 8 (the assembly tile height), got {stripe_rows}")
+        collective = pixel_shard.COLLECTIVE if collective is None else collective
+        if collective not in ("peer", "nccl"):
+            raise ValueError(f"collective must be 'peer' or 'nccl', got {collective!r}")
         self._pixel_shard = None if world_size <= 1 else (int(rank), int(world_size), group)
-        if self._handle is not None and self._pixel_shard is None:
-            T.call("nnrt_b200_fitter_set_pixel_rows", self._handle, 0, self._shape[5])
+        self._stripe_rows = None if stripe_rows is None else int(stripe_rows)
+        self._shard_collective, self._peer_ready = collective, False
+        if self._handle is not None:
+            T.call("nnrt_b200_fitter_disable_peer_reduce", self._handle)
+            if self._pixel_shard is None:
+                T.call("nnrt_b200_fitter_set_pixel_rows", self._handle, 0, self._shape[5])
+                T.call("nnrt_b200_fitter_set_pixel_stripes", self._handle, 8, 0, 1)
+
+    def _enable_peer_reduce(self, rank, world, group):
+        """Collective over `group`: every rank clears its exchange buffer, the CUDA IPC handles are gathered, every rank maps its peers.
+        All ranks take the same path: if any of them cannot map a peer (no NVLink / IPC not permitted), all fall back to the all-reduce."""
+        handle = (C.c_ubyte * 64)()
+        status = _lib.lib().nnrt_b200_fitter_peer_exchange(self._handle, None, None, handle)
+        gathered = [None] * world
+        torch.distributed.all_gather_object(gathered, bytes(handle) if status == 0 else None, group=group)
+        ok = status == 0 and all(h is not None for h in gathered)
+        if ok:
+            blob = (C.c_ubyte * (64 * world)).from_buffer_copy(b"".join(gathered))
+            ok = _lib.lib().nnrt_b200_fitter_enable_peer_reduce_ipc(self._handle, rank, world, blob) == 0
+        verdicts = [None] * world
+        torch.distributed.all_gather_object(verdicts, bool(ok), group=group)  # also the barrier the protocol asks for before the first fit
+        if not all(verdicts):
+            T.call("nnrt_b200_fitter_disable_peer_reduce", self._handle)
+            self._shard_collective = "nccl"
+            return False
+        return True
 
     def workspace_bytes(self):
         return 0 if self._handle is None else _lib.lib().nnrt_b200_fitter_workspace_bytes(self._handle)
@@ -129,8 +165,21 @@ class DeformableMeshToImageFitter:
             # iteration count, band) and replayed; the first call of a key runs eagerly (it also brings up the NCCL communicator, which
             # cannot happen under capture).
             rank, world, group = self._pixel_shard
-            begin, end = pixel_shard.pixel_rows(rank, world, self._shape[5])
-            T.call("nnrt_b200_fitter_set_pixel_rows", self._handle, begin, end)
+            if self._stripe_rows is None:
+                begin, end = pixel_shard.pixel_rows(rank, world, self._shape[5])
+                T.call("nnrt_b200_fitter_set_pixel_rows", self._handle, begin, end)
+                T.call("nnrt_b200_fitter_set_pixel_stripes", self._handle, 8, 0, 1)
+            else:
+                begin, end = 0, -self._stripe_rows  # (key only) striped: every rank walks the whole image height
+                T.call("nnrt_b200_fitter_set_pixel_rows", self._handle, 0, self._shape[5])
+                T.call("nnrt_b200_fitter_set_pixel_stripes", self._handle, self._stripe_rows, rank, world)
+            if self._shard_collective == "peer" and not self._peer_ready:
+                self._peer_ready = self._enable_peer_reduce(rank, world, group)
+            if self._shard_collective == "peer":
+                # the sums are exchanged inside the iteration's own kernels: the sharded fit is the library's captured loop
+                T.call("nnrt_b200_fitter_fit", self._handle, T.ptr(R), T.ptr(t), K.data_ptr(), ext.data_ptr(), iters, T.stream())
+                self._keep = (K, ext)
+                return
             count = C.c_int64()
             pointer = _lib.lib().nnrt_b200_fitter_accumulators(self._handle, C.byref(count))
             acc = pixel_shard.DeviceBuffer(pointer, count.value).tensor(R.device)

@@ -201,7 +201,26 @@ int nnrt_b200_fitter_set_iteration_modes(nnrt_b200_fitter* fitter, const int32_t
  * ComputeNegativeDepthGradient_... (alignment/kernel/DeformableMeshToImageFitterImpl.h:199-420). iteration_index selects the
  * IterationMode of the sequence. */
 int nnrt_b200_fitter_set_pixel_rows(nnrt_b200_fitter* fitter, int32_t row_begin, int32_t row_end);
+/* Balanced form of the same split: the rows (of the band above; the whole image by default) are cut into stripes of stripe_rows rows
+ * (a multiple of 8, the assembly tile height) dealt round-robin to stripe_count GPUs; this fitter rasterises and assembles stripes
+ * stripe_index, stripe_index + stripe_count, ... A surface that covers the middle of the frame then loads every GPU alike, where
+ * contiguous bands leave the outer GPUs idle. (8, 0, 1) = every row. The sums are the same integers either way. */
+int nnrt_b200_fitter_set_pixel_stripes(nnrt_b200_fitter* fitter, int32_t stripe_rows, int32_t stripe_index, int32_t stripe_count);
 int64_t* nnrt_b200_fitter_accumulators(nnrt_b200_fitter* fitter, int64_t* word_count);
+/* The same exchange without a library collective (no reference counterpart; the B200 form of the step): each fitter keeps its sums in
+ * a buffer of its own that the peers map over NVLink (CUDA IPC across processes, plain pointers inside one process), and the kernel
+ * that consumes the sums gathers and adds the ranks' words itself while its ARAP edge work is in flight. Call order, on every rank:
+ *   fitter_peer_exchange    allocates / clears the buffer (synchronises the device); returns its device pointer, size and, if asked,
+ *                           the 64-byte cudaIpcMemHandle_t to hand to the other processes;
+ *   enable_peer_reduce_ipc  with all ranks' handles (world x 64 bytes, rank-major; the own entry is ignored), or enable_peer_reduce
+ *                           with device pointers valid in this process (same-process use; the caller enables peer access);
+ *   a host barrier, then fitter_fit (or the split entry points) on every rank, the same number of iterations everywhere.
+ * Needs set_pixel_rows / set_pixel_stripes to give each rank its share, and a graph on the fused stem path (no stem row with more than
+ * 8 edges, no edges between coarse layers). A rank that waits more than 4 s for a peer raises an error status instead of hanging. */
+int nnrt_b200_fitter_peer_exchange(nnrt_b200_fitter* fitter, void** device_pointer, int64_t* byte_count, void* ipc_handle_out);
+int nnrt_b200_fitter_enable_peer_reduce(nnrt_b200_fitter* fitter, int32_t rank, int32_t world_size, void* const* exchange_pointers);
+int nnrt_b200_fitter_enable_peer_reduce_ipc(nnrt_b200_fitter* fitter, int32_t rank, int32_t world_size, const void* ipc_handles);
+int nnrt_b200_fitter_disable_peer_reduce(nnrt_b200_fitter* fitter);
 int nnrt_b200_fitter_iteration_data_term(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,
                                          const double* intrinsics_host, const double* extrinsics_host, void* stream);
 int nnrt_b200_fitter_iteration_solve(nnrt_b200_fitter* fitter, float* node_rotations, float* node_translations,

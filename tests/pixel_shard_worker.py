@@ -21,13 +21,13 @@ def main():
     G = nnrt.geometry
     mesh = (s["positions"], s["normals"], s["triangles"])
 
-    def fit(shard):
+    def fit(shard, collective="nccl", stripe_rows=None):
         wf = G.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
                                           G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
         fitter = nnrt.alignment.DeformableMeshToImageFitter(max_iteration_count=3, preconditioning_dampening_factor=s["lm_factor"],
                                                             arap_term_weight=s["arap_term_weight"])
         if shard:
-            fitter.shard_pixels(rank, world)
+            fitter.shard_pixels(rank, world, stripe_rows=stripe_rows, collective=collective)
         fitter.fit_to_image(wf, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]),
                             anchors=s["anchors"], anchor_weights=s["anchor_weights"])
         fitter.check_status()
@@ -41,18 +41,23 @@ def main():
                                     anchors=s["anchors"], anchor_weights=s["anchor_weights"])
                 fitter.check_status()
                 assert torch.equal(wf.node_rotations, first[0]) and torch.equal(wf.node_translations, first[1]), "graph replay differs from the eager loop"
-            assert len(fitter._shard_graphs) == 1, "the sharded loop was not captured"
+            if collective == "nccl":
+                assert len(fitter._shard_graphs) == 1, "the sharded loop was not captured"
+            else:
+                assert fitter._shard_collective == "peer" and fitter._peer_ready, "the peer reduction fell back to the all-reduce"
         return first
 
     R1, t1 = fit(False)
-    R2, t2 = fit(True)
-    # integer (fixed-point) sums all-reduced as int64: the sharded fit equals the single-GPU fit bit for bit
-    assert torch.equal(t2, t1), float((t2 - t1).abs().max())
-    assert torch.equal(R2, R1), float((R2 - R1).abs().max())
-    # identical state on every rank (replicated solve on all-reduced sums)
-    gathered = [torch.zeros_like(t2) for _ in range(world)]
-    dist.all_gather(gathered, t2)
-    assert all(torch.equal(g, gathered[0]) for g in gathered)
+    # bands + NCCL all-reduce, stripes + NCCL, stripes + the reduction fused into the stem kernel over peer memory (the default)
+    for collective, stripe_rows in (("nccl", None), ("nccl", 8), ("peer", 8), ("peer", 32)):
+        R2, t2 = fit(True, collective, stripe_rows)
+        # integer (fixed-point) sums added as int64 words: the sharded fit equals the single-GPU fit bit for bit
+        assert torch.equal(t2, t1), (collective, stripe_rows, float((t2 - t1).abs().max()))
+        assert torch.equal(R2, R1), (collective, stripe_rows, float((R2 - R1).abs().max()))
+        # identical state on every rank (replicated solve on identical sums)
+        gathered = [torch.zeros_like(t2) for _ in range(world)]
+        dist.all_gather(gathered, t2)
+        assert all(torch.equal(g, gathered[0]) for g in gathered)
     dist.barrier()
     if rank == 0:
         print("PIXEL_SHARD_OK")

@@ -114,3 +114,27 @@ def test_pixel_rows_partition_the_image():
         pixel_rows(2, 2, 480)
     with pytest.raises(ValueError):
         pixel_rows(0, 64, 120)
+
+
+def test_stripes_partition_the_image():
+    """Round-robin stripes of the pixel-sharded mode: every row belongs to exactly one rank, stripes start on the 8-row assembly tile
+    grid, and the shares differ by at most one stripe."""
+    from dynamicfuion_python_b200.pixel_shard import STRIPE_ROWS, stripe_rows_of
+    assert STRIPE_ROWS % 8 == 0
+    for height in (120, 480, 1080, 2160):
+        for world in (1, 2, 3, 4, 8):
+            for stripe in (8, 16, 32, 40):
+                owner = -np.ones(height, int)
+                counts = []
+                for r in range(world):
+                    ranges = stripe_rows_of(r, world, height, stripe)
+                    counts.append(len(ranges))
+                    for b, e in ranges:
+                        assert b % 8 == 0 and b < e <= height and (owner[b:e] == -1).all()
+                        owner[b:e] = r
+                assert (owner >= 0).all() and max(counts) - min(counts) <= 1
+                assert all(owner[v] == (v // stripe) % world for v in range(height))  # csrc/fitter_kernels.cuh::row_owned
+    with pytest.raises(ValueError):
+        stripe_rows_of(0, 2, 480, 12)
+    with pytest.raises(ValueError):
+        stripe_rows_of(2, 2, 480)
