@@ -4,6 +4,7 @@
 // no allocation, no host sync inside the loop).
 #include <vector>
 #include <algorithm>
+#include <mutex>
 #include <cstring>
 #include "fitter_kernels.cuh"
 #include "fixed_accum.cuh"
@@ -638,11 +639,46 @@ extern "C" int nnrt_b200_fitter_create(const nnrt_b200_fitter_options* options, 
 	return kOk;
 }
 
+// Exchange buffers of the peer reduction are exported to other processes (CUDA IPC). Freeing exported memory while an importer still
+// has it mapped is undefined, and a fitter cannot know when its peers have unmapped it, so these buffers (~130 KB each at 249 nodes)
+// are never returned to the driver: a destroyed fitter's buffer goes to a per-process free list and is handed to the next fitter that
+// asks for the same size on the same device.
+namespace {
+struct PooledExchange { void* pointer; size_t bytes; int device; };
+std::mutex g_exchange_mutex;
+std::vector<PooledExchange> g_exchange_pool;
+
+void release_exchange_buffer(void* pointer, size_t bytes) {
+	if (!pointer) return;
+	int device = 0;
+	cudaPointerAttributes attributes{};
+	if (cudaPointerGetAttributes(&attributes, pointer) == cudaSuccess) device = attributes.device; else cudaGetLastError();
+	std::lock_guard<std::mutex> lock(g_exchange_mutex);
+	g_exchange_pool.push_back({pointer, bytes, device});
+}
+void* acquire_exchange_buffer(size_t bytes) {
+	int device = 0;
+	cudaGetDevice(&device);
+	{
+		std::lock_guard<std::mutex> lock(g_exchange_mutex);
+		for (size_t i = 0; i < g_exchange_pool.size(); i++)
+			if (g_exchange_pool[i].bytes == bytes && g_exchange_pool[i].device == device) {
+				void* pointer = g_exchange_pool[i].pointer;
+				g_exchange_pool.erase(g_exchange_pool.begin() + (long) i);
+				return pointer;
+			}
+	}
+	void* pointer = nullptr;
+	if (cudaMalloc(&pointer, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+	return pointer;
+}
+}  // namespace
+
 extern "C" void nnrt_b200_fitter_destroy(nnrt_b200_fitter* f) {
 	if (!f) return;
 	if (f->graph_exec) cudaGraphExecDestroy(f->graph_exec);
 	nnrt_b200_fitter_disable_peer_reduce(f);
-	cudaFree(f->exchange);
+	release_exchange_buffer(f->exchange, f->exchange_bytes);
 	cudaFree(f->arena);
 	cudaFree(f->schur);  // corner buffers are allocated by set_model (their size depends on arrow_base)
 	cudaFree(f->graph_buffer);
@@ -1050,7 +1086,8 @@ extern "C" int nnrt_b200_fitter_peer_exchange(nnrt_b200_fitter* f, void** device
 	NNRT_CHECK_ARG(f, "fitter_peer_exchange: null fitter");
 	if (f->exchange == nullptr) {
 		f->exchange_bytes = exchange_flags_offset(f) + 256;
-		if (cudaMalloc(&f->exchange, f->exchange_bytes) != cudaSuccess) { f->exchange = nullptr; set_last_error("fitter_peer_exchange: cudaMalloc of %zu bytes failed", f->exchange_bytes); return kCudaError; }
+		f->exchange = static_cast<char*>(acquire_exchange_buffer(f->exchange_bytes));
+		if (f->exchange == nullptr) { set_last_error("fitter_peer_exchange: cudaMalloc of %zu bytes failed", f->exchange_bytes); return kCudaError; }
 	}
 	// a fresh exchange: zero sums, no flags raised, iteration counter 0 (every rank does this before the handles are gathered)
 	NNRT_CUDA(cudaDeviceSynchronize());
@@ -1069,7 +1106,10 @@ extern "C" int nnrt_b200_fitter_peer_exchange(nnrt_b200_fitter* f, void** device
 
 extern "C" int nnrt_b200_fitter_disable_peer_reduce(nnrt_b200_fitter* f) {
 	if (!f) return kOk;
-	if (f->peer.world > 1 && f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
+	if (f->peer.world > 1) {
+		cudaDeviceSynchronize();  // this fitter's kernels read the peers' buffers: they must have ended before the mappings go
+		if (f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
+	}
 	for (int r = 0; r < kMaxPeers; r++)
 		if (f->peer_mapped[r]) { cudaIpcCloseMemHandle(f->peer_mapped[r]); f->peer_mapped[r] = nullptr; }
 	f->peer = PeerReduce{};

@@ -89,6 +89,8 @@ class DeformableMeshToImageFitter:
     def _enable_peer_reduce(self, rank, world, group):
         """Collective over `group`: every rank clears its exchange buffer, the CUDA IPC handles are gathered, every rank maps its peers.
         All ranks take the same path: if any of them cannot map a peer (no NVLink / IPC not permitted), all fall back to the all-reduce."""
+        torch.cuda.synchronize()
+        torch.distributed.barrier(group=group)  # no rank is still reading a buffer that is about to be cleared
         handle = (C.c_ubyte * 64)()
         status = _lib.lib().nnrt_b200_fitter_peer_exchange(self._handle, None, None, handle)
         gathered = [None] * world

@@ -150,9 +150,18 @@ class HierarchicalGraphWarpField(GraphWarpField):
     Storage is in VIRTUAL order (layer 0 first, then coarser layers; `node_indices` maps virtual -> original index), because that is
     the order the fitter and the edge list work in; the reference keeps original order and re-gathers on every access. The
     accessors take the reference's `use_virtual_ordering` flag and default to the original order. The reference's own
-    inconsistencies between the two orders (rotations multiplied un-permuted, coverage weights passed
-    un-permuted, WarpMesh against un-permuted nodes) are not reproduced: both orders always describe the same field.
+    inconsistencies between the two orders are not reproduced by default: both orders always describe the
+    same field. Setting `reference_ordering_quirks = True` reproduces them for callers that depend on the
+    reference's exact behaviour with more than one layer (they are no-ops when the order is the identity):
+      * rotate_nodes(deltas, use_virtual_ordering=True) multiplies the ORIGINAL-order rotations by the virtual-order deltas, row by
+        row, and scatters the products through node_indices (HierarchicalGraphWarpField.cpp:271-277);
+      * get_node_coverage_weights(use_virtual_ordering=False) returns the node rotations (.cpp:222-224);
+      * precompute_anchors_and_weights(mesh, use_virtual_ordering=True) with MINIMAL_K_NEIGHBOR_NODE_DISTANCE pairs virtual-order
+        node positions with ORIGINAL-order coverage weights (.cpp:249-253);
+      * warp_mesh always reads its anchors as original-order indices, also those computed in virtual order (WarpField.cpp:129-144).
     `from_graph` takes an explicit graph that is already in virtual order."""
+
+    reference_ordering_quirks = False
 
     def __init__(self, nodes, node_coverage=0.05, threshold_nodes_by_distance_by_default=False, anchor_count=4, minimum_valid_anchor_count=0,
                  warp_node_coverage_computation_method=WarpNodeCoverageComputationMethod.MINIMAL_K_NEIGHBOR_NODE_DISTANCE,
@@ -264,6 +273,8 @@ class HierarchicalGraphWarpField(GraphWarpField):
         return self._to_original(self.node_translations, use_virtual_ordering)
 
     def get_node_coverage_weights(self, use_virtual_ordering=False):
+        if self.reference_ordering_quirks and not use_virtual_ordering:
+            return self._to_original(self.node_rotations, False)  # the reference returns node_rotations here (.cpp:222-224)
         return self._to_original(self.node_coverage_weights, use_virtual_ordering)
 
     def get_warped_nodes(self, use_virtual_ordering=False):
@@ -291,11 +302,32 @@ class HierarchicalGraphWarpField(GraphWarpField):
         super().translate_nodes(self._to_virtual(T.cuda(node_translation_deltas, torch.float32), use_virtual_ordering))
 
     def rotate_nodes(self, node_rotation_deltas, use_virtual_ordering=False):
-        super().rotate_nodes(self._to_virtual(T.cuda(node_rotation_deltas, torch.float32), use_virtual_ordering).contiguous())
+        deltas = T.cuda(node_rotation_deltas, torch.float32)
+        if self.reference_ordering_quirks and use_virtual_ordering and not self._identity_order:
+            # new[i] = R_original[i] deltas_virtual[i], scattered to original index node_indices[i], i.e. virtual slot i (.cpp:271-277)
+            from ..core import matmul3d
+            self.node_rotations = matmul3d(self._to_original(self.node_rotations, False).contiguous(), deltas.contiguous())
+            return
+        super().rotate_nodes(self._to_virtual(deltas, use_virtual_ordering).contiguous())
 
     def precompute_anchors_and_weights(self, input_mesh, use_virtual_ordering=False):
         """Anchors index the virtual order if `use_virtual_ordering` (what the fitter asks for, DeformableMeshToImageFitter.cpp:96-97),
         else the original order (HierarchicalGraphWarpField.cpp:228-256)."""
+        quirk = (self.reference_ordering_quirks and use_virtual_ordering and not self._identity_order
+                 and self.warp_node_coverage_computation_method != WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE)
+        if quirk:  # virtual-order positions against original-order coverage weights (.cpp:249-253)
+            return functional.compute_anchors_and_weights_euclidean_variable_node_weight(
+                T.MeshView(input_mesh).positions, self.nodes, self._to_original(self.node_coverage_weights, False).contiguous(), self.anchor_count,
+                self.minimum_valid_anchor_count)
+        if self.reference_ordering_quirks and not use_virtual_ordering and not self._identity_order:
+            # the reference searches the original-order node array: same anchor sets as below, but in ITS slot order (the K-nearest
+            # search keeps candidates in the order of the scan, KnnUtilities.h), which the blending sums follow
+            positions, nodes = T.MeshView(input_mesh).positions, self._to_original(self.nodes, False).contiguous()
+            if self.warp_node_coverage_computation_method == WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE:
+                return functional.compute_anchors_and_weights_euclidean_fixed_node_weight(positions, nodes, self.anchor_count,
+                                                                                          self.minimum_valid_anchor_count, self.node_coverage)
+            return functional.compute_anchors_and_weights_euclidean_variable_node_weight(
+                positions, nodes, self._to_original(self.node_coverage_weights, False).contiguous(), self.anchor_count, self.minimum_valid_anchor_count)
         anchors, weights = super().precompute_anchors_and_weights(input_mesh)
         if use_virtual_ordering or self._identity_order:
             return anchors, weights
@@ -309,6 +341,8 @@ class HierarchicalGraphWarpField(GraphWarpField):
             kwargs["anchors"], kwargs["anchor_weights"] = args[0], args[1]
             args = args[2:]
         anchors = kwargs.get("anchors")
+        if self.reference_ordering_quirks:
+            use_virtual_ordering = False  # WarpField::WarpMesh has no such flag: anchors always index the original order
         if anchors is not None and not (use_virtual_ordering or self._identity_order):
             anchors = T.cuda(anchors, torch.int32)
             mapped = self._original_to_virtual.to(torch.int32)[anchors.clamp(min=0).long()]

@@ -272,6 +272,7 @@ void bind_geometry(py::module_& m) {
 	hierarchical.def("get_node_translations", [](const H& self, bool v) { return self.to_original(self.node_translations, v).object; },
 	                 "use_virtual_ordering"_a = false);
 	hierarchical.def("get_node_coverage_weights", [](const H& self, bool v) -> py::object {
+		if (self.reference_ordering_quirks && !v) return self.to_original(self.node_rotations, false).object;  // the reference returns node_rotations here (.cpp:222-224)
 		return self.node_coverage_weights.defined() ? self.to_original(self.node_coverage_weights, v).object : py::none();
 	}, "use_virtual_ordering"_a = false);
 	hierarchical.def("get_warped_nodes", [](const H& self, bool v) { return self.to_original(wrap(self.GetWarpedNodes()), v).object; },
@@ -286,7 +287,7 @@ void bind_geometry(py::module_& m) {
 	                 "node_translations"_a, "use_virtual_ordering"_a = false);
 	hierarchical.def("translate_nodes", [](H& self, const py::object& d, bool v) { self.TranslateNodes(self.to_virtual(as_cuda(d, Dtype::Float32), v)); },
 	                 "node_translation_deltas"_a, "use_virtual_ordering"_a = false);
-	hierarchical.def("rotate_nodes", [](H& self, const py::object& d, bool v) { self.RotateNodes(self.to_virtual(as_cuda(d, Dtype::Float32), v)); },
+	hierarchical.def("rotate_nodes", [](H& self, const py::object& d, bool v) { self.RotateNodesOrdered(as_cuda(d, Dtype::Float32), v); },
 	                 "node_rotation_deltas"_a, "use_virtual_ordering"_a = false);
 	hierarchical.def("precompute_anchors_and_weights", [](const H& self, const py::object& mesh, bool v) {
 		return pair_to_tuple(self.PrecomputeAnchorsAndWeights(as_mesh(mesh), v));
@@ -297,7 +298,8 @@ void bind_geometry(py::module_& m) {
 	hierarchical.def("warp_mesh", [](const H& self, const py::object& input_mesh, const py::object& anchors, const py::object& anchor_weights,
 	                                 bool disable_neighbor_thresholding, const py::object& extrinsics, bool use_virtual_ordering) {
 		Dev a = as_cuda(anchors, Dtype::Int32);
-		if (!use_virtual_ordering) a = self.anchors_to_virtual(a);  // supplied anchors index the original order unless told otherwise
+		// supplied anchors index the original order unless told otherwise (with reference_ordering_quirks always: WarpField::WarpMesh has no such flag)
+		if (!use_virtual_ordering || self.reference_ordering_quirks) a = self.anchors_to_virtual(a);
 		return self.WarpMesh(input_mesh, a.object, anchor_weights, disable_neighbor_thresholding, extrinsics);
 	}, "input_mesh"_a, "anchors"_a, "anchor_weights"_a, "disable_neighbor_thresholding"_a = true, "extrinsics"_a = py::none(), "use_virtual_ordering"_a = false);
 	hierarchical.def("clone", [](const H& self) {
@@ -312,6 +314,7 @@ void bind_geometry(py::module_& m) {
 	hierarchical.def_property_readonly("layer_decimation_radii", [](const H& self) { return self.layer_decimation_radii.object; });
 	hierarchical.def_property_readonly("node_indices", [](const H& self) { return self.node_indices.object; });
 	hierarchical.def_readonly("_identity_order", &H::identity_order);
+	hierarchical.def_readwrite("reference_ordering_quirks", &H::reference_ordering_quirks);
 	hierarchical.def_readonly("first_layer_node_count", &H::first_layer_node_count);
 	hierarchical.def_readonly("layer_node_counts", &H::layer_node_counts);
 

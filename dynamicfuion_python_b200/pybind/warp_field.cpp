@@ -237,12 +237,35 @@ Dev HierarchicalGraphWarpField::to_virtual(const Dev& tensor, bool use_virtual_o
 
 // HierarchicalGraphWarpField.cpp:228-256: anchors index the virtual order if asked (the fitter does), else the original order
 std::pair<Dev, Dev> HierarchicalGraphWarpField::PrecomputeAnchorsAndWeights(const Mesh& mesh, bool use_virtual_ordering) const {
+	if (reference_ordering_quirks && use_virtual_ordering && !identity_order &&
+	    warp_node_coverage_computation_method != WarpNodeCoverageComputationMethod::FIXED_NODE_COVERAGE)  // virtual positions, original-order weights (.cpp:249-253)
+		return compute_anchors_euclidean(mesh.positions, nodes, to_original(node_coverage_weights, false), 0.f, anchor_count, minimum_valid_anchor_count);
+	if (reference_ordering_quirks && !use_virtual_ordering && !identity_order) {
+		// the reference searches the original-order node array: same anchor sets as below, in ITS slot order (scan order of the K-nearest search)
+		const Dev original_nodes = to_original(nodes, false);
+		if (warp_node_coverage_computation_method == WarpNodeCoverageComputationMethod::FIXED_NODE_COVERAGE)
+			return compute_anchors_euclidean(mesh.positions, original_nodes, Dev{}, node_coverage, anchor_count, minimum_valid_anchor_count);
+		return compute_anchors_euclidean(mesh.positions, original_nodes, to_original(node_coverage_weights, false), 0.f, anchor_count, minimum_valid_anchor_count);
+	}
 	auto [anchors, weights] = WarpField::PrecomputeAnchorsAndWeights(mesh);
 	if (use_virtual_ordering || identity_order) return {anchors, weights};
 	Dev mapped = empty(anchors.shape, Dtype::Int32);
 	check(nnrt_b200_remap_indices(anchors.data<int32_t>(), anchors.numel(), node_indices.data<int64_t>(), node_count(), mapped.data<int32_t>(), current_stream()));
 	return {mapped, weights};
 }
+void HierarchicalGraphWarpField::RotateNodesOrdered(const Dev& deltas, bool use_virtual_ordering) {
+	if (reference_ordering_quirks && use_virtual_ordering && !identity_order) {
+		// new[i] = R_original[i] deltas_virtual[i], scattered to original index node_indices[i] = virtual slot i (.cpp:271-277)
+		if (deltas.shape != node_rotations.shape) log_error("node_rotation_deltas must have shape " + node_rotations.shape_string());
+		const Dev original = to_original(node_rotations, false);
+		Dev product = empty(node_rotations.shape, Dtype::Float32);
+		check(nnrt_b200_matmul3d_3x3(original.data<float>(), deltas.data<float>(), (int32_t) node_count(), product.data<float>(), current_stream()));
+		node_rotations = product;
+		return;
+	}
+	RotateNodes(to_virtual(deltas, use_virtual_ordering));
+}
+
 Dev HierarchicalGraphWarpField::anchors_to_virtual(const Dev& anchors) const {
 	if (identity_order) return anchors;
 	Dev mapped = empty(anchors.shape, Dtype::Int32);

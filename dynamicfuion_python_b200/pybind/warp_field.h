@@ -72,6 +72,10 @@ public:
 	std::vector<RegularizationLayer> regularization_layers;
 	int64_t first_layer_node_count = 0;
 	bool identity_order = true;
+	// reproduce the reference's inconsistencies between its two node orders (see the Python mirror's class docstring and
+	// HierarchicalGraphWarpField.cpp:222-224, 249-253, 271-277; WarpField.cpp:129-144). Off by default: both orders describe one field.
+	bool reference_ordering_quirks = false;
+	void RotateNodesOrdered(const Dev& deltas, bool use_virtual_ordering);
 };
 
 }  // namespace nnrt::geometry

@@ -216,7 +216,10 @@ int64_t* nnrt_b200_fitter_accumulators(nnrt_b200_fitter* fitter, int64_t* word_c
  *                           with device pointers valid in this process (same-process use; the caller enables peer access);
  *   a host barrier, then fitter_fit (or the split entry points) on every rank, the same number of iterations everywhere.
  * Needs set_pixel_rows / set_pixel_stripes to give each rank its share, and a graph on the fused stem path (no stem row with more than
- * 8 edges, no edges between coarse layers). A rank that waits more than 4 s for a peer raises an error status instead of hanging. */
+ * 8 edges, no edges between coarse layers). A rank that waits more than 4 s for a peer raises an error status instead of hanging.
+ * Before fitter_peer_exchange (which clears the buffer) and before disable_peer_reduce / fitter_destroy, every rank's stream must be
+ * idle and the ranks must have met at a host barrier: a peer may still be reading this rank's sums of the last iteration. Exchange
+ * buffers are pooled for the life of the process, never freed, so a late importer never holds a mapping of freed memory. */
 int nnrt_b200_fitter_peer_exchange(nnrt_b200_fitter* fitter, void** device_pointer, int64_t* byte_count, void* ipc_handle_out);
 int nnrt_b200_fitter_enable_peer_reduce(nnrt_b200_fitter* fitter, int32_t rank, int32_t world_size, void* const* exchange_pointers);
 int nnrt_b200_fitter_enable_peer_reduce_ipc(nnrt_b200_fitter* fitter, int32_t rank, int32_t world_size, const void* ipc_handles);

@@ -51,6 +51,9 @@ def main():
     # bands + NCCL all-reduce, stripes + NCCL, stripes + the reduction fused into the stem kernel over peer memory (the default)
     for collective, stripe_rows in (("nccl", None), ("nccl", 8), ("peer", 8), ("peer", 32)):
         R2, t2 = fit(True, collective, stripe_rows)
+        if os.environ.get("NNRT_B200_WORKER_TRACE"):
+            torch.cuda.synchronize()
+            print(f"[rank {rank}] {collective} stripe_rows={stripe_rows} done, probe {float(torch.zeros(1, device='cuda').sum())}", flush=True)
         # integer (fixed-point) sums added as int64 words: the sharded fit equals the single-GPU fit bit for bit
         assert torch.equal(t2, t1), (collective, stripe_rows, float((t2 - t1).abs().max()))
         assert torch.equal(R2, R1), (collective, stripe_rows, float((R2 - R1).abs().max()))

@@ -145,6 +145,64 @@ def test_orders_are_consistent(nnrt):
     assert torch.allclose(got.positions, want.positions, atol=1e-6) and torch.equal(got.positions, got_virtual.positions)
 
 
+def test_reference_ordering_quirks_flag(nnrt):
+    """with `reference_ordering_quirks` set, the class reproduces the reference's inconsistencies between its two node
+    orders (HierarchicalGraphWarpField.cpp:222-224, 249-253, 271-277; WarpField.cpp:129-144), each checked here against the formula
+    the reference's code evaluates, written in numpy on original-order arrays; without the flag both orders describe one field."""
+    s = synthetic.make_scene("tinyr", 120, 160)
+    rng = np.random.default_rng(5)
+    nodes = s["positions"][rng.choice(len(s["positions"]), 60, replace=False)]
+    G = nnrt.geometry
+    method = G.WarpNodeCoverageComputationMethod
+    wf = G.HierarchicalGraphWarpField(nodes, 0.02, False, 4, 0, method.MINIMAL_K_NEIGHBOR_NODE_DISTANCE, 2, 3)
+    assert not wf._identity_order and not wf.reference_ordering_quirks
+    index = _np(wf.node_indices)  # virtual -> original
+    rotations, _ = synthetic.smooth_node_motion(nodes, 20.0, 0.0, np.random.default_rng(1))
+    deltas, _ = synthetic.smooth_node_motion(nodes, 15.0, 0.0, np.random.default_rng(2))
+    rotations, deltas = rotations.astype(np.float32), deltas.astype(np.float32)
+    weights_original = _np(wf.get_node_coverage_weights()).copy()
+    mesh = (s["positions"], s["normals"], s["triangles"])
+
+    # consistent behaviour (flag off): rotating in virtual order == rotating in original order with the permuted deltas
+    wf.set_node_rotations(rotations)
+    wf.rotate_nodes(deltas[index], use_virtual_ordering=True)
+    assert np.allclose(_np(wf.get_node_rotations()), rotations @ deltas, atol=1e-6)
+
+    wf.reference_ordering_quirks = True
+    # (1) RotateNodes(deltas, true): new[i] = R_original[i] deltas[i], then R_original[index[i]] = new[i]
+    wf.set_node_rotations(rotations)
+    virtual_deltas = deltas[index]
+    wf.rotate_nodes(virtual_deltas, use_virtual_ordering=True)
+    want = np.empty_like(rotations)
+    want[index] = rotations @ virtual_deltas
+    assert np.allclose(_np(wf.get_node_rotations()), want, atol=1e-6)
+    assert not np.allclose(want, rotations @ deltas, atol=1e-3)  # the quirk is visible on this field
+    # original-order rotation stays consistent
+    wf.set_node_rotations(rotations)
+    wf.rotate_nodes(deltas)
+    assert np.allclose(_np(wf.get_node_rotations()), rotations @ deltas, atol=1e-6)
+    # (2) GetNodeCoverageWeights(false) returns the rotations
+    assert np.array_equal(_np(wf.get_node_coverage_weights()), _np(wf.get_node_rotations()))
+    assert np.array_equal(_np(wf.get_node_coverage_weights(True)), weights_original[index])
+    # (3) PrecomputeAnchorsAndWeights(mesh, true), variable coverage: virtual-order positions with ORIGINAL-order weights
+    a_quirk, w_quirk = wf.precompute_anchors_and_weights(mesh, use_virtual_ordering=True)
+    a_want, w_want = G.functional.compute_anchors_and_weights_euclidean_variable_node_weight(s["positions"], nodes[index], weights_original, 4, 0)
+    assert np.array_equal(_np(a_quirk), _np(a_want)) and np.array_equal(_np(w_quirk), _np(w_want))
+    a_orig, w_orig = wf.precompute_anchors_and_weights(mesh)  # original order: consistent in the reference too
+    a_flat, w_flat = G.functional.compute_anchors_and_weights_euclidean_variable_node_weight(s["positions"], nodes, weights_original, 4, 0)
+    assert np.array_equal(_np(a_orig), _np(a_flat)) and np.allclose(_np(w_orig), _np(w_flat), atol=1e-7)
+    # (4) WarpMesh reads anchors as original-order indices whatever order they were computed in
+    wf.set_node_rotations(rotations)
+    t = rng.normal(0, 0.01, (60, 3)).astype(np.float32)
+    wf.set_node_translations(t)
+    got = wf.warp_mesh(mesh, a_quirk, w_quirk, use_virtual_ordering=True)
+    want_mesh = G.functional.warp_triangle_mesh(mesh, nodes, rotations, t, a_quirk, w_quirk)
+    assert torch.allclose(got.positions, want_mesh.positions, atol=1e-6)
+    wf.reference_ordering_quirks = False
+    consistent = wf.warp_mesh(mesh, a_quirk, w_quirk, use_virtual_ordering=True)
+    assert not torch.allclose(consistent.positions, want_mesh.positions, atol=1e-4)
+
+
 def test_fit_with_constructed_warp_field_matches_oracle(nnrt, oracle):
     """End to end: nodes sampled from the mesh, layers + edges built on the device by the constructor, anchors computed by the fitter
     in virtual order, one GN iteration (the 1e-3 per-iteration delta bar) — against the oracle running on the oracle-built hierarchy."""
