@@ -55,23 +55,27 @@ __host__ __device__ constexpr size_t assemble_shared_bytes(int anchor_count) {
 // that hangs off the face index is issued in one burst: the 3A vertex-anchor records and the face's node table travel
 // global -> shared with cp.async while the residual and the barycentric chain are computed from registers; the node-voting
 // loop then touches shared memory only.
-template<int A>
+// kSharded = false is the single-GPU kernel (no stripe arithmetic, one accumulator buffer); true adds the striped tile-row mapping and
+// the parity-selected accumulator buffer of a pixel-sharded fit.
+template<int A, bool kSharded>
 __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDeviceData d, DataTermParams p) {
 	constexpr int kMaxEntries = 3 * A, T = kAssembleThreads;
 	extern __shared__ __align__(16) unsigned char assemble_smem[];
 	float4* s_rec = reinterpret_cast<float4*>(assemble_smem);  // [3A * 2][T]: anchor records, then J contributions (+ node id)
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-	// peer-reduced pixel shard (fitter_kernels.cuh::PeerReduce): two buffers alternate by iteration parity
-	unsigned long long* const accumulators = d.accumulators + (d.accum_epoch ? (long long) (*d.accum_epoch & 1ull) * d.accum_parity_words : 0ll);
 	// tiles are visited in a scrambled order (multiplication by a prime modulo the tile count): the surface covers a compact
 	// part of the image, and in raster order its expensive tiles would reach the SMs as one late clump
 	const unsigned tile_count = gridDim.x * gridDim.y, linear = blockIdx.y * gridDim.x + blockIdx.x;
 	const unsigned tile = (tile_count % 1009u) && tile_count < (1u << 22) ? (linear * 1009u) % tile_count : linear;  // 32-bit: no overflow below 2^22 tiles
 	// tile row -> image row: tile rows are numbered over the stripes this GPU owns (fitter_kernels.cuh; 8-row stripes dealt to one GPU = every row)
-	const int tile_row = (int) (tile / gridDim.x), tiles_per_stripe = p.stripe_rows >> 3;
-	const int stripe = p.stripe_index + p.stripe_count * (tile_row / tiles_per_stripe);
+	const int tile_row = (int) (tile / gridDim.x);
 	const int tile_x = (int) (tile % gridDim.x) * 16 + (warp & 1) * 8;
-	const int tile_y = p.row_begin + stripe * p.stripe_rows + (tile_row % tiles_per_stripe) * 8 + (warp >> 1) * 4;
+	int tile_y = p.row_begin + tile_row * 8 + (warp >> 1) * 4;
+	if (kSharded && p.stripe_count > 1) {  // (kept off the unsharded path: three of four tiles of a frame are empty and cost little more than this prologue)
+		const int tiles_per_stripe = p.stripe_rows >> 3;
+		const int stripe = p.stripe_index + p.stripe_count * (tile_row / tiles_per_stripe);
+		tile_y = p.row_begin + stripe * p.stripe_rows + (tile_row % tiles_per_stripe) * 8 + (warp >> 1) * 4;
+	}
 	const int u = tile_x + (lane & 7), v = tile_y + (lane >> 3);
 	const bool in_image = u < p.width && v < p.row_end;
 	const int64_t px = (int64_t) v * p.width + u;
@@ -192,6 +196,9 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 	}
 	// node voting: the leader's first pending node is taken up by every lane that has it among its pairs; a node appears at most
 	// once per face vertex, and the pairs are summed in face-vertex order like the reference's per-pixel accumulation
+	// peer-reduced pixel shard (fitter_kernels.cuh::PeerReduce): two buffers alternate by iteration parity
+	unsigned long long* accumulators = d.accumulators;
+	if (kSharded && d.accum_epoch) accumulators += (long long) (*d.accum_epoch & 1ull) * d.accum_parity_words;
 	while (true) {
 		const unsigned active = __ballot_sync(0xFFFFFFFFu, pending != 0u);
 		if (active == 0u) break;
@@ -236,11 +243,14 @@ template<int A>
 static int launch_assemble_for(const FitterDeviceData& d, const DataTermParams& p, cudaStream_t s) {
 	constexpr size_t bytes = assemble_shared_bytes(A);
 	static SharedMemoryOptIn opt_in;
-	if (bytes > 48 * 1024 && opt_in.ensure(assemble_kernel<A>, bytes) != kOk) return kCudaError;
+	static SharedMemoryOptIn opt_in_sharded;
+	const bool sharded = p.stripe_count > 1 || d.accum_epoch != nullptr;
+	if (bytes > 48 * 1024 && (sharded ? opt_in_sharded.ensure(assemble_kernel<A, true>, bytes) : opt_in.ensure(assemble_kernel<A, false>, bytes)) != kOk) return kCudaError;
 	const int stripes = (p.row_end - p.row_begin + p.stripe_rows - 1) / p.stripe_rows;
 	const int owned = p.stripe_index < stripes ? (stripes - p.stripe_index + p.stripe_count - 1) / p.stripe_count : 0;
 	const dim3 grid((p.width + 15) / 16, max(1, owned * (p.stripe_rows / 8)));  // a GPU that owns nothing still resets the band queue counter
-	assemble_kernel<A><<<grid, kAssembleThreads, bytes, s>>>(d, p);
+	if (sharded) assemble_kernel<A, true><<<grid, kAssembleThreads, bytes, s>>>(d, p);
+	else assemble_kernel<A, false><<<grid, kAssembleThreads, bytes, s>>>(d, p);
 	return kOk;
 }
 

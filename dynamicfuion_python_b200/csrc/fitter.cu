@@ -231,33 +231,42 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 	return t;
 }
 // every warp reports once it no longer needs this iteration's epoch; the last one advances it
-__device__ __forceinline__ void peer_warp_done(const PeerReduce& peer, unsigned long long epoch, int lane) {
-	if (peer.world <= 1 || lane != 0) return;
+__device__ __forceinline__ void peer_warp_done(const PeerReduce* peer, unsigned long long epoch, int lane) {
+	if (lane != 0) return;
 	__threadfence();
-	if (atomicAdd(peer.done, 1u) == gridDim.x * (blockDim.x >> 5) - 1u) {
-		*peer.done = 0u;
-		*peer.epoch = epoch + 1ull;
+	if (atomicAdd(peer->done, 1u) == gridDim.x * (blockDim.x >> 5) - 1u) {
+		*peer->done = 0u;
+		*peer->epoch = epoch + 1ull;
 	}
 }
 
+// kPeer = false is the single-GPU / all-reduce kernel, byte for byte what it was before the peer reduction existed (the peer table by
+// value, or a local copy of it, gave this kernel a 300-byte stack frame and 8 more registers: 0.5 us on every single-GPU iteration);
+// kPeer = true reads the table from device memory field by field.
+template<bool kPeer>
 __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDeviceData g, ReducedSystem red, const float* __restrict__ rotations,
                                                                       const float* __restrict__ translations, unsigned long long* __restrict__ accumulators,
-                                                                      float* __restrict__ diag, float* __restrict__ rhs, PeerReduce peer) {
+                                                                      float* __restrict__ diag, float* __restrict__ rhs, const PeerReduce* __restrict__ peer) {
 	__shared__ float s_H[kStemWarps][36], s_b[kStemWarps][8], s_dinv[kStemWarps][36], s_dE[kStemWarps][20], s_y[kStemWarps][8];
 	__shared__ float s_G[kStemWarps][kMaxStemDegree][18], s_Y[kStemWarps][kMaxStemDegree][18];
 	__shared__ int s_edge[kStemWarps][kMaxStemDegree];
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const int node = blockIdx.x * kStemWarps + wib;
 	unsigned long long epoch = 0ull;
-	if (peer.world > 1) {
-		epoch = *reinterpret_cast<volatile unsigned long long*>(peer.epoch);
+	int world = 1, rank = 0;
+	if constexpr (kPeer) {
+		world = peer->world; rank = peer->rank;
+		epoch = *reinterpret_cast<volatile unsigned long long*>(peer->epoch);
 		__syncthreads();  // every warp of the CTA holds the epoch before any of them can report
-		if (blockIdx.x == 0 && (int) threadIdx.x < peer.world && (int) threadIdx.x != peer.rank) {
+		if (blockIdx.x == 0 && (int) threadIdx.x < world && (int) threadIdx.x != rank) {
 			__threadfence_system();
-			st_release_sys(peer.peer_flags[threadIdx.x] + peer.rank, epoch + 1ull);
+			st_release_sys(peer->peer_flags[threadIdx.x] + rank, epoch + 1ull);
 		}
 	}
-	if (node >= g.node_count) { peer_warp_done(peer, epoch, lane); return; }
+	if (node >= g.node_count) {
+		if constexpr (kPeer) peer_warp_done(peer, epoch, lane);
+		return;
+	}
 	float* H = s_H[wib];
 	float* b = s_b[wib];
 	// ---- stem node: lane q fetches and evaluates outgoing edge q, so the dependent loads of all edges (edge list -> endpoints ->
@@ -277,21 +286,23 @@ __global__ void __launch_bounds__(kStemWarps * 32) system_stem_kernel(GraphDevic
 	{
 		ulonglong2* acc = reinterpret_cast<ulonglong2*>(accumulators) + (int64_t) node * kAccumStride;
 		ulonglong2 words = make_ulonglong2(0ull, 0ull);
-		if (peer.world > 1) {
-			if (lane < peer.world && lane != peer.rank) {
+		if constexpr (kPeer) {
+			if (lane < world && lane != rank) {
+				const unsigned long long* flag = peer->flags + lane;
 				const unsigned long long start = global_timer_ns();
-				while (ld_acquire_sys(peer.flags + lane) < epoch + 1ull)
+				while (ld_acquire_sys(flag) < epoch + 1ull)
 					if (global_timer_ns() - start > kPeerWaitNs) { atomicExch(red.flags + 4, 1); break; }
 			}
 			__syncwarp();
-			const long long current = (long long) (epoch & 1ull) * peer.parity_words, previous = (long long) ((epoch & 1ull) ^ 1ull) * peer.parity_words;
+			const long long words_per_buffer = peer->parity_words;
+			const long long current = (long long) (epoch & 1ull) * words_per_buffer, previous = (long long) ((epoch & 1ull) ^ 1ull) * words_per_buffer;
 			const long long entry = ((long long) node * kAccumStride + lane) * 2;
 			if (lane < 27) {
-				for (int r = 0; r < peer.world; r++) {
-					const ulonglong2 w = ld_relaxed_sys_v2(peer.peer_accum[r] + current + entry);
+				for (int r = 0; r < world; r++) {
+					const ulonglong2 w = ld_relaxed_sys_v2(peer->peer_accum[r] + current + entry);
 					words.x += w.x; words.y += w.y;  // two's-complement and unsigned words: plain 64-bit adds, any order
 				}
-				*reinterpret_cast<ulonglong2*>(const_cast<unsigned long long*>(peer.peer_accum[peer.rank]) + previous + entry) = make_ulonglong2(0ull, 0ull);
+				*reinterpret_cast<ulonglong2*>(const_cast<unsigned long long*>(peer->peer_accum[rank]) + previous + entry) = make_ulonglong2(0ull, 0ull);
 			}
 			peer_warp_done(peer, epoch, lane);
 		} else if (lane < 27) {
@@ -676,8 +687,8 @@ void* acquire_exchange_buffer(size_t bytes) {
 
 extern "C" void nnrt_b200_fitter_destroy(nnrt_b200_fitter* f) {
 	if (!f) return;
-	if (f->graph_exec) cudaGraphExecDestroy(f->graph_exec);
-	nnrt_b200_fitter_disable_peer_reduce(f);
+	nnrt_b200_fitter_disable_peer_reduce(f);  // waits for this fitter's kernels if they read peers' buffers, unmaps them
+	if (f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }
 	release_exchange_buffer(f->exchange, f->exchange_bytes);
 	cudaFree(f->arena);
 	cudaFree(f->schur);  // corner buffers are allocated by set_model (their size depends on arrow_base)
@@ -943,8 +954,13 @@ namespace nnrt_b200 {
 
 struct IterationContext {
 	FitterDeviceData d; GraphDeviceData g; ArrowheadSystem sys; ReducedSystem red; DataTermParams p; NdcCamera cam; Rigid extrinsics;
-	PeerReduce peer;
+	PeerReduce peer; const PeerReduce* peer_device;  // host copy (world > 1: on) and the copy the stem kernel reads
 };
+
+// exchange buffer: [2 accumulator buffers][flag row, kMaxPeers words][iteration counter][done counter] ... [PeerReduce table at +512]
+static size_t exchange_flags_offset(const nnrt_b200_fitter* f) { return ((size_t) f->N * kAccumStride * 2 * 2 * sizeof(unsigned long long) + 255) & ~size_t(255); }
+static size_t exchange_table_offset(const nnrt_b200_fitter* f) { return exchange_flags_offset(f) + 512; }
+static_assert(sizeof(PeerReduce) <= 512 && kMaxPeers * sizeof(unsigned long long) + 16 <= 512, "exchange buffer tail layout");
 
 static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const double* T) {
 	IterationContext c{};
@@ -954,7 +970,7 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	c.d.warped_positions = f->wpos; c.d.warped_normals = f->wnrm; c.d.vertex_jacobians = f->vjac;
 	c.d.keys = f->keys; c.d.band_queue = f->queue; c.d.counters = f->counters; c.d.band_queue_capacity = (int) (f->F + 65536);
 	c.d.reference_points = f->refpts; c.d.accumulators = f->accum;
-	c.peer = f->peer;
+	c.peer = f->peer; c.peer_device = f->exchange ? reinterpret_cast<const PeerReduce*>(f->exchange + exchange_table_offset(f)) : nullptr;
 	if (f->peer.world > 1) {  // the sums go to the exported buffer of this iteration's parity
 		c.d.accumulators = reinterpret_cast<unsigned long long*>(f->exchange);
 		c.d.accum_epoch = f->peer.epoch; c.d.accum_parity_words = f->peer.parity_words;
@@ -1025,7 +1041,9 @@ static int enqueue_solve(nnrt_b200_fitter* f, const IterationContext& base, int 
 	c.sys.update_mode = iteration_mode;
 	if (f->fused_stem) {
 		c.red.update_mode = iteration_mode;
-		system_stem_kernel<<<(f->N + kStemWarps - 1) / kStemWarps, kStemWarps * 32, 0, s>>>(c.g, c.red, R, t, f->accum, f->sys_diag, f->sys_rhs, c.peer);
+		const unsigned stem_grid = (f->N + kStemWarps - 1) / kStemWarps;
+		if (c.peer.world > 1) system_stem_kernel<true><<<stem_grid, kStemWarps * 32, 0, s>>>(c.g, c.red, R, t, f->accum, f->sys_diag, f->sys_rhs, c.peer_device);
+		else system_stem_kernel<false><<<stem_grid, kStemWarps * 32, 0, s>>>(c.g, c.red, R, t, f->accum, f->sys_diag, f->sys_rhs, nullptr);
 		if (ev) { cudaEventRecord(ev[5], s); cudaEventRecord(ev[6], s); }
 		const int rc = launch_reduced_corner_solve(c.red, f->x, R, t, s);
 		if (ev) cudaEventRecord(ev[7], s);
@@ -1080,12 +1098,11 @@ extern "C" int nnrt_b200_fitter_set_pixel_stripes(nnrt_b200_fitter* f, int32_t s
 }
 
 // ---- peer-reduced pixel shard ---------------------------------------------------------------------------------------------
-static size_t exchange_flags_offset(const nnrt_b200_fitter* f) { return ((size_t) f->N * kAccumStride * 2 * 2 * sizeof(unsigned long long) + 255) & ~size_t(255); }
-
 extern "C" int nnrt_b200_fitter_peer_exchange(nnrt_b200_fitter* f, void** device_pointer, int64_t* byte_count, void* ipc_handle_out) {
 	NNRT_CHECK_ARG(f, "fitter_peer_exchange: null fitter");
+	nnrt_b200_fitter_disable_peer_reduce(f);  // the buffer (and the peer table in it) is cleared below: the mode restarts with enable_peer_reduce
 	if (f->exchange == nullptr) {
-		f->exchange_bytes = exchange_flags_offset(f) + 256;
+		f->exchange_bytes = exchange_table_offset(f) + 512;
 		f->exchange = static_cast<char*>(acquire_exchange_buffer(f->exchange_bytes));
 		if (f->exchange == nullptr) { set_last_error("fitter_peer_exchange: cudaMalloc of %zu bytes failed", f->exchange_bytes); return kCudaError; }
 	}
@@ -1134,6 +1151,7 @@ extern "C" int nnrt_b200_fitter_enable_peer_reduce(nnrt_b200_fitter* f, int32_t 
 	p.flags = p.peer_flags[rank];
 	p.epoch = p.flags + kMaxPeers;
 	p.done = reinterpret_cast<unsigned int*>(p.flags + kMaxPeers + 1);
+	NNRT_CUDA(cudaMemcpy(f->exchange + exchange_table_offset(f), &p, sizeof(p), cudaMemcpyHostToDevice));
 	f->peer = p;
 	return kOk;
 }

@@ -80,11 +80,28 @@ __device__ __forceinline__ RasterParams raster_params(const DataTermParams& p) {
 }
 
 // K3. One thread per face: gather + project (replaces ExtractFaceVertices + the bbox pass + binning), rasterise inline
-// when the pixel box is small, otherwise enqueue row bands. Pixel-sharded fits walk only the rows of this GPU's band / stripes
-// (fitter_kernels.cuh::row_owned); a larger box queues its band items stripe by stripe so that no warp of the drain kernel walks
-// rows of another GPU. Queue slots are reserved with ONE atomic per warp (at 4K nearly every face takes the queue path, and 81 608
-// atomics on one counter were a fixed ~40 us that no amount of sharding removed).
+// when the pixel box is small, otherwise enqueue row bands.
 __global__ void __launch_bounds__(256) face_raster_kernel(FitterDeviceData d, DataTermParams p, NdcCamera cam) {
+	const int64_t f = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (f >= d.face_count) return;
+	FaceNdc face;
+	if (!load_fitter_face(d, cam, (int) f, face)) return;
+	const RasterParams rp = raster_params(p);
+	PixelBox box;
+	if (!face_pixel_box(face, rp, box)) return;
+	box.v0 = max(box.v0, p.row_begin);  // pixel-sharded fits: this GPU's band of rows only
+	box.v1 = min(box.v1, p.row_end - 1);
+	if (box.v0 > box.v1) return;
+	int rows_per_band;
+	const int bands = raster_face_or_count_bands(face, (int) f, rp, box, d.keys, nullptr, rows_per_band);
+	if (bands > 0) push_bands((int) f, box, rows_per_band, bands, d.band_queue, d.counters, d.band_queue_capacity, d.counters + 1);
+}
+
+// K3 for frames whose faces mostly take the queue (large images) and for striped pixel shards: the same per-face work, but only rows
+// this GPU owns are walked (fitter_kernels.cuh::row_owned), a larger box queues its band items stripe by stripe so that no warp of the
+// drain kernel walks rows of another GPU, and queue slots are reserved with ONE atomic per warp (at 3840 x 2160 nearly every face takes
+// the queue path: 81 608 atomics on one counter were a fixed 6 us that no amount of sharding removed).
+__global__ void __launch_bounds__(256) face_raster_queue_kernel(FitterDeviceData d, DataTermParams p, NdcCamera cam) {
 	const int64_t f = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
 	const int lane = threadIdx.x & 31;
 	const RasterParams rp = raster_params(p);
@@ -176,7 +193,11 @@ void launch_warp_vertices(const FitterDeviceData& d, const float* rotations, con
 
 void launch_face_raster(const FitterDeviceData& d, const DataTermParams& p, const NdcCamera& cam, cudaStream_t s) {
 	if (d.face_count == 0) return;
-	face_raster_kernel<<<blocks_for(d.face_count, 64), 64, 0, s>>>(d, p, cam);
+	// the queue-oriented form pays a warp scan per 32 faces: worth it when faces are large (more pixels than faces by 4x: most boxes
+	// exceed the inline limit) or the rows are striped
+	const bool queue_form = p.stripe_count > 1 || (int64_t) p.height * p.width > 4 * d.face_count * (int64_t) kSmallBoxPixels;
+	if (queue_form) face_raster_queue_kernel<<<blocks_for(d.face_count, 64), 64, 0, s>>>(d, p, cam);
+	else face_raster_kernel<<<blocks_for(d.face_count, 64), 64, 0, s>>>(d, p, cam);
 }
 
 void launch_band_raster(const FitterDeviceData& d, const DataTermParams& p, const NdcCamera& cam, cudaStream_t s) {
