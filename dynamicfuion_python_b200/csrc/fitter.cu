@@ -563,7 +563,7 @@ struct nnrt_b200_fitter {
 	int *corner_edge_ids = nullptr, *corner_upper_coords = nullptr, corner_edge_count = 0;
 	float* corner_upper = nullptr;
 	float *pair_blocks = nullptr, *reduced_packed = nullptr, *reduced_dense = nullptr, *reduced_dense_rhs = nullptr;
-	unsigned long long* keys; nnrt_b200::BandItem* queue; int* counters;
+	unsigned long long* keys; nnrt_b200::FaceBandItem* queue; int* counters;
 	int32_t* diag_faces; float* diag_res; uint8_t* diag_mask;
 	// cached graph
 	cudaGraphExec_t graph_exec = nullptr;
@@ -595,7 +595,7 @@ static size_t layout(nnrt_b200_fitter* f, bool assign) {
 	f->in_offsets = f->take<int>(N + 2); f->in_edges = f->take<int>(E + 1); f->wing_columns = f->take<int>(E + 1);
 	f->refpts = f->take<float4>(PX);
 	f->keys = f->take<unsigned long long>(PX);
-	f->queue = f->take<BandItem>(F + 65536); f->counters = f->take<int>(8);
+	f->queue = f->take<FaceBandItem>(F + 65536); f->counters = f->take<int>(8);
 	f->accum = f->take<unsigned long long>((int64_t) N * kAccumStride * 2);
 	f->sys_diag = f->take<float>((int64_t) N * 36); f->sys_rhs = f->take<float>(nmax); f->wing = f->take<float>((E + 1) * 36);
 	f->dinv = f->take<float>((int64_t) N * 36); f->stem_y = f->take<float>(nmax); f->wing_x = f->take<float>((E + 1) * 36);

@@ -79,6 +79,13 @@ __device__ __forceinline__ RasterParams raster_params(const DataTermParams& p) {
 	return rp;
 }
 
+__device__ __forceinline__ FaceBandItem make_band_item(const FaceNdc& f, int face, const PixelBox& box, int y0, int y1) {
+	FaceBandItem it;
+	it.face = face; it.y0 = y0; it.y1 = y1; it.u0 = box.u0; it.u1 = box.u1;
+	it.z0 = f.z0; it.z1 = f.z1; it.z2 = f.z2; it.v0 = f.v0; it.v1 = f.v1; it.v2 = f.v2; it.pad0 = 0.f; it.pad1 = 0.f;
+	return it;
+}
+
 // K3. One thread per face: gather + project (replaces ExtractFaceVertices + the bbox pass + binning), rasterise inline
 // when the pixel box is small, otherwise enqueue row bands.
 __global__ void __launch_bounds__(256) face_raster_kernel(FitterDeviceData d, DataTermParams p, NdcCamera cam) {
@@ -94,7 +101,14 @@ __global__ void __launch_bounds__(256) face_raster_kernel(FitterDeviceData d, Da
 	if (box.v0 > box.v1) return;
 	int rows_per_band;
 	const int bands = raster_face_or_count_bands(face, (int) f, rp, box, d.keys, nullptr, rows_per_band);
-	if (bands > 0) push_bands((int) f, box, rows_per_band, bands, d.band_queue, d.counters, d.band_queue_capacity, d.counters + 1);
+	if (bands > 0) {
+		const int slot = atomicAdd(d.counters, bands);
+		if (slot + bands > d.band_queue_capacity) { atomicExch(d.counters + 1, 1); return; }
+		for (int b = 0; b < bands; b++) {
+			const int y0 = box.v0 + b * rows_per_band;
+			d.band_queue[slot + b] = make_band_item(face, (int) f, box, y0, min(box.v1, y0 + rows_per_band - 1));
+		}
+	}
 }
 
 // K3 for frames whose faces mostly take the queue (large images) and for striped pixel shards: the same per-face work, but only rows
@@ -161,15 +175,37 @@ __global__ void __launch_bounds__(256) face_raster_queue_kernel(FitterDeviceData
 	for (int stripe = first; stripe <= last; stripe += step) {
 		int y0, y1;
 		stripe_rows(stripe, y0, y1);
-		for (int y = y0; y <= y1; y += rows_per_band) d.band_queue[slot++] = BandItem{(int) f, y, min(y1, y + rows_per_band - 1), 0};
+		for (int y = y0; y <= y1; y += rows_per_band) d.band_queue[slot++] = make_band_item(face, (int) f, box, y, min(y1, y + rows_per_band - 1));
 	}
 }
 
-// K5. One warp per queued row band.
+// K5. One warp per queued row band; the next item's four words are requested before the current item's pixels are walked.
 __global__ void __launch_bounds__(256) band_raster_kernel(FitterDeviceData d, DataTermParams p, NdcCamera cam) {
 	const RasterParams rp = raster_params(p);
-	drain_band_queue(d.band_queue, d.counters, d.band_queue_capacity, rp, d.keys, nullptr,
-	                 [&](int f, FaceNdc& out) { load_fitter_face(d, cam, f, out); });
+	const int lane = threadIdx.x & 31;
+	const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int warp_count = (gridDim.x * blockDim.x) >> 5;
+	const int count = min(d.counters[0], d.band_queue_capacity);
+	const int4* queue = reinterpret_cast<const int4*>(d.band_queue);
+	int item = warp;
+	if (item >= count) return;
+	int4 w0 = queue[item * 4], w1 = queue[item * 4 + 1], w2 = queue[item * 4 + 2], w3 = queue[item * 4 + 3];
+	while (true) {
+		const int next = item + warp_count;
+		int4 n0 = w0, n1 = w1, n2 = w2, n3 = w3;
+		if (next < count) { n0 = queue[next * 4]; n1 = queue[next * 4 + 1]; n2 = queue[next * 4 + 2]; n3 = queue[next * 4 + 3]; }
+		FaceNdc f;
+		f.z0 = __int_as_float(w1.y); f.z1 = __int_as_float(w1.z); f.z2 = __int_as_float(w1.w);
+		f.v0 = make_float2(__int_as_float(w2.x), __int_as_float(w2.y)); f.v1 = make_float2(__int_as_float(w2.z), __int_as_float(w2.w));
+		f.v2 = make_float2(__int_as_float(w3.x), __int_as_float(w3.y));
+		const int face = w0.x, y0 = w0.y, y1 = w0.z, u0 = w0.w, bw = w1.x - u0 + 1;
+		const int total = bw * (y1 - y0 + 1);
+		const bool within_blur = face_box_within_blur(f, rp.blur_radius);
+		for (int k = lane; k < total; k += 32) raster_pixel(f, face, u0 + k % bw, y0 + k / bw, rp, d.keys, nullptr, within_blur);
+		if (next >= count) break;
+		item = next; w0 = n0; w1 = n1; w2 = n2; w3 = n3;
+	}
+	(void) cam;
 }
 
 __global__ void __launch_bounds__(256) fill_keys_kernel2(unsigned long long* keys, int64_t n) {
@@ -201,7 +237,7 @@ void launch_face_raster(const FitterDeviceData& d, const DataTermParams& p, cons
 }
 
 void launch_band_raster(const FitterDeviceData& d, const DataTermParams& p, const NdcCamera& cam, cudaStream_t s) {
-	band_raster_kernel<<<148 * 2, 256, 0, s>>>(d, p, cam);
+	band_raster_kernel<<<148 * 3, 256, 0, s>>>(d, p, cam);  // 77 registers: three CTAs per SM
 }
 
 void launch_fill_keys(unsigned long long* keys, int64_t n, cudaStream_t s) {

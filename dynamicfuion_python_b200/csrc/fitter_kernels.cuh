@@ -33,6 +33,18 @@ struct PeerReduce {
 	const unsigned long long* peer_accum[kMaxPeers];  // every rank's [2][parity_words] accumulators, as mapped into this process ([rank] = own)
 };
 
+// Work item of the fitter's band queue: rows [y0, y1] x columns [u0, u1] of one face, with the face's projected vertices. The
+// stage-level rasteriser's 16-byte BandItem makes the draining warp re-derive the face (item -> triangle -> three vertices -> project
+// -> pixel box: three dependent round trips per item, which is what bound band_raster_kernel at 3840 x 2160: 0.19 ms for ~100 k
+// items); here the thread that queued the item already had all of it in registers, and the drain reads four 16-byte words.
+struct __align__(16) FaceBandItem {
+	int face, y0, y1, u0;
+	int u1; float z0, z1, z2;
+	float2 v0, v1;
+	float2 v2; float pad0, pad1;
+};
+static_assert(sizeof(FaceBandItem) == 64, "four 16-byte words per queued band");
+
 struct DataTermParams {
 	int height, width;
 	Intrinsics pinhole;   // camera intrinsics as given (unprojection)
@@ -57,7 +69,7 @@ struct FitterDeviceData {
 	const float* nodes; int node_count; int arrow_base;
 	// per-iteration buffers
 	float4* warped_positions; float4* warped_normals; float4* vertex_jacobians;
-	unsigned long long* keys; BandItem* band_queue; int* counters;  // counters[0] = queue count, [1] = overflow flag, [2] = not-PD flag, [3] = accumulator range flag
+	unsigned long long* keys; FaceBandItem* band_queue; int* counters;  // counters[0] = queue count, [1] = overflow flag, [2] = not-PD flag, [3] = accumulator range flag
 	int band_queue_capacity;
 	const float4* reference_points;
 	unsigned long long* accumulators;  // [N, kAccumStride, 2] fixed-point words (fixed_accum.cuh)
