@@ -353,3 +353,6 @@ class HierarchicalGraphWarpField(GraphWarpField):
         other = super().clone()
         other.__class__ = HierarchicalGraphWarpField
         return other
+
+
+from .voxel_block_grid import BlockHashMap, NonRigidSurfaceVoxelBlockGrid, VoxelBlockGrid  # noqa: E402

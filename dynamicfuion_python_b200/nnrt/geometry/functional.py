@@ -440,8 +440,9 @@ def extract_triangle_mesh(block_keys, block_values, voxel_size, weight_threshold
     vertices, normals = T.empty((counts[0], 3), torch.float32), T.empty((counts[0], 3), torch.float32)
     colors = None if color is None else T.empty((counts[0], 3), torch.float32)
     triangles = T.empty((counts[1], 3), torch.int64)
-    T.call("nnrt_b200_extract_triangle_mesh_emit", T.ptr(keys), b, T.ptr(neighbors), T.ptr(tsdf), T.ptr(color), r, float(voxel_size), T.ptr(structure),
-           T.ptr(offsets), T.ptr(vertices), T.ptr(normals), T.ptr(colors), T.ptr(triangles), T.stream())
+    if counts[0] > 0:  # (no surface crossing among sufficiently weighted voxels: an empty mesh, as the reference returns)
+        T.call("nnrt_b200_extract_triangle_mesh_emit", T.ptr(keys), b, T.ptr(neighbors), T.ptr(tsdf), T.ptr(color), r, float(voxel_size), T.ptr(structure),
+               T.ptr(offsets), T.ptr(vertices), T.ptr(normals), T.ptr(colors), T.ptr(triangles), T.stream())
     mesh = T.MeshView((vertices, normals, triangles))
     mesh.colors = colors
     return mesh
