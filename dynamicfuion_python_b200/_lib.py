@@ -42,6 +42,7 @@ _SIGNATURES = {
     "nnrt_b200_compute_ordered_point_cloud_normals": (C.c_int, [P, I32, I32, P, P]),
     "nnrt_b200_shade_edges_flat": (C.c_int, [P, P, I32, I32, I32, F32, P, P, P]),
     "nnrt_b200_shade_vertex_colors": (C.c_int, [P, P, I32, I32, I32, P, P, P]),
+    "nnrt_b200_integrate_rigid": (C.c_int, [P, I64, P, P, P, I32, P, I32, F32, F32, P, I32, P, I32, I32, I32, I32, I32, P, P, P, F32, F32, P]),
     "nnrt_b200_integrate_non_rigid": (C.c_int, [P, I64, P, P, P, I32, P, I32, F32, F32, P, I32, P, I32, P, I32, I32, I32, I32, P, P, P, P, P, P, I32, P,
                                                 F32, I32, I32, F32, F32, P, P]),
     "nnrt_b200_integrate_non_rigid_full_scan": (C.c_int, [P, I64, P, P, P, I32, P, I32, F32, F32, P, I32, P, I32, P, I32, I32, I32, I32, P, P, P, P, P, P, I32, P,

@@ -185,6 +185,46 @@ __device__ __forceinline__ float3 voxel_camera_position(const IntegrateParams& p
 	                                                 (float) (key[2] * r + zl) * p.voxel_size));
 }
 
+// Rigid integration: Open3D's t::geometry::VoxelBlockGrid::Integrate (third party, Open3D v0.17, not in the reference checkout; the
+// reference re-exports it as nnrt.geometry.VoxelBlockGrid.integrate, pybind/geometry/geometry.cpp:170-203, and its fusion pipeline
+// integrates the first frame with it). Restated from the published kernel (VoxelBlockGridImpl.h, IntegrateCPU/CUDA): voxel -> camera
+// -> pixel (rounded); skip if depth is invalid, the voxel is behind the camera or more than the truncation behind the surface;
+// running average of the clamped, normalised projective distance (and of the colour sampled through the colour camera) with the
+// voxel weight, which is then raised by one. Parity unpinned by the reference. One thread per voxel of the listed blocks.
+__global__ void __launch_bounds__(kThreads) integrate_rigid_kernel(IntegrateParams p) {
+	const int64_t workload = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (workload >= p.voxel_count) return;
+	const int64_t r3 = (int64_t) p.block_resolution * p.block_resolution * p.block_resolution;
+	const int64_t block_index = p.block_indices[workload / r3], voxel_in_block = workload % r3;
+	const float3 voxel = voxel_camera_position(p, block_index, voxel_in_block);
+	const float2 uv = project(p.depth_k, voxel);
+	if (!in_boundary(uv.x, uv.y, p.height, p.width)) return;
+	const int64_t pixel = (int64_t) roundf(uv.y) * p.width + (int64_t) roundf(uv.x);
+	float depth = p.depth_dtype == 0 ? ((const float*) p.depth)[pixel] : (float) ((const uint16_t*) p.depth)[pixel];
+	depth = __fdiv_rn(depth, p.depth_scale);
+	float sdf = depth - voxel.z;
+	if (depth <= 0.0f || depth > p.depth_max || voxel.z <= 0.0f || sdf < -p.truncation) return;
+	sdf = __fdiv_rn(sdf < p.truncation ? sdf : p.truncation, p.truncation);
+	const int64_t linear = block_index * r3 + voxel_in_block;
+	const float voxel_weight = p.weight_dtype == 0 ? ((const float*) p.weight)[linear] : (float) ((const uint16_t*) p.weight)[linear];
+	const float inverted_weight_sum = __fdiv_rn(1.0f, voxel_weight + 1);
+	p.tsdf[linear] = (voxel_weight * p.tsdf[linear] + sdf) * inverted_weight_sum;
+	if (p.color && p.voxel_color) {
+		const float2 cuv = project(p.color_k, voxel);
+		if (in_boundary(cuv.x, cuv.y, p.color_height, p.color_width)) {
+			const int64_t cpx = (int64_t) roundf(cuv.y) * p.color_width + (int64_t) roundf(cuv.x);
+			const float multiplier = p.color_dtype == 0 ? 255.0f : 1.0f;
+#pragma unroll
+			for (int c = 0; c < 3; c++) {
+				const float in = p.color_dtype == 0 ? ((const float*) p.color)[cpx * 3 + c] : (float) ((const uint8_t*) p.color)[cpx * 3 + c];
+				p.voxel_color[linear * 3 + c] = (voxel_weight * p.voxel_color[linear * 3 + c] + in * multiplier) * inverted_weight_sum;
+			}
+		}
+	}
+	if (p.weight_dtype == 0) ((float*) const_cast<void*>(p.weight))[linear] = voxel_weight + 1;
+	else ((uint16_t*) const_cast<void*>(p.weight))[linear] = (uint16_t) (voxel_weight + 1);
+}
+
 // Full-scan form: one thread per voxel, every node offered to every voxel. Kept as the yardstick the shortlist kernel below must equal
 // bit for bit (nnrt_b200_integrate_non_rigid_full_scan).
 template<int A>
@@ -471,6 +511,34 @@ static int integrate_non_rigid_impl(bool full_scan,
 	resolve_cosines_kernel<<<blocks_for(pixel_count, 256), 256, 0, s>>>(keys, pixel_count, cos_voxel_ray_to_normal);
 	const cudaError_t err = cudaGetLastError();
 	if (err != cudaSuccess) { set_last_error("integrate_non_rigid: launch failed: %s", cudaGetErrorString(err)); return kCudaError; }
+	return kOk;
+}
+
+extern "C" int nnrt_b200_integrate_rigid(const int64_t* block_indices, int64_t block_count, const int32_t* block_keys, float* tsdf, void* weight,
+                                         int32_t weight_dtype, float* voxel_color, int32_t block_resolution, float voxel_size,
+                                         float sdf_truncation_distance, const void* depth, int32_t depth_dtype, const void* color, int32_t color_dtype,
+                                         int32_t image_height, int32_t image_width, int32_t color_height, int32_t color_width,
+                                         const double* depth_intrinsics_host, const double* color_intrinsics_host, const double* extrinsics_host,
+                                         float depth_scale, float depth_max, void* stream) {
+	NNRT_CHECK_ARG(block_keys && tsdf && weight && depth && depth_intrinsics_host && extrinsics_host, "integrate_rigid: null pointer argument");
+	NNRT_CHECK_ARG(block_count == 0 || block_indices, "integrate_rigid: block_indices is NULL");
+	NNRT_CHECK_ARG(block_resolution >= 1 && image_height > 0 && image_width > 0, "integrate_rigid: bad sizes");
+	NNRT_CHECK_ARG((weight_dtype == 0 || weight_dtype == 1) && (depth_dtype == 0 || depth_dtype == 1) && (color_dtype == 0 || color_dtype == 1),
+	               "dtype codes must be 0 or 1");
+	NNRT_CHECK_ARG(!color || (color_intrinsics_host && color_height > 0 && color_width > 0), "colour image needs its intrinsics and size");
+	IntegrateParams p{};
+	p.block_indices = block_indices; p.block_keys = block_keys; p.tsdf = tsdf; p.weight = weight; p.weight_dtype = weight_dtype; p.voxel_color = voxel_color;
+	p.block_resolution = block_resolution; p.voxel_size = voxel_size; p.truncation = sdf_truncation_distance;
+	p.depth = depth; p.depth_dtype = depth_dtype; p.color = color; p.color_dtype = color_dtype;
+	p.height = image_height; p.width = image_width; p.color_height = color_height; p.color_width = color_width;
+	p.depth_k = intrinsics_from_host(depth_intrinsics_host);
+	p.color_k = color ? intrinsics_from_host(color_intrinsics_host) : p.depth_k;
+	p.extrinsics = rigid_from_host(extrinsics_host);
+	p.depth_scale = depth_scale; p.depth_max = depth_max;
+	p.voxel_count = block_count * block_resolution * block_resolution * block_resolution;
+	if (p.voxel_count > 0) integrate_rigid_kernel<<<blocks_for(p.voxel_count, kThreads), kThreads, 0, (cudaStream_t) stream>>>(p);
+	const cudaError_t err = cudaGetLastError();
+	if (err != cudaSuccess) { set_last_error("integrate_rigid: launch failed: %s", cudaGetErrorString(err)); return kCudaError; }
 	return kOk;
 }
 

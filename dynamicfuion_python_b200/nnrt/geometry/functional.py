@@ -312,6 +312,54 @@ def warp_point_cloud_dual_quaternion(input_point_cloud, nodes, node_rotations, n
     return wp
 
 
+def integrate_voxel_blocks(block_indices, block_keys, block_values, block_resolution, voxel_size, depth, color, depth_intrinsics,
+                           color_intrinsics=None, extrinsics=None, depth_scale=1000.0, depth_max=3.0, truncation_voxel_multiplier=8.0):
+    """The voxel kernel of VoxelBlockGrid.integrate (Open3D's rigid integration, re-exported by the reference at
+    cpp/pybind/geometry/geometry.cpp:170-203) over a grid's own tensors, as integrate_non_rigid_voxel_blocks takes them. tsdf, weight
+    (raised by one per integrated voxel) and colour are updated IN PLACE."""
+    idx = T.cuda(block_indices, torch.int64)
+    keys = T.cuda(block_keys, torch.int32)
+    tsdf, weight = block_values["tsdf"], block_values["weight"]
+    voxel_color = block_values.get("color")
+    for name, tensor in (("tsdf", tsdf), ("weight", weight), ("color", voxel_color)):
+        if tensor is not None and not (isinstance(tensor, torch.Tensor) and tensor.is_cuda and tensor.is_contiguous()):
+            raise RuntimeError(f"block_values['{name}'] must be a contiguous CUDA tensor (it is updated in place)")
+    if tsdf.dtype != torch.float32 or (voxel_color is not None and voxel_color.dtype != torch.float32):
+        raise RuntimeError("tsdf and color voxel attributes must be Float32")
+    if weight.dtype == torch.float32:
+        weight_code = 0
+    elif weight.dtype in (torch.uint16, torch.int16):
+        weight_code = 1
+    else:
+        raise RuntimeError("weight voxel attribute must be Float32 or UInt16")
+    d = T.to_torch(depth.as_tensor() if hasattr(depth, "as_tensor") else depth)
+    if d.dim() == 3:
+        d = d[..., 0]
+    if d.dtype in (torch.uint16, torch.int16):
+        d, depth_code = T.cuda(d.view(torch.int16) if d.dtype == torch.uint16 else d, torch.int16), 1
+    elif d.dtype == torch.float32:
+        d, depth_code = T.cuda(d, torch.float32), 0
+    else:
+        raise RuntimeError("depth must be UInt16 or Float32")
+    h, w = d.shape
+    c, color_code, ch, cw = None, 0, 0, 0
+    if color is not None and voxel_color is not None:
+        c = T.to_torch(color.as_tensor() if hasattr(color, "as_tensor") else color)
+        if c.numel() == 0:
+            c = None
+        else:
+            color_code = 0 if c.dtype == torch.float32 else 1
+            c = T.cuda(c, torch.float32 if color_code == 0 else torch.uint8)
+            ch, cw = int(c.shape[0]), int(c.shape[1])
+    Kd = T.host_f64(depth_intrinsics, (3, 3))
+    Kc = T.host_f64(depth_intrinsics if color_intrinsics is None else color_intrinsics, (3, 3))
+    ext = T.host_f64(torch.eye(4, dtype=torch.float64) if extrinsics is None else extrinsics, (4, 4))
+    T.call("nnrt_b200_integrate_rigid", T.ptr(idx), idx.shape[0], T.ptr(keys), T.ptr(tsdf), T.ptr(weight), weight_code,
+           T.ptr(voxel_color) if c is not None else None, int(block_resolution), float(voxel_size), float(voxel_size) * float(truncation_voxel_multiplier),
+           T.ptr(d), depth_code, T.ptr(c), color_code, h, w, ch, cw, Kd.data_ptr(), Kc.data_ptr(), ext.data_ptr(), float(depth_scale), float(depth_max),
+           T.stream())
+
+
 def bounding_boxes_of_warped_blocks(block_keys, warp_field, voxel_size, block_resolution, extrinsics=None):
     """NonRigidSurfaceVoxelBlockGrid.GetBoundingBoxesOfWarpedBlocks (cpp/geometry/NonRigidSurfaceVoxelBlockGrid.cpp:120-130) -> [B,6] f32."""
     keys = T.cuda(block_keys, torch.int32)

@@ -173,6 +173,58 @@ class VoxelBlockGrid:
             raise RuntimeError("the TSDF operations need 'tsdf' and 'weight' attributes")
         return views
 
+    def compute_unique_block_coordinates(self, depth, intrinsic, extrinsic=None, depth_scale=1000.0, depth_max=3.0, trunc_voxel_multiplier=8.0):
+        """Blocks touched by the truncation band around the depth surface: Open3D's GetUniqueBlockCoordinates (re-exported at
+        pybind/geometry/geometry.cpp:152-168; third party, restated from the published DepthTouch kernel: every 4th pixel in each
+        direction, four samples along the pixel's ray from depth - truncation to depth + truncation, block = floor(point / block
+        size)). Returns [M,3] int32, each block once, in order of first appearance (Open3D's order is that of its hash map). Frame
+        bootstrap, not a per-iteration path: tensor ops + one pass through the block hash."""
+        self._assert_initialized()
+        d = T.to_torch(depth.as_tensor() if hasattr(depth, "as_tensor") else depth)
+        if d.dim() == 3:
+            d = d[..., 0]
+        if d.dtype == torch.uint16:
+            d = d.view(torch.int16).to(torch.int32) & 0xFFFF
+        d = d.to(self._device).to(torch.float32)[::4, ::4] / float(depth_scale)
+        K = T.host_f64(intrinsic, (3, 3))
+        pose = torch.linalg.inv(T.host_f64(torch.eye(4, dtype=torch.float64) if extrinsic is None else extrinsic, (4, 4)))  # camera -> world
+        rows, cols = d.shape
+        v, u = torch.meshgrid(torch.arange(rows, device=self._device, dtype=torch.float32) * 4, torch.arange(cols, device=self._device, dtype=torch.float32) * 4,
+                              indexing="ij")
+        valid = (d > 0) & (d < float(depth_max))
+        rays = torch.stack([(u - float(K[0, 2])) / float(K[0, 0]), (v - float(K[1, 2])) / float(K[1, 1]), torch.ones_like(u)], -1)[valid]  # z = 1
+        rotation, origin = pose[:3, :3].to(self._device, torch.float32), pose[:3, 3].to(self._device, torch.float32)
+        directions = rays @ rotation.t()
+        depth_valid = d[valid]
+        truncation = self.voxel_size * float(trunc_voxel_multiplier)
+        t_min, t_max = (depth_valid - truncation).clamp(min=0.0), (depth_valid + truncation).clamp(max=float(depth_max))
+        steps = torch.arange(4, device=self._device, dtype=torch.float32)
+        t = t_min[:, None] + steps[None, :] * ((t_max - t_min) / 3.0)[:, None]
+        points = origin[None, None, :] + t[..., None] * directions[:, None, :]
+        blocks = torch.floor(points / (self.voxel_size * self.block_resolution)).to(torch.int32).reshape(-1, 3)
+        scratch = BlockHashMap(max(int(blocks.shape[0]), 1), [], [], self._device)
+        scratch.activate(blocks)
+        return scratch.key_tensor()[:scratch.size()].clone()
+
+    def integrate(self, block_coords, depth, *args):
+        """integrate(block_coords, depth, color, depth_intrinsic, color_intrinsic, extrinsic, depth_scale=1000, depth_max=3,
+        trunc_voxel_multiplier=8) or integrate(block_coords, depth, intrinsic, extrinsic, depth_scale=1000, depth_max=3,
+        trunc_voxel_multiplier=8) -- the overloads the reference re-exports from Open3D (pybind/geometry/geometry.cpp:170-203): activates
+        block_coords and integrates the frame rigidly into THOSE blocks (csrc/tsdf.cu::integrate_rigid_kernel)."""
+        self._assert_initialized()
+        args = list(args)
+        first = T.to_torch(args[0].as_tensor() if hasattr(args[0], "as_tensor") else args[0]) if args and args[0] is not None else None
+        if first is not None and tuple(first.shape) == (3, 3):  # depth-only overload
+            color, depth_intrinsic, color_intrinsic, rest = None, args[0], args[0], args[1:]
+        else:
+            color, depth_intrinsic, color_intrinsic, rest = args[0], args[1], args[2], args[3:]
+        extrinsic = rest[0]
+        depth_scale, depth_max, multiplier = (list(rest[1:]) + [1000.0, 3.0, 8.0][len(rest) - 1:])[:3]
+        indices, _ = self._hashmap.activate(block_coords)
+        indices = torch.unique(indices)  # a block listed twice is integrated once
+        functional.integrate_voxel_blocks(indices.long(), self._hashmap.key_tensor(), self._value_views(), self.block_resolution, self.voxel_size, depth,
+                                          color, depth_intrinsic, color_intrinsic, extrinsic, depth_scale, depth_max, multiplier)
+
     def extract_triangle_mesh(self, weight_threshold=3.0, estimated_vertex_number=-1):
         """Specific operation for TSDF volumes. Extract triangle mesh at isosurface points (VoxelBlockGrid.cpp:461-484); marching cubes
         on the device over the active blocks, neighbour blocks through the block hash. `estimated_vertex_number` is accepted and unused:

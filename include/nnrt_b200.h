@@ -381,6 +381,16 @@ int nnrt_b200_bounding_boxes_of_warped_blocks(const int32_t* block_keys, int64_t
                                               float node_coverage, int32_t anchor_count, int32_t minimum_valid_anchor_count,
                                               float voxel_size, int32_t block_resolution, const double* extrinsics_host,
                                               float* bounding_boxes, void* stream);
+/* Rigid integration of a depth (+ colour) frame into the listed voxel blocks: what nnrt.geometry.VoxelBlockGrid.integrate re-exports
+ * from Open3D (pybind/geometry/geometry.cpp:170-203; the fusion pipeline integrates its first frame with it, apps/fusion/pipeline.py).
+ * Open3D v0.17 is third party and absent from the reference checkout: restated from its published kernel, parity unpinned. tsdf,
+ * weight (float32 or uint16, raised by one per integrated voxel) and voxel_color are updated in place. */
+int nnrt_b200_integrate_rigid(const int64_t* block_indices, int64_t block_count, const int32_t* block_keys, float* tsdf, void* weight,
+                              int32_t weight_dtype, float* voxel_color, int32_t block_resolution, float voxel_size,
+                              float sdf_truncation_distance, const void* depth, int32_t depth_dtype, const void* color, int32_t color_dtype,
+                              int32_t image_height, int32_t image_width, int32_t color_height, int32_t color_width,
+                              const double* depth_intrinsics_host, const double* color_intrinsics_host, const double* extrinsics_host,
+                              float depth_scale, float depth_max, void* stream);
 /* geometry::NonRigidSurfaceVoxelBlockGrid::GetAxisAlignedBoxesIntersectingSurfaceMask (NonRigidSurfaceVoxelBlockGrid.cpp:132-148;
  * kernel/NonRigidSurfaceVoxelBlockGridImpl.h:365-435; kernel/Segment.h): mask [B] u8 = the box is met by the truncation segment
  * (depth -+ truncation_distance along the pixel ray) of some pixel sampled with `stride`. Together with the call above this is the

@@ -471,6 +471,28 @@ def integrate_non_rigid(block_indices, block_keys, tsdf, weight, voxel_color, bl
     return cos
 
 
+def integrate_rigid(block_indices, block_keys, tsdf, weight, voxel_color, block_resolution, voxel_size, sdf_truncation_distance, depth, color,
+                    depth_intrinsics, color_intrinsics, extrinsics, depth_scale, depth_max):
+    """Open3D's VoxelBlockGrid::Integrate restated (oracle_tsdf.cpp): updates tsdf, weight (and voxel_color) in place."""
+    block_indices, block_keys = _i64(block_indices), _i32(block_keys)
+    assert tsdf.dtype == np.float32 and tsdf.flags.c_contiguous and weight.flags.c_contiguous
+    weight_dtype = 0 if weight.dtype == np.float32 else 1
+    depth = np.ascontiguousarray(depth)
+    depth_dtype = 0 if depth.dtype == np.float32 else 1
+    h, w = depth.shape
+    ch = cw = color_dtype = 0
+    if color is not None:
+        color = np.ascontiguousarray(color)
+        color_dtype = 0 if color.dtype == np.float32 else 1
+        ch, cw = color.shape[:2]
+    lib().oracle_integrate_rigid(
+        _p(block_indices), C.c_int64(block_indices.shape[0]), _p(block_keys), _p(tsdf), _p(weight), C.c_int(weight_dtype),
+        None if voxel_color is None else _p(voxel_color), C.c_int(block_resolution), C.c_float(voxel_size), C.c_float(sdf_truncation_distance),
+        _p(depth), C.c_int(depth_dtype), None if color is None else _p(color), C.c_int(color_dtype), C.c_int(h), C.c_int(w), C.c_int(ch), C.c_int(cw),
+        _p(_f64(depth_intrinsics)), _p(_f64(depth_intrinsics if color_intrinsics is None else color_intrinsics)), _p(_f64(extrinsics)),
+        C.c_float(depth_scale), C.c_float(depth_max))
+
+
 def bounding_boxes_of_warped_blocks(block_keys, nodes, node_rotations, node_translations, node_coverage, anchor_count, minimum_valid_anchor_count,
                                     voxel_size, block_resolution, extrinsics):
     keys = _i32(block_keys)

@@ -218,3 +218,52 @@ ORACLE_API void oracle_boxes_intersecting_surface_mask(const float* boxes, int64
 		}
 	}
 }
+
+// Open3D's VoxelBlockGrid::Integrate (third party v0.17, absent from the reference checkout; re-exported by the reference as
+// nnrt.geometry.VoxelBlockGrid.integrate), restated from the published kernel: see csrc/tsdf.cu::integrate_rigid_kernel. Parity unpinned.
+ORACLE_API void oracle_integrate_rigid(
+		const int64_t* block_indices, int64_t block_count, const int32_t* block_keys, float* tsdf, void* weight, int weight_dtype,
+		float* voxel_color, int block_resolution, float voxel_size, float sdf_truncation_distance, const void* depth, int depth_dtype,
+		const void* color, int color_dtype, int height, int width, int color_height, int color_width, const double* depth_intrinsics,
+		const double* color_intrinsics, const double* extrinsics, float depth_scale, float depth_max) {
+	const int64_t r3 = (int64_t) block_resolution * block_resolution * block_resolution;
+	TransformIndexer depth_transform(depth_intrinsics, extrinsics, 1.0f);
+	TransformIndexer color_transform(color_intrinsics ? color_intrinsics : depth_intrinsics, IDENTITY4, 1.0f);
+	auto in_boundary = [](float x, float y, int rows, int cols) { return y >= 0 && x >= 0 && y <= rows - 1.0f && x <= cols - 1.0f; };
+	for (int64_t workload = 0; workload < block_count * r3; workload++) {
+		const int64_t block_index = block_indices[workload / r3];
+		const int64_t voxel_in_block = workload % r3;
+		const int32_t* key = block_keys + block_index * 3;
+		const int xl = (int) (voxel_in_block % block_resolution), yl = (int) ((voxel_in_block / block_resolution) % block_resolution),
+		          zl = (int) (voxel_in_block / ((int64_t) block_resolution * block_resolution));
+		const float gx = (float) (key[0] * block_resolution + xl) * voxel_size, gy = (float) (key[1] * block_resolution + yl) * voxel_size,
+		            gz = (float) (key[2] * block_resolution + zl) * voxel_size;
+		float xc, yc, zc, u, v;
+		depth_transform.RigidTransform(gx, gy, gz, &xc, &yc, &zc);
+		depth_transform.Project(xc, yc, zc, &u, &v);
+		if (!in_boundary(u, v, height, width)) continue;
+		const int64_t pixel = (int64_t) roundf(v) * width + (int64_t) roundf(u);
+		const float d = (depth_dtype == 0 ? ((const float*) depth)[pixel] : (float) ((const uint16_t*) depth)[pixel]) / depth_scale;
+		float sdf = d - zc;
+		if (d <= 0.0f || d > depth_max || zc <= 0.0f || sdf < -sdf_truncation_distance) continue;
+		sdf = (sdf < sdf_truncation_distance ? sdf : sdf_truncation_distance) / sdf_truncation_distance;
+		const int64_t linear = block_index * r3 + voxel_in_block;
+		const float w = weight_dtype == 0 ? ((const float*) weight)[linear] : (float) ((const uint16_t*) weight)[linear];
+		const float inverted_weight_sum = 1.0f / (w + 1);
+		tsdf[linear] = (w * tsdf[linear] + sdf) * inverted_weight_sum;
+		if (color && voxel_color) {
+			float cu, cv;
+			color_transform.Project(xc, yc, zc, &cu, &cv);
+			if (in_boundary(cu, cv, color_height, color_width)) {
+				const int64_t cpx = (int64_t) roundf(cv) * color_width + (int64_t) roundf(cu);
+				const float multiplier = color_dtype == 0 ? 255.0f : 1.0f;
+				for (int c = 0; c < 3; c++) {
+					const float in = color_dtype == 0 ? ((const float*) color)[cpx * 3 + c] : (float) ((const uint8_t*) color)[cpx * 3 + c];
+					voxel_color[linear * 3 + c] = (w * voxel_color[linear * 3 + c] + in * multiplier) * inverted_weight_sum;
+				}
+			}
+		}
+		if (weight_dtype == 0) ((float*) weight)[linear] = w + 1;
+		else ((uint16_t*) weight)[linear] = (uint16_t) (w + 1);
+	}
+}
