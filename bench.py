@@ -128,7 +128,7 @@ def scaled_motion(s, scale):
 
 STAGES = ["warp_vertices", "face_raster", "band_raster", "assemble", "build_system", "stem_eliminate", "corner_solve_update"]
 STAGE_KERNEL = {"warp_vertices": "warp_vertices_kernel<4>", "face_raster": "face_raster_kernel", "band_raster": "band_raster_kernel",
-                "assemble": "assemble_kernel<4>", "build_system": "system_stem_kernel", "stem_eliminate": "(fused into system_stem_kernel)",
+                "assemble": "assemble_kernel<4, 0>", "build_system": "system_stem_kernel<0>", "stem_eliminate": "(fused into system_stem_kernel)",
                 "corner_solve_update": "reduced_gather_kernel + corner_solve_regtile_kernel<1>"}  # names as ncu prints them (<1> = <true>)
 STAGE_BOUND = {"corner_solve_update": "latency: one CTA, 3 Nc-step Cholesky dependency chain (flops and bytes are far from any roof)",
                "build_system": "latency: warp per node, 6 x 6 factorisations"}
@@ -276,7 +276,15 @@ def pixel_shard_leg(torch, dist, nnrt, dev, rank, world, frames):
     (int64 fixed-point words) summed over the ranks once per iteration. Timed with CUDA events (max over ranks) next to the same fit
     unsharded on one GPU, in three forms: bands + NCCL all-reduce, stripes + NCCL, stripes + the reduction fused into the stem kernel."""
     from dynamicfuion_python_b200 import frame_batch
-    height, width = 2160, 3840
+    block = _pixel_shard_measure(torch, dist, nnrt, dev, rank, world, frames, 2160, 3840, True)
+    # the same split at the 640 x 480 of configs[1] (VERDICT r1 item 6: does sharding a small frame cost more than it saves?)
+    small = _pixel_shard_measure(torch, dist, nnrt, dev, rank, world, max(frames, 10), HEIGHT, WIDTH, False)
+    block["small_frame"] = {k: small[k] for k in ("image", "ms_per_iteration", "ms_per_iteration_1gpu", "speedup", "parity_vs_1gpu", "variants_status")}
+    return block
+
+
+def _pixel_shard_measure(torch, dist, nnrt, dev, rank, world, frames, height, width, all_variants):
+    from dynamicfuion_python_b200 import frame_batch
     ratio = height * width / float(HEIGHT * WIDTH)
 
     def edit(s):  # the data term grows with the pixel count: keep its balance with the ARAP term of the 640x480 scene
@@ -287,6 +295,8 @@ def pixel_shard_leg(torch, dist, nnrt, dev, rank, world, frames):
                 ("bands_nccl", dict(stripe_rows=None, collective="nccl")),  # round-2 first form: contiguous bands, int64 all-reduce
                 ("stripes_nccl", dict(stripe_rows=pixel_shard.STRIPE_ROWS, collective="nccl")),
                 ("stripes_peer", dict(stripe_rows=pixel_shard.STRIPE_ROWS, collective="peer"))]  # the default of shard_pixels
+    if not all_variants:
+        variants = [variants[0], variants[3]]
     results, states, used = {}, {}, {}
     for label, shard in variants:
         q = work.sequence()
@@ -314,7 +324,7 @@ def pixel_shard_leg(torch, dist, nnrt, dev, rank, world, frames):
             q["fitter"].shard_pixels(0, 1)  # unmaps the peers' buffers
         del q
     R1, t1, s1 = states["one_gpu"]
-    head = "stripes_peer" if used["stripes_peer"] == "peer" else "stripes_nccl"
+    head = "stripes_peer" if used["stripes_peer"] == "peer" or "stripes_nccl" not in results else "stripes_nccl"
     R2, t2, s2 = states[head]
     gathered = [torch.zeros_like(t2) for _ in range(world)]
     dist.all_gather(gathered, t2)

@@ -595,7 +595,7 @@ static size_t layout(nnrt_b200_fitter* f, bool assign) {
 	f->in_offsets = f->take<int>(N + 2); f->in_edges = f->take<int>(E + 1); f->wing_columns = f->take<int>(E + 1);
 	f->refpts = f->take<float4>(PX);
 	f->keys = f->take<unsigned long long>(PX);
-	f->queue = f->take<FaceBandItem>(F + 65536); f->counters = f->take<int>(8);
+	f->counters = f->take<int>(8);
 	f->accum = f->take<unsigned long long>((int64_t) N * kAccumStride * 2);
 	f->sys_diag = f->take<float>((int64_t) N * 36); f->sys_rhs = f->take<float>(nmax); f->wing = f->take<float>((E + 1) * 36);
 	f->dinv = f->take<float>((int64_t) N * 36); f->stem_y = f->take<float>(nmax); f->wing_x = f->take<float>((E + 1) * 36);
@@ -605,6 +605,7 @@ static size_t layout(nnrt_b200_fitter* f, bool assign) {
 	f->corner_c = f->take<float>((int64_t) N * 9); f->corner_r = f->take<float>((int64_t) N * 3);
 	f->corner_ainvb = f->take<float>((int64_t) N * 9); f->corner_zr = f->take<float>((int64_t) N * 3);
 	f->diag_faces = f->take<int32_t>(PX); f->diag_res = f->take<float>(PX); f->diag_mask = f->take<uint8_t>(PX);
+	f->queue = f->take<FaceBandItem>(F + 65536);  // last: the largest buffer of a small scene, kept away from the accumulators
 	return f->arena_used;
 }
 
