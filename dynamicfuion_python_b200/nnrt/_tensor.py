@@ -52,8 +52,21 @@ def host_f64(x, shape):
     return t
 
 
+_EMPTY = {}
+
+
 def ptr(t):
-    return None if t is None else t.data_ptr()
+    """Device address for the C ABI. An empty tensor has no storage (data_ptr() == 0), which the library would read as a missing
+    argument: it gets the address of a small per-device placeholder instead (the entry points return early on a zero count)."""
+    if t is None:
+        return None
+    address = t.data_ptr()
+    if address == 0 and t.numel() == 0 and t.is_cuda:
+        index = t.device.index
+        if index not in _EMPTY:
+            _EMPTY[index] = torch.zeros(64, dtype=torch.float32, device=t.device)
+        return _EMPTY[index].data_ptr()
+    return address
 
 
 def stream():

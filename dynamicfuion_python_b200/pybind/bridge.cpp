@@ -60,10 +60,24 @@ static std::vector<int64_t> shape_of(const py::object& tensor) {
 	return shape;
 }
 
+// An empty tensor has no storage (data_ptr() == 0), which the library would read as a missing argument: it gets the address of a small
+// placeholder instead (the entry points return early on a zero count). One placeholder per process is enough: it is never dereferenced.
+static void* empty_placeholder() {
+	static py::object* keep = nullptr;
+	static void* address = nullptr;
+	if (!address) {
+		Torch& t = Torch::get();
+		keep = new py::object(t.zeros(py::make_tuple(64), py::arg("dtype") = t.dtype(Dtype::Float32), py::arg("device") = t.cuda_device_kw));
+		address = reinterpret_cast<void*>(keep->attr("data_ptr")().cast<uintptr_t>());
+	}
+	return address;
+}
+
 Dev wrap(py::object tensor) {
 	Dev d;
 	d.pointer = reinterpret_cast<void*>(tensor.attr("data_ptr")().cast<uintptr_t>());
 	d.shape = shape_of(tensor);
+	if (d.pointer == nullptr && d.numel() == 0) d.pointer = empty_placeholder();
 	d.object = std::move(tensor);
 	return d;
 }
