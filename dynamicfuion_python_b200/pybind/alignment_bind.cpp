@@ -128,6 +128,22 @@ public:
 	}
 	int64_t WorkspaceBytes() const { return handle ? nnrt_b200_fitter_workspace_bytes(handle) : 0; }
 
+	// Pixel-sharded single-frame mode (no reference counterpart; include/nnrt_b200.h "pixel-sharded"): this process fits the image
+	// rows of its stripes (stripe s -> rank s % world_size), the per-node sums of the ranks meet inside the stem kernel over NVLink
+	// peer memory. `group` is a torch.distributed process group (None = the default one): it carries the 64-byte IPC handles once, when
+	// the workspace exists, and nothing afterwards. world_size 1 turns the mode off. (The all-reduce form of the exchange lives in the
+	// ctypes front end only.)
+	void ShardPixels(int rank, int world_size, const py::object& group, int stripe_rows) {
+		if (world_size > 1 && (rank < 0 || rank >= world_size)) log_error("rank " + std::to_string(rank) + " outside world of " + std::to_string(world_size));
+		if (stripe_rows <= 0 || stripe_rows % 8) log_error("stripe_rows must be a positive multiple of 8 (the assembly tile height), got " + std::to_string(stripe_rows));
+		shard_rank = rank; shard_world = world_size > 1 ? world_size : 1; shard_stripe_rows = stripe_rows; shard_group = group;
+		peer_ready = false;
+		if (handle) {
+			check(nnrt_b200_fitter_disable_peer_reduce(handle));
+			if (shard_world == 1) check(nnrt_b200_fitter_set_pixel_stripes(handle, 8, 0, 1));
+		}
+	}
+
 	int max_iteration_count;
 	std::vector<IterationMode> iteration_mode_sequence;
 	float min_update_threshold;  // the reference never updates `maximum_update` (.cpp:100,111): unused there as well
@@ -156,6 +172,7 @@ private:
 		shape = wanted;
 		graph_key.clear();
 		mesh_key.clear();
+		peer_ready = false;  // a new workspace: its exchange buffer has not been mapped by the peers
 		std::vector<int32_t> modes;
 		for (IterationMode m : iteration_mode_sequence) modes.push_back((int32_t) m);
 		check(nnrt_b200_fitter_set_iteration_modes(handle, modes.data(), (int32_t) modes.size()));
@@ -234,10 +251,48 @@ private:
 	void fit(WarpField& warp_field, const py::handle& intrinsic_matrix, const py::handle& extrinsic_matrix, int iteration_count) {
 		const std::vector<double> K = host_matrix(intrinsic_matrix, 3, 3, false), extrinsics = host_matrix(extrinsic_matrix, 4, 4, true);
 		const int iterations = iteration_count > 0 ? iteration_count : max_iteration_count;
+		if (shard_world > 1) {
+			check(nnrt_b200_fitter_set_pixel_stripes(handle, shard_stripe_rows, shard_rank, shard_world));
+			if (!peer_ready) enable_peer_reduce();
+		}
 		check(nnrt_b200_fitter_fit(handle, warp_field.node_rotations.data<float>(), warp_field.node_translations.data<float>(), K.data(), extrinsics.data(),
 		                           iterations, stream));
 	}
 
+	// Collective over the group: every rank clears its exchange buffer, the CUDA IPC handles are gathered, every rank maps its peers.
+	void enable_peer_reduce() {
+		py::module_ dist = py::module_::import("torch.distributed");
+		Torch::get().module.attr("cuda").attr("synchronize")();
+		dist.attr("barrier")("group"_a = shard_group);  // no rank is still reading a buffer that is about to be cleared
+		unsigned char mine[64];
+		const int status = nnrt_b200_fitter_peer_exchange(handle, nullptr, nullptr, mine);
+		py::list gathered;
+		for (int r = 0; r < shard_world; r++) gathered.append(py::none());
+		py::object own = status == NNRT_B200_OK ? py::object(py::bytes(reinterpret_cast<const char*>(mine), 64)) : py::object(py::none());
+		dist.attr("all_gather_object")(gathered, own, "group"_a = shard_group);
+		std::string blob;
+		bool ok = status == NNRT_B200_OK;
+		for (int r = 0; r < shard_world && ok; r++) {
+			if (gathered[r].is_none()) { ok = false; break; }
+			blob += gathered[r].cast<std::string>();
+		}
+		if (ok) ok = nnrt_b200_fitter_enable_peer_reduce_ipc(handle, shard_rank, shard_world, blob.data()) == NNRT_B200_OK;
+		const std::string failure = ok ? std::string() : std::string(nnrt_b200_last_error());
+		py::list verdicts;
+		for (int r = 0; r < shard_world; r++) verdicts.append(py::none());
+		dist.attr("all_gather_object")(verdicts, py::bool_(ok), "group"_a = shard_group);  // also the barrier before the first fit
+		for (int r = 0; r < shard_world; r++)
+			if (!verdicts[r].cast<bool>()) {
+				nnrt_b200_fitter_disable_peer_reduce(handle);
+				log_error("shard_pixels: rank " + std::to_string(r) + " could not map its peers' exchange buffers" + (ok ? std::string() : " (" + failure + ")") +
+				          "; use the all-reduce form (dynamicfuion_python_b200.nnrt, collective=\"nccl\")");
+			}
+		peer_ready = true;
+	}
+
+	int shard_rank = 0, shard_world = 1, shard_stripe_rows = 32;
+	py::object shard_group = py::none();
+	bool peer_ready = false;
 	nnrt_b200_fitter_options options;
 	nnrt_b200_fitter* handle = nullptr;
 	std::array<int64_t, 7> shape{};
@@ -293,6 +348,7 @@ void bind_alignment(py::module_& m) {
 	           },
 	           "warp_field"_a, "canonical_mesh"_a, "reference_color_image"_a, "reference_point_cloud"_a, "reference_point_mask"_a, "intrinsic_matrix"_a,
 	           "extrinsic_matrix"_a, "rendering_image_size"_a, py::kw_only(), "anchors"_a = py::none(), "anchor_weights"_a = py::none(), "iteration_count"_a = 0);
+	fitter.def("shard_pixels", &DeformableMeshToImageFitter::ShardPixels, "rank"_a, "world_size"_a, "group"_a = py::none(), "stripe_rows"_a = 32);
 	fitter.def("check_status", &DeformableMeshToImageFitter::CheckStatus,
 	           "Waits for the stream and raises if the last fit overflowed its band queue or met a non-positive-definite block.");
 	fitter.def("diagnostics", &DeformableMeshToImageFitter::Diagnostics);

@@ -61,6 +61,26 @@ def main():
         gathered = [torch.zeros_like(t2) for _ in range(world)]
         dist.all_gather(gathered, t2)
         assert all(torch.equal(g, gathered[0]) for g in gathered)
+    # the same through the C++ front end (pybind11 module `nnrt`): stripes + peer reduction, three fits in a row on one workspace
+    from dynamicfuion_python_b200 import build
+    cxx = build.import_pybind_module()
+    GX = cxx.geometry
+    for stripe_rows in (8, 32):
+        wf = GX.HierarchicalGraphWarpField.from_graph(s["nodes"], s["edges"], s["arrow_base"], s["node_coverage"], False, 4, 0,
+                                                      GX.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, s["edge_layer_indices"], s["layer_radii"])
+        fitter = cxx.alignment.DeformableMeshToImageFitter(max_iteration_count=3, preconditioning_dampening_factor=s["lm_factor"],
+                                                           arap_term_weight=s["arap_term_weight"])
+        fitter.shard_pixels(rank, world, None, stripe_rows)
+        for repeat in range(3):
+            wf.set_node_rotations(torch.eye(3, device="cuda").repeat(len(s["nodes"]), 1, 1), True)
+            wf.set_node_translations(torch.zeros((len(s["nodes"]), 3), device="cuda"), True)
+            fitter.fit_to_image(wf, mesh, None, s["reference_points"], s["reference_mask"], s["K"], np.eye(4), (s["height"], s["width"]),
+                                anchors=s["anchors"], anchor_weights=s["anchor_weights"])
+            fitter.check_status()
+            R3, t3 = wf.get_node_rotations(True), wf.get_node_translations(True)
+            assert torch.equal(t3, t1) and torch.equal(R3, R1), ("pybind11 module", stripe_rows, repeat, float((t3 - t1).abs().max()))
+        fitter.shard_pixels(0, 1)
+        del fitter
     dist.barrier()
     if rank == 0:
         print("PIXEL_SHARD_OK")
