@@ -133,6 +133,24 @@ def test_single_iteration_parity(nnrt, oracle, config, h, w):
     np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
 
 
+@pytest.mark.parametrize("anchor_count", [1, 2, 3, 8])
+def test_single_iteration_parity_other_anchor_counts(nnrt, oracle, anchor_count):
+    """The fused kernels are instantiated for 1 .. MAX_ANCHOR_COUNT = 8 anchors per vertex (geometry/functional/kernel/Defines.h:18); every
+    other test runs the reference's default of 4. One iteration at 1, 2, 3 and 8 anchors against the oracle, same bars."""
+    s = scene_with_target(oracle, "tinyr", 120, 160)
+    s["anchors"], s["anchor_weights"] = oracle.compute_anchors(s["positions"], s["nodes"], anchor_count, 0, s["node_coverage"])
+    ref = oracle_fit(oracle, s, 1)
+    wf, fitter = _gpu_fit(nnrt, s, 1)
+    d = fitter.diagnostics()
+    assert np.array_equal(_np(d["pixel_face_indices"]), ref["pixel_faces"]) and np.array_equal(_np(d["residual_mask"]), ref["residual_mask"])
+    for name, got, want, rtol, floor in (("residuals", d["residuals"], ref["residuals"], 1e-4, 1e-6), ("J^T J", d["hessian_diagonal"], ref["hessian_diag"][0], 1e-4, 1e-6),
+                                         ("J^T r", d["negative_gradient"], ref["negative_gradient"][0], 1e-4, 1e-4), ("deltas", d["deltas"], ref["deltas"][0], 1e-3, 1e-2)):
+        ok, worst = rel_close(_np(got), want, rtol, floor_scale=floor)
+        assert ok, f"{name} {worst} at {anchor_count} anchors"
+    np.testing.assert_allclose(_np(wf.node_translations), ref["translations"], rtol=1e-3, atol=1e-6)
+    np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
+
+
 @pytest.mark.skipif(bool(os.environ.get("NNRT_B200_SKIP_SLOW_TESTS")), reason="slow (about a minute on the 16-core GPU box: the oracle at 4.45 M triangles)")
 def test_single_iteration_parity_at_c3_size(nnrt_mirror, oracle):
     """BASELINE.json configs[2] (4.45 M triangles, 1920 x 1080, 1681 + 289 nodes: the cluster corner kernel on 867 unknowns): one GN
