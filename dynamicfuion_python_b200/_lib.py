@@ -73,6 +73,7 @@ _SIGNATURES = {
     "nnrt_b200_fitter_workspace_bytes": (I64, [P]),
     "nnrt_b200_fitter_set_model": (C.c_int, [P, P, P, P, P, P, I32, P, P, I32, P, P, P, P]),
     "nnrt_b200_fitter_set_iteration_modes": (C.c_int, [P, P, I32]),
+    "nnrt_b200_fitter_set_mesh_size": (C.c_int, [P, I64, I64]),
     "nnrt_b200_fitter_set_pixel_rows": (C.c_int, [P, I32, I32]),
     "nnrt_b200_fitter_set_pixel_stripes": (C.c_int, [P, I32, I32, I32]),
     "nnrt_b200_fitter_peer_exchange": (C.c_int, [P, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), P]),

@@ -532,6 +532,7 @@ __global__ void __launch_bounds__(256) diagnostics_convert_kernel(const int32_t*
 struct nnrt_b200_fitter {
 	nnrt_b200_fitter_options opt;
 	int64_t V, F, E; int N, A, H, W;
+	int64_t V_cap = 0, F_cap = 0;  // the workspace is sized for these; V, F are the counts of the mesh currently set (fitter_set_mesh_size)
 	int arrow_base = 0, corner_blocks = 0;
 	bool graph_set = false, mesh_set = false, reference_set = false, fused_stem = true;
 	int row_begin = 0, row_end = 0;  // pixel band of a pixel-sharded fit; row_end == 0: whole image
@@ -582,7 +583,7 @@ namespace nnrt_b200 {
 static size_t layout(nnrt_b200_fitter* f, bool assign) {
 	// two passes: measure (arena == nullptr), then assign
 	f->arena_used = 0;
-	const int64_t V = f->V, F = f->F, E = f->E, PX = (int64_t) f->H * f->W;
+	const int64_t V = f->V_cap, F = f->F_cap, E = f->E, PX = (int64_t) f->H * f->W;
 	const int N = f->N, A = f->A;
 	const int64_t nmax = (int64_t) N * 6;  // corner can be at most all nodes
 	(void) assign;
@@ -635,7 +636,7 @@ extern "C" int nnrt_b200_fitter_create(const nnrt_b200_fitter_options* options, 
 	NNRT_CHECK_ARG(opt.preconditioning_dampening_factor >= 0.f && opt.preconditioning_dampening_factor <= 1.f,
 	               "`preconditioning_dampening_factor` should be a small non-negative value between 0 and 1. Got %f.", opt.preconditioning_dampening_factor);
 	auto* f = new nnrt_b200_fitter();
-	f->opt = opt; f->V = vertex_count; f->F = face_count; f->E = edge_count; f->N = node_count; f->A = anchor_count;
+	f->opt = opt; f->V = f->V_cap = vertex_count; f->F = f->F_cap = face_count; f->E = edge_count; f->N = node_count; f->A = anchor_count;
 	f->H = image_height; f->W = image_width;
 	const size_t bytes = layout(f, false);
 	if (cudaMalloc(&f->arena, bytes) != cudaSuccess) { delete f; set_last_error("fitter_create: cudaMalloc of %zu bytes failed", bytes); return kCudaError; }
@@ -909,6 +910,18 @@ extern "C" int nnrt_b200_fitter_set_mesh(nnrt_b200_fitter* f, const float* verte
 	return kOk;
 }
 
+extern "C" int nnrt_b200_fitter_set_mesh_size(nnrt_b200_fitter* f, int64_t vertex_count, int64_t face_count) {
+	NNRT_CHECK_ARG(f, "fitter_set_mesh_size: null fitter");
+	NNRT_CHECK_ARG(vertex_count > 0 && face_count > 0, "fitter_set_mesh_size: counts must be positive");
+	NNRT_CHECK_ARG(vertex_count <= f->V_cap && face_count <= f->F_cap, "the workspace holds up to %lld vertices and %lld faces, asked for %lld and %lld",
+	               (long long) f->V_cap, (long long) f->F_cap, (long long) vertex_count, (long long) face_count);
+	if (vertex_count == f->V && face_count == f->F) return kOk;
+	if (f->graph_exec) { cudaGraphExecDestroy(f->graph_exec); f->graph_exec = nullptr; }  // launch sizes are part of the captured graph
+	f->V = vertex_count; f->F = face_count;
+	f->mesh_set = false;
+	return kOk;
+}
+
 extern "C" int nnrt_b200_fitter_set_model(nnrt_b200_fitter* f, const float* vertex_positions, const float* vertex_normals,
                                           const int64_t* triangles, const float* nodes, const int32_t* edges, int32_t arrow_base,
                                           const int8_t* edge_layer_indices, const float* layer_decimation_radii, int32_t layer_count,
@@ -969,7 +982,7 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	c.d.anchors = f->anchors; c.d.anchor_weights = f->weights; c.d.anchor_count = f->A;
 	c.d.nodes = f->nodes; c.d.node_count = f->N; c.d.arrow_base = f->arrow_base;
 	c.d.warped_positions = f->wpos; c.d.warped_normals = f->wnrm; c.d.vertex_jacobians = f->vjac;
-	c.d.keys = f->keys; c.d.band_queue = f->queue; c.d.counters = f->counters; c.d.band_queue_capacity = (int) (f->F + 65536);
+	c.d.keys = f->keys; c.d.band_queue = f->queue; c.d.counters = f->counters; c.d.band_queue_capacity = (int) (f->F_cap + 65536);
 	c.d.reference_points = f->refpts; c.d.accumulators = f->accum;
 	c.peer = f->peer; c.peer_device = f->exchange ? reinterpret_cast<const PeerReduce*>(f->exchange + exchange_table_offset(f)) : nullptr;
 	if (f->peer.world > 1) {  // the sums go to the exported buffer of this iteration's parity

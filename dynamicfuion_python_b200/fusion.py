@@ -31,7 +31,7 @@ from . import nnrt as _default_nnrt
 class FusionLoop:
     def __init__(self, intrinsics, extrinsics=None, voxel_size=0.004, block_resolution=8, block_count=4096, node_spacing=0.03, node_coverage=None,
                  anchor_count=4, layer_count=2, depth_scale=1000.0, far_clipping_distance=3.0, truncation_voxel_multiplier=2.0, weight_threshold=0.5,
-                 fitter=None, nnrt=None):
+                 fitter=None, nnrt=None, warm_start_rotations=False):
         """Solver settings: with the reference's defaults (arap_term_weight 200, no damping) and overlapping anchor weights the reference's
         iteration diverges on multi-node graphs (dynamicfuion_python_b200/synthetic.py, DESIGN.md "reference behaviour"); the defaults here
         are the contractive ones the parity scenes use: node coverage a quarter of the node spacing, arap_term_weight 20, lambda 1."""
@@ -44,8 +44,11 @@ class FusionLoop:
         node_coverage = node_spacing / 4.0 if node_coverage is None else node_coverage
         self.node_spacing, self.node_coverage, self.anchor_count, self.layer_count = node_spacing, node_coverage, anchor_count, layer_count
         self.depth_scale, self.far, self.truncation, self.weight_threshold = depth_scale, far_clipping_distance, truncation_voxel_multiplier, weight_threshold
-        self.fitter = fitter if fitter is not None else self.nnrt.alignment.DeformableMeshToImageFitter(
-            max_iteration_count=10, preconditioning_dampening_factor=1.0, arap_term_weight=20.0)
+        self.fitter = fitter  # None: made in first_frame, when the image size is known (the ARAP weight follows it)
+        # Each frame is fitted canonical -> current, so the node state of the previous frame is only a starting point. Translations are
+        # carried over; rotations restart from the identity by default: the reference iteration is not contractive in warm-started
+        # rotations (bench.py makes the same choice; measured on the 640 x 480 relief: divergence within three frames otherwise).
+        self.warm_start_rotations = warm_start_rotations
         self.graph = self._fit_graph = self.canonical_mesh = self.warped_mesh = None
         self.frame_index = 0
 
@@ -85,6 +88,12 @@ class FusionLoop:
             (g.get_node_positions(True) * self._mirror).contiguous(), g.get_edges(), g.first_layer_node_count, self.node_coverage, False, self.anchor_count, 0,
             G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, g.get_edge_layer_indices(), g.get_layer_decimation_radii())
         height, width = (int(x) for x in (depth.shape[0], depth.shape[1]))
+        if self.fitter is None:
+            # the data term grows with the number of pixels a node sees, the ARAP term does not: the weight that keeps the iteration
+            # contractive at 160 x 120 (20) is scaled by the square root of the pixel ratio (80 at 640 x 480; measured stable over 8
+            # frames there with 20 mm node spacing, divergent at 20 and at 200 -- tests/measure/fusion_loop_times.py)
+            self.fitter = self.nnrt.alignment.DeformableMeshToImageFitter(
+                max_iteration_count=10, preconditioning_dampening_factor=1.0, arap_term_weight=20.0 * float(np.sqrt(height * width / 19200.0)))
         self._fit_K = self.K.copy()
         self._fit_K[0, 2], self._fit_K[1, 2] = width - 0.5 - self.K[0, 2], self.K[1, 2] + 0.5
         self.warped_mesh, self.frame_index = self.canonical_mesh, 1
@@ -104,7 +113,10 @@ class FusionLoop:
         self.volume.hashmap().activate(blocks)
         # non-rigid alignment in the mirrored frame, warm-started from the field's current state; result mapped back
         fit = self._fit_graph
-        fit.set_node_rotations((self.graph.get_node_rotations(True) * self._mirror_block).contiguous(), True)
+        if self.warm_start_rotations:
+            fit.set_node_rotations((self.graph.get_node_rotations(True) * self._mirror_block).contiguous(), True)
+        else:
+            fit.reset_rotations()
         fit.set_node_translations((self.graph.get_node_translations(True) * self._mirror).contiguous(), True)
         self.fitter.fit_to_image(fit, self._mirrored_mesh(self.canonical_mesh), color, depth, None, self._fit_K, None, self.depth_scale)
         self.fitter.check_status()

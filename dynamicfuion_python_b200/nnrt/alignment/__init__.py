@@ -39,6 +39,7 @@ class DeformableMeshToImageFitter:
         self._shard_collective, self._peer_ready = "nccl", False
         self._shard_graphs, self._shard_seen, self._shard_keep = {}, None, None
         self._shape = None
+        self._capacity = (0, 0)
         self._model_key = None
         self._keep = None
 
@@ -56,11 +57,22 @@ class DeformableMeshToImageFitter:
     def _ensure(self, shape):
         if self._handle is not None and self._shape == shape:
             return
+        v, f, n, e, a, h, w = shape
+        same_problem = self._handle is not None and self._shape[2:] == shape[2:]
+        if same_problem and v <= self._capacity[0] and f <= self._capacity[1]:
+            # a canonical mesh re-extracted every frame changes its counts: the workspace is kept, only the launch sizes change
+            T.call("nnrt_b200_fitter_set_mesh_size", self._handle, v, f)
+            self._shape = shape
+            return
+        # a mesh that outgrew the workspace gets headroom, so that a slowly growing surface does not reallocate every frame; the first
+        # workspace of a problem is exact (a fixed canonical mesh, the usual case, wastes nothing)
+        capacity = (v + v // 2, f + f // 2) if same_problem else (v, f)
         self._release()
         handle = C.c_void_p()
-        v, f, n, e, a, h, w = shape
-        _lib.check(_lib.lib().nnrt_b200_fitter_create(C.byref(self.options), v, f, n, e, a, h, w, C.byref(handle)))
-        self._handle, self._shape, self._model_key = handle, shape, None
+        _lib.check(_lib.lib().nnrt_b200_fitter_create(C.byref(self.options), capacity[0], capacity[1], n, e, a, h, w, C.byref(handle)))
+        self._handle, self._shape, self._model_key, self._capacity = handle, shape, None, capacity
+        if capacity != (v, f):
+            T.call("nnrt_b200_fitter_set_mesh_size", handle, v, f)
         self._peer_ready = False  # a new fitter object: its exchange buffer has not been mapped by the peers
         modes = (C.c_int32 * len(self.iteration_mode_sequence))(*[int(m) for m in self.iteration_mode_sequence])
         _lib.check(_lib.lib().nnrt_b200_fitter_set_iteration_modes(handle, modes, len(self.iteration_mode_sequence)))

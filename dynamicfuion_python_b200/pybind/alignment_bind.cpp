@@ -2,6 +2,7 @@
 // here under its natural name with the constructor's argument names and defaults) as a C++ host class over the nnrt_b200_fitter_* C ABI.
 #include "warp_field.h"
 
+#include <algorithm>
 #include <array>
 #include <cstring>
 
@@ -166,9 +167,20 @@ private:
 	}
 	void ensure(const std::array<int64_t, 7>& wanted) {
 		if (handle && wanted == shape) return;
+		const bool same_problem = handle && std::equal(wanted.begin() + 2, wanted.end(), shape.begin() + 2);
+		if (same_problem && wanted[0] <= capacity[0] && wanted[1] <= capacity[1]) {
+			// a canonical mesh re-extracted every frame changes its counts: the workspace is kept, only the launch sizes change
+			check(nnrt_b200_fitter_set_mesh_size(handle, wanted[0], wanted[1]));
+			shape = wanted;
+			mesh_key.clear();
+			return;
+		}
+		// a mesh that outgrew the workspace gets headroom; the first workspace of a problem is exact
+		capacity = same_problem ? std::array<int64_t, 2>{wanted[0] + wanted[0] / 2, wanted[1] + wanted[1] / 2} : std::array<int64_t, 2>{wanted[0], wanted[1]};
 		release();
-		check(nnrt_b200_fitter_create(&options, wanted[0], wanted[1], (int32_t) wanted[2], wanted[3], (int32_t) wanted[4], (int32_t) wanted[5],
+		check(nnrt_b200_fitter_create(&options, capacity[0], capacity[1], (int32_t) wanted[2], wanted[3], (int32_t) wanted[4], (int32_t) wanted[5],
 		                              (int32_t) wanted[6], &handle));
+		if (capacity[0] != wanted[0] || capacity[1] != wanted[1]) check(nnrt_b200_fitter_set_mesh_size(handle, wanted[0], wanted[1]));
 		shape = wanted;
 		graph_key.clear();
 		mesh_key.clear();
@@ -296,6 +308,7 @@ private:
 	nnrt_b200_fitter_options options;
 	nnrt_b200_fitter* handle = nullptr;
 	std::array<int64_t, 7> shape{};
+	std::array<int64_t, 2> capacity{};  // vertex / face counts the workspace was created for
 	std::vector<int64_t> graph_key, mesh_key;
 	void* stream = nullptr;  // torch's current stream, looked up once per fit_to_image call
 	std::vector<py::object> keep_graph, keep_mesh, keep_reference;  // inputs of work still queued on the stream

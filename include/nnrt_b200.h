@@ -186,6 +186,10 @@ int nnrt_b200_fitter_set_graph(nnrt_b200_fitter* fitter, const float* nodes, con
                                const float* node_coverage_weights, void* stream);
 int nnrt_b200_fitter_set_mesh(nnrt_b200_fitter* fitter, const float* vertex_positions, const float* vertex_normals,
                               const int64_t* triangles, const int32_t* anchors, const float* anchor_weights, void* stream);
+/* The workspace is sized by fitter_create's vertex / face counts; a canonical mesh that changes from frame to frame (re-extracted from
+ * the TSDF volume) may have any counts up to those: set them before set_mesh. Changing them drops the captured iteration graph (launch
+ * sizes are part of it) but keeps the allocation. No reference counterpart (the reference allocates per call). */
+int nnrt_b200_fitter_set_mesh_size(nnrt_b200_fitter* fitter, int64_t vertex_count, int64_t face_count);
 /* IterationMode sequence (alignment/IterationMode.h:24-28: 0 ALL, 1 TRANSLATION_ONLY, 2 ROTATION_ONLY), host array, cycled by
  * iteration % count (DeformableMeshToImageFitter.cpp:112). Default {ALL}. Non-ALL modes solve the 3 x 3 block of the active half
  * (.cpp:198, 262-272) and are defined for edge-free warp fields only, as in the reference (fit returns an error otherwise). */

@@ -133,6 +133,46 @@ def test_single_iteration_parity(nnrt, oracle, config, h, w):
     np.testing.assert_allclose(_np(wf.node_rotations), ref["rotations"], rtol=1e-3, atol=1e-6)
 
 
+def test_workspace_follows_a_changing_canonical_mesh(nnrt, oracle):
+    """A canonical mesh re-extracted from the volume every frame changes its vertex and face counts. The fitter keeps its workspace while
+    the counts fit (nnrt_b200_fitter_set_mesh_size) and reallocates with headroom when they outgrow it; either way the fit equals that
+    of a fresh fitter on the same mesh, bit for bit."""
+    s = scene_with_target(oracle, "tinyr", 120, 160)
+    V = len(s["positions"])
+
+    def truncated(keep):  # the first `keep` vertices and the faces that only use them
+        faces = s["triangles"][(s["triangles"] < keep).all(1)]
+        return dict(s, positions=s["positions"][:keep], normals=s["normals"][:keep], triangles=faces, anchors=s["anchors"][:keep],
+                    anchor_weights=s["anchor_weights"][:keep])
+
+    G = nnrt.geometry
+    args = dict(max_iteration_count=3, preconditioning_dampening_factor=s["lm_factor"], arap_term_weight=s["arap_term_weight"])
+    shared = nnrt.alignment.DeformableMeshToImageFitter(**args)
+
+    def fit(fitter, scene):
+        wf = G.HierarchicalGraphWarpField.from_graph(scene["nodes"], scene["edges"], scene["arrow_base"], scene["node_coverage"], False, 4, 0,
+                                                     G.WarpNodeCoverageComputationMethod.FIXED_NODE_COVERAGE, 4, scene["edge_layer_indices"], scene["layer_radii"])
+        fitter.fit_to_image(wf, (scene["positions"], scene["normals"], scene["triangles"]), None, scene["reference_points"], scene["reference_mask"], scene["K"],
+                            np.eye(4), (scene["height"], scene["width"]), anchors=scene["anchors"], anchor_weights=scene["anchor_weights"])
+        fitter.check_status()
+        return _np(wf.get_node_rotations(True)).copy(), _np(wf.get_node_translations(True)).copy()
+
+    # shrink, grow back, outgrow (reallocation), shrink, full again. (Not below 0.8 V: a node that loses all its vertices gets an exactly
+    # zero rotation update, whose Rodrigues formula is 0 / 0 in the reference and here -- NaN on both sides, equal_nan below.)
+    sizes = [int(V * 0.9), int(V * 0.8), int(V * 0.9), V, int(V * 0.85), V]
+    workspace = []
+    for keep in sizes:
+        scene = truncated(keep)
+        got = fit(shared, scene)
+        want = fit(nnrt.alignment.DeformableMeshToImageFitter(**args), scene)
+        assert np.array_equal(got[0], want[0], equal_nan=True) and np.array_equal(got[1], want[1], equal_nan=True), keep
+        assert np.isfinite(got[0]).all()
+        workspace.append(shared.workspace_bytes())
+    assert workspace[0] == workspace[1] == workspace[2]      # kept while the mesh fits
+    assert workspace[3] > workspace[2]                         # outgrown: reallocated, with headroom
+    assert workspace[3] == workspace[4] == workspace[5]
+
+
 @pytest.mark.parametrize("anchor_count", [1, 2, 3, 8])
 def test_single_iteration_parity_other_anchor_counts(nnrt, oracle, anchor_count):
     """The fused kernels are instantiated for 1 .. MAX_ANCHOR_COUNT = 8 anchors per vertex (geometry/functional/kernel/Defines.h:18); every
