@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 			fn[0] = make_float3(na.x, na.y, na.z); fn[1] = make_float3(nb.x, nb.y, nb.z); fn[2] = make_float3(nc.x, nc.y, nc.z);
 		}
 		const float4 ref = d.reference_points[px];
-		const float2 ray = make_float2(pixel_to_ndc(u, p.width, p.height), pixel_to_ndc(v, p.height, p.width));
+		const float2 ray = make_float2(pixel_centre(p.ndc_x, u, p.width, p.height), pixel_centre(p.ndc_y, v, p.height, p.width));
 		FaceNdc fndc;
 		fndc.v0 = project(p.ndc, fv[0]); fndc.v1 = project(p.ndc, fv[1]); fndc.v2 = project(p.ndc, fv[2]);
 		fndc.z0 = fv[0].z; fndc.z1 = fv[1].z; fndc.z2 = fv[2].z;

@@ -566,6 +566,7 @@ struct nnrt_b200_fitter {
 	float *pair_blocks = nullptr, *reduced_packed = nullptr, *reduced_dense = nullptr, *reduced_dense_rhs = nullptr;
 	unsigned long long* keys; nnrt_b200::FaceBandItem* queue; int* counters;
 	int32_t* diag_faces; float* diag_res; uint8_t* diag_mask;
+	float *ndc_x, *ndc_y;  // pixel centres in NDC (raster_core.cuh)
 	// cached graph
 	cudaGraphExec_t graph_exec = nullptr;
 	struct GraphKey { float* R; float* t; double K[9]; double T[16]; int iters; } graph_key{};  // an instantiated graph launches into any stream
@@ -606,6 +607,7 @@ static size_t layout(nnrt_b200_fitter* f, bool assign) {
 	f->corner_c = f->take<float>((int64_t) N * 9); f->corner_r = f->take<float>((int64_t) N * 3);
 	f->corner_ainvb = f->take<float>((int64_t) N * 9); f->corner_zr = f->take<float>((int64_t) N * 3);
 	f->diag_faces = f->take<int32_t>(PX); f->diag_res = f->take<float>(PX); f->diag_mask = f->take<uint8_t>(PX);
+	f->ndc_x = f->take<float>(f->W); f->ndc_y = f->take<float>(f->H);
 	f->queue = f->take<FaceBandItem>(F + 65536);  // last: the largest buffer of a small scene, kept away from the accumulators
 	return f->arena_used;
 }
@@ -646,6 +648,7 @@ extern "C" int nnrt_b200_fitter_create(const nnrt_b200_fitter_options* options, 
 	memset(f->host_flags, 0, 8 * sizeof(int));
 	f->schur = nullptr; f->corner_rhs = nullptr;
 	cudaMemset(f->arena, 0, bytes);
+	launch_fill_pixel_centres(f->ndc_x, f->ndc_y, f->H, f->W, nullptr);
 	launch_fill_keys(f->keys, (int64_t) f->H * f->W, nullptr);
 	if (cudaDeviceSynchronize() != cudaSuccess) { nnrt_b200_fitter_destroy(f); set_last_error("fitter_create: workspace initialisation failed"); return kCudaError; }
 	*out_fitter = f;
@@ -1016,6 +1019,7 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	c.p.blur_radius = 0.5f / (fminf((float) f->H, (float) f->W) / 2.0f);
 	c.p.row_begin = f->row_begin; c.p.row_end = f->row_end > 0 ? f->row_end : f->H;
 	c.p.stripe_rows = f->stripe_rows; c.p.stripe_index = f->stripe_index; c.p.stripe_count = f->stripe_count;
+	c.p.ndc_x = f->ndc_x; c.p.ndc_y = f->ndc_y;
 	c.p.write_diagnostics = 1;
 	c.extrinsics = rigid_from_host(T);
 	return c;

@@ -76,6 +76,7 @@ __device__ __forceinline__ RasterParams raster_params(const DataTermParams& p) {
 	RasterParams rp;
 	rp.height = p.height; rp.width = p.width; rp.blur_radius = p.blur_radius;
 	rp.perspective_correct = p.perspective_correct; rp.clip_bary = 0; rp.cull_back_faces = 1;
+	rp.ndc_x = p.ndc_x; rp.ndc_y = p.ndc_y;
 	return rp;
 }
 
@@ -208,6 +209,12 @@ __global__ void __launch_bounds__(256) band_raster_kernel(FitterDeviceData d, Da
 	(void) cam;
 }
 
+__global__ void __launch_bounds__(256) fill_pixel_centres_kernel(float* __restrict__ ndc_x, float* __restrict__ ndc_y, int height, int width) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < width) ndc_x[i] = pixel_to_ndc(i, width, height);
+	if (i < height) ndc_y[i] = pixel_to_ndc(i, height, width);
+}
+
 __global__ void __launch_bounds__(256) fill_keys_kernel2(unsigned long long* keys, int64_t n) {
 	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
 	if (i < n) keys[i] = kEmptyKey;
@@ -238,6 +245,10 @@ void launch_face_raster(const FitterDeviceData& d, const DataTermParams& p, cons
 
 void launch_band_raster(const FitterDeviceData& d, const DataTermParams& p, const NdcCamera& cam, cudaStream_t s) {
 	band_raster_kernel<<<148 * 3, 256, 0, s>>>(d, p, cam);  // 77 registers: three CTAs per SM
+}
+
+void launch_fill_pixel_centres(float* ndc_x, float* ndc_y, int height, int width, cudaStream_t s) {
+	fill_pixel_centres_kernel<<<blocks_for(max(height, width), 256), 256, 0, s>>>(ndc_x, ndc_y, height, width);
 }
 
 void launch_fill_keys(unsigned long long* keys, int64_t n, cudaStream_t s) {

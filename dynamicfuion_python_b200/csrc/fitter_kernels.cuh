@@ -58,6 +58,7 @@ struct DataTermParams {
 	// pixel-sharded fits, balanced form: the rows are cut into stripes of `stripe_rows` (a multiple of the 8-row assembly tile) dealt
 	// round-robin to `stripe_count` GPUs; this GPU owns stripes stripe_index, stripe_index + stripe_count, ... (8, 0, 1 = every row)
 	int stripe_rows, stripe_index, stripe_count;
+	const float* ndc_x; const float* ndc_y;  // pixel centres in NDC, [width] and [height] (raster_core.cuh::RasterParams); filled at fitter_create
 	int write_diagnostics;   // per-pixel face / residual / mask of this iteration are kept (the last iteration of a fit; every split or profiled one)
 };
 
@@ -86,5 +87,6 @@ void launch_face_raster(const FitterDeviceData& d, const DataTermParams& p, cons
 void launch_band_raster(const FitterDeviceData& d, const DataTermParams& p, const NdcCamera& cam, cudaStream_t s);
 int launch_assemble(const FitterDeviceData& d, const DataTermParams& p, cudaStream_t s);
 void launch_fill_keys(unsigned long long* keys, int64_t n, cudaStream_t s);
+void launch_fill_pixel_centres(float* ndc_x, float* ndc_y, int height, int width, cudaStream_t s);
 
 }  // namespace nnrt_b200

@@ -262,6 +262,7 @@ extern "C" int nnrt_b200_rasterize_ndc_triangles(const float* face_vertices_ndc,
 	rp.height = image_height; rp.width = image_width;
 	rp.blur_radius = blur_radius_pixels / (fminf((float) image_height, (float) image_width) / 2.0f);
 	rp.perspective_correct = perspective_correct; rp.clip_bary = clip_barycentric; rp.cull_back_faces = cull_back_faces;
+	rp.ndc_x = nullptr; rp.ndc_y = nullptr;  // the one-off stage entry computes the pixel centres on the fly
 	const int queue_capacity = (int) (face_count > (1 << 20) ? face_count : (1 << 20));
 	unsigned long long* keys = nullptr;
 	BandItem* queue = nullptr;

@@ -19,7 +19,14 @@ struct RasterParams {
 	int height, width;
 	float blur_radius;      // NDC units
 	int perspective_correct, clip_bary, cull_back_faces;
+	// optional tables of the pixel centres in NDC, ndc_x[u] = pixel_to_ndc(u, width, height), ndc_y[v] = pixel_to_ndc(v, height, width),
+	// filled by that very function (bit-identical values): a load instead of an IEEE division per use. nullptr: computed on the fly.
+	const float* ndc_x; const float* ndc_y;
 };
+
+__device__ __forceinline__ float pixel_centre(const float* __restrict__ table, int i, int dim1, int dim2) {
+	return table ? __ldg(table + i) : pixel_to_ndc(i, dim1, dim2);
+}
 
 struct BandItem { int face, y0, y1, pad; };
 
@@ -27,7 +34,7 @@ struct PixelBox { int u0, u1, v0, v1; };  // inclusive, empty if u0 > u1 or v0 >
 
 // Exact integer range of pixels whose centres pass the reference's bounding-box test lo <= centre(i) <= hi (the same float
 // expression shade_pixel evaluates; it is monotone in i, so a float estimate corrected by stepping is exact and tight).
-__device__ __forceinline__ void pixel_range(float lo, float hi, int dim1, int dim2, int& i0, int& i1) {
+__device__ __forceinline__ void pixel_range(float lo, float hi, int dim1, int dim2, int& i0, int& i1, const float* __restrict__ table = nullptr) {
 	if (!(lo <= hi)) { i0 = 0; i1 = dim1 - 1; return; }  // NaN bounds: shade_pixel's comparisons reject nothing, walk the whole axis
 	const float range = ndc_range(dim1, dim2);
 	const float offset = range / 2.0f;
@@ -36,10 +43,10 @@ __device__ __forceinline__ void pixel_range(float lo, float hi, int dim1, int di
 	const float f1 = ((hi + offset) * (float) dim1 - offset) / range;
 	i0 = (int) ceilf(fminf(fmaxf(f0, 0.f), (float) dim1));
 	i1 = (int) floorf(fminf(fmaxf(f1, -1.f), (float) (dim1 - 1)));
-	while (i0 > 0 && pixel_to_ndc(i0 - 1, dim1, dim2) >= lo) i0--;
-	while (i0 < dim1 && pixel_to_ndc(i0, dim1, dim2) < lo) i0++;
-	while (i1 < dim1 - 1 && pixel_to_ndc(i1 + 1, dim1, dim2) <= hi) i1++;
-	while (i1 >= 0 && pixel_to_ndc(i1, dim1, dim2) > hi) i1--;
+	while (i0 > 0 && pixel_centre(table, i0 - 1, dim1, dim2) >= lo) i0--;
+	while (i0 < dim1 && pixel_centre(table, i0, dim1, dim2) < lo) i0++;
+	while (i1 < dim1 - 1 && pixel_centre(table, i1 + 1, dim1, dim2) <= hi) i1++;
+	while (i1 >= 0 && pixel_centre(table, i1, dim1, dim2) > hi) i1--;
 }
 
 __device__ __forceinline__ bool face_pixel_box(const FaceNdc& f, const RasterParams& rp, PixelBox& box) {
@@ -49,15 +56,15 @@ __device__ __forceinline__ bool face_pixel_box(const FaceNdc& f, const RasterPar
 	if (fmax3(f.z0, f.z1, f.z2) < kEps) return false;
 	const float x_min = fmin3(f.v0.x, f.v1.x, f.v2.x) - rp.blur_radius, x_max = fmax3(f.v0.x, f.v1.x, f.v2.x) + rp.blur_radius;
 	const float y_min = fmin3(f.v0.y, f.v1.y, f.v2.y) - rp.blur_radius, y_max = fmax3(f.v0.y, f.v1.y, f.v2.y) + rp.blur_radius;
-	pixel_range(x_min, x_max, rp.width, rp.height, box.u0, box.u1);
-	pixel_range(y_min, y_max, rp.height, rp.width, box.v0, box.v1);
+	pixel_range(x_min, x_max, rp.width, rp.height, box.u0, box.u1, rp.ndc_x);
+	pixel_range(y_min, y_max, rp.height, rp.width, box.v0, box.v1, rp.ndc_y);
 	return box.u0 <= box.u1 && box.v0 <= box.v1;
 }
 
 __device__ __forceinline__ void raster_pixel(const FaceNdc& f, int face, int u, int v, const RasterParams& rp,
                                              unsigned long long* __restrict__ keys, const unsigned long long* __restrict__ floor_keys,
                                              bool within_blur) {
-	const float2 pixel = make_float2(pixel_to_ndc(u, rp.width, rp.height), pixel_to_ndc(v, rp.height, rp.width));
+	const float2 pixel = make_float2(pixel_centre(rp.ndc_x, u, rp.width, rp.height), pixel_centre(rp.ndc_y, v, rp.height, rp.width));
 	Fragment frag;
 	if (!shade_pixel(f, pixel, rp.blur_radius, rp.perspective_correct != 0, rp.clip_bary != 0, rp.cull_back_faces != 0, frag, within_blur)) return;
 	const unsigned long long key = pack_key(frag.depth, face);
