@@ -103,8 +103,10 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 			}
 		}
 		float3 fv[3], fn[3];
+		float inverse_depth[3];
 		{
 			const float4 a = d.warped_positions[tri.x], b = d.warped_positions[tri.y], c = d.warped_positions[tri.z];
+			inverse_depth[0] = a.w; inverse_depth[1] = b.w; inverse_depth[2] = c.w;
 			fv[0] = make_float3(a.x, a.y, a.z); fv[1] = make_float3(b.x, b.y, b.z); fv[2] = make_float3(c.x, c.y, c.z);
 			const float4 na = d.warped_normals[tri.x], nb = d.warped_normals[tri.y], nc = d.warped_normals[tri.z];
 			fn[0] = make_float3(na.x, na.y, na.z); fn[1] = make_float3(nb.x, nb.y, nb.z); fn[2] = make_float3(nc.x, nc.y, nc.z);
@@ -112,7 +114,9 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 		const float4 ref = d.reference_points[px];
 		const float2 ray = make_float2(pixel_centre(p.ndc_x, u, p.width, p.height), pixel_centre(p.ndc_y, v, p.height, p.width));
 		FaceNdc fndc;
-		fndc.v0 = project(p.ndc, fv[0]); fndc.v1 = project(p.ndc, fv[1]); fndc.v2 = project(p.ndc, fv[2]);
+		fndc.v0 = project_with_inverse_depth(p.ndc, fv[0].x, fv[0].y, inverse_depth[0]);
+		fndc.v1 = project_with_inverse_depth(p.ndc, fv[1].x, fv[1].y, inverse_depth[1]);
+		fndc.v2 = project_with_inverse_depth(p.ndc, fv[2].x, fv[2].y, inverse_depth[2]);
 		fndc.z0 = fv[0].z; fndc.z1 = fv[1].z; fndc.z2 = fv[2].z;
 		Fragment frag;
 		shade_pixel(fndc, ray, p.blur_radius, p.perspective_correct != 0, false, true, frag, true);  // the raster pass accepted this pixel

@@ -54,16 +54,16 @@ __global__ void __launch_bounds__(256) warp_vertices_kernel(FitterDeviceData d, 
 		d.vertex_jacobians[(i * A + a) * 2] = rec0;
 		d.vertex_jacobians[(i * A + a) * 2 + 1] = rec1;
 	}
-	d.warped_positions[i] = make_float4(wp.x, wp.y, wp.z, 0.f);
+	d.warped_positions[i] = make_float4(wp.x, wp.y, wp.z, __fdiv_rn(1.0f, wp.z));  // w = 1 / z for the projections downstream
 	d.warped_normals[i] = make_float4(wn.x, wn.y, wn.z, 0.f);
 }
 
 __device__ __forceinline__ bool load_fitter_face(const FitterDeviceData& d, const NdcCamera& cam, int f, FaceNdc& out) {
 	const int4 tri = d.triangles[f];
 	const float4 a = d.warped_positions[tri.x], b = d.warped_positions[tri.y], c = d.warped_positions[tri.z];
-	out.v0 = project(cam.k, make_float3(a.x, a.y, a.z)); out.z0 = a.z;
-	out.v1 = project(cam.k, make_float3(b.x, b.y, b.z)); out.z1 = b.z;
-	out.v2 = project(cam.k, make_float3(c.x, c.y, c.z)); out.z2 = c.z;
+	out.v0 = project_with_inverse_depth(cam.k, a.x, a.y, a.w); out.z0 = a.z;
+	out.v1 = project_with_inverse_depth(cam.k, b.x, b.y, b.w); out.z1 = b.z;
+	out.v2 = project_with_inverse_depth(cam.k, c.x, c.y, c.w); out.z2 = c.z;
 	// clip mask of GetMeshNdcFaceVerticesAndClipMask(near 0, far 10): the depth test never rejects (OR of both conditions)
 	const bool in0 = out.v0.y >= cam.min_y && out.v0.x >= cam.min_x && out.v0.y <= cam.max_y && out.v0.x <= cam.max_x;
 	const bool in1 = out.v1.y >= cam.min_y && out.v1.x >= cam.min_x && out.v1.y <= cam.max_y && out.v1.x <= cam.max_x;
