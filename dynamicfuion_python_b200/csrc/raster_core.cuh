@@ -39,8 +39,9 @@ __device__ __forceinline__ void pixel_range(float lo, float hi, int dim1, int di
 	const float range = ndc_range(dim1, dim2);
 	const float offset = range / 2.0f;
 	// centre(i) = -offset + (range*i + offset)/dim1  =>  i = ((x + offset)*dim1 - offset)/range
-	const float f0 = ((lo + offset) * (float) dim1 - offset) / range;
-	const float f1 = ((hi + offset) * (float) dim1 - offset) / range;
+	// (the estimate only has to land near the answer -- the loops below step to the exact range -- so it may use the fast division)
+	const float f0 = __fdividef((lo + offset) * (float) dim1 - offset, range);
+	const float f1 = __fdividef((hi + offset) * (float) dim1 - offset, range);
 	i0 = (int) ceilf(fminf(fmaxf(f0, 0.f), (float) dim1));
 	i1 = (int) floorf(fminf(fmaxf(f1, -1.f), (float) (dim1 - 1)));
 	while (i0 > 0 && pixel_centre(table, i0 - 1, dim1, dim2) >= lo) i0--;
