@@ -22,6 +22,7 @@ _SIGNATURES = {
     "nnrt_b200_point_to_plane_distances": (C.c_int, [P, P, P, I64, P, P]),
     "nnrt_b200_warped_surface_jacobians": (C.c_int, [P, P, I64, P, P, P, P, I32, P, P, P]),
     "nnrt_b200_rasterized_surface_jacobians": (C.c_int, [P, P, P, P, P, I32, I32, I32, P, I32, P, P, P]),
+    "nnrt_b200_selfcheck_shared_divisor_quotients": (C.c_int, [P, P, I64, P, P, P]),
     "nnrt_b200_associate_faces_with_anchors": (C.c_int, [P, I64, P, I32, P, P, P]),
     "nnrt_b200_solve_block_sparse_arrowhead_cholesky": (C.c_int, [P, I32, I32, P, P, I64, P, P, I64, P, P, P]),
     "nnrt_b200_arrowhead_schur_complement": (C.c_int, [P, I32, I32, P, P, I64, P, P, I64, P, P]),

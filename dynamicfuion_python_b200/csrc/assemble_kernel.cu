@@ -133,8 +133,8 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 		const bool rendered_valid = depth > 0 && depth < p.max_depth;
 		float3 wl = make_float3(0.f, 0.f, 0.f);
 		if (rendered_valid)
-			wl = make_float3(__fdiv_rn(__fmul_rn(__fsub_rn((float) u, p.pinhole.cx), depth), p.pinhole.fx),
-			                 __fdiv_rn(__fmul_rn(__fsub_rn((float) v, p.pinhole.cy), depth), p.pinhole.fy), depth);
+			wl = make_float3(__fmul_rn(__fsub_rn((float) u, p.pinhole.cx), depth) / SharedDivisor{p.pinhole.fx, p.pinhole_inverse_fx},
+			                 __fmul_rn(__fsub_rn((float) v, p.pinhole.cy), depth) / SharedDivisor{p.pinhole.fy, p.pinhole_inverse_fy}, depth);
 		const bool mask = rendered_valid && ref.w != 0.f;
 		const float3 pm = make_float3(__fsub_rn(wl.x, ref.x), __fsub_rn(wl.y, ref.y), __fsub_rn(wl.z, ref.z));
 		const float r_raw = __fadd_rn(__fmul_rn(nl.x, pm.x), __fadd_rn(__fmul_rn(nl.y, pm.y), __fmul_rn(nl.z, pm.z)));  // dot3 = x + (y + z)
@@ -159,7 +159,8 @@ __global__ void __launch_bounds__(kAssembleThreads) assemble_kernel(FitterDevice
 		float dr_dV[9], dr_dN[9];
 		if (contributes) {
 			BaryJacobian J;
-			barycentric_jacobian(J, ray, fv, p.ndc, p.perspective_correct != 0, rho);
+			const float2 projected[3] = {fndc.v0, fndc.v1, fndc.v2};
+			barycentric_jacobian(J, ray, fv, projected, inverse_depth, p.ndc, p.perspective_correct != 0, rho);
 #pragma unroll
 			for (int c = 0; c < 9; c++) {
 				const float w0 = col_mix(fv, 0, J, c) + (c % 3 == 0 ? rho[c / 3] : 0.f);

@@ -58,6 +58,21 @@ __device__ __forceinline__ float2 project(const Intrinsics& k, float3 p) {
 __device__ __forceinline__ float2 project_with_inverse_depth(const Intrinsics& k, float x, float y, float inv_z) {
 	return make_float2(__fadd_rn(__fmul_rn(__fmul_rn(k.fx, x), inv_z), k.cx), __fadd_rn(__fmul_rn(__fmul_rn(k.fy, y), inv_z), k.cy));
 }
+// Several numerators over ONE denominator, bit for bit the IEEE quotient (a zero quotient may differ in its sign only, -0 numerator
+// over a positive divisor; nothing downstream tells the two zeros apart): r = RN(1 / d) once, then per numerator
+//   q = RN(a r),  e = a - q d (exact in one FMA),  a / d = RN(q + e r)
+// (Markstein's correction: with a correctly rounded reciprocal the corrected quotient is the correctly rounded one. It is the tail of the
+// sequence the compiler emits for every `/` -- here the reciprocal and its refinement are shared, 3 instructions per quotient instead
+// of ~10. A plain multiply by r is NOT enough: the half-ulp differences grow to 1e-3 .. 1e-2 in J^T J through the cancellations of the
+// barycentric chain, DESIGN.md "Measured and dropped".) Valid for finite non-zero d and quotients in the normal range, which is what
+// the Jacobian chain divides by (area + eps, area^2 + eps, depth, g^2 >= eps^2); checked against `/` on the device over 2^24 pairs
+// by tests/test_gpu_stages.py::test_shared_divisor_quotient_is_the_ieee_quotient.
+struct SharedDivisor { float d, r; };
+__device__ __forceinline__ SharedDivisor shared_divisor(float d) { return SharedDivisor{d, __frcp_rn(d)}; }
+__device__ __forceinline__ float operator/(float a, const SharedDivisor& s) {
+	const float q = __fmul_rn(a, s.r);
+	return __fmaf_rn(__fmaf_rn(-q, s.d, a), s.r, q);
+}
 __device__ __forceinline__ float3 rigid_transform(const Rigid& t, float3 p) {
 	return make_float3(p.x * t.e[0] + p.y * t.e[1] + p.z * t.e[2] + t.e[3], p.x * t.e[4] + p.y * t.e[5] + p.z * t.e[6] + t.e[7],
 	                   p.x * t.e[8] + p.y * t.e[9] + p.z * t.e[10] + t.e[11]);
@@ -121,15 +136,16 @@ __device__ __forceinline__ bool shade_pixel(const FaceNdc& f, float2 pixel, floa
 	const bool z_invalid = fmax3(f.z0, f.z1, f.z2) < kEps;
 	if (pixel.x > x_max || pixel.x < x_min || pixel.y > y_max || pixel.y < y_min || z_invalid) return false;
 	if ((cull_back_faces && is_back_face) || zero_area) return false;
-	const float area_eps = __fadd_rn(face_area, kEps);
-	float3 bary = make_float3(__fdiv_rn(edge_fn(pixel, f.v1, f.v2), area_eps), __fdiv_rn(edge_fn(pixel, f.v2, f.v0), area_eps),
-	                          __fdiv_rn(edge_fn(pixel, f.v0, f.v1), area_eps));
+	// (both triples of quotients share a denominator: SharedDivisor above, the IEEE quotient's bits; the face's reciprocal is
+	// loop-invariant in the callers' pixel loops)
+	const SharedDivisor area_eps = shared_divisor(__fadd_rn(face_area, kEps));
+	float3 bary = make_float3(edge_fn(pixel, f.v1, f.v2) / area_eps, edge_fn(pixel, f.v2, f.v0) / area_eps, edge_fn(pixel, f.v0, f.v1) / area_eps);
 	if (perspective_correct) {
 		const float n0 = __fmul_rn(__fmul_rn(bary.x, f.z1), f.z2);
 		const float n1 = __fmul_rn(__fmul_rn(f.z0, bary.y), f.z2);
 		const float n2 = __fmul_rn(__fmul_rn(f.z0, f.z1), bary.z);
-		const float den = fmaxf(__fadd_rn(__fadd_rn(n0, n1), n2), kEps);
-		bary = make_float3(__fdiv_rn(n0, den), __fdiv_rn(n1, den), __fdiv_rn(n2, den));
+		const SharedDivisor den = shared_divisor(fmaxf(__fadd_rn(__fadd_rn(n0, n1), n2), kEps));
+		bary = make_float3(n0 / den, n1 / den, n2 / den);
 	}
 	float3 bc = bary;
 	if (clip_bary) {

@@ -1012,7 +1012,8 @@ static IterationContext make_context(nnrt_b200_fitter* f, const double* K, const
 	c.red.block_pair_count = f->listed_pairs; c.red.block_pairs = f->block_pairs; c.red.packed = f->reduced_packed;
 	c.red.dense = f->reduced_dense; c.red.dense_rhs = f->reduced_dense_rhs; c.red.flags = f->counters;
 	c.cam = ndc_camera_from_host(K, f->H, f->W);
-	c.p.height = f->H; c.p.width = f->W; c.p.pinhole = intrinsics_from_host(K); c.p.ndc = c.cam.k; c.p.max_depth = f->opt.max_depth;
+	c.p.height = f->H; c.p.width = f->W; c.p.pinhole = intrinsics_from_host(K); c.p.pinhole_inverse_fx = 1.0f / c.p.pinhole.fx; c.p.pinhole_inverse_fy = 1.0f / c.p.pinhole.fy;
+	c.p.ndc = c.cam.k; c.p.max_depth = f->opt.max_depth;
 	c.p.perspective_correct = f->opt.use_perspective_correction; c.p.use_tukey = f->opt.use_tukey_penalty;
 	c.p.tukey_cutoff = f->opt.tukey_penalty_cutoff;
 	// RasterizeNdcTriangles(..., blur 0.5 px, ...) (DeformableMeshToImageFitter.cpp:124-127); ImageSpaceDistanceToNdc

@@ -48,6 +48,7 @@ static_assert(sizeof(FaceBandItem) == 64, "four 16-byte words per queued band");
 struct DataTermParams {
 	int height, width;
 	Intrinsics pinhole;   // camera intrinsics as given (unprojection)
+	float pinhole_inverse_fx, pinhole_inverse_fy;  // 1.0f / fx, 1.0f / fy, correctly rounded on the host (common.cuh::SharedDivisor)
 	Intrinsics ndc;       // NDC intrinsics (projection / Jacobians)
 	float max_depth;
 	int perspective_correct;

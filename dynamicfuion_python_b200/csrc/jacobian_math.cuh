@@ -11,18 +11,20 @@ namespace nnrt_b200 {
 struct BaryJacobian { float m[3][9]; };
 
 // `stored_bary` is only read when !perspective_correct (sub-areas are then recovered from the stored coordinates).
-__device__ __forceinline__ void barycentric_jacobian(BaryJacobian& J, float2 ray, const float3 v[3], const Intrinsics& ndc,
-                                                     bool perspective_correct, const float* stored_bary) {
-	float2 p[3];
-#pragma unroll
-	for (int k = 0; k < 3; k++) p[k] = project(ndc, v[k]);
+// `p` are the projections of `v` (common.cuh::project) and `inverse_depth` the correctly rounded 1 / v[k].z they were made with: a caller
+// that has already projected the face (the fused assembly: shade_pixel's face) hands them in, and the face area, the sub-areas and
+// their quotients below become common subexpressions of its own.
+__device__ __forceinline__ void barycentric_jacobian(BaryJacobian& J, float2 ray, const float3 v[3], const float2 p[3], const float inverse_depth[3],
+                                                     const Intrinsics& ndc, bool perspective_correct, const float* stored_bary) {
 	const float area = edge_fn(p[0], p[1], p[2]) + kEps;
 	const float area_sq = area * area;
+	// every denominator below is shared by several quotients: common.cuh::SharedDivisor (the IEEE quotient's bits, a third of its instructions)
+	const SharedDivisor over_area = shared_divisor(area);
 	float sub[3], distorted[3];
 	if (perspective_correct) {
 		sub[0] = edge_fn(ray, p[1], p[2]); sub[1] = edge_fn(ray, p[2], p[0]); sub[2] = edge_fn(ray, p[0], p[1]);
 #pragma unroll
-		for (int k = 0; k < 3; k++) distorted[k] = sub[k] / area;
+		for (int k = 0; k < 3; k++) distorted[k] = sub[k] / over_area;
 	} else {
 #pragma unroll
 		for (int k = 0; k < 3; k++) { distorted[k] = stored_bary[k]; sub[k] = stored_bary[k] * area; }
@@ -39,11 +41,11 @@ __device__ __forceinline__ void barycentric_jacobian(BaryJacobian& J, float2 ray
 		dS[r][a] = make_float2(p[b].y - ray.y, ray.x - p[b].x);
 		dS[r][b] = make_float2(ray.y - p[a].y, p[a].x - ray.x);
 	}
-	const float den = area_sq + kEps;
+	const SharedDivisor den = shared_divisor(area_sq + kEps);
 #pragma unroll
 	for (int i = 0; i < 3; i++) {
 		// 2x3 projection Jacobian of vertex i
-		const float z = v[i].z, z_sq = z * z;
+		const SharedDivisor z = SharedDivisor{v[i].z, inverse_depth[i]}, z_sq = shared_divisor(v[i].z * v[i].z);
 		const float px0 = ndc.fx / z, px2 = -ndc.fx * v[i].x / z_sq;
 		const float py1 = ndc.fy / z, py2 = -ndc.fy * v[i].y / z_sq;
 #pragma unroll
@@ -66,7 +68,7 @@ __device__ __forceinline__ void barycentric_jacobian(BaryJacobian& J, float2 ray
 		const float z12 = z1 * z2, z02 = z0 * z2, z01 = z0 * z1;
 		const float n0 = distorted[0] * z12, n1 = distorted[1] * z02, n2 = distorted[2] * z01;
 		const float g = fmaxf(n0 + n1 + n2, kEps);
-		const float g_sq = g * g;
+		const SharedDivisor g_sq = shared_divisor(g * g);
 		const float Dd[3][3] = {{(g - n0) * z12 / g_sq, -n0 * z02 / g_sq, -n0 * z01 / g_sq},
 		                        {-n1 * z12 / g_sq, (g - n1) * z02 / g_sq, -n1 * z01 / g_sq},
 		                        {-n2 * z12 / g_sq, -n2 * z02 / g_sq, (g - n2) * z01 / g_sq}};
@@ -87,6 +89,19 @@ __device__ __forceinline__ void barycentric_jacobian(BaryJacobian& J, float2 ray
 #pragma unroll
 			for (int i = 0; i < 3; i++) J.m[r][i * 3 + 2] += Dz[r][i];
 	}
+}
+
+// the same from the camera-space vertices alone
+__device__ __forceinline__ void barycentric_jacobian(BaryJacobian& J, float2 ray, const float3 v[3], const Intrinsics& ndc,
+                                                     bool perspective_correct, const float* stored_bary) {
+	float2 p[3];
+	float inverse_depth[3];
+#pragma unroll
+	for (int k = 0; k < 3; k++) {
+		inverse_depth[k] = __fdiv_rn(1.0f, v[k].z);
+		p[k] = project_with_inverse_depth(ndc, v[k].x, v[k].y, inverse_depth[k]);
+	}
+	barycentric_jacobian(J, ray, v, p, inverse_depth, ndc, perspective_correct, stored_bary);
 }
 
 // out[r][c] = sum_k M_k[r] * J[k][c]  where M_k are the three column vectors (face vertices or normals)

@@ -327,6 +327,26 @@ extern "C" int nnrt_b200_rasterized_surface_jacobians(const float* warped_positi
 	return kOk;
 }
 
+// device check of common.cuh::SharedDivisor: both quotients of every pair, for a bitwise comparison by the test
+__global__ void shared_divisor_quotients_kernel(const float* __restrict__ numerators, const float* __restrict__ divisors, int64_t count,
+                                                float* __restrict__ shared_quotients, float* __restrict__ ieee_quotients) {
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= count) return;
+	const float a = numerators[i], d = divisors[i];
+	shared_quotients[i] = a / shared_divisor(d);
+	ieee_quotients[i] = __fdiv_rn(a, d);
+}
+
+extern "C" int nnrt_b200_selfcheck_shared_divisor_quotients(const float* numerators, const float* divisors, int64_t count,
+                                                            float* shared_quotients, float* ieee_quotients, void* stream) {
+	NNRT_CHECK_ARG(numerators && divisors && shared_quotients && ieee_quotients, "selfcheck_shared_divisor_quotients: null pointer argument");
+	if (count == 0) return kOk;
+	shared_divisor_quotients_kernel<<<blocks_for(count, 256), 256, 0, (cudaStream_t) stream>>>(numerators, divisors, count, shared_quotients,
+	                                                                                           ieee_quotients);
+	NNRT_LAUNCH_CHECK();
+	return kOk;
+}
+
 extern "C" int nnrt_b200_associate_faces_with_anchors(const int64_t* triangles, int64_t face_count, const int32_t* vertex_anchors,
                                                       int32_t anchor_count, int32_t* face_anchor_entries, int32_t* face_anchor_counts,
                                                       void* stream) {

@@ -111,6 +111,13 @@ int nnrt_b200_rasterized_surface_jacobians(const float* warped_positions, const 
                                            int32_t perspective_correct, float* rendered_vertex_jacobians,
                                            float* rendered_normal_jacobians, void* stream);
 
+/* Self-check of the division the Jacobian chain uses (csrc/common.cuh::SharedDivisor: one reciprocal per denominator, a corrected
+ * multiply per numerator). The reference divides with `/` throughout BarycentricCoordinateJacobians.h:43-419; this entry returns, for
+ * `count` (numerator, divisor) pairs on the device, the quotient of the shared-divisor form and of the IEEE division, which the parity
+ * test compares bit for bit. */
+int nnrt_b200_selfcheck_shared_divisor_quotients(const float* numerators, const float* divisors, int64_t count, float* shared_quotients,
+                                                 float* ieee_quotients, void* stream);
+
 /* alignment::functional::AssociateFacesWithAnchors (alignment/functional/kernel/AssociateFacesWithAnchorsImpl.h:33-107).
  * Compact replacement of the 1152 B/face Blob: face_anchor_entries [F, 3*A, 2] int32 = (node index, packed slots:
  * byte k = anchor slot of face vertex k or 0xFF), in the reference's first-appearance order; face_anchor_counts [F] int32. */

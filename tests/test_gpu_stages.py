@@ -134,3 +134,32 @@ def test_jacobian_stages(nnrt, oracle):
             for fv in range(3):
                 slot = (int(e[f, k, 1]) >> (8 * fv)) & 0xFF
                 assert (slot if slot != 0xFF else -1) == fa[f, k, 4 + fv]
+
+
+def test_shared_divisor_quotient_is_the_ieee_quotient():
+    """csrc/common.cuh::SharedDivisor (the division of the barycentric Jacobian chain: one reciprocal per denominator, a corrected multiply
+    per numerator) against the device's IEEE division, BIT FOR BIT, over 2^24 pairs: half spread over twenty decades, half drawn from
+    the ranges the chain divides in (areas and squared areas of NDC triangles from 1e-8 up, depths 0.3 .. 5 m, g^2 up to z^4)."""
+    from dynamicfuion_python_b200 import _lib
+    lib = _lib.lib()
+    n = 1 << 24
+    g = torch.Generator(device="cuda").manual_seed(11)
+    def spread(lo, hi, count, signed):
+        magnitude = torch.exp(torch.empty(count, device="cuda").uniform_(float(np.log(lo)), float(np.log(hi)), generator=g))
+        magnitude = magnitude * torch.empty(count, device="cuda").uniform_(1.0, 2.0, generator=g)
+        if signed:
+            magnitude = magnitude * (torch.randint(0, 2, (count,), device="cuda", generator=g).float() * 2 - 1)
+        return magnitude
+    half = n // 2
+    numerators = torch.cat([spread(1e-10, 1e10, half, True), spread(1e-9, 1e3, half, True)])
+    divisors = torch.cat([spread(1e-10, 1e10, half, True), spread(1e-8, 7e2, half, False)])
+    numerators[:4] = torch.tensor([0.0, 1.0, -3.0, 1e-8], device="cuda")  # exact cases: zero numerator, exact quotients
+    divisors[:4] = torch.tensor([2.5, 1.0, 3.0, 1e-8], device="cuda")
+    shared, ieee = torch.empty(n, device="cuda"), torch.empty(n, device="cuda")
+    rc = lib.nnrt_b200_selfcheck_shared_divisor_quotients(numerators.data_ptr(), divisors.data_ptr(), n, shared.data_ptr(), ieee.data_ptr(),
+                                                          torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, lib.nnrt_b200_last_error()
+    torch.cuda.synchronize()
+    assert torch.equal(ieee, numerators / divisors)  # the comparison arm is the division torch (and the oracle's host code) performs
+    mismatches = int((shared.view(torch.int32) != ieee.view(torch.int32)).sum())
+    assert mismatches == 0, mismatches
